@@ -1,0 +1,216 @@
+"""ctypes binding of ``libb200phylo.so`` (the C ABI in ``include/b200phylo.h``).
+
+This is the only compute path of the package: there is no CPU fallback.  If the shared
+library is missing or no B200 is present, construction raises ``EngineError``.
+
+The role this object plays in the reference is the one ``bito``'s instance plays
+under torchtree-bito's ``TreeLikelihoodModel`` (selected with ``--engine bitorch``,
+/root/reference/modules/macro_flu.nf:119-122): set tree / tip data / model once, then
+ask for log-likelihood and branch gradients for new branch lengths.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Optional, Tuple
+
+import numpy as np
+
+__all__ = ["Engine", "EngineError", "library_path", "load_library", "EXPORTED_SYMBOLS"]
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_NAME = "libb200phylo.so"
+
+EXPORTED_SYMBOLS = (
+    "b2p_create", "b2p_destroy", "b2p_last_error", "b2p_version", "b2p_get_info",
+    "b2p_set_topology", "b2p_set_tip_states", "b2p_set_pattern_weights", "b2p_set_eigen",
+    "b2p_set_categories", "b2p_loglik", "b2p_loglik_grad", "b2p_loglik_grad_host",
+    "b2p_set_profiling", "b2p_last_kernel_ms", "b2p_get_post_partials",
+)
+
+
+class EngineError(RuntimeError):
+    pass
+
+
+class _Config(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in (
+        "n_tips", "n_patterns", "n_categories", "n_states", "precision", "device",
+        "warps_per_block", "flags")]
+
+
+class _Info(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in (
+        "n_tips", "n_patterns", "n_categories", "n_states", "precision", "warps_per_block",
+        "cols_per_tile", "n_tiles", "grid_blocks", "blocks_per_sm", "n_sms", "post_rounds",
+        "tree_depth", "regs_per_thread")] + [(n, ctypes.c_int64) for n in (
+            "device_bytes", "alg_bytes_loglik", "alg_bytes_grad")]
+
+
+def library_path() -> str:
+    return os.path.join(_HERE, _LIB_NAME)
+
+
+_lib = None
+
+
+def load_library():
+    """Load the C-ABI library and declare prototypes.  Fails loudly when it is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = library_path()
+    if not os.path.exists(path):
+        raise EngineError(
+            f"{path} not found: build it with `python -m b200phylo.build` "
+            "(nvcc, sm_100a).  There is no CPU fallback.")
+    lib = ctypes.CDLL(path)
+    vp, dp = ctypes.c_void_p, ctypes.POINTER(ctypes.c_double)
+    lib.b2p_create.argtypes = [ctypes.POINTER(_Config), ctypes.POINTER(vp)]
+    lib.b2p_destroy.argtypes = [vp]
+    lib.b2p_last_error.argtypes = [vp]
+    lib.b2p_last_error.restype = ctypes.c_char_p
+    lib.b2p_version.argtypes = []
+    lib.b2p_get_info.argtypes = [vp, ctypes.POINTER(_Info)]
+    lib.b2p_set_topology.argtypes = [vp, ctypes.POINTER(ctypes.c_int32)]
+    lib.b2p_set_tip_states.argtypes = [vp, ctypes.POINTER(ctypes.c_uint8)]
+    lib.b2p_set_pattern_weights.argtypes = [vp, dp]
+    lib.b2p_set_eigen.argtypes = [vp, dp, dp, dp, dp]
+    lib.b2p_set_categories.argtypes = [vp, dp, dp]
+    lib.b2p_loglik.argtypes = [vp, vp, vp, vp]
+    lib.b2p_loglik_grad.argtypes = [vp, vp, vp, vp, vp]
+    lib.b2p_loglik_grad_host.argtypes = [vp, dp, dp, dp]
+    lib.b2p_set_profiling.argtypes = [vp, ctypes.c_int]
+    lib.b2p_last_kernel_ms.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
+    lib.b2p_get_post_partials.argtypes = [vp, ctypes.c_int32, dp]
+    for name in EXPORTED_SYMBOLS:
+        if name != "b2p_last_error":
+            getattr(lib, name).restype = ctypes.c_int
+    _lib = lib
+    return lib
+
+
+def _dptr(a: np.ndarray):
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
+
+
+class Engine:
+    """One likelihood instance on one B200.
+
+    Parameters mirror ``b2p_config``; arrays follow ``include/b200phylo.h``:
+    ``triples`` int32 [N-1, 3] post-order, ``masks`` uint8 [N, P], ``weights`` [P].
+    """
+
+    def __init__(self, n_tips: int, n_patterns: int, n_categories: int = 1,
+                 precision: str = "float64", device: int = 0, warps_per_block: int = 0):
+        self._h = ctypes.c_void_p()
+        self._lib = load_library()
+        prec = {"float64": 64, "float32": 32, 64: 64, 32: 32}.get(precision)
+        if prec is None:
+            raise ValueError(f"precision must be float64 or float32, got {precision!r}")
+        cfg = _Config(int(n_tips), int(n_patterns), int(n_categories), 4, prec, int(device),
+                      int(warps_per_block), 0)
+        rc = self._lib.b2p_create(ctypes.byref(cfg), ctypes.byref(self._h))
+        if rc != 0:
+            msg = self._lib.b2p_last_error(None).decode()
+            self._h = ctypes.c_void_p()
+            raise EngineError(f"b2p_create failed ({rc}): {msg}")
+        self.n_tips, self.n_patterns, self.n_categories = int(n_tips), int(n_patterns), int(n_categories)
+        self.n_branches = 2 * self.n_tips - 2
+        self.precision = "float32" if prec == 32 else "float64"
+        self.device = int(device)
+
+    # ------------------------------------------------------------------ plumbing
+    def _check(self, rc: int, what: str) -> None:
+        if rc != 0:
+            raise EngineError(f"{what} failed ({rc}): {self._lib.b2p_last_error(self._h).decode()}")
+
+    def close(self) -> None:
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.b2p_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self) -> dict:
+        out = _Info()
+        self._check(self._lib.b2p_get_info(self._h, ctypes.byref(out)), "b2p_get_info")
+        return {n: int(getattr(out, n)) for n, _ in _Info._fields_}
+
+    # --------------------------------------------------------------------- setup
+    def set_topology(self, triples) -> None:
+        t = np.ascontiguousarray(triples, dtype=np.int32)
+        if t.shape != (self.n_tips - 1, 3):
+            raise ValueError(f"triples must have shape ({self.n_tips - 1}, 3), got {t.shape}")
+        self._check(self._lib.b2p_set_topology(
+            self._h, t.ctypes.data_as(ctypes.POINTER(ctypes.c_int32))), "b2p_set_topology")
+
+    def set_tip_states(self, masks) -> None:
+        m = np.ascontiguousarray(masks, dtype=np.uint8)
+        if m.shape != (self.n_tips, self.n_patterns):
+            raise ValueError(f"masks must have shape ({self.n_tips}, {self.n_patterns}), got {m.shape}")
+        self._check(self._lib.b2p_set_tip_states(
+            self._h, m.ctypes.data_as(ctypes.POINTER(ctypes.c_uint8))), "b2p_set_tip_states")
+
+    def set_pattern_weights(self, weights) -> None:
+        w = np.ascontiguousarray(weights, dtype=np.float64)
+        if w.shape != (self.n_patterns,):
+            raise ValueError(f"weights must have shape ({self.n_patterns},), got {w.shape}")
+        self._check(self._lib.b2p_set_pattern_weights(self._h, _dptr(w)), "b2p_set_pattern_weights")
+
+    def set_eigen(self, evec, ivec, evals, freqs) -> None:
+        a = [np.ascontiguousarray(x, dtype=np.float64) for x in (evec, ivec, evals, freqs)]
+        if a[0].shape != (4, 4) or a[1].shape != (4, 4) or a[2].shape != (4,) or a[3].shape != (4,):
+            raise ValueError("eigen system must be 4x4, 4x4, 4, 4")
+        self._check(self._lib.b2p_set_eigen(self._h, *map(_dptr, a)), "b2p_set_eigen")
+
+    def set_categories(self, rates, weights) -> None:
+        r = np.ascontiguousarray(rates, dtype=np.float64)
+        w = np.ascontiguousarray(weights, dtype=np.float64)
+        if r.shape != (self.n_categories,) or w.shape != (self.n_categories,):
+            raise ValueError(f"rates/weights must have shape ({self.n_categories},)")
+        self._check(self._lib.b2p_set_categories(self._h, _dptr(r), _dptr(w)), "b2p_set_categories")
+
+    def set_model(self, subst_model, site_model) -> None:
+        e = subst_model.eigen()
+        self.set_eigen(e.evec, e.ivec, e.evals, e.freqs)
+        self.set_categories(site_model.rates, site_model.weights)
+
+    # ---------------------------------------------------------------- evaluation
+    def loglik_grad_device(self, d_bl: int, d_logl: int, d_grad: Optional[int], stream: int = 0) -> None:
+        """Asynchronous evaluation on raw device pointers (e.g. ``tensor.data_ptr()``)."""
+        if d_grad is None:
+            self._check(self._lib.b2p_loglik(self._h, d_bl, d_logl, stream), "b2p_loglik")
+        else:
+            self._check(self._lib.b2p_loglik_grad(self._h, d_bl, d_logl, d_grad, stream),
+                        "b2p_loglik_grad")
+
+    def loglik_grad_host(self, branch_lengths, want_grad: bool = True) -> Tuple[float, Optional[np.ndarray]]:
+        """Host buffers in, host results out (H2D + kernels + D2H + sync inside)."""
+        bl = np.ascontiguousarray(branch_lengths, dtype=np.float64)
+        if bl.shape != (self.n_branches,):
+            raise ValueError(f"branch_lengths must have shape ({self.n_branches},), got {bl.shape}")
+        logl = ctypes.c_double()
+        grad = np.empty(self.n_branches) if want_grad else None
+        self._check(self._lib.b2p_loglik_grad_host(
+            self._h, _dptr(bl), ctypes.byref(logl), _dptr(grad) if want_grad else None),
+            "b2p_loglik_grad_host")
+        return float(logl.value), grad
+
+    def set_profiling(self, enabled: bool) -> None:
+        self._check(self._lib.b2p_set_profiling(self._h, int(bool(enabled))), "b2p_set_profiling")
+
+    def last_kernel_ms(self) -> float:
+        ms = ctypes.c_float()
+        self._check(self._lib.b2p_last_kernel_ms(self._h, ctypes.byref(ms)), "b2p_last_kernel_ms")
+        return float(ms.value)
+
+    def post_partials(self, node: int) -> np.ndarray:
+        out = np.empty((self.n_patterns, self.n_categories, 4))
+        self._check(self._lib.b2p_get_post_partials(self._h, int(node), _dptr(out)),
+                    "b2p_get_post_partials")
+        return out

@@ -1,0 +1,109 @@
+// Device-side helpers for the 4-state traversal kernels (sm_100a only).
+//
+// Data layout in HBM:
+//   partials  [internal node][column][state]   column = pattern * K + category
+//   one column of one node = 4 states = 32 B (fp64) / 16 B (fp32) = one 256-bit or
+//   128-bit access per thread, so a warp moves 1 KB / 512 B contiguous per node.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b2p {
+
+// Lazy power-of-two rescaling thresholds (exact in binary floating point).
+template <typename T> struct Scale;
+template <> struct Scale<double> {
+  static __device__ __forceinline__ double threshold() { return 6.223015277861142e-61; }  // 2^-200
+  static __device__ __forceinline__ double factor() { return 1.6069380442589903e+60; }    // 2^+200
+  static __device__ __forceinline__ double log_factor() { return 138.62943611198907; }    // 200 ln 2
+};
+template <> struct Scale<float> {
+  static __device__ __forceinline__ float threshold() { return 9.094947017729282e-13f; }  // 2^-40
+  static __device__ __forceinline__ float factor() { return 1099511627776.0f; }           // 2^+40
+  static __device__ __forceinline__ double log_factor() { return 27.725887222397812; }    // 40 ln 2
+};
+
+// ---- one column (4 states) global load / store --------------------------------
+// Partials are written and re-read inside one launch, so these are coherent
+// (non-.nc) accesses.  fp64 uses the sm_100 256-bit LDG/STG.
+__device__ __forceinline__ void ld_col(const double* p, double (&x)[4]) {
+  asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];"
+               : "=d"(x[0]), "=d"(x[1]), "=d"(x[2]), "=d"(x[3])
+               : "l"(p)
+               : "memory");
+}
+__device__ __forceinline__ void st_col(double* p, const double (&x)[4]) {
+  asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(x[0]), "d"(x[1]),
+               "d"(x[2]), "d"(x[3])
+               : "memory");
+}
+__device__ __forceinline__ void ld_col(const float* p, float (&x)[4]) {
+  asm volatile("ld.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(x[0]), "=f"(x[1]), "=f"(x[2]), "=f"(x[3])
+               : "l"(p)
+               : "memory");
+}
+__device__ __forceinline__ void st_col(float* p, const float (&x)[4]) {
+  asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(x[0]), "f"(x[1]),
+               "f"(x[2]), "f"(x[3])
+               : "memory");
+}
+
+template <typename T>
+__device__ __forceinline__ void tip_col(uint8_t m, T (&x)[4]) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) x[j] = (T)((m >> j) & 1);
+}
+
+// ---- reductions over the K category lanes of one pattern -----------------------
+// Lanes of a pattern are adjacent and K-aligned (tile origin is a multiple of K).
+template <int K, typename T>
+__device__ __forceinline__ T group_sum(T v, int lane, int kk) {
+  if (K == 1) return v;
+  if (K == 2 || K == 4 || K == 8 || K == 16 || K == 32) {
+#pragma unroll
+    for (int o = 1; o < K; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+  }
+  // generic K (runtime kk): gather from the group's lanes
+  const int base = lane - lane % kk;
+  T s = (T)0;
+  for (int j = 0; j < kk; ++j) s += __shfl_sync(0xffffffffu, v, (base + j) & 31);
+  return s;
+}
+template <int K, typename T>
+__device__ __forceinline__ T group_max(T v, int lane, int kk) {
+  if (K == 1) return v;
+  if (K == 2 || K == 4 || K == 8 || K == 16 || K == 32) {
+#pragma unroll
+    for (int o = 1; o < K; o <<= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+  }
+  const int base = lane - lane % kk;
+  T s = v;
+  for (int j = 0; j < kk; ++j) s = fmax(s, __shfl_sync(0xffffffffu, v, (base + j) & 31));
+  return s;
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// y = M x with M row-major 4x4 in shared memory (broadcast / conflict-free reads)
+template <typename T>
+__device__ __forceinline__ void matvec(const T* __restrict__ m, const T (&x)[4], T (&y)[4]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    y[i] = m[4 * i] * x[0] + m[4 * i + 1] * x[1] + m[4 * i + 2] * x[2] + m[4 * i + 3] * x[3];
+}
+// y = M^T x
+template <typename T>
+__device__ __forceinline__ void matvec_t(const T* __restrict__ m, const T (&x)[4], T (&y)[4]) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    y[j] = m[j] * x[0] + m[4 + j] * x[1] + m[8 + j] * x[2] + m[12 + j] * x[3];
+}
+
+}  // namespace b2p

@@ -1,0 +1,144 @@
+/*
+ * b200phylo.h — C ABI of libb200phylo.so: tree log-likelihood + branch-length gradient
+ * on one NVIDIA B200 (sm_100a).  Plain pointers and sizes only; no C++/torch types.
+ *
+ * What this boundary replaces.  /root/reference holds no likelihood code: its
+ * contenders reach a native engine through (i) BEAGLE's C API as driven by bito /
+ * torchtree-bito (selected with `--engine bitorch`, /root/reference/modules/macro_flu.nf:119-122,
+ * and by `bitorch-benchmark`, /root/reference/modules/micro.nf:8,47-53) and (ii)
+ * physher's treelikelihood (`physher-benchmark`, /root/reference/modules/micro.nf:20-24).
+ * Each entry point below names the BEAGLE-style call an integrator would otherwise
+ * bind (upstream recall, not verifiable on this box — SURVEY.md §2.1) and the
+ * reference JSON / CLI element that feeds it.
+ *
+ * Conventions
+ *   - every function returns B2P_OK (0) or a negative error code; never throws;
+ *     b2p_last_error() returns the message for the last failure on that instance
+ *     (pass NULL for failures of b2p_create itself).
+ *   - node ids: tips 0..N-1, internal nodes N..2N-2 in post-order, root = 2N-2;
+ *     a branch is named by its child node id, so branch arrays have length 2N-2.
+ *   - pointers called h_* are host memory, d_* are device memory on the instance's
+ *     device.  The instance owns all scratch (partials, matrices, schedules); the
+ *     caller owns every buffer it passes in.  Setup calls (b2p_set_*) copy from host
+ *     and synchronise; evaluation calls with a stream are asynchronous on that stream
+ *     and perform no hidden synchronisation.
+ *   - one instance = one device; an instance is not thread-safe; instances are
+ *     independent.  There is no CPU fallback: creation fails without a CUDA device.
+ */
+#ifndef B200PHYLO_H
+#define B200PHYLO_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2P_OK 0
+#define B2P_ERR_ARG (-1)       /* bad argument / call order */
+#define B2P_ERR_CUDA (-2)      /* CUDA runtime error (message has the cudaError string) */
+#define B2P_ERR_ALLOC (-3)     /* host or device allocation failed */
+#define B2P_ERR_UNSUPPORTED (-4)
+
+#define B2P_PRECISION_F64 64
+#define B2P_PRECISION_F32 32
+
+typedef struct b2p_instance b2p_instance;
+
+typedef struct b2p_config {
+  int32_t n_tips;       /* N >= 2 */
+  int32_t n_patterns;   /* P >= 1 (this rank's slice when sharded) */
+  int32_t n_categories; /* K >= 1 rate categories, K <= 32 */
+  int32_t n_states;     /* 4 (nucleotide); other sizes: B2P_ERR_UNSUPPORTED */
+  int32_t precision;    /* B2P_PRECISION_F64 | B2P_PRECISION_F32 (partials / matrices) */
+  int32_t device;       /* CUDA device ordinal */
+  int32_t warps_per_block; /* 0 = auto; schedule width W (nodes in flight per tile) */
+  int32_t flags;        /* reserved, 0 */
+} b2p_config;
+
+typedef struct b2p_info {
+  int32_t n_tips, n_patterns, n_categories, n_states, precision;
+  int32_t warps_per_block;  /* W */
+  int32_t cols_per_tile;    /* (pattern,category) columns one warp carries */
+  int32_t n_tiles;          /* column tiles = independent traversals */
+  int32_t grid_blocks;      /* persistent CTAs launched */
+  int32_t blocks_per_sm;    /* residency the launch was sized for */
+  int32_t n_sms;
+  int32_t post_rounds;      /* schedule length of one pass (pre-order is its reverse) */
+  int32_t tree_depth;       /* longest root-to-cherry path, in internal nodes */
+  int32_t regs_per_thread;  /* of the traversal kernel in use */
+  int64_t device_bytes;     /* scratch owned by the instance */
+  int64_t alg_bytes_loglik; /* (2N-3)U + N*P */
+  int64_t alg_bytes_grad;   /* (5N-9)U + 2*N*P */
+} b2p_info;
+
+/* BEAGLE: beagleCreateInstance / beagleFinalizeInstance. */
+int b2p_create(const b2p_config* cfg, b2p_instance** out);
+int b2p_destroy(b2p_instance* h);
+const char* b2p_last_error(const b2p_instance* h);
+int b2p_version(void);
+int b2p_get_info(const b2p_instance* h, b2p_info* out);
+
+/* Tree topology: h_triples int32 [N-1][3] rows (node, left, right) in post-order.
+ * Fed by "tree_model" (/root/reference/flu_H3N2/phylotorch-JC69.template:14-44) and
+ * `-t <newick>` (/root/reference/modules/micro.nf:20,47).  BEAGLE: the operations
+ * array of beagleUpdatePartials / beagleUpdatePrePartials.  Builds the level-free
+ * list schedule used by both passes. */
+int b2p_set_topology(b2p_instance* h, const int32_t* h_triples);
+
+/* Tip data: h_masks uint8 [N][P], bit i set = state i compatible (A=1,C=2,G=4,T=8;
+ * gap/N = 15).  Fed by "site_pattern" (/root/reference/flu_H3N2/phylotorch-JC69.template:59-69,
+ * /root/reference/flu_H3N2/physher-JC69.template:11-21).  BEAGLE: beagleSetTipStates /
+ * beagleSetTipPartials. */
+int b2p_set_tip_states(b2p_instance* h, const uint8_t* h_masks);
+
+/* Pattern weights: h_weights double [P].  BEAGLE: beagleSetPatternWeights. */
+int b2p_set_pattern_weights(b2p_instance* h, const double* h_weights);
+
+/* Substitution model as an eigen system Q = V diag(lambda) V^-1, row-major [S][S],
+ * plus stationary frequencies [S].  Fed by "substitution_model"
+ * (/root/reference/flu_H3N2/phylotorch-JC69.template:70-73) and `--gtr`
+ * (/root/reference/modules/micro.nf:52).  BEAGLE: beagleSetEigenDecomposition +
+ * beagleSetStateFrequencies. */
+int b2p_set_eigen(b2p_instance* h, const double* h_evec, const double* h_ivec,
+                  const double* h_evals, const double* h_freqs);
+
+/* Rate categories: h_rates, h_weights double [K].  Fed by "site_model"
+ * (/root/reference/flu_H3N2/phylotorch-JC69.template:45-48).  BEAGLE:
+ * beagleSetCategoryRates + beagleSetCategoryWeights. */
+int b2p_set_categories(b2p_instance* h, const double* h_rates, const double* h_weights);
+
+/* Log-likelihood only.  d_bl: device double [2N-2] branch lengths (substitutions per
+ * site, by child node id); d_logl: device double [1].  BEAGLE:
+ * beagleUpdateTransitionMatrices + beagleUpdatePartials + beagleCalculateRootLogLikelihoods.
+ * Times the "evaluation" rows of the micro CSV (/root/reference/plot.Rmd:353). */
+int b2p_loglik(b2p_instance* h, const double* d_bl, double* d_logl, void* cuda_stream);
+
+/* Log-likelihood and d logL / d branch length for all 2N-2 branches.  d_grad: device
+ * double [2N-2].  BEAGLE: the above + beagleUpdatePrePartials +
+ * beagleCalculateEdgeDerivatives (bito phylo_gradients).  Times the "gradient" rows
+ * (/root/reference/plot.Rmd:362). */
+int b2p_loglik_grad(b2p_instance* h, const double* d_bl, double* d_logl, double* d_grad,
+                    void* cuda_stream);
+
+/* Host-buffer form of b2p_loglik_grad: copies h_bl in, runs, copies logL and the
+ * gradient out and synchronises.  h_grad may be NULL (log-likelihood only).  This is
+ * the call a ctypes / cgo / pybind integrator with CPU-resident parameters makes. */
+int b2p_loglik_grad_host(b2p_instance* h, const double* h_bl, double* h_logl,
+                         double* h_grad);
+
+/* Kernel timing for roofline reports: when enabled, the traversal kernel of every
+ * evaluation is bracketed by CUDA events on the evaluation's stream;
+ * b2p_last_kernel_ms synchronises on the last pair and returns its duration. */
+int b2p_set_profiling(b2p_instance* h, int enabled);
+int b2p_last_kernel_ms(b2p_instance* h, float* ms_out);
+
+/* Debug / test access: copy the post-order partials of internal node `node` as
+ * double [P][K][S] (converted from the working precision) into h_out. */
+int b2p_get_post_partials(b2p_instance* h, int32_t node, double* h_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PHYLO_H */
