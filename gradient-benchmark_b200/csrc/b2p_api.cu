@@ -19,7 +19,7 @@ static thread_local std::string g_create_error;
 struct b2p_instance {
   b2p_config cfg{};
   int n_sms = 0;
-  int W = 0, cols_per_tile = 0, n_tiles = 0, grid = 0, blocks_per_sm = 0;
+  int W = 0, D = 2, cols_per_tile = 0, n_tiles = 0, grid = 0, blocks_per_sm = 0;
   int n_rounds = 0, tree_depth = 0, regs = 0;
   size_t smem_bytes = 0;
   bool have_topology = false, have_tips = false, have_weights = false, have_eigen = false,
@@ -78,33 +78,36 @@ static int dev_alloc(b2p_instance* h, T** p, size_t n_bytes) {
 }
 
 // ---------------------------------------------------------------- kernel selection
-template <typename T, int K, int W, int MINB>
+template <typename T, int K, int W, int MINB, int D>
 static void pick(const void** grad, const void** eval) {
-  *grad = (const void*)traverse_kernel<T, K, W, true, MINB>;
-  *eval = (const void*)traverse_kernel<T, K, W, false, MINB>;
+  *grad = (const void*)traverse_kernel<T, K, W, true, MINB, D>;
+  *eval = (const void*)traverse_kernel<T, K, W, false, MINB, D>;
 }
-template <typename T>
-static bool select_kernels(int K, int W, const void** grad, const void** eval) {
+template <typename T, int D>
+static bool select_kernels_d(int K, int W, const void** grad, const void** eval) {
   if (W == 8) {
-    if (K == 1) pick<T, 1, 8, 3>(grad, eval);
-    else if (K == 4) pick<T, 4, 8, 3>(grad, eval);
-    else pick<T, 0, 8, 2>(grad, eval);
+    if (K == 1) pick<T, 1, 8, 3, D>(grad, eval);
+    else if (K == 4) pick<T, 4, 8, 3, D>(grad, eval);
+    else pick<T, 0, 8, 2, D>(grad, eval);
     return true;
   }
   if (W == 16) {
-    if (K == 1) pick<T, 1, 16, 2>(grad, eval);
-    else if (K == 4) pick<T, 4, 16, 2>(grad, eval);
-    else pick<T, 0, 16, 1>(grad, eval);
+    if (K == 1) pick<T, 1, 16, 2, D>(grad, eval);
+    else if (K == 4) pick<T, 4, 16, 2, D>(grad, eval);
+    else pick<T, 0, 16, 1, D>(grad, eval);
     return true;
   }
+  return false;
+}
+template <typename T>
+static bool select_kernels(int K, int W, int D, const void** grad, const void** eval) {
+  if (D == 2) return select_kernels_d<T, 2>(K, W, grad, eval);
+  if (D == 3) return select_kernels_d<T, 3>(K, W, grad, eval);
   return false;
 }
 
 static size_t elem_size(const b2p_instance* h) {
   return h->cfg.precision == B2P_PRECISION_F32 ? 4 : 8;
-}
-static int mat_stride(const b2p_instance* h) {
-  return h->cfg.precision == B2P_PRECISION_F32 ? MatStride<float>::v : MatStride<double>::v;
 }
 
 extern "C" {
@@ -170,10 +173,17 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   }
   h->n_tiles = (int)((n_cols + h->cols_per_tile - 1) / h->cols_per_tile);
 
-  bool ok = (cfg->precision == B2P_PRECISION_F32) ? select_kernels<float>(K, W, &h->k_grad, &h->k_eval)
-                                                  : select_kernels<double>(K, W, &h->k_grad, &h->k_eval);
-  if (!ok) { delete h; return fail(nullptr, B2P_ERR_ARG, "b2p_create: no kernel for W=%d", W); }
-  h->smem_bytes = (size_t)W * 4 * K * mat_stride(h) * es;
+  int D = 2;
+  if (const char* s = getenv("B2P_STAGES")) D = atoi(s);
+  h->D = D;
+  bool ok = (cfg->precision == B2P_PRECISION_F32) ? select_kernels<float>(K, W, D, &h->k_grad, &h->k_eval)
+                                                  : select_kernels<double>(K, W, D, &h->k_grad, &h->k_eval);
+  if (!ok) { delete h; return fail(nullptr, B2P_ERR_ARG, "b2p_create: no kernel for W=%d stages=%d", W, D); }
+  h->smem_bytes = (size_t)W * D * (cfg->precision == B2P_PRECISION_F32 ? stage_bytes<float>(K) : stage_bytes<double>(K));
+  if (h->smem_bytes > 227 * 1024) {
+    delete h;
+    return fail(nullptr, B2P_ERR_UNSUPPORTED, "b2p_create: K=%d needs %zu bytes of shared memory per CTA", K, h->smem_bytes);
+  }
 
   int rc = B2P_OK;
   auto bail = [&](int code) { std::string m = h->err; b2p_destroy(h); g_create_error = m; return code; };
@@ -248,7 +258,7 @@ int b2p_destroy(b2p_instance* h) {
 // Unit tasks (one per internal node) with in-tree precedence on W identical slots:
 // Hu's highest-level-first rule is makespan-optimal.  Level = distance from the root.
 // The pre-order pass runs the same rounds in reverse (optimal for the out-tree).
-static int build_schedule(int N, const int32_t* triples, int W, std::vector<int4>& sched,
+static int build_schedule(int N, const int32_t* triples, int W, int D, std::vector<int4>& sched,
                           int* depth_out, std::string& why) {
   const int n_nodes = 2 * N - 1, root = 2 * N - 2;
   std::vector<int> left(n_nodes, -1), right(n_nodes, -1), parent(n_nodes, -1);
@@ -300,7 +310,25 @@ static int build_schedule(int N, const int32_t* triples, int W, std::vector<int4
       if (v != root && --pending[parent[v]] == 0) ready.push({depth[parent[v]], -parent[v]});
     }
   }
-  return (int)(sched.size() / W);
+  // Prefetch distances (in rounds) for the asynchronous operand pipeline: how many rounds
+  // before its own a task's inputs are final.  Post-order: after both internal children;
+  // pre-order (rounds run in reverse): after the parent.
+  const int R = (int)(sched.size() / W);
+  std::vector<int> round_of(n_nodes, -1);
+  for (int i = 0; i < (int)sched.size(); ++i)
+    if (sched[i].x >= 0) round_of[sched[i].x] = i / W;
+  for (int4& e : sched) {
+    if (e.x < 0) continue;
+    const int r = round_of[e.x];
+    int last_child = -1;
+    if (e.y >= N) last_child = std::max(last_child, round_of[e.y]);
+    if (e.z >= N) last_child = std::max(last_child, round_of[e.z]);
+    const int d_post = std::max(0, std::min(D - 1, r - 1 - last_child));
+    int d_pre = 0;
+    if (e.x != root) d_pre = std::max(0, std::min(D - 1, round_of[parent[e.x]] - r - 1));
+    e.w = d_post | (d_pre << 2);
+  }
+  return R;
 }
 
 template <typename T>
@@ -369,7 +397,7 @@ int b2p_set_topology(b2p_instance* h, const int32_t* h_triples) {
   std::vector<int4> sched;
   std::string why;
   int depth = 0;
-  const int rounds = build_schedule(h->cfg.n_tips, h_triples, h->W, sched, &depth, why);
+  const int rounds = build_schedule(h->cfg.n_tips, h_triples, h->W, h->D, sched, &depth, why);
   if (rounds < 0) return fail(h, B2P_ERR_ARG, "b2p_set_topology: %s", why.c_str());
   CU(cudaSetDevice(h->cfg.device));
   CU(cudaMemcpy(h->d_sched, sched.data(), sched.size() * sizeof(int4), cudaMemcpyHostToDevice));

@@ -49,6 +49,37 @@ __device__ __forceinline__ void st_col(float* p, const float (&x)[4]) {
                : "memory");
 }
 
+
+// ---- Ampere-style async copies (LDGSTS): global -> shared without registers -------
+// .cg = cache at L2 only, so a column written by another warp of this CTA earlier in
+// the launch is always read coherently.
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// One column staged in shared memory.  fp64: two 16 B halves in separate 512 B planes
+// (conflict-free LDS.128); fp32: one 16 B unit.
+__device__ __forceinline__ void lds_col(const unsigned char* op, int lane, double (&x)[4]) {
+  const double2 a = *reinterpret_cast<const double2*>(op + lane * 16);
+  const double2 b = *reinterpret_cast<const double2*>(op + 512 + lane * 16);
+  x[0] = a.x; x[1] = a.y; x[2] = b.x; x[3] = b.y;
+}
+__device__ __forceinline__ void lds_col(const unsigned char* op, int lane, float (&x)[4]) {
+  const float4 a = *reinterpret_cast<const float4*>(op + lane * 16);
+  x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w;
+}
+__device__ __forceinline__ void cp_col(unsigned char* op, int lane, const double* g) {
+  cp_async16(op + lane * 16, g);
+  cp_async16(op + 512 + lane * 16, g + 2);
+}
+__device__ __forceinline__ void cp_col(unsigned char* op, int lane, const float* g) {
+  cp_async16(op + lane * 16, g);
+}
+
 template <typename T>
 __device__ __forceinline__ void tip_col(uint8_t m, T (&x)[4]) {
 #pragma unroll
