@@ -19,17 +19,16 @@ static thread_local std::string g_create_error;
 struct b2p_instance {
   b2p_config cfg{};
   int n_sms = 0;
-  int W = 0, D = 2, cols_per_tile = 0, n_tiles = 0, grid = 0, blocks_per_sm = 0;
+  int W = 0, D = 2, NC = 1, cols_per_tile = 0, n_tiles = 0, grid = 0, blocks_per_sm = 0;
   int n_rounds = 0, tree_depth = 0, regs = 0;
   size_t smem_bytes = 0;
   bool have_topology = false, have_tips = false, have_weights = false, have_eigen = false,
        have_cats = false;
   // device scratch
-  int4* d_sched = nullptr;
+  SchedEntry* d_sched = nullptr;
   uint8_t* d_tips = nullptr;
   double* d_weights = nullptr;
   void* d_pmat = nullptr;
-  void* d_dpmat = nullptr;
   void* d_post = nullptr;
   void* d_pre = nullptr;
   double* d_lpart = nullptr;
@@ -44,6 +43,7 @@ struct b2p_instance {
   int64_t device_bytes = 0;
   ModelParams model{};
   double freqs[4]{};
+  double qmat[16]{};
   double cat_w[kMaxCat]{};
   const void* k_grad = nullptr;  // selected traversal kernels
   const void* k_eval = nullptr;
@@ -78,31 +78,26 @@ static int dev_alloc(b2p_instance* h, T** p, size_t n_bytes) {
 }
 
 // ---------------------------------------------------------------- kernel selection
-template <typename T, int K, int W, int MINB, int D>
+// (W warps, NC columns per lane, min CTAs/SM) variants; D = 2 pipeline stages.
+template <typename T, int K, int W, int NC, int MINB>
 static void pick(const void** grad, const void** eval) {
-  *grad = (const void*)traverse_kernel<T, K, W, true, MINB, D>;
-  *eval = (const void*)traverse_kernel<T, K, W, false, MINB, D>;
+  *grad = (const void*)traverse_kernel<T, K, W, NC, true, MINB, 2>;
+  *eval = (const void*)traverse_kernel<T, K, W, NC, false, MINB, 2>;
 }
-template <typename T, int D>
-static bool select_kernels_d(int K, int W, const void** grad, const void** eval) {
-  if (W == 8) {
-    if (K == 1) pick<T, 1, 8, 3, D>(grad, eval);
-    else if (K == 4) pick<T, 4, 8, 3, D>(grad, eval);
-    else pick<T, 0, 8, 2, D>(grad, eval);
-    return true;
-  }
-  if (W == 16) {
-    if (K == 1) pick<T, 1, 16, 2, D>(grad, eval);
-    else if (K == 4) pick<T, 4, 16, 2, D>(grad, eval);
-    else pick<T, 0, 16, 1, D>(grad, eval);
-    return true;
-  }
-  return false;
+template <typename T, int K>
+static bool select_k(int W, int NC, const void** grad, const void** eval) {
+  if (W == 8 && NC == 1) pick<T, K, 8, 1, 3>(grad, eval);
+  else if (W == 8 && NC == 2) pick<T, K, 8, 2, 2>(grad, eval);
+  else if (W == 16 && NC == 1) pick<T, K, 16, 1, 2>(grad, eval);
+  else if (W == 16 && NC == 2) pick<T, K, 16, 2, 1>(grad, eval);
+  else return false;
+  return true;
 }
 template <typename T>
-static bool select_kernels(int K, int W, int D, const void** grad, const void** eval) {
-  if (D == 2) return select_kernels_d<T, 2>(K, W, grad, eval);
-  if (D == 3) return select_kernels_d<T, 3>(K, W, grad, eval);
+static bool select_kernels(int K, int W, int NC, const void** grad, const void** eval) {
+  if (K == 1) return select_k<T, 1>(W, NC, grad, eval);
+  if (K == 4) return select_k<T, 4>(W, NC, grad, eval);
+  if (W == 8 && NC == 1) { pick<T, 0, 8, 1, 2>(grad, eval); return true; }
   return false;
 }
 
@@ -156,30 +151,28 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   const size_t es = elem_size(h);
   const size_t n_cols = (size_t)P * K;
 
-  // schedule width
-  int W = cfg->warps_per_block;
+  // launch shape: W warps (= schedule width), NC columns per lane.  Defaults: two
+  // columns per lane once that still yields at least one tile per SM.
+  const bool generic_k = !(K == 1 || K == 4);
+  const int cpw = (32 / K) * K;
+  int W = cfg->warps_per_block, NC = 0;
   if (const char* s = getenv("B2P_WARPS")) W = atoi(s);
+  if (const char* s = getenv("B2P_NC")) NC = atoi(s);
   if (W == 0) W = 8;
-  if (K > 8) W = 8;
-  if (W != 8 && W != 16) {
-    delete h;
-    return fail(nullptr, B2P_ERR_ARG, "b2p_create: warps_per_block must be 0, 8 or 16");
-  }
-  h->W = W;
-  h->cols_per_tile = (32 / K) * K;
+  if (NC == 0) NC = ((n_cols + 2 * cpw - 1) / (2 * cpw) >= (size_t)h->n_sms) ? 2 : 1;
+  if (generic_k) { W = 8; NC = 1; }
+  h->W = W; h->NC = NC; h->D = 2;
+  h->cols_per_tile = NC * cpw;
   if (const char* s = getenv("B2P_COLS_PER_TILE")) {
     int c = atoi(s);
-    if (c >= K && c <= 32 && c % K == 0) h->cols_per_tile = c;
+    if (c >= K && c <= NC * cpw && c % K == 0) h->cols_per_tile = c;
   }
   h->n_tiles = (int)((n_cols + h->cols_per_tile - 1) / h->cols_per_tile);
-
-  int D = 2;
-  if (const char* s = getenv("B2P_STAGES")) D = atoi(s);
-  h->D = D;
-  bool ok = (cfg->precision == B2P_PRECISION_F32) ? select_kernels<float>(K, W, D, &h->k_grad, &h->k_eval)
-                                                  : select_kernels<double>(K, W, D, &h->k_grad, &h->k_eval);
-  if (!ok) { delete h; return fail(nullptr, B2P_ERR_ARG, "b2p_create: no kernel for W=%d stages=%d", W, D); }
-  h->smem_bytes = (size_t)W * D * (cfg->precision == B2P_PRECISION_F32 ? stage_bytes<float>(K) : stage_bytes<double>(K));
+  bool ok = (cfg->precision == B2P_PRECISION_F32) ? select_kernels<float>(K, W, NC, &h->k_grad, &h->k_eval)
+                                                  : select_kernels<double>(K, W, NC, &h->k_grad, &h->k_eval);
+  if (!ok) { delete h; return fail(nullptr, B2P_ERR_ARG, "b2p_create: no kernel for W=%d NC=%d K=%d", W, NC, K); }
+  h->smem_bytes = (size_t)W * (cfg->precision == B2P_PRECISION_F32 ? warp_smem_bytes<float>(K, NC, 2)
+                                                                    : warp_smem_bytes<double>(K, NC, 2));
   if (h->smem_bytes > 227 * 1024) {
     delete h;
     return fail(nullptr, B2P_ERR_UNSUPPORTED, "b2p_create: K=%d needs %zu bytes of shared memory per CTA", K, h->smem_bytes);
@@ -212,11 +205,10 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   h->grid = std::min(h->n_tiles, bps * h->n_sms);
 
   const size_t n_br = 2 * (size_t)N - 2;
-  if ((rc = dev_alloc(h, &h->d_sched, sizeof(int4) * (size_t)(N - 1) * W))) return bail(rc);
+  if ((rc = dev_alloc(h, &h->d_sched, sizeof(SchedEntry) * (size_t)(N - 1) * W))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_tips, (size_t)N * P))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_weights, sizeof(double) * P))) return bail(rc);
   if ((rc = dev_alloc(h, (char**)&h->d_pmat, n_br * K * 16 * es))) return bail(rc);
-  if ((rc = dev_alloc(h, (char**)&h->d_dpmat, n_br * K * 16 * es))) return bail(rc);
   if ((rc = dev_alloc(h, (char**)&h->d_post, (size_t)(N - 1) * n_cols * 4 * es))) return bail(rc);
   if ((rc = dev_alloc(h, (char**)&h->d_pre, (size_t)(N - 1) * n_cols * 4 * es))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_lpart, sizeof(double) * h->grid))) return bail(rc);
@@ -240,8 +232,7 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
 int b2p_destroy(b2p_instance* h) {
   if (!h) return B2P_OK;
   cudaSetDevice(h->cfg.device);
-  cudaFree(h->d_sched); cudaFree(h->d_tips); cudaFree(h->d_weights); cudaFree(h->d_pmat);
-  cudaFree(h->d_dpmat); cudaFree(h->d_post); cudaFree(h->d_pre); cudaFree(h->d_lpart);
+  cudaFree(h->d_sched); cudaFree(h->d_tips); cudaFree(h->d_weights); cudaFree(h->d_pmat); cudaFree(h->d_post); cudaFree(h->d_pre); cudaFree(h->d_lpart);
   cudaFree(h->d_gpart); cudaFree(h->d_bl_stage); cudaFree(h->d_out_stage);
   if (h->h_pin_in) cudaFreeHost(h->h_pin_in);
   if (h->h_pin_out) cudaFreeHost(h->h_pin_out);
@@ -258,7 +249,7 @@ int b2p_destroy(b2p_instance* h) {
 // Unit tasks (one per internal node) with in-tree precedence on W identical slots:
 // Hu's highest-level-first rule is makespan-optimal.  Level = distance from the root.
 // The pre-order pass runs the same rounds in reverse (optimal for the out-tree).
-static int build_schedule(int N, const int32_t* triples, int W, int D, std::vector<int4>& sched,
+static int build_schedule(int N, int P, int K, const int32_t* triples, int W, int D, std::vector<SchedEntry>& sched,
                           int* depth_out, std::string& why) {
   const int n_nodes = 2 * N - 1, root = 2 * N - 2;
   std::vector<int> left(n_nodes, -1), right(n_nodes, -1), parent(n_nodes, -1);
@@ -300,9 +291,9 @@ static int build_schedule(int N, const int32_t* triples, int W, int D, std::vect
     for (int s = 0; s < W; ++s) {
       if (s < (int)round_nodes.size()) {
         const int v = round_nodes[s];
-        sched.push_back(make_int4(v, left[v], right[v], 0));
+        sched.push_back(SchedEntry{v, left[v], right[v], 0, 0u, 0u, 0u, 0u});
       } else {
-        sched.push_back(make_int4(-1, -1, -1, 0));
+        sched.push_back(SchedEntry{-1, -1, -1, 0, 0u, 0u, 0u, 0u});
       }
     }
     for (int v : round_nodes) {
@@ -316,17 +307,22 @@ static int build_schedule(int N, const int32_t* triples, int W, int D, std::vect
   const int R = (int)(sched.size() / W);
   std::vector<int> round_of(n_nodes, -1);
   for (int i = 0; i < (int)sched.size(); ++i)
-    if (sched[i].x >= 0) round_of[sched[i].x] = i / W;
-  for (int4& e : sched) {
-    if (e.x < 0) continue;
-    const int r = round_of[e.x];
+    if (sched[i].v >= 0) round_of[sched[i].v] = i / W;
+  const uint64_t n_cols = (uint64_t)P * K;
+  auto offset = [&](int id) -> unsigned {
+    return id >= N ? (unsigned)((uint64_t)(id - N) * n_cols) : (unsigned)((uint64_t)id * P);
+  };
+  for (SchedEntry& e : sched) {
+    if (e.v < 0) continue;
+    const int r = round_of[e.v];
     int last_child = -1;
-    if (e.y >= N) last_child = std::max(last_child, round_of[e.y]);
-    if (e.z >= N) last_child = std::max(last_child, round_of[e.z]);
+    if (e.l >= N) last_child = std::max(last_child, round_of[e.l]);
+    if (e.r >= N) last_child = std::max(last_child, round_of[e.r]);
     const int d_post = std::max(0, std::min(D - 1, r - 1 - last_child));
     int d_pre = 0;
-    if (e.x != root) d_pre = std::max(0, std::min(D - 1, round_of[parent[e.x]] - r - 1));
-    e.w = d_post | (d_pre << 2);
+    if (e.v != root) d_pre = std::max(0, std::min(D - 1, round_of[parent[e.v]] - r - 1));
+    e.fl = d_post | (d_pre << 2);
+    e.voff = offset(e.v); e.loff = offset(e.l); e.roff = offset(e.r);
   }
   return R;
 }
@@ -338,11 +334,15 @@ static void fill_params(const b2p_instance* h, TraverseParams<T>& p) {
   p.cols_per_tile = h->cols_per_tile; p.n_tiles = h->n_tiles; p.n_rounds = h->n_rounds;
   p.n_branches = 2 * N - 2;
   p.sched = h->d_sched; p.tips = h->d_tips; p.weights = h->d_weights;
-  p.pmat = (const T*)h->d_pmat; p.dpmat = (const T*)h->d_dpmat;
+  p.pmat = (const T*)h->d_pmat;
   p.post = (T*)h->d_post; p.pre = (T*)h->d_pre;
   p.lpart = h->d_lpart; p.gpart = h->d_gpart;
   for (int i = 0; i < 4; ++i) p.freqs[i] = h->freqs[i];
-  for (int k = 0; k < kMaxCat; ++k) p.cat_w[k] = k < K ? h->cat_w[k] : 0.0;
+  for (int i = 0; i < 16; ++i) p.q[i] = (T)h->qmat[i];
+  for (int k = 0; k < kMaxCat; ++k) {
+    p.cat_w[k] = k < K ? h->cat_w[k] : 0.0;
+    p.rates[k] = k < K ? h->model.rates[k] : 0.0;
+  }
 }
 
 template <typename T>
@@ -351,8 +351,7 @@ static cudaError_t launch_eval(b2p_instance* h, const double* d_bl, double* d_lo
   const int N = h->cfg.n_tips, K = h->cfg.n_categories;
   const int n_br = 2 * N - 2;
   const int total = n_br * K * 16;
-  transition_kernel<T><<<(total + 255) / 256, 256, 0, st>>>(h->model, d_bl, n_br, K, (T*)h->d_pmat,
-                                                           (T*)h->d_dpmat);
+  transition_kernel<T><<<(total + 255) / 256, 256, 0, st>>>(h->model, d_bl, n_br, K, (T*)h->d_pmat);
   TraverseParams<T> p;
   fill_params(h, p);
   void* args[] = {&p};
@@ -394,13 +393,13 @@ int b2p_get_info(const b2p_instance* h, b2p_info* o) {
 
 int b2p_set_topology(b2p_instance* h, const int32_t* h_triples) {
   if (!h || !h_triples) return h ? fail(h, B2P_ERR_ARG, "b2p_set_topology: null triples") : B2P_ERR_ARG;
-  std::vector<int4> sched;
+  std::vector<SchedEntry> sched;
   std::string why;
   int depth = 0;
-  const int rounds = build_schedule(h->cfg.n_tips, h_triples, h->W, h->D, sched, &depth, why);
+  const int rounds = build_schedule(h->cfg.n_tips, h->cfg.n_patterns, h->cfg.n_categories, h_triples, h->W, h->D, sched, &depth, why);
   if (rounds < 0) return fail(h, B2P_ERR_ARG, "b2p_set_topology: %s", why.c_str());
   CU(cudaSetDevice(h->cfg.device));
-  CU(cudaMemcpy(h->d_sched, sched.data(), sched.size() * sizeof(int4), cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(h->d_sched, sched.data(), sched.size() * sizeof(SchedEntry), cudaMemcpyHostToDevice));
   h->n_rounds = rounds;
   h->tree_depth = depth;
   h->have_topology = true;
@@ -434,6 +433,12 @@ int b2p_set_eigen(b2p_instance* h, const double* evec, const double* ivec, const
   memcpy(h->model.ivec, ivec, sizeof(double) * 16);
   memcpy(h->model.evals, evals, sizeof(double) * 4);
   memcpy(h->freqs, freqs, sizeof(double) * 4);
+  for (int i = 0; i < 4; ++i)
+    for (int l = 0; l < 4; ++l) {
+      double acc = 0.0;
+      for (int j = 0; j < 4; ++j) acc += evec[i * 4 + j] * evals[j] * ivec[j * 4 + l];
+      h->qmat[i * 4 + l] = acc;
+    }
   h->have_eigen = true;
   return B2P_OK;
 }
