@@ -1,0 +1,130 @@
+"""``b200phylo-benchmark`` — the micro-benchmark CLI contract.
+
+Honours the flags the pipeline passes to every ``<program>-benchmark``
+(/root/reference/modules/micro.nf:47-53; physher form :20-24):
+
+    -i <fasta>  -t <newick>  -r <replicates>  -s <branch-length scaler>  -o <csv>
+    [--gtr]  [-d float32]
+
+and writes the CSV whose header, once ``program,size,rep,precision,`` is prepended by
+the pipeline's awk (/root/reference/modules/micro.nf:54-56), yields the columns
+``plot.Rmd`` reads: ``function,mode,JIT,time`` (/root/reference/plot.Rmd:257-266).
+Rows: ``treelikelihoodJC69,{evaluation,gradient},off,<seconds for all replicates>``
+and, with ``--gtr``, ``treelikelihoodGTR,...`` (/root/reference/plot.Rmd:262,305).
+
+Like the other contenders each replicate is one call of the public model object: branch
+lengths in, log-likelihood (and ``backward()`` for the gradient rows) out.  Branch
+lengths live on the GPU across replicates, as torchtree's parameters live in torch
+tensors across replicates.  An extra, separate file ``<csv>.b200.json`` carries
+evaluations/s and achieved GB/s (never mixed into the contract CSV).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import sys
+import time
+from typing import List, Optional
+
+import numpy as np
+import torch
+
+from .alignment import compress_alignment, read_fasta
+from .sitemodel import ConstantSiteModel
+from .substitution import GTR, JC69
+from .tree import Tree
+from .treelikelihood import TreeLikelihoodModel, UnrootedTreeModel
+
+__all__ = ["main", "run_benchmark"]
+
+
+def _time_loop(fn, replicates: int) -> float:
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(replicates):
+        fn()
+    torch.cuda.synchronize()
+    return time.perf_counter() - t0
+
+
+def run_benchmark(fasta: str, newick: str, replicates: int, scaler: float, gtr: bool,
+                  dtype: str = "float64", device: int = 0, warmup: int = 3) -> List[dict]:
+    aln = read_fasta(fasta)
+    with open(newick) as fh:
+        tree = Tree.from_newick(fh.read(), taxa=aln.names)
+    tree = tree.scaled(scaler)
+    sp = compress_alignment(aln)
+    dev = torch.device(f"cuda:{device}")
+    torch.cuda.set_device(dev)
+    rows = []
+    models = [("treelikelihoodJC69", JC69())]
+    if gtr:
+        # the reference's --gtr run uses fixed, non-trivial GTR parameters; only time is recorded
+        models.append(("treelikelihoodGTR", GTR((1.0, 2.0, 1.0, 1.0, 2.0, 1.0), (0.3, 0.2, 0.2, 0.3))))
+    for fname, subst in models:
+        bl = torch.tensor(tree.branch_lengths, dtype=torch.float64, device=dev)
+        tm = UnrootedTreeModel("tree", tree, bl)
+        model = TreeLikelihoodModel("like", sp, tm, subst, ConstantSiteModel(), precision=dtype,
+                                    device=device)
+
+        def evaluation():
+            with torch.no_grad():
+                return model()
+
+        def gradient():
+            bl.grad = None
+            model().backward()
+
+        bl.requires_grad_(False)
+        for _ in range(warmup):
+            evaluation()
+        t_eval = _time_loop(evaluation, replicates)
+        logl = float(evaluation())
+        bl.requires_grad_(True)
+        for _ in range(warmup):
+            gradient()
+        t_grad = _time_loop(gradient, replicates)
+        info = model.engine.info()
+        rows.append({"function": fname, "mode": "evaluation", "JIT": "off", "time": t_eval,
+                     "logl": logl, "alg_bytes": info["alg_bytes_loglik"]})
+        rows.append({"function": fname, "mode": "gradient", "JIT": "off", "time": t_grad,
+                     "logl": logl, "alg_bytes": info["alg_bytes_grad"],
+                     "grad_norm": float(bl.grad.norm())})
+        model.close()
+    for r in rows:
+        r.update(n_taxa=tree.n_tips, n_patterns=sp.n_patterns, replicates=replicates, dtype=dtype)
+    return rows
+
+
+def main(argv: Optional[List[str]] = None) -> int:
+    ap = argparse.ArgumentParser(prog="b200phylo-benchmark", description=__doc__.split("\n")[0])
+    ap.add_argument("-i", "--input", required=True, help="alignment (FASTA)")
+    ap.add_argument("-t", "--tree", required=True, help="tree (Newick, name_date tips)")
+    ap.add_argument("-r", "--replicates", type=int, required=True)
+    ap.add_argument("-s", "--scaler", type=float, default=1.0, help="branch-length scaler")
+    ap.add_argument("-o", "--output", required=True, help="output CSV")
+    ap.add_argument("-d", "--dtype", choices=["float64", "float32"], default="float64")
+    ap.add_argument("--gtr", action="store_true", help="also time a GTR tree likelihood")
+    ap.add_argument("--device", type=int, default=0)
+    a = ap.parse_args(argv)
+    if not torch.cuda.is_available():
+        print("b200phylo-benchmark: no CUDA device; this engine has no CPU fallback", file=sys.stderr)
+        return 2
+    rows = run_benchmark(a.input, a.tree, a.replicates, a.scaler, a.gtr, a.dtype, a.device)
+    with open(a.output, "w") as fh:
+        fh.write("function,mode,JIT,time\n")
+        for r in rows:
+            fh.write(f"{r['function']},{r['mode']},{r['JIT']},{r['time']}\n")
+    extra = []
+    for r in rows:
+        e = dict(r)
+        e["evals_per_s"] = r["replicates"] / r["time"]
+        e["achieved_gbs"] = r["alg_bytes"] * r["replicates"] / r["time"] / 1e9
+        extra.append(e)
+    with open(a.output + ".b200.json", "w") as fh:
+        json.dump(extra, fh, indent=1)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

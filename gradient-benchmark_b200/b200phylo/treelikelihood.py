@@ -1,0 +1,336 @@
+"""``TreeLikelihoodModel`` — the plugin surface of the hot path.
+
+In the reference a likelihood engine is swapped in by naming its class in the JSON
+``"type"`` of the ``"like"`` object (/root/reference/flu_H3N2/phylotorch-JC69.template:11-74;
+``--engine bitorch`` does exactly that for torchtree-bito,
+/root/reference/modules/macro_flu.nf:119-122).  This class keeps that surface:
+
+* same five named sub-objects (``tree_model``, ``site_model``, ``branch_model``,
+  ``site_pattern``, ``substitution_model``) and a ``from_json(data, dic)`` classmethod;
+* ``model()`` returns the log-likelihood as a ``torch.Tensor`` that is differentiable
+  w.r.t. ``tree_model.branch_lengths()`` (and, through torch's chain rule, the clock
+  rate and anything upstream of the branch lengths);
+* like torchtree-bito, ``forward`` asks the native engine for the log-likelihood AND the
+  analytic branch gradient in one pass and ``backward`` only scales the cached gradient.
+
+torchtree itself is not installable here, so the sub-objects are
+duck-typed: anything with ``branch_lengths()`` / ``rates`` / ``eigen()`` works, and the
+small classes in this file stand in for torchtree's when it is absent.
+
+There is no CPU fallback: evaluation goes through ``libb200phylo.so`` on a B200 or raises.
+"""
+from __future__ import annotations
+
+from typing import Any, Dict, Optional
+
+import numpy as np
+import torch
+
+from .alignment import Alignment, SitePattern, compress_alignment
+from .engine import Engine, EngineError
+from .parallel import allreduce_sum_, rank_world, shard_bounds
+from .sitemodel import ConstantSiteModel, GammaSiteModel
+from .substitution import GTR, HKY, JC69, SubstitutionModel
+from .tree import Tree
+
+__all__ = ["TreeLikelihoodModel", "TreeLikelihoodFunction", "UnrootedTreeModel",
+           "StrictClockModel", "Parameter"]
+
+
+class Parameter:
+    """Minimal stand-in for torchtree's ``Parameter``: an id + a tensor."""
+
+    def __init__(self, id_: Optional[str], tensor: torch.Tensor):
+        self.id = id_
+        self.tensor = tensor
+
+    @property
+    def requires_grad(self) -> bool:
+        return self.tensor.requires_grad
+
+    @requires_grad.setter
+    def requires_grad(self, flag: bool) -> None:
+        self.tensor.requires_grad_(flag)
+
+
+class UnrootedTreeModel:
+    """Tree with free branch lengths — the micro benchmark's parameterisation
+    ("input = branch lengths", /root/reference/plot.Rmd:41-48).  ``branch_lengths()``
+    has length ``2N-2`` indexed by child node id, the same order as the gradient."""
+
+    def __init__(self, id_: Optional[str], tree: Tree, branch_lengths: Optional[torch.Tensor] = None,
+                 device: Optional[torch.device] = None):
+        self.id = id_
+        self.tree = tree
+        if branch_lengths is None:
+            branch_lengths = torch.tensor(tree.branch_lengths, dtype=torch.float64, device=device)
+        self._bl = Parameter(f"{id_}.blens" if id_ else None, branch_lengths)
+
+    @property
+    def n_tips(self) -> int:
+        return self.tree.n_tips
+
+    @property
+    def taxa(self):
+        return self.tree.names
+
+    @property
+    def post_triples(self) -> np.ndarray:
+        return self.tree.post_triples
+
+    def branch_lengths(self) -> torch.Tensor:
+        return self._bl.tensor
+
+    def parameters(self):
+        return [self._bl]
+
+
+class StrictClockModel:
+    """One rate for every branch (/root/reference/flu_H3N2/phylotorch-JC69.template:49-58)."""
+
+    def __init__(self, id_: Optional[str], rate: torch.Tensor):
+        self.id = id_
+        self._rate = Parameter(f"{id_}.rate" if id_ else None, rate)
+
+    @property
+    def rates(self) -> torch.Tensor:
+        return self._rate.tensor
+
+    def parameters(self):
+        return [self._rate]
+
+
+class TreeLikelihoodFunction(torch.autograd.Function):
+    """logL(branch lengths) with the analytic gradient computed in ``forward``.
+
+    ``branch_lengths`` may live on the engine's CUDA device (zero-copy, asynchronous on
+    the current stream) or on the host (pinned staging inside ``b2p_loglik_grad_host``).
+    With an initialised process group the per-rank partial results are summed with one
+    all-reduce of ``2N-1`` doubles.
+    """
+
+    @staticmethod
+    def forward(ctx, branch_lengths: torch.Tensor, model: "TreeLikelihoodModel") -> torch.Tensor:
+        eng = model.engine
+        need_grad = branch_lengths.requires_grad
+        bl = branch_lengths.detach()
+        if bl.dim() != 1 or bl.shape[0] != eng.n_branches:
+            raise ValueError(f"branch_lengths must have shape ({eng.n_branches},), got {tuple(bl.shape)}")
+        if bl.is_cuda:
+            if bl.device.index != eng.device:
+                raise EngineError(f"branch lengths on cuda:{bl.device.index}, engine on cuda:{eng.device}")
+            bl64 = bl.to(torch.float64).contiguous()
+            out = torch.empty(1 + eng.n_branches, dtype=torch.float64, device=bl.device)
+            stream = torch.cuda.current_stream(bl.device).cuda_stream
+            eng.loglik_grad_device(bl64.data_ptr(), out.data_ptr(),
+                                   out.data_ptr() + 8 if need_grad else None, stream)
+            if not need_grad:
+                out = out[:1]
+        else:
+            logl, grad = eng.loglik_grad_host(bl.to(torch.float64).numpy(), want_grad=need_grad)
+            out = torch.empty(1 + (eng.n_branches if need_grad else 0), dtype=torch.float64)
+            out[0] = logl
+            if need_grad:
+                out[1:] = torch.from_numpy(grad)
+            if model.world_size > 1:
+                out = out.to(f"cuda:{eng.device}")
+        if model.world_size > 1:
+            allreduce_sum_(out, model.group)
+            out = out.to(bl.device)
+        if need_grad:
+            ctx.save_for_backward(out[1:])
+        ctx.in_dtype = branch_lengths.dtype
+        return out[0].to(branch_lengths.dtype)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        (g,) = ctx.saved_tensors
+        return (grad_output * g).to(ctx.in_dtype), None
+
+
+class TreeLikelihoodModel:
+    """Tree + site patterns + substitution model + site model (+ clock) → logL tensor.
+
+    Constructor argument order follows torchtree's / torchtree-bito's
+    ``TreeLikelihoodModel(id_, site_pattern, tree_model, subst_model, site_model,
+    clock_model)`` (upstream recall).  ``precision`` is the engine's
+    working type for partials ("float64" default, "float32" for ``-d float32``,
+    /root/reference/modules/micro.nf:42-45).  When a ``torch.distributed`` group is
+    initialised (or ``rank``/``world_size`` are given) the instance keeps only its
+    contiguous pattern slice and all-reduces results.
+    """
+
+    def __init__(self, id_: Optional[str], site_pattern: SitePattern, tree_model, subst_model,
+                 site_model=None, clock_model=None, precision: str = "float64",
+                 device: Optional[int] = None, rank: Optional[int] = None,
+                 world_size: Optional[int] = None, group=None, warps_per_block: int = 0):
+        self.id = id_
+        self.tree_model = tree_model
+        self.subst_model = subst_model
+        self.site_model = site_model if site_model is not None else ConstantSiteModel()
+        self.clock_model = clock_model
+        self.group = group
+        r, w = rank_world(group)
+        self.rank = r if rank is None else int(rank)
+        self.world_size = w if world_size is None else int(world_size)
+        taxa = list(tree_model.taxa) if getattr(tree_model, "taxa", None) else None
+        if taxa and list(site_pattern.names) != taxa:
+            site_pattern = site_pattern.reorder(taxa)
+        self.site_pattern_full = site_pattern
+        if self.world_size > 1:
+            if site_pattern.n_patterns < self.world_size:
+                raise ValueError("fewer site patterns than ranks")
+            lo, hi = shard_bounds(site_pattern.n_patterns, self.world_size, self.rank)
+            site_pattern = site_pattern.slice(lo, hi)
+        self.site_pattern = site_pattern
+        if device is None:
+            device = torch.cuda.current_device() if torch.cuda.is_available() else 0
+        n_cat = len(np.asarray(self.site_model.rates))
+        self.engine = Engine(tree_model.n_tips, site_pattern.n_patterns, n_cat,
+                             precision=precision, device=device, warps_per_block=warps_per_block)
+        self.engine.set_topology(tree_model.post_triples)
+        self.engine.set_tip_states(site_pattern.masks)
+        self.engine.set_pattern_weights(site_pattern.weights)
+        self.update_model()
+
+    def update_model(self) -> None:
+        """Push the substitution / site model to the engine (call after changing them)."""
+        self.engine.set_model(self.subst_model, self.site_model)
+
+    # ---------------------------------------------------------------- evaluation
+    def _scaled_branch_lengths(self) -> torch.Tensor:
+        bl = self.tree_model.branch_lengths()
+        if self.clock_model is not None:
+            bl = self.clock_model.rates * bl
+        return bl
+
+    def __call__(self, *args, **kwargs) -> torch.Tensor:
+        return TreeLikelihoodFunction.apply(self._scaled_branch_lengths(), self)
+
+    def log_likelihood(self) -> float:
+        with torch.no_grad():
+            return float(self())
+
+    def parameters(self):
+        out = list(self.tree_model.parameters())
+        if self.clock_model is not None:
+            out += list(self.clock_model.parameters())
+        return out
+
+    def close(self) -> None:
+        self.engine.close()
+
+    # ------------------------------------------------------------------- JSON
+    @classmethod
+    def from_json(cls, data: Dict[str, Any], dic: Dict[str, Any]) -> "TreeLikelihoodModel":
+        """Build from the ``"like"`` object of the reference's model JSON
+        (/root/reference/flu_H3N2/phylotorch-JC69.template:11-74).
+
+        ``dic`` maps ids to already-built objects (torchtree's registry); sub-objects given
+        as strings are looked up there, dict sub-objects are built by the small parsers
+        below (newick / Alignment / JC69-HKY-GTR / Constant-Gamma / StrictClock).  Extra
+        keys understood: ``"precision"`` ("float64" | "float32"), ``"device"``.
+        """
+        def resolve(key, builder, required=True):
+            spec = data.get(key)
+            if spec is None:
+                if required:
+                    raise KeyError(f"TreeLikelihoodModel JSON needs {key!r}")
+                return None
+            if isinstance(spec, str):
+                if spec not in dic:
+                    raise KeyError(f"{key}: id {spec!r} not found")
+                return dic[spec]
+            obj = builder(spec)
+            if isinstance(spec, dict) and "id" in spec:
+                dic[spec["id"]] = obj
+            return obj
+
+        site_pattern = resolve("site_pattern", lambda s: _site_pattern_from_json(s, dic))
+        tree_model = resolve("tree_model", lambda s: _tree_model_from_json(s, dic, site_pattern))
+        subst_model = resolve("substitution_model", _subst_model_from_json)
+        site_model = resolve("site_model", _site_model_from_json, required=False)
+        clock_model = resolve("branch_model", _clock_from_json, required=False)
+        obj = cls(data.get("id"), site_pattern, tree_model, subst_model, site_model, clock_model,
+                  precision=data.get("precision", "float64"), device=data.get("device"))
+        if "id" in data:
+            dic[data["id"]] = obj
+        return obj
+
+
+def _tensor_from_json(spec) -> torch.Tensor:
+    if isinstance(spec, dict):  # {"type": "Parameter", "tensor": [...], "full": [n]}
+        t = spec.get("tensor")
+        if "full" in spec:
+            return torch.full(tuple(spec["full"]), float(t), dtype=torch.float64)
+        return torch.as_tensor(t, dtype=torch.float64).reshape(-1)
+    return torch.as_tensor(spec, dtype=torch.float64).reshape(-1)
+
+
+def _site_pattern_from_json(spec, dic) -> SitePattern:
+    aln = spec["alignment"]
+    if isinstance(aln, str):
+        aln = dic[aln]
+    if isinstance(aln, Alignment):
+        return compress_alignment(aln)
+    if "file" in aln:
+        from .alignment import read_fasta
+        return compress_alignment(read_fasta(aln["file"]))
+    seqs = aln["sequences"]  # [{"taxon": name, "sequence": "ACGT..."}]
+    return compress_alignment(Alignment([s["taxon"] for s in seqs], [s["sequence"] for s in seqs]))
+
+
+def _tree_model_from_json(spec, dic, site_pattern: SitePattern):
+    newick = spec.get("newick")
+    if newick is None and "file" in spec:
+        with open(spec["file"]) as fh:
+            newick = fh.read()
+    if newick is None:
+        raise KeyError("tree_model JSON needs 'newick' or 'file'")
+    tree = Tree.from_newick(newick, taxa=list(site_pattern.names))
+    bl = None
+    if "branch_lengths" in spec:
+        bl = _tensor_from_json(spec["branch_lengths"])
+    return UnrootedTreeModel(spec.get("id"), tree, bl)
+
+
+def _subst_model_from_json(spec) -> SubstitutionModel:
+    kind = (spec.get("type") or "").split(".")[-1].upper()
+    freqs = spec.get("frequencies")
+    if isinstance(freqs, dict):
+        freqs = freqs.get("tensor")
+    freqs = tuple(freqs) if freqs is not None else (0.25,) * 4
+    if kind == "JC69":
+        return JC69()
+    if kind == "HKY":
+        kappa = spec.get("kappa", 1.0)
+        if isinstance(kappa, dict):
+            kappa = kappa.get("tensor")
+        return HKY(float(np.asarray(kappa).reshape(-1)[0]), freqs)
+    if kind == "GTR":
+        rates = spec.get("rates", (1.0,) * 6)
+        if isinstance(rates, dict):
+            rates = rates.get("tensor")
+        return GTR(tuple(rates), freqs)
+    raise ValueError(f"unsupported substitution model type {spec.get('type')!r}")
+
+
+def _site_model_from_json(spec):
+    kind = (spec.get("type") or "ConstantSiteModel").split(".")[-1]
+    if kind == "ConstantSiteModel":
+        return ConstantSiteModel()
+    if kind in ("GammaSiteModel", "WeibullSiteModel"):
+        shape = spec.get("shape", 0.5)
+        if isinstance(shape, dict):
+            shape = shape.get("tensor")
+        if kind == "WeibullSiteModel":
+            raise ValueError("WeibullSiteModel is not built; use GammaSiteModel")
+        return GammaSiteModel(float(np.asarray(shape).reshape(-1)[0]), int(spec.get("categories", 4)))
+    raise ValueError(f"unsupported site model type {spec.get('type')!r}")
+
+
+def _clock_from_json(spec) -> StrictClockModel:
+    kind = (spec.get("type") or "").split(".")[-1]
+    if kind != "StrictClockModel":
+        raise ValueError(f"unsupported branch model type {spec.get('type')!r}")
+    return StrictClockModel(spec.get("id"), _tensor_from_json(spec["rate"]))
