@@ -25,7 +25,7 @@ EXPORTED_SYMBOLS = (
     "b2p_create", "b2p_destroy", "b2p_last_error", "b2p_version", "b2p_get_info",
     "b2p_set_topology", "b2p_set_tip_states", "b2p_set_pattern_weights", "b2p_set_eigen",
     "b2p_set_categories", "b2p_loglik", "b2p_loglik_grad", "b2p_loglik_grad_host",
-    "b2p_set_profiling", "b2p_last_kernel_ms", "b2p_get_post_partials",
+    "b2p_set_profiling", "b2p_last_kernel_ms", "b2p_kernel_ms_stats", "b2p_get_post_partials",
 )
 
 
@@ -82,6 +82,7 @@ def load_library():
     lib.b2p_loglik_grad_host.argtypes = [vp, dp, dp, dp]
     lib.b2p_set_profiling.argtypes = [vp, ctypes.c_int]
     lib.b2p_last_kernel_ms.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
+    lib.b2p_kernel_ms_stats.argtypes = [vp, dp, ctypes.POINTER(ctypes.c_int32)]
     lib.b2p_get_post_partials.argtypes = [vp, ctypes.c_int32, dp]
     for name in EXPORTED_SYMBOLS:
         if name != "b2p_last_error":
@@ -208,6 +209,13 @@ class Engine:
         ms = ctypes.c_float()
         self._check(self._lib.b2p_last_kernel_ms(self._h, ctypes.byref(ms)), "b2p_last_kernel_ms")
         return float(ms.value)
+
+    def kernel_ms_stats(self) -> Tuple[float, int]:
+        """(total ms, launches) of the traversal kernel since ``set_profiling(True)``."""
+        tot, n = ctypes.c_double(), ctypes.c_int32()
+        self._check(self._lib.b2p_kernel_ms_stats(self._h, ctypes.byref(tot), ctypes.byref(n)),
+                    "b2p_kernel_ms_stats")
+        return float(tot.value), int(n.value)
 
     def post_partials(self, node: int) -> np.ndarray:
         out = np.empty((self.n_patterns, self.n_categories, 4))

@@ -65,37 +65,38 @@ def random_patterns(n_tips: int, n_patterns: int, seed: int = SEQ_SEED, p_change
 
 def _simulated(name, n_tips, model, site_model, n_patterns: Optional[int] = None,
                n_sites: Optional[int] = None, shape="coalescent", precision="float64",
-               mean_branch=0.02) -> Workload:
+               mean_branch=0.02, seq_seed: int = SEQ_SEED) -> Workload:
     tree = simulate_tree(n_tips, shape=shape, seed=TREE_SEED, mean_branch=mean_branch)
     rates = np.asarray(site_model.rates)
     pm = model.p_t(tree.branch_lengths[:, None] * rates[None, :])
     if n_patterns is not None:
-        sp = simulate_patterns(tree, pm, model.freqs, n_patterns, seed=SEQ_SEED,
+        sp = simulate_patterns(tree, pm, model.freqs, n_patterns, seed=seq_seed,
                                cat_weights=site_model.weights)
     else:
-        aln = simulate_alignment(tree, pm, model.freqs, n_sites, seed=SEQ_SEED,
+        aln = simulate_alignment(tree, pm, model.freqs, n_sites, seed=seq_seed,
                                  cat_weights=site_model.weights)
         sp = compress_alignment(aln)
     return Workload(name, tree, sp, model, site_model, precision)
 
 
 def make_workload(name: str, precision: Optional[str] = None, n_tips: Optional[int] = None,
-                  n_patterns: Optional[int] = None) -> Workload:
-    """Build one of the named workloads; ``n_tips`` / ``n_patterns`` shrink it for tests."""
+                  n_patterns: Optional[int] = None, seq_seed: int = SEQ_SEED) -> Workload:
+    """Build one of the named workloads; ``n_tips`` / ``n_patterns`` shrink it for tests;
+    ``seq_seed`` draws a different alignment on the same tree (per-rank shards)."""
     pi = (0.3, 0.2, 0.2, 0.3)
     if name == "jc69_20x1000":  # BASELINE.json configs[0]
-        w = _simulated(name, n_tips or 20, JC69(), ConstantSiteModel(), n_sites=n_patterns or 1000)
+        w = _simulated(name, n_tips or 20, JC69(), ConstantSiteModel(), n_sites=n_patterns or 1000, seq_seed=seq_seed)
     elif name == "jc69_1000x10k":  # configs[1] — the headline metric
-        w = _simulated(name, n_tips or 1000, JC69(), ConstantSiteModel(), n_patterns=n_patterns or 10000)
+        w = _simulated(name, n_tips or 1000, JC69(), ConstantSiteModel(), n_patterns=n_patterns or 10000, seq_seed=seq_seed)
     elif name == "hky_g4_flu":  # configs[2]
         w = _simulated(name, n_tips or 1704, HKY(3.0, pi), GammaSiteModel(0.5, 4),
-                       n_sites=n_patterns or 1701)
+                       n_sites=n_patterns or 1701, seq_seed=seq_seed)
     elif name == "gtr_g4_5000x100k":  # configs[3] (per-rank slices are cut by the caller)
         w = _simulated(name, n_tips or 5000, GTR((1, 2, 1, 1, 2, 1), pi), GammaSiteModel(0.5, 4),
-                       n_patterns=n_patterns or 100000)
+                       n_patterns=n_patterns or 100000, seq_seed=seq_seed)
     elif name == "gtr_g4_5000x10k":  # north-star gate shape
         w = _simulated(name, n_tips or 5000, GTR((1, 2, 1, 1, 2, 1), pi), GammaSiteModel(0.5, 4),
-                       n_patterns=n_patterns or 10000)
+                       n_patterns=n_patterns or 10000, seq_seed=seq_seed)
     else:
         raise ValueError(f"unknown workload {name!r}; known: {sorted(WORKLOADS)}")
     if precision:

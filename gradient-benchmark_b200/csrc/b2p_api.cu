@@ -38,8 +38,10 @@ struct b2p_instance {
   double* h_pin_in = nullptr;
   double* h_pin_out = nullptr;
   cudaStream_t own_stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  bool profiling = false, have_timing = false;
+  static constexpr int kProfRing = 1024;  // event pairs kept while profiling is on
+  std::vector<cudaEvent_t> ev0, ev1;
+  int64_t prof_count = 0;
+  bool profiling = false;
   int64_t device_bytes = 0;
   ModelParams model{};
   double freqs[4]{};
@@ -220,9 +222,8 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
     fail(h, B2P_ERR_ALLOC, "cudaMallocHost: %s", cudaGetErrorString(e));
     return bail(B2P_ERR_ALLOC);
   }
-  if ((e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking)) != cudaSuccess ||
-      (e = cudaEventCreate(&h->ev0)) != cudaSuccess || (e = cudaEventCreate(&h->ev1)) != cudaSuccess) {
-    fail(h, B2P_ERR_CUDA, "stream/event creation: %s", cudaGetErrorString(e));
+  if ((e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking)) != cudaSuccess) {
+    fail(h, B2P_ERR_CUDA, "stream creation: %s", cudaGetErrorString(e));
     return bail(B2P_ERR_CUDA);
   }
   *out = h;
@@ -237,8 +238,8 @@ int b2p_destroy(b2p_instance* h) {
   if (h->h_pin_in) cudaFreeHost(h->h_pin_in);
   if (h->h_pin_out) cudaFreeHost(h->h_pin_out);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
-  if (h->ev0) cudaEventDestroy(h->ev0);
-  if (h->ev1) cudaEventDestroy(h->ev1);
+  for (cudaEvent_t ev : h->ev0) cudaEventDestroy(ev);
+  for (cudaEvent_t ev : h->ev1) cudaEventDestroy(ev);
   delete h;
   return B2P_OK;
 }
@@ -355,11 +356,12 @@ static cudaError_t launch_eval(b2p_instance* h, const double* d_bl, double* d_lo
   TraverseParams<T> p;
   fill_params(h, p);
   void* args[] = {&p};
-  if (h->profiling) cudaEventRecord(h->ev0, st);
+  const int slot = (int)(h->prof_count % b2p_instance::kProfRing);
+  if (h->profiling) cudaEventRecord(h->ev0[slot], st);
   cudaError_t e = cudaLaunchKernel(d_grad ? h->k_grad : h->k_eval, dim3(h->grid), dim3(h->W * 32), args,
                                    h->smem_bytes, st);
   if (e != cudaSuccess) return e;
-  if (h->profiling) { cudaEventRecord(h->ev1, st); h->have_timing = true; }
+  if (h->profiling) { cudaEventRecord(h->ev1[slot], st); ++h->prof_count; }
   const int nb = d_grad ? n_br : 0;
   reduce_kernel<<<(nb + 31) / 32 + 1, 512, 0, st>>>(h->d_gpart, h->d_lpart, h->grid, nb, d_grad, d_logl);
   return cudaGetLastError();
@@ -499,16 +501,42 @@ int b2p_loglik_grad_host(b2p_instance* h, const double* h_bl, double* h_logl, do
 
 int b2p_set_profiling(b2p_instance* h, int enabled) {
   if (!h) return B2P_ERR_ARG;
+  CU(cudaSetDevice(h->cfg.device));
+  if (enabled && h->ev0.empty()) {
+    h->ev0.resize(b2p_instance::kProfRing, nullptr);
+    h->ev1.resize(b2p_instance::kProfRing, nullptr);
+    for (int i = 0; i < b2p_instance::kProfRing; ++i) {
+      CU(cudaEventCreate(&h->ev0[i]));
+      CU(cudaEventCreate(&h->ev1[i]));
+    }
+  }
   h->profiling = enabled != 0;
-  h->have_timing = false;
+  h->prof_count = 0;
   return B2P_OK;
 }
 
 int b2p_last_kernel_ms(b2p_instance* h, float* ms_out) {
   if (!h || !ms_out) return B2P_ERR_ARG;
-  if (!h->have_timing) return fail(h, B2P_ERR_ARG, "b2p_last_kernel_ms: no profiled evaluation yet");
-  CU(cudaEventSynchronize(h->ev1));
-  CU(cudaEventElapsedTime(ms_out, h->ev0, h->ev1));
+  if (h->prof_count == 0) return fail(h, B2P_ERR_ARG, "b2p_last_kernel_ms: no profiled evaluation yet");
+  const int slot = (int)((h->prof_count - 1) % b2p_instance::kProfRing);
+  CU(cudaEventSynchronize(h->ev1[slot]));
+  CU(cudaEventElapsedTime(ms_out, h->ev0[slot], h->ev1[slot]));
+  return B2P_OK;
+}
+
+int b2p_kernel_ms_stats(b2p_instance* h, double* total_ms, int32_t* n_launches) {
+  if (!h || !total_ms || !n_launches) return B2P_ERR_ARG;
+  const int64_t n = std::min<int64_t>(h->prof_count, b2p_instance::kProfRing);
+  double tot = 0.0;
+  for (int64_t i = 0; i < n; ++i) {
+    const int slot = (int)((h->prof_count - 1 - i) % b2p_instance::kProfRing);
+    float ms = 0.f;
+    CU(cudaEventSynchronize(h->ev1[slot]));
+    CU(cudaEventElapsedTime(&ms, h->ev0[slot], h->ev1[slot]));
+    tot += ms;
+  }
+  *total_ms = tot;
+  *n_launches = (int32_t)n;
   return B2P_OK;
 }
 

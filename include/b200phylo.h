@@ -133,6 +133,9 @@ int b2p_loglik_grad_host(b2p_instance* h, const double* h_bl, double* h_logl,
  * b2p_last_kernel_ms synchronises on the last pair and returns its duration. */
 int b2p_set_profiling(b2p_instance* h, int enabled);
 int b2p_last_kernel_ms(b2p_instance* h, float* ms_out);
+/* Sum of the traversal-kernel durations of the evaluations issued since profiling was
+ * enabled (the most recent 1024 at most) and their count; synchronises on them. */
+int b2p_kernel_ms_stats(b2p_instance* h, double* total_ms, int32_t* n_launches);
 
 /* Debug / test access: copy the post-order partials of internal node `node` as
  * double [P][K][S] (converted from the working precision) into h_out. */
