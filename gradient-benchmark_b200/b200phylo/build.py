@@ -13,7 +13,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _CSRC = os.path.normpath(os.path.join(_HERE, "..", "csrc"))
 _OUT = os.path.join(_HERE, "libb200phylo.so")
 _SOURCES = ["b2p_api.cu"]
-_DEPS = ["b2p_api.cu", "b2p_kernels.cuh", "b2p_device.cuh", os.path.join("..", "..", "include", "b200phylo.h")]
+_DEPS = sorted(f for f in os.listdir(_CSRC) if f.endswith((".cu", ".cuh", ".h"))) + [
+    os.path.join("..", "..", "include", "b200phylo.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

@@ -11,6 +11,7 @@
 
 #include "../../include/b200phylo.h"
 #include "b2p_kernels.cuh"
+#include "b2p_plan.h"
 
 using namespace b2p;
 
@@ -49,6 +50,15 @@ struct b2p_instance {
   double cat_w[kMaxCat]{};
   const void* k_grad = nullptr;  // selected traversal kernels
   const void* k_eval = nullptr;
+  // wave engine (b2p_wave.cuh)
+  bool wave = true;
+  WaveGeometry wg;
+  WaveEntry* d_wpost = nullptr;
+  WaveEntry* d_wpre = nullptr;
+  int w_rounds_post = 0, w_rounds_pre = 0;
+  long long w_ring_post = 0, w_ring_pre = 0, w_pre_global = 0;
+  const void* wk_grad = nullptr;
+  const void* wk_eval = nullptr;
   mutable std::string err;
 };
 
@@ -101,6 +111,22 @@ static bool select_kernels(int K, int W, int NC, const void** grad, const void**
   if (K == 4) return select_k<T, 4>(W, NC, grad, eval);
   if (W == 8 && NC == 1) { pick<T, 0, 8, 1, 2>(grad, eval); return true; }
   return false;
+}
+
+template <typename T, int K>
+static bool wave_select_nt(int nt, const void** grad, const void** eval) {
+  if (nt == 1024) { *grad = (const void*)wave_kernel<T, K, 1024, true>; *eval = (const void*)wave_kernel<T, K, 1024, false>; }
+  else if (nt == 768) { *grad = (const void*)wave_kernel<T, K, 768, true>; *eval = (const void*)wave_kernel<T, K, 768, false>; }
+  else if (nt == 512) { *grad = (const void*)wave_kernel<T, K, 512, true>; *eval = (const void*)wave_kernel<T, K, 512, false>; }
+  else if (nt == 256) { *grad = (const void*)wave_kernel<T, K, 256, true>; *eval = (const void*)wave_kernel<T, K, 256, false>; }
+  else return false;
+  return true;
+}
+template <typename T>
+static bool wave_select(int K, int nt, const void** grad, const void** eval) {
+  if (K == 1) return wave_select_nt<T, 1>(nt, grad, eval);
+  if (K == 4) return wave_select_nt<T, 4>(nt, grad, eval);
+  return wave_select_nt<T, 0>(nt, grad, eval);
 }
 
 static size_t elem_size(const b2p_instance* h) {
@@ -206,6 +232,35 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   h->blocks_per_sm = bps;
   h->grid = std::min(h->n_tiles, bps * h->n_sms);
 
+  // wave engine geometry (default); B2P_ENGINE=v3 selects the older per-warp pipeline
+  h->wave = true;
+  if (const char* s = getenv("B2P_ENGINE")) h->wave = strcmp(s, "v3") != 0;
+  if (h->wave) {
+    int nt_force = 0, ct_force = 0;
+    if (const char* s = getenv("B2P_NT")) nt_force = atoi(s);
+    if (const char* s = getenv("B2P_CT")) ct_force = atoi(s);
+    if (!plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms, (size_t)prop.sharedMemPerBlockOptin - 1024, nt_force,
+                       ct_force, h->wg)) {
+      fail(h, B2P_ERR_UNSUPPORTED, "b2p_create: no wave geometry fits shared memory (K=%d)", K);
+      return bail(B2P_ERR_UNSUPPORTED);
+    }
+    ok = (cfg->precision == B2P_PRECISION_F32) ? wave_select<float>(K, h->wg.nt, &h->wk_grad, &h->wk_eval)
+                                               : wave_select<double>(K, h->wg.nt, &h->wk_grad, &h->wk_eval);
+    if (!ok) { fail(h, B2P_ERR_ARG, "b2p_create: no wave kernel for NT=%d", h->wg.nt); return bail(B2P_ERR_ARG); }
+    for (const void* k : {h->wk_grad, h->wk_eval}) {
+      if ((e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->wg.smem)) != cudaSuccess) {
+        fail(h, B2P_ERR_CUDA, "cudaFuncSetAttribute(wave smem=%zu): %s", h->wg.smem, cudaGetErrorString(e));
+        return bail(B2P_ERR_CUDA);
+      }
+    }
+    if ((e = cudaFuncGetAttributes(&fa, h->wk_grad)) != cudaSuccess) {
+      fail(h, B2P_ERR_CUDA, "cudaFuncGetAttributes(wave): %s", cudaGetErrorString(e));
+      return bail(B2P_ERR_CUDA);
+    }
+    h->regs = fa.numRegs;
+    h->grid = std::max(h->grid, h->wg.grid);  // sizes the per-CTA partial arrays for either engine
+  }
+
   const size_t n_br = 2 * (size_t)N - 2;
   if ((rc = dev_alloc(h, &h->d_sched, sizeof(SchedEntry) * (size_t)(N - 1) * W))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_tips, (size_t)N * P))) return bail(rc);
@@ -233,6 +288,7 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
 int b2p_destroy(b2p_instance* h) {
   if (!h) return B2P_OK;
   cudaSetDevice(h->cfg.device);
+  cudaFree(h->d_wpost); cudaFree(h->d_wpre);
   cudaFree(h->d_sched); cudaFree(h->d_tips); cudaFree(h->d_weights); cudaFree(h->d_pmat); cudaFree(h->d_post); cudaFree(h->d_pre); cudaFree(h->d_lpart);
   cudaFree(h->d_gpart); cudaFree(h->d_bl_stage); cudaFree(h->d_out_stage);
   if (h->h_pin_in) cudaFreeHost(h->h_pin_in);
@@ -347,23 +403,56 @@ static void fill_params(const b2p_instance* h, TraverseParams<T>& p) {
 }
 
 template <typename T>
+static void fill_wave_params(const b2p_instance* h, WaveParams<T>& p) {
+  const int N = h->cfg.n_tips, K = h->cfg.n_categories, P = h->cfg.n_patterns;
+  const WaveGeometry& g = h->wg;
+  p.n_tips = N; p.n_patterns = P; p.n_cat = K; p.n_cols = P * K;
+  p.ct = g.ct; p.ts = g.ts; p.cpw = g.cpw; p.wn = g.wn;
+  p.n_tiles = g.n_tiles; p.rounds_post = h->w_rounds_post; p.rounds_pre = h->w_rounds_pre;
+  p.n_branches = 2 * N - 2;
+  p.ring_cap = g.ring_cap; p.pj = g.pj;
+  p.off_ent = g.off_ent; p.off_mats = g.off_mats; p.off_stage = g.off_stage; p.off_ring = g.off_ring;
+  p.off_part = g.off_part; p.off_scount = g.off_scount;
+  p.post = h->d_wpost; p.pre = h->d_wpre;
+  p.tips = h->d_tips; p.weights = h->d_weights; p.pmat = (const T*)h->d_pmat;
+  p.msg = (T*)h->d_post; p.pre_g = (T*)h->d_pre;
+  p.lpart = h->d_lpart; p.gpart = h->d_gpart;
+  for (int i = 0; i < 4; ++i) p.freqs[i] = h->freqs[i];
+  for (int i = 0; i < 16; ++i) p.q[i] = (T)h->qmat[i];
+  for (int k = 0; k < kMaxCatW; ++k) {
+    p.cat_w[k] = k < K ? h->cat_w[k] : 0.0;
+    p.rates[k] = k < K ? h->model.rates[k] : 0.0;
+  }
+}
+
+template <typename T>
 static cudaError_t launch_eval(b2p_instance* h, const double* d_bl, double* d_logl, double* d_grad,
                                cudaStream_t st) {
   const int N = h->cfg.n_tips, K = h->cfg.n_categories;
   const int n_br = 2 * N - 2;
   const int total = n_br * K * 16;
   transition_kernel<T><<<(total + 255) / 256, 256, 0, st>>>(h->model, d_bl, n_br, K, (T*)h->d_pmat);
-  TraverseParams<T> p;
-  fill_params(h, p);
-  void* args[] = {&p};
   const int slot = (int)(h->prof_count % b2p_instance::kProfRing);
   if (h->profiling) cudaEventRecord(h->ev0[slot], st);
-  cudaError_t e = cudaLaunchKernel(d_grad ? h->k_grad : h->k_eval, dim3(h->grid), dim3(h->W * 32), args,
-                                   h->smem_bytes, st);
+  cudaError_t e;
+  int n_parts;
+  if (h->wave) {
+    WaveParams<T> wp;
+    fill_wave_params(h, wp);
+    void* args[] = {&wp};
+    e = cudaLaunchKernel(d_grad ? h->wk_grad : h->wk_eval, dim3(h->wg.grid), dim3(h->wg.nt), args, h->wg.smem, st);
+    n_parts = h->wg.grid;
+  } else {
+    TraverseParams<T> p;
+    fill_params(h, p);
+    void* args[] = {&p};
+    n_parts = std::min(h->n_tiles, h->blocks_per_sm * h->n_sms);
+    e = cudaLaunchKernel(d_grad ? h->k_grad : h->k_eval, dim3(n_parts), dim3(h->W * 32), args, h->smem_bytes, st);
+  }
   if (e != cudaSuccess) return e;
   if (h->profiling) { cudaEventRecord(h->ev1[slot], st); ++h->prof_count; }
   const int nb = d_grad ? n_br : 0;
-  reduce_kernel<<<(nb + 31) / 32 + 1, 512, 0, st>>>(h->d_gpart, h->d_lpart, h->grid, nb, d_grad, d_logl);
+  reduce_kernel<<<(nb + 31) / 32 + 1, 512, 0, st>>>(h->d_gpart, h->d_lpart, n_parts, nb, d_grad, d_logl);
   return cudaGetLastError();
 }
 
@@ -386,6 +475,10 @@ int b2p_get_info(const b2p_instance* h, b2p_info* o) {
   o->precision = h->cfg.precision;
   o->warps_per_block = h->W; o->cols_per_tile = h->cols_per_tile; o->n_tiles = h->n_tiles;
   o->grid_blocks = h->grid; o->blocks_per_sm = h->blocks_per_sm; o->n_sms = h->n_sms;
+  if (h->wave) {
+    o->warps_per_block = h->wg.nt / 32; o->cols_per_tile = h->wg.ct; o->n_tiles = h->wg.n_tiles;
+    o->grid_blocks = h->wg.grid; o->blocks_per_sm = 1;
+  }
   o->post_rounds = h->n_rounds; o->tree_depth = h->tree_depth; o->regs_per_thread = h->regs;
   o->device_bytes = h->device_bytes;
   o->alg_bytes_loglik = (2 * N - 3) * U + N * P;
@@ -404,6 +497,20 @@ int b2p_set_topology(b2p_instance* h, const int32_t* h_triples) {
   CU(cudaMemcpy(h->d_sched, sched.data(), sched.size() * sizeof(SchedEntry), cudaMemcpyHostToDevice));
   h->n_rounds = rounds;
   h->tree_depth = depth;
+  if (h->wave) {
+    WaveSchedule ws;
+    if (!plan_schedule(h->cfg.n_tips, h_triples, h->wg.wn, h->wg.ring_cap, ws, why))
+      return fail(h, B2P_ERR_ARG, "b2p_set_topology: %s", why.c_str());
+    cudaFree(h->d_wpost); cudaFree(h->d_wpre);
+    h->d_wpost = h->d_wpre = nullptr;
+    CU(cudaMalloc((void**)&h->d_wpost, ws.post.size() * sizeof(WaveEntry)));
+    CU(cudaMalloc((void**)&h->d_wpre, ws.pre.size() * sizeof(WaveEntry)));
+    CU(cudaMemcpy(h->d_wpost, ws.post.data(), ws.post.size() * sizeof(WaveEntry), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(h->d_wpre, ws.pre.data(), ws.pre.size() * sizeof(WaveEntry), cudaMemcpyHostToDevice));
+    h->w_rounds_post = ws.rounds_post; h->w_rounds_pre = ws.rounds_pre;
+    h->w_ring_post = ws.ring_reads_post; h->w_ring_pre = ws.ring_reads_pre; h->w_pre_global = ws.pre_global_blocks;
+    h->n_rounds = ws.rounds_post;
+  }
   h->have_topology = true;
   return B2P_OK;
 }

@@ -122,6 +122,17 @@ __device__ __forceinline__ double warp_sum(double v) {
   return v;
 }
 
+// 16-byte aligned row of a staged 4x4 matrix
+__device__ __forceinline__ void load_row(const double* m, double (&r)[4]) {
+  const double2 a = *reinterpret_cast<const double2*>(m);
+  const double2 b = *reinterpret_cast<const double2*>(m + 2);
+  r[0] = a.x; r[1] = a.y; r[2] = b.x; r[3] = b.y;
+}
+__device__ __forceinline__ void load_row(const float* m, float (&r)[4]) {
+  const float4 a = *reinterpret_cast<const float4*>(m);
+  r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w;
+}
+
 // y = M x with M row-major 4x4 in shared memory (broadcast / conflict-free reads)
 template <typename T>
 __device__ __forceinline__ void matvec(const T* __restrict__ m, const T (&x)[4], T (&y)[4]) {

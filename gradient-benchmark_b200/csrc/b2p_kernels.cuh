@@ -113,17 +113,6 @@ struct Ctx {
   __device__ __forceinline__ Ctx(const TraverseParams<T>& p_) : p(p_) {}
 };
 
-// 16-byte aligned row of a staged 4x4 matrix
-__device__ __forceinline__ void load_row(const double* m, double (&r)[4]) {
-  const double2 a = *reinterpret_cast<const double2*>(m);
-  const double2 b = *reinterpret_cast<const double2*>(m + 2);
-  r[0] = a.x; r[1] = a.y; r[2] = b.x; r[3] = b.y;
-}
-__device__ __forceinline__ void load_row(const float* m, float (&r)[4]) {
-  const float4 a = *reinterpret_cast<const float4*>(m);
-  r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w;
-}
-
 // Issue the asynchronous copies (LDGSTS) of one task's operands and matrices into a
 // stage.  PASS 0 = post-order (children partials); PASS 1 = pre-order (adds the parent's
 // pre-partial).  Tip children are 1-byte masks carried in registers instead.
