@@ -25,7 +25,7 @@ EXPORTED_SYMBOLS = (
     "b2p_create", "b2p_destroy", "b2p_last_error", "b2p_version", "b2p_get_info",
     "b2p_set_topology", "b2p_set_tip_states", "b2p_set_pattern_weights", "b2p_set_eigen",
     "b2p_set_categories", "b2p_loglik", "b2p_loglik_grad", "b2p_loglik_grad_host",
-    "b2p_set_profiling", "b2p_last_kernel_ms", "b2p_kernel_ms_stats", "b2p_get_post_partials",
+    "b2p_set_profiling", "b2p_last_kernel_ms", "b2p_kernel_ms_stats", "b2p_get_branch_partials",
 )
 
 
@@ -43,8 +43,10 @@ class _Info(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in (
         "n_tips", "n_patterns", "n_categories", "n_states", "precision", "warps_per_block",
         "cols_per_tile", "n_tiles", "grid_blocks", "blocks_per_sm", "n_sms", "post_rounds",
-        "tree_depth", "regs_per_thread")] + [(n, ctypes.c_int64) for n in (
-            "device_bytes", "alg_bytes_loglik", "alg_bytes_grad")]
+        "tree_depth", "regs_per_thread", "tasks_per_round", "pre_rounds", "ring_blocks",
+        "smem_bytes")] + [(n, ctypes.c_int64) for n in (
+            "device_bytes", "alg_bytes_loglik", "alg_bytes_grad", "ring_reads_post", "ring_reads_pre",
+            "pre_global_blocks")]
 
 
 def library_path() -> str:
@@ -83,7 +85,7 @@ def load_library():
     lib.b2p_set_profiling.argtypes = [vp, ctypes.c_int]
     lib.b2p_last_kernel_ms.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
     lib.b2p_kernel_ms_stats.argtypes = [vp, dp, ctypes.POINTER(ctypes.c_int32)]
-    lib.b2p_get_post_partials.argtypes = [vp, ctypes.c_int32, dp]
+    lib.b2p_get_branch_partials.argtypes = [vp, ctypes.c_int32, dp]
     for name in EXPORTED_SYMBOLS:
         if name != "b2p_last_error":
             getattr(lib, name).restype = ctypes.c_int
@@ -217,8 +219,9 @@ class Engine:
                     "b2p_kernel_ms_stats")
         return float(tot.value), int(n.value)
 
-    def post_partials(self, node: int) -> np.ndarray:
+    def branch_partials(self, node: int) -> np.ndarray:
+        """P_node x_node of an internal non-root node as [P, K, 4] (debug / tests)."""
         out = np.empty((self.n_patterns, self.n_categories, 4))
-        self._check(self._lib.b2p_get_post_partials(self._h, int(node), _dptr(out)),
-                    "b2p_get_post_partials")
+        self._check(self._lib.b2p_get_branch_partials(self._h, int(node), _dptr(out)),
+                    "b2p_get_branch_partials")
         return out

@@ -1,0 +1,71 @@
+// Small kernels around the traversal (sm_100a): SURVEY.md §8(a) rows a2, a4, a6.
+//   K1 transition_kernel   P(t) for every branch x category, one launch      (row a2)
+//   K4 reduce_kernel       deterministic sum of per-CTA partial results      (rows a4, a6)
+#pragma once
+#include "b2p_device.cuh"
+
+namespace b2p {
+
+constexpr int kMaxCat = 32;
+
+struct ModelParams {  // passed by value to K1
+  double evec[16], ivec[16], evals[4];
+  double rates[kMaxCat];
+};
+
+// ---------------------------------------------------------------------------- K1
+// One thread per (branch, category, matrix entry).  P = V e^{lambda r t} V^-1, computed
+// in fp64, stored as T.  (dP/dt = r Q P is never formed: the pre-order kernel applies Q
+// from the constant bank to P x instead.)
+template <typename T>
+__global__ void transition_kernel(ModelParams m, const double* __restrict__ bl, int n_branches,
+                                  int n_cat, T* __restrict__ pmat) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int total = n_branches * n_cat * 16;
+  if (idx >= total) return;
+  const int e = idx & 15, bk = idx >> 4;
+  const int k = bk % n_cat, b = bk / n_cat;
+  const int i = e >> 2, l = e & 3;
+  const double t = bl[b] * m.rates[k];
+  double p = 0.0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) p += m.evec[i * 4 + j] * m.ivec[j * 4 + l] * exp(m.evals[j] * t);
+  pmat[idx] = (T)p;
+}
+
+// ---------------------------------------------------------------------------- K4
+// grad[b] = sum_g gpart[g][b];  logl = sum_g lpart[g].  Fixed summation order.
+__global__ void __launch_bounds__(512) reduce_kernel(const double* __restrict__ gpart,
+                                                     const double* __restrict__ lpart, int n_parts,
+                                                     int n_branches, double* __restrict__ grad,
+                                                     double* __restrict__ logl) {
+  __shared__ double sh[16][33];
+  const int x = threadIdx.x & 31, y = threadIdx.x >> 5;
+  if (blockIdx.x == gridDim.x - 1) {  // last block: log-likelihood
+    double s = 0.0;
+    for (int g = threadIdx.x; g < n_parts; g += 512) s += lpart[g];
+    s = warp_sum(s);
+    if (x == 0) sh[y][0] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t = 0.0;
+      for (int i = 0; i < 16; ++i) t += sh[i][0];
+      *logl = t;
+    }
+    return;
+  }
+  const int b = blockIdx.x * 32 + x;
+  double s = 0.0;
+  if (b < n_branches)
+    for (int g = y; g < n_parts; g += 16) s += gpart[(size_t)g * n_branches + b];
+  sh[y][x] = s;
+  __syncthreads();
+  if (y == 0 && b < n_branches) {
+    double t = 0.0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) t += sh[i][x];
+    grad[b] = t;
+  }
+}
+
+}  // namespace b2p

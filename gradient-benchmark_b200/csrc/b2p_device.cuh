@@ -116,6 +116,20 @@ __device__ __forceinline__ T group_max(T v, int lane, int kk) {
   return s;
 }
 
+template <int K>
+__device__ __forceinline__ int group_max_int(int v, int lane, int kk) {
+  if (K == 1) return v;
+  if (K == 2 || K == 4 || K == 8 || K == 16 || K == 32) {
+#pragma unroll
+    for (int o = 1; o < K; o <<= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+  }
+  const int base = lane - lane % kk;
+  int s = v;
+  for (int j = 0; j < kk; ++j) s = max(s, __shfl_sync(0xffffffffu, v, (base + j) & 31));
+  return s;
+}
+
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -21,7 +21,8 @@ namespace b2p {
 
 struct WaveGeometry {
   int nt = 0, ct = 0, ts = 0, cpw = 32, wn = 0, ring_cap = 0, pj = 0, n_tiles = 0, grid = 0;
-  int off_ent = 0, off_mats = 0, off_stage = 0, off_ring = 0, off_part = 0, off_scount = 0;
+  int off_task = 0, off_ahead = 0, off_mats = 0, off_stage = 0, off_ring = 0, off_part = 0, off_scount = 0;
+  int blk = 0;  // bytes of one block (ct columns)
   size_t smem = 0;
 };
 
@@ -30,7 +31,8 @@ inline int align16(int x) { return (x + 15) & ~15; }
 // Choose the tile width and thread geometry.  elem = sizeof(T).  Returns false if even
 // the smallest block size does not fit.
 inline bool plan_geometry(int n_tips, int n_cols, int K, int elem, int n_sms, size_t smem_max, int nt_force,
-                          int ct_force, WaveGeometry& g) {
+                          int ct_force, int ctas_per_sm, WaveGeometry& g) {
+  n_sms *= ctas_per_sm;
   const bool packed = (32 % K) == 0;
   const int cpw = packed ? 32 : (32 / K) * K;
   const int ct_max = 128, ct_min = (8 + K - 1) / K * K;
@@ -41,7 +43,6 @@ inline bool plan_geometry(int n_tips, int n_cols, int K, int elem, int n_sms, si
   ct = std::min(ct, std::max(K, (n_cols + K - 1) / K * K));
   if (ct_force > 0) ct = std::max(K, ct_force / K * K);
   const int ts = packed ? ct : ((ct + cpw - 1) / cpw) * 32;
-  const int planes = elem == 8 ? 2 : 1;
   const int mat_bytes = elem == 8 ? 144 : 80;
   const int nts[4] = {1024, 768, 512, 256};
   for (int nt : nts) {
@@ -51,16 +52,18 @@ inline bool plan_geometry(int n_tips, int n_cols, int K, int elem, int n_sms, si
     if (wn < 1) continue;
     const int pj = (ts + 30) / 32 + 1;
     int off = 0;
-    g.off_ent = off; off += align16(3 * wn * 32);
+    const int blk = ct * 4 * elem;
+    g.off_task = off; off += 2 * wn * 32;
+    g.off_ahead = off; off += 2 * wn * 32;
     g.off_mats = off; off += align16(2 * wn * 3 * K * mat_bytes);
-    g.off_stage = off; off += 3 * nt * 16 * planes;
+    g.off_stage = off; off += 3 * wn * blk;
     g.off_part = off; off += align16(2 * wn * (16 + 16 * pj));
     g.off_scount = off; off += align16(ct * 4);
     g.off_ring = off;
-    const int blk = ct * 4 * elem;
     const long long left = (long long)smem_max - off;
     int ring_cap = (int)std::min<long long>(left / (2LL * blk), 2LL * wn);
     if (ring_cap < wn) continue;
+    g.blk = blk;
     g.nt = nt; g.ct = ct; g.ts = ts; g.cpw = cpw; g.wn = wn; g.ring_cap = ring_cap; g.pj = pj;
     g.n_tiles = (n_cols + ct - 1) / ct;
     g.grid = std::min(g.n_tiles, n_sms);
@@ -71,20 +74,37 @@ inline bool plan_geometry(int n_tips, int n_cols, int K, int elem, int n_sms, si
 }
 
 struct WaveSchedule {
-  std::vector<WaveEntry> post, pre;
+  std::vector<WaveTask> post_task, pre_task;
+  std::vector<WaveAhead> post_ahead, pre_ahead;
   int rounds_post = 0, rounds_pre = 0, depth = 0;
   long long ring_reads_post = 0, ring_reads_pre = 0, pre_global_blocks = 0;
 };
 
-inline WaveEntry idle_entry() {
-  WaveEntry e{};
-  e.v = e.l = e.r = -1;
-  e.kl = e.kr = e.kv = KIND_TIP;
-  return e;
+inline WaveTask idle_task() {
+  WaveTask t{};
+  t.l = t.r = -1;
+  t.src_l = t.src_r = t.src_v = t.dst0 = t.dst1 = kNoBlock;
+  return t;
+}
+inline WaveAhead idle_ahead() {
+  WaveAhead a{};
+  a.g_l = a.g_r = a.g_v = kNoFetch;
+  a.m[0] = a.m[1] = a.m[2] = -1;
+  return a;
 }
 
 // triples: [N-1][3] (node, left, right), node ids N..2N-2 in post-order (validated here).
-inline bool plan_schedule(int N, const int32_t* triples, int wn, int ring_cap, WaveSchedule& out, std::string& why) {
+inline bool plan_schedule(int N, int P, int K, const int32_t* triples, const WaveGeometry& g, WaveSchedule& out,
+                          std::string& why) {
+  const int wn = g.wn, ring_cap = g.ring_cap;
+  const unsigned n_cols = (unsigned)P * (unsigned)K;
+  if ((unsigned long long)(N - 1) * n_cols > 0xFFFFFFF0ull || (unsigned long long)N * P > 0xFFFFFFF0ull) {
+    why = "problem too large for 32-bit column offsets";
+    return false;
+  }
+  auto ring_off = [&](int round, int idx) { return (unsigned short)((g.off_ring + ((round & 1) * ring_cap + idx) * g.blk) / 16); };
+  auto stage_off = [&](int op, int slot) { return (unsigned short)((g.off_stage + (op * wn + slot) * g.blk) / 16); };
+  auto gcol = [&](int node) { return (unsigned)(node - N) * n_cols; };
   const int n_nodes = 2 * N - 1, root = 2 * N - 2;
   std::vector<int> left(n_nodes, -1), right(n_nodes, -1), parent(n_nodes, -1);
   std::vector<char> seen(n_nodes, 0);
@@ -135,21 +155,25 @@ inline bool plan_schedule(int N, const int32_t* triples, int wn, int ring_cap, W
       ++r;
     }
     out.rounds_post = r;
-    out.post.assign((size_t)r * wn, idle_entry());
+    out.post_task.assign((size_t)r * wn, idle_task());
+    out.post_ahead.assign((size_t)r * wn, idle_ahead());
     for (int v = N; v < n_nodes; ++v) {
-      WaveEntry& e = out.post[(size_t)round_post[v] * wn + slot_post[v]];
-      e.v = v; e.l = left[v]; e.r = right[v];
-      auto route = [&](int c, unsigned char& kind, unsigned short& ring_idx) {
-        if (c < N) { kind = KIND_TIP; return; }
-        if (round_post[c] == round_post[v] - 1) { kind = KIND_RING; ring_idx = (unsigned short)slot_post[c]; ++out.ring_reads_post; }
-        else kind = KIND_GLOBAL;
+      const int rv = round_post[v], sv = slot_post[v];
+      WaveTask& t = out.post_task[(size_t)rv * wn + sv];
+      WaveAhead& a = out.post_ahead[(size_t)rv * wn + sv];
+      t.l = left[v]; t.r = right[v];
+      auto route = [&](int c, int op, unsigned short& src, unsigned& fetch, int& mat) {
+        if (c < N) { src = kNoBlock; fetch = (unsigned)c * (unsigned)P; a.kinds |= 1u << op; mat = c; return; }
+        if (round_post[c] == rv - 1) { src = ring_off(rv - 1, slot_post[c]); ++out.ring_reads_post; }
+        else { src = stage_off(op, sv); fetch = gcol(c); }
       };
-      route(e.l, e.kl, e.ring_l);
-      route(e.r, e.kr, e.ring_r);
-      e.kv = KIND_ROOT;
-      if (v != root) {
-        e.flags = F_O0_GLOBAL;  // the pre-order pass always reads m_v from global memory
-        if (round_post[parent[v]] == round_post[v] + 1) { e.flags |= F_O0_RING; e.ring_o0 = (unsigned short)slot_post[v]; }
+      route(t.l, 0, t.src_l, a.g_l, a.m[1]);
+      route(t.r, 1, t.src_r, a.g_r, a.m[2]);
+      if (v == root) t.flags = TF_ROOT;
+      else {
+        a.m[0] = v;
+        t.gout0 = gcol(v);  // the pre-order pass always reads m_v from global memory
+        if (round_post[parent[v]] == rv + 1) t.dst0 = ring_off(rv, sv);
       }
     }
   }
@@ -186,32 +210,45 @@ inline bool plan_schedule(int N, const int32_t* triples, int wn, int ring_cap, W
       ++r;
     }
     out.rounds_pre = r;
-    out.pre.assign((size_t)r * wn, idle_entry());
+    out.pre_task.assign((size_t)r * wn, idle_task());
+    out.pre_ahead.assign((size_t)r * wn, idle_ahead());
     std::vector<int> ring_next(r, 0);  // ring blocks handed out per producer round
     for (int v = N; v < n_nodes; ++v) {
-      WaveEntry& e = out.pre[(size_t)round_pre[v] * wn + slot_pre[v]];
-      e.v = v; e.l = left[v]; e.r = right[v];
-      e.kl = e.l < N ? KIND_TIP : KIND_GLOBAL;
-      e.kr = e.r < N ? KIND_TIP : KIND_GLOBAL;
-      if (v == root) e.kv = KIND_ROOT;
+      const int rv = round_pre[v], sv = slot_pre[v];
+      WaveTask& t = out.pre_task[(size_t)rv * wn + sv];
+      WaveAhead& a = out.pre_ahead[(size_t)rv * wn + sv];
+      t.l = left[v]; t.r = right[v];
+      a.m[1] = t.l; a.m[2] = t.r;
+      for (int op = 0; op < 2; ++op) {
+        const int c = op ? t.r : t.l;
+        unsigned short& src = op ? t.src_r : t.src_l;
+        unsigned& fetch = op ? a.g_r : a.g_l;
+        if (c < N) { src = kNoBlock; fetch = (unsigned)c * (unsigned)P; a.kinds |= 1u << op; }
+        else { src = stage_off(op, sv); fetch = gcol(c); t.flags |= op ? TF_INT_R : TF_INT_L; }
+      }
+      if (v == root) t.flags |= TF_ROOT;
     }
     // route u_c from each producer (parent task) to its consumer (child task)
     for (int v = N; v < n_nodes; ++v) {
-      WaveEntry& e = out.pre[(size_t)round_pre[v] * wn + slot_pre[v]];
+      const int rv = round_pre[v];
+      WaveTask& t = out.pre_task[(size_t)rv * wn + slot_pre[v]];
       for (int side = 0; side < 2; ++side) {
-        const int c = side ? e.r : e.l;
+        const int c = side ? t.r : t.l;
         if (c < N) continue;
-        WaveEntry& ce = out.pre[(size_t)round_pre[c] * wn + slot_pre[c]];
-        if (round_pre[c] == round_pre[v] + 1) {
-          const int idx = ring_next[round_pre[v]]++;
+        const int rc = round_pre[c], sc = slot_pre[c];
+        WaveTask& ct = out.pre_task[(size_t)rc * wn + sc];
+        WaveAhead& ca = out.pre_ahead[(size_t)rc * wn + sc];
+        if (rc == rv + 1) {
+          const int idx = ring_next[rv]++;
           if (idx >= ring_cap) { why = "internal error: ring budget exceeded"; return false; }
-          ce.kv = KIND_RING; ce.ring_v = (unsigned short)idx;
-          if (side) { e.flags |= F_O1_RING; e.ring_o1 = (unsigned short)idx; }
-          else { e.flags |= F_O0_RING; e.ring_o0 = (unsigned short)idx; }
+          ct.src_v = ring_off(rv, idx);
+          (side ? t.dst1 : t.dst0) = ring_off(rv, idx);
           ++out.ring_reads_pre;
         } else {
-          ce.kv = KIND_GLOBAL;
-          e.flags |= side ? F_O1_GLOBAL : F_O0_GLOBAL;
+          ct.src_v = stage_off(2, sc);
+          ca.g_v = gcol(c);
+          t.flags |= side ? TF_G1 : TF_G0;
+          (side ? t.gout1 : t.gout0) = gcol(c);
           ++out.pre_global_blocks;
         }
       }

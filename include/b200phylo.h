@@ -53,24 +53,31 @@ typedef struct b2p_config {
   int32_t n_states;     /* 4 (nucleotide); other sizes: B2P_ERR_UNSUPPORTED */
   int32_t precision;    /* B2P_PRECISION_F64 | B2P_PRECISION_F32 (partials / matrices) */
   int32_t device;       /* CUDA device ordinal */
-  int32_t warps_per_block; /* 0 = auto; schedule width W (nodes in flight per tile) */
+  int32_t warps_per_block; /* 0 = auto; threads per CTA / 32 (32, 24, 16 or 8) */
   int32_t flags;        /* reserved, 0 */
 } b2p_config;
 
 typedef struct b2p_info {
   int32_t n_tips, n_patterns, n_categories, n_states, precision;
-  int32_t warps_per_block;  /* W */
-  int32_t cols_per_tile;    /* (pattern,category) columns one warp carries */
+  int32_t warps_per_block;  /* threads per CTA / 32 */
+  int32_t cols_per_tile;    /* (pattern,category) columns one CTA walks the tree for at a time */
   int32_t n_tiles;          /* column tiles = independent traversals */
   int32_t grid_blocks;      /* persistent CTAs launched */
   int32_t blocks_per_sm;    /* residency the launch was sized for */
   int32_t n_sms;
-  int32_t post_rounds;      /* schedule length of one pass (pre-order is its reverse) */
+  int32_t post_rounds;      /* schedule length of the post-order pass */
   int32_t tree_depth;       /* longest root-to-cherry path, in internal nodes */
   int32_t regs_per_thread;  /* of the traversal kernel in use */
+  int32_t tasks_per_round;  /* node tasks a CTA executes side by side */
+  int32_t pre_rounds;       /* schedule length of the pre-order pass */
+  int32_t ring_blocks;      /* shared-memory ring capacity per round parity */
+  int32_t smem_bytes;       /* dynamic shared memory per CTA */
   int64_t device_bytes;     /* scratch owned by the instance */
   int64_t alg_bytes_loglik; /* (2N-3)U + N*P */
   int64_t alg_bytes_grad;   /* (5N-9)U + 2*N*P */
+  int64_t ring_reads_post;  /* operand blocks served from shared memory instead of L2/HBM */
+  int64_t ring_reads_pre;
+  int64_t pre_global_blocks; /* pre-order blocks that had to go through global memory */
 } b2p_info;
 
 /* BEAGLE: beagleCreateInstance / beagleFinalizeInstance. */
@@ -83,8 +90,8 @@ int b2p_get_info(const b2p_instance* h, b2p_info* out);
 /* Tree topology: h_triples int32 [N-1][3] rows (node, left, right) in post-order.
  * Fed by "tree_model" (/root/reference/flu_H3N2/phylotorch-JC69.template:14-44) and
  * `-t <newick>` (/root/reference/modules/micro.nf:20,47).  BEAGLE: the operations
- * array of beagleUpdatePartials / beagleUpdatePrePartials.  Builds the level-free
- * list schedule used by both passes. */
+ * array of beagleUpdatePartials / beagleUpdatePrePartials.  Builds the static
+ * schedules of both passes (list scheduling, Hu's level rule). */
 int b2p_set_topology(b2p_instance* h, const int32_t* h_triples);
 
 /* Tip data: h_masks uint8 [N][P], bit i set = state i compatible (A=1,C=2,G=4,T=8;
@@ -137,9 +144,10 @@ int b2p_last_kernel_ms(b2p_instance* h, float* ms_out);
  * enabled (the most recent 1024 at most) and their count; synchronises on them. */
 int b2p_kernel_ms_stats(b2p_instance* h, double* total_ms, int32_t* n_launches);
 
-/* Debug / test access: copy the post-order partials of internal node `node` as
- * double [P][K][S] (converted from the working precision) into h_out. */
-int b2p_get_post_partials(b2p_instance* h, int32_t node, double* h_out);
+/* Debug / test access: copy what internal non-root node `node` sent to its parent in
+ * the last evaluation, m = P_node x_node (x_node = post-order partial, possibly rescaled
+ * by a power of two per pattern), as double [P][K][S] into h_out.  BEAGLE: beagleGetPartials. */
+int b2p_get_branch_partials(b2p_instance* h, int32_t node, double* h_out);
 
 #ifdef __cplusplus
 }

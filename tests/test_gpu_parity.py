@@ -123,7 +123,8 @@ def test_zero_length_branches():
     _check(w)
 
 
-def test_post_partials_match_oracle():
+def test_branch_partials_match_oracle():
+    """What a node sends to its parent, P_v x_v, against the oracle's post-order partials."""
     from oracle import oracle
     w = make_workload("hky_g4_flu", n_tips=12, n_patterns=90)
     eng = make_engine(w)
@@ -131,9 +132,9 @@ def test_post_partials_match_oracle():
     e = w.eigen_args()
     pm = oracle.transition_matrices(w.tree.branch_lengths, e[0], e[1], e[2], e[4])
     post, _ = oracle.post_order(w.tree.post_triples, w.patterns.partials(), pm)
-    for node in (w.n_tips, w.n_tips + 3, 2 * w.n_tips - 2):
-        got = eng.post_partials(node)  # [P, K, 4], unnormalised (lazy scaling never fires here)
-        ref = np.transpose(post[node], (1, 0, 2))
+    for node in (w.n_tips, w.n_tips + 3, 2 * w.n_tips - 3):
+        got = eng.branch_partials(node)  # [P, K, 4]
+        ref = np.einsum("kij,kpj->pki", pm[node], post[node])
         ratio = got / ref
         assert np.allclose(ratio, ratio[:, :1, :1], rtol=1e-11)  # equal up to the per-pattern scale
     eng.close()
