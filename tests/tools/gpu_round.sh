@@ -1,6 +1,7 @@
 #!/bin/bash
 # One GPU call: tests, smoke, bench, then ncu launch list + full capture of the traversal kernel.
 mkdir -p gpurun_out
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.log 2>&1; nproc >> gpurun_out/smi.log
 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
 tail -15 gpurun_out/pytest_gpu.log
 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -4 gpurun_out/smoke.log
@@ -11,5 +12,5 @@ $BENCH_SMALL > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/launches.csv $BENCH_SMALL > gpurun_out/ncu1.log 2>&1
 echo "ncu launches rc=$?"
 $BENCH_SMALL > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:traverse -s 3 -c 2 -f -o gpurun_out/prof $BENCH_SMALL > gpurun_out/ncu2.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:wave_kernel -s 3 -c 1 -f -o gpurun_out/prof $BENCH_SMALL > gpurun_out/ncu2.log 2>&1
 echo "ncu full rc=$?"; ls -la gpurun_out
