@@ -43,10 +43,10 @@ class _Info(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in (
         "n_tips", "n_patterns", "n_categories", "n_states", "precision", "warps_per_block",
         "cols_per_tile", "n_tiles", "grid_blocks", "blocks_per_sm", "n_sms", "post_rounds",
-        "tree_depth", "regs_per_thread", "tasks_per_round", "pre_rounds", "ring_blocks",
-        "smem_bytes")] + [(n, ctypes.c_int64) for n in (
-            "device_bytes", "alg_bytes_loglik", "alg_bytes_grad", "ring_reads_post", "ring_reads_pre",
-            "pre_global_blocks")]
+        "tree_depth", "regs_per_thread", "tasks_per_round", "pre_rounds", "pool_blocks",
+        "smem_bytes", "copy_depth", "reserved0")] + [(n, ctypes.c_int64) for n in (
+            "device_bytes", "alg_bytes_loglik", "alg_bytes_grad", "resident_reads", "block_loads",
+            "block_stores")]
 
 
 def library_path() -> str:

@@ -11,6 +11,7 @@
 #include "../../include/b200phylo.h"
 #include "b2p_aux.cuh"
 #include "b2p_plan.h"
+#include "b2p_walk.cuh"
 
 using namespace b2p;
 
@@ -21,22 +22,18 @@ struct b2p_instance {
   int n_sms = 0, regs = 0, ctas_per_sm = 1;
   bool have_topology = false, have_tips = false, have_weights = false, have_eigen = false,
        have_cats = false;
-  // geometry + schedules of the wave kernel
-  WaveGeometry wg;
-  int rounds_post = 0, rounds_pre = 0, tree_depth = 0;
-  long long ring_post = 0, ring_pre = 0, pre_global = 0;
-  const void* k_grad = nullptr;
-  const void* k_eval = nullptr;
+  // geometry + plan of the traversal kernel
+  WalkGeometry wg;
+  WalkPlan plan;  // records are released after upload; the statistics stay
+  const void* kernel = nullptr;
   // device scratch
-  WaveTask* d_post_task = nullptr;
-  WaveAhead* d_post_ahead = nullptr;
-  WaveTask* d_pre_task = nullptr;
-  WaveAhead* d_pre_ahead = nullptr;
-  uint8_t* d_tips = nullptr;
+  unsigned char* d_records = nullptr;
+  int* d_mat_dst = nullptr;
+  void* d_mats = nullptr;  // [rounds][wn][3][K] matrices in schedule order
+  uint8_t* d_tips = nullptr;  // [tile][N][ct_pad]
   double* d_weights = nullptr;
-  void* d_pmat = nullptr;
-  void* d_msg = nullptr;   // [N-1][P*K][4] messages m_v = P_v x_v
-  void* d_pre = nullptr;   // [N-1][P*K][4] pre-order partials that are read >= 2 rounds later
+  void* d_msg = nullptr;   // [tile][N-1] blocks: messages m_v = P_v x_v
+  void* d_pre = nullptr;   // [tile][N-1] blocks: pre-order partials that left shared memory
   double* d_lpart = nullptr;
   double* d_gpart = nullptr;
   double* d_bl_stage = nullptr;   // for the host-buffer entry point
@@ -84,27 +81,21 @@ static int dev_alloc(b2p_instance* h, T** p, size_t n_bytes) {
 }
 
 // ---------------------------------------------------------------- kernel selection
-template <typename T, int K, int NT, int MINB>
-static void wave_pick(const void** grad, const void** eval) {
-  *grad = (const void*)wave_kernel<T, K, NT, MINB, true>;
-  *eval = (const void*)wave_kernel<T, K, NT, MINB, false>;
-}
 template <typename T, int K>
-static bool wave_select_nt(int nt, int minb, const void** grad, const void** eval) {
-  if (minb == 1 && nt == 1024) wave_pick<T, K, 1024, 1>(grad, eval);
-  else if (minb == 1 && nt == 768) wave_pick<T, K, 768, 1>(grad, eval);
-  else if (minb == 1 && nt == 512) wave_pick<T, K, 512, 1>(grad, eval);
-  else if (minb == 1 && nt == 256) wave_pick<T, K, 256, 1>(grad, eval);
-  else if (minb == 2 && nt == 512) wave_pick<T, K, 512, 2>(grad, eval);
-  else if (minb == 2 && nt == 256) wave_pick<T, K, 256, 2>(grad, eval);
-  else return false;
-  return true;
+static const void* walk_select_nt(int nt) {
+  switch (nt) {
+    case 1024: return (const void*)walk_kernel<T, K, 1024>;
+    case 768: return (const void*)walk_kernel<T, K, 768>;
+    case 512: return (const void*)walk_kernel<T, K, 512>;
+    case 256: return (const void*)walk_kernel<T, K, 256>;
+  }
+  return nullptr;
 }
 template <typename T>
-static bool wave_select(int K, int nt, int minb, const void** grad, const void** eval) {
-  if (K == 1) return wave_select_nt<T, 1>(nt, minb, grad, eval);
-  if (K == 4) return wave_select_nt<T, 4>(nt, minb, grad, eval);
-  return wave_select_nt<T, 0>(nt, minb, grad, eval);
+static const void* walk_select(int K, int nt) {
+  if (K == 1) return walk_select_nt<T, 1>(nt);
+  if (K == 4) return walk_select_nt<T, 4>(nt);
+  return walk_select_nt<T, 0>(nt);
 }
 
 static size_t elem_size(const b2p_instance* h) {
@@ -122,8 +113,8 @@ const char* b2p_last_error(const b2p_instance* h) {
 int b2p_destroy(b2p_instance* h) {
   if (!h) return B2P_OK;
   cudaSetDevice(h->cfg.device);
-  cudaFree(h->d_post_task); cudaFree(h->d_post_ahead); cudaFree(h->d_pre_task); cudaFree(h->d_pre_ahead);
-  cudaFree(h->d_tips); cudaFree(h->d_weights); cudaFree(h->d_pmat); cudaFree(h->d_msg); cudaFree(h->d_pre);
+  cudaFree(h->d_records); cudaFree(h->d_mat_dst); cudaFree(h->d_mats);
+  cudaFree(h->d_tips); cudaFree(h->d_weights); cudaFree(h->d_msg); cudaFree(h->d_pre);
   cudaFree(h->d_lpart); cudaFree(h->d_gpart); cudaFree(h->d_bl_stage); cudaFree(h->d_out_stage);
   if (h->h_pin_in) cudaFreeHost(h->h_pin_in);
   if (h->h_pin_out) cudaFreeHost(h->h_pin_out);
@@ -174,42 +165,37 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   int rc = B2P_OK;
   auto bail = [&](int code) { std::string m = h->err; b2p_destroy(h); g_create_error = m; return code; };
 
-  // geometry: threads per CTA (warps_per_block * 32 if given), CTAs per SM, tile width
-  int nt_force = cfg->warps_per_block > 0 ? cfg->warps_per_block * 32 : 0, ct_force = 0, cps = 1;
+  // geometry: threads per CTA (warps_per_block * 32 if given), tile width, copy depth
+  int nt_force = cfg->warps_per_block > 0 ? cfg->warps_per_block * 32 : 0, ct_force = 0, depth = 1;
   if (const char* s = getenv("B2P_NT")) nt_force = atoi(s);
   if (const char* s = getenv("B2P_CT")) ct_force = atoi(s);
-  if (const char* s = getenv("B2P_CTAS_PER_SM")) cps = std::max(1, std::min(2, atoi(s)));
-  h->ctas_per_sm = cps;
-  // per-CTA budget: the opt-in maximum, or half the SM's shared memory minus the 1 KB system reservation per CTA
-  const size_t smem_budget = cps == 1 ? (size_t)prop.sharedMemPerBlockOptin - 1024
-                                      : (size_t)prop.sharedMemPerMultiprocessor / 2 - 2048;
-  if (cps == 2 && nt_force == 0) nt_force = 512;
-  if (!plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms, smem_budget, nt_force, ct_force, cps, h->wg)) {
+  if (const char* s = getenv("B2P_DEPTH")) depth = atoi(s);
+  h->ctas_per_sm = 1;
+  const size_t smem_budget = (size_t)prop.sharedMemPerBlockOptin - 1024;  // static shared + reservation
+  if (!plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms, smem_budget, nt_force, ct_force, 1, depth, h->wg)) {
     fail(h, B2P_ERR_UNSUPPORTED, "b2p_create: no kernel geometry fits shared memory (K=%d, threads=%d)", K, nt_force);
     return bail(B2P_ERR_UNSUPPORTED);
   }
-  const bool ok = (cfg->precision == B2P_PRECISION_F32) ? wave_select<float>(K, h->wg.nt, cps, &h->k_grad, &h->k_eval)
-                                                        : wave_select<double>(K, h->wg.nt, cps, &h->k_grad, &h->k_eval);
-  if (!ok) { fail(h, B2P_ERR_ARG, "b2p_create: no kernel for %d threads x %d CTAs/SM", h->wg.nt, cps); return bail(B2P_ERR_ARG); }
-  for (const void* k : {h->k_grad, h->k_eval}) {
-    if ((e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->wg.smem)) != cudaSuccess) {
-      fail(h, B2P_ERR_CUDA, "cudaFuncSetAttribute(smem=%zu): %s", h->wg.smem, cudaGetErrorString(e));
-      return bail(B2P_ERR_CUDA);
-    }
+  h->kernel = (cfg->precision == B2P_PRECISION_F32) ? walk_select<float>(K, h->wg.nt) : walk_select<double>(K, h->wg.nt);
+  if (!h->kernel) { fail(h, B2P_ERR_ARG, "b2p_create: no kernel for %d threads", h->wg.nt); return bail(B2P_ERR_ARG); }
+  if ((e = cudaFuncSetAttribute(h->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->wg.smem)) != cudaSuccess) {
+    fail(h, B2P_ERR_CUDA, "cudaFuncSetAttribute(smem=%zu): %s", h->wg.smem, cudaGetErrorString(e));
+    return bail(B2P_ERR_CUDA);
   }
   cudaFuncAttributes fa;
-  if ((e = cudaFuncGetAttributes(&fa, h->k_grad)) != cudaSuccess) {
+  if ((e = cudaFuncGetAttributes(&fa, h->kernel)) != cudaSuccess) {
     fail(h, B2P_ERR_CUDA, "cudaFuncGetAttributes: %s (was the library built for sm_100a?)", cudaGetErrorString(e));
     return bail(B2P_ERR_CUDA);
   }
   h->regs = fa.numRegs;
 
   const size_t n_br = 2 * (size_t)N - 2;
-  if ((rc = dev_alloc(h, &h->d_tips, (size_t)N * P))) return bail(rc);
+  const size_t part_bytes = (size_t)h->wg.n_tiles * (size_t)(N - 1) * (size_t)h->wg.blk;
+  if ((rc = dev_alloc(h, &h->d_tips, (size_t)h->wg.n_tiles * N * h->wg.ct_pad))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_weights, sizeof(double) * P))) return bail(rc);
-  if ((rc = dev_alloc(h, (char**)&h->d_pmat, n_br * K * 16 * es))) return bail(rc);
-  if ((rc = dev_alloc(h, (char**)&h->d_msg, (size_t)(N - 1) * n_cols * 4 * es))) return bail(rc);
-  if ((rc = dev_alloc(h, (char**)&h->d_pre, (size_t)(N - 1) * n_cols * 4 * es))) return bail(rc);
+  if ((rc = dev_alloc(h, &h->d_mat_dst, sizeof(int) * 2 * n_br))) return bail(rc);
+  if ((rc = dev_alloc(h, (char**)&h->d_msg, part_bytes))) return bail(rc);
+  if ((rc = dev_alloc(h, (char**)&h->d_pre, part_bytes))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_lpart, sizeof(double) * h->wg.grid))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_gpart, sizeof(double) * (size_t)h->wg.grid * n_br))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_bl_stage, sizeof(double) * n_br))) return bail(rc);
@@ -230,21 +216,23 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
 }  // extern "C"
 
 template <typename T>
-static void fill_wave_params(const b2p_instance* h, WaveParams<T>& p) {
+static void fill_walk_params(const b2p_instance* h, bool grad, WalkParams<T>& p) {
   const int N = h->cfg.n_tips, K = h->cfg.n_categories, P = h->cfg.n_patterns;
-  const WaveGeometry& g = h->wg;
-  p.n_tips = N; p.n_patterns = P; p.n_cat = K; p.n_cols = P * K;
-  p.ct = g.ct; p.ts = g.ts; p.cpw = g.cpw; p.wn = g.wn;
-  p.n_tiles = g.n_tiles; p.rounds_post = h->rounds_post; p.rounds_pre = h->rounds_pre;
-  p.n_branches = 2 * N - 2;
-  p.pj = g.pj; p.plane = g.ct * 16; p.stage_op_stride = g.wn * g.blk; p.pad0 = 0;
-  p.off_task = g.off_task; p.off_ahead = g.off_ahead; p.off_mats = g.off_mats; p.off_stage = g.off_stage;
-  p.off_part = g.off_part; p.off_scount = g.off_scount;
-  p.post_task = h->d_post_task; p.post_ahead = h->d_post_ahead;
-  p.pre_task = h->d_pre_task; p.pre_ahead = h->d_pre_ahead;
-  p.tips = h->d_tips; p.weights = h->d_weights; p.pmat = (const T*)h->d_pmat;
-  p.msg = (T*)h->d_msg; p.pre_g = (T*)h->d_pre;
-  p.lpart = h->d_lpart; p.gpart = h->d_gpart;
+  const WalkGeometry& g = h->wg;
+  p.n_tiles = g.n_tiles; p.rounds_run = grad ? h->plan.rounds : h->plan.rounds_post;
+  p.n_branches = 2 * N - 2; p.n_cat = K; p.n_cols = P * K; p.n_patterns = P;
+  p.ct = g.ct; p.ts = g.ts; p.cpw = g.cpw; p.wn = g.wn; p.stages = g.stages; p.depth = g.depth;
+  p.blk = g.blk; p.plane = g.ct * 16; p.ct_pad = g.ct_pad; p.mat_stride = g.mat_stride;
+  p.mats_bytes = g.mats_bytes; p.cr_bytes = g.cr_bytes; p.ir_bytes = g.ir_bytes; p.tips_bytes = g.tips_bytes;
+  p.off_bar = g.off_bar; p.off_cr = g.off_cr; p.off_ir = g.off_ir; p.off_mats = g.off_mats; p.off_tips = g.off_tips;
+  p.off_gbuf = g.off_gbuf; p.off_gids = g.off_gids; p.off_scount = g.off_scount;
+  p.ir_base = h->plan.ir_base; p.boot_base = h->plan.boot_base;
+  for (int i = 0; i < 4; ++i) { p.boot_n[i] = h->plan.boot_n[i]; p.boot_tx[i] = h->plan.boot_tx[i]; }
+  p.tile_stride_part = (unsigned long long)(N - 1) * g.blk;
+  p.tile_stride_tips = (unsigned long long)N * g.ct_pad;
+  p.records = h->d_records; p.mats = (const unsigned char*)h->d_mats;
+  p.msg = (unsigned char*)h->d_msg; p.pre = (unsigned char*)h->d_pre; p.tips = h->d_tips;
+  p.weights = h->d_weights; p.lpart = h->d_lpart; p.gpart = h->d_gpart;
   for (int i = 0; i < 4; ++i) p.freqs[i] = h->freqs[i];
   for (int i = 0; i < 16; ++i) p.q[i] = (T)h->qmat[i];
   for (int k = 0; k < kMaxCatW; ++k) {
@@ -259,14 +247,14 @@ static cudaError_t launch_eval(b2p_instance* h, const double* d_bl, double* d_lo
   const int N = h->cfg.n_tips, K = h->cfg.n_categories;
   const int n_br = 2 * N - 2;
   const int total = n_br * K * 16;
-  transition_kernel<T><<<(total + 255) / 256, 256, 0, st>>>(h->model, d_bl, n_br, K, (T*)h->d_pmat);
+  transition_kernel<T><<<(total + 255) / 256, 256, 0, st>>>(h->model, d_bl, n_br, N, K, h->d_mat_dst,
+                                                            h->wg.mat_stride / (int)sizeof(T), (T*)h->d_mats);
   const int slot = (int)(h->prof_count % b2p_instance::kProfRing);
   if (h->profiling) cudaEventRecord(h->ev0[slot], st);
-  WaveParams<T> wp;
-  fill_wave_params(h, wp);
+  WalkParams<T> wp;
+  fill_walk_params(h, d_grad != nullptr, wp);
   void* args[] = {&wp};
-  cudaError_t e = cudaLaunchKernel(d_grad ? h->k_grad : h->k_eval, dim3(h->wg.grid), dim3(h->wg.nt), args,
-                                   h->wg.smem, st);
+  cudaError_t e = cudaLaunchKernel(h->kernel, dim3(h->wg.grid), dim3(h->wg.nt), args, h->wg.smem, st);
   if (e != cudaSuccess) return e;
   if (h->profiling) { cudaEventRecord(h->ev1[slot], st); ++h->prof_count; }
   const int nb = d_grad ? n_br : 0;
@@ -293,50 +281,64 @@ int b2p_get_info(const b2p_instance* h, b2p_info* o) {
   o->precision = h->cfg.precision;
   o->warps_per_block = h->wg.nt / 32; o->cols_per_tile = h->wg.ct; o->n_tiles = h->wg.n_tiles;
   o->grid_blocks = h->wg.grid; o->blocks_per_sm = h->ctas_per_sm; o->n_sms = h->n_sms;
-  o->post_rounds = h->rounds_post; o->tree_depth = h->tree_depth; o->regs_per_thread = h->regs;
-  o->tasks_per_round = h->wg.wn; o->pre_rounds = h->rounds_pre; o->ring_blocks = h->wg.ring_cap;
+  o->post_rounds = h->plan.rounds_post; o->tree_depth = h->plan.tree_depth; o->regs_per_thread = h->regs;
+  o->tasks_per_round = h->plan.wn_eff; o->pre_rounds = h->plan.rounds_pre; o->pool_blocks = h->wg.n_pool;
   o->smem_bytes = (int32_t)h->wg.smem;
+  o->copy_depth = h->wg.depth;
   o->device_bytes = h->device_bytes;
   o->alg_bytes_loglik = (2 * N - 3) * U + N * P;
   o->alg_bytes_grad = (5 * N - 9) * U + 2 * N * P;
-  o->ring_reads_post = h->ring_post; o->ring_reads_pre = h->ring_pre; o->pre_global_blocks = h->pre_global;
+  o->resident_reads = h->plan.resident_reads;
+  o->block_loads = h->plan.loads_msg + h->plan.loads_pre;
+  o->block_stores = h->plan.stores_msg + h->plan.stores_pre;
   return B2P_OK;
 }
 
 int b2p_set_topology(b2p_instance* h, const int32_t* h_triples) {
   if (!h || !h_triples) return h ? fail(h, B2P_ERR_ARG, "b2p_set_topology: null triples") : B2P_ERR_ARG;
-  WaveSchedule ws;
+  WalkPlan plan;
   std::string why;
-  if (!plan_schedule(h->cfg.n_tips, h->cfg.n_patterns, h->cfg.n_categories, h_triples, h->wg, ws, why))
+  if (!plan_walk_auto(h->cfg.n_tips, h_triples, h->wg, plan, why))
     return fail(h, B2P_ERR_ARG, "b2p_set_topology: %s", why.c_str());
   CU(cudaSetDevice(h->cfg.device));
   CU(cudaDeviceSynchronize());
-  cudaFree(h->d_post_task); cudaFree(h->d_post_ahead); cudaFree(h->d_pre_task); cudaFree(h->d_pre_ahead);
-  h->d_post_task = h->d_pre_task = nullptr;
-  h->d_post_ahead = h->d_pre_ahead = nullptr;
+  cudaFree(h->d_records); cudaFree(h->d_mats);
+  h->d_records = nullptr; h->d_mats = nullptr;
   h->have_topology = false;
-  auto up = [&](auto** dst, const auto& v) -> cudaError_t {
-    cudaError_t e = cudaMalloc((void**)dst, v.size() * sizeof(v[0]));
-    if (e != cudaSuccess) return e;
-    return cudaMemcpy(*dst, v.data(), v.size() * sizeof(v[0]), cudaMemcpyHostToDevice);
-  };
-  CU(up(&h->d_post_task, ws.post_task));
-  CU(up(&h->d_post_ahead, ws.post_ahead));
-  CU(up(&h->d_pre_task, ws.pre_task));
-  CU(up(&h->d_pre_ahead, ws.pre_ahead));
-  h->rounds_post = ws.rounds_post; h->rounds_pre = ws.rounds_pre; h->tree_depth = ws.depth;
-  h->ring_post = ws.ring_reads_post; h->ring_pre = ws.ring_reads_pre; h->pre_global = ws.pre_global_blocks;
+  const size_t mats_bytes = (size_t)plan.rounds * h->wg.mats_bytes;
+  CU(cudaMalloc((void**)&h->d_records, plan.records.size()));
+  CU(cudaMemcpy(h->d_records, plan.records.data(), plan.records.size(), cudaMemcpyHostToDevice));
+  CU(cudaMalloc(&h->d_mats, mats_bytes));
+  CU(cudaMemset(h->d_mats, 0, mats_bytes));
+  CU(cudaMemcpy(h->d_mat_dst, plan.mat_dst.data(), plan.mat_dst.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+  plan.records.clear(); plan.records.shrink_to_fit();
+  plan.mat_dst.clear(); plan.mat_dst.shrink_to_fit();
+  h->plan = std::move(plan);
   h->have_topology = true;
   return B2P_OK;
 }
 
 int b2p_set_tip_states(b2p_instance* h, const uint8_t* h_masks) {
   if (!h || !h_masks) return h ? fail(h, B2P_ERR_ARG, "b2p_set_tip_states: null masks") : B2P_ERR_ARG;
-  const size_t n = (size_t)h->cfg.n_tips * h->cfg.n_patterns;
+  const int N = h->cfg.n_tips, P = h->cfg.n_patterns, K = h->cfg.n_categories;
+  const size_t n = (size_t)N * P;
   for (size_t i = 0; i < n; ++i)
     if (h_masks[i] > 15) return fail(h, B2P_ERR_ARG, "b2p_set_tip_states: mask %u > 15 at %zu", h_masks[i], i);
+  // one row of ct_pad bytes per (tile, tip): the mask of each column's pattern; padding = 15 (any state)
+  const WalkGeometry& g = h->wg;
+  std::vector<uint8_t> tiled((size_t)g.n_tiles * N * g.ct_pad, 15);
+  const long long n_cols = (long long)P * K;
+  for (int tile = 0; tile < g.n_tiles; ++tile)
+    for (int tip = 0; tip < N; ++tip) {
+      uint8_t* row = tiled.data() + ((size_t)tile * N + tip) * g.ct_pad;
+      const uint8_t* src = h_masks + (size_t)tip * P;
+      for (int c = 0; c < g.ct; ++c) {
+        const long long cg = (long long)tile * g.ct + c;
+        if (cg < n_cols) row[c] = src[cg / K];
+      }
+    }
   CU(cudaSetDevice(h->cfg.device));
-  CU(cudaMemcpy(h->d_tips, h_masks, n, cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(h->d_tips, tiled.data(), tiled.size(), cudaMemcpyHostToDevice));
   h->have_tips = true;
   return B2P_OK;
 }
@@ -467,15 +469,27 @@ int b2p_get_branch_partials(b2p_instance* h, int32_t node, double* h_out) {
   const int N = h->cfg.n_tips;
   if (node < N || node >= 2 * N - 2)
     return fail(h, B2P_ERR_ARG, "b2p_get_branch_partials: node %d is not an internal non-root node", node);
-  const size_t n = (size_t)h->cfg.n_patterns * h->cfg.n_categories * 4;
+  const WalkGeometry& g = h->wg;
+  const long long n_cols = (long long)h->cfg.n_patterns * h->cfg.n_categories;
   CU(cudaSetDevice(h->cfg.device));
   CU(cudaDeviceSynchronize());
-  if (h->cfg.precision == B2P_PRECISION_F64) {
-    CU(cudaMemcpy(h_out, (const double*)h->d_msg + (size_t)(node - N) * n, n * 8, cudaMemcpyDeviceToHost));
-  } else {
-    std::vector<float> tmp(n);
-    CU(cudaMemcpy(tmp.data(), (const float*)h->d_msg + (size_t)(node - N) * n, n * 4, cudaMemcpyDeviceToHost));
-    for (size_t i = 0; i < n; ++i) h_out[i] = tmp[i];
+  std::vector<unsigned char> blk(g.blk);
+  for (int tile = 0; tile < g.n_tiles; ++tile) {
+    const unsigned char* src = (const unsigned char*)h->d_msg + ((size_t)tile * (N - 1) + (node - N)) * g.blk;
+    CU(cudaMemcpy(blk.data(), src, g.blk, cudaMemcpyDeviceToHost));
+    for (int c = 0; c < g.ct; ++c) {
+      const long long cg = (long long)tile * g.ct + c;
+      if (cg >= n_cols) break;
+      double* o = h_out + cg * 4;
+      if (h->cfg.precision == B2P_PRECISION_F64) {  // two planes of [ct][2]
+        const double* p0 = (const double*)blk.data() + 2 * c;
+        const double* p1 = (const double*)(blk.data() + (size_t)g.ct * 16) + 2 * c;
+        o[0] = p0[0]; o[1] = p0[1]; o[2] = p1[0]; o[3] = p1[1];
+      } else {
+        const float* p0 = (const float*)blk.data() + 4 * c;
+        for (int i = 0; i < 4; ++i) o[i] = p0[i];
+      }
+    }
   }
   return B2P_OK;
 }

@@ -15,11 +15,16 @@ struct ModelParams {  // passed by value to K1
 
 // ---------------------------------------------------------------------------- K1
 // One thread per (branch, category, matrix entry).  P = V e^{lambda r t} V^-1, computed
-// in fp64, stored as T.  (dP/dt = r Q P is never formed: the pre-order kernel applies Q
+// in fp64, stored as T — directly into the traversal kernel's per-round matrix bundles
+// (schedule order, so one bulk copy per round brings every matrix that round needs).
+// mat_dst[2b], mat_dst[2b+1]: the branch's matrix slot in the post- / pre-order rounds
+// (-1: not used there).  Tip branches are stored transposed: the traversal picks a COLUMN
+// of P by the tip's state.  (dP/dt = r Q P is never formed: the pre-order task applies Q
 // from the constant bank to P x instead.)
 template <typename T>
-__global__ void transition_kernel(ModelParams m, const double* __restrict__ bl, int n_branches,
-                                  int n_cat, T* __restrict__ pmat) {
+__global__ void transition_kernel(ModelParams m, const double* __restrict__ bl, int n_branches, int n_tips,
+                                  int n_cat, const int* __restrict__ mat_dst, int mat_stride_elems,
+                                  T* __restrict__ bundles) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int total = n_branches * n_cat * 16;
   if (idx >= total) return;
@@ -30,7 +35,12 @@ __global__ void transition_kernel(ModelParams m, const double* __restrict__ bl, 
   double p = 0.0;
 #pragma unroll
   for (int j = 0; j < 4; ++j) p += m.evec[i * 4 + j] * m.ivec[j * 4 + l] * exp(m.evals[j] * t);
-  pmat[idx] = (T)p;
+  const int at = b < n_tips ? l * 4 + i : e;
+#pragma unroll
+  for (int w = 0; w < 2; ++w) {
+    const int slot = mat_dst[2 * b + w];
+    if (slot >= 0) bundles[((size_t)slot * n_cat + k) * mat_stride_elems + at] = (T)p;
+  }
 }
 
 // ---------------------------------------------------------------------------- K4

@@ -1,37 +1,93 @@
-// Host-side planner of the wave kernel (b2p_wave.cuh): tile / thread geometry, shared
-// memory layout, and the static schedules of both passes with operand routing.
+// Host-side planner of the traversal kernel (b2p_walk.cuh): tile / thread geometry, the
+// shared-memory layout, the static schedule of both passes, the static allocation of the
+// shared-memory block pool, and the per-round copy lists the kernel's copy warp executes.
+// Plain C++ (also compiled by g++ for tests/tools/plan_check.cpp).
 //
-// Scheduling model.  Unit tasks (one per internal node) on WN identical slots per round.
-//   post-order pass: in-tree precedence, a parent may run the round after its last child
-//     (that child's message then comes from the ring; older ones from global memory).
-//     Hu's highest-level-first rule (level = distance from the root) is makespan-optimal.
-//   pre-order pass: out-tree precedence (a node after its parent); priority = height of the
-//     node's subtree.  A task that runs exactly one round after its parent reads u_v from
-//     the ring; the ring holds at most ring_cap blocks per round, so when the budget is
-//     spent such tasks are deferred by a round and read u_v from global memory instead.
+// Scheduling.  Unit tasks (one per internal node per pass) on wn slots per round.
+//   post-order rounds: in-tree precedence; Hu's highest-level-first rule (level = distance
+//     from the root) is makespan-optimal for unit tasks on identical slots.
+//   pre-order rounds: out-tree precedence; priority = height of the node's subtree.
+//   The two passes are concatenated into ONE round sequence, so the copy pipeline never
+//   drains between them.
+// Block pool.  Every block a round reads or writes lives in a pool block chosen here.
+//   A produced value (message m_v, pre-order partial u_c) stays resident until its last
+//   reader if the pool has room; under pressure the resident value whose next use is
+//   farthest away is dropped (Belady) and that use is served by a bulk load issued `depth`
+//   rounds ahead instead.  Messages are always stored to HBM (the pre-order pass needs all
+//   of them); pre-order partials only when they are dropped.
+// Timing rules the allocation obeys (checked by plan_check.cpp):
+//   L  a load for round f is issued at the top of round f - depth (rounds < depth: before
+//      round 0); its block must be unused from then until round f has read it.
+//   S  a store of a round-p result is issued at the top of round p + 1 and has finished
+//      reading shared memory before round p + 1 ends; the block may be rewritten from
+//      the top of round p + 2.
+//   R  a block read by tasks of round r may be rewritten from the top of round r + 1.
 #pragma once
 #include <algorithm>
+#include <climits>
+#include <cstring>
 #include <queue>
 #include <string>
 #include <vector>
 
-#include "b2p_wave.cuh"
+#include "b2p_walk_types.h"
 
 namespace b2p {
 
-struct WaveGeometry {
-  int nt = 0, ct = 0, ts = 0, cpw = 32, wn = 0, ring_cap = 0, pj = 0, n_tiles = 0, grid = 0;
-  int off_task = 0, off_ahead = 0, off_mats = 0, off_stage = 0, off_ring = 0, off_part = 0, off_scount = 0;
-  int blk = 0;  // bytes of one block (ct columns)
+struct WalkGeometry {
+  int nt = 0, ct = 0, ts = 0, cpw = 32, wn = 0, depth = 1, stages = 2, n_tiles = 0, grid = 0;
+  int elem = 8, K = 1;
+  int ct_pad = 0;      // bytes of one tip row of a tile (ct rounded up to 16)
+  int blk = 0;         // bytes of one block
+  int mat_stride = 0;  // bytes between 4x4 matrices (padded: bank shift between categories)
+  int mats_bytes = 0;  // one round's matrix bundle: wn * 3 * K matrices
+  int cr_bytes = 0;    // one round's descriptors + branch ids
+  int ir_bytes = 0;    // one round's issue record (header + max_jobs jobs)
+  int tips_bytes = 0;  // one round's tip rows: wn * 2 rows
+  int max_jobs = 0;
+  int off_bar = 0, off_cr = 0, off_ir = 0, off_mats = 0, off_tips = 0, off_gbuf = 0, off_gids = 0,
+      off_scount = 0, off_pool = 0;
+  int n_pool = 0;
   size_t smem = 0;
 };
 
 inline int align16(int x) { return (x + 15) & ~15; }
 
-// Choose the tile width and thread geometry.  elem = sizeof(T).  Returns false if even
-// the smallest block size does not fit.
+// Shared-memory layout for a given (nt, ct, wn); returns the number of pool blocks (< 0: does not fit).
+inline int layout_walk(WalkGeometry& g, size_t smem_max) {
+  const int S = g.stages, wn = g.wn, K = g.K;
+  g.blk = g.ct * 4 * g.elem;
+  g.ct_pad = align16(g.ct);
+  g.mat_stride = g.elem == 8 ? 144 : 80;
+  g.mats_bytes = wn * 3 * K * g.mat_stride;
+  g.cr_bytes = align16(wn * 16 + wn * 8);
+  g.max_jobs = 7 * wn + 3;
+  g.ir_bytes = 16 + g.max_jobs * 16;
+  g.tips_bytes = wn * 2 * g.ct_pad;
+  int off = 0;
+  g.off_bar = off; off += 64;  // up to 8 mbarriers
+  g.off_cr = off; off += S * g.cr_bytes;
+  g.off_ir = off; off += S * g.ir_bytes;
+  g.off_mats = off; off += align16(S * g.mats_bytes);
+  g.off_tips = off; off += S * g.tips_bytes;
+  g.off_gbuf = off; off += 2 * wn * g.ct * 16;
+  g.off_gids = off; off += align16(2 * wn * 8);
+  g.off_scount = off; off += align16(g.ct * 4);
+  off = (off + 127) & ~127;
+  g.off_pool = off;
+  const long long left = (long long)smem_max - off;
+  if (left < g.blk) return -1;
+  // descriptors address shared memory in 16-byte units with 16 bits
+  long long n = left / g.blk;
+  while (n > 0 && (g.off_pool + n * g.blk) / 16 > 0xFFF0) --n;
+  g.n_pool = (int)n;
+  g.smem = (size_t)g.off_pool + (size_t)g.n_pool * g.blk;
+  return g.n_pool;
+}
+
+// Choose the tile width and thread geometry.  elem = sizeof(T).
 inline bool plan_geometry(int n_tips, int n_cols, int K, int elem, int n_sms, size_t smem_max, int nt_force,
-                          int ct_force, int ctas_per_sm, WaveGeometry& g) {
+                          int ct_force, int ctas_per_sm, int depth, WalkGeometry& g) {
   n_sms *= ctas_per_sm;
   const bool packed = (32 % K) == 0;
   const int cpw = packed ? 32 : (32 / K) * K;
@@ -43,69 +99,65 @@ inline bool plan_geometry(int n_tips, int n_cols, int K, int elem, int n_sms, si
   ct = std::min(ct, std::max(K, (n_cols + K - 1) / K * K));
   if (ct_force > 0) ct = std::max(K, ct_force / K * K);
   const int ts = packed ? ct : ((ct + cpw - 1) / cpw) * 32;
-  const int mat_bytes = elem == 8 ? 144 : 80;
   const int nts[4] = {1024, 768, 512, 256};
   for (int nt : nts) {
     if (nt_force > 0 && nt != nt_force) continue;
     if (ts > nt) continue;
     int wn = std::min(std::min(nt / ts, std::max(1, n_tips - 1)), 64);
+    for (; wn >= 1; --wn) {
+      g = WalkGeometry();
+      g.nt = nt; g.ct = ct; g.ts = ts; g.cpw = cpw; g.wn = wn; g.elem = elem; g.K = K;
+      g.depth = std::max(1, std::min(depth, 3)); g.stages = g.depth + 1;
+      const int n_pool = layout_walk(g, smem_max);
+      // enough blocks for one full round of operands in flight per stage plus two rounds of results
+      if (n_pool >= std::max(3 * g.stages + 4, 4 * wn)) break;
+    }
     if (wn < 1) continue;
-    const int pj = (ts + 30) / 32 + 1;
-    int off = 0;
-    const int blk = ct * 4 * elem;
-    g.off_task = off; off += 2 * wn * 32;
-    g.off_ahead = off; off += 2 * wn * 32;
-    g.off_mats = off; off += align16(2 * wn * 3 * K * mat_bytes);
-    g.off_stage = off; off += 3 * wn * blk;
-    g.off_part = off; off += align16(2 * wn * (16 + 16 * pj));
-    g.off_scount = off; off += align16(ct * 4);
-    g.off_ring = off;
-    const long long left = (long long)smem_max - off;
-    int ring_cap = (int)std::min<long long>(left / (2LL * blk), 2LL * wn);
-    if (ring_cap < wn) continue;
-    g.blk = blk;
-    g.nt = nt; g.ct = ct; g.ts = ts; g.cpw = cpw; g.wn = wn; g.ring_cap = ring_cap; g.pj = pj;
     g.n_tiles = (n_cols + ct - 1) / ct;
     g.grid = std::min(g.n_tiles, n_sms);
-    g.smem = (size_t)off + 2ULL * ring_cap * blk;
     return true;
   }
   return false;
 }
 
-struct WaveSchedule {
-  std::vector<WaveTask> post_task, pre_task;
-  std::vector<WaveAhead> post_ahead, pre_ahead;
-  int rounds_post = 0, rounds_pre = 0, depth = 0;
-  long long ring_reads_post = 0, ring_reads_pre = 0, pre_global_blocks = 0;
+struct WalkPlan {
+  int rounds_post = 0, rounds_pre = 0, rounds = 0, tree_depth = 0, wn_eff = 0;
+  std::vector<uint8_t> records;  // [rounds] CR, then [rounds] IR, then the boot jobs
+  uint32_t ir_base = 0, boot_base = 0;
+  uint32_t boot_n[4] = {0, 0, 0, 0}, boot_tx[4] = {0, 0, 0, 0};  // loads of rounds 0..depth-1
+  std::vector<int32_t> mat_dst;  // [2N-2][2]: matrix slot ((round*wn+slot)*3+which) in the post / pre bundles, -1 none
+  long long resident_reads = 0, loads_msg = 0, loads_pre = 0, stores_msg = 0, stores_pre = 0, evictions = 0;
+  int max_jobs_used = 0;
 };
 
-inline WaveTask idle_task() {
-  WaveTask t{};
-  t.l = t.r = -1;
-  t.src_l = t.src_r = t.src_v = t.dst0 = t.dst1 = kNoBlock;
-  return t;
-}
-inline WaveAhead idle_ahead() {
-  WaveAhead a{};
-  a.g_l = a.g_r = a.g_v = kNoFetch;
-  a.m[0] = a.m[1] = a.m[2] = -1;
-  return a;
-}
+namespace plan_detail {
+struct Use { int round, node, op; };  // op: 0 left, 1 right, 2 parent side
+struct Value {
+  int prod = -1;             // producing round
+  std::vector<Use> uses;     // by round
+  int next = 0;              // first use not yet served
+  int block = -1;            // resident pool block
+  bool store = false;        // needs a copy in HBM
+  int dst_block = -1;        // block it is produced into
+};
+struct Fetch { int vid, use; };
+struct LoadRec { uint32_t kind, goff, soff, bytes; };
+}  // namespace plan_detail
 
 // triples: [N-1][3] (node, left, right), node ids N..2N-2 in post-order (validated here).
-inline bool plan_schedule(int N, int P, int K, const int32_t* triples, const WaveGeometry& g, WaveSchedule& out,
-                          std::string& why) {
-  const int wn = g.wn, ring_cap = g.ring_cap;
-  const unsigned n_cols = (unsigned)P * (unsigned)K;
-  if ((unsigned long long)(N - 1) * n_cols > 0xFFFFFFF0ull || (unsigned long long)N * P > 0xFFFFFFF0ull) {
-    why = "problem too large for 32-bit column offsets";
+inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int wn_eff, int budget, WalkPlan& out,
+                      std::string& why) {
+  using namespace plan_detail;
+  const int wn = g.wn, D = g.depth, S = g.stages, NB = g.n_pool, K = g.K;
+  wn_eff = std::max(1, std::min(wn_eff, wn));
+  out = WalkPlan();
+  out.wn_eff = wn_eff;
+  const int n_nodes = 2 * N - 1, root = 2 * N - 2;
+  if ((unsigned long long)(N - 1) * (unsigned long long)g.blk > 0xFFFFFFF0ull ||
+      (unsigned long long)N * (unsigned long long)g.ct_pad > 0xFFFFFFF0ull) {
+    why = "tile too large for 32-bit copy offsets";
     return false;
   }
-  auto ring_off = [&](int round, int idx) { return (unsigned short)((g.off_ring + ((round & 1) * ring_cap + idx) * g.blk) / 16); };
-  auto stage_off = [&](int op, int slot) { return (unsigned short)((g.off_stage + (op * wn + slot) * g.blk) / 16); };
-  auto gcol = [&](int node) { return (unsigned)(node - N) * n_cols; };
-  const int n_nodes = 2 * N - 1, root = 2 * N - 2;
   std::vector<int> left(n_nodes, -1), right(n_nodes, -1), parent(n_nodes, -1);
   std::vector<char> seen(n_nodes, 0);
   for (int e = 0; e < N - 1; ++e) {
@@ -130,131 +182,372 @@ inline bool plan_schedule(int N, int P, int K, const int32_t* triples, const Wav
     if (right[v] >= N) h = std::max(h, height[right[v]] + 1);
     height[v] = h;
   }
-  out.depth = max_depth + 1;
-  using Item = std::pair<int, int>;  // (priority, -node)
+  out.tree_depth = max_depth + 1;
 
-  // ---------------------------------------------------------------- post-order pass
-  std::vector<int> round_post(n_nodes, -1), slot_post(n_nodes, -1), pending(n_nodes, 0);
+  // ------------------------------------------------------------------ schedule
+  // Memory-aware list scheduling.  cnt[j] bounds the pool blocks that cannot be reclaimed
+  // at the top of round j: operands of rounds j..j+D (loaded or resident, they must sit in
+  // the pool by then) plus the results of rounds j-1 and j (being produced / being stored).
+  // A task joins round f only if every window it touches stays within the budget, so the
+  // allocation below always finds a free or droppable block.
+  using Item = std::pair<int, int>;  // (priority, -node)
+  std::vector<int> rnd_post(n_nodes, -1), slot_post(n_nodes, -1), rnd_pre(n_nodes, -1), slot_pre(n_nodes, -1);
+  std::vector<std::vector<int>> tasks;  // per global round: node ids by slot
+  std::vector<int> cnt;
+  auto cnt_at = [&](int j) -> int& { if ((int)cnt.size() <= j) cnt.resize(j + 1, 0); return cnt[j]; };
+  // try to add a task to round f: operands produced in rounds px[0..n_op), n_out results
+  auto try_add = [&](int f, const int* px, int n_op, int n_out) -> bool {
+    int inc[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // windows f-D .. f+1  (D <= 3)
+    for (int o = 0; o < n_op; ++o)
+      for (int j = std::max(f - D, 0); j <= f; ++j)
+        if (j >= px[o] + 2) ++inc[j - (f - D)];
+    inc[D] += n_out;      // window f
+    inc[D + 1] += n_out;  // window f + 1
+    for (int w = 0; w <= D + 1; ++w) {
+      const int j = f - D + w;
+      if (j < 0 || inc[w] == 0) continue;
+      if (cnt_at(j) + inc[w] > budget) return false;
+    }
+    for (int w = 0; w <= D + 1; ++w) {
+      const int j = f - D + w;
+      if (j >= 0) cnt_at(j) += inc[w];
+    }
+    return true;
+  };
   {
+    std::vector<int> pending(n_nodes, 0);
     std::priority_queue<Item> ready;
     for (int v = N; v < n_nodes; ++v) {
       pending[v] = (left[v] >= N) + (right[v] >= N);
       if (pending[v] == 0) ready.push({depth[v], -v});
     }
-    int done = 0, r = 0;
-    std::vector<int> chosen;
+    int done = 0;
+    std::vector<Item> skipped;
     while (done < N - 1) {
-      chosen.clear();
-      while ((int)chosen.size() < wn && !ready.empty()) { chosen.push_back(-ready.top().second); ready.pop(); }
-      if (chosen.empty()) { why = "post schedule stalled"; return false; }
-      for (int i = 0; i < (int)chosen.size(); ++i) { round_post[chosen[i]] = r; slot_post[chosen[i]] = i; }
+      std::vector<int> chosen;
+      const int q = (int)tasks.size();
+      skipped.clear();
+      // the root runs alone in the last post-order round (every rescale count is final then)
+      while ((int)chosen.size() < wn_eff && !ready.empty()) {
+        const Item it = ready.top();
+        const int v = -it.second;
+        if (v == root && !chosen.empty()) break;
+        ready.pop();
+        int px[2], n_op = 0;
+        if (left[v] >= N) px[n_op++] = rnd_post[left[v]];
+        if (right[v] >= N) px[n_op++] = rnd_post[right[v]];
+        if (!try_add(q, px, n_op, v == root ? 0 : 1)) { skipped.push_back(it); continue; }
+        chosen.push_back(v);
+        if (v == root) break;
+      }
+      for (const Item& it : skipped) ready.push(it);
+      if (chosen.empty() && ready.empty()) { why = "post schedule stalled"; return false; }
+      if ((int)tasks.size() > 8 * N + 64) { why = "pool exhausted (schedule)"; return false; }
+      for (int i = 0; i < (int)chosen.size(); ++i) { rnd_post[chosen[i]] = q; slot_post[chosen[i]] = i; }
+      tasks.push_back(chosen);
+      // successors become ready for the NEXT round
       for (int v : chosen) {
         ++done;
         if (v != root && --pending[parent[v]] == 0) ready.push({depth[parent[v]], -parent[v]});
       }
-      ++r;
     }
-    out.rounds_post = r;
-    out.post_task.assign((size_t)r * wn, idle_task());
-    out.post_ahead.assign((size_t)r * wn, idle_ahead());
-    for (int v = N; v < n_nodes; ++v) {
-      const int rv = round_post[v], sv = slot_post[v];
-      WaveTask& t = out.post_task[(size_t)rv * wn + sv];
-      WaveAhead& a = out.post_ahead[(size_t)rv * wn + sv];
-      t.l = left[v]; t.r = right[v];
-      auto route = [&](int c, int op, unsigned short& src, unsigned& fetch, int& mat) {
-        if (c < N) { src = kNoBlock; fetch = (unsigned)c * (unsigned)P; a.kinds |= 1u << op; mat = c; return; }
-        if (round_post[c] == rv - 1) { src = ring_off(rv - 1, slot_post[c]); ++out.ring_reads_post; }
-        else { src = stage_off(op, sv); fetch = gcol(c); }
-      };
-      route(t.l, 0, t.src_l, a.g_l, a.m[1]);
-      route(t.r, 1, t.src_r, a.g_r, a.m[2]);
-      if (v == root) t.flags = TF_ROOT;
-      else {
-        a.m[0] = v;
-        t.gout0 = gcol(v);  // the pre-order pass always reads m_v from global memory
-        if (round_post[parent[v]] == rv + 1) t.dst0 = ring_off(rv, sv);
-      }
-    }
+    out.rounds_post = (int)tasks.size();
   }
-
-  // ----------------------------------------------------------------- pre-order pass
-  std::vector<int> round_pre(n_nodes, -1), slot_pre(n_nodes, -1);
   {
     std::priority_queue<Item> ready;
     ready.push({height[root], -root});
-    int done = 0, r = 0;
-    std::vector<int> chosen;
-    std::vector<Item> deferred;
+    int done = 0;
+    std::vector<Item> skipped;
     while (done < N - 1) {
-      chosen.clear();
-      deferred.clear();
-      int ring_used = 0;
-      while ((int)chosen.size() < wn && !ready.empty()) {
+      std::vector<int> chosen;
+      const int q = (int)tasks.size();
+      skipped.clear();
+      while ((int)chosen.size() < wn_eff && !ready.empty()) {
         const Item it = ready.top();
-        ready.pop();
         const int v = -it.second;
-        const bool needs_ring = v != root && round_pre[parent[v]] == r - 1;
-        if (needs_ring && ring_used >= ring_cap) { deferred.push_back(it); continue; }
-        ring_used += needs_ring;
+        ready.pop();
+        int px[3], n_op = 0;
+        if (left[v] >= N) px[n_op++] = rnd_post[left[v]];
+        if (right[v] >= N) px[n_op++] = rnd_post[right[v]];
+        if (v != root) px[n_op++] = rnd_pre[parent[v]];
+        if (!try_add(q, px, n_op, (left[v] >= N) + (right[v] >= N))) { skipped.push_back(it); continue; }
         chosen.push_back(v);
       }
-      for (const Item& it : deferred) ready.push(it);
-      if (chosen.empty() && deferred.empty()) { why = "pre schedule stalled"; return false; }
-      for (int i = 0; i < (int)chosen.size(); ++i) { round_pre[chosen[i]] = r; slot_pre[chosen[i]] = i; }
+      for (const Item& it : skipped) ready.push(it);
+      if (chosen.empty() && ready.empty()) { why = "pre schedule stalled"; return false; }
+      if ((int)tasks.size() > 16 * N + 128) { why = "pool exhausted (schedule)"; return false; }
+      for (int i = 0; i < (int)chosen.size(); ++i) { rnd_pre[chosen[i]] = q; slot_pre[chosen[i]] = i; }
+      tasks.push_back(chosen);
       for (int v : chosen) {
         ++done;
         if (left[v] >= N) ready.push({height[left[v]], -left[v]});
         if (right[v] >= N) ready.push({height[right[v]], -right[v]});
       }
-      ++r;
     }
-    out.rounds_pre = r;
-    out.pre_task.assign((size_t)r * wn, idle_task());
-    out.pre_ahead.assign((size_t)r * wn, idle_ahead());
-    std::vector<int> ring_next(r, 0);  // ring blocks handed out per producer round
-    for (int v = N; v < n_nodes; ++v) {
-      const int rv = round_pre[v], sv = slot_pre[v];
-      WaveTask& t = out.pre_task[(size_t)rv * wn + sv];
-      WaveAhead& a = out.pre_ahead[(size_t)rv * wn + sv];
-      t.l = left[v]; t.r = right[v];
-      a.m[1] = t.l; a.m[2] = t.r;
-      for (int op = 0; op < 2; ++op) {
-        const int c = op ? t.r : t.l;
-        unsigned short& src = op ? t.src_r : t.src_l;
-        unsigned& fetch = op ? a.g_r : a.g_l;
-        if (c < N) { src = kNoBlock; fetch = (unsigned)c * (unsigned)P; a.kinds |= 1u << op; }
-        else { src = stage_off(op, sv); fetch = gcol(c); t.flags |= op ? TF_INT_R : TF_INT_L; }
+    out.rounds = (int)tasks.size();
+    out.rounds_pre = out.rounds - out.rounds_post;
+  }
+  const int R = out.rounds, Rpost = out.rounds_post;
+
+  // ------------------------------------------------------------ values and uses
+  // vid: message of internal non-root v -> v - N ; pre-order partial of c -> (N-1) + (c - N)
+  const int n_int = N - 1;
+  std::vector<Value> val(2 * (size_t)n_int);
+  auto vid_m = [&](int v) { return v - N; };
+  auto vid_u = [&](int c) { return n_int + (c - N); };
+  for (int v = N; v < root; ++v) {
+    Value& m = val[vid_m(v)];
+    const int p = parent[v], side = (right[p] == v) ? 1 : 0;
+    m.prod = rnd_post[v];
+    m.store = true;
+    m.uses.push_back({rnd_post[p], p, side});
+    m.uses.push_back({rnd_pre[p], p, side});
+    Value& u = val[vid_u(v)];
+    u.prod = rnd_pre[p];
+    u.uses.push_back({rnd_pre[v], v, 2});
+  }
+  // resolved operand / result blocks per task
+  std::vector<int> src_post(2 * (size_t)n_nodes, -1), src_pre(3 * (size_t)n_nodes, -1), dst_pre(2 * (size_t)n_nodes, -1),
+      dst_post(n_nodes, -1);
+  auto set_src = [&](const Use& u, int blk_idx) {
+    if (u.round < Rpost) src_post[2 * (size_t)u.node + u.op] = blk_idx;
+    else src_pre[3 * (size_t)u.node + u.op] = blk_idx;
+  };
+
+  // ------------------------------------------------------------- pool simulation
+  const int INF = INT_MAX;
+  std::vector<int> free_at(NB, 0);
+  std::vector<int> resident;  // vids with a resident block
+  std::vector<std::vector<Fetch>> fetch_req(R);
+  std::vector<std::vector<LoadRec>> loads(R), stores(R + 1);
+  auto drop = [&](int vid) {
+    for (size_t i = 0; i < resident.size(); ++i)
+      if (resident[i] == vid) { resident[i] = resident.back(); resident.pop_back(); return; }
+  };
+  auto alloc = [&](int i) -> int {
+    for (int b = 0; b < NB; ++b)
+      if (free_at[b] <= i) return b;
+    int best = -1, best_next = -1;
+    for (int vid : resident) {
+      const Value& v = val[vid];
+      if (v.prod + 2 > i) continue;
+      const int nx = v.uses[v.next].round;
+      if (nx < i + D + 1) continue;
+      if (nx > best_next) { best_next = nx; best = vid; }
+    }
+    if (best < 0) return -1;
+    Value& v = val[best];
+    const int b = v.block;
+    for (int k = v.next; k < (int)v.uses.size(); ++k) fetch_req[v.uses[k].round].push_back({best, k});
+    v.block = -1;
+    v.store = true;
+    drop(best);
+    ++out.evictions;
+    return b;
+  };
+  for (int i = 0; i < R; ++i) {
+    // loads issued at the top of round i
+    const int f_lo = (i == 0) ? 0 : i + D, f_hi = std::min(R - 1, i + D);
+    for (int f = f_lo; f <= f_hi; ++f) {
+      for (size_t k = 0; k < fetch_req[f].size(); ++k) {
+        const Fetch fr = fetch_req[f][k];
+        const int b = alloc(i);
+        if (b < 0) { why = "pool exhausted (loads)"; return false; }
+        free_at[b] = f + 1;
+        const Value& v = val[fr.vid];
+        set_src(v.uses[fr.use], b);
+        const bool is_m = fr.vid < n_int;
+        const int node = is_m ? N + fr.vid : N + (fr.vid - n_int);
+        loads[f].push_back({is_m ? JK_MSG : JK_PRE, (uint32_t)(node - N) * (uint32_t)g.blk,
+                            (uint32_t)(g.off_pool + b * g.blk), (uint32_t)g.blk});
+        (is_m ? out.loads_msg : out.loads_pre) += 1;
       }
-      if (v == root) t.flags |= TF_ROOT;
     }
-    // route u_c from each producer (parent task) to its consumer (child task)
-    for (int v = N; v < n_nodes; ++v) {
-      const int rv = round_pre[v];
-      WaveTask& t = out.pre_task[(size_t)rv * wn + slot_pre[v]];
-      for (int side = 0; side < 2; ++side) {
-        const int c = side ? t.r : t.l;
-        if (c < N) continue;
-        const int rc = round_pre[c], sc = slot_pre[c];
-        WaveTask& ct = out.pre_task[(size_t)rc * wn + sc];
-        WaveAhead& ca = out.pre_ahead[(size_t)rc * wn + sc];
-        if (rc == rv + 1) {
-          const int idx = ring_next[rv]++;
-          if (idx >= ring_cap) { why = "internal error: ring budget exceeded"; return false; }
-          ct.src_v = ring_off(rv, idx);
-          (side ? t.dst1 : t.dst0) = ring_off(rv, idx);
-          ++out.ring_reads_pre;
-        } else {
-          ct.src_v = stage_off(2, sc);
-          ca.g_v = gcol(c);
-          t.flags |= side ? TF_G1 : TF_G0;
-          (side ? t.gout1 : t.gout0) = gcol(c);
-          ++out.pre_global_blocks;
+    // results of round i
+    for (int v : tasks[i]) {
+      if (i < Rpost) {
+        if (v == root) continue;
+        const int b = alloc(i);
+        if (b < 0) { why = "pool exhausted (results)"; return false; }
+        Value& m = val[vid_m(v)];
+        m.block = m.dst_block = b;
+        free_at[b] = INF;
+        dst_post[v] = b;
+        resident.push_back(vid_m(v));
+        for (const Use& u : m.uses) set_src(u, b);
+      } else {
+        for (int side = 0; side < 2; ++side) {
+          const int c = side ? right[v] : left[v];
+          if (c < N) continue;
+          const int b = alloc(i);
+          if (b < 0) { why = "pool exhausted (results)"; return false; }
+          Value& u = val[vid_u(c)];
+          u.block = u.dst_block = b;
+          free_at[b] = INF;
+          dst_pre[2 * (size_t)v + side] = b;
+          resident.push_back(vid_u(c));
+          for (const Use& us : u.uses) set_src(us, b);
         }
+      }
+    }
+    // reads of round i
+    for (int v : tasks[i]) {
+      auto served = [&](int vid) {
+        Value& x = val[vid];
+        if (x.block < 0) return;  // this use comes from a load
+        if (x.uses[x.next].round != i) return;
+        ++out.resident_reads;
+        ++x.next;
+        if (x.next == (int)x.uses.size()) {
+          free_at[x.block] = x.store ? std::max(x.prod + 2, i + 1) : i + 1;  // no store: nothing reads it later
+          x.block = -1;
+          drop(vid);
+        }
+      };
+      if (left[v] >= N) served(vid_m(left[v]));
+      if (right[v] >= N) served(vid_m(right[v]));
+      if (i >= Rpost && v != root) served(vid_u(v));
+    }
+    // uses of round i that were turned into loads: advance the cursor of dropped values
+    for (const Fetch& fr : fetch_req[i]) {
+      Value& x = val[fr.vid];
+      if (x.block < 0 && x.next <= fr.use) x.next = fr.use + 1;
+    }
+  }
+  // stores: every message; dropped pre-order partials
+  for (int vid = 0; vid < (int)val.size(); ++vid) {
+    const Value& x = val[vid];
+    if (x.prod < 0 || !x.store) continue;
+    const bool is_m = vid < n_int;
+    const int node = is_m ? N + vid : N + (vid - n_int);
+    stores[x.prod + 1].push_back({is_m ? JK_MSG : JK_PRE, (uint32_t)(node - N) * (uint32_t)g.blk,
+                                  (uint32_t)(g.off_pool + x.dst_block * g.blk), (uint32_t)g.blk});
+    (is_m ? out.stores_msg : out.stores_pre) += 1;
+  }
+
+  // -------------------------------------------------------------------- records
+  const uint32_t cr_total = (uint32_t)R * g.cr_bytes;
+  out.ir_base = cr_total;
+  out.boot_base = out.ir_base + (uint32_t)R * g.ir_bytes;
+  // fixed per-round loads: tip rows, matrix bundle, the round's own records
+  for (int f = 0; f < R; ++f) {
+    const int st = f % S;
+    for (int s = 0; s < (int)tasks[f].size(); ++s) {
+      const int v = tasks[f][s];
+      for (int side = 0; side < 2; ++side) {
+        const int c = side ? right[v] : left[v];
+        if (c >= N) continue;
+        loads[f].push_back({JK_TIPS, (uint32_t)c * (uint32_t)g.ct_pad,
+                            (uint32_t)(g.off_tips + st * g.tips_bytes + (s * 2 + side) * g.ct_pad), (uint32_t)g.ct_pad});
+      }
+    }
+    if (!tasks[f].empty())
+      loads[f].push_back({JK_MATS, (uint32_t)f * (uint32_t)g.mats_bytes, (uint32_t)(g.off_mats + st * g.mats_bytes),
+                          (uint32_t)((int)tasks[f].size() * 3 * K * g.mat_stride)});
+    loads[f].push_back({JK_REC, (uint32_t)f * (uint32_t)g.cr_bytes, (uint32_t)(g.off_cr + st * g.cr_bytes), (uint32_t)g.cr_bytes});
+  }
+  // issue records: IR[q] = loads of round q + D, stores of round q - 1
+  std::vector<uint32_t> ir_len(R, 16);
+  for (int q = 0; q < R; ++q) {
+    const int n_l = q + D < R ? (int)loads[q + D].size() + 1 : 0;  // + the IR of round q + D itself
+    const int n_s = (int)stores[q].size();
+    if (n_l + n_s > g.max_jobs) { why = "too many copies in one round"; return false; }
+    out.max_jobs_used = std::max(out.max_jobs_used, n_l + n_s);
+    ir_len[q] = 16u + 16u * (uint32_t)(n_l + n_s);
+  }
+  size_t n_boot = 0;
+  for (int f = 0; f < std::min(D, R); ++f) n_boot += loads[f].size() + 1;
+  out.records.assign((size_t)out.boot_base + n_boot * 16, 0);
+  auto ir_job = [&](int f) {
+    return WalkJob{out.ir_base + (uint32_t)f * (uint32_t)g.ir_bytes, (uint32_t)(g.off_ir + (f % S) * g.ir_bytes), ir_len[f], JK_REC};
+  };
+  auto job_of = [&](const LoadRec& l) { return WalkJob{l.goff, l.soff, l.bytes, l.kind}; };
+  for (int q = 0; q < R; ++q) {
+    uint8_t* p = out.records.data() + out.ir_base + (size_t)q * g.ir_bytes;
+    WalkIssueHeader h{0, 0, 0, q >= Rpost ? 1u : 0u};
+    WalkJob* jobs = reinterpret_cast<WalkJob*>(p + 16);
+    int n = 0;
+    if (q + D < R) {
+      for (const LoadRec& l : loads[q + D]) { jobs[n++] = job_of(l); h.tx_bytes += l.bytes; }
+      jobs[n] = ir_job(q + D); h.tx_bytes += jobs[n].bytes; ++n;
+      h.n_loads = (uint32_t)n;
+    }
+    for (const LoadRec& l : stores[q]) jobs[n++] = job_of(l);
+    h.n_stores = (uint32_t)n - h.n_loads;
+    std::memcpy(p, &h, 16);
+  }
+  {
+    WalkJob* jobs = reinterpret_cast<WalkJob*>(out.records.data() + out.boot_base);
+    int n = 0;
+    for (int f = 0; f < std::min(D, R); ++f) {
+      const int n0 = n;
+      for (const LoadRec& l : loads[f]) { jobs[n++] = job_of(l); out.boot_tx[f] += l.bytes; }
+      jobs[n] = ir_job(f); out.boot_tx[f] += jobs[n].bytes; ++n;
+      out.boot_n[f] = (uint32_t)(n - n0);
+    }
+  }
+  // descriptors + branch ids
+  auto off16 = [&](int b) { return b < 0 ? kNoBlk : (uint16_t)((g.off_pool + b * g.blk) / 16); };
+  out.mat_dst.assign(2 * (size_t)(2 * N - 2), -1);
+  for (int q = 0; q < R; ++q) {
+    uint8_t* p = out.records.data() + (size_t)q * g.cr_bytes;
+    WalkDesc* d = reinterpret_cast<WalkDesc*>(p);
+    WalkIds* ids = reinterpret_cast<WalkIds*>(p + wn * 16);
+    for (int s = 0; s < wn; ++s) {
+      d[s] = WalkDesc{kNoBlk, kNoBlk, kNoBlk, kNoBlk, kNoBlk, 0, 0, 0};
+      ids[s] = WalkIds{-1, -1};
+    }
+    for (int s = 0; s < (int)tasks[q].size(); ++s) {
+      const int v = tasks[q][s], l = left[v], r = right[v];
+      const int slot3 = (q * wn + s) * 3;
+      WalkDesc& e = d[s];
+      e.flags = WF_LIVE;
+      if (l < N) e.flags |= WF_TIP_L;
+      if (r < N) e.flags |= WF_TIP_R;
+      if (v == root) e.flags |= WF_ROOT;
+      if (q < Rpost) {
+        e.src_l = off16(src_post[2 * (size_t)v]);
+        e.src_r = off16(src_post[2 * (size_t)v + 1]);
+        if (v != root) { e.dst0 = off16(dst_post[v]); out.mat_dst[2 * (size_t)v] = slot3; }
+        else ids[s] = WalkIds{-2, -1};
+        if (l < N) out.mat_dst[2 * (size_t)l] = slot3 + 1;
+        if (r < N) out.mat_dst[2 * (size_t)r] = slot3 + 2;
+      } else {
+        e.src_l = off16(src_pre[3 * (size_t)v]);
+        e.src_r = off16(src_pre[3 * (size_t)v + 1]);
+        e.src_v = v == root ? kNoBlk : off16(src_pre[3 * (size_t)v + 2]);
+        if (l >= N) { e.flags |= WF_OUT_L; e.dst0 = off16(dst_pre[2 * (size_t)v]); }
+        if (r >= N) { e.flags |= WF_OUT_R; e.dst1 = off16(dst_pre[2 * (size_t)v + 1]); }
+        out.mat_dst[2 * (size_t)l + 1] = slot3 + 1;
+        out.mat_dst[2 * (size_t)r + 1] = slot3 + 2;
+        ids[s] = WalkIds{l, r};
+      }
+      // every non-tip operand must have been resolved
+      if ((l >= N && e.src_l == kNoBlk) || (r >= N && e.src_r == kNoBlk) ||
+          (q >= Rpost && v != root && e.src_v == kNoBlk)) {
+        why = "internal error: unresolved operand";
+        return false;
       }
     }
   }
   return true;
+}
+
+// Plan against the whole pool; if the allocation still fails (the scheduler's count is an
+// upper bound, so it should not), retry with a smaller budget and then fewer slots.
+inline bool plan_walk_auto(int N, const int32_t* triples, const WalkGeometry& g, WalkPlan& out, std::string& why) {
+  auto retry = [&]() {
+    return why.find("pool exhausted") != std::string::npos || why.find("too many copies") != std::string::npos;
+  };
+  for (int budget = g.n_pool; budget >= 3 * g.stages + 4; budget -= std::max(1, g.n_pool / 16)) {
+    if (plan_walk(N, triples, g, g.wn, budget, out, why)) return true;
+    if (!retry()) return false;
+  }
+  for (int w = g.wn / 2; w >= 1; w /= 2) {
+    if (plan_walk(N, triples, g, w, g.n_pool, out, why)) return true;
+    if (!retry()) return false;
+  }
+  return false;
 }
 
 }  // namespace b2p

@@ -70,14 +70,16 @@ typedef struct b2p_info {
   int32_t regs_per_thread;  /* of the traversal kernel in use */
   int32_t tasks_per_round;  /* node tasks a CTA executes side by side */
   int32_t pre_rounds;       /* schedule length of the pre-order pass */
-  int32_t ring_blocks;      /* shared-memory ring capacity per round parity */
+  int32_t pool_blocks;      /* shared-memory blocks the planner allocates operands / results in */
   int32_t smem_bytes;       /* dynamic shared memory per CTA */
+  int32_t copy_depth;       /* rounds a bulk load is issued ahead of its use */
+  int32_t reserved0;
   int64_t device_bytes;     /* scratch owned by the instance */
   int64_t alg_bytes_loglik; /* (2N-3)U + N*P */
   int64_t alg_bytes_grad;   /* (5N-9)U + 2*N*P */
-  int64_t ring_reads_post;  /* operand blocks served from shared memory instead of L2/HBM */
-  int64_t ring_reads_pre;
-  int64_t pre_global_blocks; /* pre-order blocks that had to go through global memory */
+  int64_t resident_reads;   /* per tile: operand blocks read where they were produced (no copy) */
+  int64_t block_loads;      /* per tile: operand blocks bulk-loaded from HBM/L2 */
+  int64_t block_stores;     /* per tile: result blocks bulk-stored to HBM */
 } b2p_info;
 
 /* BEAGLE: beagleCreateInstance / beagleFinalizeInstance. */
@@ -91,7 +93,8 @@ int b2p_get_info(const b2p_instance* h, b2p_info* out);
  * Fed by "tree_model" (/root/reference/flu_H3N2/phylotorch-JC69.template:14-44) and
  * `-t <newick>` (/root/reference/modules/micro.nf:20,47).  BEAGLE: the operations
  * array of beagleUpdatePartials / beagleUpdatePrePartials.  Builds the static
- * schedules of both passes (list scheduling, Hu's level rule). */
+ * schedule of both passes (list scheduling, Hu's level rule), the shared-memory
+ * block allocation and the per-round copy lists of the traversal kernel. */
 int b2p_set_topology(b2p_instance* h, const int32_t* h_triples);
 
 /* Tip data: h_masks uint8 [N][P], bit i set = state i compatible (A=1,C=2,G=4,T=8;

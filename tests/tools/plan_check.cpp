@@ -1,0 +1,209 @@
+// CPU-side checker of the traversal kernel's static plan (test tooling, no GPU).
+// Replays the records b2p_plan.h emits — descriptors, copy lists — against a symbolic
+// shared-memory pool (each block holds the NAME of a value, not numbers) and verifies
+// every timing rule the kernel relies on:
+//   * an operand read finds exactly the value the tree says it should (message of the
+//     child / pre-order partial of the node), and never a block whose load is in flight;
+//   * a result is never written into a block that is read or written by another task of
+//     the same round, that has a load in flight, or that a store is still reading;
+//   * a load reads HBM only after the store of that value has completed (>= 2 rounds);
+//   * every message is stored exactly once; transaction byte counts match the job lists.
+// usage: plan_check N shape seed ct K elem smem_bytes depth [nt]   -> prints "OK ..." or "FAIL ..."
+#include <cstdio>
+#include <cstdlib>
+#include <map>
+#include <random>
+#include <string>
+#include <vector>
+
+#include "../../gradient-benchmark_b200/csrc/b2p_plan.h"
+
+using namespace b2p;
+
+static std::vector<int32_t> random_triples(int N, int shape, unsigned seed) {
+  // shape 0: random joins (coalescent-like), 1: caterpillar, 2: balanced
+  std::mt19937 rng(seed);
+  std::vector<int32_t> tr;
+  std::vector<int> roots(N);
+  for (int i = 0; i < N; ++i) roots[i] = i;
+  int next = N;
+  while (roots.size() > 1) {
+    size_t a, b;
+    if (shape == 1) { a = roots.size() - 1; b = 0; }
+    else if (shape == 2) { a = 0; b = 1; }
+    else { a = rng() % roots.size(); do { b = rng() % roots.size(); } while (b == a); }
+    const int l = roots[a], r = roots[b];
+    if (a < b) std::swap(a, b);
+    roots.erase(roots.begin() + a);
+    roots.erase(roots.begin() + b);
+    tr.push_back(next); tr.push_back(l); tr.push_back(r);
+    if (shape == 2) roots.push_back(next); else roots.insert(roots.begin(), next);
+    ++next;
+  }
+  return tr;
+}
+
+#define FAIL(...) do { printf("FAIL "); printf(__VA_ARGS__); printf("\n"); return 1; } while (0)
+
+int main(int argc, char** argv) {
+  if (argc < 9) { printf("usage\n"); return 2; }
+  const int N = atoi(argv[1]), shape = atoi(argv[2]), seed = atoi(argv[3]), ct = atoi(argv[4]), K = atoi(argv[5]),
+            elem = atoi(argv[6]), smem = atoi(argv[7]), depth = atoi(argv[8]), nt = argc > 9 ? atoi(argv[9]) : 0;
+  std::vector<int32_t> tr = random_triples(N, shape, seed);
+  WalkGeometry g;
+  if (!plan_geometry(N, ct * 148, K, elem, 148, smem, nt, ct, 1, depth, g)) FAIL("geometry");
+  WalkPlan plan;
+  std::string why;
+  if (!plan_walk_auto(N, tr.data(), g, plan, why)) FAIL("plan: %s", why.c_str());
+  const int R = plan.rounds, Rpost = plan.rounds_post, D = g.depth, S = g.stages, wn = g.wn, root = 2 * N - 2;
+  std::vector<int> left(2 * N - 1, -1), right(2 * N - 1, -1), parent(2 * N - 1, -1);
+  for (int e = 0; e < N - 1; ++e) { const int v = tr[3 * e]; left[v] = tr[3 * e + 1]; right[v] = tr[3 * e + 2]; parent[left[v]] = parent[right[v]] = v; }
+  // which node is the post-order task at (round, slot)?  from the matrix destinations
+  std::map<int, int> post_node_at;  // slot3 -> node
+  for (int v = N; v < root; ++v) {
+    if (plan.mat_dst[2 * v] < 0 || plan.mat_dst[2 * v] % 3 != 0) FAIL("mat_dst own of %d", v);
+    post_node_at[plan.mat_dst[2 * v]] = v;
+  }
+  for (int b = 0; b < 2 * N - 2; ++b) {
+    if (plan.mat_dst[2 * b + 1] < 0) FAIL("branch %d has no pre-order matrix slot", b);
+    if (b < N && plan.mat_dst[2 * b] < 0) FAIL("tip %d has no post-order matrix slot", b);
+  }
+  const uint8_t* rec = plan.records.data();
+  // symbolic pool: tag = 1 + vid (vid: message of v -> v-N ; partial of c -> (N-1)+(c-N)), 0 = nothing
+  const int NB = g.n_pool;
+  std::vector<int> tag(NB, 0), inflight_until(NB, 0), store_busy(NB, -1);
+  std::map<int, int> stored_at;  // vid -> iteration the store was issued
+  auto blk_of = [&](uint32_t soff) { return ((int)soff - g.off_pool) / g.blk; };
+  auto check_soff = [&](uint32_t soff) { return (int)soff >= g.off_pool && ((int)soff - g.off_pool) % g.blk == 0 && blk_of(soff) < NB; };
+  long long n_loads = 0, n_stores = 0, n_tasks = 0;
+  std::vector<int> done_post(2 * N - 1, 0), done_pre(2 * N - 1, 0);
+  auto do_load = [&](const WalkJob& j, int iter, int f) -> const char* {
+    if (j.bytes % 16 || j.soff % 16 || j.goff % 16) return "alignment";
+    if (j.kind == JK_MSG || j.kind == JK_PRE) {
+      if (!check_soff(j.soff) || (int)j.bytes != g.blk || j.goff % g.blk) return "bad block job";
+      const int b = blk_of(j.soff), node = N + (int)(j.goff / g.blk);
+      const int vid = j.kind == JK_MSG ? node - N : (N - 1) + (node - N);
+      if (!stored_at.count(vid)) return "load of a value that was never stored";
+      if (iter < stored_at[vid] + 2) return "load issued before its store completed";
+      if (store_busy[b] == iter) return "load into a block a store is reading";
+      if (inflight_until[b] > iter) return "load into a block with a load in flight";
+      tag[b] = 1 + vid; inflight_until[b] = f;
+      ++n_loads;
+    } else if (j.kind == JK_TIPS) {
+      if ((int)j.bytes != g.ct_pad || (int)j.soff < g.off_tips + (f % S) * g.tips_bytes ||
+          (int)(j.soff + j.bytes) > g.off_tips + (f % S + 1) * g.tips_bytes) return "tips job";
+    } else if (j.kind == JK_MATS) {
+      if ((int)j.soff != g.off_mats + (f % S) * g.mats_bytes || (int)j.bytes > g.mats_bytes || j.goff != (uint32_t)f * g.mats_bytes) return "mats job";
+    } else if (j.kind == JK_REC) {
+      const bool is_cr = j.goff == (uint32_t)f * g.cr_bytes && (int)j.soff == g.off_cr + (f % S) * g.cr_bytes && (int)j.bytes == g.cr_bytes;
+      const bool is_ir = j.goff == plan.ir_base + (uint32_t)f * g.ir_bytes && (int)j.soff == g.off_ir + (f % S) * g.ir_bytes && (int)j.bytes <= g.ir_bytes;
+      if (!is_cr && !is_ir) return "record job";
+    } else return "kind";
+    return nullptr;
+  };
+  // boot
+  {
+    const WalkJob* jobs = reinterpret_cast<const WalkJob*>(rec + plan.boot_base);
+    int j0 = 0;
+    for (int f = 0; f < D && f < R; ++f) {
+      uint32_t tx = 0;
+      for (uint32_t j = 0; j < plan.boot_n[f]; ++j) {
+        if (const char* e = do_load(jobs[j0 + j], 0, f)) FAIL("boot round %d: %s", f, e);
+        tx += jobs[j0 + j].bytes;
+      }
+      if (tx != plan.boot_tx[f]) FAIL("boot tx");
+      j0 += plan.boot_n[f];
+    }
+  }
+  for (int q = 0; q < R; ++q) {
+    const uint8_t* ir = rec + plan.ir_base + (size_t)q * g.ir_bytes;
+    WalkIssueHeader h;
+    memcpy(&h, ir, 16);
+    const WalkJob* jobs = reinterpret_cast<const WalkJob*>(ir + 16);
+    if (h.pass != (q >= Rpost ? 1u : 0u)) FAIL("pass flag round %d", q);
+    if ((int)(h.n_loads + h.n_stores) > g.max_jobs) FAIL("too many jobs");
+    if (q + D >= R && h.n_loads) FAIL("loads past the end");
+    // stores first mark their blocks busy for this round (both are issued at the top of round q)
+    for (uint32_t j = h.n_loads; j < h.n_loads + h.n_stores; ++j) {
+      const WalkJob& jb = jobs[j];
+      if (!(jb.kind == JK_MSG || jb.kind == JK_PRE) || !check_soff(jb.soff) || (int)jb.bytes != g.blk) FAIL("store job");
+      const int b = blk_of(jb.soff), node = N + (int)(jb.goff / g.blk);
+      const int vid = jb.kind == JK_MSG ? node - N : (N - 1) + (node - N);
+      if (tag[b] != 1 + vid) FAIL("round %d: store of value %d finds tag %d", q, vid, tag[b] - 1);
+      if (inflight_until[b] > q) FAIL("store from a block with a load in flight");
+      if (stored_at.count(vid)) FAIL("value %d stored twice", vid);
+      stored_at[vid] = q;
+      store_busy[b] = q;
+      ++n_stores;
+    }
+    uint32_t tx = 0;
+    for (uint32_t j = 0; j < h.n_loads; ++j) {
+      if (const char* e = do_load(jobs[j], q, q + D)) FAIL("round %d load %u: %s", q, j, e);
+      tx += jobs[j].bytes;
+    }
+    if (tx != h.tx_bytes) FAIL("tx bytes round %d", q);
+    // tasks of round q
+    const WalkDesc* d = reinterpret_cast<const WalkDesc*>(rec + (size_t)q * g.cr_bytes);
+    const WalkIds* ids = reinterpret_cast<const WalkIds*>(rec + (size_t)q * g.cr_bytes + wn * 16);
+    std::vector<int> reads, writes;
+    std::vector<std::pair<int, int>> produced;  // (block, vid)
+    auto off_blk = [&](uint16_t o) { return blk_of((uint32_t)o * 16); };
+    for (int s = 0; s < wn; ++s) {
+      const WalkDesc& e = d[s];
+      if (!(e.flags & WF_LIVE)) continue;
+      ++n_tasks;
+      int v;
+      if (q < Rpost) {
+        if (e.flags & WF_ROOT) v = root;
+        else {
+          auto it = post_node_at.find((q * wn + s) * 3);
+          if (it == post_node_at.end()) FAIL("round %d slot %d: unknown post task", q, s);
+          v = it->second;
+        }
+        if (done_post[v]++) FAIL("post task %d twice", v);
+      } else {
+        if (ids[s].a < 0 || parent[ids[s].a] != parent[ids[s].b]) FAIL("ids");
+        v = parent[ids[s].a];
+        if (left[v] != ids[s].a || right[v] != ids[s].b) FAIL("ids order");
+        if (done_pre[v]++) FAIL("pre task %d twice", v);
+        if (v != root && !done_pre[parent[v]]) FAIL("pre task %d before its parent", v);
+      }
+      const int l = left[v], r = right[v];
+      if (((e.flags & WF_TIP_L) != 0) != (l < N) || ((e.flags & WF_TIP_R) != 0) != (r < N)) FAIL("tip flags");
+      auto need = [&](uint16_t src, int vid, const char* what) -> bool {
+        if (src == kNoBlk || !check_soff((uint32_t)src * 16)) { printf("FAIL round %d node %d: %s operand offset\n", q, v, what); return false; }
+        const int b = off_blk(src);
+        if (tag[b] != 1 + vid) { printf("FAIL round %d node %d: %s operand block %d holds %d, want %d\n", q, v, what, b, tag[b] - 1, vid); return false; }
+        if (inflight_until[b] > q) { printf("FAIL round %d node %d: %s operand load lands in round %d\n", q, v, what, inflight_until[b]); return false; }
+        reads.push_back(b);
+        return true;
+      };
+      if (l >= N && !need(e.src_l, l - N, "left")) return 1;
+      if (r >= N && !need(e.src_r, r - N, "right")) return 1;
+      if (q < Rpost) {
+        if (!done_post[l >= N ? l : v] || !done_post[r >= N ? r : v]) FAIL("post task %d before a child", v);
+        if (v != root) { writes.push_back(off_blk(e.dst0)); produced.push_back({off_blk(e.dst0), v - N}); }
+      } else {
+        if (v != root && !need(e.src_v, (N - 1) + (v - N), "parent-side")) return 1;
+        if (((e.flags & WF_OUT_L) != 0) != (l >= N) || ((e.flags & WF_OUT_R) != 0) != (r >= N)) FAIL("out flags");
+        if (l >= N) { writes.push_back(off_blk(e.dst0)); produced.push_back({off_blk(e.dst0), (N - 1) + (l - N)}); }
+        if (r >= N) { writes.push_back(off_blk(e.dst1)); produced.push_back({off_blk(e.dst1), (N - 1) + (r - N)}); }
+      }
+    }
+    for (size_t i = 0; i < writes.size(); ++i) {
+      const int b = writes[i];
+      if (b < 0 || b >= NB) FAIL("round %d: result block out of range", q);
+      if (inflight_until[b] > q) FAIL("round %d: result into a block with a load in flight (lands %d)", q, inflight_until[b]);
+      if (store_busy[b] == q) FAIL("round %d: result into block %d that a store is reading", q, b);
+      for (int rb : reads) if (rb == b) FAIL("round %d: block %d read and written in the same round", q, b);
+      for (size_t k = 0; k < i; ++k) if (writes[k] == b) FAIL("round %d: block %d written twice", q, b);
+    }
+    for (auto& pr : produced) tag[pr.first] = 1 + pr.second;
+  }
+  for (int v = N; v <= root; ++v) if (!done_post[v] || !done_pre[v]) FAIL("task %d missing", v);
+  for (int v = N; v < root; ++v) if (!stored_at.count(v - N)) FAIL("message %d never stored", v);
+  printf("OK N=%d shape=%d ct=%d K=%d elem=%d depth=%d nt=%d wn=%d wn_eff=%d pool=%d rounds=%d+%d tasks=%lld resident_reads=%lld loads=%lld stores=%lld evictions=%lld max_jobs=%d/%d smem=%zu\n",
+         N, shape, g.ct, K, elem, D, g.nt, wn, plan.wn_eff, NB, Rpost, plan.rounds_pre, n_tasks, plan.resident_reads, n_loads, n_stores,
+         plan.evictions, plan.max_jobs_used, g.max_jobs, g.smem);
+  return 0;
+}
