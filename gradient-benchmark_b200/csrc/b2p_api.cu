@@ -30,12 +30,15 @@ struct b2p_instance {
   unsigned char* d_records = nullptr;
   int* d_mat_dst = nullptr;
   void* d_mats = nullptr;  // [rounds][wn][3][K] matrices in schedule order
-  uint8_t* d_tips = nullptr;  // [tile][N][ct_pad]
+  uint8_t* d_tips = nullptr;      // [tile][2N][ct_pad] masks per column, tip rows in schedule order
+  uint8_t* d_tips_raw = nullptr;  // [N][P] as given by the caller
+  int* d_tip_order = nullptr;     // [2N] tip id of each scheduled row
   double* d_weights = nullptr;
   void* d_msg = nullptr;   // [tile][N-1] blocks: messages m_v = P_v x_v
   void* d_pre = nullptr;   // [tile][N-1] blocks: pre-order partials that left shared memory
   double* d_lpart = nullptr;
   double* d_gpart = nullptr;
+  long long* d_trace = nullptr;  // B2P_TRACE=<file>: per-round clock stamps of CTA 0 (debug)
   double* d_bl_stage = nullptr;   // for the host-buffer entry point
   double* d_out_stage = nullptr;  // [1 + 2N-2]
   double* h_pin_in = nullptr;
@@ -114,8 +117,8 @@ int b2p_destroy(b2p_instance* h) {
   if (!h) return B2P_OK;
   cudaSetDevice(h->cfg.device);
   cudaFree(h->d_records); cudaFree(h->d_mat_dst); cudaFree(h->d_mats);
-  cudaFree(h->d_tips); cudaFree(h->d_weights); cudaFree(h->d_msg); cudaFree(h->d_pre);
-  cudaFree(h->d_lpart); cudaFree(h->d_gpart); cudaFree(h->d_bl_stage); cudaFree(h->d_out_stage);
+  cudaFree(h->d_tips); cudaFree(h->d_tips_raw); cudaFree(h->d_tip_order); cudaFree(h->d_weights); cudaFree(h->d_msg); cudaFree(h->d_pre);
+  cudaFree(h->d_lpart); cudaFree(h->d_trace); cudaFree(h->d_gpart); cudaFree(h->d_bl_stage); cudaFree(h->d_out_stage);
   if (h->h_pin_in) cudaFreeHost(h->h_pin_in);
   if (h->h_pin_out) cudaFreeHost(h->h_pin_out);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -191,7 +194,9 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
 
   const size_t n_br = 2 * (size_t)N - 2;
   const size_t part_bytes = (size_t)h->wg.n_tiles * (size_t)(N - 1) * (size_t)h->wg.blk;
-  if ((rc = dev_alloc(h, &h->d_tips, (size_t)h->wg.n_tiles * N * h->wg.ct_pad))) return bail(rc);
+  if ((rc = dev_alloc(h, &h->d_tips, (size_t)h->wg.n_tiles * 2 * N * h->wg.ct_pad))) return bail(rc);
+  if ((rc = dev_alloc(h, &h->d_tips_raw, (size_t)N * P))) return bail(rc);
+  if ((rc = dev_alloc(h, &h->d_tip_order, sizeof(int) * 2 * N))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_weights, sizeof(double) * P))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_mat_dst, sizeof(int) * 2 * n_br))) return bail(rc);
   if ((rc = dev_alloc(h, (char**)&h->d_msg, part_bytes))) return bail(rc);
@@ -229,10 +234,10 @@ static void fill_walk_params(const b2p_instance* h, bool grad, WalkParams<T>& p)
   p.ir_base = h->plan.ir_base; p.boot_base = h->plan.boot_base;
   for (int i = 0; i < 4; ++i) { p.boot_n[i] = h->plan.boot_n[i]; p.boot_tx[i] = h->plan.boot_tx[i]; }
   p.tile_stride_part = (unsigned long long)(N - 1) * g.blk;
-  p.tile_stride_tips = (unsigned long long)N * g.ct_pad;
+  p.tile_stride_tips = 2ull * N * g.ct_pad;
   p.records = h->d_records; p.mats = (const unsigned char*)h->d_mats;
   p.msg = (unsigned char*)h->d_msg; p.pre = (unsigned char*)h->d_pre; p.tips = h->d_tips;
-  p.weights = h->d_weights; p.lpart = h->d_lpart; p.gpart = h->d_gpart;
+  p.weights = h->d_weights; p.lpart = h->d_lpart; p.gpart = h->d_gpart; p.trace = h->d_trace;
   for (int i = 0; i < 4; ++i) p.freqs[i] = h->freqs[i];
   for (int i = 0; i < 16; ++i) p.q[i] = (T)h->qmat[i];
   for (int k = 0; k < kMaxCatW; ++k) {
@@ -260,6 +265,19 @@ static cudaError_t launch_eval(b2p_instance* h, const double* d_bl, double* d_lo
   const int nb = d_grad ? n_br : 0;
   reduce_kernel<<<(nb + 31) / 32 + 1, 512, 0, st>>>(h->d_gpart, h->d_lpart, h->wg.grid, nb, d_grad, d_logl);
   return cudaGetLastError();
+}
+
+// Tip masks per tile in schedule order: one bulk copy per round brings the rows it needs.
+static int retile_tips(b2p_instance* h) {
+  const WalkGeometry& g = h->wg;
+  const int N = h->cfg.n_tips;
+  const long long total = (long long)g.n_tiles * 2 * N * g.ct_pad;
+  CU(cudaSetDevice(h->cfg.device));
+  tile_tips_kernel<<<(unsigned)((total + 255) / 256), 256>>>(h->d_tips_raw, h->d_tip_order, g.n_tiles, 2 * N, g.ct, g.ct_pad,
+                                                              h->cfg.n_patterns, h->cfg.n_categories, h->d_tips);
+  CU(cudaGetLastError());
+  CU(cudaDeviceSynchronize());
+  return B2P_OK;
 }
 
 static int check_ready(b2p_instance* h) {
@@ -311,34 +329,31 @@ int b2p_set_topology(b2p_instance* h, const int32_t* h_triples) {
   CU(cudaMalloc(&h->d_mats, mats_bytes));
   CU(cudaMemset(h->d_mats, 0, mats_bytes));
   CU(cudaMemcpy(h->d_mat_dst, plan.mat_dst.data(), plan.mat_dst.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+  if ((int)plan.tip_order.size() != 2 * h->cfg.n_tips) return fail(h, B2P_ERR_ARG, "b2p_set_topology: internal error (tip rows)");
+  CU(cudaMemcpy(h->d_tip_order, plan.tip_order.data(), plan.tip_order.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+  plan.tip_order.clear(); plan.tip_order.shrink_to_fit();
   plan.records.clear(); plan.records.shrink_to_fit();
   plan.mat_dst.clear(); plan.mat_dst.shrink_to_fit();
   h->plan = std::move(plan);
+  if (getenv("B2P_TRACE")) {
+    cudaFree(h->d_trace);
+    CU(cudaMalloc((void**)&h->d_trace, sizeof(long long) * 10 * h->plan.rounds));
+    CU(cudaMemset(h->d_trace, 0, sizeof(long long) * 10 * h->plan.rounds));
+  }
   h->have_topology = true;
+  if (h->have_tips) { int rc = retile_tips(h); if (rc) return rc; }
   return B2P_OK;
 }
 
 int b2p_set_tip_states(b2p_instance* h, const uint8_t* h_masks) {
   if (!h || !h_masks) return h ? fail(h, B2P_ERR_ARG, "b2p_set_tip_states: null masks") : B2P_ERR_ARG;
-  const int N = h->cfg.n_tips, P = h->cfg.n_patterns, K = h->cfg.n_categories;
+  const int N = h->cfg.n_tips, P = h->cfg.n_patterns;
   const size_t n = (size_t)N * P;
   for (size_t i = 0; i < n; ++i)
     if (h_masks[i] > 15) return fail(h, B2P_ERR_ARG, "b2p_set_tip_states: mask %u > 15 at %zu", h_masks[i], i);
-  // one row of ct_pad bytes per (tile, tip): the mask of each column's pattern; padding = 15 (any state)
-  const WalkGeometry& g = h->wg;
-  std::vector<uint8_t> tiled((size_t)g.n_tiles * N * g.ct_pad, 15);
-  const long long n_cols = (long long)P * K;
-  for (int tile = 0; tile < g.n_tiles; ++tile)
-    for (int tip = 0; tip < N; ++tip) {
-      uint8_t* row = tiled.data() + ((size_t)tile * N + tip) * g.ct_pad;
-      const uint8_t* src = h_masks + (size_t)tip * P;
-      for (int c = 0; c < g.ct; ++c) {
-        const long long cg = (long long)tile * g.ct + c;
-        if (cg < n_cols) row[c] = src[cg / K];
-      }
-    }
   CU(cudaSetDevice(h->cfg.device));
-  CU(cudaMemcpy(h->d_tips, tiled.data(), tiled.size(), cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(h->d_tips_raw, h_masks, n, cudaMemcpyHostToDevice));
+  if (h->have_topology) { int rc = retile_tips(h); if (rc) return rc; }
   h->have_tips = true;
   return B2P_OK;
 }
@@ -420,6 +435,19 @@ int b2p_loglik_grad_host(b2p_instance* h, const double* h_bl, double* h_logl, do
   CU(cudaStreamSynchronize(h->own_stream));
   *h_logl = h->h_pin_out[0];
   if (h_grad) memcpy(h_grad, h->h_pin_out + 1, sizeof(double) * n_br);
+  if (h->d_trace && h_grad) {
+    const int R = h->plan.rounds;
+    std::vector<long long> tr(10 * (size_t)R);
+    CU(cudaMemcpy(tr.data(), h->d_trace, tr.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+    if (FILE* f = fopen(getenv("B2P_TRACE"), "w")) {
+      for (int w = 0; w < 2; ++w)
+        for (int q = 0; q < R; ++q) {
+          const long long* r = tr.data() + ((size_t)w * R + q) * 5;
+          fprintf(f, "%d %d %lld %lld %lld %lld %lld\n", w, q, r[0], r[1], r[2], r[3], r[4]);
+        }
+      fclose(f);
+    }
+  }
   return B2P_OK;
 }
 

@@ -43,6 +43,23 @@ __global__ void transition_kernel(ModelParams m, const double* __restrict__ bl, 
   }
 }
 
+// ---------------------------------------------------------------------------- K0 (setup)
+// Tip state masks per tile: out[tile][row][c] = mask of tip order[row] at the pattern of
+// column tile*ct + c; 15 (any state) for padding columns.  Runs when tips or topology change.
+__global__ void tile_tips_kernel(const uint8_t* __restrict__ raw, const int* __restrict__ order, int n_tiles,
+                                 int n_rows, int ct, int ct_pad, int n_patterns, int n_cat, uint8_t* __restrict__ out) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long total = (long long)n_tiles * n_rows * ct_pad;
+  if (idx >= total) return;
+  const int c = (int)(idx % ct_pad);
+  const long long tr = idx / ct_pad;
+  const int row = (int)(tr % n_rows), tile = (int)(tr / n_rows);
+  const long long cg = (long long)tile * ct + c;
+  uint8_t m = 15;
+  if (c < ct && cg < (long long)n_patterns * n_cat) m = raw[(size_t)order[row] * n_patterns + cg / n_cat];
+  out[idx] = m;
+}
+
 // ---------------------------------------------------------------------------- K4
 // grad[b] = sum_g gpart[g][b];  logl = sum_g lpart[g].  Fixed summation order.
 __global__ void __launch_bounds__(512) reduce_kernel(const double* __restrict__ gpart,

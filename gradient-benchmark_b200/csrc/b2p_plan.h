@@ -125,6 +125,8 @@ struct WalkPlan {
   std::vector<uint8_t> records;  // [rounds] CR, then [rounds] IR, then the boot jobs
   uint32_t ir_base = 0, boot_base = 0;
   uint32_t boot_n[4] = {0, 0, 0, 0}, boot_tx[4] = {0, 0, 0, 0};  // loads of rounds 0..depth-1
+  std::vector<int32_t> tip_order;    // tip id of every tip row in schedule order (each tip: once per pass)
+  std::vector<int32_t> tip_row_off;  // [rounds + 1] first row of each round
   std::vector<int32_t> mat_dst;  // [2N-2][2]: matrix slot ((round*wn+slot)*3+which) in the post / pre bundles, -1 none
   long long resident_reads = 0, loads_msg = 0, loads_pre = 0, stores_msg = 0, stores_pre = 0, evictions = 0;
   int max_jobs_used = 0;
@@ -154,7 +156,7 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
   out.wn_eff = wn_eff;
   const int n_nodes = 2 * N - 1, root = 2 * N - 2;
   if ((unsigned long long)(N - 1) * (unsigned long long)g.blk > 0xFFFFFFF0ull ||
-      (unsigned long long)N * (unsigned long long)g.ct_pad > 0xFFFFFFF0ull) {
+      2ull * (unsigned long long)N * (unsigned long long)g.ct_pad > 0xFFFFFFF0ull) {
     why = "tile too large for 32-bit copy offsets";
     return false;
   }
@@ -429,18 +431,27 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
   const uint32_t cr_total = (uint32_t)R * g.cr_bytes;
   out.ir_base = cr_total;
   out.boot_base = out.ir_base + (uint32_t)R * g.ir_bytes;
-  // fixed per-round loads: tip rows, matrix bundle, the round's own records
+  // fixed per-round loads: tip rows (one copy: rows are stored in schedule order), matrix
+  // bundle, the round's own records
+  // row within the round's tip copy, per (task, side)
+  std::vector<uint16_t> tip_row_post(2 * (size_t)n_nodes, 0), tip_row_pre(2 * (size_t)n_nodes, 0);
+  out.tip_row_off.assign(R + 1, 0);
   for (int f = 0; f < R; ++f) {
     const int st = f % S;
+    int rows = 0;
     for (int s = 0; s < (int)tasks[f].size(); ++s) {
       const int v = tasks[f][s];
       for (int side = 0; side < 2; ++side) {
         const int c = side ? right[v] : left[v];
         if (c >= N) continue;
-        loads[f].push_back({JK_TIPS, (uint32_t)c * (uint32_t)g.ct_pad,
-                            (uint32_t)(g.off_tips + st * g.tips_bytes + (s * 2 + side) * g.ct_pad), (uint32_t)g.ct_pad});
+        (f < Rpost ? tip_row_post : tip_row_pre)[2 * (size_t)v + side] = (uint16_t)rows++;
+        out.tip_order.push_back(c);
       }
     }
+    out.tip_row_off[f + 1] = out.tip_row_off[f] + rows;
+    if (rows)
+      loads[f].push_back({JK_TIPS, (uint32_t)out.tip_row_off[f] * (uint32_t)g.ct_pad,
+                          (uint32_t)(g.off_tips + st * g.tips_bytes), (uint32_t)(rows * g.ct_pad)});
     if (!tasks[f].empty())
       loads[f].push_back({JK_MATS, (uint32_t)f * (uint32_t)g.mats_bytes, (uint32_t)(g.off_mats + st * g.mats_bytes),
                           (uint32_t)((int)tasks[f].size() * 3 * K * g.mat_stride)});
@@ -502,6 +513,8 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
       const int slot3 = (q * wn + s) * 3;
       WalkDesc& e = d[s];
       e.flags = WF_LIVE;
+      e.pad0 = (q < Rpost ? tip_row_post : tip_row_pre)[2 * (size_t)v];      // tip row of the left child
+      e.pad1 = (q < Rpost ? tip_row_post : tip_row_pre)[2 * (size_t)v + 1];  // ... of the right child
       if (l < N) e.flags |= WF_TIP_L;
       if (r < N) e.flags |= WF_TIP_R;
       if (v == root) e.flags |= WF_ROOT;

@@ -31,6 +31,8 @@
 namespace b2p {
 
 constexpr int kMaxCatW = 32;
+// lanes per warp that may issue result stores: stores per round <= 2 * wn <= NT / 4 = 8 * (NT / 32)
+constexpr int kStoreLanes = 8;
 
 template <typename T>
 struct WalkParams {
@@ -42,15 +44,16 @@ struct WalkParams {
   unsigned ir_base, boot_base;
   unsigned boot_n[4], boot_tx[4];
   unsigned long long tile_stride_part;  // (N-1) * blk
-  unsigned long long tile_stride_tips;  // N * ct_pad
+  unsigned long long tile_stride_tips;  // 2N * ct_pad
   const unsigned char* records;
   const unsigned char* mats;  // [rounds][wn][3][K] matrices in schedule order (written by K1)
   unsigned char* msg;         // [tile][N-1] blocks: m_v
   unsigned char* pre;         // [tile][N-1] blocks: u_c that had to leave shared memory
-  const unsigned char* tips;  // [tile][N][ct_pad] state masks per column
+  const unsigned char* tips;  // [tile][2N][ct_pad] state masks per column, tip rows in schedule order
   const double* weights;      // [P]
   double* lpart;              // [grid]
   double* gpart;              // [grid][2N-2]
+  long long* trace;           // debug: [2][rounds][5] clock stamps of CTA 0 (warp 0 / last warp), or null
   T q[16];
   double freqs[4];
   double cat_w[kMaxCatW];
@@ -238,33 +241,48 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
     int st = 0;  // stage of the current round: q % S
     for (int q = 0; q < R; ++q) {
       const int par = q & 1;
+      const bool tr = p.trace && blockIdx.x == 0 && (t == 0 || t == NT - 32) && tile == 0;
+      long long* trow = tr ? p.trace + ((t ? 1 : 0) * (long long)R + q) * 5 : nullptr;
+      if (tr) trow[0] = clock64();
       mbar_wait(bar0 + 8 * st, (phase_bits >> st) & 1u);
+      if (tr) trow[1] = clock64();
       phase_bits ^= 1u << st;
       const unsigned char* ir = smem + p.off_ir + st * p.ir_bytes;
       const uint4 hdr = *reinterpret_cast<const uint4*>(ir);
-      if (warp == 0) {
+      {
+        // Copy issue, spread over the warps: job j belongs to warp j % (NT/32), one lane each
+        // (a bulk-copy instruction costs its thread ~50 cycles; 32 lanes of one warp would
+        // serialise).  Stores (results of round q-1) go first: the end of this round waits
+        // until they have read shared memory.
+        constexpr int NW = NT / 32;
         const int st_next = st == 0 ? S - 1 : st - 1;  // (q + D) % S with S = D + 1
         const unsigned bar = bar0 + 8 * st_next;
         const unsigned n_loads = (q + D < R) ? hdr.x : 0u;
         const uint4* jobs = reinterpret_cast<const uint4*>(ir + 16);
-        if (lane == 0 && n_loads) mbar_expect_tx(bar, hdr.z);
-        __syncwarp();
-        for (unsigned j = lane; j < n_loads; j += 32) {
+        if (t == 0 && n_loads) mbar_expect_tx(bar, hdr.z);
+        const unsigned n_st = hdr.y;
+        // lane l of warp w takes jobs w + NW * l
+        const unsigned j = warp + NW * lane;
+        if (lane < kStoreLanes) {  // these lanes commit one (possibly empty) group per round
+          if (j < n_st) {
+            const uint4 jb = jobs[hdr.x + j];
+            bulk_store(const_cast<unsigned char*>(gptr(jb.w, jb.x)), sbase + jb.y, jb.z);
+          }
+          bulk_commit();
+        }
+        if (j < n_loads) {
           const uint4 jb = jobs[j];
           bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar);
         }
-        for (unsigned j = hdr.x + lane; j < hdr.x + hdr.y; j += 32) {
-          const uint4 jb = jobs[j];
-          bulk_store(const_cast<unsigned char*>(gptr(jb.w, jb.x)), sbase + jb.y, jb.z);
-        }
-        bulk_commit();
       }
-
+      if (tr) trow[2] = clock64();
       // ---- this thread's task
+      unsigned tip_l = 0, tip_r = 0;
       unsigned flags = 0, src_l = kNoBlk, src_r = kNoBlk, src_v = kNoBlk, dst0 = kNoBlk, dst1 = kNoBlk;
       const unsigned char* cr = smem + p.off_cr + st * p.cr_bytes;
       if (in_slot) {
         const uint4 dw = *reinterpret_cast<const uint4*>(cr + s * 16);
+        tip_l = dw.w & 0xffffu; tip_r = dw.w >> 16;
         src_l = dw.x & 0xffffu; src_r = dw.x >> 16;
         src_v = dw.y & 0xffffu; dst0 = dw.y >> 16;
         dst1 = dw.z & 0xffffu; flags = dw.z >> 16;
@@ -280,14 +298,14 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
         const T* m0 = reinterpret_cast<const T*>(mslot);
         const T* m1 = reinterpret_cast<const T*>(mslot + kk * p.mat_stride);
         const T* m2 = reinterpret_cast<const T*>(mslot + 2 * kk * p.mat_stride);
-        const unsigned char* tiprow = smem + p.off_tips + st * p.tips_bytes + s * 2 * p.ct_pad + col;
+        const unsigned char* tiprow = smem + p.off_tips + st * p.tips_bytes + col;
         T ma[4], mb[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) ma[i] = mb[i] = (T)0;
         if (live) {
-          if (flags & WF_TIP_L) tip_message(m1, tiprow[0], ma);
+          if (flags & WF_TIP_L) tip_message(m1, tiprow[tip_l * p.ct_pad], ma);
           else s_ld(smem + src_l * 16 + c16, plane, ma);
-          if (flags & WF_TIP_R) tip_message(m2, tiprow[p.ct_pad], mb);
+          if (flags & WF_TIP_R) tip_message(m2, tiprow[tip_r * p.ct_pad], mb);
           else s_ld(smem + src_r * 16 + c16, plane, mb);
         }
         double2* gslot = reinterpret_cast<double2*>(smem + p.off_gbuf) + (par * p.wn + s) * p.ct + col;
@@ -392,11 +410,13 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
       }
 
       fence_async_smem();
-      if (warp == 0) {
+      if (lane < kStoreLanes) {
         asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         asm volatile("cp.async.bulk.wait_group 1;" ::: "memory");
       }
+      if (tr) trow[3] = clock64();
       __syncthreads();
+      if (tr) trow[4] = clock64();
       st = st + 1 == S ? 0 : st + 1;
     }
     // fold the last round
@@ -423,7 +443,7 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
         }
       }
     }
-    if (warp == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if (lane < kStoreLanes) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     __syncthreads();
   }
 

@@ -34,7 +34,7 @@ struct WalkDesc {
   uint16_t src_v;         // pre: parent-side partial of the node (kNoBlk: root)
   uint16_t dst0, dst1;    // post: dst0 = message of the node; pre: partials of the children
   uint16_t flags;
-  uint16_t pad0, pad1;
+  uint16_t pad0, pad1;    // tip rows (within the round's tip-row copy) of the left / right child
 };
 static_assert(sizeof(WalkDesc) == 16, "WalkDesc must be 16 bytes");
 

@@ -90,8 +90,9 @@ int main(int argc, char** argv) {
       tag[b] = 1 + vid; inflight_until[b] = f;
       ++n_loads;
     } else if (j.kind == JK_TIPS) {
-      if ((int)j.bytes != g.ct_pad || (int)j.soff < g.off_tips + (f % S) * g.tips_bytes ||
-          (int)(j.soff + j.bytes) > g.off_tips + (f % S + 1) * g.tips_bytes) return "tips job";
+      if ((int)j.soff != g.off_tips + (f % S) * g.tips_bytes || (int)j.bytes > g.tips_bytes ||
+          (int)j.goff != plan.tip_row_off[f] * g.ct_pad ||
+          (int)j.bytes != (plan.tip_row_off[f + 1] - plan.tip_row_off[f]) * g.ct_pad) return "tips job";
     } else if (j.kind == JK_MATS) {
       if ((int)j.soff != g.off_mats + (f % S) * g.mats_bytes || (int)j.bytes > g.mats_bytes || j.goff != (uint32_t)f * g.mats_bytes) return "mats job";
     } else if (j.kind == JK_REC) {
@@ -170,6 +171,9 @@ int main(int argc, char** argv) {
       }
       const int l = left[v], r = right[v];
       if (((e.flags & WF_TIP_L) != 0) != (l < N) || ((e.flags & WF_TIP_R) != 0) != (r < N)) FAIL("tip flags");
+      const int nrows = plan.tip_row_off[q + 1] - plan.tip_row_off[q];
+      if (l < N && (e.pad0 >= nrows || plan.tip_order[plan.tip_row_off[q] + e.pad0] != l)) FAIL("round %d: left tip row", q);
+      if (r < N && (e.pad1 >= nrows || plan.tip_order[plan.tip_row_off[q] + e.pad1] != r)) FAIL("round %d: right tip row", q);
       auto need = [&](uint16_t src, int vid, const char* what) -> bool {
         if (src == kNoBlk || !check_soff((uint32_t)src * 16)) { printf("FAIL round %d node %d: %s operand offset\n", q, v, what); return false; }
         const int b = off_blk(src);
