@@ -173,9 +173,11 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   if (const char* s = getenv("B2P_NT")) nt_force = atoi(s);
   if (const char* s = getenv("B2P_CT")) ct_force = atoi(s);
   if (const char* s = getenv("B2P_DEPTH")) depth = atoi(s);
+  int n_copy = 2;
+  if (const char* s = getenv("B2P_NP")) n_copy = std::max(1, std::min(4, atoi(s)));
   h->ctas_per_sm = 1;
   const size_t smem_budget = (size_t)prop.sharedMemPerBlockOptin - 1024;  // static shared + reservation
-  if (!plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms, smem_budget, nt_force, ct_force, 1, depth, h->wg)) {
+  if (!plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms, smem_budget, nt_force, ct_force, 1, depth, n_copy, h->wg)) {
     fail(h, B2P_ERR_UNSUPPORTED, "b2p_create: no kernel geometry fits shared memory (K=%d, threads=%d)", K, nt_force);
     return bail(B2P_ERR_UNSUPPORTED);
   }
@@ -225,7 +227,7 @@ static void fill_walk_params(const b2p_instance* h, bool grad, WalkParams<T>& p)
   const int N = h->cfg.n_tips, K = h->cfg.n_categories, P = h->cfg.n_patterns;
   const WalkGeometry& g = h->wg;
   p.n_tiles = g.n_tiles; p.rounds_run = grad ? h->plan.rounds : h->plan.rounds_post;
-  p.n_branches = 2 * N - 2; p.n_cat = K; p.n_cols = P * K; p.n_patterns = P;
+  p.n_branches = 2 * N - 2; p.n_cat = K; p.n_cols = P * K; p.n_patterns = P; p.n_copy_warps = g.n_copy_warps; p.pad_ = 0;
   p.ct = g.ct; p.ts = g.ts; p.cpw = g.cpw; p.wn = g.wn; p.stages = g.stages; p.depth = g.depth;
   p.blk = g.blk; p.plane = g.ct * 16; p.ct_pad = g.ct_pad; p.mat_stride = g.mat_stride;
   p.mats_bytes = g.mats_bytes; p.cr_bytes = g.cr_bytes; p.ir_bytes = g.ir_bytes; p.tips_bytes = g.tips_bytes;

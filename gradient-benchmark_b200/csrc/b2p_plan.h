@@ -36,7 +36,7 @@ namespace b2p {
 
 struct WalkGeometry {
   int nt = 0, ct = 0, ts = 0, cpw = 32, wn = 0, depth = 1, stages = 2, n_tiles = 0, grid = 0;
-  int elem = 8, K = 1;
+  int elem = 8, K = 1, n_copy_warps = 1;
   int ct_pad = 0;      // bytes of one tip row of a tile (ct rounded up to 16)
   int blk = 0;         // bytes of one block
   int mat_stride = 0;  // bytes between 4x4 matrices (padded: bank shift between categories)
@@ -87,7 +87,7 @@ inline int layout_walk(WalkGeometry& g, size_t smem_max) {
 
 // Choose the tile width and thread geometry.  elem = sizeof(T).
 inline bool plan_geometry(int n_tips, int n_cols, int K, int elem, int n_sms, size_t smem_max, int nt_force,
-                          int ct_force, int ctas_per_sm, int depth, WalkGeometry& g) {
+                          int ct_force, int ctas_per_sm, int depth, int n_copy_warps, WalkGeometry& g) {
   n_sms *= ctas_per_sm;
   const bool packed = (32 % K) == 0;
   const int cpw = packed ? 32 : (32 / K) * K;
@@ -102,12 +102,12 @@ inline bool plan_geometry(int n_tips, int n_cols, int K, int elem, int n_sms, si
   const int nts[4] = {1024, 768, 512, 256};
   for (int nt : nts) {
     if (nt_force > 0 && nt != nt_force) continue;
-    if (ts > nt) continue;
-    int wn = std::min(std::min(nt / ts, std::max(1, n_tips - 1)), 64);
+    if (ts > nt - 32 * n_copy_warps) continue;  // the last warps only issue copies
+    int wn = std::min(std::min((nt - 32 * n_copy_warps) / ts, std::max(1, n_tips - 1)), 64);
     for (; wn >= 1; --wn) {
       g = WalkGeometry();
       g.nt = nt; g.ct = ct; g.ts = ts; g.cpw = cpw; g.wn = wn; g.elem = elem; g.K = K;
-      g.depth = std::max(1, std::min(depth, 3)); g.stages = g.depth + 1;
+      g.depth = std::max(1, std::min(depth, 3)); g.stages = g.depth + 1; g.n_copy_warps = n_copy_warps;
       const int n_pool = layout_walk(g, smem_max);
       // enough blocks for one full round of operands in flight per stage plus two rounds of results
       if (n_pool >= std::max(3 * g.stages + 4, 4 * wn)) break;

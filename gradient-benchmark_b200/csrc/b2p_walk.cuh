@@ -7,7 +7,8 @@
 // (slot t / ts, column t % ts) — slots are packed at thread granularity so an awkward tile
 // width (68 columns at 1000 taxa x 10k patterns on 148 SMs) still fills the lanes.
 //
-// Data movement is entirely asynchronous and issued by ONE warp from lists the host
+// Data movement is entirely asynchronous and issued by ONE warp (the last one, which holds
+// no compute threads) from lists the host
 // planner wrote (b2p_plan.h): every operand block, tip row, matrix bundle and descriptor
 // record of round q + depth is a cp.async.bulk (TMA, UBLKCP in SASS) global -> shared copy
 // that completes on the mbarrier of that round; every result block is written to shared
@@ -31,13 +32,11 @@
 namespace b2p {
 
 constexpr int kMaxCatW = 32;
-// lanes per warp that may issue result stores: stores per round <= 2 * wn <= NT / 4 = 8 * (NT / 32)
-constexpr int kStoreLanes = 8;
 
 template <typename T>
 struct WalkParams {
   int n_tiles, rounds_run, n_branches, n_cat;
-  int n_cols, n_patterns;
+  int n_cols, n_patterns, n_copy_warps, pad_;
   int ct, ts, cpw, wn, stages, depth;
   int blk, plane, ct_pad, mat_stride, mats_bytes, cr_bytes, ir_bytes, tips_bytes;
   int off_bar, off_cr, off_ir, off_mats, off_tips, off_gbuf, off_gids, off_scount;
@@ -223,7 +222,7 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
                                : kind == JK_MATS ? p.mats : p.records;
       return b + goff;
     };
-    if (warp == 0) {  // boot: loads of rounds 0 .. depth-1
+    if (warp == NT / 32 - 1) {  // boot: loads of rounds 0 .. depth-1
       const uint4* jobs = reinterpret_cast<const uint4*>(p.records + p.boot_base);
       unsigned j0 = 0;
       for (int f = 0; f < D && f < R; ++f) {
@@ -249,28 +248,24 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
       phase_bits ^= 1u << st;
       const unsigned char* ir = smem + p.off_ir + st * p.ir_bytes;
       const uint4 hdr = *reinterpret_cast<const uint4*>(ir);
-      {
-        // Copy issue, spread over the warps: job j belongs to warp j % (NT/32), one lane each
-        // (a bulk-copy instruction costs its thread ~50 cycles; 32 lanes of one warp would
-        // serialise).  Stores (results of round q-1) go first: the end of this round waits
-        // until they have read shared memory.
-        constexpr int NW = NT / 32;
+      if (warp >= NT / 32 - p.n_copy_warps) {
+        // Copy warps (the last warps hold no compute threads): stores of round q-1's results
+        // first — the end of this round waits until they have read shared memory — then the
+        // loads of round q + depth.  Issuing them from warps of their own lets the copies
+        // overlap the arithmetic; one warp issues a bulk copy every ~100 cycles, so several
+        // share the list (job j belongs to copy warp j % n_copy_warps).
         const int st_next = st == 0 ? S - 1 : st - 1;  // (q + D) % S with S = D + 1
         const unsigned bar = bar0 + 8 * st_next;
         const unsigned n_loads = (q + D < R) ? hdr.x : 0u;
         const uint4* jobs = reinterpret_cast<const uint4*>(ir + 16);
-        if (t == 0 && n_loads) mbar_expect_tx(bar, hdr.z);
-        const unsigned n_st = hdr.y;
-        // lane l of warp w takes jobs w + NW * l
-        const unsigned j = warp + NW * lane;
-        if (lane < kStoreLanes) {  // these lanes commit one (possibly empty) group per round
-          if (j < n_st) {
-            const uint4 jb = jobs[hdr.x + j];
-            bulk_store(const_cast<unsigned char*>(gptr(jb.w, jb.x)), sbase + jb.y, jb.z);
-          }
-          bulk_commit();
+        const unsigned np = p.n_copy_warps, pw = warp - (NT / 32 - np);
+        if (pw == 0 && lane == 0 && n_loads) mbar_expect_tx(bar, hdr.z);
+        for (unsigned j = pw + np * lane; j < hdr.y; j += 32 * np) {
+          const uint4 jb = jobs[hdr.x + j];
+          bulk_store(const_cast<unsigned char*>(gptr(jb.w, jb.x)), sbase + jb.y, jb.z);
         }
-        if (j < n_loads) {
+        bulk_commit();  // one (possibly empty) group per lane per round
+        for (unsigned j = pw + np * lane; j < n_loads; j += 32 * np) {
           const uint4 jb = jobs[j];
           bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar);
         }
@@ -410,7 +405,7 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
       }
 
       fence_async_smem();
-      if (lane < kStoreLanes) {
+      if (warp >= NT / 32 - p.n_copy_warps) {
         asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         asm volatile("cp.async.bulk.wait_group 1;" ::: "memory");
       }
@@ -443,7 +438,7 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
         }
       }
     }
-    if (lane < kStoreLanes) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if (warp >= NT / 32 - p.n_copy_warps) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     __syncthreads();
   }
 

@@ -51,7 +51,7 @@ int main(int argc, char** argv) {
             elem = atoi(argv[6]), smem = atoi(argv[7]), depth = atoi(argv[8]), nt = argc > 9 ? atoi(argv[9]) : 0;
   std::vector<int32_t> tr = random_triples(N, shape, seed);
   WalkGeometry g;
-  if (!plan_geometry(N, ct * 148, K, elem, 148, smem, nt, ct, 1, depth, g)) FAIL("geometry");
+  if (!plan_geometry(N, ct * 148, K, elem, 148, smem, nt, ct, 1, depth, 1, g)) FAIL("geometry");
   WalkPlan plan;
   std::string why;
   if (!plan_walk_auto(N, tr.data(), g, plan, why)) FAIL("plan: %s", why.c_str());
