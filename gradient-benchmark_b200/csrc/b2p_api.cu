@@ -85,20 +85,27 @@ static int dev_alloc(b2p_instance* h, T** p, size_t n_bytes) {
 
 // ---------------------------------------------------------------- kernel selection
 template <typename T, int K>
-static const void* walk_select_nt(int nt) {
+static const void* walk_select_nt(int nt, int cpt) {
+  if (cpt == 2) {
+    switch (nt) {
+      case 512: return (const void*)walk_kernel<T, K, 512, 2>;
+      case 256: return (const void*)walk_kernel<T, K, 256, 2>;
+    }
+    return nullptr;
+  }
   switch (nt) {
-    case 1024: return (const void*)walk_kernel<T, K, 1024>;
-    case 768: return (const void*)walk_kernel<T, K, 768>;
-    case 512: return (const void*)walk_kernel<T, K, 512>;
-    case 256: return (const void*)walk_kernel<T, K, 256>;
+    case 1024: return (const void*)walk_kernel<T, K, 1024, 1>;
+    case 768: return (const void*)walk_kernel<T, K, 768, 1>;
+    case 512: return (const void*)walk_kernel<T, K, 512, 1>;
+    case 256: return (const void*)walk_kernel<T, K, 256, 1>;
   }
   return nullptr;
 }
 template <typename T>
-static const void* walk_select(int K, int nt) {
-  if (K == 1) return walk_select_nt<T, 1>(nt);
-  if (K == 4) return walk_select_nt<T, 4>(nt);
-  return walk_select_nt<T, 0>(nt);
+static const void* walk_select(int K, int nt, int cpt) {
+  if (K == 1) return walk_select_nt<T, 1>(nt, cpt);
+  if (K == 4) return walk_select_nt<T, 4>(nt, cpt);
+  return walk_select_nt<T, 0>(nt, cpt);
 }
 
 static size_t elem_size(const b2p_instance* h) {
@@ -173,15 +180,16 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   if (const char* s = getenv("B2P_NT")) nt_force = atoi(s);
   if (const char* s = getenv("B2P_CT")) ct_force = atoi(s);
   if (const char* s = getenv("B2P_DEPTH")) depth = atoi(s);
-  int n_copy = 2;
+  int n_copy = 2, cpt = 2;
   if (const char* s = getenv("B2P_NP")) n_copy = std::max(1, std::min(4, atoi(s)));
+  if (const char* s = getenv("B2P_CPT")) cpt = atoi(s) == 1 ? 1 : 2;
   h->ctas_per_sm = 1;
   const size_t smem_budget = (size_t)prop.sharedMemPerBlockOptin - 1024;  // static shared + reservation
-  if (!plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms, smem_budget, nt_force, ct_force, 1, depth, n_copy, h->wg)) {
+  if (!plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms, smem_budget, nt_force, ct_force, depth, n_copy, cpt, h->wg)) {
     fail(h, B2P_ERR_UNSUPPORTED, "b2p_create: no kernel geometry fits shared memory (K=%d, threads=%d)", K, nt_force);
     return bail(B2P_ERR_UNSUPPORTED);
   }
-  h->kernel = (cfg->precision == B2P_PRECISION_F32) ? walk_select<float>(K, h->wg.nt) : walk_select<double>(K, h->wg.nt);
+  h->kernel = (cfg->precision == B2P_PRECISION_F32) ? walk_select<float>(K, h->wg.nt, h->wg.cpt) : walk_select<double>(K, h->wg.nt, h->wg.cpt);
   if (!h->kernel) { fail(h, B2P_ERR_ARG, "b2p_create: no kernel for %d threads", h->wg.nt); return bail(B2P_ERR_ARG); }
   if ((e = cudaFuncSetAttribute(h->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->wg.smem)) != cudaSuccess) {
     fail(h, B2P_ERR_CUDA, "cudaFuncSetAttribute(smem=%zu): %s", h->wg.smem, cudaGetErrorString(e));
@@ -227,12 +235,12 @@ static void fill_walk_params(const b2p_instance* h, bool grad, WalkParams<T>& p)
   const int N = h->cfg.n_tips, K = h->cfg.n_categories, P = h->cfg.n_patterns;
   const WalkGeometry& g = h->wg;
   p.n_tiles = g.n_tiles; p.rounds_run = grad ? h->plan.rounds : h->plan.rounds_post;
-  p.n_branches = 2 * N - 2; p.n_cat = K; p.n_cols = P * K; p.n_patterns = P; p.n_copy_warps = g.n_copy_warps; p.pad_ = 0;
+  p.n_branches = 2 * N - 2; p.n_cat = K; p.n_cols = P * K; p.n_patterns = P; p.n_copy_warps = g.n_copy_warps;
   p.ct = g.ct; p.ts = g.ts; p.cpw = g.cpw; p.wn = g.wn; p.stages = g.stages; p.depth = g.depth;
   p.blk = g.blk; p.plane = g.ct * 16; p.ct_pad = g.ct_pad; p.mat_stride = g.mat_stride;
-  p.mats_bytes = g.mats_bytes; p.cr_bytes = g.cr_bytes; p.ir_bytes = g.ir_bytes; p.tips_bytes = g.tips_bytes;
-  p.off_bar = g.off_bar; p.off_cr = g.off_cr; p.off_ir = g.off_ir; p.off_mats = g.off_mats; p.off_tips = g.off_tips;
-  p.off_gbuf = g.off_gbuf; p.off_gids = g.off_gids; p.off_scount = g.off_scount;
+  p.frame_bytes = g.frame_bytes; p.off_frame = g.off_frame; p.rel_cr = g.rel_cr; p.rel_mats = g.rel_mats;
+  p.rel_tips = g.rel_tips;
+  p.off_bar = g.off_bar; p.off_gbuf = g.off_gbuf; p.off_gids = g.off_gids; p.off_scount = g.off_scount;
   p.ir_base = h->plan.ir_base; p.boot_base = h->plan.boot_base;
   for (int i = 0; i < 4; ++i) { p.boot_n[i] = h->plan.boot_n[i]; p.boot_tx[i] = h->plan.boot_tx[i]; }
   p.tile_stride_part = (unsigned long long)(N - 1) * g.blk;

@@ -37,6 +37,9 @@ namespace b2p {
 struct WalkGeometry {
   int nt = 0, ct = 0, ts = 0, cpw = 32, wn = 0, depth = 1, stages = 2, n_tiles = 0, grid = 0;
   int elem = 8, K = 1, n_copy_warps = 1;
+  int cpt = 1;         // columns per thread (2: thread tt of a slot owns columns tt and tt + ts)
+  int frame_bytes = 0; // one stage's frame: issue record | descriptors + ids | matrices | tip rows
+  int off_frame = 0, rel_ir = 0, rel_cr = 0, rel_mats = 0, rel_tips = 0;
   int ct_pad = 0;      // bytes of one tip row of a tile (ct rounded up to 16)
   int blk = 0;         // bytes of one block
   int mat_stride = 0;  // bytes between 4x4 matrices (padded: bank shift between categories)
@@ -66,11 +69,15 @@ inline int layout_walk(WalkGeometry& g, size_t smem_max) {
   g.tips_bytes = wn * 2 * g.ct_pad;
   int off = 0;
   g.off_bar = off; off += 64;  // up to 8 mbarriers
-  g.off_cr = off; off += S * g.cr_bytes;
-  g.off_ir = off; off += S * g.ir_bytes;
-  g.off_mats = off; off += align16(S * g.mats_bytes);
-  g.off_tips = off; off += S * g.tips_bytes;
-  g.off_gbuf = off; off += 2 * wn * g.ct * 16;
+  g.rel_ir = 0;
+  g.rel_cr = g.rel_ir + g.ir_bytes;
+  g.rel_mats = g.rel_cr + g.cr_bytes;
+  g.rel_tips = g.rel_mats + align16(g.mats_bytes);
+  g.frame_bytes = g.rel_tips + g.tips_bytes;
+  g.off_frame = off; off += S * g.frame_bytes;
+  g.off_ir = g.off_frame + g.rel_ir; g.off_cr = g.off_frame + g.rel_cr;
+  g.off_mats = g.off_frame + g.rel_mats; g.off_tips = g.off_frame + g.rel_tips;
+  g.off_gbuf = off; off += 2 * wn * g.ts * 16;  // one (sum_a, sum_b) pair per compute thread
   g.off_gids = off; off += align16(2 * wn * 8);
   g.off_scount = off; off += align16(g.ct * 4);
   off = (off + 127) & ~127;
@@ -85,31 +92,35 @@ inline int layout_walk(WalkGeometry& g, size_t smem_max) {
   return g.n_pool;
 }
 
-// Choose the tile width and thread geometry.  elem = sizeof(T).
-inline bool plan_geometry(int n_tips, int n_cols, int K, int elem, int n_sms, size_t smem_max, int nt_force,
-                          int ct_force, int ctas_per_sm, int depth, int n_copy_warps, WalkGeometry& g) {
-  n_sms *= ctas_per_sm;
+// Choose the tile width and thread geometry.  elem = sizeof(T).  cpt = columns per thread
+// (2 halves the per-column cost of descriptors, matrix reads and address arithmetic; it
+// needs the 128 registers a 512-thread CTA leaves each thread).
+inline bool plan_geometry_cpt(int n_tips, int n_cols, int K, int elem, int n_sms, size_t smem_max, int nt_force,
+                              int ct_force, int depth, int n_copy_warps, int cpt, WalkGeometry& g) {
   const bool packed = (32 % K) == 0;
+  if (cpt == 2 && !packed) return false;
   const int cpw = packed ? 32 : (32 / K) * K;
-  const int ct_max = 128, ct_min = (8 + K - 1) / K * K;
+  const int q = K * cpt;  // tile widths are multiples of this
+  const int ct_max = 128, ct_min = (8 + q - 1) / q * q;
   int m = std::max(1, (int)((n_cols + (long long)n_sms * ct_max - 1) / ((long long)n_sms * ct_max)));
   int ct = (int)((n_cols + (long long)n_sms * m - 1) / ((long long)n_sms * m));
-  ct = (ct + K - 1) / K * K;
+  ct = (ct + q - 1) / q * q;
   ct = std::max(ct, ct_min);
-  ct = std::min(ct, std::max(K, (n_cols + K - 1) / K * K));
-  if (ct_force > 0) ct = std::max(K, ct_force / K * K);
-  const int ts = packed ? ct : ((ct + cpw - 1) / cpw) * 32;
-  const int nts[4] = {1024, 768, 512, 256};
-  for (int nt : nts) {
+  ct = std::min(ct, std::max(q, (n_cols + q - 1) / q * q));
+  if (ct_force > 0) ct = std::max(q, ct_force / q * q);
+  const int ts = packed ? ct / cpt : ((ct + cpw - 1) / cpw) * 32;  // threads per slot
+  const int nts1[4] = {1024, 768, 512, 256}, nts2[4] = {512, 256, 0, 0};
+  for (int nt : (cpt == 2 ? nts2 : nts1)) {
+    if (nt == 0) continue;
     if (nt_force > 0 && nt != nt_force) continue;
     if (ts > nt - 32 * n_copy_warps) continue;  // the last warps only issue copies
     int wn = std::min(std::min((nt - 32 * n_copy_warps) / ts, std::max(1, n_tips - 1)), 64);
     for (; wn >= 1; --wn) {
       g = WalkGeometry();
-      g.nt = nt; g.ct = ct; g.ts = ts; g.cpw = cpw; g.wn = wn; g.elem = elem; g.K = K;
+      g.nt = nt; g.ct = ct; g.ts = ts; g.cpw = cpw; g.wn = wn; g.elem = elem; g.K = K; g.cpt = cpt;
       g.depth = std::max(1, std::min(depth, 3)); g.stages = g.depth + 1; g.n_copy_warps = n_copy_warps;
       const int n_pool = layout_walk(g, smem_max);
-      // enough blocks for one full round of operands in flight per stage plus two rounds of results
+      // enough blocks for one full round of operands in flight per stage plus the round's results
       if (n_pool >= std::max(3 * g.stages + 4, 4 * wn)) break;
     }
     if (wn < 1) continue;
@@ -118,6 +129,13 @@ inline bool plan_geometry(int n_tips, int n_cols, int K, int elem, int n_sms, si
     return true;
   }
   return false;
+}
+inline bool plan_geometry(int n_tips, int n_cols, int K, int elem, int n_sms, size_t smem_max, int nt_force,
+                          int ct_force, int depth, int n_copy_warps, int cpt_want, WalkGeometry& g) {
+  if (cpt_want == 2 &&
+      plan_geometry_cpt(n_tips, n_cols, K, elem, n_sms, smem_max, nt_force, ct_force, depth, n_copy_warps, 2, g))
+    return true;
+  return plan_geometry_cpt(n_tips, n_cols, K, elem, n_sms, smem_max, nt_force, ct_force, depth, n_copy_warps, 1, g);
 }
 
 struct WalkPlan {
@@ -451,11 +469,11 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
     out.tip_row_off[f + 1] = out.tip_row_off[f] + rows;
     if (rows)
       loads[f].push_back({JK_TIPS, (uint32_t)out.tip_row_off[f] * (uint32_t)g.ct_pad,
-                          (uint32_t)(g.off_tips + st * g.tips_bytes), (uint32_t)(rows * g.ct_pad)});
+                          (uint32_t)(g.off_tips + st * g.frame_bytes), (uint32_t)(rows * g.ct_pad)});
     if (!tasks[f].empty())
-      loads[f].push_back({JK_MATS, (uint32_t)f * (uint32_t)g.mats_bytes, (uint32_t)(g.off_mats + st * g.mats_bytes),
+      loads[f].push_back({JK_MATS, (uint32_t)f * (uint32_t)g.mats_bytes, (uint32_t)(g.off_mats + st * g.frame_bytes),
                           (uint32_t)((int)tasks[f].size() * 3 * K * g.mat_stride)});
-    loads[f].push_back({JK_REC, (uint32_t)f * (uint32_t)g.cr_bytes, (uint32_t)(g.off_cr + st * g.cr_bytes), (uint32_t)g.cr_bytes});
+    loads[f].push_back({JK_REC, (uint32_t)f * (uint32_t)g.cr_bytes, (uint32_t)(g.off_cr + st * g.frame_bytes), (uint32_t)g.cr_bytes});
   }
   // issue records: IR[q] = loads of round q + D, stores of round q - 1
   std::vector<uint32_t> ir_len(R, 16);
@@ -470,7 +488,7 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
   for (int f = 0; f < std::min(D, R); ++f) n_boot += loads[f].size() + 1;
   out.records.assign((size_t)out.boot_base + n_boot * 16, 0);
   auto ir_job = [&](int f) {
-    return WalkJob{out.ir_base + (uint32_t)f * (uint32_t)g.ir_bytes, (uint32_t)(g.off_ir + (f % S) * g.ir_bytes), ir_len[f], JK_REC};
+    return WalkJob{out.ir_base + (uint32_t)f * (uint32_t)g.ir_bytes, (uint32_t)(g.off_ir + (f % S) * g.frame_bytes), ir_len[f], JK_REC};
   };
   auto job_of = [&](const LoadRec& l) { return WalkJob{l.goff, l.soff, l.bytes, l.kind}; };
   for (int q = 0; q < R; ++q) {

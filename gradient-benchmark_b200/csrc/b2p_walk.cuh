@@ -4,11 +4,12 @@
 // One persistent CTA owns a tile of ct adjacent columns (column = pattern x category) and
 // walks the WHOLE tree for it, so every dependency is CTA-local: no grid sync, no flags.
 // Per round the CTA runs up to wn independent node tasks side by side; thread t works on
-// (slot t / ts, column t % ts) — slots are packed at thread granularity so an awkward tile
-// width (68 columns at 1000 taxa x 10k patterns on 148 SMs) still fills the lanes.
+// slot t / ts and on column t % ts of the tile (with two columns per thread: t % ts and
+// ts + t % ts) — slots are packed at thread granularity so an awkward tile width (68
+// columns at 1000 taxa x 10k patterns on 148 SMs) still fills the lanes.
 //
-// Data movement is entirely asynchronous and issued by ONE warp (the last one, which holds
-// no compute threads) from lists the host
+// Data movement is entirely asynchronous and issued by the copy warps (the last warps of
+// the CTA, which hold no compute threads) from lists the host
 // planner wrote (b2p_plan.h): every operand block, tip row, matrix bundle and descriptor
 // record of round q + depth is a cp.async.bulk (TMA, UBLKCP in SASS) global -> shared copy
 // that completes on the mbarrier of that round; every result block is written to shared
@@ -24,7 +25,10 @@
 // A tip child's message is a column of P picked by its state mask (stored transposed, so
 // the column is one 32-byte read); ambiguity masks sum the compatible columns.
 // Gradient sums over a slot's columns go through shared memory and are folded one round
-// later by one warp per slot (fixed order: deterministic).
+// later by the copy warps (fixed order: deterministic).
+// All shared-memory traffic uses 32-bit shared addresses (ld/st.shared), and everything a
+// round needs besides operand blocks sits in one per-stage FRAME, so the per-round address
+// arithmetic of a thread is one add per pointer.
 #pragma once
 #include "b2p_device.cuh"
 #include "b2p_walk_types.h"
@@ -36,10 +40,11 @@ constexpr int kMaxCatW = 32;
 template <typename T>
 struct WalkParams {
   int n_tiles, rounds_run, n_branches, n_cat;
-  int n_cols, n_patterns, n_copy_warps, pad_;
-  int ct, ts, cpw, wn, stages, depth;
-  int blk, plane, ct_pad, mat_stride, mats_bytes, cr_bytes, ir_bytes, tips_bytes;
-  int off_bar, off_cr, off_ir, off_mats, off_tips, off_gbuf, off_gids, off_scount;
+  int n_cols, n_patterns, n_copy_warps, wn;
+  int ct, ts, cpw, stages, depth;
+  int blk, plane, ct_pad, mat_stride;
+  int frame_bytes, off_frame, rel_cr, rel_mats, rel_tips;  // rel_ir == 0
+  int off_bar, off_gbuf, off_gids, off_scount;
   unsigned ir_base, boot_base;
   unsigned boot_n[4], boot_tx[4];
   unsigned long long tile_stride_part;  // (N-1) * blk
@@ -52,7 +57,7 @@ struct WalkParams {
   const double* weights;      // [P]
   double* lpart;              // [grid]
   double* gpart;              // [grid][2N-2]
-  long long* trace;           // debug: [2][rounds][5] clock stamps of CTA 0 (warp 0 / last warp), or null
+  long long* trace;           // debug build (-DB2P_TRACE_CLOCKS): [2][rounds][5] clock stamps of CTA 0
   T q[16];
   double freqs[4];
   double cat_w[kMaxCatW];
@@ -90,31 +95,66 @@ __device__ __forceinline__ void bulk_store(void* dst, unsigned src, unsigned byt
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-// ---- one column (4 states) in shared memory ---------------------------------------------
-// fp64: two 16-byte halves in separate planes (consecutive threads -> consecutive 16 B =>
-// conflict-free LDS.128 / STS.128); fp32: one 16 B unit.
-__device__ __forceinline__ void s_ld(const unsigned char* p, int plane, double (&x)[4]) {
-  const double2 a = *reinterpret_cast<const double2*>(p);
-  const double2 b = *reinterpret_cast<const double2*>(p + plane);
-  x[0] = a.x; x[1] = a.y; x[2] = b.x; x[3] = b.y;
+// ---- shared memory through 32-bit shared addresses ---------------------------------------
+__device__ __forceinline__ uint4 lds_u4(unsigned a) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+  return v;
 }
-__device__ __forceinline__ void s_ld(const unsigned char* p, int, float (&x)[4]) {
-  const float4 a = *reinterpret_cast<const float4*>(p);
-  x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w;
+__device__ __forceinline__ unsigned lds_u32(unsigned a) {
+  unsigned v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
 }
-__device__ __forceinline__ void s_st(unsigned char* p, int plane, const double (&x)[4]) {
-  *reinterpret_cast<double2*>(p) = make_double2(x[0], x[1]);
-  *reinterpret_cast<double2*>(p + plane) = make_double2(x[2], x[3]);
+__device__ __forceinline__ unsigned lds_u8(unsigned a) {
+  unsigned v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
 }
-__device__ __forceinline__ void s_st(unsigned char* p, int, const float (&x)[4]) {
-  *reinterpret_cast<float4*>(p) = make_float4(x[0], x[1], x[2], x[3]);
+__device__ __forceinline__ int2 lds_i2(unsigned a) {
+  int2 v;
+  asm volatile("ld.shared.v2.s32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts_i2(unsigned a, int2 v) {
+  asm volatile("st.shared.v2.s32 [%0], {%1,%2};" ::"r"(a), "r"(v.x), "r"(v.y) : "memory");
+}
+__device__ __forceinline__ double2 lds_d2(unsigned a) {
+  double2 v;
+  asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts_d2(unsigned a, double x, double y) {
+  asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(a), "d"(x), "d"(y) : "memory");
+}
+// 4 consecutive values (a matrix row, or the transposed matrix's row = a column of P)
+__device__ __forceinline__ void lds_row(unsigned a, double (&r)[4]) {
+  const double2 x = lds_d2(a), y = lds_d2(a + 16);
+  r[0] = x.x; r[1] = x.y; r[2] = y.x; r[3] = y.y;
+}
+__device__ __forceinline__ void lds_row(unsigned a, float (&r)[4]) {
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]) : "r"(a));
+}
+// one column (4 states) of a block.  fp64: two 16-byte halves in separate planes (consecutive
+// threads -> consecutive 16 B => conflict-free LDS.128 / STS.128); fp32: one 16 B unit.
+__device__ __forceinline__ void lds_col(unsigned a, unsigned plane, double (&x)[4]) {
+  const double2 u = lds_d2(a), v = lds_d2(a + plane);
+  x[0] = u.x; x[1] = u.y; x[2] = v.x; x[3] = v.y;
+}
+__device__ __forceinline__ void lds_col(unsigned a, unsigned, float (&x)[4]) { lds_row(a, x); }
+__device__ __forceinline__ void sts_col(unsigned a, unsigned plane, const double (&x)[4]) {
+  sts_d2(a, x[0], x[1]);
+  sts_d2(a + plane, x[2], x[3]);
+}
+__device__ __forceinline__ void sts_col(unsigned a, unsigned, const float (&x)[4]) {
+  asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(x[0]), "f"(x[1]), "f"(x[2]), "f"(x[3]) : "memory");
 }
 
-// Message of a tip child from the transposed matrix mt (mt[4*j + i] = P[i][j]).
+// Message of a tip child from the transposed matrix at mt (mt[4*j + i] = P[i][j]).
 template <typename T>
-__device__ __forceinline__ void tip_message(const T* mt, unsigned mask, T (&y)[4]) {
+__device__ __forceinline__ void tip_message(unsigned mt, unsigned mask, T (&y)[4]) {
   if (__popc(mask) == 1) {
-    load_row(mt + 4 * (__ffs(mask) - 1), y);
+    lds_row(mt + (__ffs(mask) - 1) * 4 * (unsigned)sizeof(T), y);
   } else {
 #pragma unroll
     for (int i = 0; i < 4; ++i) y[i] = (T)0;
@@ -122,34 +162,10 @@ __device__ __forceinline__ void tip_message(const T* mt, unsigned mask, T (&y)[4
     for (int j = 0; j < 4; ++j)
       if ((mask >> j) & 1u) {
         T r[4];
-        load_row(mt + 4 * j, r);
+        lds_row(mt + j * 4 * (unsigned)sizeof(T), r);
 #pragma unroll
         for (int i = 0; i < 4; ++i) y[i] += r[i];
       }
-  }
-}
-
-// y = M x, rows of M read as 16-byte units
-template <typename T>
-__device__ __forceinline__ void matvec_rows(const T* m, const T (&x)[4], T (&y)[4]) {
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    T r[4];
-    load_row(m + 4 * i, r);
-    y[i] = r[0] * x[0] + r[1] * x[1] + r[2] * x[2] + r[3] * x[3];
-  }
-}
-// y = M^T x
-template <typename T>
-__device__ __forceinline__ void matvec_t_rows(const T* m, const T (&x)[4], T (&y)[4]) {
-#pragma unroll
-  for (int j = 0; j < 4; ++j) y[j] = (T)0;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    T r[4];
-    load_row(m + 4 * i, r);
-#pragma unroll
-    for (int j = 0; j < 4; ++j) y[j] += r[j] * x[i];
   }
 }
 
@@ -179,26 +195,251 @@ __device__ __forceinline__ int rescale(int lane, int kk, float (&y)[4]) {
   return 0;
 }
 
-template <typename T, int K, int NT>
+// Per-thread constants (all shared-memory addresses are 32-bit).
+template <int CPT>
+struct WalkThread {
+  unsigned sc16;   // shared base + 16 * column: block offsets (descriptor * 16) are added to this
+  unsigned dB;     // 16 * ts: the thread's second column inside a block (CPT == 2)
+  unsigned plane;  // fp64: bytes between the two halves of a column
+  unsigned o_mat;  // frame-relative: matrix 0 of this thread's (slot, category)
+  unsigned mk;     // bytes between a slot's matrices 0, 1, 2 (K * mat_stride)
+  unsigned o_tip;  // frame-relative: this thread's column in tip row 0
+  unsigned ct_pad, ts;
+  int lane, kk, k;
+  double w[CPT];   // pattern weights of the thread's columns (0 for padding columns)
+};
+
+struct TaskDesc {
+  unsigned src_l, src_r, src_v, dst0, dst1, flags, tip_l, tip_r;
+};
+__device__ __forceinline__ TaskDesc unpack_desc(const uint4 dw) {
+  TaskDesc d;
+  d.src_l = dw.x & 0xffffu; d.src_r = dw.x >> 16;
+  d.src_v = dw.y & 0xffffu; d.dst0 = dw.y >> 16;
+  d.dst1 = dw.z & 0xffffu; d.flags = dw.z >> 16;
+  d.tip_l = dw.w & 0xffffu; d.tip_r = dw.w >> 16;
+  return d;
+}
+
+// Children's messages of the task -> registers (zeros for idle lanes).
+template <typename T, int CPT>
+__device__ __forceinline__ void load_messages(const WalkThread<CPT>& th, unsigned frame, const TaskDesc& d, bool live,
+                                              T (&ma)[CPT][4], T (&mb)[CPT][4]) {
+#pragma unroll
+  for (int c = 0; c < CPT; ++c) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) ma[c][i] = mb[c][i] = (T)0;
+    if (!live) continue;
+    if (d.flags & WF_TIP_L) tip_message(frame + th.o_mat + th.mk, lds_u8(frame + th.o_tip + d.tip_l * th.ct_pad + c * th.ts), ma[c]);
+    else lds_col(th.sc16 + d.src_l * 16 + c * th.dB, th.plane, ma[c]);
+    if (d.flags & WF_TIP_R) tip_message(frame + th.o_mat + 2 * th.mk, lds_u8(frame + th.o_tip + d.tip_r * th.ct_pad + c * th.ts), mb[c]);
+    else lds_col(th.sc16 + d.src_r * 16 + c * th.dB, th.plane, mb[c]);
+  }
+}
+
+// ------------------------------------------------------------------ post-order task
+//   x_v = m_l o m_r (rescaled when tiny) ;  m_v = P_v x_v ; root: site likelihoods -> log-likelihood term
+template <typename T, int K, int CPT>
+__device__ __forceinline__ void post_task(const WalkParams<T>& p, const WalkThread<CPT>& th, unsigned frame, const TaskDesc& d,
+                                          bool live, int* scount, int col, unsigned gslot) {
+  T ma[CPT][4], mb[CPT][4];
+  load_messages<T, CPT>(th, frame, d, live, ma, mb);
+  int bumped[CPT];
+#pragma unroll
+  for (int c = 0; c < CPT; ++c) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) ma[c][i] *= mb[c][i];
+    bumped[c] = rescale<K>(th.lane, th.kk, ma[c]);
+  }
+  const bool is_root = (d.flags & WF_ROOT) != 0;
+  if (live && !is_root) {
+    T mv[CPT][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      T r[4];
+      lds_row(frame + th.o_mat + i * 4 * (unsigned)sizeof(T), r);
+#pragma unroll
+      for (int c = 0; c < CPT; ++c)
+        mv[c][i] = r[0] * ma[c][0] + r[1] * ma[c][1] + r[2] * ma[c][2] + r[3] * ma[c][3];
+    }
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) {
+      if (bumped[c] && th.k == 0) atomicAdd(scount + col + c * th.ts, 1);
+      sts_col(th.sc16 + d.dst0 * 16 + c * th.dB, th.plane, mv[c]);
+    }
+  }
+  if (K != 1 || is_root) {
+    double term = 0.0;
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) {
+      T site = (T)p.freqs[0] * ma[c][0] + (T)p.freqs[1] * ma[c][1] + (T)p.freqs[2] * ma[c][2] + (T)p.freqs[3] * ma[c][3];
+      site = group_sum<K>(site * (T)p.cat_w[th.k], th.lane, th.kk);
+      if (live && is_root && th.k == 0)
+        term += th.w[c] * (log((double)site) - (double)(scount[col + c * th.ts] + bumped[c]) * Scale<T>::log_factor());
+    }
+    if (live && is_root) sts_d2(gslot, term, 0.0);
+  }
+}
+
+// ------------------------------------------------------------------- pre-order task
+//   q_l = u_v o m_r, q_r = u_v o m_l ; L = q_l . m_l ; dL/dt_l = r_k q_l.(Q m_l) ; u_l = P_l^T q_l (same for r)
+template <typename T, int K, int CPT>
+__device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThread<CPT>& th, unsigned frame, const TaskDesc& d,
+                                         bool live, unsigned gslot) {
+  T ma[CPT][4], mb[CPT][4];
+  load_messages<T, CPT>(th, frame, d, live, ma, mb);
+  T ql[CPT][4], qr[CPT][4];
+  double gl = 0.0, gr = 0.0;
+#pragma unroll
+  for (int c = 0; c < CPT; ++c) {
+    T u[4];
+    if (live && d.src_v != kNoBlk) lds_col(th.sc16 + d.src_v * 16 + c * th.dB, th.plane, u);
+    else {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) u[i] = live ? (T)p.freqs[i] : (T)0;
+    }
+    T den = (T)0, numl = (T)0, numr = (T)0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      ql[c][i] = u[i] * mb[c][i];
+      qr[c][i] = u[i] * ma[c][i];
+      den += ql[c][i] * ma[c][i];
+    }
+    // d/dt (P x) = r Q (P x): Q comes from the constant bank
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const T dl = p.q[4 * i] * ma[c][0] + p.q[4 * i + 1] * ma[c][1] + p.q[4 * i + 2] * ma[c][2] + p.q[4 * i + 3] * ma[c][3];
+      const T dr = p.q[4 * i] * mb[c][0] + p.q[4 * i + 1] * mb[c][1] + p.q[4 * i + 2] * mb[c][2] + p.q[4 * i + 3] * mb[c][3];
+      numl += ql[c][i] * dl;
+      numr += qr[c][i] * dr;
+    }
+    if (K != 1) {
+      const T cw = (T)p.cat_w[th.k], cwr = (T)(p.cat_w[th.k] * p.rates[th.k]);
+      den = group_sum<K>(den * cw, th.lane, th.kk);
+      numl = group_sum<K>(numl * cwr, th.lane, th.kk);
+      numr = group_sum<K>(numr * cwr, th.lane, th.kk);
+    }
+    if (live && th.k == 0) {
+      // K == 1: the single category's weight cancels, its rate multiplies the numerators
+      const double inv = (K == 1 ? th.w[c] * p.rates[0] : th.w[c]) / (double)den;
+      gl += (double)numl * inv;
+      gr += (double)numr * inv;
+    }
+  }
+  if (live) sts_d2(gslot, gl, gr);
+  // pre-order partials of the internal children: u_c = P_c^T q_c  (ma / mb are dead)
+  const bool want_l = live && (d.flags & WF_OUT_L), want_r = live && (d.flags & WF_OUT_R);
+  if (K != 1 || want_l) {
+#pragma unroll
+    for (int c = 0; c < CPT; ++c)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) ma[c][j] = (T)0;
+    if (want_l) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        T r[4];
+        lds_row(frame + th.o_mat + th.mk + i * 4 * (unsigned)sizeof(T), r);
+#pragma unroll
+        for (int c = 0; c < CPT; ++c)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) ma[c][j] += r[j] * ql[c][i];
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) {
+      (void)rescale<K>(th.lane, th.kk, ma[c]);
+      if (want_l) sts_col(th.sc16 + d.dst0 * 16 + c * th.dB, th.plane, ma[c]);
+    }
+  }
+  if (K != 1 || want_r) {
+#pragma unroll
+    for (int c = 0; c < CPT; ++c)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) mb[c][j] = (T)0;
+    if (want_r) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        T r[4];
+        lds_row(frame + th.o_mat + 2 * th.mk + i * 4 * (unsigned)sizeof(T), r);
+#pragma unroll
+        for (int c = 0; c < CPT; ++c)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) mb[c][j] += r[j] * qr[c][i];
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) {
+      (void)rescale<K>(th.lane, th.kk, mb[c]);
+      if (want_r) sts_col(th.sc16 + d.dst1 * 16 + c * th.dB, th.plane, mb[c]);
+    }
+  }
+}
+
+// Fold one round's per-thread sums (done by the copy warps one round later): slot s2's ts
+// pairs -> (a, b), added to the branch gradients / the log-likelihood in a fixed order.
+// A warp folds four slots at a time, eight lanes each.
+template <typename T>
+__device__ __forceinline__ void fold_round(const WalkParams<T>& p, unsigned sbase, int par, int pw, int lane, bool first_tile,
+                                           double& ll_acc) {
+  const unsigned gids = sbase + p.off_gids + par * p.wn * 8;
+  const unsigned gbuf = sbase + p.off_gbuf + par * p.wn * p.ts * 16;
+  const int li = lane & 7;
+  for (int s0 = pw * 4; s0 < p.wn; s0 += p.n_copy_warps * 4) {
+    const int s2 = s0 + (lane >> 3);
+    int2 ids = make_int2(-1, -1);
+    if (s2 < p.wn) ids = lds_i2(gids + s2 * 8);
+    double a = 0.0, b = 0.0;
+    if (ids.x != -1) {
+      for (int c = li; c < p.ts; c += 8) {
+        // lanes of a slot that hold no column (K does not divide 32) never wrote their pair
+        if ((c & 31) >= p.cpw || (c >> 5) * p.cpw + (c & 31) >= p.ct) continue;
+        const double2 v = lds_d2(gbuf + (s2 * p.ts + c) * 16);
+        a += v.x; b += v.y;
+      }
+    }
+    const double oa = __shfl_xor_sync(0xffffffffu, a, 4), ob = __shfl_xor_sync(0xffffffffu, b, 4);
+    double v = (li & 4) ? (b + ob) : (a + oa);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    if ((li & 3) == 0) {
+      const int id = li ? ids.y : ids.x;
+      if (id == -2) ll_acc += v;
+      else if (id >= 0) {
+        double* gp = p.gpart + (size_t)blockIdx.x * p.n_branches + id;
+        *gp = first_tile ? v : *gp + v;
+      }
+    }
+  }
+}
+
+template <typename T, int K, int NT, int CPT>
 __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ WalkParams<T> p) {
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ double red[NT / 32];
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int kk = K > 0 ? K : p.n_cat;
+  const int first_copy_warp = NT / 32 - p.n_copy_warps;
+  const bool copier = warp >= first_copy_warp;
   const int s = t / p.ts;
   const int tt = t - s * p.ts;
-  int col = (tt >> 5) * p.cpw + (tt & 31);
-  const bool in_slot = s < p.wn && (tt & 31) < p.cpw && col < p.ct;
+  int col = CPT == 2 ? tt : (tt >> 5) * p.cpw + (tt & 31);
+  const bool in_slot = s < p.wn && (CPT == 2 || ((tt & 31) < p.cpw && col < p.ct));
   if (!in_slot) col = 0;
-  const int k = col % kk;
-  const int c16 = col * 16;
-  const int plane = p.plane;
   const int S = p.stages, D = p.depth, R = p.rounds_run;
   const unsigned sbase = smem_u32(smem);
   const unsigned bar0 = sbase + p.off_bar;
   int* scount = reinterpret_cast<int*>(smem + p.off_scount);
-  const T cw = (T)p.cat_w[k];
-  const T cwr = (T)(p.cat_w[k] * p.rates[k]);
+
+  WalkThread<CPT> th;
+  th.lane = lane; th.kk = kk; th.k = col % kk;
+  th.sc16 = sbase + col * 16; th.dB = p.ts * 16; th.plane = p.plane;
+  th.mk = kk * p.mat_stride;
+  th.o_mat = p.rel_mats + ((in_slot ? s : 0) * 3 * kk + th.k) * p.mat_stride;
+  th.o_tip = p.rel_tips + col;
+  th.ct_pad = p.ct_pad; th.ts = p.ts;
+  const unsigned o_desc = p.rel_cr + (in_slot ? s : 0) * 16;
+  const unsigned o_ids = p.rel_cr + p.wn * 16 + (in_slot ? s : 0) * 8;
+  const unsigned o_gslot = p.off_gbuf + ((in_slot ? s : 0) * p.ts + tt) * 16;
 
   if (t == 0) {
     for (int j = 0; j < S; ++j) mbar_init(bar0 + 8 * j, 1);
@@ -210,12 +451,15 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
   bool first_tile = true;
 
   for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, first_tile = false) {
-    const int cg = tile * p.ct + col;
-    const double w_p = (in_slot && cg < p.n_cols) ? __ldg(p.weights + cg / kk) : 0.0;
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) {
+      const int cg = tile * p.ct + col + c * p.ts;
+      th.w[c] = (in_slot && cg < p.n_cols) ? __ldg(p.weights + cg / kk) : 0.0;
+    }
     for (int i = t; i < p.ct; i += NT) scount[i] = 0;
     __syncthreads();
-    const unsigned char* base_msg = p.msg + (unsigned long long)tile * p.tile_stride_part;
-    const unsigned char* base_pre = p.pre + (unsigned long long)tile * p.tile_stride_part;
+    unsigned char* base_msg = p.msg + (unsigned long long)tile * p.tile_stride_part;
+    unsigned char* base_pre = p.pre + (unsigned long long)tile * p.tile_stride_part;
     const unsigned char* base_tips = p.tips + (unsigned long long)tile * p.tile_stride_tips;
     auto gptr = [&](unsigned kind, unsigned goff) -> const unsigned char* {
       const unsigned char* b = kind == JK_MSG ? base_msg : kind == JK_PRE ? base_pre : kind == JK_TIPS ? base_tips
@@ -237,208 +481,85 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
       }
     }
 
-    int st = 0;  // stage of the current round: q % S
+    int st = 0;                                // stage of the current round: q % S
+    unsigned frame = sbase + p.off_frame;      // its frame
     for (int q = 0; q < R; ++q) {
       const int par = q & 1;
+#ifdef B2P_TRACE_CLOCKS
       const bool tr = p.trace && blockIdx.x == 0 && (t == 0 || t == NT - 32) && tile == 0;
       long long* trow = tr ? p.trace + ((t ? 1 : 0) * (long long)R + q) * 5 : nullptr;
       if (tr) trow[0] = clock64();
+#endif
       mbar_wait(bar0 + 8 * st, (phase_bits >> st) & 1u);
-      if (tr) trow[1] = clock64();
       phase_bits ^= 1u << st;
-      const unsigned char* ir = smem + p.off_ir + st * p.ir_bytes;
-      const uint4 hdr = *reinterpret_cast<const uint4*>(ir);
-      if (warp >= NT / 32 - p.n_copy_warps) {
-        // Copy warps (the last warps hold no compute threads): stores of round q-1's results
-        // first — the end of this round waits until they have read shared memory — then the
-        // loads of round q + depth.  Issuing them from warps of their own lets the copies
-        // overlap the arithmetic; one warp issues a bulk copy every ~100 cycles, so several
-        // share the list (job j belongs to copy warp j % n_copy_warps).
-        const int st_next = st == 0 ? S - 1 : st - 1;  // (q + D) % S with S = D + 1
+#ifdef B2P_TRACE_CLOCKS
+      if (tr) trow[1] = clock64();
+#endif
+      if (copier) {
+        // Copy warps: stores of round q-1's results first — the end of this round waits until
+        // they have read shared memory — then the loads of round q + depth.  Issuing them from
+        // warps of their own lets the copies overlap the arithmetic; one warp issues a bulk copy
+        // every ~100 cycles, so several share the list (job j belongs to copy warp j % n).
+        const uint4 hdr = lds_u4(frame);
+        const unsigned st_next = st == 0 ? S - 1 : st - 1;  // (q + D) % S with S = D + 1
         const unsigned bar = bar0 + 8 * st_next;
         const unsigned n_loads = (q + D < R) ? hdr.x : 0u;
-        const uint4* jobs = reinterpret_cast<const uint4*>(ir + 16);
-        const unsigned np = p.n_copy_warps, pw = warp - (NT / 32 - np);
+        const unsigned jobs = frame + 16;
+        const unsigned np = p.n_copy_warps, pw = warp - first_copy_warp;
         if (pw == 0 && lane == 0 && n_loads) mbar_expect_tx(bar, hdr.z);
         for (unsigned j = pw + np * lane; j < hdr.y; j += 32 * np) {
-          const uint4 jb = jobs[hdr.x + j];
+          const uint4 jb = lds_u4(jobs + (hdr.x + j) * 16);
           bulk_store(const_cast<unsigned char*>(gptr(jb.w, jb.x)), sbase + jb.y, jb.z);
         }
         bulk_commit();  // one (possibly empty) group per lane per round
         for (unsigned j = pw + np * lane; j < n_loads; j += 32 * np) {
-          const uint4 jb = jobs[j];
+          const uint4 jb = lds_u4(jobs + j * 16);
           bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar);
         }
-      }
-      if (tr) trow[2] = clock64();
-      // ---- this thread's task
-      unsigned tip_l = 0, tip_r = 0;
-      unsigned flags = 0, src_l = kNoBlk, src_r = kNoBlk, src_v = kNoBlk, dst0 = kNoBlk, dst1 = kNoBlk;
-      const unsigned char* cr = smem + p.off_cr + st * p.cr_bytes;
-      if (in_slot) {
-        const uint4 dw = *reinterpret_cast<const uint4*>(cr + s * 16);
-        tip_l = dw.w & 0xffffu; tip_r = dw.w >> 16;
-        src_l = dw.x & 0xffffu; src_r = dw.x >> 16;
-        src_v = dw.y & 0xffffu; dst0 = dw.y >> 16;
-        dst1 = dw.z & 0xffffu; flags = dw.z >> 16;
-        if (col == 0) {
-          int2 ids = *reinterpret_cast<const int2*>(cr + p.wn * 16 + s * 8);
-          if (!(flags & WF_LIVE)) ids = make_int2(-1, -1);
-          reinterpret_cast<int2*>(smem + p.off_gids)[par * p.wn + s] = ids;
-        }
-      }
-      const bool live = (flags & WF_LIVE) != 0;
-      if (K != 1 || live) {  // K == 1: no warp-collective inside a task, idle lanes skip it
-        const unsigned char* mslot = smem + p.off_mats + st * p.mats_bytes + (s * 3 * kk + k) * p.mat_stride;
-        const T* m0 = reinterpret_cast<const T*>(mslot);
-        const T* m1 = reinterpret_cast<const T*>(mslot + kk * p.mat_stride);
-        const T* m2 = reinterpret_cast<const T*>(mslot + 2 * kk * p.mat_stride);
-        const unsigned char* tiprow = smem + p.off_tips + st * p.tips_bytes + col;
-        T ma[4], mb[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) ma[i] = mb[i] = (T)0;
-        if (live) {
-          if (flags & WF_TIP_L) tip_message(m1, tiprow[tip_l * p.ct_pad], ma);
-          else s_ld(smem + src_l * 16 + c16, plane, ma);
-          if (flags & WF_TIP_R) tip_message(m2, tiprow[tip_r * p.ct_pad], mb);
-          else s_ld(smem + src_r * 16 + c16, plane, mb);
-        }
-        double2* gslot = reinterpret_cast<double2*>(smem + p.off_gbuf) + (par * p.wn + s) * p.ct + col;
-        if (hdr.w == 0) {
-          // ------------------------------------------------------------ post-order task
-          T y[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) y[i] = ma[i] * mb[i];
-          const int bumped = rescale<K>(lane, kk, y);
-          const bool is_root = (flags & WF_ROOT) != 0;
-          if (live && !is_root) {
-            if (bumped && k == 0) atomicAdd(scount + col, 1);
-            T mv[4];
-            matvec_rows(m0, y, mv);
-            s_st(smem + dst0 * 16 + c16, plane, mv);
-          }
-          if (K != 1 || is_root) {
-            T site = (T)p.freqs[0] * y[0] + (T)p.freqs[1] * y[1] + (T)p.freqs[2] * y[2] + (T)p.freqs[3] * y[3];
-            site = group_sum<K>(site * cw, lane, kk);
-            if (live && is_root) {
-              double term = 0.0;
-              if (k == 0) term = w_p * (log((double)site) - (double)(scount[col] + bumped) * Scale<T>::log_factor());
-              *gslot = make_double2(term, 0.0);
-            }
-          }
-        } else {
-          // ------------------------------------------------------------- pre-order task
-          T u[4];
-          if (live && src_v != kNoBlk) s_ld(smem + src_v * 16 + c16, plane, u);
-          else {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) u[i] = live ? (T)p.freqs[i] : (T)0;
-          }
-          T ql[4], qr[4];
-          T den = (T)0, numl = (T)0, numr = (T)0;
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            ql[i] = u[i] * mb[i];
-            qr[i] = u[i] * ma[i];
-            den += ql[i] * ma[i];
-          }
-          // d/dt (P x) = r Q (P x): Q comes from the constant bank
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const T dl = p.q[4 * i] * ma[0] + p.q[4 * i + 1] * ma[1] + p.q[4 * i + 2] * ma[2] + p.q[4 * i + 3] * ma[3];
-            const T dr = p.q[4 * i] * mb[0] + p.q[4 * i + 1] * mb[1] + p.q[4 * i + 2] * mb[2] + p.q[4 * i + 3] * mb[3];
-            numl += ql[i] * dl;
-            numr += qr[i] * dr;
-          }
-          if (K != 1) {
-            den = group_sum<K>(den * cw, lane, kk);
-            numl = group_sum<K>(numl * cwr, lane, kk);
-            numr = group_sum<K>(numr * cwr, lane, kk);
-          }
-          if (live) {
-            double gl = 0.0, gr = 0.0;
-            if (k == 0) {
-              // K == 1: the single category's weight cancels, its rate multiplies the numerators
-              const double inv = (K == 1 ? w_p * p.rates[0] : w_p) / (double)den;
-              gl = (double)numl * inv;
-              gr = (double)numr * inv;
-            }
-            *gslot = make_double2(gl, gr);
-          }
-          // pre-order partials of the internal children: u_c = P_c^T q_c  (ma / mb are dead)
-          const bool want_l = live && (flags & WF_OUT_L), want_r = live && (flags & WF_OUT_R);
-          if (K != 1 || want_l) {
-            if (want_l) matvec_t_rows(m1, ql, ma);
-            (void)rescale<K>(lane, kk, ma);
-            if (want_l) s_st(smem + dst0 * 16 + c16, plane, ma);
-          }
-          if (K != 1 || want_r) {
-            if (want_r) matvec_t_rows(m2, qr, mb);
-            (void)rescale<K>(lane, kk, mb);
-            if (want_r) s_st(smem + dst1 * 16 + c16, plane, mb);
-          }
-        }
-      }
-
-      // ---- fold the previous round's gradient / likelihood sums (one warp per slot)
-      if (q > 0) {
-        const int2* gids = reinterpret_cast<const int2*>(smem + p.off_gids) + (par ^ 1) * p.wn;
-        for (int s2 = warp; s2 < p.wn; s2 += NT / 32) {
-          const int2 ids = gids[s2];
-          if (ids.x == -1) continue;
-          const double2* gb = reinterpret_cast<const double2*>(smem + p.off_gbuf) + ((par ^ 1) * p.wn + s2) * p.ct;
-          double a = 0.0, b = 0.0;
-          for (int c = lane; c < p.ct; c += 32) { const double2 v = gb[c]; a += v.x; b += v.y; }
-          const double oa = __shfl_xor_sync(0xffffffffu, a, 16), ob = __shfl_xor_sync(0xffffffffu, b, 16);
-          double v = (lane & 16) ? (b + ob) : (a + oa);
-#pragma unroll
-          for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-          if ((lane & 15) == 0) {
-            const int id = lane ? ids.y : ids.x;
-            if (id == -2) ll_acc += v;
-            else if (id >= 0) {
-              double* gp = p.gpart + (size_t)blockIdx.x * p.n_branches + id;
-              *gp = first_tile ? v : *gp + v;
-            }
-          }
-        }
-      }
-
-      fence_async_smem();
-      if (warp >= NT / 32 - p.n_copy_warps) {
+#ifdef B2P_TRACE_CLOCKS
+        if (tr) trow[2] = clock64();
+#endif
+        if (q > 0) fold_round(p, sbase, par ^ 1, pw, lane, first_tile, ll_acc);
         asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         asm volatile("cp.async.bulk.wait_group 1;" ::: "memory");
-      }
-      if (tr) trow[3] = clock64();
-      __syncthreads();
-      if (tr) trow[4] = clock64();
-      st = st + 1 == S ? 0 : st + 1;
-    }
-    // fold the last round
-    {
-      const int par = (R - 1) & 1;
-      const int2* gids = reinterpret_cast<const int2*>(smem + p.off_gids) + par * p.wn;
-      for (int s2 = warp; s2 < p.wn; s2 += NT / 32) {
-        const int2 ids = gids[s2];
-        if (ids.x == -1) continue;
-        const double2* gb = reinterpret_cast<const double2*>(smem + p.off_gbuf) + (par * p.wn + s2) * p.ct;
-        double a = 0.0, b = 0.0;
-        for (int c = lane; c < p.ct; c += 32) { const double2 v = gb[c]; a += v.x; b += v.y; }
-        const double oa = __shfl_xor_sync(0xffffffffu, a, 16), ob = __shfl_xor_sync(0xffffffffu, b, 16);
-        double v = (lane & 16) ? (b + ob) : (a + oa);
-#pragma unroll
-        for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if ((lane & 15) == 0) {
-          const int id = lane ? ids.y : ids.x;
-          if (id == -2) ll_acc += v;
-          else if (id >= 0) {
-            double* gp = p.gpart + (size_t)blockIdx.x * p.n_branches + id;
-            *gp = first_tile ? v : *gp + v;
+      } else {
+        // ---- this thread's task
+        const unsigned pass = lds_u32(frame + 12);
+        TaskDesc d;
+        d.flags = 0;
+        if (in_slot) {
+          d = unpack_desc(lds_u4(frame + o_desc));
+          if (tt == 0) {  // what the fold of the next round does with this slot's sums
+            const bool sums = (d.flags & WF_LIVE) && (pass != 0 || (d.flags & WF_ROOT));
+            sts_i2(sbase + p.off_gids + (par * p.wn + s) * 8, sums ? lds_i2(frame + o_ids) : make_int2(-1, -1));
           }
         }
+        const bool live = (d.flags & WF_LIVE) != 0;
+#ifdef B2P_TRACE_CLOCKS
+        if (tr) trow[2] = clock64();
+#endif
+        if (K != 1 || live) {  // K == 1: no warp-collective inside a task, idle lanes skip it
+          const unsigned gslot = sbase + o_gslot + par * p.wn * p.ts * 16;
+          if (pass == 0) post_task<T, K, CPT>(p, th, frame, d, live, scount, col, gslot);
+          else pre_task<T, K, CPT>(p, th, frame, d, live, gslot);
+        }
       }
+      // shared-memory results of this round (generic proxy) before the bulk copies (async
+      // proxy) that read them or overwrite their blocks
+      fence_async_smem();
+#ifdef B2P_TRACE_CLOCKS
+      if (tr) trow[3] = clock64();
+#endif
+      __syncthreads();
+#ifdef B2P_TRACE_CLOCKS
+      if (tr) trow[4] = clock64();
+#endif
+      if (++st == S) { st = 0; frame = sbase + p.off_frame; } else frame += p.frame_bytes;
     }
-    if (warp >= NT / 32 - p.n_copy_warps) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if (copier) {
+      fold_round(p, sbase, (R - 1) & 1, warp - first_copy_warp, lane, first_tile, ll_acc);
+      asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    }
     __syncthreads();
   }
 

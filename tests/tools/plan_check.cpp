@@ -8,7 +8,7 @@
 //     the same round, that has a load in flight, or that a store is still reading;
 //   * a load reads HBM only after the store of that value has completed (>= 2 rounds);
 //   * every message is stored exactly once; transaction byte counts match the job lists.
-// usage: plan_check N shape seed ct K elem smem_bytes depth [nt]   -> prints "OK ..." or "FAIL ..."
+// usage: plan_check N shape seed ct K elem smem_bytes depth [nt [cpt]]   -> prints "OK ..." or "FAIL ..."
 #include <cstdio>
 #include <cstdlib>
 #include <map>
@@ -48,10 +48,10 @@ static std::vector<int32_t> random_triples(int N, int shape, unsigned seed) {
 int main(int argc, char** argv) {
   if (argc < 9) { printf("usage\n"); return 2; }
   const int N = atoi(argv[1]), shape = atoi(argv[2]), seed = atoi(argv[3]), ct = atoi(argv[4]), K = atoi(argv[5]),
-            elem = atoi(argv[6]), smem = atoi(argv[7]), depth = atoi(argv[8]), nt = argc > 9 ? atoi(argv[9]) : 0;
+            elem = atoi(argv[6]), smem = atoi(argv[7]), depth = atoi(argv[8]), nt = argc > 9 ? atoi(argv[9]) : 0, cpt = argc > 10 ? atoi(argv[10]) : 1;
   std::vector<int32_t> tr = random_triples(N, shape, seed);
   WalkGeometry g;
-  if (!plan_geometry(N, ct * 148, K, elem, 148, smem, nt, ct, 1, depth, 1, g)) FAIL("geometry");
+  if (!plan_geometry(N, ct * 148, K, elem, 148, smem, nt, ct, depth, 2, cpt, g)) FAIL("geometry");
   WalkPlan plan;
   std::string why;
   if (!plan_walk_auto(N, tr.data(), g, plan, why)) FAIL("plan: %s", why.c_str());
@@ -90,14 +90,14 @@ int main(int argc, char** argv) {
       tag[b] = 1 + vid; inflight_until[b] = f;
       ++n_loads;
     } else if (j.kind == JK_TIPS) {
-      if ((int)j.soff != g.off_tips + (f % S) * g.tips_bytes || (int)j.bytes > g.tips_bytes ||
+      if ((int)j.soff != g.off_tips + (f % S) * g.frame_bytes || (int)j.bytes > g.tips_bytes ||
           (int)j.goff != plan.tip_row_off[f] * g.ct_pad ||
           (int)j.bytes != (plan.tip_row_off[f + 1] - plan.tip_row_off[f]) * g.ct_pad) return "tips job";
     } else if (j.kind == JK_MATS) {
-      if ((int)j.soff != g.off_mats + (f % S) * g.mats_bytes || (int)j.bytes > g.mats_bytes || j.goff != (uint32_t)f * g.mats_bytes) return "mats job";
+      if ((int)j.soff != g.off_mats + (f % S) * g.frame_bytes || (int)j.bytes > g.mats_bytes || j.goff != (uint32_t)f * g.mats_bytes) return "mats job";
     } else if (j.kind == JK_REC) {
-      const bool is_cr = j.goff == (uint32_t)f * g.cr_bytes && (int)j.soff == g.off_cr + (f % S) * g.cr_bytes && (int)j.bytes == g.cr_bytes;
-      const bool is_ir = j.goff == plan.ir_base + (uint32_t)f * g.ir_bytes && (int)j.soff == g.off_ir + (f % S) * g.ir_bytes && (int)j.bytes <= g.ir_bytes;
+      const bool is_cr = j.goff == (uint32_t)f * g.cr_bytes && (int)j.soff == g.off_cr + (f % S) * g.frame_bytes && (int)j.bytes == g.cr_bytes;
+      const bool is_ir = j.goff == plan.ir_base + (uint32_t)f * g.ir_bytes && (int)j.soff == g.off_ir + (f % S) * g.frame_bytes && (int)j.bytes <= g.ir_bytes;
       if (!is_cr && !is_ir) return "record job";
     } else return "kind";
     return nullptr;
@@ -206,8 +206,8 @@ int main(int argc, char** argv) {
   }
   for (int v = N; v <= root; ++v) if (!done_post[v] || !done_pre[v]) FAIL("task %d missing", v);
   for (int v = N; v < root; ++v) if (!stored_at.count(v - N)) FAIL("message %d never stored", v);
-  printf("OK N=%d shape=%d ct=%d K=%d elem=%d depth=%d nt=%d wn=%d wn_eff=%d pool=%d rounds=%d+%d tasks=%lld resident_reads=%lld loads=%lld stores=%lld evictions=%lld max_jobs=%d/%d smem=%zu\n",
-         N, shape, g.ct, K, elem, D, g.nt, wn, plan.wn_eff, NB, Rpost, plan.rounds_pre, n_tasks, plan.resident_reads, n_loads, n_stores,
+  printf("OK N=%d shape=%d ct=%d cpt=%d K=%d elem=%d depth=%d nt=%d wn=%d wn_eff=%d pool=%d rounds=%d+%d tasks=%lld resident_reads=%lld loads=%lld stores=%lld evictions=%lld max_jobs=%d/%d smem=%zu\n",
+         N, shape, g.ct, g.cpt, K, elem, D, g.nt, wn, plan.wn_eff, NB, Rpost, plan.rounds_pre, n_tasks, plan.resident_reads, n_loads, n_stores,
          plan.evictions, plan.max_jobs_used, g.max_jobs, g.smem);
   return 0;
 }
