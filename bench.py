@@ -4,7 +4,7 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
 
 A *step* is one evaluation of log-likelihood + all 2N-2 branch-length derivatives over one
-rank's site patterns (K1 transition matrices -> traversal kernel -> reduce kernel), plus,
+rank's site patterns (K1 transition matrices -> walk kernel (both passes) -> reduce kernel), plus,
 for N>1, the single all-reduce of 2N-1 doubles that finishes a sharded evaluation.  The
 default workload is BASELINE.json configs[1]: JC69, 1000 taxa x 10k patterns, fp64.  With
 N>1 every rank holds its own 10k-pattern shard of one N*10k-pattern alignment on the same
@@ -57,6 +57,16 @@ def hbm_peak():
             return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
     except Exception:
         return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic(workload, precision):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the traversal kernel, per launch, from the
+    committed `ncu --set full` capture of this workload (profiles/ncu_traffic.json); None if absent."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as fh:
+            return float(json.load(fh)[f"{workload}:{precision}"]["dram_bytes"])
+    except Exception:
+        return None
 
 
 class ClockSampler:
@@ -273,13 +283,15 @@ def run_b200(a):
                        "l2": f"no flush: per-step working set {(2 * (w.n_tips - 1) * U) / 1e6:.0f} MB of partials > 126 MB L2",
                        "collective": "1 NCCL all-reduce of 2N-1 doubles per step" if world > 1 else "none",
                        "engine": {k: info[k] for k in ("warps_per_block", "cols_per_tile", "n_tiles", "grid_blocks",
-                                                        "blocks_per_sm", "post_rounds", "tree_depth", "regs_per_thread")}},
+                                                        "post_rounds", "pre_rounds", "tasks_per_round", "tree_depth",
+                                                        "regs_per_thread", "smem_bytes", "pool_blocks", "copy_depth",
+                                                        "resident_reads", "block_loads", "block_stores")}},
             "e2e": {"value": world * a.steps / dt_e2e, "unit": unit, "ms_per_step": dt_e2e / a.steps * 1e3,
                     "h2d_bytes_per_step": n_br * 8, "d2h_bytes_per_step": (n_br + 1) * 8,
                     "api": "TreeLikelihoodModel()(host tensor).backward() -> b2p_loglik_grad_host"},
             "gpu_launches": 3 * a.steps,
-            "roofline": {"bound": "hbm", "kernel": "traverse_kernel", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+            "roofline": {"bound": "hbm", "kernel": "walk_kernel", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(a.workload, a.precision),
                          "alg_bytes_per_launch": alg, "kernel_ms": k_avg_ms, "launches_timed": k_n,
                          "share_of_step": k_ms / (ms_total * k_n / a.steps) if k_n else None, "peak_source": peak_src},
             "clocks": clocks,

@@ -33,7 +33,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return _OUT
     nvcc = os.environ.get("NVCC", "nvcc")
-    cmd = [nvcc, *NVCC_FLAGS, "-o", _OUT, *[os.path.join(_CSRC, s) for s in _SOURCES]]
+    extra = os.environ.get("B2P_NVCC_EXTRA", "").split()  # e.g. -DB2P_TRACE_CLOCKS (debug build)
+    cmd = [nvcc, *NVCC_FLAGS, *extra, "-o", _OUT, *[os.path.join(_CSRC, s) for s in _SOURCES]]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd))
