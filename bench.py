@@ -247,7 +247,7 @@ def run_b200(a):
         bl_host.grad = None
         logl = model()
         logl.backward()
-        return float(logl), bl_host.grad
+        return float(logl.detach()), bl_host.grad
 
     for _ in range(max(3, a.warmup // 2)):
         step_host()

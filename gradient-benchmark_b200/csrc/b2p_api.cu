@@ -347,8 +347,8 @@ int b2p_set_topology(b2p_instance* h, const int32_t* h_triples) {
   h->plan = std::move(plan);
   if (getenv("B2P_TRACE")) {
     cudaFree(h->d_trace);
-    CU(cudaMalloc((void**)&h->d_trace, sizeof(long long) * 10 * h->plan.rounds));
-    CU(cudaMemset(h->d_trace, 0, sizeof(long long) * 10 * h->plan.rounds));
+    CU(cudaMalloc((void**)&h->d_trace, sizeof(long long) * 16 * h->plan.rounds));
+    CU(cudaMemset(h->d_trace, 0, sizeof(long long) * 16 * h->plan.rounds));
   }
   h->have_topology = true;
   if (h->have_tips) { int rc = retile_tips(h); if (rc) return rc; }
@@ -447,13 +447,13 @@ int b2p_loglik_grad_host(b2p_instance* h, const double* h_bl, double* h_logl, do
   if (h_grad) memcpy(h_grad, h->h_pin_out + 1, sizeof(double) * n_br);
   if (h->d_trace && h_grad) {
     const int R = h->plan.rounds;
-    std::vector<long long> tr(10 * (size_t)R);
+    std::vector<long long> tr(16 * (size_t)R);
     CU(cudaMemcpy(tr.data(), h->d_trace, tr.size() * sizeof(long long), cudaMemcpyDeviceToHost));
     if (FILE* f = fopen(getenv("B2P_TRACE"), "w")) {
       for (int w = 0; w < 2; ++w)
         for (int q = 0; q < R; ++q) {
-          const long long* r = tr.data() + ((size_t)w * R + q) * 5;
-          fprintf(f, "%d %d %lld %lld %lld %lld %lld\n", w, q, r[0], r[1], r[2], r[3], r[4]);
+          const long long* r = tr.data() + ((size_t)w * R + q) * 8;
+          fprintf(f, "%d %d %lld %lld %lld %lld %lld %lld %lld\n", w, q, r[0], r[1], r[2], r[3], r[4], r[5], r[6]);
         }
       fclose(f);
     }

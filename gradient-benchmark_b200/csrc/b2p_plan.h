@@ -25,6 +25,7 @@
 #pragma once
 #include <algorithm>
 #include <climits>
+#include <cstdlib>
 #include <cstring>
 #include <queue>
 #include <string>
@@ -274,34 +275,44 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
     out.rounds_post = (int)tasks.size();
   }
   {
-    std::priority_queue<Item> ready;
-    ready.push({height[root], -root});
+    // Two ready sets: `fresh` = children of the previous round's tasks (their parent-side
+    // partial still sits in the pool: no store, no load), `old` = everything else.  Fresh
+    // tasks go first, by subtree height; the walk becomes wn depth-first fronts in parallel.
+    // B2P_PRE_LOCALITY=0 (planner experiments) restores pure height priority.
+    const bool locality = !(getenv("B2P_PRE_LOCALITY") && atoi(getenv("B2P_PRE_LOCALITY")) == 0);
+    std::priority_queue<Item> fresh, old;
+    fresh.push({height[root], -root});
     int done = 0;
     std::vector<Item> skipped;
     while (done < N - 1) {
       std::vector<int> chosen;
       const int q = (int)tasks.size();
       skipped.clear();
-      while ((int)chosen.size() < wn_eff && !ready.empty()) {
-        const Item it = ready.top();
-        const int v = -it.second;
-        ready.pop();
-        int px[3], n_op = 0;
-        if (left[v] >= N) px[n_op++] = rnd_post[left[v]];
-        if (right[v] >= N) px[n_op++] = rnd_post[right[v]];
-        if (v != root) px[n_op++] = rnd_pre[parent[v]];
-        if (!try_add(q, px, n_op, (left[v] >= N) + (right[v] >= N))) { skipped.push_back(it); continue; }
-        chosen.push_back(v);
+      for (int pass = 0; pass < 2; ++pass) {
+        std::priority_queue<Item>& ready = pass == 0 ? fresh : old;
+        while ((int)chosen.size() < wn_eff && !ready.empty()) {
+          const Item it = ready.top();
+          const int v = -it.second;
+          ready.pop();
+          int px[3], n_op = 0;
+          if (left[v] >= N) px[n_op++] = rnd_post[left[v]];
+          if (right[v] >= N) px[n_op++] = rnd_post[right[v]];
+          if (v != root) px[n_op++] = rnd_pre[parent[v]];
+          if (!try_add(q, px, n_op, (left[v] >= N) + (right[v] >= N))) { skipped.push_back(it); continue; }
+          chosen.push_back(v);
+        }
       }
-      for (const Item& it : skipped) ready.push(it);
-      if (chosen.empty() && ready.empty()) { why = "pre schedule stalled"; return false; }
+      while (!fresh.empty()) { old.push(fresh.top()); fresh.pop(); }  // not taken: no longer fresh
+      for (const Item& it : skipped) old.push(it);
+      if (chosen.empty() && old.empty()) { why = "pre schedule stalled"; return false; }
       if ((int)tasks.size() > 16 * N + 128) { why = "pool exhausted (schedule)"; return false; }
       for (int i = 0; i < (int)chosen.size(); ++i) { rnd_pre[chosen[i]] = q; slot_pre[chosen[i]] = i; }
       tasks.push_back(chosen);
       for (int v : chosen) {
         ++done;
-        if (left[v] >= N) ready.push({height[left[v]], -left[v]});
-        if (right[v] >= N) ready.push({height[right[v]], -right[v]});
+        std::priority_queue<Item>& dst = locality ? fresh : old;
+        if (left[v] >= N) dst.push({height[left[v]], -left[v]});
+        if (right[v] >= N) dst.push({height[right[v]], -right[v]});
       }
     }
     out.rounds = (int)tasks.size();

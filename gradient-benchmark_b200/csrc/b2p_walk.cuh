@@ -487,7 +487,7 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
       const int par = q & 1;
 #ifdef B2P_TRACE_CLOCKS
       const bool tr = p.trace && blockIdx.x == 0 && (t == 0 || t == NT - 32) && tile == 0;
-      long long* trow = tr ? p.trace + ((t ? 1 : 0) * (long long)R + q) * 5 : nullptr;
+      long long* trow = tr ? p.trace + ((t ? 1 : 0) * (long long)R + q) * 8 : nullptr;
       if (tr) trow[0] = clock64();
 #endif
       mbar_wait(bar0 + 8 * st, (phase_bits >> st) & 1u);
@@ -512,7 +512,11 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
           bulk_store(const_cast<unsigned char*>(gptr(jb.w, jb.x)), sbase + jb.y, jb.z);
         }
         bulk_commit();  // one (possibly empty) group per lane per round
-        for (unsigned j = pw + np * lane; j < n_loads; j += 32 * np) {
+#ifdef B2P_TRACE_CLOCKS
+        if (tr) trow[5] = clock64();
+#endif
+        // the first loads of the list are issued by the compute warps, one each (below)
+        for (unsigned j = first_copy_warp + pw + np * lane; j < n_loads; j += 32 * np) {
           const uint4 jb = lds_u4(jobs + j * 16);
           bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar);
         }
@@ -520,11 +524,21 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
         if (tr) trow[2] = clock64();
 #endif
         if (q > 0) fold_round(p, sbase, par ^ 1, pw, lane, first_tile, ll_acc);
+#ifdef B2P_TRACE_CLOCKS
+        if (tr) trow[6] = clock64();
+#endif
         asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         asm volatile("cp.async.bulk.wait_group 1;" ::: "memory");
       } else {
+        // ---- one load of round q + depth per compute warp: a bulk copy costs its issuing warp
+        // ~100 cycles, so the copy warps alone would be the critical path of the round
+        const uint4 hdr = lds_u4(frame);
+        if (lane == 0 && q + D < R && (unsigned)warp < hdr.x) {
+          const uint4 jb = lds_u4(frame + 16 + warp * 16);
+          bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar0 + 8 * (st == 0 ? S - 1 : st - 1));
+        }
         // ---- this thread's task
-        const unsigned pass = lds_u32(frame + 12);
+        const unsigned pass = hdr.w;
         TaskDesc d;
         d.flags = 0;
         if (in_slot) {

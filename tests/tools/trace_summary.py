@@ -9,6 +9,10 @@ for w in (0, 1):
     print("warp", "0" if w == 0 else "last", "cycles per round (start to start): post %.0f pre %.0f" % (rt[:rp].mean(), rt[rp:].mean()))
     print("  mean post: wait %.0f issue %.0f compute %.0f bar %.0f" % tuple(d[:rp].mean(0)))
     print("  mean pre : wait %.0f issue %.0f compute %.0f bar %.0f" % tuple(d[rp:].mean(0)))
+    if w == 1 and x.shape[1] >= 7:
+        c = np.column_stack([x[:, 5] - x[:, 1], x[:, 2] - x[:, 5], x[:, 6] - x[:, 2], x[:, 3] - x[:, 6]])
+        print("  copy warp post: stores %.0f loads %.0f fold %.0f wait_group %.0f" % tuple(c[1:rp].mean(0)))
+        print("  copy warp pre : stores %.0f loads %.0f fold %.0f wait_group %.0f" % tuple(c[rp:].mean(0)))
     if w == 0:
         for q in range(0, len(x), 10):
             print("  round %3d: wait %5d issue %5d compute %5d bar %5d  next-start %6d" % (q, *d[q], rt[q] if q < len(rt) else 0))
