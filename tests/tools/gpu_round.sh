@@ -12,5 +12,5 @@ $BENCH_SMALL > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/launches.csv $BENCH_SMALL > gpurun_out/ncu1.log 2>&1
 echo "ncu launches rc=$?"
 $BENCH_SMALL > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:wave_kernel -s 3 -c 1 -f -o gpurun_out/prof $BENCH_SMALL > gpurun_out/ncu2.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:walk_kernel -s 3 -c 1 -f -o gpurun_out/prof $BENCH_SMALL > gpurun_out/ncu2.log 2>&1
 echo "ncu full rc=$?"; ls -la gpurun_out
