@@ -195,6 +195,18 @@ __device__ __forceinline__ int rescale(int lane, int kk, float (&y)[4]) {
   return 0;
 }
 
+// 1 / x for a positive, normal x (a site likelihood, rescaled to stay far from the
+// denormals): hardware seed + two Newton steps, relative error ~1e-16, no slow path.
+__device__ __forceinline__ double fast_rcp(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  double e = fma(-x, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-x, r, 1.0);
+  r = fma(r, e, r);
+  return r;
+}
+
 // Per-thread constants (all shared-memory addresses are 32-bit).
 template <int CPT>
 struct WalkThread {
@@ -241,9 +253,8 @@ __device__ __forceinline__ void load_messages(const WalkThread<CPT>& th, unsigne
 //   x_v = m_l o m_r (rescaled when tiny) ;  m_v = P_v x_v ; root: site likelihoods -> log-likelihood term
 template <typename T, int K, int CPT>
 __device__ __forceinline__ void post_task(const WalkParams<T>& p, const WalkThread<CPT>& th, unsigned frame, const TaskDesc& d,
-                                          bool live, int* scount, int col, unsigned gslot) {
-  T ma[CPT][4], mb[CPT][4];
-  load_messages<T, CPT>(th, frame, d, live, ma, mb);
+                                          bool live, int* scount, int col, unsigned gslot, T (&ma)[CPT][4],
+                                          T (&mb)[CPT][4]) {
   int bumped[CPT];
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
@@ -285,9 +296,7 @@ __device__ __forceinline__ void post_task(const WalkParams<T>& p, const WalkThre
 //   q_l = u_v o m_r, q_r = u_v o m_l ; L = q_l . m_l ; dL/dt_l = r_k q_l.(Q m_l) ; u_l = P_l^T q_l (same for r)
 template <typename T, int K, int CPT>
 __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThread<CPT>& th, unsigned frame, const TaskDesc& d,
-                                         bool live, unsigned gslot) {
-  T ma[CPT][4], mb[CPT][4];
-  load_messages<T, CPT>(th, frame, d, live, ma, mb);
+                                         bool live, unsigned gslot, T (&ma)[CPT][4], T (&mb)[CPT][4]) {
   T ql[CPT][4], qr[CPT][4];
   double gl = 0.0, gr = 0.0;
 #pragma unroll
@@ -321,7 +330,7 @@ __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThrea
     }
     if (live && th.k == 0) {
       // K == 1: the single category's weight cancels, its rate multiplies the numerators
-      const double inv = (K == 1 ? th.w[c] * p.rates[0] : th.w[c]) / (double)den;
+      const double inv = (K == 1 ? th.w[c] * p.rates[0] : th.w[c]) * fast_rcp((double)den);
       gl += (double)numl * inv;
       gr += (double)numr * inv;
     }
@@ -530,14 +539,7 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
         asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         asm volatile("cp.async.bulk.wait_group 1;" ::: "memory");
       } else {
-        // ---- one load of round q + depth per compute warp: a bulk copy costs its issuing warp
-        // ~100 cycles, so the copy warps alone would be the critical path of the round
         const uint4 hdr = lds_u4(frame);
-        if (lane == 0 && q + D < R && (unsigned)warp < hdr.x) {
-          const uint4 jb = lds_u4(frame + 16 + warp * 16);
-          bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar0 + 8 * (st == 0 ? S - 1 : st - 1));
-        }
-        // ---- this thread's task
         const unsigned pass = hdr.w;
         TaskDesc d;
         d.flags = 0;
@@ -549,13 +551,28 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
           }
         }
         const bool live = (d.flags & WF_LIVE) != 0;
+        // ---- one load of round q + depth per compute warp (a bulk copy costs its issuing warp
+        // ~100 cycles: the copy warps alone would be the critical path of the round).  In the
+        // longer pre-order rounds it is placed after the operand reads so that the two overlap.
+        const bool my_job = lane == 0 && q + D < R && (unsigned)warp < hdr.x;
+        const unsigned bar_next = bar0 + 8 * (st == 0 ? S - 1 : st - 1);
+        if (my_job && pass == 0) {
+          const uint4 jb = lds_u4(frame + 16 + warp * 16);
+          bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar_next);
+        }
+        T ma[CPT][4], mb[CPT][4];
+        if (K != 1 || live) load_messages<T, CPT>(th, frame, d, live, ma, mb);
+        if (my_job && pass != 0) {
+          const uint4 jb = lds_u4(frame + 16 + warp * 16);
+          bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar_next);
+        }
 #ifdef B2P_TRACE_CLOCKS
         if (tr) trow[2] = clock64();
 #endif
         if (K != 1 || live) {  // K == 1: no warp-collective inside a task, idle lanes skip it
           const unsigned gslot = sbase + o_gslot + par * p.wn * p.ts * 16;
-          if (pass == 0) post_task<T, K, CPT>(p, th, frame, d, live, scount, col, gslot);
-          else pre_task<T, K, CPT>(p, th, frame, d, live, gslot);
+          if (pass == 0) post_task<T, K, CPT>(p, th, frame, d, live, scount, col, gslot, ma, mb);
+          else pre_task<T, K, CPT>(p, th, frame, d, live, gslot, ma, mb);
         }
       }
       // shared-memory results of this round (generic proxy) before the bulk copies (async
