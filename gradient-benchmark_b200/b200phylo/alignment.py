@@ -57,30 +57,38 @@ class Alignment:
 
 @dataclass
 class SitePattern:
-    """Unique alignment columns: ``masks`` uint8 [N, P], ``weights`` float64 [P]."""
+    """Unique alignment columns: ``masks`` uint8 [N, P], ``weights`` float64 [P].
+
+    ``n_states`` 4: ``masks`` are IUPAC bit masks.  More states (codon models): ``masks``
+    holds the state CODE of each tip (0..n_states-1; anything else = missing)."""
 
     names: List[str]
     masks: np.ndarray
     weights: np.ndarray
+    n_states: int = 4
 
     @property
     def n_patterns(self) -> int:
         return self.masks.shape[1]
 
     def partials(self) -> np.ndarray:
-        """float64 [N, P, 4] tip partials (0/1) — what the oracle consumes."""
+        """float64 [N, P, S] tip partials (0/1) — what the oracle consumes."""
+        if self.n_states != 4:
+            out = (self.masks[..., None] == np.arange(self.n_states, dtype=np.uint8)).astype(np.float64)
+            out[self.masks >= self.n_states] = 1.0
+            return out
         bits = (self.masks[..., None] >> np.arange(4, dtype=np.uint8)) & 1
         return bits.astype(np.float64)
 
     def reorder(self, taxa: Sequence[str]) -> "SitePattern":
         index = {nm: i for i, nm in enumerate(self.names)}
         rows = [index[t] for t in taxa]
-        return SitePattern(list(taxa), self.masks[rows], self.weights)
+        return SitePattern(list(taxa), self.masks[rows], self.weights, self.n_states)
 
     def slice(self, start: int, stop: int) -> "SitePattern":
         """Contiguous pattern shard (multi-GPU sharding)."""
         return SitePattern(self.names, np.ascontiguousarray(self.masks[:, start:stop]),
-                           self.weights[start:stop].copy())
+                           self.weights[start:stop].copy(), self.n_states)
 
 
 def read_fasta(path: str) -> Alignment:
@@ -116,15 +124,16 @@ def compress_alignment(aln: Alignment) -> SitePattern:
 
 def _evolve(tree, p_mats: np.ndarray, freqs: np.ndarray, n_sites: int, rng,
             site_cat: np.ndarray) -> np.ndarray:
-    """States uint8 [n_nodes, n_sites] evolved root→tips. p_mats [B, K, 4, 4]."""
+    """States uint8 [n_nodes, n_sites] evolved root→tips. p_mats [B, K, S, S]."""
+    n_st = p_mats.shape[-1]
     states = np.empty((tree.n_nodes, n_sites), dtype=np.uint8)
-    states[tree.root] = rng.choice(4, size=n_sites, p=freqs)
+    states[tree.root] = rng.choice(n_st, size=n_sites, p=freqs)
     for v in range(tree.n_nodes - 1, tree.n_tips - 1, -1):
         for c in tree.children[v]:
             pm = p_mats[c][site_cat, states[v]]  # [n_sites, 4] row of P for parent state
             cum = np.cumsum(pm, axis=1)
             u = rng.random(n_sites)[:, None]
-            states[c] = np.minimum((u > cum).sum(axis=1), 3).astype(np.uint8)
+            states[c] = np.minimum((u > cum).sum(axis=1), n_st - 1).astype(np.uint8)
     return states
 
 
@@ -172,6 +181,8 @@ def simulate_patterns(tree, p_mats: np.ndarray, freqs: np.ndarray, n_patterns: i
         guard += 1
         if guard > 10000:
             raise RuntimeError("could not reach the requested number of unique patterns")
-    masks = (1 << np.stack(cols, axis=1)).astype(np.uint8)
+    n_st = p_mats.shape[-1]
+    codes = np.stack(cols, axis=1)
+    masks = (1 << codes).astype(np.uint8) if n_st == 4 else codes.astype(np.uint8)
     names = tree.names or [f"t{i}" for i in range(tree.n_tips)]
-    return SitePattern(list(names), masks, np.asarray(counts, dtype=np.float64))
+    return SitePattern(list(names), masks, np.asarray(counts, dtype=np.float64), n_st)

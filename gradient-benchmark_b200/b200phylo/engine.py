@@ -102,17 +102,20 @@ class Engine:
 
     Parameters mirror ``b2p_config``; arrays follow ``include/b200phylo.h``:
     ``triples`` int32 [N-1, 3] post-order, ``masks`` uint8 [N, P], ``weights`` [P].
+    ``n_states`` 4 selects the nucleotide walk kernel; 5..64 (e.g. 61 codons) the
+    dense-state path, where the tip bytes are state codes (>= n_states: missing).
     """
 
     def __init__(self, n_tips: int, n_patterns: int, n_categories: int = 1,
-                 precision: str = "float64", device: int = 0, warps_per_block: int = 0):
+                 precision: str = "float64", device: int = 0, warps_per_block: int = 0, n_states: int = 4):
         self._h = ctypes.c_void_p()
         self._lib = load_library()
         prec = {"float64": 64, "float32": 32, 64: 64, 32: 32}.get(precision)
         if prec is None:
             raise ValueError(f"precision must be float64 or float32, got {precision!r}")
-        cfg = _Config(int(n_tips), int(n_patterns), int(n_categories), 4, prec, int(device),
+        cfg = _Config(int(n_tips), int(n_patterns), int(n_categories), int(n_states), prec, int(device),
                       int(warps_per_block), 0)
+        self.n_states = int(n_states)
         rc = self._lib.b2p_create(ctypes.byref(cfg), ctypes.byref(self._h))
         if rc != 0:
             msg = self._lib.b2p_last_error(None).decode()
@@ -167,8 +170,9 @@ class Engine:
 
     def set_eigen(self, evec, ivec, evals, freqs) -> None:
         a = [np.ascontiguousarray(x, dtype=np.float64) for x in (evec, ivec, evals, freqs)]
-        if a[0].shape != (4, 4) or a[1].shape != (4, 4) or a[2].shape != (4,) or a[3].shape != (4,):
-            raise ValueError("eigen system must be 4x4, 4x4, 4, 4")
+        n = self.n_states
+        if a[0].shape != (n, n) or a[1].shape != (n, n) or a[2].shape != (n,) or a[3].shape != (n,):
+            raise ValueError(f"eigen system must be {n}x{n}, {n}x{n}, {n}, {n}")
         self._check(self._lib.b2p_set_eigen(self._h, *map(_dptr, a)), "b2p_set_eigen")
 
     def set_categories(self, rates, weights) -> None:

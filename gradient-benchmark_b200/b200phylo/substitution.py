@@ -14,7 +14,7 @@ from dataclasses import dataclass
 
 import numpy as np
 
-__all__ = ["SubstitutionModel", "JC69", "HKY", "GTR", "GeneralReversible"]
+__all__ = ["SubstitutionModel", "JC69", "HKY", "GTR", "GeneralReversible", "CodonGY94"]
 
 
 @dataclass
@@ -91,3 +91,34 @@ class GeneralReversible(SubstitutionModel):
     def __init__(self, rates, freqs):
         super().__init__(rates, freqs)
         self.n_states = len(self.freqs)
+
+
+class CodonGY94(GeneralReversible):
+    """61-state Goldman-Yang-style codon model (BASELINE.json configs[4]): sense codons of the
+    standard code; exchangeability 0 for multi-nucleotide changes, ``kappa`` for transitions,
+    ``omega`` for non-synonymous changes; codon frequencies from nucleotide frequencies (F1x4)."""
+
+    _AA = "FFLLSSSSYY**CC*WLLLLPPPPHHQQRRRRIIIMTTTTNNKKSSRRVVVVAAAADDEEGGGG"  # TCAG order
+
+    def __init__(self, kappa: float = 2.0, omega: float = 0.5, nuc_freqs=(0.25, 0.25, 0.25, 0.25)):
+        nuc = "TCAG"
+        pi_n = dict(zip("ACGT", np.asarray(nuc_freqs, dtype=np.float64)))
+        codons = [a + b + c for a in nuc for b in nuc for c in nuc]
+        sense = [(cd, aa) for cd, aa in zip(codons, self._AA) if aa != "*"]
+        self.codons = [cd for cd, _ in sense]
+        purines = {"A", "G"}
+        n = len(sense)
+        rates = []
+        for i in range(n):
+            for j in range(i + 1, n):
+                (ci, ai), (cj, aj) = sense[i], sense[j]
+                diff = [(x, y) for x, y in zip(ci, cj) if x != y]
+                if len(diff) != 1:
+                    rates.append(0.0)
+                    continue
+                x, y = diff[0]
+                r = kappa if (x in purines) == (y in purines) else 1.0
+                rates.append(r * (1.0 if ai == aj else omega))
+        freqs = [pi_n[c[0]] * pi_n[c[1]] * pi_n[c[2]] for c in self.codons]
+        super().__init__(rates, freqs)
+        self.kappa, self.omega = float(kappa), float(omega)

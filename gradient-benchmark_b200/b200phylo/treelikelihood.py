@@ -187,7 +187,8 @@ class TreeLikelihoodModel:
             device = torch.cuda.current_device() if torch.cuda.is_available() else 0
         n_cat = len(np.asarray(self.site_model.rates))
         self.engine = Engine(tree_model.n_tips, site_pattern.n_patterns, n_cat,
-                             precision=precision, device=device, warps_per_block=warps_per_block)
+                             precision=precision, device=device, warps_per_block=warps_per_block,
+                             n_states=getattr(site_pattern, "n_states", 4))
         self.engine.set_topology(tree_model.post_triples)
         self.engine.set_tip_states(site_pattern.masks)
         self.engine.set_pattern_weights(site_pattern.weights)

@@ -2,6 +2,7 @@
 // Host side: instance state, the wave planner (b2p_plan.h), launch sizing.
 #include <algorithm>
 #include <cstdarg>
+#include <cstddef>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -12,6 +13,7 @@
 #include "b2p_aux.cuh"
 #include "b2p_plan.h"
 #include "b2p_walk.cuh"
+#include "b2p_dense.cuh"
 
 using namespace b2p;
 
@@ -53,6 +55,17 @@ struct b2p_instance {
   double freqs[4]{};
   double qmat[16]{};
   double cat_w[kMaxCat]{};
+  // dense-state path (5..64 states, b2p_dense.cuh): null for 4-state instances
+  struct Dense {
+    int S = 0, cols_pad = 0, n_tiles = 0;
+    double *evec = nullptr, *ivec = nullptr, *evals = nullptr, *q = nullptr, *qt = nullptr, *freqs = nullptr;
+    double *P = nullptr, *PT = nullptr, *D = nullptr, *weights = nullptr, *msg = nullptr, *pre = nullptr;
+    uint8_t* codes = nullptr;
+    int* scount = nullptr;
+    DenseNode* nodes = nullptr;                 // post-order levels, then pre-order levels
+    std::vector<int> post_off, pre_off;         // level boundaries into `nodes`
+    int root = 0;
+  }* dense = nullptr;
   mutable std::string err;
 };
 
@@ -112,6 +125,157 @@ static size_t elem_size(const b2p_instance* h) {
   return h->cfg.precision == B2P_PRECISION_F32 ? 4 : 8;
 }
 
+
+// ------------------------------------------------------------------ dense-state path (host)
+static int dense_create(b2p_instance* h) {
+  const int N = h->cfg.n_tips, P = h->cfg.n_patterns, S = h->cfg.n_states;
+  b2p_instance::Dense* d = new (std::nothrow) b2p_instance::Dense();
+  if (!d) return fail(h, B2P_ERR_ALLOC, "out of host memory");
+  h->dense = d;
+  d->S = S;
+  d->n_tiles = (P + DT - 1) / DT;
+  d->cols_pad = d->n_tiles * DT;
+  const size_t n_br = 2 * (size_t)N - 2, mat = (size_t)SP * SP * sizeof(double);
+  const size_t part = (size_t)(N - 1) * SP * d->cols_pad * sizeof(double);
+  int rc;
+  if ((rc = dev_alloc(h, &d->evec, sizeof(double) * S * S)) || (rc = dev_alloc(h, &d->ivec, sizeof(double) * S * S)) ||
+      (rc = dev_alloc(h, &d->evals, sizeof(double) * SP)) || (rc = dev_alloc(h, &d->q, mat)) || (rc = dev_alloc(h, &d->qt, mat)) ||
+      (rc = dev_alloc(h, &d->freqs, sizeof(double) * SP)) || (rc = dev_alloc(h, &d->P, n_br * mat)) ||
+      (rc = dev_alloc(h, &d->PT, n_br * mat)) || (rc = dev_alloc(h, &d->D, n_br * mat)) ||
+      (rc = dev_alloc(h, &d->weights, sizeof(double) * d->cols_pad)) || (rc = dev_alloc(h, (char**)&d->msg, part)) ||
+      (rc = dev_alloc(h, (char**)&d->pre, part)) || (rc = dev_alloc(h, &d->codes, (size_t)N * d->cols_pad)) ||
+      (rc = dev_alloc(h, &d->scount, sizeof(int) * d->cols_pad)) || (rc = dev_alloc(h, &d->nodes, sizeof(DenseNode) * 2 * (N - 1))) ||
+      (rc = dev_alloc(h, &h->d_lpart, sizeof(double) * d->n_tiles)) ||
+      (rc = dev_alloc(h, &h->d_gpart, sizeof(double) * (size_t)d->n_tiles * n_br)) ||
+      (rc = dev_alloc(h, &h->d_bl_stage, sizeof(double) * n_br)) || (rc = dev_alloc(h, &h->d_out_stage, sizeof(double) * (n_br + 1))))
+    return rc;
+  CU(cudaMemset(d->msg, 0, part));
+  CU(cudaMemset(d->pre, 0, part));
+  CU(cudaMallocHost((void**)&h->h_pin_in, sizeof(double) * n_br));
+  CU(cudaMallocHost((void**)&h->h_pin_out, sizeof(double) * (n_br + 1)));
+  CU(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+  CU(cudaFuncSetAttribute((const void*)dense_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * SP * SP * 8));
+  CU(cudaFuncSetAttribute((const void*)dense_pre_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 5 * SP * SP * 8));
+  cudaFuncAttributes fa;
+  CU(cudaFuncGetAttributes(&fa, (const void*)dense_pre_kernel));
+  h->regs = fa.numRegs;
+  return B2P_OK;
+}
+
+// Level lists: post-order levels bottom-up (a node after both children), pre-order levels by depth.
+static int dense_set_topology(b2p_instance* h, const int32_t* tr) {
+  const int N = h->cfg.n_tips, n_nodes = 2 * N - 1, root = 2 * N - 2;
+  b2p_instance::Dense* d = h->dense;
+  std::vector<int> left(n_nodes, -1), right(n_nodes, -1), parent(n_nodes, -1), lvl(n_nodes, 0), dep(n_nodes, 0);
+  std::vector<char> seen(n_nodes, 0);
+  for (int e = 0; e < N - 1; ++e) {
+    const int v = tr[3 * e], l = tr[3 * e + 1], r = tr[3 * e + 2];
+    if (v != N + e) return fail(h, B2P_ERR_ARG, "b2p_set_topology: triples must list internal nodes N..2N-2 in order (post-order ids)");
+    if (l < 0 || r < 0 || l >= v || r >= v || l == r) return fail(h, B2P_ERR_ARG, "b2p_set_topology: child id out of range / not in post-order");
+    if (seen[l] || seen[r]) return fail(h, B2P_ERR_ARG, "b2p_set_topology: a node has two parents");
+    seen[l] = seen[r] = 1;
+    left[v] = l; right[v] = r; parent[l] = parent[r] = v;
+    lvl[v] = std::max(l >= N ? lvl[l] + 1 : 0, r >= N ? lvl[r] + 1 : 0);
+  }
+  for (int v = 0; v < root; ++v)
+    if (!seen[v]) return fail(h, B2P_ERR_ARG, "b2p_set_topology: tree is not connected (node without parent)");
+  int max_dep = 0;
+  for (int v = root - 1; v >= N; --v) { dep[v] = dep[parent[v]] + 1; max_dep = std::max(max_dep, dep[v]); }
+  std::vector<DenseNode> nodes;
+  d->post_off.assign(1, 0);
+  for (int L = 0; L <= lvl[root]; ++L) {
+    for (int v = N; v < n_nodes; ++v)
+      if (lvl[v] == L) nodes.push_back({v, left[v], right[v], 0});
+    d->post_off.push_back((int)nodes.size());
+  }
+  d->pre_off.assign(1, (int)nodes.size());
+  for (int L = 0; L <= max_dep; ++L) {
+    for (int v = N; v < n_nodes; ++v)
+      if (dep[v] == L) nodes.push_back({v, left[v], right[v], 0});
+    d->pre_off.push_back((int)nodes.size());
+  }
+  d->root = root;
+  h->plan.rounds_post = lvl[root] + 1; h->plan.rounds_pre = max_dep + 1; h->plan.rounds = h->plan.rounds_post + h->plan.rounds_pre;
+  h->plan.tree_depth = max_dep + 1;
+  CU(cudaSetDevice(h->cfg.device));
+  CU(cudaDeviceSynchronize());
+  CU(cudaMemcpy(d->nodes, nodes.data(), nodes.size() * sizeof(DenseNode), cudaMemcpyHostToDevice));
+  h->have_topology = true;
+  return B2P_OK;
+}
+
+static int dense_set_tips(b2p_instance* h, const uint8_t* codes) {
+  const int N = h->cfg.n_tips, P = h->cfg.n_patterns;
+  b2p_instance::Dense* d = h->dense;
+  std::vector<uint8_t> pad((size_t)N * d->cols_pad, 255);
+  for (int i = 0; i < N; ++i) memcpy(pad.data() + (size_t)i * d->cols_pad, codes + (size_t)i * P, P);
+  CU(cudaSetDevice(h->cfg.device));
+  CU(cudaMemcpy(d->codes, pad.data(), pad.size(), cudaMemcpyHostToDevice));
+  h->have_tips = true;
+  return B2P_OK;
+}
+
+static int dense_set_weights(b2p_instance* h, const double* w) {
+  b2p_instance::Dense* d = h->dense;
+  std::vector<double> pad(d->cols_pad, 0.0);
+  memcpy(pad.data(), w, sizeof(double) * h->cfg.n_patterns);
+  CU(cudaSetDevice(h->cfg.device));
+  CU(cudaMemcpy(d->weights, pad.data(), pad.size() * sizeof(double), cudaMemcpyHostToDevice));
+  h->have_weights = true;
+  return B2P_OK;
+}
+
+static int dense_set_eigen(b2p_instance* h, const double* evec, const double* ivec, const double* evals, const double* freqs) {
+  b2p_instance::Dense* d = h->dense;
+  const int S = d->S;
+  std::vector<double> q((size_t)SP * SP, 0.0), qt((size_t)SP * SP, 0.0), ev(SP, 0.0), fr(SP, 0.0);
+  for (int i = 0; i < S; ++i)
+    for (int l = 0; l < S; ++l) {
+      double acc = 0.0;
+      for (int j = 0; j < S; ++j) acc += evec[i * S + j] * evals[j] * ivec[j * S + l];
+      q[(size_t)i * SP + l] = acc;
+      qt[(size_t)l * SP + i] = acc;
+    }
+  for (int i = 0; i < S; ++i) { ev[i] = evals[i]; fr[i] = freqs[i]; }
+  CU(cudaSetDevice(h->cfg.device));
+  CU(cudaMemcpy(d->evec, evec, sizeof(double) * S * S, cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(d->ivec, ivec, sizeof(double) * S * S, cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(d->evals, ev.data(), sizeof(double) * SP, cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(d->freqs, fr.data(), sizeof(double) * SP, cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(d->q, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(d->qt, qt.data(), qt.size() * sizeof(double), cudaMemcpyHostToDevice));
+  h->have_eigen = true;
+  return B2P_OK;
+}
+
+static cudaError_t dense_launch(b2p_instance* h, const double* d_bl, double* d_logl, double* d_grad, cudaStream_t st) {
+  b2p_instance::Dense* d = h->dense;
+  const int N = h->cfg.n_tips, n_br = 2 * N - 2;
+  DenseParams p;
+  p.n_tips = N; p.n_states = d->S; p.n_cols = h->cfg.n_patterns; p.cols_pad = d->cols_pad;
+  p.n_tiles = d->n_tiles; p.n_branches = n_br; p.rate = h->model.rates[0];
+  p.P = d->P; p.PT = d->PT; p.D = d->D; p.Q = d->q; p.QT = d->qt; p.freqs = d->freqs; p.codes = d->codes;
+  p.weights = d->weights; p.msg = d->msg; p.pre = d->pre; p.scount = d->scount; p.lpart = h->d_lpart; p.gpart = h->d_gpart;
+  dense_transition_kernel<<<n_br, DNT, 0, st>>>(d->evec, d->ivec, d->evals, d->q, d_bl, p.rate, d->S, d->P, d->PT, d->D);
+  cudaError_t e = cudaMemsetAsync(d->scount, 0, sizeof(int) * d->cols_pad, st);
+  if (e != cudaSuccess) return e;
+  const int slot = (int)(h->prof_count % b2p_instance::kProfRing);
+  if (h->profiling) cudaEventRecord(h->ev0[slot], st);
+  for (size_t L = 0; L + 1 < d->post_off.size(); ++L) {
+    const int n = d->post_off[L + 1] - d->post_off[L];
+    if (n > 0) dense_post_kernel<<<dim3(n, d->n_tiles), DNT, 2 * SP * SP * 8, st>>>(p, d->nodes + d->post_off[L], d->root);
+  }
+  if (d_grad)
+    for (size_t L = 0; L + 1 < d->pre_off.size(); ++L) {
+      const int n = d->pre_off[L + 1] - d->pre_off[L];
+      if (n > 0) dense_pre_kernel<<<dim3(n, d->n_tiles), DNT, 5 * SP * SP * 8, st>>>(p, d->nodes + d->pre_off[L], d->root);
+    }
+  if (h->profiling) { cudaEventRecord(h->ev1[slot], st); ++h->prof_count; }
+  const int nb = d_grad ? n_br : 0;
+  reduce_kernel<<<(nb + 31) / 32 + 1, 512, 0, st>>>(h->d_gpart, h->d_lpart, d->n_tiles, nb, d_grad, d_logl);
+  return cudaGetLastError();
+}
+
 extern "C" {
 
 int b2p_version(void) { return 2; }
@@ -126,6 +290,14 @@ int b2p_destroy(b2p_instance* h) {
   cudaFree(h->d_records); cudaFree(h->d_mat_dst); cudaFree(h->d_mats);
   cudaFree(h->d_tips); cudaFree(h->d_tips_raw); cudaFree(h->d_tip_order); cudaFree(h->d_weights); cudaFree(h->d_msg); cudaFree(h->d_pre);
   cudaFree(h->d_lpart); cudaFree(h->d_trace); cudaFree(h->d_gpart); cudaFree(h->d_bl_stage); cudaFree(h->d_out_stage);
+  if (h->dense) {
+    b2p_instance::Dense* d = h->dense;
+    for (void* p : {(void*)d->evec, (void*)d->ivec, (void*)d->evals, (void*)d->q, (void*)d->qt, (void*)d->freqs, (void*)d->P,
+                    (void*)d->PT, (void*)d->D, (void*)d->weights, (void*)d->msg, (void*)d->pre, (void*)d->codes,
+                    (void*)d->scount, (void*)d->nodes})
+      cudaFree(p);
+    delete d;
+  }
   if (h->h_pin_in) cudaFreeHost(h->h_pin_in);
   if (h->h_pin_out) cudaFreeHost(h->h_pin_out);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -143,8 +315,10 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
     return fail(h, B2P_ERR_ARG, "b2p_create: need n_tips >= 2, n_patterns >= 1, n_categories >= 1");
   if (cfg->n_categories > kMaxCat)
     return fail(h, B2P_ERR_UNSUPPORTED, "b2p_create: n_categories > %d", kMaxCat);
-  if (cfg->n_states != 4)
-    return fail(h, B2P_ERR_UNSUPPORTED, "b2p_create: only 4-state models are built (got %d)",
+  if (cfg->n_states != 4 && (cfg->n_states < 5 || cfg->n_states > SP))
+    return fail(h, B2P_ERR_UNSUPPORTED, "b2p_create: n_states must be 4 or 5..%d (got %d)", SP, cfg->n_states);
+  if (cfg->n_states != 4 && (cfg->n_categories != 1 || cfg->precision != B2P_PRECISION_F64))
+    return fail(h, B2P_ERR_UNSUPPORTED, "b2p_create: the dense-state path (n_states = %d) is built for one rate category in fp64",
                 cfg->n_states);
   if (cfg->precision != B2P_PRECISION_F64 && cfg->precision != B2P_PRECISION_F32)
     return fail(h, B2P_ERR_ARG, "b2p_create: precision must be 64 or 32");
@@ -175,6 +349,11 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   int rc = B2P_OK;
   auto bail = [&](int code) { std::string m = h->err; b2p_destroy(h); g_create_error = m; return code; };
 
+  if (cfg->n_states != 4) {
+    if ((rc = dense_create(h))) return bail(rc);
+    *out = h;
+    return B2P_OK;
+  }
   // geometry: threads per CTA (warps_per_block * 32 if given), tile width, copy depth
   int nt_force = cfg->warps_per_block > 0 ? cfg->warps_per_block * 32 : 0, ct_force = 0, depth = 1;
   if (const char* s = getenv("B2P_NT")) nt_force = atoi(s);
@@ -304,8 +483,18 @@ extern "C" {
 int b2p_get_info(const b2p_instance* h, b2p_info* o) {
   if (!h || !o) return B2P_ERR_ARG;
   const int64_t N = h->cfg.n_tips, P = h->cfg.n_patterns, K = h->cfg.n_categories;
-  const int64_t U = P * K * 4 * (int64_t)elem_size(h);
-  o->n_tips = (int)N; o->n_patterns = (int)P; o->n_categories = (int)K; o->n_states = 4;
+  const int64_t U = P * K * h->cfg.n_states * (int64_t)elem_size(h);
+  o->n_tips = (int)N; o->n_patterns = (int)P; o->n_categories = (int)K; o->n_states = h->cfg.n_states;
+  if (h->dense) {
+    memset(&o->precision, 0, sizeof(*o) - offsetof(b2p_info, precision));
+    o->precision = h->cfg.precision; o->warps_per_block = DNT / 32; o->cols_per_tile = DT; o->n_tiles = h->dense->n_tiles;
+    o->grid_blocks = h->dense->n_tiles; o->blocks_per_sm = 1; o->n_sms = h->n_sms;
+    o->post_rounds = h->plan.rounds_post; o->pre_rounds = h->plan.rounds_pre; o->tree_depth = h->plan.tree_depth;
+    o->regs_per_thread = h->regs; o->smem_bytes = 5 * SP * SP * 8; o->device_bytes = h->device_bytes;
+    o->alg_bytes_loglik = (2 * N - 3) * U + N * P;
+    o->alg_bytes_grad = (5 * N - 9) * U + 2 * N * P;
+    return B2P_OK;
+  }
   o->precision = h->cfg.precision;
   o->warps_per_block = h->wg.nt / 32; o->cols_per_tile = h->wg.ct; o->n_tiles = h->wg.n_tiles;
   o->grid_blocks = h->wg.grid; o->blocks_per_sm = h->ctas_per_sm; o->n_sms = h->n_sms;
@@ -324,6 +513,7 @@ int b2p_get_info(const b2p_instance* h, b2p_info* o) {
 
 int b2p_set_topology(b2p_instance* h, const int32_t* h_triples) {
   if (!h || !h_triples) return h ? fail(h, B2P_ERR_ARG, "b2p_set_topology: null triples") : B2P_ERR_ARG;
+  if (h->dense) return dense_set_topology(h, h_triples);
   WalkPlan plan;
   std::string why;
   if (!plan_walk_auto(h->cfg.n_tips, h_triples, h->wg, plan, why))
@@ -357,6 +547,7 @@ int b2p_set_topology(b2p_instance* h, const int32_t* h_triples) {
 
 int b2p_set_tip_states(b2p_instance* h, const uint8_t* h_masks) {
   if (!h || !h_masks) return h ? fail(h, B2P_ERR_ARG, "b2p_set_tip_states: null masks") : B2P_ERR_ARG;
+  if (h->dense) return dense_set_tips(h, h_masks);  // bytes are state codes (>= n_states: missing)
   const int N = h->cfg.n_tips, P = h->cfg.n_patterns;
   const size_t n = (size_t)N * P;
   for (size_t i = 0; i < n; ++i)
@@ -370,6 +561,7 @@ int b2p_set_tip_states(b2p_instance* h, const uint8_t* h_masks) {
 
 int b2p_set_pattern_weights(b2p_instance* h, const double* h_weights) {
   if (!h || !h_weights) return h ? fail(h, B2P_ERR_ARG, "b2p_set_pattern_weights: null") : B2P_ERR_ARG;
+  if (h->dense) return dense_set_weights(h, h_weights);
   CU(cudaSetDevice(h->cfg.device));
   CU(cudaMemcpy(h->d_weights, h_weights, sizeof(double) * h->cfg.n_patterns, cudaMemcpyHostToDevice));
   h->have_weights = true;
@@ -380,6 +572,7 @@ int b2p_set_eigen(b2p_instance* h, const double* evec, const double* ivec, const
                   const double* freqs) {
   if (!h || !evec || !ivec || !evals || !freqs)
     return h ? fail(h, B2P_ERR_ARG, "b2p_set_eigen: null argument") : B2P_ERR_ARG;
+  if (h->dense) return dense_set_eigen(h, evec, ivec, evals, freqs);
   memcpy(h->model.evec, evec, sizeof(double) * 16);
   memcpy(h->model.ivec, ivec, sizeof(double) * 16);
   memcpy(h->model.evals, evals, sizeof(double) * 4);
@@ -411,9 +604,9 @@ static int eval_common(b2p_instance* h, const double* d_bl, double* d_logl, doub
   if (rc) return rc;
   if (!d_bl || !d_logl) return fail(h, B2P_ERR_ARG, "evaluation: null device pointer");
   cudaStream_t st = (cudaStream_t)stream;
-  cudaError_t e = (h->cfg.precision == B2P_PRECISION_F32)
-                      ? launch_eval<float>(h, d_bl, d_logl, d_grad, st)
-                      : launch_eval<double>(h, d_bl, d_logl, d_grad, st);
+  cudaError_t e = h->dense ? dense_launch(h, d_bl, d_logl, d_grad, st)
+                  : (h->cfg.precision == B2P_PRECISION_F32) ? launch_eval<float>(h, d_bl, d_logl, d_grad, st)
+                                                            : launch_eval<double>(h, d_bl, d_logl, d_grad, st);
   if (e != cudaSuccess) return fail(h, B2P_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
   return B2P_OK;
 }
@@ -505,6 +698,7 @@ int b2p_kernel_ms_stats(b2p_instance* h, double* total_ms, int32_t* n_launches) 
 int b2p_get_branch_partials(b2p_instance* h, int32_t node, double* h_out) {
   if (!h || !h_out) return B2P_ERR_ARG;
   const int N = h->cfg.n_tips;
+  if (h->dense) return fail(h, B2P_ERR_UNSUPPORTED, "b2p_get_branch_partials: 4-state instances only");
   if (node < N || node >= 2 * N - 2)
     return fail(h, B2P_ERR_ARG, "b2p_get_branch_partials: node %d is not an internal non-root node", node);
   const WalkGeometry& g = h->wg;

@@ -38,7 +38,8 @@ def grad_err(g, g_ref):
 
 def make_engine(w: Workload, precision=None, **kw):
     from b200phylo.engine import Engine
-    eng = Engine(w.n_tips, w.n_patterns, w.n_categories, precision=precision or w.precision, **kw)
+    eng = Engine(w.n_tips, w.n_patterns, w.n_categories, precision=precision or w.precision,
+                 n_states=getattr(w.patterns, "n_states", 4), **kw)
     eng.set_topology(w.tree.post_triples)
     eng.set_tip_states(w.patterns.masks)
     eng.set_pattern_weights(w.patterns.weights)

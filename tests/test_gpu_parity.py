@@ -150,11 +150,57 @@ def test_setup_errors_are_reported():
     with pytest.raises(EngineError, match="mask"):
         eng.set_tip_states(np.full((4, 8), 16, dtype=np.uint8))
     eng.close()
-    with pytest.raises(EngineError, match="4-state|n_states|unsupported"):
+    with pytest.raises(EngineError, match="4-state|n_states|unsupported|one rate category"):
         import ctypes
         from b200phylo import engine as E
         h = ctypes.c_void_p()
-        cfg = E._Config(4, 8, 1, 20, 64, 0, 0, 0)
+        cfg = E._Config(4, 8, 1, 200, 64, 0, 0, 0)
         rc = E.load_library().b2p_create(ctypes.byref(cfg), ctypes.byref(h))
         if rc != 0:
             raise EngineError(E.load_library().b2p_last_error(None).decode())
+
+
+# ---- dense-state path: 61-state codon model (BASELINE.json configs[4]) --------------------
+@pytest.mark.parametrize("n,p", [(2, 3), (12, 40), (60, 130), (150, 333)])
+def test_codon_parity(n, p):
+    """logL and branch gradient of the 61-state path against the numpy oracle (analytic
+    two-pass formulation, generic in the state count)."""
+    w = make_workload("codon_500x2000", n_tips=n, n_patterns=p)
+    assert w.patterns.n_states == 61
+    eng = make_engine(w)
+    try:
+        logl, grad = eng.loglik_grad_host(w.tree.branch_lengths)
+        logl_only, _ = eng.loglik_grad_host(w.tree.branch_lengths, want_grad=False)
+    finally:
+        eng.close()
+    ol, og = oracle_np(w)
+    assert rel_err(logl, ol) < TOL_LOGL_F64, (logl, ol)
+    assert rel_err(logl_only, ol) < TOL_LOGL_F64
+    assert grad_err(grad, og) < TOL_GRAD_F64
+
+
+def test_codon_missing_states_and_rescaling():
+    """Missing codons (code 255) are all-ones tips; a deep caterpillar tree underflows
+    61-state partials without rescaling (61^-400)."""
+    from b200phylo.alignment import simulate_patterns
+    base = make_workload("codon_500x2000", n_tips=8, n_patterns=8)
+    tree = simulate_tree(400, shape="caterpillar", seed=3, mean_branch=0.05)
+    # sequences evolved on the tree: with random codes the likelihood is dominated by the
+    # ~1e-9 entries of P (three-nucleotide changes), whose eigen-form rounding error makes
+    # any two implementations disagree at 1e-9 — an ill-conditioned input, not a parity case
+    pm = base.subst_model.p_t(tree.branch_lengths[:, None] * np.ones(1)[None, :])
+    sp = simulate_patterns(tree, pm, base.subst_model.freqs, 70, seed=9)
+    rng = np.random.default_rng(5)
+    codes = sp.masks.copy()
+    codes[rng.random(codes.shape) < 0.1] = 255
+    sp = SitePattern(sp.names, codes, sp.weights, 61)
+    w = Workload("codon_deep", tree, sp, base.subst_model, base.site_model)
+    eng = make_engine(w)
+    try:
+        logl, grad = eng.loglik_grad_host(w.tree.branch_lengths)
+    finally:
+        eng.close()
+    ol, og = oracle_np(w)
+    assert np.isfinite(logl) and logl < -1e4
+    assert rel_err(logl, ol) < TOL_LOGL_F64, (logl, ol)
+    assert grad_err(grad, og) < TOL_GRAD_F64

@@ -34,7 +34,8 @@ def main():
         t0 = time.time()
         w = make_workload(name, n_tips=nt, n_patterns=npat)
         t_gen = time.time() - t0
-        eng = Engine(w.n_tips, w.n_patterns, w.n_categories, precision=prec)
+        ns = getattr(w.patterns, 'n_states', 4)
+        eng = Engine(w.n_tips, w.n_patterns, w.n_categories, precision=prec, n_states=ns)
         eng.set_topology(w.tree.post_triples)
         eng.set_tip_states(w.patterns.masks)
         eng.set_pattern_weights(w.patterns.weights)
@@ -47,8 +48,13 @@ def main():
                 "gen_s": round(t_gen, 2), "logl": logl, "logl_evalonly": logl_e}
         if check:
             t0 = time.time()
-            ol, og = c_oracle.loglik_and_gradient(w.tree.post_triples, w.patterns.masks, w.patterns.weights,
-                                                  bl, *w.eigen_args())
+            if ns == 4:
+                ol, og = c_oracle.loglik_and_gradient(w.tree.post_triples, w.patterns.masks, w.patterns.weights,
+                                                      bl, *w.eigen_args())
+            else:
+                from oracle import oracle as np_oracle
+                ol, og = np_oracle.loglik_and_gradient(w.tree.post_triples, w.patterns.partials(), w.patterns.weights,
+                                                       bl, *w.eigen_args())
             line["oracle_s"] = round(time.time() - t0, 3)
             line["oracle_logl"] = ol
             line["rel_logl"] = abs(logl - ol) / abs(ol)
