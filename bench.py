@@ -125,16 +125,26 @@ def build_workload(name, precision, rank):
 
 def cpu_port_rate(w, seconds, n_threads=0, min_evals=3):
     """Timed C oracle (CPU port of the physher/BEAGLE-style analytic two-pass path)."""
-    from oracle import c_oracle
-    args = (w.tree.post_triples, w.patterns.masks, w.patterns.weights, w.tree.branch_lengths, *w.eigen_args())
-    c_oracle.loglik_and_gradient(*args, n_threads=n_threads)  # warm-up
+    fn, cores = cpu_port(w, n_threads)
+    fn()  # warm-up
     n, t0 = 0, time.perf_counter()
     while n < min_evals or time.perf_counter() - t0 < seconds:
-        logl, _ = c_oracle.loglik_and_gradient(*args, n_threads=n_threads)
+        logl, _ = fn()
         n += 1
     dt = time.perf_counter() - t0
-    cores = n_threads or c_oracle.max_threads()
     return n / dt, cores, n, dt, logl
+
+
+def cpu_port(w, n_threads=0):
+    """The CPU implementation of the path for this workload and the cores it uses: the C/OpenMP
+    port for 4-state models, the numpy restatement (BLAS threads) for dense-state models."""
+    if getattr(w.patterns, "n_states", 4) == 4:
+        from oracle import c_oracle
+        args = (w.tree.post_triples, w.patterns.masks, w.patterns.weights, w.tree.branch_lengths, *w.eigen_args())
+        return (lambda: c_oracle.loglik_and_gradient(*args, n_threads=n_threads)), (n_threads or c_oracle.max_threads())
+    from oracle import oracle
+    args = (w.tree.post_triples, w.patterns.partials(), w.patterns.weights, w.tree.branch_lengths, *w.eigen_args())
+    return (lambda: oracle.loglik_and_gradient(*args)), 1  # numpy einsum contractions: one core
 
 
 def run_reference(a):
@@ -145,15 +155,13 @@ def run_reference(a):
     if rank != 0:
         return 0
     w = build_workload(a.workload, a.precision, 0)
-    from oracle import c_oracle
-    args = (w.tree.post_triples, w.patterns.masks, w.patterns.weights, w.tree.branch_lengths, *w.eigen_args())
+    fn, cores = cpu_port(w)
     for _ in range(max(a.warmup, 1)):
-        c_oracle.loglik_and_gradient(*args)
+        fn()
     t0 = time.perf_counter()
     for _ in range(a.steps):
-        c_oracle.loglik_and_gradient(*args)
+        fn()
     dt = time.perf_counter() - t0
-    cores = c_oracle.max_threads()
     value = a.steps / dt
     unit = UNIT_FMT.format(n=w.n_tips, p=w.n_patterns)
     line = {
@@ -270,6 +278,7 @@ def run_b200(a):
         alg = info["alg_bytes_grad"]
         k_avg_ms = k_ms / max(k_n, 1)
         achieved = alg / (k_avg_ms * 1e-3) / 1e9
+        dense = info["n_states"] != 4
         unit = UNIT_FMT.format(n=w.n_tips, p=w.n_patterns)
         U = w.n_patterns * w.n_categories * 4 * (8 if a.precision == "float64" else 4)
         line = {
@@ -280,7 +289,7 @@ def run_b200(a):
             "config": {"workload": a.workload, "n_taxa": w.n_tips, "patterns_per_gpu": w.n_patterns,
                        "total_patterns": w.n_patterns * world, "categories": w.n_categories,
                        "model": type(w.subst_model).__name__, "tree": "coalescent, seed 20261104",
-                       "l2": f"no flush: per-step working set {(2 * (w.n_tips - 1) * U) / 1e6:.0f} MB of partials > 126 MB L2",
+                       "l2": f"no flush: per-step working set {(2 * (w.n_tips - 1) * U * info['n_states'] // 4) / 1e6:.0f} MB of partials > 126 MB L2",
                        "collective": "1 NCCL all-reduce of 2N-1 doubles per step" if world > 1 else "none",
                        "engine": {k: info[k] for k in ("warps_per_block", "cols_per_tile", "n_tiles", "grid_blocks",
                                                         "post_rounds", "pre_rounds", "tasks_per_round", "tree_depth",
@@ -297,11 +306,31 @@ def run_b200(a):
             "clocks": clocks,
             "logl": float(result_dev[0]),
         }
+        if dense:
+            # compute-bound; algorithmic flops per evaluation
+            # (N-1) P K (4S^2+S) + (2N-2) P K (6S^2+4S), against an fp64 matmul measured in this run
+            S, N_, P_, K_ = info["n_states"], w.n_tips, w.n_patterns, w.n_categories
+            flops = (N_ - 1) * P_ * K_ * (4 * S * S + S) + (2 * N_ - 2) * P_ * K_ * (6 * S * S + 4 * S)
+            a_ = torch.randn(4096, 4096, dtype=torch.float64, device=dev)
+            best = 1e9
+            for _ in range(5):
+                m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                m0.record(); torch.matmul(a_, a_); m1.record(); torch.cuda.synchronize()
+                best = min(best, m0.elapsed_time(m1))
+            peak_tf = 2 * 4096 ** 3 / (best * 1e-3) / 1e12
+            ach_tf = flops / (k_avg_ms * 1e-3) / 1e12
+            line["dtype"] = "f64"
+            line["gpu_launches"] = (2 + info["post_rounds"] + info["pre_rounds"] + 1) * a.steps
+            line["roofline"] = {"bound": "tensor", "kernel": "dense_post_kernel + dense_pre_kernel (one launch per tree level)",
+                                "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf, "traffic": None,
+                                "alg_flops_per_eval": flops, "kernel_ms": k_avg_ms, "launches_timed": k_n,
+                                "peak_source": "fp64 torch.matmul 4096^3 (cuBLAS DGEMM), best of 5, measured in this run"}
         if not a.no_cpu_baseline:
             rate, cores, n, secs, logl_cpu = cpu_port_rate(w, a.cpu_seconds)
-            rate1, _, n1, secs1, _ = cpu_port_rate(w, min(a.cpu_seconds, 5.0), n_threads=1, min_evals=2)
+            rate1 = rate if dense else cpu_port_rate(w, min(a.cpu_seconds, 5.0), n_threads=1, min_evals=2)[0]
             line["cpu_baseline"] = {"value": rate, "unit": unit, "cores": cores, "kind": "port",
-                                    "sample": f"{n} full evaluations of the same workload in {secs:.1f} s (C oracle, OpenMP)",
+                                    "sample": f"{n} full evaluations of the same workload in {secs:.1f} s "
+                                              + ("(numpy restatement, one core)" if dense else "(C oracle, OpenMP)"),
                                     "single_core_value": rate1,
                                     "logl_rel_diff_vs_gpu": abs(logl_cpu - result_dev[0]) / abs(logl_cpu) if world == 1 else None}
         print(json.dumps(line), flush=True)
