@@ -50,7 +50,8 @@ typedef struct b2p_config {
   int32_t n_tips;       /* N >= 2 */
   int32_t n_patterns;   /* P >= 1 (this rank's slice when sharded) */
   int32_t n_categories; /* K >= 1 rate categories, K <= 32 */
-  int32_t n_states;     /* 4 (nucleotide); other sizes: B2P_ERR_UNSUPPORTED */
+  int32_t n_states;     /* 4 (nucleotide walk kernel) or 5..64 (dense-state path, e.g. 61 codons:
+                           one rate category, fp64) */
   int32_t precision;    /* B2P_PRECISION_F64 | B2P_PRECISION_F32 (partials / matrices) */
   int32_t device;       /* CUDA device ordinal */
   int32_t warps_per_block; /* 0 = auto; threads per CTA / 32 (32, 24, 16 or 8) */
@@ -98,7 +99,8 @@ int b2p_get_info(const b2p_instance* h, b2p_info* out);
 int b2p_set_topology(b2p_instance* h, const int32_t* h_triples);
 
 /* Tip data: h_masks uint8 [N][P], bit i set = state i compatible (A=1,C=2,G=4,T=8;
- * gap/N = 15).  Fed by "site_pattern" (/root/reference/flu_H3N2/phylotorch-JC69.template:59-69,
+ * gap/N = 15).  For n_states > 4 the bytes are state CODES (0..n_states-1; any other
+ * value = missing data).  Fed by "site_pattern" (/root/reference/flu_H3N2/phylotorch-JC69.template:59-69,
  * /root/reference/flu_H3N2/physher-JC69.template:11-21).  BEAGLE: beagleSetTipStates /
  * beagleSetTipPartials. */
 int b2p_set_tip_states(b2p_instance* h, const uint8_t* h_masks);
@@ -107,7 +109,7 @@ int b2p_set_tip_states(b2p_instance* h, const uint8_t* h_masks);
 int b2p_set_pattern_weights(b2p_instance* h, const double* h_weights);
 
 /* Substitution model as an eigen system Q = V diag(lambda) V^-1, row-major [S][S],
- * plus stationary frequencies [S].  Fed by "substitution_model"
+ * plus stationary frequencies [S] (S = n_states).  Fed by "substitution_model"
  * (/root/reference/flu_H3N2/phylotorch-JC69.template:70-73) and `--gtr`
  * (/root/reference/modules/micro.nf:52).  BEAGLE: beagleSetEigenDecomposition +
  * beagleSetStateFrequencies. */
