@@ -207,7 +207,6 @@ __global__ void __launch_bounds__(DNT, 1) dense_pre_kernel(const DenseParams p, 
   const DenseNode nd = nodes[blockIdx.x];
   const int col0 = blockIdx.y * DT, t = threadIdx.x;
   const int ti = t & 15, tc = t >> 4;
-  const bool int_l = nd.l >= p.n_tips, int_r = nd.r >= p.n_tips;
   for (int e = t; e < SP * DT; e += DNT) {
     const int k = e / DT, c = e % DT;
     const double ml = child_message(p, nd.l, k, col0 + c), mr = child_message(p, nd.r, k, col0 + c);
