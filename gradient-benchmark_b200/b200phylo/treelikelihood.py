@@ -34,7 +34,7 @@ from .substitution import GTR, HKY, JC69, SubstitutionModel
 from .tree import Tree
 
 __all__ = ["TreeLikelihoodModel", "TreeLikelihoodFunction", "UnrootedTreeModel",
-           "StrictClockModel", "Parameter"]
+           "StrictClockModel", "Parameter", "TransformedParameter"]
 
 
 class Parameter:
@@ -51,6 +51,34 @@ class Parameter:
     @requires_grad.setter
     def requires_grad(self, flag: bool) -> None:
         self.tensor.requires_grad_(flag)
+
+
+class TransformedParameter:
+    """``transform(x)`` of an unconstrained ``Parameter`` — the reference's JSON wraps ratios
+    in a sigmoid and the root height in an affine shift
+    (/root/reference/flu_H3N2/phylotorch-JC69.template:17-42)."""
+
+    _TRANSFORMS = {
+        "SigmoidTransform": lambda x, kw: torch.sigmoid(x),
+        "ExpTransform": lambda x, kw: torch.exp(x),
+        "AffineTransform": lambda x, kw: kw.get("loc", 0.0) + kw.get("scale", 1.0) * x,
+    }
+
+    def __init__(self, id_: Optional[str], x: Parameter, transform: str, parameters: Optional[dict] = None):
+        name = transform.split(".")[-1]
+        if name not in self._TRANSFORMS:
+            raise ValueError(f"unsupported transform {transform!r}")
+        self.id = id_
+        self.x = x
+        self._fn = self._TRANSFORMS[name]
+        self._kw = dict(parameters or {})
+
+    @property
+    def tensor(self) -> torch.Tensor:
+        return self._fn(self.x.tensor, self._kw)
+
+    def parameters(self):
+        return [self.x]
 
 
 class UnrootedTreeModel:
@@ -200,6 +228,8 @@ class TreeLikelihoodModel:
 
     # ---------------------------------------------------------------- evaluation
     def _scaled_branch_lengths(self) -> torch.Tensor:
+        if self.clock_model is not None and getattr(self.tree_model, "fuses_clock_rate", False):
+            return self.tree_model.branch_lengths(rate=self.clock_model.rates)
         bl = self.tree_model.branch_lengths()
         if self.clock_model is not None:
             bl = self.clock_model.rates * bl
@@ -248,7 +278,7 @@ class TreeLikelihoodModel:
             return obj
 
         site_pattern = resolve("site_pattern", lambda s: _site_pattern_from_json(s, dic))
-        tree_model = resolve("tree_model", lambda s: _tree_model_from_json(s, dic, site_pattern))
+        tree_model = resolve("tree_model", lambda s: _tree_model_from_json(s, dic, site_pattern, data.get("device")))
         subst_model = resolve("substitution_model", _subst_model_from_json)
         site_model = resolve("site_model", _site_model_from_json, required=False)
         clock_model = resolve("branch_model", _clock_from_json, required=False)
@@ -281,7 +311,25 @@ def _site_pattern_from_json(spec, dic) -> SitePattern:
     return compress_alignment(Alignment([s["taxon"] for s in seqs], [s["sequence"] for s in seqs]))
 
 
-def _tree_model_from_json(spec, dic, site_pattern: SitePattern):
+def _parameter_from_json(spec, dic, device=None):
+    """``Parameter`` / ``TransformedParameter`` objects of the reference JSON (or an id)."""
+    if isinstance(spec, str):
+        return dic[spec]
+    kind = (spec.get("type") or "Parameter").split(".")[-1] if isinstance(spec, dict) else "Parameter"
+    if kind == "TransformedParameter":
+        obj = TransformedParameter(spec.get("id"), _parameter_from_json(spec["x"], dic, device), spec["transform"],
+                                   spec.get("parameters"))
+    else:
+        t = _tensor_from_json(spec)
+        if device is not None:
+            t = t.to(device)
+        obj = Parameter(spec.get("id") if isinstance(spec, dict) else None, t)
+    if isinstance(spec, dict) and "id" in spec:
+        dic[spec["id"]] = obj
+    return obj
+
+
+def _tree_model_from_json(spec, dic, site_pattern: SitePattern, device=None):
     newick = spec.get("newick")
     if newick is None and "file" in spec:
         with open(spec["file"]) as fh:
@@ -289,6 +337,13 @@ def _tree_model_from_json(spec, dic, site_pattern: SitePattern):
     if newick is None:
         raise KeyError("tree_model JSON needs 'newick' or 'file'")
     tree = Tree.from_newick(newick, taxa=list(site_pattern.names))
+    if (spec.get("type") or "").split(".")[-1] == "ReparameterizedTimeTreeModel":
+        from .timetree import ReparameterizedTimeTreeModel
+        dev = device if device is not None else (torch.cuda.current_device() if torch.cuda.is_available() else 0)
+        cuda = torch.device(f"cuda:{dev}")
+        ratios = _parameter_from_json(spec["ratios"], dic, cuda) if "ratios" in spec else None
+        root_height = _parameter_from_json(spec["root_height"], dic, cuda) if "root_height" in spec else None
+        return ReparameterizedTimeTreeModel(spec.get("id"), tree, None, ratios, root_height, device=dev)
     bl = None
     if "branch_lengths" in spec:
         bl = _tensor_from_json(spec["branch_lengths"])

@@ -1,0 +1,294 @@
+// Time-tree kernels (sm_100a): node heights from ratios / root height, the log-Jacobian of
+// that map, branch lengths from heights, the constant-size coalescent — values and vector-
+// Jacobian products.  SURVEY.md §8(f) rows 1-2; the functions the reference's micro benchmark
+// times next to the tree likelihood (/root/reference/plot.Rmd:49-60).
+//
+// These are O(N) functions of a few thousand doubles: latency-bound, not bandwidth-bound.
+// What matters is (i) one launch per function, no host round trip, so they chain with the
+// likelihood kernels on one stream, and (ii) a short dependent chain.  The height recursion
+// h_i = b_i + r_i (h_parent - b_i) depends on the parent, so nodes are laid out by depth
+// ("level order", parents before children) and a single CTA walks the levels with all of a
+// node's operands staged in shared memory.  Real time trees are ladder-like: most levels
+// hold a handful of nodes.  Runs of levels no wider than a warp are walked by warp 0 alone
+// with __syncwarp between levels (one __syncthreads per run instead of one per level).
+//
+// Arithmetic uses the non-contracting intrinsics so results match the CPU restatement
+// (oracle/timetree_oracle.py) bit for bit where the summation order is the same.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b2p {
+
+constexpr int TT_NT = 512;  // threads of the single-CTA kernels
+
+// One run of levels.  narrow: every level in [lvl_begin, lvl_end) has <= 32 nodes.
+struct TTSegment { int lvl_begin, lvl_end, narrow, pad; };
+
+struct TTDev {
+  int n_tips, n_int;        // N, M = N-1
+  int n_levels, n_segments;
+  int in_smem;              // level arrays fit shared memory
+  // level order (position idx = 0..M-1, root at 0)
+  const int* node;          // [M] internal index i = node id - N
+  const int* ppos;          // [M] position of the parent (-1: root)
+  const int* kpos;          // [M][2] positions of the internal children, lower node id first (-1: tip)
+  const double* bound_l;    // [M] b_i in level order
+  const int* lvl_off;       // [n_levels + 1]
+  const TTSegment* seg;     // [n_segments]
+  // node order
+  const int* parent_all;    // [2N-2] node id of the parent
+  const int* kids;          // [M][2] node ids of the children, lower id first
+  const double* bound;      // [M]
+  const double* tip_h;      // [N]
+  const double* tip_sorted; // [N] ascending
+  const int* tip_rank;      // [N] rank of tip in (height, id) order
+  // scratch
+  double* work;             // [5 M + 2] fallback for the level arrays when they do not fit shared memory
+  double* ev_t;             // [2N-1] coalescent: event times by rank
+  double* ev_c;             // [2N-1] coalescent: C(k, 2) after the event, by rank
+  unsigned* ticket;         // coalescent: CTA completion counter
+};
+
+__device__ __forceinline__ double tt_block_sum(double v, double* red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double s = 0.0;
+  const int nw = (blockDim.x + 31) >> 5;
+  for (int w = 0; w < nw; ++w) s += red[w];  // every thread, same order
+  return s;
+}
+
+// ------------------------------------------------------------------------- node heights
+// params [M]: ratios of nodes N..2N-3, root height last.  heights [M] in node order.
+__global__ void __launch_bounds__(TT_NT) tt_heights_kernel(const TTDev t, const double* __restrict__ params,
+                                                          double* __restrict__ heights) {
+  extern __shared__ __align__(16) unsigned char tt_sm[];
+  const int M = t.n_int, tid = threadIdx.x;
+  double* h = t.in_smem ? reinterpret_cast<double*>(tt_sm) : t.work;
+  double* r = h + M;
+  double* b = r + M;
+  int* pp = reinterpret_cast<int*>(b + M);
+  int* off = pp + M;
+  for (int i = tid; i < M; i += TT_NT) {
+    r[i] = params[t.node[i]];
+    b[i] = t.bound_l[i];
+    pp[i] = t.ppos[i];
+  }
+  for (int i = tid; i <= t.n_levels; i += TT_NT) off[i] = t.lvl_off[i];
+  __syncthreads();
+  for (int s = 0; s < t.n_segments; ++s) {
+    const TTSegment sg = t.seg[s];
+    if (sg.narrow) {
+      if (tid < 32) {
+        int idx = off[sg.lvl_begin] + tid;
+        bool on = idx < off[sg.lvl_begin + 1];
+        double ri = on ? r[idx] : 0.0, bi = on ? b[idx] : 0.0;
+        int pi = on ? pp[idx] : -1;
+        for (int l = sg.lvl_begin; l < sg.lvl_end; ++l) {
+          const int cur = idx;
+          const bool con = on;
+          const double rc = ri, bc = bi;
+          const int pc = pi;
+          if (l + 1 < sg.lvl_end) {  // operands of the next level: independent of this level's result
+            idx = off[l + 1] + tid;
+            on = idx < off[l + 2];
+            ri = on ? r[idx] : 0.0; bi = on ? b[idx] : 0.0; pi = on ? pp[idx] : -1;
+          }
+          if (con) h[cur] = pc < 0 ? rc : __dadd_rn(bc, __dmul_rn(rc, __dsub_rn(h[pc], bc)));
+          __syncwarp();
+        }
+      }
+    } else {
+      for (int idx = off[sg.lvl_begin] + tid; idx < off[sg.lvl_end]; idx += TT_NT) {
+        const int pc = pp[idx];
+        const double bc = b[idx];
+        h[idx] = pc < 0 ? r[idx] : __dadd_rn(bc, __dmul_rn(r[idx], __dsub_rn(h[pc], bc)));
+      }
+    }
+    __syncthreads();
+  }
+  for (int i = tid; i < M; i += TT_NT) heights[t.node[i]] = h[i];
+}
+
+// J^T g: grad_params[i] = a_i (h_parent - b_i), a_i = g_i + sum over internal children r_c a_c.
+__global__ void __launch_bounds__(TT_NT) tt_heights_vjp_kernel(const TTDev t, const double* __restrict__ params,
+                                                              const double* __restrict__ heights,
+                                                              const double* __restrict__ grad_heights,
+                                                              double* __restrict__ grad_params) {
+  extern __shared__ __align__(16) unsigned char tt_sm[];
+  const int M = t.n_int, tid = threadIdx.x;
+  double* a = t.in_smem ? reinterpret_cast<double*>(tt_sm) : t.work;
+  double* w = a + M;  // r_i a_i
+  double* r = w + M;
+  int2* kp = reinterpret_cast<int2*>(r + M);
+  int* off = reinterpret_cast<int*>(kp + M);
+  for (int i = tid; i < M; i += TT_NT) {
+    const int nd = t.node[i];
+    a[i] = grad_heights[nd];
+    r[i] = t.ppos[i] < 0 ? 0.0 : params[nd];
+    kp[i] = reinterpret_cast<const int2*>(t.kpos)[i];
+  }
+  for (int i = tid; i <= t.n_levels; i += TT_NT) off[i] = t.lvl_off[i];
+  __syncthreads();
+  for (int s = t.n_segments - 1; s >= 0; --s) {
+    const TTSegment sg = t.seg[s];
+    if (sg.narrow) {
+      if (tid < 32) {
+        for (int l = sg.lvl_end - 1; l >= sg.lvl_begin; --l) {
+          const int idx = off[l] + tid;
+          if (idx < off[l + 1]) {
+            const int2 k = kp[idx];
+            double v = a[idx];
+            if (k.x >= 0) v = __dadd_rn(v, w[k.x]);
+            if (k.y >= 0) v = __dadd_rn(v, w[k.y]);
+            a[idx] = v;
+            w[idx] = __dmul_rn(r[idx], v);
+          }
+          __syncwarp();
+        }
+      }
+    } else {
+      for (int idx = off[sg.lvl_begin] + tid; idx < off[sg.lvl_end]; idx += TT_NT) {
+        const int2 k = kp[idx];
+        double v = a[idx];
+        if (k.x >= 0) v = __dadd_rn(v, w[k.x]);
+        if (k.y >= 0) v = __dadd_rn(v, w[k.y]);
+        a[idx] = v;
+        w[idx] = __dmul_rn(r[idx], v);
+      }
+    }
+    __syncthreads();
+  }
+  for (int i = tid; i < M; i += TT_NT) {
+    const int nd = t.node[i], pp = t.ppos[i];
+    grad_params[nd] = pp < 0 ? a[i] : __dmul_rn(a[i], __dsub_rn(heights[t.node[pp]], t.bound_l[i]));
+  }
+}
+
+// ------------------------------------------------------------------------ log-Jacobian
+// logj = sum_{i != root} log(h_parent(i) - b_i);  grad[j] = sum_{internal children c} 1/(h_j - b_c)
+__global__ void __launch_bounds__(TT_NT) tt_log_jacobian_kernel(const TTDev t, const double* __restrict__ heights,
+                                                               double* __restrict__ logj, double* __restrict__ grad) {
+  __shared__ double red[TT_NT / 32];
+  const int M = t.n_int, N = t.n_tips;
+  double s = 0.0;
+  for (int i = threadIdx.x; i < M; i += TT_NT) {
+    if (i < M - 1) s += log(heights[t.parent_all[N + i] - N] - t.bound[i]);
+    if (grad) {
+      const int2 k = reinterpret_cast<const int2*>(t.kids)[i];
+      const double hj = heights[i];
+      double g = 0.0;
+      if (k.x >= N) g = __dadd_rn(g, __drcp_rn(__dsub_rn(hj, t.bound[k.x - N])));
+      if (k.y >= N) g = __dadd_rn(g, __drcp_rn(__dsub_rn(hj, t.bound[k.y - N])));
+      grad[i] = g;
+    }
+  }
+  s = tt_block_sum(s, red);
+  if (threadIdx.x == 0 && logj) *logj = s;
+}
+
+// ---------------------------------------------------------------------- branch lengths
+// bl[c] = rate (h_parent(c) - h_c); rate may be null (1).
+__global__ void tt_branch_lengths_kernel(const TTDev t, const double* __restrict__ heights,
+                                         const double* __restrict__ rate, double* __restrict__ bl) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x, N = t.n_tips;
+  if (c >= 2 * N - 2) return;
+  const double rt = rate ? *rate : 1.0;
+  const double hc = c < N ? t.tip_h[c] : heights[c - N];
+  bl[c] = __dmul_rn(rt, __dsub_rn(heights[t.parent_all[c] - N], hc));
+}
+
+// grad_heights[j] = rate (g[k0] + g[k1] - g[j]);  grad_rate = sum_c g[c] (h_parent - h_c)
+__global__ void __launch_bounds__(TT_NT) tt_branch_lengths_vjp_kernel(const TTDev t, const double* __restrict__ heights,
+                                                                     const double* __restrict__ rate,
+                                                                     const double* __restrict__ grad_bl,
+                                                                     double* __restrict__ grad_heights,
+                                                                     double* __restrict__ grad_rate) {
+  __shared__ double red[TT_NT / 32];
+  const int M = t.n_int, N = t.n_tips;
+  const double rt = rate ? *rate : 1.0;
+  double s = 0.0;
+  for (int i = threadIdx.x; i < M; i += TT_NT) {
+    const int2 k = reinterpret_cast<const int2*>(t.kids)[i];
+    const double hj = heights[i];
+    const double g0 = grad_bl[k.x], g1 = grad_bl[k.y];
+    double g = __dadd_rn(__dmul_rn(rt, g0), __dmul_rn(rt, g1));
+    if (i < M - 1) g = __dsub_rn(g, __dmul_rn(rt, grad_bl[N + i]));
+    if (grad_heights) grad_heights[i] = g;
+    const double h0 = k.x < N ? t.tip_h[k.x] : heights[k.x - N];
+    const double h1 = k.y < N ? t.tip_h[k.y] : heights[k.y - N];
+    s += g0 * (hj - h0) + g1 * (hj - h1);
+  }
+  s = tt_block_sum(s, red);
+  if (threadIdx.x == 0 && grad_rate) *grad_rate = s;
+}
+
+// ------------------------------------------------------------------ constant coalescent
+// Events (all 2N-1 nodes) are ranked by (height, tips before internal nodes, id) by counting:
+// 8 lanes per event share the scan over the internal heights.  Each event writes its time and
+// C(k,2) after it at its rank; the last CTA to finish sums the intervals
+//   logp = -(1/theta) sum_j C_j (t_{j+1} - t_j) - (N-1) log theta.
+// grad_heights[e] = -(k_e - 1)/theta (k_e lineages just before the merge), grad_theta = S/theta^2 - (N-1)/theta.
+constexpr int TTC_NT = 256, TTC_LANES = 8, TTC_EV = TTC_NT / TTC_LANES;
+
+__global__ void __launch_bounds__(TTC_NT) tt_coalescent_kernel(const TTDev t, const double* __restrict__ heights,
+                                                              const double* __restrict__ theta_p,
+                                                              double* __restrict__ logp, double* __restrict__ grad_heights,
+                                                              double* __restrict__ grad_theta) {
+  __shared__ double red[TTC_NT / 32];
+  __shared__ unsigned last;
+  const int N = t.n_tips, M = t.n_int, E = 2 * N - 1;
+  const int sub = threadIdx.x & (TTC_LANES - 1);
+  const int e = blockIdx.x * TTC_EV + threadIdx.x / TTC_LANES;
+  const double theta = *theta_p;
+  const bool live = e < E, internal = e >= N;
+  const double te = !live ? 0.0 : internal ? heights[e - N] : t.tip_h[e];
+  const int self = e - N;
+  int below = 0;  // internal nodes ordered before this event
+  if (live && internal) {
+    for (int j = sub; j < M; j += TTC_LANES) {
+      const double hj = heights[j];
+      below += (hj < te || (hj == te && j < self)) ? 1 : 0;
+    }
+  } else if (live) {
+    for (int j = sub; j < M; j += TTC_LANES) below += heights[j] < te ? 1 : 0;
+  }
+#pragma unroll
+  for (int o = TTC_LANES / 2; o > 0; o >>= 1) below += __shfl_xor_sync(0xffffffffu, below, o);
+  if (live && sub == 0) {
+    int tips_before;
+    if (internal) {  // tips with height <= te
+      int lo = 0, hi = N;
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if (t.tip_sorted[mid] <= te) lo = mid + 1; else hi = mid; }
+      tips_before = lo;
+    } else {
+      tips_before = t.tip_rank[e];
+    }
+    const int k_before = tips_before - below;
+    const int k_after = internal ? k_before - 1 : k_before + 1;
+    const int rank = tips_before + below;
+    t.ev_t[rank] = te;
+    t.ev_c[rank] = 0.5 * (double)k_after * (double)(k_after - 1);
+    if (internal && grad_heights) grad_heights[self] = -(double)(k_before - 1) / theta;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) last = atomicAdd(t.ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  double s = 0.0;
+  for (int j = threadIdx.x; j < E - 1; j += TTC_NT) s += __ldcg(t.ev_c + j) * (__ldcg(t.ev_t + j + 1) - __ldcg(t.ev_t + j));
+  s = tt_block_sum(s, red);
+  if (threadIdx.x == 0) {
+    if (logp) *logp = -s / theta - (double)(N - 1) * log(theta);
+    if (grad_theta) *grad_theta = s / (theta * theta) - (double)(N - 1) / theta;
+    *t.ticket = 0u;  // ready for the next launch on this stream
+  }
+}
+
+}  // namespace b2p

@@ -154,6 +154,57 @@ int b2p_kernel_ms_stats(b2p_instance* h, double* total_ms, int32_t* n_launches);
  * by a power of two per pattern), as double [P][K][S] into h_out.  BEAGLE: beagleGetPartials. */
 int b2p_get_branch_partials(b2p_instance* h, int32_t node, double* h_out);
 
+/* ------------------------------------------------------------------------------------
+ * Time trees: the functions the micro benchmark times next to
+ * the tree likelihood — ratio_transform, ratio_transform_jacobian, coalescent
+ * (/root/reference/plot.Rmd:49-60) — and the pieces the macro model chains in front of it:
+ * ReparameterizedTimeTreeModel ratios / root height -> node heights -> branch lengths x
+ * strict-clock rate (/root/reference/flu_H3N2/phylotorch-JC69.template:14-58), constant
+ * coalescent prior (:75-100).  In torchtree these are GeneralNodeHeightTransform and
+ * ConstantCoalescent (Python loops over nodes / a sort); physher has them in C behind
+ * "reparam" / "include_jacobian" (/root/reference/flu_H3N2/physher-JC69.template:9,43-44).
+ *
+ * A b2p_timetree holds one dated topology on one device.  Vectors:
+ *   params  [N-1]  ratios of internal nodes N..2N-3 (each in [0,1]), then the root height
+ *   heights [N-1]  heights of internal nodes N..2N-2 (time before the most recent tip)
+ *   bl      [2N-2] branch lengths by child node id, as b2p_loglik takes them
+ * Every evaluation call is one kernel launch on `cuda_stream`, asynchronous, device
+ * pointers only (all fp64), no hidden synchronisation; calls on one handle must be issued
+ * to one stream at a time (they share scratch).  *_vjp calls return J^T g for an upstream
+ * gradient g (what autograd's backward needs). */
+typedef struct b2p_timetree b2p_timetree;
+
+/* h_triples as in b2p_set_topology; h_tip_heights [N] >= 0 (sampling dates as heights). */
+int b2p_timetree_create(int32_t n_tips, const int32_t* h_triples, const double* h_tip_heights,
+                        int32_t device, b2p_timetree** out);
+int b2p_timetree_destroy(b2p_timetree* t);
+const char* b2p_timetree_last_error(const b2p_timetree* t);
+/* tree depth in levels, runs of levels the height kernels walk, 1 if they run out of shared memory */
+int b2p_timetree_get_info(const b2p_timetree* t, int32_t* n_levels, int32_t* n_segments, int32_t* in_smem);
+
+/* ratio_transform: h_root = params[N-2]; h_i = b_i + r_i (h_parent(i) - b_i), b_i = latest
+ * sampling height below i. */
+int b2p_timetree_heights(b2p_timetree* t, const double* d_params, double* d_heights, void* cuda_stream);
+/* d_grad_params [N-1] = (d heights / d params)^T d_grad_heights; d_heights = output of the call above. */
+int b2p_timetree_heights_vjp(b2p_timetree* t, const double* d_params, const double* d_heights,
+                             const double* d_grad_heights, double* d_grad_params, void* cuda_stream);
+/* ratio_transform_jacobian: *d_logj = sum_{i != root} log(h_parent(i) - b_i); d_grad_heights [N-1]
+ * its gradient w.r.t. the internal heights.  Either output may be NULL. */
+int b2p_timetree_log_jacobian(b2p_timetree* t, const double* d_heights, double* d_logj,
+                              double* d_grad_heights, void* cuda_stream);
+/* bl[c] = rate (h_parent(c) - h_c); d_rate points at one double on the device, NULL = 1. */
+int b2p_timetree_branch_lengths(b2p_timetree* t, const double* d_heights, const double* d_rate,
+                                double* d_bl, void* cuda_stream);
+/* d_grad_heights [N-1] and *d_grad_rate from d_grad_bl [2N-2]; either output may be NULL. */
+int b2p_timetree_branch_lengths_vjp(b2p_timetree* t, const double* d_heights, const double* d_rate,
+                                    const double* d_grad_bl, double* d_grad_heights,
+                                    double* d_grad_rate, void* cuda_stream);
+/* coalescent (constant population size theta = *d_theta): log density of the node heights,
+ * gradient w.r.t. the internal heights [N-1] and w.r.t. theta.  Outputs may be NULL. */
+int b2p_coalescent_constant(b2p_timetree* t, const double* d_heights, const double* d_theta,
+                            double* d_logp, double* d_grad_heights, double* d_grad_theta,
+                            void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -20,7 +20,9 @@ def test_header_declares_expected_entry_points():
     syms = _declared_symbols()
     for s in ("b2p_create", "b2p_destroy", "b2p_set_topology", "b2p_set_tip_states",
               "b2p_set_pattern_weights", "b2p_set_eigen", "b2p_set_categories", "b2p_loglik",
-              "b2p_loglik_grad", "b2p_loglik_grad_host", "b2p_last_error"):
+              "b2p_loglik_grad", "b2p_loglik_grad_host", "b2p_last_error", "b2p_timetree_create",
+              "b2p_timetree_heights", "b2p_timetree_heights_vjp", "b2p_timetree_log_jacobian",
+              "b2p_timetree_branch_lengths", "b2p_coalescent_constant"):
         assert s in syms
 
 
@@ -30,7 +32,8 @@ def test_library_builds_loads_and_exports_every_declared_symbol():
     lib = engine.load_library()
     for s in _declared_symbols():
         assert hasattr(lib, s), f"{s} declared in include/b200phylo.h but not exported"
-    assert set(_declared_symbols()) == set(engine.EXPORTED_SYMBOLS)
+    from b200phylo.timetree import TIMETREE_SYMBOLS
+    assert set(_declared_symbols()) == set(engine.EXPORTED_SYMBOLS) | set(TIMETREE_SYMBOLS)
     assert lib.b2p_version() >= 1
 
 
@@ -68,3 +71,15 @@ def test_product_code_never_imports_oracle():
                 src = open(os.path.join(d, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle", src, flags=re.M), f
                 assert "phylo_oracle" not in src, f
+
+
+def test_timetree_create_fails_loudly_without_gpu():
+    import numpy as np
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from b200phylo.engine import EngineError
+    from b200phylo.timetree import TimeTreeEngine
+    tr = np.array([[3, 0, 1], [4, 2, 3]], dtype=np.int32)
+    with pytest.raises(EngineError, match="no CUDA device|no CPU fallback"):
+        TimeTreeEngine(tr, np.zeros(3))
