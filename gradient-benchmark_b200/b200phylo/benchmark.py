@@ -12,6 +12,11 @@ the pipeline's awk (/root/reference/modules/micro.nf:54-56), yields the columns
 Rows: ``treelikelihoodJC69,{evaluation,gradient},off,<seconds for all replicates>``
 and, with ``--gtr``, ``treelikelihoodGTR,...`` (/root/reference/plot.Rmd:262,305).
 
+When the tip labels carry sampling dates (``name_date``, /root/reference/bin/helper.py:28-47)
+the time-tree functions of the micro benchmark are timed too
+(/root/reference/plot.Rmd:49-60,301-303): ``ratio_transform``, ``ratio_transform_jacobian``
+and ``coalescent`` x ``evaluation|gradient``.
+
 Like the other contenders each replicate is one call of the public model object: branch
 lengths in, log-likelihood (and ``backward()`` for the gradient rows) out.  Branch
 lengths live on the GPU across replicates, as torchtree's parameters live in torch
@@ -32,6 +37,7 @@ import torch
 from .alignment import compress_alignment, read_fasta
 from .sitemodel import ConstantSiteModel
 from .substitution import GTR, JC69
+from .timetree import (ConstantCoalescentModel, ReparameterizedTimeTreeModel, tip_heights_from_names)
 from .tree import Tree
 from .treelikelihood import TreeLikelihoodModel, UnrootedTreeModel
 
@@ -52,6 +58,12 @@ def run_benchmark(fasta: str, newick: str, replicates: int, scaler: float, gtr: 
     aln = read_fasta(fasta)
     with open(newick) as fh:
         tree = Tree.from_newick(fh.read(), taxa=aln.names)
+    time_tree = tree
+    try:
+        tip_heights_from_names(tree.names)
+        dated = True
+    except ValueError:
+        dated = False
     tree = tree.scaled(scaler)
     sp = compress_alignment(aln)
     dev = torch.device(f"cuda:{device}")
@@ -91,8 +103,62 @@ def run_benchmark(fasta: str, newick: str, replicates: int, scaler: float, gtr: 
                      "logl": logl, "alg_bytes": info["alg_bytes_grad"],
                      "grad_norm": float(bl.grad.norm())})
         model.close()
+    if dated:
+        rows += run_time_functions(time_tree, replicates, device, warmup)
     for r in rows:
         r.update(n_taxa=tree.n_tips, n_patterns=sp.n_patterns, replicates=replicates, dtype=dtype)
+    return rows
+
+
+def run_time_functions(tree: Tree, replicates: int, device: int = 0, warmup: int = 3) -> List[dict]:
+    """ratio_transform (ratios/root height -> internal heights, derivatives w.r.t. ratios),
+    ratio_transform_jacobian (heights -> log|det J|, derivatives w.r.t. heights) and coalescent
+    (heights + population size -> log density, derivatives w.r.t. both)
+    (/root/reference/plot.Rmd:49-60).  One kernel launch per evaluation, one more per gradient."""
+    tm = ReparameterizedTimeTreeModel("tree", tree, None, device=device)
+    dev = torch.device(f"cuda:{device}")
+    ratios, root = tm.ratios, tm.root_height
+    heights = tm.heights().detach()
+    theta = torch.tensor([4.0], dtype=torch.float64, device=dev)
+    coal = ConstantCoalescentModel("coalescent", tm, theta)
+    ones = torch.ones_like(heights)
+    rows = []
+
+    def both(fname, evaluation, gradient, leaves):
+        for x in leaves:
+            x.requires_grad_(False)
+        for _ in range(warmup):
+            evaluation()
+        t_eval = _time_loop(evaluation, replicates)
+        for x in leaves:
+            x.requires_grad_(True)
+        for _ in range(warmup):
+            gradient()
+        t_grad = _time_loop(gradient, replicates)
+        for x in leaves:
+            x.requires_grad_(False)
+            x.grad = None
+        rows.append({"function": fname, "mode": "evaluation", "JIT": "off", "time": t_eval, "alg_bytes": 0})
+        rows.append({"function": fname, "mode": "gradient", "JIT": "off", "time": t_grad, "alg_bytes": 0})
+
+    def transform_grad():
+        ratios.grad = None
+        root.grad = None
+        tm.heights().backward(ones)
+
+    def jacobian_grad():
+        heights.grad = None
+        tm.log_jacobian(heights).backward()
+
+    def coalescent_grad():
+        heights.grad = None
+        theta.grad = None
+        coal(heights).backward()
+
+    both("ratio_transform", lambda: tm.heights(), transform_grad, [ratios, root])
+    both("ratio_transform_jacobian", lambda: tm.log_jacobian(heights), jacobian_grad, [heights])
+    both("coalescent", lambda: coal(heights), coalescent_grad, [heights, theta])
+    tm.close()
     return rows
 
 

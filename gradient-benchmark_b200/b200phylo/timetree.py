@@ -23,13 +23,14 @@ import torch
 from .engine import EngineError, load_library
 from .tree import Tree
 
-__all__ = ["TimeTreeEngine", "ReparameterizedTimeTreeModel", "ConstantCoalescentModel",
+__all__ = ["TimeTreeEngine", "ReparameterizedTimeTreeModel", "ConstantCoalescentModel", "JointTimeTreeDensity",
            "tip_heights_from_names", "TIMETREE_SYMBOLS"]
 
 TIMETREE_SYMBOLS = (
     "b2p_timetree_create", "b2p_timetree_destroy", "b2p_timetree_last_error", "b2p_timetree_get_info",
     "b2p_timetree_heights", "b2p_timetree_heights_vjp", "b2p_timetree_log_jacobian",
     "b2p_timetree_branch_lengths", "b2p_timetree_branch_lengths_vjp", "b2p_coalescent_constant",
+    "b2p_joint_density_grad",
 )
 
 _declared = False
@@ -53,6 +54,7 @@ def _lib():
         lib.b2p_timetree_branch_lengths.argtypes = [vp] * 5
         lib.b2p_timetree_branch_lengths_vjp.argtypes = [vp] * 7
         lib.b2p_coalescent_constant.argtypes = [vp] * 7
+        lib.b2p_joint_density_grad.argtypes = [vp, vp, vp, vp, vp, ctypes.c_int32, vp, vp, vp, vp, vp]
         for name in TIMETREE_SYMBOLS:
             if name != "b2p_timetree_last_error":
                 getattr(lib, name).restype = ctypes.c_int
@@ -172,6 +174,21 @@ class TimeTreeEngine:
                                                       gt.data_ptr() if want_grad else None, self._stream()), "coalescent")
         return out, gh, gt
 
+    def joint_density_grad(self, like_engine, params, rate=None, theta=None, include_jacobian: bool = True):
+        """``b2p_joint_density_grad``: returns ``(out[4], grad_params, grad_rate, grad_theta)``."""
+        m = self.n_tips - 1
+        p = self._vec(params, m, "params")
+        r = self._vec(rate, 1, "rate") if rate is not None else None
+        th = self._vec(theta, 1, "theta") if theta is not None else None
+        out = torch.zeros(4, dtype=torch.float64, device=p.device)
+        gp, gr = self._new(m), self._new(1)
+        gt = self._new(1) if th is not None else None
+        self._check(self._lib.b2p_joint_density_grad(
+            like_engine._h, self._h, p.data_ptr(), r.data_ptr() if r is not None else None,
+            th.data_ptr() if th is not None else None, 1 if include_jacobian else 0, out.data_ptr(), gp.data_ptr(),
+            gr.data_ptr(), gt.data_ptr() if gt is not None else None, self._stream()), "joint_density_grad")
+        return out, gp, gr, gt
+
     def close(self) -> None:
         if self._h:
             self._lib.b2p_timetree_destroy(self._h)
@@ -241,6 +258,24 @@ class _ConstantCoalescent(torch.autograd.Function):
     def backward(ctx, g):
         gh, gt = ctx.saved_tensors
         return g * gh, g * gt, None
+
+
+class _JointDensity(torch.autograd.Function):
+    """value and gradient in the forward call (one C call, nine launches); backward scales."""
+
+    @staticmethod
+    def forward(ctx, params, rate, theta, tt: TimeTreeEngine, like_engine, include_jacobian: bool):
+        out, gp, gr, gt = tt.joint_density_grad(like_engine, params, rate, theta, include_jacobian)
+        ctx.has = (rate is not None, theta is not None)
+        ctx.save_for_backward(gp, gr.reshape(rate.shape) if rate is not None else gr,
+                              gt.reshape(theta.shape) if theta is not None else gr)
+        ctx.mark_non_differentiable(out)
+        return out[0].clone(), out
+
+    @staticmethod
+    def backward(ctx, g, _unused):
+        gp, gr, gt = ctx.saved_tensors
+        return g * gp, (g * gr if ctx.has[0] else None), (g * gt if ctx.has[1] else None), None, None, None
 
 
 # ------------------------------------------------------------------------- models
@@ -331,6 +366,35 @@ class ConstantCoalescentModel:
 
     def parameters(self):
         return self.theta.parameters() if hasattr(self.theta, "parameters") else [self.theta]
+
+
+class JointTimeTreeDensity:
+    """log p(alignment | tree, rate) + log p(heights | theta) + log|det J| as ONE engine call —
+    the density the reference's macro benchmark differentiates 5000 times per run
+    (/root/reference/flu_H3N2/phylotorch-JC69.template:11-100, /root/reference/modules/macro_flu.nf:6,133).
+    ``like`` is a ``TreeLikelihoodModel`` built on ``tree_model``; priors on rate / theta are
+    plain torch terms the caller adds."""
+
+    def __init__(self, like, tree_model: ReparameterizedTimeTreeModel, coalescent: Optional[ConstantCoalescentModel] = None,
+                 include_jacobian: bool = True):
+        if like.world_size > 1:
+            raise NotImplementedError("sharded likelihoods go through TreeLikelihoodModel (all-reduce per evaluation)")
+        self.like, self.tree_model, self.coalescent = like, tree_model, coalescent
+        self.include_jacobian = include_jacobian
+        self.terms: Optional[torch.Tensor] = None  # [total, logL, coalescent, log-Jacobian] of the last call
+
+    def __call__(self) -> torch.Tensor:
+        clock = self.like.clock_model
+        rate = clock.rates if clock is not None else None
+        dev = f"cuda:{self.tree_model.engine.device}"
+        if rate is not None and not rate.is_cuda:
+            rate = rate.to(dev)
+        theta = None
+        if self.coalescent is not None:
+            theta = getattr(self.coalescent.theta, "tensor", self.coalescent.theta)
+        total, self.terms = _JointDensity.apply(self.tree_model.params(), rate, theta, self.tree_model.engine,
+                                                self.like.engine, self.include_jacobian)
+        return total
 
 
 def initial_params_from_tree(tree: Tree, tip_heights: np.ndarray, min_branch: float = 1e-6) -> np.ndarray:

@@ -19,6 +19,7 @@ static thread_local std::string g_tt_create_error;
 
 struct b2p_timetree {
   int n_tips = 0, device = 0;
+  double* joint = nullptr;  // scratch of b2p_joint_density_grad: heights, bl, grad_bl, 3 x grad_heights, terms
   TTDev dev{};
   size_t smem_fwd = 0, smem_bwd = 0;
   std::vector<void*> allocs;
@@ -147,23 +148,30 @@ int b2p_timetree_create(int32_t n_tips, const int32_t* h_triples, const double* 
       (rc = tt_upload(t, parent_all, &d.parent_all)) || (rc = tt_upload(t, kids, &d.kids)) || (rc = tt_upload(t, bound, &d.bound)) ||
       (rc = tt_upload(t, tip_h, &d.tip_h)) || (rc = tt_upload(t, tip_sorted, &d.tip_sorted)) || (rc = tt_upload(t, tip_rank, &d.tip_rank)))
     return bail(rc);
-  std::vector<double> zeros(5 * (size_t)M + 2, 0.0), zev(n_nodes, 0.0);
+  std::vector<double> zeros(6 * (size_t)M + 8, 0.0), zev(n_nodes, 0.0);
   std::vector<unsigned> zt(1, 0u);
   const double *work = nullptr, *ev_t = nullptr, *ev_c = nullptr;
   const unsigned* ticket = nullptr;
   if ((rc = tt_upload(t, zeros, &work)) || (rc = tt_upload(t, zev, &ev_t)) || (rc = tt_upload(t, zev, &ev_c)) ||
       (rc = tt_upload(t, zt, &ticket)))
     return bail(rc);
+  {
+    std::vector<double> zj(4 * (size_t)M + 2 * (size_t)(2 * N - 2) + 8, 0.0);
+    const double* jp = nullptr;
+    if ((rc = tt_upload(t, zj, &jp))) return bail(rc);
+    t->joint = const_cast<double*>(jp);
+  }
   d.work = const_cast<double*>(work); d.ev_t = const_cast<double*>(ev_t); d.ev_c = const_cast<double*>(ev_c);
   d.ticket = const_cast<unsigned*>(ticket);
-  // shared-memory footprints: heights: h, r, b (double) + parent position + level offsets;
-  // vjp: a, w, r (double) + two child positions + level offsets
-  t->smem_fwd = 28 * (size_t)M + 4 * (size_t)(n_levels + 1) + 16;
-  t->smem_bwd = 32 * (size_t)M + 4 * (size_t)(n_levels + 1) + 16;
+  // shared-memory footprints: heights: {r, b}, h (double) + parent position + {first, count} per level;
+  // vjp: a, w, r (double) + two child positions + {first, count} per level
+  // (each array has one spare slot, see b2p_timetree.cuh)
+  t->smem_fwd = 28 * (size_t)(M + 1) + 8 * (size_t)n_levels + 16;
+  t->smem_bwd = 32 * (size_t)(M + 1) + 8 * (size_t)n_levels + 16;
   d.in_smem = t->smem_bwd <= (size_t)prop.sharedMemPerBlockOptin ? 1 : 0;
   if (d.in_smem) {
-    cudaError_t e1 = cudaFuncSetAttribute(tt_heights_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t->smem_fwd);
-    cudaError_t e2 = cudaFuncSetAttribute(tt_heights_vjp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t->smem_bwd);
+    cudaError_t e1 = cudaFuncSetAttribute(tt_heights_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t->smem_fwd);
+    cudaError_t e2 = cudaFuncSetAttribute(tt_heights_vjp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t->smem_bwd);
     if (e1 != cudaSuccess || e2 != cudaSuccess) {
       tt_fail(t, B2P_ERR_CUDA, "cudaFuncSetAttribute(smem=%zu): %s (was the library built for sm_100a?)", t->smem_bwd,
               cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
@@ -193,7 +201,8 @@ int b2p_timetree_get_info(const b2p_timetree* t, int32_t* n_levels, int32_t* n_s
 int b2p_timetree_heights(b2p_timetree* t, const double* d_params, double* d_heights, void* cuda_stream) {
   if (!t || !d_params || !d_heights) return t ? tt_fail(t, B2P_ERR_ARG, "b2p_timetree_heights: null pointer") : B2P_ERR_ARG;
   TCU(cudaSetDevice(t->device));
-  tt_heights_kernel<<<1, TT_NT, t->smem_fwd, (cudaStream_t)cuda_stream>>>(t->dev, d_params, d_heights);
+  if (t->dev.in_smem) tt_heights_kernel<true><<<1, TT_NT, t->smem_fwd, (cudaStream_t)cuda_stream>>>(t->dev, d_params, d_heights);
+  else tt_heights_kernel<false><<<1, TT_NT, 0, (cudaStream_t)cuda_stream>>>(t->dev, d_params, d_heights);
   TT_LAUNCHED("b2p_timetree_heights");
   return B2P_OK;
 }
@@ -203,7 +212,10 @@ int b2p_timetree_heights_vjp(b2p_timetree* t, const double* d_params, const doub
   if (!t || !d_params || !d_heights || !d_grad_heights || !d_grad_params)
     return t ? tt_fail(t, B2P_ERR_ARG, "b2p_timetree_heights_vjp: null pointer") : B2P_ERR_ARG;
   TCU(cudaSetDevice(t->device));
-  tt_heights_vjp_kernel<<<1, TT_NT, t->smem_bwd, (cudaStream_t)cuda_stream>>>(t->dev, d_params, d_heights, d_grad_heights, d_grad_params);
+  if (t->dev.in_smem)
+    tt_heights_vjp_kernel<true><<<1, TT_NT, t->smem_bwd, (cudaStream_t)cuda_stream>>>(t->dev, d_params, d_heights, d_grad_heights, d_grad_params, TTJoin{});
+  else
+    tt_heights_vjp_kernel<false><<<1, TT_NT, 0, (cudaStream_t)cuda_stream>>>(t->dev, d_params, d_heights, d_grad_heights, d_grad_params, TTJoin{});
   TT_LAUNCHED("b2p_timetree_heights_vjp");
   return B2P_OK;
 }
@@ -240,11 +252,58 @@ int b2p_coalescent_constant(b2p_timetree* t, const double* d_heights, const doub
                             double* d_grad_heights, double* d_grad_theta, void* cuda_stream) {
   if (!t || !d_heights || !d_theta || (!d_logp && !d_grad_heights && !d_grad_theta))
     return t ? tt_fail(t, B2P_ERR_ARG, "b2p_coalescent_constant: null pointer") : B2P_ERR_ARG;
+  if (reinterpret_cast<uintptr_t>(d_heights) & 15) return tt_fail(t, B2P_ERR_ARG, "b2p_coalescent_constant: d_heights must be 16-byte aligned");
   TCU(cudaSetDevice(t->device));
   const int E = 2 * t->n_tips - 1;
   tt_coalescent_kernel<<<(E + TTC_EV - 1) / TTC_EV, TTC_NT, 0, (cudaStream_t)cuda_stream>>>(t->dev, d_heights, d_theta, d_logp,
                                                                                            d_grad_heights, d_grad_theta);
   TT_LAUNCHED("b2p_coalescent_constant");
+  return B2P_OK;
+}
+
+int b2p_joint_density_grad(b2p_instance* like, b2p_timetree* t, const double* d_params, const double* d_rate,
+                           const double* d_theta, int32_t include_jacobian, double* d_out, double* d_grad_params,
+                           double* d_grad_rate, double* d_grad_theta, void* cuda_stream) {
+  if (!t || !like || !d_params || !d_out || !d_grad_params)
+    return t ? tt_fail(t, B2P_ERR_ARG, "b2p_joint_density_grad: null pointer") : B2P_ERR_ARG;
+  if (d_theta && !d_grad_theta) return tt_fail(t, B2P_ERR_ARG, "b2p_joint_density_grad: d_theta without d_grad_theta");
+  const int N = t->n_tips, M = N - 1, B = 2 * N - 2;
+  b2p_info info;
+  if (b2p_get_info(like, &info) != B2P_OK || info.n_tips != N)
+    return tt_fail(t, B2P_ERR_ARG, "b2p_joint_density_grad: likelihood instance and time tree differ in tip count");
+  TCU(cudaSetDevice(t->device));
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  double* heights = t->joint;          // [M]
+  double* bl = heights + M + (M & 1);  // [B]  (kept 16-byte aligned)
+  double* gbl = bl + B;                // [B]
+  double* gh_bl = gbl + B;             // [M]
+  double* gh_j = gh_bl + M;            // [M]
+  double* gh_c = gh_j + M;             // [M]
+  double* scratch_rate = gh_c + M;     // [1] when the caller does not want d/d rate
+  int rc;
+  if ((rc = b2p_timetree_heights(t, d_params, heights, st))) return rc;
+  if ((rc = b2p_timetree_branch_lengths(t, heights, d_rate, bl, st))) return rc;
+  if ((rc = b2p_loglik_grad(like, bl, d_out + 1, gbl, st)))
+    return tt_fail(t, rc, "b2p_joint_density_grad: likelihood: %s", b2p_last_error(like));
+  if ((rc = b2p_timetree_branch_lengths_vjp(t, heights, d_rate, gbl, gh_bl, d_grad_rate ? d_grad_rate : scratch_rate, st))) return rc;
+  TTJoin join{};
+  join.term[0] = d_out + 1;
+  if (d_theta) {
+    if ((rc = b2p_coalescent_constant(t, heights, d_theta, d_out + 2, gh_c, d_grad_theta, st))) return rc;
+    join.g1 = gh_c;
+    join.term[1] = d_out + 2;
+  }
+  if (include_jacobian) {
+    if ((rc = b2p_timetree_log_jacobian(t, heights, d_out + 3, gh_j, st))) return rc;
+    join.g2 = gh_j;
+    join.term[2] = d_out + 3;
+  }
+  join.total = d_out;
+  if (t->dev.in_smem)
+    tt_heights_vjp_kernel<true><<<1, TT_NT, t->smem_bwd, st>>>(t->dev, d_params, heights, gh_bl, d_grad_params, join);
+  else
+    tt_heights_vjp_kernel<false><<<1, TT_NT, 0, st>>>(t->dev, d_params, heights, gh_bl, d_grad_params, join);
+  TT_LAUNCHED("b2p_joint_density_grad");
   return B2P_OK;
 }
 

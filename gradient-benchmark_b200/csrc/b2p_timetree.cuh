@@ -44,7 +44,7 @@ struct TTDev {
   const double* tip_sorted; // [N] ascending
   const int* tip_rank;      // [N] rank of tip in (height, id) order
   // scratch
-  double* work;             // [5 M + 2] fallback for the level arrays when they do not fit shared memory
+  double* work;             // [6 M + 8] fallback for the level arrays when they do not fit shared memory
   double* ev_t;             // [2N-1] coalescent: event times by rank
   double* ev_c;             // [2N-1] coalescent: C(k, 2) after the event, by rank
   unsigned* ticket;         // coalescent: CTA completion counter
@@ -64,49 +64,71 @@ __device__ __forceinline__ double tt_block_sum(double v, double* red) {
 
 // ------------------------------------------------------------------------- node heights
 // params [M]: ratios of nodes N..2N-3, root height last.  heights [M] in node order.
+// Extra inputs of the adjoint kernel when it closes a joint-density evaluation
+// (b2p_joint_density_grad): more upstream gradients w.r.t. the heights, and the scalar terms to add up.
+struct TTJoin {
+  const double* g1;
+  const double* g2;
+  const double* term[3];
+  double* total;
+};
+
+// SMEM: the level arrays live in shared memory (a compile-time fact, so the walk uses
+// LDS/STS with 32-bit addresses rather than generic loads); otherwise in global scratch.
+//
+// A run of narrow levels is one warp's serial chain, and with a single warp issuing, its
+// speed is the instruction count per level.  So the loop body is kept to the chain itself:
+// every array has one spare slot M (r = b = 0, its own parent, no children) that idle lanes
+// are pointed at instead of being predicated off, the root (always alone on level 0) is
+// handled before the loop, and the next level's operands are fetched ahead of the chain.
+template <bool SMEM>
 __global__ void __launch_bounds__(TT_NT) tt_heights_kernel(const TTDev t, const double* __restrict__ params,
                                                           double* __restrict__ heights) {
   extern __shared__ __align__(16) unsigned char tt_sm[];
   const int M = t.n_int, tid = threadIdx.x;
-  double* h = t.in_smem ? reinterpret_cast<double*>(tt_sm) : t.work;
-  double* r = h + M;
-  double* b = r + M;
-  int* pp = reinterpret_cast<int*>(b + M);
-  int* off = pp + M;
+  double2* rb = SMEM ? reinterpret_cast<double2*>(tt_sm) : reinterpret_cast<double2*>(t.work);  // {r, b}
+  double* h = reinterpret_cast<double*>(rb + M + 1);
+  int2* lv = reinterpret_cast<int2*>(h + M + 1);  // {first position, node count} per level
+  int* pp = reinterpret_cast<int*>(lv + t.n_levels);
   for (int i = tid; i < M; i += TT_NT) {
-    r[i] = params[t.node[i]];
-    b[i] = t.bound_l[i];
+    rb[i] = make_double2(params[t.node[i]], t.bound_l[i]);
     pp[i] = t.ppos[i];
   }
-  for (int i = tid; i <= t.n_levels; i += TT_NT) off[i] = t.lvl_off[i];
+  for (int i = tid; i < t.n_levels; i += TT_NT) { const int o = t.lvl_off[i]; lv[i] = make_int2(o, t.lvl_off[i + 1] - o); }
+  if (tid == 0) { rb[M] = make_double2(0.0, 0.0); pp[M] = M; h[M] = 0.0; }
   __syncthreads();
+  if (tid == 0) h[0] = rb[0].x;  // the root's "ratio" slot carries the root height
+  __syncthreads();
+  TTSegment nxt = t.seg[0];
   for (int s = 0; s < t.n_segments; ++s) {
-    const TTSegment sg = t.seg[s];
+    const TTSegment sg = nxt;
+    if (s + 1 < t.n_segments) nxt = t.seg[s + 1];  // in flight while this run is walked
+    const int lb = sg.lvl_begin == 0 ? 1 : sg.lvl_begin;
     if (sg.narrow) {
-      if (tid < 32) {
-        int idx = off[sg.lvl_begin] + tid;
-        bool on = idx < off[sg.lvl_begin + 1];
-        double ri = on ? r[idx] : 0.0, bi = on ? b[idx] : 0.0;
-        int pi = on ? pp[idx] : -1;
-        for (int l = sg.lvl_begin; l < sg.lvl_end; ++l) {
+      if (tid < 32 && lb < sg.lvl_end) {
+        int2 v = lv[lb];
+        int idx = tid < v.y ? v.x + tid : M;
+        double2 q = rb[idx];
+        int pc = pp[idx];
+        for (int l = lb; l < sg.lvl_end; ++l) {
           const int cur = idx;
-          const bool con = on;
-          const double rc = ri, bc = bi;
-          const int pc = pi;
+          const double2 c = q;
+          const int pcur = pc;
           if (l + 1 < sg.lvl_end) {  // operands of the next level: independent of this level's result
-            idx = off[l + 1] + tid;
-            on = idx < off[l + 2];
-            ri = on ? r[idx] : 0.0; bi = on ? b[idx] : 0.0; pi = on ? pp[idx] : -1;
+            v = lv[l + 1];
+            idx = tid < v.y ? v.x + tid : M;
+            q = rb[idx];
+            pc = pp[idx];
           }
-          if (con) h[cur] = pc < 0 ? rc : __dadd_rn(bc, __dmul_rn(rc, __dsub_rn(h[pc], bc)));
+          h[cur] = __dadd_rn(c.y, __dmul_rn(c.x, __dsub_rn(h[pcur], c.y)));
           __syncwarp();
         }
       }
     } else {
-      for (int idx = off[sg.lvl_begin] + tid; idx < off[sg.lvl_end]; idx += TT_NT) {
-        const int pc = pp[idx];
-        const double bc = b[idx];
-        h[idx] = pc < 0 ? r[idx] : __dadd_rn(bc, __dmul_rn(r[idx], __dsub_rn(h[pc], bc)));
+      const int2 v = lv[lb];
+      for (int idx = v.x + tid; idx < v.x + v.y; idx += TT_NT) {
+        const double2 c = rb[idx];
+        h[idx] = __dadd_rn(c.y, __dmul_rn(c.x, __dsub_rn(h[pp[idx]], c.y)));
       }
     }
     __syncthreads();
@@ -115,50 +137,72 @@ __global__ void __launch_bounds__(TT_NT) tt_heights_kernel(const TTDev t, const 
 }
 
 // J^T g: grad_params[i] = a_i (h_parent - b_i), a_i = g_i + sum over internal children r_c a_c.
+template <bool SMEM>
 __global__ void __launch_bounds__(TT_NT) tt_heights_vjp_kernel(const TTDev t, const double* __restrict__ params,
                                                               const double* __restrict__ heights,
                                                               const double* __restrict__ grad_heights,
-                                                              double* __restrict__ grad_params) {
+                                                              double* __restrict__ grad_params, const TTJoin join) {
   extern __shared__ __align__(16) unsigned char tt_sm[];
   const int M = t.n_int, tid = threadIdx.x;
-  double* a = t.in_smem ? reinterpret_cast<double*>(tt_sm) : t.work;
-  double* w = a + M;  // r_i a_i
-  double* r = w + M;
-  int2* kp = reinterpret_cast<int2*>(r + M);
-  int* off = reinterpret_cast<int*>(kp + M);
+  double* a = SMEM ? reinterpret_cast<double*>(tt_sm) : t.work;
+  double* w = a + M + 1;  // r_i a_i; slot M stays 0 and stands in for a tip child
+  double* r = w + M + 1;
+  int2* kp = reinterpret_cast<int2*>(r + M + 1);
+  int2* lv = kp + M + 1;
   for (int i = tid; i < M; i += TT_NT) {
     const int nd = t.node[i];
-    a[i] = grad_heights[nd];
+    double g = grad_heights[nd];
+    if (join.g1) g += join.g1[nd];
+    if (join.g2) g += join.g2[nd];
+    a[i] = g;
     r[i] = t.ppos[i] < 0 ? 0.0 : params[nd];
-    kp[i] = reinterpret_cast<const int2*>(t.kpos)[i];
+    int2 k = reinterpret_cast<const int2*>(t.kpos)[i];
+    if (k.x < 0) k.x = M;
+    if (k.y < 0) k.y = M;
+    kp[i] = k;
   }
-  for (int i = tid; i <= t.n_levels; i += TT_NT) off[i] = t.lvl_off[i];
+  for (int i = tid; i < t.n_levels; i += TT_NT) { const int o = t.lvl_off[i]; lv[i] = make_int2(o, t.lvl_off[i + 1] - o); }
+  if (tid == 0) {
+    a[M] = 0.0; w[M] = 0.0; r[M] = 0.0; kp[M] = make_int2(M, M);
+    if (join.total) {  // joint density: sum of the terms the earlier launches on this stream left behind
+      double s = 0.0;
+      for (int k = 0; k < 3; ++k) if (join.term[k]) s += *join.term[k];
+      *join.total = s;
+    }
+  }
   __syncthreads();
+  TTSegment nxt = t.seg[t.n_segments - 1];
   for (int s = t.n_segments - 1; s >= 0; --s) {
-    const TTSegment sg = t.seg[s];
+    const TTSegment sg = nxt;
+    if (s > 0) nxt = t.seg[s - 1];
     if (sg.narrow) {
       if (tid < 32) {
+        int2 v = lv[sg.lvl_end - 1];
+        int idx = tid < v.y ? v.x + tid : M;
+        int2 k = kp[idx];
+        double ai = a[idx], ri = r[idx];
         for (int l = sg.lvl_end - 1; l >= sg.lvl_begin; --l) {
-          const int idx = off[l] + tid;
-          if (idx < off[l + 1]) {
-            const int2 k = kp[idx];
-            double v = a[idx];
-            if (k.x >= 0) v = __dadd_rn(v, w[k.x]);
-            if (k.y >= 0) v = __dadd_rn(v, w[k.y]);
-            a[idx] = v;
-            w[idx] = __dmul_rn(r[idx], v);
+          const int cur = idx;
+          const int2 kc = k;
+          const double ac = ai, rc = ri;
+          if (l > sg.lvl_begin) {
+            v = lv[l - 1];
+            idx = tid < v.y ? v.x + tid : M;
+            k = kp[idx]; ai = a[idx]; ri = r[idx];
           }
+          const double sum = __dadd_rn(__dadd_rn(ac, w[kc.x]), w[kc.y]);
+          a[cur] = sum;
+          w[cur] = __dmul_rn(rc, sum);
           __syncwarp();
         }
       }
     } else {
-      for (int idx = off[sg.lvl_begin] + tid; idx < off[sg.lvl_end]; idx += TT_NT) {
+      const int2 v = lv[sg.lvl_begin];
+      for (int idx = v.x + tid; idx < v.x + v.y; idx += TT_NT) {
         const int2 k = kp[idx];
-        double v = a[idx];
-        if (k.x >= 0) v = __dadd_rn(v, w[k.x]);
-        if (k.y >= 0) v = __dadd_rn(v, w[k.y]);
-        a[idx] = v;
-        w[idx] = __dmul_rn(r[idx], v);
+        const double sum = __dadd_rn(__dadd_rn(a[idx], w[k.x]), w[k.y]);
+        a[idx] = sum;
+        w[idx] = __dmul_rn(r[idx], sum);
       }
     }
     __syncthreads();
@@ -249,13 +293,20 @@ __global__ void __launch_bounds__(TTC_NT) tt_coalescent_kernel(const TTDev t, co
   const double te = !live ? 0.0 : internal ? heights[e - N] : t.tip_h[e];
   const int self = e - N;
   int below = 0;  // internal nodes ordered before this event
-  if (live && internal) {
-    for (int j = sub; j < M; j += TTC_LANES) {
-      const double hj = heights[j];
-      below += (hj < te || (hj == te && j < self)) ? 1 : 0;
+  if (live) {
+    // two heights per load, loads batched by the unroll: the scan is L1-latency-bound otherwise
+    const double2* h2 = reinterpret_cast<const double2*>(heights);
+    const int half = M >> 1, tie = internal ? self : -1;  // a tip sorts before every internal node of equal height
+#pragma unroll 8
+    for (int j2 = sub; j2 < half; j2 += TTC_LANES) {
+      const double2 hv = h2[j2];
+      below += (hv.x < te || (hv.x == te && 2 * j2 < tie)) ? 1 : 0;
+      below += (hv.y < te || (hv.y == te && 2 * j2 + 1 < tie)) ? 1 : 0;
     }
-  } else if (live) {
-    for (int j = sub; j < M; j += TTC_LANES) below += heights[j] < te ? 1 : 0;
+    if ((M & 1) && sub == 0) {
+      const double hj = heights[M - 1];
+      below += (hj < te || (hj == te && M - 1 < tie)) ? 1 : 0;
+    }
   }
 #pragma unroll
   for (int o = TTC_LANES / 2; o > 0; o >>= 1) below += __shfl_xor_sync(0xffffffffu, below, o);
@@ -282,6 +333,7 @@ __global__ void __launch_bounds__(TTC_NT) tt_coalescent_kernel(const TTDev t, co
   if (!last) return;
   __threadfence();
   double s = 0.0;
+#pragma unroll 4
   for (int j = threadIdx.x; j < E - 1; j += TTC_NT) s += __ldcg(t.ev_c + j) * (__ldcg(t.ev_t + j + 1) - __ldcg(t.ev_t + j));
   s = tt_block_sum(s, red);
   if (threadIdx.x == 0) {

@@ -200,10 +200,30 @@ int b2p_timetree_branch_lengths_vjp(b2p_timetree* t, const double* d_heights, co
                                     const double* d_grad_bl, double* d_grad_heights,
                                     double* d_grad_rate, void* cuda_stream);
 /* coalescent (constant population size theta = *d_theta): log density of the node heights,
- * gradient w.r.t. the internal heights [N-1] and w.r.t. theta.  Outputs may be NULL. */
+ * gradient w.r.t. the internal heights [N-1] and w.r.t. theta.  Outputs may be NULL;
+ * d_heights must be 16-byte aligned (any cudaMalloc / torch allocation is). */
 int b2p_coalescent_constant(b2p_timetree* t, const double* d_heights, const double* d_theta,
                             double* d_logp, double* d_grad_heights, double* d_grad_theta,
                             void* cuda_stream);
+
+/* The macro benchmark's model density and its gradient in one call
+ * (/root/reference/flu_H3N2/phylotorch-JC69.template:11-100: tree likelihood under a strict
+ * clock + constant coalescent on the node heights + log-Jacobian of the ratio transform; the
+ * ADVI loop evaluates exactly this, value and gradient, once per iteration,
+ * /root/reference/modules/macro_flu.nf:133).  Chains ratios/root height -> heights -> branch
+ * lengths -> b2p_loglik_grad -> back to d/d(ratios, root height), d/d rate, d/d theta on the
+ * device: nine launches on `cuda_stream`, no synchronisation, no host round trip.
+ *   like             likelihood instance for the same topology (same device)
+ *   d_rate           strict-clock rate (one double), NULL = 1
+ *   d_theta          population size; NULL leaves the coalescent term out
+ *   include_jacobian add log|det J| of the ratio transform
+ *   d_out [4]        total, log-likelihood, coalescent log-density, log-Jacobian (absent terms are
+ *                    left untouched and not added)
+ *   d_grad_params [N-1], d_grad_rate [1] (may be NULL), d_grad_theta [1] (required with d_theta) */
+int b2p_joint_density_grad(b2p_instance* like, b2p_timetree* t, const double* d_params,
+                           const double* d_rate, const double* d_theta, int32_t include_jacobian,
+                           double* d_out, double* d_grad_params, double* d_grad_rate,
+                           double* d_grad_theta, void* cuda_stream);
 
 #ifdef __cplusplus
 }

@@ -212,3 +212,110 @@ def test_time_tree_from_json_template():
                                          *w.eigen_args())
     assert rel_err(float(logl), ol) < 1e-10
     m.close()
+
+
+def test_cli_writes_time_function_rows(tmp_path):
+    """Dated tip labels -> the CLI also times ratio_transform, ratio_transform_jacobian and
+    coalescent (/root/reference/plot.Rmd:49-60,301-303) in the same CSV vocabulary."""
+    import csv
+    import os
+    import subprocess
+    import sys
+    from b200phylo.alignment import simulate_alignment, write_fasta
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    w = make_workload("jc69_20x1000")
+    n = w.n_tips
+    tree = w.tree
+    # a clock-like dated tree: tip date = latest date - (height implied by the branch lengths)
+    time_tree = tree.scaled(1000.0)
+    heights = time_tree.node_heights()
+    tree.names = [f"t{i}_{2015.0 - heights[i]:.6f}" for i in range(n)]
+    time_tree.names = list(tree.names)
+    pm = w.subst_model.p_t(tree.branch_lengths[:, None] * np.ones(1)[None, :])
+    aln = simulate_alignment(tree, pm, w.subst_model.freqs, 500, seed=9)
+    fa, nw, out = tmp_path / "a.fasta", tmp_path / "t.nwk", tmp_path / "out.csv"
+    write_fasta(str(fa), aln)
+    nw.write_text(time_tree.to_newick(17))
+    subprocess.check_call([sys.executable, os.path.join(root, "bin", "b200phylo-benchmark"), "-i", str(fa),
+                           "-t", str(nw), "-r", "20", "-s", "0.001", "-o", str(out)])
+    rows = list(csv.reader(open(out)))
+    assert rows[0] == ["function", "mode", "JIT", "time"]
+    assert [r[:2] for r in rows[1:]] == [
+        ["treelikelihoodJC69", "evaluation"], ["treelikelihoodJC69", "gradient"],
+        ["ratio_transform", "evaluation"], ["ratio_transform", "gradient"],
+        ["ratio_transform_jacobian", "evaluation"], ["ratio_transform_jacobian", "gradient"],
+        ["coalescent", "evaluation"], ["coalescent", "gradient"]]
+    assert all(float(r[3]) > 0 and r[2] == "off" for r in rows[1:])
+
+
+def test_initial_params_reproduce_the_dated_tree():
+    from b200phylo.timetree import ReparameterizedTimeTreeModel
+    w = make_workload("jc69_20x1000", n_tips=80, n_patterns=50)
+    tree = w.tree.scaled(1000.0)
+    hh = tree.node_heights()
+    tm = ReparameterizedTimeTreeModel("tree", tree, hh[: tree.n_tips].copy())
+    got = tm.heights().cpu().numpy()
+    np.testing.assert_allclose(got, hh[tree.n_tips:], rtol=1e-9, atol=1e-9)
+    bl = tm.branch_lengths().cpu().numpy()
+    np.testing.assert_allclose(bl, tree.branch_lengths, rtol=1e-7, atol=1e-9)
+    tm.close()
+
+
+@pytest.mark.parametrize("with_coalescent,with_jacobian", [(True, True), (False, True), (True, False)])
+def test_joint_density_single_call_matches_the_chain(with_coalescent, with_jacobian):
+    """b2p_joint_density_grad (one C call) against the oracle chain and against the
+    function-by-function autograd path."""
+    from b200phylo.timetree import ConstantCoalescentModel, JointTimeTreeDensity, ReparameterizedTimeTreeModel
+    from b200phylo.treelikelihood import StrictClockModel, TreeLikelihoodModel
+    w = make_workload("hky_g4_flu", n_tips=90, n_patterns=500)
+    n = w.n_tips
+    rng = np.random.default_rng(15)
+    tips = rng.uniform(0.0, 8.0, n)
+    tips[7] = 0.0
+    x = rng.uniform(0.1, 0.9, n - 1)
+    x[n - 2] = 15.0
+    ratios = cu(x[: n - 2]).requires_grad_(True)
+    root = cu(x[n - 2:]).requires_grad_(True)
+    rate = cu([0.004]).requires_grad_(True)
+    theta = cu([6.0]).requires_grad_(True)
+    tm = ReparameterizedTimeTreeModel("tree", w.tree, tips, ratios, root)
+    like = TreeLikelihoodModel("like", w.patterns, tm, w.subst_model, w.site_model, StrictClockModel("clock", rate))
+    coal = ConstantCoalescentModel("coalescent", tm, theta) if with_coalescent else None
+    joint = JointTimeTreeDensity(like, tm, coal, include_jacobian=with_jacobian)
+    total = joint()
+    (3.0 * total).backward()
+    got = [t.grad.clone() for t in (ratios, root, rate)] + ([theta.grad.clone()] if with_coalescent else [])
+    terms = joint.terms.cpu().numpy()
+    # oracle chain
+    tr = w.tree.post_triples
+    oh = tto.heights_from_ratios(n, tr, tips, x)
+    ol, og = oracle_c(w, bl=tto.branch_lengths(n, tr, tips, oh, 0.004))
+    gh, grate = tto.branch_lengths_vjp(n, tr, tips, oh, 0.004, og)
+    want = ol
+    assert rel_err(terms[1], ol) < 1e-10
+    if with_coalescent:
+        cl, cgh, cgt = tto.constant_coalescent(n, tips, oh, 6.0)
+        gh, want = gh + cgh, want + cl
+        assert rel_err(terms[2], cl) < 1e-12
+        assert float(got[3]) == pytest.approx(3.0 * cgt, rel=1e-10)
+    if with_jacobian:
+        gh, want = gh + tto.log_jacobian_grad(n, tr, tips, oh), want + tto.log_jacobian(n, tr, tips, oh)
+    gx = tto.heights_vjp(n, tr, tips, x, gh)
+    assert rel_err(float(total.detach()), want) < 1e-10 and rel_err(terms[0], want) < 1e-10
+    assert grad_err(got[0].cpu().numpy(), 3.0 * gx[: n - 2]) < 1e-8
+    assert float(got[1]) == pytest.approx(3.0 * gx[n - 2], rel=1e-8)
+    assert float(got[2]) == pytest.approx(3.0 * grate, rel=1e-8)
+    # the function-by-function path gives the same numbers
+    for t in (ratios, root, rate, theta):
+        t.grad = None
+    h = tm.heights()
+    sep = like()
+    if with_coalescent:
+        sep = sep + coal(h)
+    if with_jacobian:
+        sep = sep + tm.log_jacobian(h)
+    (3.0 * sep).backward()
+    assert rel_err(float(sep.detach()), float(total.detach())) < 1e-13
+    assert grad_err(ratios.grad.cpu().numpy(), got[0].cpu().numpy()) < 1e-12
+    like.close()
+    tm.close()
