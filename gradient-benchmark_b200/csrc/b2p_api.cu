@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -370,7 +371,11 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   }
   h->kernel = (cfg->precision == B2P_PRECISION_F32) ? walk_select<float>(K, h->wg.nt, h->wg.cpt) : walk_select<double>(K, h->wg.nt, h->wg.cpt);
   if (!h->kernel) { fail(h, B2P_ERR_ARG, "b2p_create: no kernel for %d threads", h->wg.nt); return bail(B2P_ERR_ARG); }
-  if ((e = cudaFuncSetAttribute(h->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->wg.smem)) != cudaSuccess) {
+  // function attributes are process-wide: never lower what another live instance asked for
+  static std::map<const void*, size_t> smem_asked;
+  size_t& asked = smem_asked[h->kernel];
+  asked = std::max(asked, h->wg.smem);
+  if ((e = cudaFuncSetAttribute(h->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asked)) != cudaSuccess) {
     fail(h, B2P_ERR_CUDA, "cudaFuncSetAttribute(smem=%zu): %s", h->wg.smem, cudaGetErrorString(e));
     return bail(B2P_ERR_CUDA);
   }

@@ -18,10 +18,10 @@ using namespace b2p;
 static thread_local std::string g_tt_create_error;
 
 struct b2p_timetree {
-  int n_tips = 0, device = 0;
+  int n_tips = 0, device = 0, n_sms = 0;
   double* joint = nullptr;  // scratch of b2p_joint_density_grad: heights, bl, grad_bl, 3 x grad_heights, terms
   TTDev dev{};
-  size_t smem_fwd = 0, smem_bwd = 0;
+  size_t smem_fwd = 0, smem_bwd = 0, smem_coal = 0;
   std::vector<void*> allocs;
   mutable std::string err;
 };
@@ -140,6 +140,7 @@ int b2p_timetree_create(int32_t n_tips, const int32_t* h_triples, const double* 
     tt_fail(t, B2P_ERR_UNSUPPORTED, "b2p_timetree_create: built for sm_100a (B200), device is sm_%d%d", prop.major, prop.minor);
     return bail(B2P_ERR_UNSUPPORTED);
   }
+  t->n_sms = prop.multiProcessorCount;
   TTDev& d = t->dev;
   d.n_tips = N; d.n_int = M; d.n_levels = n_levels; d.n_segments = (int)seg.size();
   int rc = B2P_OK;
@@ -170,8 +171,8 @@ int b2p_timetree_create(int32_t n_tips, const int32_t* h_triples, const double* 
   t->smem_bwd = 32 * (size_t)(M + 1) + 8 * (size_t)n_levels + 16;
   d.in_smem = t->smem_bwd <= (size_t)prop.sharedMemPerBlockOptin ? 1 : 0;
   if (d.in_smem) {
-    cudaError_t e1 = cudaFuncSetAttribute(tt_heights_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t->smem_fwd);
-    cudaError_t e2 = cudaFuncSetAttribute(tt_heights_vjp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t->smem_bwd);
+    cudaError_t e1 = cudaFuncSetAttribute(tt_heights_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prop.sharedMemPerBlockOptin);
+    cudaError_t e2 = cudaFuncSetAttribute(tt_heights_vjp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prop.sharedMemPerBlockOptin);
     if (e1 != cudaSuccess || e2 != cudaSuccess) {
       tt_fail(t, B2P_ERR_CUDA, "cudaFuncSetAttribute(smem=%zu): %s (was the library built for sm_100a?)", t->smem_bwd,
               cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
@@ -179,6 +180,14 @@ int b2p_timetree_create(int32_t n_tips, const int32_t* h_triples, const double* 
     }
   } else {
     t->smem_fwd = t->smem_bwd = 0;
+  }
+  // coalescent: internal heights + sorted tip heights per CTA, when two CTAs still fit an SM
+  t->smem_coal = 8 * ((size_t)((M + 1) & ~1) + N);
+  if (t->smem_coal > 100 * 1024) t->smem_coal = 0;
+  // (function attributes are process-wide: always ask for the cap, never for this tree's size)
+  if (cudaFuncSetAttribute(tt_coalescent_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024) != cudaSuccess) {
+    tt_fail(t, B2P_ERR_CUDA, "cudaFuncSetAttribute(coalescent smem=%zu) failed", t->smem_coal);
+    return bail(B2P_ERR_CUDA);
   }
   *out = t;
   return B2P_OK;
@@ -255,8 +264,13 @@ int b2p_coalescent_constant(b2p_timetree* t, const double* d_heights, const doub
   if (reinterpret_cast<uintptr_t>(d_heights) & 15) return tt_fail(t, B2P_ERR_ARG, "b2p_coalescent_constant: d_heights must be 16-byte aligned");
   TCU(cudaSetDevice(t->device));
   const int E = 2 * t->n_tips - 1;
-  tt_coalescent_kernel<<<(E + TTC_EV - 1) / TTC_EV, TTC_NT, 0, (cudaStream_t)cuda_stream>>>(t->dev, d_heights, d_theta, d_logp,
-                                                                                           d_grad_heights, d_grad_theta);
+  const int grid = std::min((E + TTC_EV - 1) / TTC_EV, t->n_sms * (t->smem_coal > 56 * 1024 ? 2 : 4));
+  if (t->smem_coal)
+    tt_coalescent_kernel<true><<<grid, TTC_NT, t->smem_coal, (cudaStream_t)cuda_stream>>>(t->dev, d_heights, d_theta, d_logp,
+                                                                                       d_grad_heights, d_grad_theta);
+  else
+    tt_coalescent_kernel<false><<<grid, TTC_NT, 0, (cudaStream_t)cuda_stream>>>(t->dev, d_heights, d_theta, d_logp,
+                                                                               d_grad_heights, d_grad_theta);
   TT_LAUNCHED("b2p_coalescent_constant");
   return B2P_OK;
 }

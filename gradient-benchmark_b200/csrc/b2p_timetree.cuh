@@ -45,8 +45,8 @@ struct TTDev {
   const int* tip_rank;      // [N] rank of tip in (height, id) order
   // scratch
   double* work;             // [6 M + 8] fallback for the level arrays when they do not fit shared memory
-  double* ev_t;             // [2N-1] coalescent: event times by rank
-  double* ev_c;             // [2N-1] coalescent: C(k, 2) after the event, by rank
+  double* ev_t;             // [2N-1] coalescent: per-CTA partial sums
+  double* ev_c;             // unused
   unsigned* ticket;         // coalescent: CTA completion counter
 };
 
@@ -272,69 +272,105 @@ __global__ void __launch_bounds__(TT_NT) tt_branch_lengths_vjp_kernel(const TTDe
 }
 
 // ------------------------------------------------------------------ constant coalescent
-// Events (all 2N-1 nodes) are ranked by (height, tips before internal nodes, id) by counting:
-// 8 lanes per event share the scan over the internal heights.  Each event writes its time and
-// C(k,2) after it at its rank; the last CTA to finish sums the intervals
-//   logp = -(1/theta) sum_j C_j (t_{j+1} - t_j) - (N-1) log theta.
-// grad_heights[e] = -(k_e - 1)/theta (k_e lineages just before the merge), grad_theta = S/theta^2 - (N-1)/theta.
+// logp = -(1/theta) S - (N-1) log theta,  S = sum over intervals of C(k,2) x length.
+// Summed by parts, S = sum over events of t_e (C(k before e) - C(k after e)): a merge of k
+// lineages contributes t_e (k-1), a tip that joins k lineages -t_e k.  So every event only
+// needs k_e = (tips ordered before it) - (internal nodes ordered before it), its rank in the
+// order (height, tips before internal nodes, id) — found by counting, no sort, no neighbours:
+// 8 lanes per event share the scan over the internal heights (staged in shared memory once
+// per CTA: all events of a CTA scan the same array, so reading it from L2 in lockstep would
+// leave one load in flight per CTA), the tips-before count is a binary search in the tip
+// heights sorted at set-up.  CTAs leave partial sums; the last one to finish adds them in
+// index order.  grad_heights[e] = -(k_e - 1)/theta, grad_theta = S/theta^2 - (N-1)/theta.
 constexpr int TTC_NT = 256, TTC_LANES = 8, TTC_EV = TTC_NT / TTC_LANES;
 
+template <bool SMEM>
 __global__ void __launch_bounds__(TTC_NT) tt_coalescent_kernel(const TTDev t, const double* __restrict__ heights,
                                                               const double* __restrict__ theta_p,
                                                               double* __restrict__ logp, double* __restrict__ grad_heights,
                                                               double* __restrict__ grad_theta) {
+  extern __shared__ __align__(16) unsigned char tt_sm[];
   __shared__ double red[TTC_NT / 32];
   __shared__ unsigned last;
   const int N = t.n_tips, M = t.n_int, E = 2 * N - 1;
+  const int Mp = (M + 1) & ~1;
+  const double* hs = heights;
+  const double* ts = t.tip_sorted;
+  if (SMEM) {
+    double* sh = reinterpret_cast<double*>(tt_sm);
+    for (int i = threadIdx.x; i < M; i += TTC_NT) sh[i] = heights[i];
+    for (int i = threadIdx.x; i < N; i += TTC_NT) sh[Mp + i] = t.tip_sorted[i];
+    hs = sh;
+    ts = sh + Mp;
+    __syncthreads();
+  }
   const int sub = threadIdx.x & (TTC_LANES - 1);
-  const int e = blockIdx.x * TTC_EV + threadIdx.x / TTC_LANES;
   const double theta = *theta_p;
-  const bool live = e < E, internal = e >= N;
-  const double te = !live ? 0.0 : internal ? heights[e - N] : t.tip_h[e];
-  const int self = e - N;
-  int below = 0;  // internal nodes ordered before this event
-  if (live) {
-    // two heights per load, loads batched by the unroll: the scan is L1-latency-bound otherwise
-    const double2* h2 = reinterpret_cast<const double2*>(heights);
-    const int half = M >> 1, tie = internal ? self : -1;  // a tip sorts before every internal node of equal height
+  const double2* h2 = reinterpret_cast<const double2*>(hs);
+  const int half = M >> 1;
+  double part = 0.0;
+  for (int e0 = blockIdx.x * TTC_EV; e0 < E; e0 += gridDim.x * TTC_EV) {  // whole CTA iterates together
+    const int e = e0 + threadIdx.x / TTC_LANES;
+    const bool live = e < E, internal = e >= N;
+    const double te = !live ? 0.0 : internal ? hs[e - N] : t.tip_h[e];
+    const int self = e - N;
+    // internal nodes strictly below, and at or below: a tip sorts before every internal node of its
+    // height, so for a tip "below" is the strict count; an internal node counts itself in `le`
+    // and, in the rare tie with another internal node, falls back to the id order.
+    int lt = 0, le = 0;
+    if (live) {
 #pragma unroll 8
-    for (int j2 = sub; j2 < half; j2 += TTC_LANES) {
-      const double2 hv = h2[j2];
-      below += (hv.x < te || (hv.x == te && 2 * j2 < tie)) ? 1 : 0;
-      below += (hv.y < te || (hv.y == te && 2 * j2 + 1 < tie)) ? 1 : 0;
+      for (int j2 = sub; j2 < half; j2 += TTC_LANES) {
+        const double2 hv = h2[j2];
+        lt += (hv.x < te) + (hv.y < te);
+        le += (hv.x <= te) + (hv.y <= te);
+      }
+      if ((M & 1) && sub == 0) {
+        const double hj = hs[M - 1];
+        lt += hj < te;
+        le += hj <= te;
+      }
     }
-    if ((M & 1) && sub == 0) {
-      const double hj = heights[M - 1];
-      below += (hj < te || (hj == te && M - 1 < tie)) ? 1 : 0;
-    }
-  }
 #pragma unroll
-  for (int o = TTC_LANES / 2; o > 0; o >>= 1) below += __shfl_xor_sync(0xffffffffu, below, o);
-  if (live && sub == 0) {
-    int tips_before;
-    if (internal) {  // tips with height <= te
-      int lo = 0, hi = N;
-      while (lo < hi) { const int mid = (lo + hi) >> 1; if (t.tip_sorted[mid] <= te) lo = mid + 1; else hi = mid; }
-      tips_before = lo;
-    } else {
-      tips_before = t.tip_rank[e];
+    for (int o = TTC_LANES / 2; o > 0; o >>= 1) {
+      lt += __shfl_xor_sync(0xffffffffu, lt, o);
+      le += __shfl_xor_sync(0xffffffffu, le, o);
     }
-    const int k_before = tips_before - below;
-    const int k_after = internal ? k_before - 1 : k_before + 1;
-    const int rank = tips_before + below;
-    t.ev_t[rank] = te;
-    t.ev_c[rank] = 0.5 * (double)k_after * (double)(k_after - 1);
-    if (internal && grad_heights) grad_heights[self] = -(double)(k_before - 1) / theta;
+    // other internal nodes at exactly this height (rare): lower id first.  Warp-uniform branch
+    // so the shuffles stay converged; groups without a tie add nothing.
+    const bool tied = live && internal && le - lt > 1;
+    if (__any_sync(0xffffffffu, tied)) {
+      int extra = 0;
+      if (tied)
+        for (int j = sub; j < self; j += TTC_LANES) extra += hs[j] == te;
+#pragma unroll
+      for (int o = TTC_LANES / 2; o > 0; o >>= 1) extra += __shfl_xor_sync(0xffffffffu, extra, o);
+      lt += extra;
+    }
+    if (live && sub == 0) {
+      if (internal) {
+        const int below = lt;
+        int lo = 0, hi = N;  // tips with height <= te
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (ts[mid] <= te) lo = mid + 1; else hi = mid; }
+        const int k = lo - below;  // lineages just before the merge
+        part += te * (double)(k - 1);
+        if (grad_heights) grad_heights[self] = -(double)(k - 1) / theta;
+      } else {
+        part -= te * (double)(t.tip_rank[e] - lt);
+      }
+    }
   }
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) last = atomicAdd(t.ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
+  part = tt_block_sum(part, red);
+  if (threadIdx.x == 0) {
+    t.ev_t[blockIdx.x] = part;
+    __threadfence();
+    last = atomicAdd(t.ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
+  }
   __syncthreads();
   if (!last) return;
   __threadfence();
   double s = 0.0;
-#pragma unroll 4
-  for (int j = threadIdx.x; j < E - 1; j += TTC_NT) s += __ldcg(t.ev_c + j) * (__ldcg(t.ev_t + j + 1) - __ldcg(t.ev_t + j));
+  for (int j = threadIdx.x; j < (int)gridDim.x; j += TTC_NT) s += __ldcg(t.ev_t + j);
   s = tt_block_sum(s, red);
   if (threadIdx.x == 0) {
     if (logp) *logp = -s / theta - (double)(N - 1) * log(theta);

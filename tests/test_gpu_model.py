@@ -96,10 +96,12 @@ def test_cli_contract_end_to_end(tmp_path):
                                "-t", str(nw), "-r", "20", "-s", "0.001", "-o", str(out), "--gtr"] + extra)
         rows = list(csv.reader(open(out)))
         assert rows[0] == ["function", "mode", "JIT", "time"]
-        assert [r[:3] for r in rows[1:]] == [
+        assert [r[:3] for r in rows[1:5]] == [
             ["treelikelihoodJC69", "evaluation", "off"], ["treelikelihoodJC69", "gradient", "off"],
             ["treelikelihoodGTR", "evaluation", "off"], ["treelikelihoodGTR", "gradient", "off"]]
         assert all(float(r[3]) > 0 for r in rows[1:])
+        # dated tip labels: the time-tree functions follow (/root/reference/plot.Rmd:49-60)
+        assert [r[0] for r in rows[5:]] == ["ratio_transform"] * 2 + ["ratio_transform_jacobian"] * 2 + ["coalescent"] * 2
         side = json.load(open(str(out) + ".b200.json"))
         from b200phylo.alignment import compress_alignment
         w2 = Workload("c", w.tree, compress_alignment(aln), JC69(), ConstantSiteModel())
@@ -179,3 +181,19 @@ def test_gate_shape_gtr_g4_5000x10k_linearity():
     e.close()
     ol, og = oracle_c(ws)
     assert rel_err(l, ol) < 1e-10 and grad_err(g, og) < 1e-8
+
+
+def test_two_live_instances_of_different_size():
+    """Kernel attributes (dynamic shared memory) are process-wide: creating a second, smaller
+    instance must not break launches of the first."""
+    wa = make_workload("jc69_20x1000", n_tips=300, n_patterns=3000)
+    wb = make_workload("jc69_20x1000", n_tips=12, n_patterns=40)
+    ea = make_engine(wa)
+    eb = make_engine(wb)
+    la, ga = ea.loglik_grad_host(wa.tree.branch_lengths)
+    lb, gb = eb.loglik_grad_host(wb.tree.branch_lengths)
+    la2, _ = ea.loglik_grad_host(wa.tree.branch_lengths)
+    assert la == la2
+    assert rel_err(la, oracle_c(wa)[0]) < 1e-10 and rel_err(lb, oracle_c(wb)[0]) < 1e-10
+    ea.close()
+    eb.close()
