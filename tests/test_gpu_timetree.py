@@ -319,3 +319,36 @@ def test_joint_density_single_call_matches_the_chain(with_coalescent, with_jacob
     assert grad_err(ratios.grad.cpu().numpy(), got[0].cpu().numpy()) < 1e-12
     like.close()
     tm.close()
+
+
+def test_advi_cli_runs_and_prints_parsable_progress(tmp_path):
+    """b200phylo-advi with the macro pipeline's flags (/root/reference/modules/macro_flu.nf:124-137):
+    the ELBO goes up and the progress lines parse with bin/time-parser.py's torchtree pattern."""
+    import os
+    import re
+    import subprocess
+    import sys
+    from b200phylo.alignment import simulate_alignment, write_fasta
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    w = make_workload("jc69_20x1000")
+    n = w.n_tips
+    tree = w.tree
+    time_tree = tree.scaled(1000.0)
+    heights = time_tree.node_heights()
+    tree.names = [f"t{i}_{2015.0 - heights[i]:.6f}" for i in range(n)]
+    time_tree.names = list(tree.names)
+    pm = w.subst_model.p_t(tree.branch_lengths[:, None] * np.ones(1)[None, :])
+    aln = simulate_alignment(tree, pm, w.subst_model.freqs, 800, seed=9)
+    fa, nw = tmp_path / "a.fasta", tmp_path / "t.nwk"
+    write_fasta(str(fa), aln)
+    nw.write_text(time_tree.to_newick(17))
+    txt = subprocess.check_output([sys.executable, os.path.join(root, "bin", "b200phylo-advi"), "-i", str(fa), "-t", str(nw),
+                                   "--clock", "strict", "--coalescent", "constant", "--heights_init", "tree",
+                                   "--rate_init", "0.001", "--clockpr", "exponential", "--lr", "0.01", "--elbo_samples", "1",
+                                   "--tol_rel_obj", "0", "--iter", "400", "--samples", "0", "--print_every", "50"], text=True)
+    pat = re.compile(r"\s+(\d+)\s+(-\d+\.\d+).+")  # /root/reference/bin/time-parser.py:60-61
+    rows = [(int(m.group(1)), float(m.group(2))) for m in map(pat.match, txt.splitlines()) if m]
+    assert rows[0][0] == 1 and rows[-1][0] == 400 and len(rows) == 9
+    assert all(np.isfinite(e) for _, e in rows)
+    assert np.mean([e for _, e in rows[-3:]]) > rows[0][1]  # variational fit improves on the start
+    assert "Ran inference for 400 iterations" in txt
