@@ -651,7 +651,7 @@ int b2p_loglik_grad_host(b2p_instance* h, const double* h_bl, double* h_logl, do
       for (int w = 0; w < 2; ++w)
         for (int q = 0; q < R; ++q) {
           const long long* r = tr.data() + ((size_t)w * R + q) * 8;
-          fprintf(f, "%d %d %lld %lld %lld %lld %lld %lld %lld\n", w, q, r[0], r[1], r[2], r[3], r[4], r[5], r[6]);
+          fprintf(f, "%d %d %lld %lld %lld %lld %lld %lld %lld %lld\n", w, q, r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7]);
         }
       fclose(f);
     }

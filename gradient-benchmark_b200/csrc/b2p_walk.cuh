@@ -560,6 +560,9 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
           const uint4 jb = lds_u4(frame + 16 + warp * 16);
           bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar_next);
         }
+#ifdef B2P_TRACE_CLOCKS
+        if (tr) trow[7] = clock64();
+#endif
         T ma[CPT][4], mb[CPT][4];
         if (K != 1 || live) load_messages<T, CPT>(th, frame, d, live, ma, mb);
         if (my_job && pass != 0) {

@@ -13,6 +13,9 @@ for w in (0, 1):
         c = np.column_stack([x[:, 5] - x[:, 1], x[:, 2] - x[:, 5], x[:, 6] - x[:, 2], x[:, 3] - x[:, 6]])
         print("  copy warp post: stores %.0f loads %.0f fold %.0f wait_group %.0f" % tuple(c[1:rp].mean(0)))
         print("  copy warp pre : stores %.0f loads %.0f fold %.0f wait_group %.0f" % tuple(c[rp:].mean(0)))
+    if w == 0 and x.shape[1] >= 8:
+        print("  compute warp 0, post rounds: desc+own load issue %.0f, operand reads %.0f" % ((x[:rp, 7] - x[:rp, 1]).mean(), (x[:rp, 2] - x[:rp, 7]).mean()))
+        print("  compute warp 0, pre rounds : desc %.0f, operand reads + own load issue %.0f" % ((x[rp:, 7] - x[rp:, 1]).mean(), (x[rp:, 2] - x[rp:, 7]).mean()))
     if w == 0:
         for q in range(0, len(x), 10):
             print("  round %3d: wait %5d issue %5d compute %5d bar %5d  next-start %6d" % (q, *d[q], rt[q] if q < len(rt) else 0))
