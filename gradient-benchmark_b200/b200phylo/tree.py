@@ -22,7 +22,7 @@ from typing import List, Optional, Sequence
 
 import numpy as np
 
-__all__ = ["Tree", "simulate_tree", "parse_newick"]
+__all__ = ["Tree", "simulate_tree", "parse_newick", "read_lsd_nexus"]
 
 
 @dataclass
@@ -239,6 +239,21 @@ def parse_newick(text: str, taxa: Optional[Sequence[str]] = None,
     tree = Tree(n, children, bl, names_out)
     tree.validate()
     return tree
+
+
+def read_lsd_nexus(path: str, taxa: Optional[Sequence[str]] = None) -> Tree:
+    """Dated tree written by lsd2 (``*.date.nexus``): the ``tree 1 = ...`` line with its
+    ``[&date="..."]`` node annotations dropped — what ``helper.py convert`` does before the
+    contenders see the tree (/root/reference/bin/helper.py:169-176, /root/reference/main.nf:18-40)."""
+    newick = None
+    with open(path) as fh:
+        for line in fh:
+            if line.lstrip().lower().startswith("tree 1 = "):
+                newick = line.strip()[len("tree 1 = "):].strip()
+    if newick is None:
+        raise ValueError(f"{path}: no 'tree 1 = ' line")
+    newick = re.sub(r'\[&date="\d+\.?\d*"\]', "", newick)
+    return parse_newick(newick, taxa=taxa)
 
 
 def _renumber(n: int, raw_children: dict, raw_len: dict, root) -> Tree:

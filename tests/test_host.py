@@ -130,3 +130,18 @@ def test_json_subobject_parsers():
     assert float(clock.rates[0]) == 0.001
     with pytest.raises(ValueError):
         tl._subst_model_from_json({"type": "WAG"})
+
+
+def test_read_lsd_nexus(tmp_path):
+    """lsd2's dated Nexus (/root/reference/bin/helper.py:169-176): annotations are dropped,
+    the tree and its branch lengths survive."""
+    from b200phylo.tree import read_lsd_nexus
+    p = tmp_path / "lsd.out.date.nexus"
+    p.write_text('#NEXUS\nBegin trees;\ntree 1 = ((a_2001[&date="2001"]:1.5,b_2003.5[&date="2003.5"]:4)[&date="1999.5"]:2,'
+                 'c_2000[&date="2000"]:2.5)[&date="1997.5"];\nEnd;\n')
+    t = read_lsd_nexus(str(p))
+    assert sorted(t.names) == ["a_2001", "b_2003.5", "c_2000"]
+    bl = {t.names[i]: t.branch_lengths[i] for i in range(3)}
+    assert bl == {"a_2001": 1.5, "b_2003.5": 4.0, "c_2000": 2.5}
+    from b200phylo.timetree import tip_heights_from_names
+    np.testing.assert_allclose(tip_heights_from_names(["a_2001", "b_2003.5", "c_2000"]), [2.5, 0.0, 3.5])
