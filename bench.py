@@ -208,10 +208,17 @@ def run_b200(a):
     info = eng.info()
     out = torch.zeros(1 + n_br, dtype=torch.float64, device=dev)
     stream = torch.cuda.current_stream(dev)
+    # N > 1: the engine's reduction kernel is the all-reduce (NVLink peer stores, b2p_peer_*);
+    # NCCL only if the peer mapping cannot be set up or B2P_NCCL_ALLREDUCE=1 asks for it
+    fused = False
+    if world > 1 and info["n_states"] == 4:
+        from b200phylo.parallel import attach_peers
+        fused = attach_peers(eng)
+    model.fused_allreduce = fused
 
     def step_device():
         eng.loglik_grad_device(bl_dev.data_ptr(), out.data_ptr(), out.data_ptr() + 8, stream.cuda_stream)
-        if world > 1:
+        if world > 1 and not fused:
             dist.all_reduce(out)
 
     def barrier():
@@ -290,7 +297,8 @@ def run_b200(a):
                        "total_patterns": w.n_patterns * world, "categories": w.n_categories,
                        "model": type(w.subst_model).__name__, "tree": "coalescent, seed 20261104",
                        "l2": f"no flush: per-step working set {(2 * (w.n_tips - 1) * U * info['n_states'] // 4) / 1e6:.0f} MB of partials > 126 MB L2",
-                       "collective": "1 NCCL all-reduce of 2N-1 doubles per step" if world > 1 else "none",
+                       "collective": ("fused into the reduction kernel: NVLink peer stores + flags, sum in rank order (b2p_peer_*)" if fused
+                                      else "1 NCCL all-reduce of 2N-1 doubles per step") if world > 1 else "none",
                        "engine": {k: info[k] for k in ("warps_per_block", "cols_per_tile", "n_tiles", "grid_blocks",
                                                         "post_rounds", "pre_rounds", "tasks_per_round", "tree_depth",
                                                         "regs_per_thread", "smem_bytes", "pool_blocks", "copy_depth",

@@ -26,6 +26,7 @@ EXPORTED_SYMBOLS = (
     "b2p_set_topology", "b2p_set_tip_states", "b2p_set_pattern_weights", "b2p_set_eigen",
     "b2p_set_categories", "b2p_loglik", "b2p_loglik_grad", "b2p_loglik_grad_host",
     "b2p_set_profiling", "b2p_last_kernel_ms", "b2p_kernel_ms_stats", "b2p_get_branch_partials",
+    "b2p_peer_export", "b2p_peer_attach", "b2p_peer_status",
 )
 
 
@@ -86,6 +87,9 @@ def load_library():
     lib.b2p_last_kernel_ms.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
     lib.b2p_kernel_ms_stats.argtypes = [vp, dp, ctypes.POINTER(ctypes.c_int32)]
     lib.b2p_get_branch_partials.argtypes = [vp, ctypes.c_int32, dp]
+    lib.b2p_peer_export.argtypes = [vp, ctypes.c_int32, ctypes.c_char_p]
+    lib.b2p_peer_attach.argtypes = [vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_char_p]
+    lib.b2p_peer_status.argtypes = [vp, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
     for name in EXPORTED_SYMBOLS:
         if name != "b2p_last_error":
             getattr(lib, name).restype = ctypes.c_int
@@ -207,6 +211,26 @@ class Engine:
             self._h, _dptr(bl), ctypes.byref(logl), _dptr(grad) if want_grad else None),
             "b2p_loglik_grad_host")
         return float(logl.value), grad
+
+    # ------------------------------------------------------------- multi-GPU peers
+    def peer_export(self, world: int) -> bytes:
+        """Allocate this rank's receive buffer; returns its 64-byte CUDA IPC handle."""
+        buf = ctypes.create_string_buffer(64)
+        self._check(self._lib.b2p_peer_export(self._h, int(world), buf), "b2p_peer_export")
+        return buf.raw
+
+    def peer_attach(self, rank: int, world: int, handles) -> None:
+        """``handles``: every rank's export, in rank order.  From here on evaluations return
+        results already summed over ranks (the reduction kernel is the all-reduce)."""
+        blob = b"".join(handles)
+        if len(blob) != 64 * world:
+            raise ValueError("need one 64-byte handle per rank")
+        self._check(self._lib.b2p_peer_attach(self._h, int(rank), int(world), blob), "b2p_peer_attach")
+
+    def peer_status(self) -> Tuple[bool, int]:
+        a, e = ctypes.c_int32(), ctypes.c_int32()
+        self._check(self._lib.b2p_peer_status(self._h, ctypes.byref(a), ctypes.byref(e)), "b2p_peer_status")
+        return bool(a.value), int(e.value)
 
     def set_profiling(self, enabled: bool) -> None:
         self._check(self._lib.b2p_set_profiling(self._h, int(bool(enabled))), "b2p_set_profiling")

@@ -16,7 +16,7 @@ from typing import Optional, Tuple
 
 import torch
 
-__all__ = ["shard_bounds", "rank_world", "allreduce_sum_"]
+__all__ = ["shard_bounds", "rank_world", "allreduce_sum_", "attach_peers"]
 
 
 def shard_bounds(n_patterns: int, world_size: int, rank: int) -> Tuple[int, int]:
@@ -52,3 +52,46 @@ def allreduce_sum_(buf: torch.Tensor, group=None) -> torch.Tensor:
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
     return buf
+
+
+def attach_peers(engine, group=None) -> bool:
+    """Turn the engine's final reduction into the all-reduce (``b2p_peer_*``): every rank
+    exports its receive buffer, the 64-byte CUDA IPC handles are all-gathered through the
+    process group, and each rank maps its peers' buffers.  Returns False (and leaves the
+    NCCL all-reduce in charge) when there is no group, a single rank, more than 8 ranks,
+    ``B2P_NCCL_ALLREDUCE=1``, or when ANY rank fails to export/map — the decision is agreed
+    across ranks so that all of them take the same path."""
+    import os
+
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized()):
+        return False
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    if world < 2 or world > 8 or os.environ.get("B2P_NCCL_ALLREDUCE") == "1":
+        return False
+    dev = torch.device(f"cuda:{engine.device}")
+    try:
+        handle = engine.peer_export(world)
+    except Exception:
+        handle = None
+    ok = torch.tensor([1 if handle is not None else 0], dtype=torch.int32, device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+    if int(ok.item()) == 0:
+        return False
+    mine = torch.tensor(list(handle), dtype=torch.uint8, device=dev)
+    every = [torch.empty(64, dtype=torch.uint8, device=dev) for _ in range(world)]
+    dist.all_gather(every, mine, group=group)
+    try:
+        engine.peer_attach(rank, world, [bytes(t.cpu().tolist()) for t in every])
+        attached = 1
+    except Exception:
+        attached = 0
+    ok = torch.tensor([attached], dtype=torch.int32, device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+    if int(ok.item()) == 0:
+        if attached:
+            raise RuntimeError("peer attach succeeded on this rank but failed on another; cannot mix paths")
+        return False
+    dist.barrier(group=group)
+    return True

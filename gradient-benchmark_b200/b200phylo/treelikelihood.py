@@ -28,7 +28,7 @@ import torch
 
 from .alignment import Alignment, SitePattern, compress_alignment
 from .engine import Engine, EngineError
-from .parallel import allreduce_sum_, rank_world, shard_bounds
+from .parallel import allreduce_sum_, attach_peers, rank_world, shard_bounds
 from .sitemodel import ConstantSiteModel, GammaSiteModel
 from .substitution import GTR, HKY, JC69, SubstitutionModel
 from .tree import Tree
@@ -160,9 +160,9 @@ class TreeLikelihoodFunction(torch.autograd.Function):
             out[0] = logl
             if need_grad:
                 out[1:] = torch.from_numpy(grad)
-            if model.world_size > 1:
+        if model.world_size > 1 and not model.fused_allreduce:  # fused: the engine already summed over ranks
+            if not out.is_cuda:
                 out = out.to(f"cuda:{eng.device}")
-        if model.world_size > 1:
             allreduce_sum_(out, model.group)
             out = out.to(bl.device)
         if need_grad:
@@ -221,6 +221,11 @@ class TreeLikelihoodModel:
         self.engine.set_tip_states(site_pattern.masks)
         self.engine.set_pattern_weights(site_pattern.weights)
         self.update_model()
+        # multi-GPU: the engine's own reduction kernel doubles as the all-reduce over NVLink
+        # peer memory; NCCL stays the path only where that cannot be set up
+        self.fused_allreduce = False
+        if self.world_size > 1 and getattr(site_pattern, "n_states", 4) == 4 and rank is None:
+            self.fused_allreduce = attach_peers(self.engine, group)
 
     def update_model(self) -> None:
         """Push the substitution / site model to the engine (call after changing them)."""

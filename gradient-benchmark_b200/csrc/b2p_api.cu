@@ -44,6 +44,14 @@ struct b2p_instance {
   long long* d_trace = nullptr;  // B2P_TRACE=<file>: per-round clock stamps of CTA 0 (debug)
   double* d_bl_stage = nullptr;   // for the host-buffer entry point
   double* d_out_stage = nullptr;  // [1 + 2N-2]
+  // multi-GPU: peer-mapped receive buffers of the fused reduce + all-reduce (b2p_peer_*)
+  struct Peer {
+    int rank = -1, world = 0;
+    unsigned char* own = nullptr;            // [2][world][2N-1] doubles, then [2][world] flags, ticket, err
+    void* mapped[kMaxPeers] = {};            // peers' buffers opened through CUDA IPC (own entry: own)
+    unsigned long long epoch = 0;
+    bool attached = false;
+  } peer;
   double* h_pin_in = nullptr;
   double* h_pin_out = nullptr;
   cudaStream_t own_stream = nullptr;
@@ -285,9 +293,12 @@ const char* b2p_last_error(const b2p_instance* h) {
   return h ? h->err.c_str() : g_create_error.c_str();
 }
 
+static void peer_release(b2p_instance* h);
+
 int b2p_destroy(b2p_instance* h) {
   if (!h) return B2P_OK;
   cudaSetDevice(h->cfg.device);
+  peer_release(h);
   cudaFree(h->d_records); cudaFree(h->d_mat_dst); cudaFree(h->d_mats);
   cudaFree(h->d_tips); cudaFree(h->d_tips_raw); cudaFree(h->d_tip_order); cudaFree(h->d_weights); cudaFree(h->d_msg); cudaFree(h->d_pre);
   cudaFree(h->d_lpart); cudaFree(h->d_trace); cudaFree(h->d_gpart); cudaFree(h->d_bl_stage); cudaFree(h->d_out_stage);
@@ -440,6 +451,28 @@ static void fill_walk_params(const b2p_instance* h, bool grad, WalkParams<T>& p)
   }
 }
 
+static size_t peer_recv_bytes(const b2p_instance* h, int world) {
+  return sizeof(double) * 2 * (size_t)world * (2 * (size_t)h->cfg.n_tips - 1);
+}
+
+// Arguments of the fused reduction + all-reduce for the next evaluation (advances the epoch).
+static PeerArgs peer_args(b2p_instance* h) {
+  PeerArgs pa{};
+  b2p_instance::Peer& pr = h->peer;
+  pa.rank = pr.rank; pa.world = pr.world; pa.n_out = 2 * h->cfg.n_tips - 1;
+  pa.epoch = ++pr.epoch;
+  const size_t recv = peer_recv_bytes(h, pr.world);
+  for (int r = 0; r < pr.world; ++r) {
+    unsigned char* base = (unsigned char*)pr.mapped[r];
+    pa.recv[r] = (double*)base;
+    pa.flags[r] = (unsigned long long*)(base + recv);
+  }
+  unsigned char* tail = pr.own + recv + sizeof(unsigned long long) * 2 * pr.world;
+  pa.ticket = (unsigned*)tail;
+  pa.err = (unsigned*)(tail + 8);
+  return pa;
+}
+
 template <typename T>
 static cudaError_t launch_eval(b2p_instance* h, const double* d_bl, double* d_logl, double* d_grad,
                                cudaStream_t st) {
@@ -457,7 +490,12 @@ static cudaError_t launch_eval(b2p_instance* h, const double* d_bl, double* d_lo
   if (e != cudaSuccess) return e;
   if (h->profiling) { cudaEventRecord(h->ev1[slot], st); ++h->prof_count; }
   const int nb = d_grad ? n_br : 0;
-  reduce_kernel<<<(nb + 31) / 32 + 1, 512, 0, st>>>(h->d_gpart, h->d_lpart, h->wg.grid, nb, d_grad, d_logl);
+  if (h->peer.attached) {
+    PeerArgs pa = peer_args(h);
+    reduce_exchange_kernel<<<(nb + 31) / 32 + 1, 512, 0, st>>>(h->d_gpart, h->d_lpart, h->wg.grid, nb, d_grad, d_logl, pa);
+  } else {
+    reduce_kernel<<<(nb + 31) / 32 + 1, 512, 0, st>>>(h->d_gpart, h->d_lpart, h->wg.grid, nb, d_grad, d_logl);
+  }
   return cudaGetLastError();
 }
 
@@ -657,6 +695,77 @@ int b2p_loglik_grad_host(b2p_instance* h, const double* h_bl, double* h_logl, do
     }
   }
   return B2P_OK;
+}
+
+// ------------------------------------------------------------------ multi-GPU peer exchange
+int b2p_peer_export(b2p_instance* h, int32_t world, void* h_handle_out) {
+  if (!h || !h_handle_out) return h ? fail(h, B2P_ERR_ARG, "b2p_peer_export: null pointer") : B2P_ERR_ARG;
+  if (h->dense) return fail(h, B2P_ERR_UNSUPPORTED, "b2p_peer_export: the dense-state path all-reduces through the caller");
+  if (world < 2 || world > kMaxPeers) return fail(h, B2P_ERR_ARG, "b2p_peer_export: world must be 2..%d", kMaxPeers);
+  if (h->peer.own) return fail(h, B2P_ERR_ARG, "b2p_peer_export: already exported");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  CU(cudaSetDevice(h->cfg.device));
+  const size_t bytes = peer_recv_bytes(h, world) + sizeof(unsigned long long) * 2 * world + 16;
+  void* p = nullptr;
+  if (cudaMalloc(&p, bytes) != cudaSuccess) return fail(h, B2P_ERR_ALLOC, "b2p_peer_export: cudaMalloc(%zu) failed", bytes);
+  h->peer.own = (unsigned char*)p;
+  h->peer.world = world;
+  CU(cudaMemset(p, 0, bytes));
+  CU(cudaDeviceSynchronize());
+  cudaIpcMemHandle_t hd;
+  CU(cudaIpcGetMemHandle(&hd, p));
+  memcpy(h_handle_out, &hd, sizeof hd);
+  return B2P_OK;
+}
+
+int b2p_peer_attach(b2p_instance* h, int32_t rank, int32_t world, const void* h_handles) {
+  if (!h || !h_handles) return h ? fail(h, B2P_ERR_ARG, "b2p_peer_attach: null pointer") : B2P_ERR_ARG;
+  b2p_instance::Peer& pr = h->peer;
+  if (!pr.own || pr.world != world) return fail(h, B2P_ERR_ARG, "b2p_peer_attach: call b2p_peer_export(world) first");
+  if (rank < 0 || rank >= world) return fail(h, B2P_ERR_ARG, "b2p_peer_attach: rank out of range");
+  if (pr.attached) return fail(h, B2P_ERR_ARG, "b2p_peer_attach: already attached");
+  CU(cudaSetDevice(h->cfg.device));
+  for (int r = 0; r < world; ++r) {
+    if (r == rank) { pr.mapped[r] = pr.own; continue; }
+    cudaIpcMemHandle_t hd;
+    memcpy(&hd, (const unsigned char*)h_handles + 64 * (size_t)r, sizeof hd);
+    void* p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, hd, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      for (int q = 0; q < r; ++q)
+        if (q != rank && pr.mapped[q]) { cudaIpcCloseMemHandle(pr.mapped[q]); pr.mapped[q] = nullptr; }
+      cudaGetLastError();
+      return fail(h, B2P_ERR_CUDA, "b2p_peer_attach: cudaIpcOpenMemHandle(rank %d): %s", r, cudaGetErrorString(e));
+    }
+    pr.mapped[r] = p;
+  }
+  pr.rank = rank;
+  pr.attached = true;
+  return B2P_OK;
+}
+
+int b2p_peer_status(b2p_instance* h, int32_t* attached, int32_t* error_word) {
+  if (!h) return B2P_ERR_ARG;
+  if (attached) *attached = h->peer.attached ? 1 : 0;
+  if (error_word) {
+    *error_word = 0;
+    if (h->peer.own) {
+      CU(cudaSetDevice(h->cfg.device));
+      unsigned e = 0;
+      const size_t off = peer_recv_bytes(h, h->peer.world) + sizeof(unsigned long long) * 2 * h->peer.world + 8;
+      CU(cudaMemcpy(&e, h->peer.own + off, sizeof e, cudaMemcpyDeviceToHost));
+      *error_word = (int32_t)e;
+    }
+  }
+  return B2P_OK;
+}
+
+static void peer_release(b2p_instance* h) {
+  b2p_instance::Peer& pr = h->peer;
+  for (int r = 0; r < pr.world; ++r)
+    if (pr.attached && r != pr.rank && pr.mapped[r]) cudaIpcCloseMemHandle(pr.mapped[r]);
+  cudaFree(pr.own);
+  pr = b2p_instance::Peer();
 }
 
 int b2p_set_profiling(b2p_instance* h, int enabled) {

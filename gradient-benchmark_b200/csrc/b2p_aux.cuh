@@ -95,4 +95,86 @@ __global__ void __launch_bounds__(512) reduce_kernel(const double* __restrict__ 
   }
 }
 
+// ------------------------------------------------------------------ K4 + all-reduce
+// Multi-GPU: every rank holds a pattern shard, the results
+// [logL, g_0 .. g_{2N-3}] must be summed over ranks.  Instead of a reduction kernel followed
+// by a library all-reduce (two launches + a ~30 us latency-bound collective for 16 KB), the
+// reduction kernel itself is the collective: each CTA stores its 32 sums straight into slot
+// `rank` of EVERY peer's receive buffer over NVLink (peer-mapped memory, plain stores), the
+// last CTA to finish publishes a flag on every peer, waits for every peer's flag, and adds
+// the `world` slots in rank order — the same order on every rank, so all ranks get the same
+// bits.  Two slot sets alternate by epoch: a rank can be at most one evaluation ahead of a
+// peer (it needs that peer's flag to finish), so the set being written is never the set
+// still being read.
+constexpr int kMaxPeers = 8;
+
+struct PeerArgs {
+  int rank, world, n_out;          // n_out = 2N-1 (slot stride; evaluation-only calls use element 0)
+  unsigned long long epoch;        // same on every rank: evaluations are issued in lock step
+  double* recv[kMaxPeers];         // [2][world][n_out] on each rank
+  unsigned long long* flags[kMaxPeers];  // [2][world] on each rank
+  unsigned* ticket;                // local CTA completion counter
+  unsigned* err;                   // local: set when a peer's flag did not arrive in time
+};
+
+__global__ void __launch_bounds__(512) reduce_exchange_kernel(const double* __restrict__ gpart,
+                                                              const double* __restrict__ lpart, int n_parts,
+                                                              int n_branches, double* __restrict__ grad,
+                                                              double* __restrict__ logl, const PeerArgs pa) {
+  __shared__ double sh[16][33];
+  __shared__ unsigned last;
+  const int x = threadIdx.x & 31, y = threadIdx.x >> 5;
+  const int set = (int)(pa.epoch & 1ull);
+  const size_t slot = ((size_t)set * pa.world + pa.rank) * pa.n_out;
+  if (blockIdx.x == gridDim.x - 1) {  // log-likelihood
+    double s = 0.0;
+    for (int g = threadIdx.x; g < n_parts; g += 512) s += lpart[g];
+    s = warp_sum(s);
+    if (x == 0) sh[y][0] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t = 0.0;
+      for (int i = 0; i < 16; ++i) t += sh[i][0];
+      for (int r = 0; r < pa.world; ++r) pa.recv[r][slot] = t;
+    }
+  } else {
+    const int b = blockIdx.x * 32 + x;
+    double s = 0.0;
+    if (b < n_branches)
+      for (int g = y; g < n_parts; g += 16) s += gpart[(size_t)g * n_branches + b];
+    sh[y][x] = s;
+    __syncthreads();
+    if (y == 0 && b < n_branches) {
+      double t = 0.0;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) t += sh[i][x];
+      for (int r = 0; r < pa.world; ++r) pa.recv[r][slot + 1 + b] = t;
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) last = atomicAdd(pa.ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
+  __syncthreads();
+  if (!last) return;
+  __threadfence_system();
+  if (threadIdx.x < pa.world) {
+    volatile unsigned long long* out = pa.flags[threadIdx.x] + (size_t)set * pa.world + pa.rank;
+    *out = pa.epoch;
+    volatile unsigned long long* in = pa.flags[pa.rank] + (size_t)set * pa.world + threadIdx.x;
+    const long long t0 = clock64();
+    while (*in < pa.epoch) {
+      if (clock64() - t0 > 8000000000ll) { *pa.err = 1u + threadIdx.x; break; }  // ~4 s: report, do not hang
+    }
+  }
+  __syncthreads();
+  __threadfence_system();
+  const double* mine = pa.recv[pa.rank] + (size_t)set * pa.world * pa.n_out;
+  for (int i = threadIdx.x; i < 1 + n_branches; i += 512) {
+    double t = 0.0;
+    for (int r = 0; r < pa.world; ++r) t += __ldcg(mine + (size_t)r * pa.n_out + i);
+    if (i == 0) *logl = t; else grad[i - 1] = t;
+  }
+  if (threadIdx.x == 0) *pa.ticket = 0u;
+}
+
 }  // namespace b2p

@@ -140,6 +140,23 @@ int b2p_loglik_grad(b2p_instance* h, const double* d_bl, double* d_logl, double*
 int b2p_loglik_grad_host(b2p_instance* h, const double* h_bl, double* h_logl,
                          double* h_grad);
 
+/* Multi-GPU, one process per GPU: pattern shards per rank, results summed
+ * over ranks.  With peers attached the final reduction kernel of every evaluation IS the
+ * all-reduce: it stores its sums into every peer's receive buffer over NVLink (CUDA IPC
+ * peer-mapped memory), exchanges flags and adds the slots in rank order, so d_logl / d_grad
+ * come back already summed over all ranks, bit-identical on every rank, with no library
+ * collective and no extra launch.  All ranks must then issue their evaluations in the same
+ * order (as with any collective).  Set-up, once per instance, on every rank:
+ *   b2p_peer_export(h, world, handle64)        allocate the receive buffer, get its IPC handle
+ *   <all-gather the 64-byte handles by any means, e.g. torch.distributed>
+ *   b2p_peer_attach(h, rank, world, handles)   open the peers' buffers ([world][64] bytes)
+ * b2p_peer_status reports whether peers are attached and a nonzero error word if a peer's
+ * flag ever failed to arrive within ~4 s (the kernel then gives up instead of hanging).
+ * world <= 8 (one NVSwitch domain); 4-state instances only. */
+int b2p_peer_export(b2p_instance* h, int32_t world, void* h_handle_out);
+int b2p_peer_attach(b2p_instance* h, int32_t rank, int32_t world, const void* h_handles);
+int b2p_peer_status(b2p_instance* h, int32_t* attached, int32_t* error_word);
+
 /* Kernel timing for roofline reports: when enabled, the traversal kernel of every
  * evaluation is bracketed by CUDA events on the evaluation's stream;
  * b2p_last_kernel_ms synchronises on the last pair and returns its duration. */
