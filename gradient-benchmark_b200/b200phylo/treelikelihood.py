@@ -133,8 +133,9 @@ class TreeLikelihoodFunction(torch.autograd.Function):
 
     ``branch_lengths`` may live on the engine's CUDA device (zero-copy, asynchronous on
     the current stream) or on the host (pinned staging inside ``b2p_loglik_grad_host``).
-    With an initialised process group the per-rank partial results are summed with one
-    all-reduce of ``2N-1`` doubles.
+    With an initialised process group the per-rank results are summed over ranks: inside
+    the engine's reduction kernel over NVLink peer memory (``model.fused_allreduce``), else
+    with one NCCL all-reduce of ``2N-1`` doubles.
     """
 
     @staticmethod
