@@ -46,6 +46,9 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="jc69_1000x10k")
     ap.add_argument("--precision", default="float64", choices=["float64", "float32"])
+    ap.add_argument("--patterns", type=int, default=0,
+                    help="site patterns per GPU (0: the workload's own size); e.g. --workload gtr_g4_5000x100k "
+                         "--patterns 12500 --gpus 8 is BASELINE configs[3]")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -118,9 +121,9 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def build_workload(name, precision, rank):
+def build_workload(name, precision, rank, n_patterns=0):
     from b200phylo.workloads import SEQ_SEED, make_workload
-    return make_workload(name, precision=precision, seq_seed=SEQ_SEED + rank)
+    return make_workload(name, precision=precision, seq_seed=SEQ_SEED + rank, n_patterns=n_patterns or None)
 
 
 def cpu_port_rate(w, seconds, n_threads=0, min_evals=3):
@@ -154,7 +157,7 @@ def run_reference(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    w = build_workload(a.workload, a.precision, 0)
+    w = build_workload(a.workload, a.precision, 0, a.patterns)
     fn, cores = cpu_port(w)
     for _ in range(max(a.warmup, 1)):
         fn()
@@ -198,7 +201,7 @@ def run_b200(a):
     if world != a.gpus and rank == 0:
         print(f"bench.py: --gpus {a.gpus} but WORLD_SIZE={world}; using {world}", file=sys.stderr)
 
-    w = build_workload(a.workload, a.precision, rank)
+    w = build_workload(a.workload, a.precision, rank, a.patterns)
     n_br = 2 * w.n_tips - 2
     # world_size=1 on the model: each rank already holds exactly its own shard
     bl_dev = torch.tensor(w.tree.branch_lengths, dtype=torch.float64, device=dev)

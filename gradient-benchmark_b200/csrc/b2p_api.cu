@@ -371,7 +371,7 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   if (const char* s = getenv("B2P_NT")) nt_force = atoi(s);
   if (const char* s = getenv("B2P_CT")) ct_force = atoi(s);
   if (const char* s = getenv("B2P_DEPTH")) depth = atoi(s);
-  int n_copy = 2, cpt = 2;
+  int n_copy = 3, cpt = 2;  // three copy warps issuing every bulk copy measured best (profiles/r01_sweep_copy_warps.txt)
   if (const char* s = getenv("B2P_NP")) n_copy = std::max(1, std::min(4, atoi(s)));
   if (const char* s = getenv("B2P_CPT")) cpt = atoi(s) == 1 ? 1 : 2;
   h->ctas_per_sm = 1;
@@ -431,6 +431,7 @@ static void fill_walk_params(const b2p_instance* h, bool grad, WalkParams<T>& p)
   const WalkGeometry& g = h->wg;
   p.n_tiles = g.n_tiles; p.rounds_run = grad ? h->plan.rounds : h->plan.rounds_post;
   p.n_branches = 2 * N - 2; p.n_cat = K; p.n_cols = P * K; p.n_patterns = P; p.n_copy_warps = g.n_copy_warps;
+  p.cw_loads = getenv("B2P_CW_LOADS") ? std::max(0, std::min(atoi(getenv("B2P_CW_LOADS")), g.nt / 32 - g.n_copy_warps)) : 0;
   p.ct = g.ct; p.ts = g.ts; p.cpw = g.cpw; p.wn = g.wn; p.stages = g.stages; p.depth = g.depth;
   p.blk = g.blk; p.plane = g.ct * 16; p.ct_pad = g.ct_pad; p.mat_stride = g.mat_stride;
   p.frame_bytes = g.frame_bytes; p.off_frame = g.off_frame; p.rel_cr = g.rel_cr; p.rel_mats = g.rel_mats;

@@ -41,6 +41,7 @@ template <typename T>
 struct WalkParams {
   int n_tiles, rounds_run, n_branches, n_cat;
   int n_cols, n_patterns, n_copy_warps, wn;
+  int cw_loads;  // loads of the next round issued by the compute warps, one each (0: the copy warps issue all)
   int ct, ts, cpw, stages, depth;
   int blk, plane, ct_pad, mat_stride;
   int frame_bytes, off_frame, rel_cr, rel_mats, rel_tips;  // rel_ir == 0
@@ -525,7 +526,7 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
         if (tr) trow[5] = clock64();
 #endif
         // the first loads of the list are issued by the compute warps, one each (below)
-        for (unsigned j = first_copy_warp + pw + np * lane; j < n_loads; j += 32 * np) {
+        for (unsigned j = p.cw_loads + pw + np * lane; j < n_loads; j += 32 * np) {
           const uint4 jb = lds_u4(jobs + j * 16);
           bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar);
         }
@@ -551,10 +552,12 @@ __global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ Wal
           }
         }
         const bool live = (d.flags & WF_LIVE) != 0;
-        // ---- one load of round q + depth per compute warp (a bulk copy costs its issuing warp
-        // ~100 cycles: the copy warps alone would be the critical path of the round).  In the
-        // longer pre-order rounds it is placed after the operand reads so that the two overlap.
-        const bool my_job = lane == 0 && q + D < R && (unsigned)warp < hdr.x;
+        // ---- optionally (cw_loads > 0) one load of round q + depth per compute warp: a bulk copy
+        // costs its issuing warp 100-300 cycles, so with few copy warps these can be the round's
+        // critical path; with three copy warps they are not, and the compute warps keep the
+        // cycles (default cw_loads = 0).  In the longer pre-order rounds the issue is placed
+        // after the operand reads so that the two overlap.
+        const bool my_job = lane == 0 && q + D < R && (unsigned)warp < hdr.x && warp < p.cw_loads;
         const unsigned bar_next = bar0 + 8 * (st == 0 ? S - 1 : st - 1);
         if (my_job && pass == 0) {
           const uint4 jb = lds_u4(frame + 16 + warp * 16);
