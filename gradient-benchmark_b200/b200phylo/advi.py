@@ -49,7 +49,7 @@ class _Holder:
 
 def run_advi(fasta: str, newick: str, iterations: int, lr: float = 1e-4, rate_init: float = 0.001,
              theta_init: float = 3.0, seed: int = 1, print_every: int = 100, device: int = 0,
-             out=sys.stdout, precision: str = "float64") -> dict:
+             out=sys.stdout, precision: str = "float64", cuda_graph: bool = True) -> dict:
     aln = read_fasta(fasta)
     with open(newick) as fh:
         tree = Tree.from_newick(fh.read(), taxa=aln.names)
@@ -75,7 +75,7 @@ def run_advi(fasta: str, newick: str, iterations: int, lr: float = 1e-4, rate_in
                                precision=precision, device=device)
     coal = ConstantCoalescentModel("coalescent", tm, theta)
     joint = JointTimeTreeDensity(like, tm, coal, include_jacobian=True)
-    opt = torch.optim.Adam([mu, log_sigma], lr=lr, maximize=True)
+    opt = torch.optim.Adam([mu, log_sigma], lr=lr, maximize=True, capturable=cuda_graph)
     const_entropy = 0.5 * dim * (1.0 + math.log(2.0 * math.pi))
 
     def elbo_sample() -> torch.Tensor:
@@ -90,24 +90,59 @@ def run_advi(fasta: str, newick: str, iterations: int, lr: float = 1e-4, rate_in
         log_prior = -zt.sum() + (math.log(1000.0) - 1000.0 * torch.exp(zc)).sum()  # OneOnX(theta), Exponential(1000)(rate)
         return joint() + log_det + log_prior + log_sigma.sum() + const_entropy
 
+    def iteration() -> torch.Tensor:
+        opt.zero_grad(set_to_none=True)
+        elbo = elbo_sample()
+        elbo.backward()
+        opt.step()
+        return elbo.detach()
+
     out.write(f"  {'iter':>6}  {'ELBO':>16}  {'seconds':>10}\n")
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     elbo_val = float("nan")
     history = []
-    for it in range(1, iterations + 1):
-        opt.zero_grad(set_to_none=True)
-        elbo = elbo_sample()
-        elbo.backward()
-        opt.step()
+
+    def report(it: int, elbo: torch.Tensor) -> None:
+        nonlocal elbo_val
         if it % print_every == 0 or it == 1 or it == iterations:
-            elbo_val = float(elbo.detach())
+            elbo_val = float(elbo)
             history.append((it, elbo_val))
             out.write(f"  {it:6d}  {elbo_val:16.3f}  {time.perf_counter() - t0:10.3f}\n")
             out.flush()
+
+    # One iteration = sample, density + gradient (b2p_joint_density_grad), Adam.  Its GPU work is
+    # a few hundred microseconds; issued call by call the Python interpreter is the bottleneck.
+    # So after three eager iterations the whole iteration is captured once into a CUDA graph
+    # (the engine launches on torch's current stream, so its kernels are captured like torch's
+    # own) and the remaining iterations are graph replays.
+    it = 0
+    graph = None
+    if cuda_graph and iterations > 4:
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                it += 1
+                report(it, iteration())
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        it += 1
+        with torch.cuda.graph(graph):
+            static_elbo = iteration()
+        graph.replay()  # capture does not execute: this is iteration `it`
+        report(it, static_elbo)
+    while it < iterations:
+        it += 1
+        if graph is not None:
+            graph.replay()
+            report(it, static_elbo)
+        else:
+            report(it, iteration())
     torch.cuda.synchronize()
     wall = time.perf_counter() - t0
-    res = {"iterations": iterations, "seconds": wall, "iters_per_s": iterations / wall, "elbo": elbo_val,
+    res = {"iterations": iterations, "seconds": wall, "cuda_graph": graph is not None, "iters_per_s": iterations / wall, "elbo": elbo_val,
            "history": history, "n_taxa": n, "n_patterns": sp.n_patterns,
            "rate": float(torch.exp(mu[n - 1]).detach()), "theta": float(torch.exp(mu[n]).detach()),
            "root_height": shift + float(torch.exp(mu[n - 2]).detach())}
@@ -133,6 +168,7 @@ def main(argv: Optional[List[str]] = None) -> int:
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--print_every", type=int, default=100)
     ap.add_argument("--device", type=int, default=0)
+    ap.add_argument("--no_cuda_graph", action="store_true", help="issue every iteration call by call")
     ap.add_argument("-d", "--dtype", choices=["float64", "float32"], default="float64")
     a = ap.parse_args(argv)
     if a.elbo_samples != 1:
@@ -141,7 +177,7 @@ def main(argv: Optional[List[str]] = None) -> int:
         print("b200phylo-advi: no CUDA device; this engine has no CPU fallback", file=sys.stderr)
         return 2
     res = run_advi(a.input, a.tree, a.iter, a.lr, a.rate_init, seed=a.seed, print_every=a.print_every,
-                   device=a.device, precision=a.dtype)
+                   device=a.device, precision=a.dtype, cuda_graph=not a.no_cuda_graph)
     sys.stdout.write(f"Ran inference for {res['iterations']} iterations in {res['seconds']:.3f} s "
                      f"({res['iters_per_s']:.1f} iterations/s)\n")
     return 0

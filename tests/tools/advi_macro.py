@@ -33,7 +33,8 @@ with tempfile.TemporaryDirectory() as d:
     write_fasta(fa, aln)
     open(nw, "w").write(time_tree.to_newick(17))
     buf = io.StringIO()
-    res = run_advi(fa, nw, iters, lr=1e-4, rate_init=0.001, print_every=max(1, iters // 10), out=buf)
+    res = run_advi(fa, nw, iters, lr=1e-4, rate_init=0.001, print_every=max(1, iters // 10), out=buf,
+                   cuda_graph=os.environ.get("B2P_ADVI_EAGER") != "1")
 print(buf.getvalue())
 res["history"] = res["history"][-3:]
 res["sites"] = sites
