@@ -151,9 +151,9 @@ int b2p_timetree_create(int32_t n_tips, const int32_t* h_triples, const double* 
     return bail(rc);
   std::vector<double> zeros(6 * (size_t)M + 8, 0.0), zev(n_nodes, 0.0);
   std::vector<unsigned> zt(1, 0u);
-  const double *work = nullptr, *ev_t = nullptr, *ev_c = nullptr;
+  const double *work = nullptr, *ev_t = nullptr;
   const unsigned* ticket = nullptr;
-  if ((rc = tt_upload(t, zeros, &work)) || (rc = tt_upload(t, zev, &ev_t)) || (rc = tt_upload(t, zev, &ev_c)) ||
+  if ((rc = tt_upload(t, zeros, &work)) || (rc = tt_upload(t, zev, &ev_t)) ||
       (rc = tt_upload(t, zt, &ticket)))
     return bail(rc);
   {
@@ -162,7 +162,7 @@ int b2p_timetree_create(int32_t n_tips, const int32_t* h_triples, const double* 
     if ((rc = tt_upload(t, zj, &jp))) return bail(rc);
     t->joint = const_cast<double*>(jp);
   }
-  d.work = const_cast<double*>(work); d.ev_t = const_cast<double*>(ev_t); d.ev_c = const_cast<double*>(ev_c);
+  d.work = const_cast<double*>(work); d.ev_t = const_cast<double*>(ev_t);
   d.ticket = const_cast<unsigned*>(ticket);
   // shared-memory footprints: heights: {r, b}, h (double) + parent position + {first, count} per level;
   // vjp: a, w, r (double) + two child positions + {first, count} per level

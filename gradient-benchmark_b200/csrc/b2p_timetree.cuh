@@ -46,7 +46,6 @@ struct TTDev {
   // scratch
   double* work;             // [6 M + 8] fallback for the level arrays when they do not fit shared memory
   double* ev_t;             // [2N-1] coalescent: per-CTA partial sums
-  double* ev_c;             // unused
   unsigned* ticket;         // coalescent: CTA completion counter
 };
 

@@ -204,3 +204,19 @@ def test_codon_missing_states_and_rescaling():
     assert np.isfinite(logl) and logl < -1e4
     assert rel_err(logl, ol) < TOL_LOGL_F64, (logl, ol)
     assert grad_err(grad, og) < TOL_GRAD_F64
+
+
+@pytest.mark.parametrize("env", [{"B2P_NP": "2", "B2P_CW_LOADS": "14"}, {"B2P_NP": "1"}, {"B2P_NP": "4", "B2P_CW_LOADS": "3"},
+                                 {"B2P_CPT": "1"}, {"B2P_DEPTH": "2"}])
+def test_kernel_knobs_keep_parity(env, monkeypatch):
+    """The tuning knobs (copy warps, who issues the loads, columns per thread, prefetch depth)
+    select different schedules of the same arithmetic: results must not move."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    for name, nt, npat in (("jc69_1000x10k", 120, 900), ("hky_g4_flu", 90, 333)):
+        w = make_workload(name, n_tips=nt, n_patterns=npat)
+        eng = make_engine(w)
+        logl, grad = eng.loglik_grad_host(w.tree.branch_lengths)
+        ol, og = oracle_c(w)
+        assert rel_err(logl, ol) < 1e-10 and grad_err(grad, og) < 1e-8, (env, name)
+        eng.close()
