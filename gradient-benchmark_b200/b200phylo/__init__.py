@@ -4,7 +4,7 @@ Host side (Python) over ``libb200phylo.so`` (C ABI, ``include/b200phylo.h``; han
 sm_100a kernels in ``../csrc``).  No CPU fallback.
 """
 from .alignment import Alignment, SitePattern, compress_alignment, read_fasta, write_fasta  # noqa: F401
-from .sitemodel import ConstantSiteModel, GammaSiteModel  # noqa: F401
+from .sitemodel import ConstantSiteModel, GammaSiteModel, WeibullSiteModel  # noqa: F401
 from .substitution import GTR, HKY, JC69, GeneralReversible  # noqa: F401
 from .tree import Tree, parse_newick, simulate_tree  # noqa: F401
 

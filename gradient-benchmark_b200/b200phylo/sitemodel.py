@@ -10,7 +10,7 @@ from __future__ import annotations
 
 import numpy as np
 
-__all__ = ["ConstantSiteModel", "GammaSiteModel"]
+__all__ = ["ConstantSiteModel", "GammaSiteModel", "WeibullSiteModel"]
 
 
 class ConstantSiteModel:
@@ -37,4 +37,20 @@ class GammaSiteModel:
             rates = (upper - lower) * k
         self.alpha = a
         self.rates = np.asarray(rates, dtype=np.float64)
+        self.weights = np.full(k, 1.0 / k)
+
+
+class WeibullSiteModel:
+    """Discretised Weibull(shape, scale 1) rate heterogeneity as torchtree parameterises it
+    (upstream recall): K equal-weight categories at the quantiles of the bin
+    midpoints, ``r_k = (-log(1 - (2k+1)/(2K)))^(1/shape)``, normalised to mean 1.  The Weibull
+    quantile is closed-form, which is why autodiff frameworks prefer it to the Gamma."""
+
+    def __init__(self, shape: float = 1.0, categories: int = 4):
+        k = int(categories)
+        a = float(shape)
+        q = (2.0 * np.arange(k) + 1.0) / (2.0 * k)
+        rates = np.power(-np.log1p(-q), 1.0 / a)
+        self.shape = a
+        self.rates = rates / rates.mean()
         self.weights = np.full(k, 1.0 / k)

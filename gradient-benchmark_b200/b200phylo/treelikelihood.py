@@ -29,7 +29,7 @@ import torch
 from .alignment import Alignment, SitePattern, compress_alignment
 from .engine import Engine, EngineError
 from .parallel import allreduce_sum_, attach_peers, rank_world, shard_bounds
-from .sitemodel import ConstantSiteModel, GammaSiteModel
+from .sitemodel import ConstantSiteModel, GammaSiteModel, WeibullSiteModel
 from .substitution import GTR, HKY, JC69, SubstitutionModel
 from .tree import Tree
 
@@ -386,7 +386,7 @@ def _site_model_from_json(spec):
         if isinstance(shape, dict):
             shape = shape.get("tensor")
         if kind == "WeibullSiteModel":
-            raise ValueError("WeibullSiteModel is not built; use GammaSiteModel")
+            return WeibullSiteModel(float(np.asarray(shape).reshape(-1)[0]), int(spec.get("categories", 4)))
         return GammaSiteModel(float(np.asarray(shape).reshape(-1)[0]), int(spec.get("categories", 4)))
     raise ValueError(f"unsupported site model type {spec.get('type')!r}")
 

@@ -145,3 +145,14 @@ def test_read_lsd_nexus(tmp_path):
     assert bl == {"a_2001": 1.5, "b_2003.5": 4.0, "c_2000": 2.5}
     from b200phylo.timetree import tip_heights_from_names
     np.testing.assert_allclose(tip_heights_from_names(["a_2001", "b_2003.5", "c_2000"]), [2.5, 0.0, 3.5])
+
+
+def test_weibull_site_model():
+    from b200phylo.sitemodel import WeibullSiteModel
+    from b200phylo import treelikelihood as tl
+    m = WeibullSiteModel(1.0, 4)  # shape 1 = exponential: quantiles -log(1-q)
+    q = -np.log1p(-np.array([0.125, 0.375, 0.625, 0.875]))
+    np.testing.assert_allclose(m.rates, q / q.mean(), rtol=1e-15)
+    assert m.rates.mean() == pytest.approx(1.0) and np.all(np.diff(m.rates) > 0) and m.weights.sum() == pytest.approx(1.0)
+    j = tl._site_model_from_json({"type": "WeibullSiteModel", "shape": {"tensor": [0.7]}, "categories": 6})
+    assert len(j.rates) == 6 and j.rates.mean() == pytest.approx(1.0)
