@@ -26,7 +26,7 @@ EXPORTED_SYMBOLS = (
     "b2p_set_topology", "b2p_set_tip_states", "b2p_set_pattern_weights", "b2p_set_eigen",
     "b2p_set_categories", "b2p_loglik", "b2p_loglik_grad", "b2p_loglik_grad_host",
     "b2p_set_profiling", "b2p_last_kernel_ms", "b2p_kernel_ms_stats", "b2p_get_branch_partials",
-    "b2p_peer_export", "b2p_peer_attach", "b2p_peer_status",
+    "b2p_peer_export", "b2p_peer_attach", "b2p_peer_status", "b2p_set_gradient_operator",
 )
 
 
@@ -87,6 +87,7 @@ def load_library():
     lib.b2p_last_kernel_ms.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
     lib.b2p_kernel_ms_stats.argtypes = [vp, dp, ctypes.POINTER(ctypes.c_int32)]
     lib.b2p_get_branch_partials.argtypes = [vp, ctypes.c_int32, dp]
+    lib.b2p_set_gradient_operator.argtypes = [vp, dp, dp]
     lib.b2p_peer_export.argtypes = [vp, ctypes.c_int32, ctypes.c_char_p]
     lib.b2p_peer_attach.argtypes = [vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_char_p]
     lib.b2p_peer_status.argtypes = [vp, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
@@ -211,6 +212,19 @@ class Engine:
             self._h, _dptr(bl), ctypes.byref(logl), _dptr(grad) if want_grad else None),
             "b2p_loglik_grad_host")
         return float(logl.value), grad
+
+    def set_gradient_operator(self, op=None, scale=None) -> None:
+        """Replace (Q, category rates) in the pre-order contraction by a 4x4 operator and a
+        per-category scale (``None`` restores the branch-length gradient)."""
+        if op is None:
+            self._check(self._lib.b2p_set_gradient_operator(self._h, None, None), "b2p_set_gradient_operator")
+            return
+        a = np.ascontiguousarray(op, dtype=np.float64).reshape(16)
+        sc = None if scale is None else np.ascontiguousarray(scale, dtype=np.float64)
+        if sc is not None and sc.shape != (self.n_categories,):
+            raise ValueError("scale must have one entry per rate category")
+        self._check(self._lib.b2p_set_gradient_operator(self._h, _dptr(a), _dptr(sc) if sc is not None else None),
+                    "b2p_set_gradient_operator")
 
     # ------------------------------------------------------------- multi-GPU peers
     def peer_export(self, world: int) -> bytes:

@@ -64,6 +64,10 @@ struct b2p_instance {
   double freqs[4]{};
   double qmat[16]{};
   double cat_w[kMaxCat]{};
+  // b2p_set_gradient_operator: what the pre-order pass contracts instead of (Q, rates)
+  bool grad_op_set = false;
+  double grad_op[16]{};
+  double grad_scale[kMaxCat]{};
   // dense-state path (5..64 states, b2p_dense.cuh): null for 4-state instances
   struct Dense {
     int S = 0, cols_pad = 0, n_tiles = 0;
@@ -445,10 +449,10 @@ static void fill_walk_params(const b2p_instance* h, bool grad, WalkParams<T>& p)
   p.msg = (unsigned char*)h->d_msg; p.pre = (unsigned char*)h->d_pre; p.tips = h->d_tips;
   p.weights = h->d_weights; p.lpart = h->d_lpart; p.gpart = h->d_gpart; p.trace = h->d_trace;
   for (int i = 0; i < 4; ++i) p.freqs[i] = h->freqs[i];
-  for (int i = 0; i < 16; ++i) p.q[i] = (T)h->qmat[i];
+  for (int i = 0; i < 16; ++i) p.q[i] = (T)(h->grad_op_set ? h->grad_op[i] : h->qmat[i]);
   for (int k = 0; k < kMaxCatW; ++k) {
     p.cat_w[k] = k < K ? h->cat_w[k] : 0.0;
-    p.rates[k] = k < K ? h->model.rates[k] : 0.0;
+    p.rates[k] = k < K ? (h->grad_op_set ? h->grad_scale[k] : h->model.rates[k]) : 0.0;
   }
 }
 
@@ -639,6 +643,16 @@ int b2p_set_categories(b2p_instance* h, const double* rates, const double* weigh
     h->cat_w[k] = weights[k];
   }
   h->have_cats = true;
+  return B2P_OK;
+}
+
+int b2p_set_gradient_operator(b2p_instance* h, const double* h_op, const double* h_scale) {
+  if (!h) return B2P_ERR_ARG;
+  if (h->dense) return fail(h, B2P_ERR_UNSUPPORTED, "b2p_set_gradient_operator: 4-state instances only");
+  if (!h_op) { h->grad_op_set = false; return B2P_OK; }
+  for (int i = 0; i < 16; ++i) h->grad_op[i] = h_op[i];
+  for (int k = 0; k < h->cfg.n_categories; ++k) h->grad_scale[k] = h_scale ? h_scale[k] : 1.0;
+  h->grad_op_set = true;
   return B2P_OK;
 }
 

@@ -140,6 +140,19 @@ int b2p_loglik_grad(b2p_instance* h, const double* d_bl, double* d_logl, double*
 int b2p_loglik_grad_host(b2p_instance* h, const double* h_bl, double* h_logl,
                          double* h_grad);
 
+/* Gradients w.r.t. substitution-model parameters come out of the same
+ * two passes.  The pre-order pass contracts, per branch b and category k, the pre-order
+ * vector q with A m (m = P x, the branch's post-order message); for branch lengths A = Q and
+ * the category scale is its rate.  With another operator the "gradient" output becomes
+ *     g_b = sum_p (w_p / L_p) sum_k c_k s_k  q_{b,k}^T A m_{b,k}          (c_k category weights)
+ * — with A = E_ij (a single 1) and s = a one-hot vector that is entry (i,j) of the outer-
+ * product sum G_{b,k} = sum_p (w_p / L_p) c_k q m^T, and 16 K evaluations give every G_{b,k}.
+ * Any parameter theta of Q, of the frequencies or of the category rates then has
+ *     dlogL/dtheta = sum_{b,k} < G_{b,k} P_{b,k}^{-T} , dP_{b,k}/dtheta > + sum_i (dpi_i/dtheta) G_{root child}[i][i] / pi_i,
+ * a few thousand 4x4 products the caller does (b200phylo/paramgrad.py).  h_op: 16 doubles,
+ * row-major (NULL restores Q and the rates); h_scale: K doubles (NULL = all 1). */
+int b2p_set_gradient_operator(b2p_instance* h, const double* h_op, const double* h_scale);
+
 /* Multi-GPU, one process per GPU: pattern shards per rank, results summed
  * over ranks.  With peers attached the final reduction kernel of every evaluation IS the
  * all-reduce: it stores its sums into every peer's receive buffer over NVLink (CUDA IPC
