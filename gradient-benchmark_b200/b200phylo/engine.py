@@ -246,6 +246,13 @@ class Engine:
         self._check(self._lib.b2p_peer_status(self._h, ctypes.byref(a), ctypes.byref(e)), "b2p_peer_status")
         return bool(a.value), int(e.value)
 
+    def loglik_grad_host_ptr(self, h_bl: int, h_logl: int, h_grad: Optional[int]) -> None:
+        """``b2p_loglik_grad_host`` on raw host addresses (e.g. CPU ``tensor.data_ptr()``):
+        [2N-2] doubles in, one double and optionally [2N-2] doubles out; synchronous."""
+        self._check(self._lib.b2p_loglik_grad_host(
+            self._h, ctypes.cast(h_bl, ctypes.POINTER(ctypes.c_double)), ctypes.cast(h_logl, ctypes.POINTER(ctypes.c_double)),
+            ctypes.cast(h_grad, ctypes.POINTER(ctypes.c_double)) if h_grad else None), "b2p_loglik_grad_host")
+
     def set_profiling(self, enabled: bool) -> None:
         self._check(self._lib.b2p_set_profiling(self._h, int(bool(enabled))), "b2p_set_profiling")
 

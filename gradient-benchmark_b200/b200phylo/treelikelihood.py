@@ -156,11 +156,11 @@ class TreeLikelihoodFunction(torch.autograd.Function):
             if not need_grad:
                 out = out[:1]
         else:
-            logl, grad = eng.loglik_grad_host(bl.to(torch.float64).numpy(), want_grad=need_grad)
+            # host tensors: the C entry point reads the branch lengths and writes [logL, gradient]
+            # straight from / into torch's own buffers (no numpy detour, one allocation)
+            bl64 = bl.to(torch.float64).contiguous()
             out = torch.empty(1 + (eng.n_branches if need_grad else 0), dtype=torch.float64)
-            out[0] = logl
-            if need_grad:
-                out[1:] = torch.from_numpy(grad)
+            eng.loglik_grad_host_ptr(bl64.data_ptr(), out.data_ptr(), out.data_ptr() + 8 if need_grad else None)
         if model.world_size > 1 and not model.fused_allreduce:  # fused: the engine already summed over ranks
             if not out.is_cuda:
                 out = out.to(f"cuda:{eng.device}")
