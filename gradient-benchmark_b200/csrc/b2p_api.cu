@@ -378,9 +378,17 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   int n_copy = 3, cpt = 2;  // three copy warps issuing every bulk copy measured best (profiles/r01_sweep_copy_warps.txt)
   if (const char* s = getenv("B2P_NP")) n_copy = std::max(1, std::min(4, atoi(s)));
   if (const char* s = getenv("B2P_CPT")) cpt = atoi(s) == 1 ? 1 : 2;
+  // B2P_CTAS=2: two 256-thread CTAs per SM, each with half the shared memory.  They run out of
+  // phase (separate barriers), so one's operand reads overlap the other's arithmetic.
   h->ctas_per_sm = 1;
-  const size_t smem_budget = (size_t)prop.sharedMemPerBlockOptin - 1024;  // static shared + reservation
-  if (!plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms, smem_budget, nt_force, ct_force, depth, n_copy, cpt, h->wg)) {
+  if (const char* s = getenv("B2P_CTAS")) h->ctas_per_sm = atoi(s) == 2 ? 2 : 1;
+  size_t smem_budget = (size_t)prop.sharedMemPerBlockOptin - 1024;  // static shared + reservation
+  if (h->ctas_per_sm == 2) {
+    smem_budget = ((size_t)prop.sharedMemPerMultiprocessor - 2 * 1024) / 2 - 1024;
+    nt_force = 256;
+    if (!getenv("B2P_NP")) n_copy = 2;
+  }
+  if (!plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, ct_force, depth, n_copy, cpt, h->wg)) {
     fail(h, B2P_ERR_UNSUPPORTED, "b2p_create: no kernel geometry fits shared memory (K=%d, threads=%d)", K, nt_force);
     return bail(B2P_ERR_UNSUPPORTED);
   }

@@ -423,7 +423,7 @@ __device__ __forceinline__ void fold_round(const WalkParams<T>& p, unsigned sbas
 }
 
 template <typename T, int K, int NT, int CPT>
-__global__ void __launch_bounds__(NT, 1) walk_kernel(const __grid_constant__ WalkParams<T> p) {
+__global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __grid_constant__ WalkParams<T> p) {
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ double red[NT / 32];
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;

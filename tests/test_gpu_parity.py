@@ -207,7 +207,7 @@ def test_codon_missing_states_and_rescaling():
 
 
 @pytest.mark.parametrize("env", [{"B2P_NP": "2", "B2P_CW_LOADS": "14"}, {"B2P_NP": "1"}, {"B2P_NP": "4", "B2P_CW_LOADS": "3"},
-                                 {"B2P_CPT": "1"}, {"B2P_DEPTH": "2"}])
+                                 {"B2P_CPT": "1"}, {"B2P_DEPTH": "2"}, {"B2P_CTAS": "2"}])
 def test_kernel_knobs_keep_parity(env, monkeypatch):
     """The tuning knobs (copy warps, who issues the loads, columns per thread, prefetch depth)
     select different schedules of the same arithmetic: results must not move."""
