@@ -324,12 +324,15 @@ __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThrea
       numr += qr[c][i] * dr;
     }
     if (K != 1) {
+      // the site likelihood is the sum over the pattern's K category lanes; the numerators
+      // need no such exchange: every lane adds its own category's share and the fold sums
+      // over all lanes of the slot anyway
       const T cw = (T)p.cat_w[th.k], cwr = (T)(p.cat_w[th.k] * p.rates[th.k]);
       den = group_sum<K>(den * cw, th.lane, th.kk);
-      numl = group_sum<K>(numl * cwr, th.lane, th.kk);
-      numr = group_sum<K>(numr * cwr, th.lane, th.kk);
+      numl *= cwr;
+      numr *= cwr;
     }
-    if (live && th.k == 0) {
+    if (live) {
       // K == 1: the single category's weight cancels, its rate multiplies the numerators
       const double inv = (K == 1 ? th.w[c] * p.rates[0] : th.w[c]) * fast_rcp((double)den);
       gl += (double)numl * inv;
