@@ -509,10 +509,12 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
       if (tr) trow[1] = clock64();
 #endif
       if (copier) {
-        // Copy warps: stores of round q-1's results first — the end of this round waits until
-        // they have read shared memory — then the loads of round q + depth.  Issuing them from
-        // warps of their own lets the copies overlap the arithmetic; one warp issues a bulk copy
-        // every ~100 cycles, so several share the list (job j belongs to copy warp j % n).
+        // Copy warps: the loads of round q + depth, then the stores of round q-1's results.
+        // Issuing them from warps of their own lets the copies overlap the arithmetic; one warp
+        // issues a bulk copy every ~100 cycles, so several share the lists (job j belongs to
+        // copy warp j % n).  Order within the round is free: the planner never lets a load
+        // target a block whose store is issued in the same round, nor read back a value before
+        // the round after its store completed (rules S and L, tests/tools/plan_check.cpp).
         const uint4 hdr = lds_u4(frame);
         const unsigned st_next = st == 0 ? S - 1 : st - 1;  // (q + D) % S with S = D + 1
         const unsigned bar = bar0 + 8 * st_next;
@@ -520,19 +522,21 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
         const unsigned jobs = frame + 16;
         const unsigned np = p.n_copy_warps, pw = warp - first_copy_warp;
         if (pw == 0 && lane == 0 && n_loads) mbar_expect_tx(bar, hdr.z);
+        // loads of round q + depth first: they are what the next round waits for (issued after
+        // the stores they arrived ~700 cycles late in the post-order rounds); the stores only
+        // have to have read shared memory by the end of this round
+        for (unsigned j = p.cw_loads + pw + np * lane; j < n_loads; j += 32 * np) {
+          const uint4 jb = lds_u4(jobs + j * 16);
+          bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar);
+        }
+#ifdef B2P_TRACE_CLOCKS
+        if (tr) trow[5] = clock64();
+#endif
         for (unsigned j = pw + np * lane; j < hdr.y; j += 32 * np) {
           const uint4 jb = lds_u4(jobs + (hdr.x + j) * 16);
           bulk_store(const_cast<unsigned char*>(gptr(jb.w, jb.x)), sbase + jb.y, jb.z);
         }
         bulk_commit();  // one (possibly empty) group per lane per round
-#ifdef B2P_TRACE_CLOCKS
-        if (tr) trow[5] = clock64();
-#endif
-        // the first loads of the list are issued by the compute warps, one each (below)
-        for (unsigned j = p.cw_loads + pw + np * lane; j < n_loads; j += 32 * np) {
-          const uint4 jb = lds_u4(jobs + j * 16);
-          bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar);
-        }
 #ifdef B2P_TRACE_CLOCKS
         if (tr) trow[2] = clock64();
 #endif
