@@ -388,7 +388,17 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
     nt_force = 256;
     if (!getenv("B2P_NP")) n_copy = 2;
   }
-  if (!plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, ct_force, depth, n_copy, cpt, h->wg)) {
+  bool planned = plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, ct_force, depth, n_copy, cpt, h->wg);
+  if (planned && !getenv("B2P_NP") && n_copy == 3) {
+    // The third copy warp costs a slot's worth of compute threads.  It pays (2-4 %, profiles/
+    // r01_sweep_copy_warps.txt) unless the tile width quantises badly: when two copy warps give
+    // over 15 % more tasks per round, take those (e.g. 12 500 patterns x Gamma-4: 7 slots vs 6).
+    WalkGeometry g2;
+    if (plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, ct_force, depth, 2, cpt, g2) &&
+        g2.nt == h->wg.nt && g2.ct == h->wg.ct && g2.wn * 100 > h->wg.wn * 115)
+      h->wg = g2;
+  }
+  if (!planned) {
     fail(h, B2P_ERR_UNSUPPORTED, "b2p_create: no kernel geometry fits shared memory (K=%d, threads=%d)", K, nt_force);
     return bail(B2P_ERR_UNSUPPORTED);
   }
