@@ -51,24 +51,41 @@ __global__ void __launch_bounds__(DNT) dense_transition_kernel(const double* __r
   const int b = blockIdx.x;
   if (threadIdx.x < SP) ex[threadIdx.x] = threadIdx.x < S ? exp(evals[threadIdx.x] * bl[b] * rate) : 0.0;
   __syncthreads();
-  for (int e = threadIdx.x; e < SP * SP; e += DNT) {
-    const int i = e / SP, l = e % SP;
-    double acc = 0.0;
-    if (i < S && l < S)
-      for (int j = 0; j < S; ++j) acc += evec[i * S + j] * ex[j] * ivec[j * S + l];
-    sp[i][l] = acc;
+  // four entries per thread at a time: independent accumulators hide the latency of the 61-long chains
+  for (int e0 = threadIdx.x; e0 < SP * SP; e0 += 4 * DNT) {
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+    const int l = e0 % SP;  // e0 + u * DNT keeps the column (DNT is a multiple of SP)
+    if (l < S)
+      for (int j = 0; j < S; ++j) {
+        const double w = ex[j] * ivec[j * S + l];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int i = (e0 + u * DNT) / SP;
+          if (i < S) acc[u] = fma(evec[i * S + j], w, acc[u]);
+        }
+      }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) sp[(e0 + u * DNT) / SP][l] = acc[u];
   }
   __syncthreads();
   double* p = P + (size_t)b * SP * SP;
   double* pt = PT + (size_t)b * SP * SP;
   double* d = D + (size_t)b * SP * SP;
-  for (int e = threadIdx.x; e < SP * SP; e += DNT) {
-    const int i = e / SP, l = e % SP;
-    p[e] = sp[i][l];
-    pt[e] = sp[l][i];
-    double acc = 0.0;
-    for (int j = 0; j < S; ++j) acc += q[i * SP + j] * sp[j][l];
-    d[e] = acc;
+  for (int e0 = threadIdx.x; e0 < SP * SP; e0 += 4 * DNT) {
+    const int l = e0 % SP;
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int j = 0; j < S; ++j) {
+      const double w = sp[j][l];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) acc[u] = fma(q[((e0 + u * DNT) / SP) * SP + j], w, acc[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int e = e0 + u * DNT, i = e / SP;
+      p[e] = sp[i][l];
+      pt[e] = sp[l][i];
+      d[e] = acc[u];
+    }
   }
 }
 
@@ -194,53 +211,49 @@ __global__ void __launch_bounds__(DNT, 1) dense_post_kernel(const DenseParams p,
 }
 
 // ----------------------------------------------------------------------- pre-order level
-// grid (nodes of the depth level, tiles).  Dynamic shared memory: A, ML, MR, QL, QR (5 x 32 KB).
-__global__ void __launch_bounds__(DNT, 1) dense_pre_kernel(const DenseParams p, const DenseNode* __restrict__ nodes, int root) {
+// grid (nodes of the depth level, tiles, 2): blockIdx.z picks the child the CTA works for, so a
+// CTA holds one matrix and that child's message / outside vector (3 x 32 KB): two CTAs fit an
+// SM and a narrow level near the root spreads over twice as many SMs.  Both CTAs of a node read
+// the same three operand tiles (the second read is an L2 hit).
+__global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, const DenseNode* __restrict__ nodes, int root) {
   extern __shared__ __align__(16) unsigned char dsm[];
   double (*A)[SP] = reinterpret_cast<double (*)[SP]>(dsm);
-  double (*ML)[DT] = reinterpret_cast<double (*)[DT]>(dsm + 1 * SP * SP * 8);
-  double (*MR)[DT] = reinterpret_cast<double (*)[DT]>(dsm + 2 * SP * SP * 8);
-  double (*QL)[DT] = reinterpret_cast<double (*)[DT]>(dsm + 3 * SP * SP * 8);
-  double (*QR)[DT] = reinterpret_cast<double (*)[DT]>(dsm + 4 * SP * SP * 8);
+  double (*M)[DT] = reinterpret_cast<double (*)[DT]>(dsm + 1 * SP * SP * 8);   // the child's message
+  double (*Qc)[DT] = reinterpret_cast<double (*)[DT]>(dsm + 2 * SP * SP * 8);  // everything outside its branch
   __shared__ double red[DNT / 32];
-  __shared__ double s_inv[DT], s_numl[DT], s_numr[DT];
+  __shared__ double s_inv[DT], s_num[DT];
   const DenseNode nd = nodes[blockIdx.x];
+  const int side = blockIdx.z;
+  const int c = side ? nd.r : nd.l;
   const int col0 = blockIdx.y * DT, t = threadIdx.x;
   const int ti = t & 15, tc = t >> 4;
   for (int e = t; e < SP * DT; e += DNT) {
-    const int k = e / DT, c = e % DT;
-    const double ml = child_message(p, nd.l, k, col0 + c), mr = child_message(p, nd.r, k, col0 + c);
+    const int k = e / DT, cc = e % DT;
+    const double ml = child_message(p, nd.l, k, col0 + cc), mr = child_message(p, nd.r, k, col0 + cc);
     const double u = nd.v == root ? (k < p.n_states ? p.freqs[k] : 0.0)
-                                  : p.pre[((size_t)(nd.v - p.n_tips) * SP + k) * p.cols_pad + col0 + c];
-    ML[k][c] = ml; MR[k][c] = mr;
-    QL[k][c] = u * mr; QR[k][c] = u * ml;
+                                  : p.pre[((size_t)(nd.v - p.n_tips) * SP + k) * p.cols_pad + col0 + cc];
+    M[k][cc] = side ? mr : ml;
+    Qc[k][cc] = u * (side ? ml : mr);
   }
-  if (t < DT) { s_numl[t] = 0.0; s_numr[t] = 0.0; }
+  if (t < DT) s_num[t] = 0.0;
   __syncthreads();
-  // site likelihood (denominator) and the tip-side numerators, one column per thread
+  // site likelihood (denominator) and, for a tip child, the numerator: one column per thread
   if (t < DT) {
     double den = 0.0;
-    for (int k = 0; k < SP; ++k) den += QL[k][t] * ML[k][t];
+    for (int k = 0; k < SP; ++k) den += Qc[k][t] * M[k][t];
     s_inv[t] = p.weights[col0 + t] * p.rate / den;
-    for (int side = 0; side < 2; ++side) {
-      const int c = side ? nd.r : nd.l;
-      if (c >= p.n_tips) continue;
+    if (c < p.n_tips) {
       const unsigned code = p.codes[(size_t)c * p.cols_pad + col0 + t];
       double num = 0.0;  // missing state: Q 1 = 0
       if (code < (unsigned)p.n_states) {
         const double* d = p.D + (size_t)c * SP * SP + code;
-        const double (*Qc)[DT] = side ? QR : QL;
         for (int i = 0; i < p.n_states; ++i) num += Qc[i][t] * d[(size_t)i * SP];
       }
-      (side ? s_numr : s_numl)[t] = num;
+      s_num[t] = num;
     }
   }
-  // internal children: numerator q.(Q m) and the child's pre-order partial P^T q
-  for (int side = 0; side < 2; ++side) {
-    const int c = side ? nd.r : nd.l;
-    if (c < p.n_tips) continue;
-    double (*M)[DT] = side ? MR : ML;
-    double (*Qc)[DT] = side ? QR : QL;
+  // internal child: numerator q.(Q m) and the child's pre-order partial P^T q
+  if (c >= p.n_tips) {
     double acc[4][4];
     __syncthreads();
     load_matrix(A, p.QT);  // (Q m)[i] = sum_k Q[i][k] m[k]: A[k][i] = Q^T
@@ -253,7 +266,7 @@ __global__ void __launch_bounds__(DNT, 1) dense_pre_kernel(const DenseParams p, 
       for (int a = 0; a < 4; ++a) part += Qc[4 * ti + a][4 * tc + b] * acc[a][b];
 #pragma unroll
       for (int o = 1; o < 16; o <<= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-      if (ti == 0) (side ? s_numr : s_numl)[4 * tc + b] = part;
+      if (ti == 0) s_num[4 * tc + b] = part;
     }
     __syncthreads();
     load_matrix(A, p.P + (size_t)c * SP * SP);  // (P^T q)[j] = sum_i P[i][j] q[i]: A[i][j] = P
@@ -270,14 +283,10 @@ __global__ void __launch_bounds__(DNT, 1) dense_pre_kernel(const DenseParams p, 
     }
   }
   __syncthreads();
-  double gl = 0.0, gr = 0.0;
-  if (t < DT && p.weights[col0 + t] != 0.0) { gl = s_numl[t] * s_inv[t]; gr = s_numr[t] * s_inv[t]; }
-  const double sl = cta_sum(gl, red);
-  const double sr = cta_sum(gr, red);
-  if (t == 0) {
-    p.gpart[(size_t)blockIdx.y * p.n_branches + nd.l] = sl;
-    p.gpart[(size_t)blockIdx.y * p.n_branches + nd.r] = sr;
-  }
+  double g = 0.0;
+  if (t < DT && p.weights[col0 + t] != 0.0) g = s_num[t] * s_inv[t];
+  const double sg = cta_sum(g, red);
+  if (t == 0) p.gpart[(size_t)blockIdx.y * p.n_branches + c] = sg;
 }
 
 }  // namespace b2p
