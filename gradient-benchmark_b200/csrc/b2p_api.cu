@@ -167,8 +167,8 @@ static int dense_create(b2p_instance* h) {
   CU(cudaMallocHost((void**)&h->h_pin_in, sizeof(double) * n_br));
   CU(cudaMallocHost((void**)&h->h_pin_out, sizeof(double) * (n_br + 1)));
   CU(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
-  CU(cudaFuncSetAttribute((const void*)dense_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * SP * SP * 8));
-  CU(cudaFuncSetAttribute((const void*)dense_pre_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * SP * SP * 8));
+  CU(cudaFuncSetAttribute((const void*)dense_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * DENSE_TILE_BYTES));
+  CU(cudaFuncSetAttribute((const void*)dense_pre_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * DENSE_TILE_BYTES));
   cudaFuncAttributes fa;
   CU(cudaFuncGetAttributes(&fa, (const void*)dense_pre_kernel));
   h->regs = fa.numRegs;
@@ -276,12 +276,12 @@ static cudaError_t dense_launch(b2p_instance* h, const double* d_bl, double* d_l
   if (h->profiling) cudaEventRecord(h->ev0[slot], st);
   for (size_t L = 0; L + 1 < d->post_off.size(); ++L) {
     const int n = d->post_off[L + 1] - d->post_off[L];
-    if (n > 0) dense_post_kernel<<<dim3(n, d->n_tiles), DNT, 2 * SP * SP * 8, st>>>(p, d->nodes + d->post_off[L], d->root);
+    if (n > 0) dense_post_kernel<<<dim3(n, d->n_tiles), DNT, 2 * DENSE_TILE_BYTES, st>>>(p, d->nodes + d->post_off[L], d->root);
   }
   if (d_grad)
     for (size_t L = 0; L + 1 < d->pre_off.size(); ++L) {
       const int n = d->pre_off[L + 1] - d->pre_off[L];
-      if (n > 0) dense_pre_kernel<<<dim3(n, d->n_tiles, 2), DNT, 3 * SP * SP * 8, st>>>(p, d->nodes + d->pre_off[L], d->root);
+      if (n > 0) dense_pre_kernel<<<dim3(n, d->n_tiles, 2), DNT, 3 * DENSE_TILE_BYTES, st>>>(p, d->nodes + d->pre_off[L], d->root);
     }
   if (h->profiling) { cudaEventRecord(h->ev1[slot], st); ++h->prof_count; }
   const int nb = d_grad ? n_br : 0;
@@ -556,7 +556,7 @@ int b2p_get_info(const b2p_instance* h, b2p_info* o) {
     o->precision = h->cfg.precision; o->warps_per_block = DNT / 32; o->cols_per_tile = DT; o->n_tiles = h->dense->n_tiles;
     o->grid_blocks = h->dense->n_tiles; o->blocks_per_sm = 1; o->n_sms = h->n_sms;
     o->post_rounds = h->plan.rounds_post; o->pre_rounds = h->plan.rounds_pre; o->tree_depth = h->plan.tree_depth;
-    o->regs_per_thread = h->regs; o->smem_bytes = 3 * SP * SP * 8; o->device_bytes = h->device_bytes;
+    o->regs_per_thread = h->regs; o->smem_bytes = 3 * DENSE_TILE_BYTES; o->device_bytes = h->device_bytes;
     o->alg_bytes_loglik = (2 * N - 3) * U + N * P;
     o->alg_bytes_grad = (5 * N - 9) * U + 2 * N * P;
     return B2P_OK;

@@ -18,6 +18,9 @@ namespace b2p {
 constexpr int SP = 64;   // padded state count
 constexpr int DT = 64;   // patterns per tile
 constexpr int DNT = 256; // threads per CTA
+constexpr int LD = 72;   // row stride (doubles) of every shared-memory tile: 576 B = 64 B mod 128 B, so the
+                         // four k-rows of an mma fragment land in alternating halves of the banks
+constexpr int DENSE_TILE_BYTES = SP * LD * 8;
 
 struct DenseNode { int v, l, r, pad; };
 
@@ -90,55 +93,103 @@ __global__ void __launch_bounds__(DNT) dense_transition_kernel(const double* __r
 }
 
 // ---------------------------------------------------------------------------- helpers
-// Message of child c for (state k, column col): internal -> msg row, tip -> P[k][code] (or 1).
-__device__ __forceinline__ double child_message(const DenseParams& p, int c, int k, int col) {
-  if (c >= p.n_tips) return p.msg[((size_t)(c - p.n_tips) * SP + k) * p.cols_pad + col];
-  if (k >= p.n_states) return 0.0;
-  const unsigned code = p.codes[(size_t)c * p.cols_pad + col];
-  return code < (unsigned)p.n_states ? p.P[((size_t)c * SP + k) * SP + code] : 1.0;
-}
+// Thread t of the CTA owns, in every 64x64 operand tile, the column pair cp = 2 (t & 31) of the
+// rows kr + 8 j (kr = t >> 5, j = 0..7).  All fetches of a tile half (j = 4 h .. 4 h + 3) are issued
+// into registers before the first shared-memory store, so a thread keeps up to 16 independent
+// 16-byte loads in flight: the load phase runs at memory throughput, not at one latency per row.
+constexpr int DH = 4;  // rows per thread and tile half
 
-// acc[a][b] = sum_k A[k][4*ti + a] * X[k][4*tc + b]   (both operands in shared memory)
-__device__ __forceinline__ void tile_product(const double (*A)[SP], const double (*X)[DT], int ti, int tc, double (&acc)[4][4]) {
+// Rows k0 + 8 u (u < DH) of child c's message at columns col, col + 1: an internal child's row of
+// msg, a tip's P[k][code] (1 for a missing state, 0 in the padding rows).
+__device__ __forceinline__ void fetch_message(const DenseParams& p, int c, int col, int k0, unsigned code0, unsigned code1,
+                                              double2 (&v)[DH]) {
+  if (c >= p.n_tips) {
+    const double* g = p.msg + ((size_t)(c - p.n_tips) * SP + k0) * p.cols_pad + col;
 #pragma unroll
-  for (int a = 0; a < 4; ++a)
+    for (int u = 0; u < DH; ++u) v[u] = *reinterpret_cast<const double2*>(g + (size_t)u * 8 * p.cols_pad);
+  } else {
+    const double* g = p.P + ((size_t)c * SP + k0) * SP;
+    const bool known0 = code0 < (unsigned)p.n_states, known1 = code1 < (unsigned)p.n_states;
 #pragma unroll
-    for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
-#pragma unroll 4
-  for (int k = 0; k < SP; ++k) {
-    const double2 a0 = *reinterpret_cast<const double2*>(&A[k][4 * ti]);
-    const double2 a1 = *reinterpret_cast<const double2*>(&A[k][4 * ti + 2]);
-    const double2 x0 = *reinterpret_cast<const double2*>(&X[k][4 * tc]);
-    const double2 x1 = *reinterpret_cast<const double2*>(&X[k][4 * tc + 2]);
-    const double av[4] = {a0.x, a0.y, a1.x, a1.y}, xv[4] = {x0.x, x0.y, x1.x, x1.y};
-#pragma unroll
-    for (int a = 0; a < 4; ++a)
-#pragma unroll
-      for (int b = 0; b < 4; ++b) acc[a][b] = fma(av[a], xv[b], acc[a][b]);
-  }
-}
-
-__device__ __forceinline__ void load_matrix(double (*A)[SP], const double* __restrict__ g) {
-  for (int e = threadIdx.x * 2; e < SP * SP; e += DNT * 2)
-    *reinterpret_cast<double2*>(&A[0][0] + e) = *reinterpret_cast<const double2*>(g + e);
-}
-
-// Lazy power-of-two rescale of a register tile: the column maximum over all 64 states is
-// gathered over the 16 threads (ti = lane & 15) that share the tile's columns.
-__device__ __forceinline__ void rescale_tile(double (&acc)[4][4], int (&bumped)[4]) {
-#pragma unroll
-  for (int b = 0; b < 4; ++b) {
-    int h = 0;
-#pragma unroll
-    for (int a = 0; a < 4; ++a) h = max(h, __double2hiint(acc[a][b]));
-#pragma unroll
-    for (int o = 1; o < 16; o <<= 1) h = max(h, __shfl_xor_sync(0xffffffffu, h, o));
-    bumped[b] = (h < 0x33700000 && h > 0) ? 1 : 0;  // < 2^-200
-    if (bumped[b]) {
-#pragma unroll
-      for (int a = 0; a < 4; ++a) acc[a][b] *= Scale<double>::factor();
+    for (int u = 0; u < DH; ++u) {
+      const double fill = k0 + 8 * u < p.n_states ? 1.0 : 0.0;
+      v[u].x = known0 ? g[u * 8 * SP + code0] : fill;
+      v[u].y = known1 ? g[u * 8 * SP + code1] : fill;
     }
   }
+}
+
+__device__ __forceinline__ void fetch_codes(const DenseParams& p, int c, int col, unsigned& code0, unsigned& code1) {
+  code0 = code1 = 0;
+  if (c < p.n_tips) {
+    const uchar2 cd = *reinterpret_cast<const uchar2*>(p.codes + (size_t)c * p.cols_pad + col);
+    code0 = cd.x; code1 = cd.y;
+  }
+}
+
+__device__ __forceinline__ void fetch_matrix(const double* __restrict__ g, int k0, int cp, double2 (&v)[DH]) {
+#pragma unroll
+  for (int u = 0; u < DH; ++u) v[u] = *reinterpret_cast<const double2*>(g + (k0 + 8 * u) * SP + cp);
+}
+
+__device__ __forceinline__ void store_rows(double (*T)[LD], int k0, int cp, const double2 (&v)[DH]) {
+#pragma unroll
+  for (int u = 0; u < DH; ++u) *reinterpret_cast<double2*>(&T[k0 + 8 * u][cp]) = v[u];
+}
+
+// fp64 tensor-core product (mma.sync m8n8k4, the DMMA path of sm_100a: the 4 x 4 register-tile
+// version of this loop was bound by shared-memory wavefronts, 8 doubles read per 16 FMAs).
+// Warp w owns the 8 columns 8 w .. 8 w + 7 of the tile and all 64 rows:
+//   acc[mi][j] = sum_k A[k][8 mi + g] * X[k][8 w + 2 tg + j],  g = lane >> 2, tg = lane & 3.
+// Fragments: a = A[k0 + tg][8 mi + g], b = X[k0 + tg][8 w + g]; nine 8-byte reads feed 8 mmas
+// (2048 FMAs per warp).
+__device__ __forceinline__ void dmma(double (&c)[2], double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
+__device__ __forceinline__ void tile_product(const double (*A)[LD], const double (*X)[LD], int warp, int lane, double (&acc)[8][2]) {
+  const int g = lane >> 2, tg = lane & 3;
+#pragma unroll
+  for (int mi = 0; mi < 8; ++mi) acc[mi][0] = acc[mi][1] = 0.0;
+#pragma unroll 4
+  for (int k0 = 0; k0 < SP; k0 += 4) {
+    const double b = X[k0 + tg][8 * warp + g];
+    const double* ar = &A[k0 + tg][g];
+#pragma unroll
+    for (int mi = 0; mi < 8; ++mi) dmma(acc[mi], ar[8 * mi], b);
+  }
+}
+
+// The thread's part of a shared-memory tile in the accumulator layout: rows 8 mi + g, columns
+// 8 w + 2 tg + {0, 1}.
+__device__ __forceinline__ void read_block(const double (*T)[LD], int warp, int lane, double (&v)[8][2]) {
+  const int g = lane >> 2, tg = lane & 3;
+#pragma unroll
+  for (int mi = 0; mi < 8; ++mi) {
+    const double2 x = *reinterpret_cast<const double2*>(&T[8 * mi + g][8 * warp + 2 * tg]);
+    v[mi][0] = x.x; v[mi][1] = x.y;
+  }
+}
+
+// Sum / maximum over the 8 lanes (same tg) that share the thread's two columns; every one of them
+// receives the result.
+__device__ __forceinline__ double column_sum(double v) {
+#pragma unroll
+  for (int o = 4; o < 32; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ int column_max(int v) {
+#pragma unroll
+  for (int o = 4; o < 32; o <<= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+// 1 if the column whose entries (this thread's share) are v[.][j] lies below 2^-200
+__device__ __forceinline__ int column_small(const double (&v)[8][2], int j) {
+  int h = 0;
+#pragma unroll
+  for (int mi = 0; mi < 8; ++mi) h = max(h, __double2hiint(v[mi][j]));
+  h = column_max(h);
+  return (h < 0x33700000 && h > 0) ? 1 : 0;
 }
 
 // sum over the CTA (DNT threads), result valid in thread 0
@@ -155,45 +206,52 @@ __device__ __forceinline__ double cta_sum(double v, double* red) {
 
 // ---------------------------------------------------------------------- post-order level
 // grid (nodes of the level, tiles).  Dynamic shared memory: A [SP][SP], X [SP][DT].
-__global__ void __launch_bounds__(DNT, 1) dense_post_kernel(const DenseParams p, const DenseNode* __restrict__ nodes, int root) {
+__global__ void __launch_bounds__(DNT, 2) dense_post_kernel(const DenseParams p, const DenseNode* __restrict__ nodes, int root) {
   extern __shared__ __align__(16) unsigned char dsm[];
-  double (*A)[SP] = reinterpret_cast<double (*)[SP]>(dsm);
-  double (*X)[DT] = reinterpret_cast<double (*)[DT]>(dsm + SP * SP * 8);
+  double (*A)[LD] = reinterpret_cast<double (*)[LD]>(dsm);
+  double (*X)[LD] = reinterpret_cast<double (*)[LD]>(dsm + DENSE_TILE_BYTES);
   __shared__ double red[DNT / 32];
   const DenseNode nd = nodes[blockIdx.x];
   const int col0 = blockIdx.y * DT, t = threadIdx.x;
-  const int ti = t & 15, tc = t >> 4;
-  if (nd.v != root) load_matrix(A, p.PT + (size_t)nd.v * SP * SP);
-  for (int e = t; e < SP * DT; e += DNT) {
-    const int k = e / DT, c = e % DT;
-    X[k][c] = child_message(p, nd.l, k, col0 + c) * child_message(p, nd.r, k, col0 + c);
+  const int warp = t >> 5, lane = t & 31, g = lane >> 2, tg = lane & 3;
+  const int kr = t >> 5, cp = 2 * (t & 31);
+  const bool is_root = nd.v == root;
+  unsigned lc0, lc1, rc0, rc1;
+  fetch_codes(p, nd.l, col0 + cp, lc0, lc1);
+  fetch_codes(p, nd.r, col0 + cp, rc0, rc1);
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int k0 = kr + 32 * h;
+    double2 ml[DH], mr[DH], am[DH];
+    fetch_message(p, nd.l, col0 + cp, k0, lc0, lc1, ml);
+    fetch_message(p, nd.r, col0 + cp, k0, rc0, rc1, mr);
+    if (!is_root) fetch_matrix(p.PT + (size_t)nd.v * SP * SP, k0, cp, am);
+#pragma unroll
+    for (int u = 0; u < DH; ++u) { ml[u].x *= mr[u].x; ml[u].y *= mr[u].y; }
+    store_rows(X, k0, cp, ml);
+    if (!is_root) store_rows(A, k0, cp, am);
   }
   __syncthreads();
-  if (nd.v != root) {
+  if (!is_root) {
     // x_v is rescaled BEFORE the product (same rule as the 4-state kernel): the column
     // maximum of X decides, the product carries the factor through.
-    double acc[4][4];
-    tile_product(A, X, ti, tc, acc);
-    // column maxima of x (threads 0..DT-1, one column each)
-    __shared__ int bump[DT];
-    if (t < DT) {
-      int h = 0;
-      for (int k = 0; k < SP; ++k) h = max(h, __double2hiint(X[k][t]));
-      const int b = (h < 0x33700000 && h > 0) ? 1 : 0;
-      bump[t] = b;
-      if (b) atomicAdd(p.scount + col0 + t, 1);
-    }
-    __syncthreads();
-    double* out = p.msg + (size_t)(nd.v - p.n_tips) * SP * p.cols_pad + col0 + 4 * tc;
+    int bump[2];
+    {
+      double x[8][2];
+      read_block(X, warp, lane, x);
 #pragma unroll
-    for (int a = 0; a < 4; ++a) {
-      double y[4];
-#pragma unroll
-      for (int b = 0; b < 4; ++b) y[b] = bump[4 * tc + b] ? acc[a][b] * Scale<double>::factor() : acc[a][b];
-      double* o = out + (size_t)(4 * ti + a) * p.cols_pad;
-      *reinterpret_cast<double2*>(o) = make_double2(y[0], y[1]);
-      *reinterpret_cast<double2*>(o + 2) = make_double2(y[2], y[3]);
+      for (int j = 0; j < 2; ++j) {
+        bump[j] = column_small(x, j);
+        if (bump[j] && g == 0) atomicAdd(p.scount + col0 + 8 * warp + 2 * tg + j, 1);
+      }
     }
+    double acc[8][2];
+    tile_product(A, X, warp, lane, acc);
+    double* out = p.msg + ((size_t)(nd.v - p.n_tips) * SP + g) * p.cols_pad + col0 + 8 * warp + 2 * tg;
+    const double f0 = bump[0] ? Scale<double>::factor() : 1.0, f1 = bump[1] ? Scale<double>::factor() : 1.0;
+#pragma unroll
+    for (int mi = 0; mi < 8; ++mi)
+      *reinterpret_cast<double2*>(out + (size_t)8 * mi * p.cols_pad) = make_double2(acc[mi][0] * f0, acc[mi][1] * f1);
   } else {
     double term = 0.0;
     if (t < DT) {
@@ -214,78 +272,122 @@ __global__ void __launch_bounds__(DNT, 1) dense_post_kernel(const DenseParams p,
 // grid (nodes of the depth level, tiles, 2): blockIdx.z picks the child the CTA works for, so a
 // CTA holds one matrix and that child's message / outside vector (3 x 32 KB): two CTAs fit an
 // SM and a narrow level near the root spreads over twice as many SMs.  Both CTAs of a node read
-// the same three operand tiles (the second read is an L2 hit).
+// the same three operand tiles (the second read is an L2 hit).  Site likelihoods and numerators
+// are summed in the product's own thread layout (4 x 4 blocks, 16-lane shuffles), so no warp
+// waits on a 64-thread serial section; Q^T arrives with the operand tiles, and P_c is fetched
+// into registers while the first product runs.
 __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, const DenseNode* __restrict__ nodes, int root) {
   extern __shared__ __align__(16) unsigned char dsm[];
-  double (*A)[SP] = reinterpret_cast<double (*)[SP]>(dsm);
-  double (*M)[DT] = reinterpret_cast<double (*)[DT]>(dsm + 1 * SP * SP * 8);   // the child's message
-  double (*Qc)[DT] = reinterpret_cast<double (*)[DT]>(dsm + 2 * SP * SP * 8);  // everything outside its branch
+  double (*A)[LD] = reinterpret_cast<double (*)[LD]>(dsm);
+  double (*M)[LD] = reinterpret_cast<double (*)[LD]>(dsm + 1 * DENSE_TILE_BYTES);   // the child's message
+  double (*Qc)[LD] = reinterpret_cast<double (*)[LD]>(dsm + 2 * DENSE_TILE_BYTES);  // everything outside its branch
   __shared__ double red[DNT / 32];
-  __shared__ double s_inv[DT], s_num[DT];
   const DenseNode nd = nodes[blockIdx.x];
   const int side = blockIdx.z;
   const int c = side ? nd.r : nd.l;
   const int col0 = blockIdx.y * DT, t = threadIdx.x;
-  const int ti = t & 15, tc = t >> 4;
-  for (int e = t; e < SP * DT; e += DNT) {
-    const int k = e / DT, cc = e % DT;
-    const double ml = child_message(p, nd.l, k, col0 + cc), mr = child_message(p, nd.r, k, col0 + cc);
-    const double u = nd.v == root ? (k < p.n_states ? p.freqs[k] : 0.0)
-                                  : p.pre[((size_t)(nd.v - p.n_tips) * SP + k) * p.cols_pad + col0 + cc];
-    M[k][cc] = side ? mr : ml;
-    Qc[k][cc] = u * (side ? ml : mr);
-  }
-  if (t < DT) s_num[t] = 0.0;
-  __syncthreads();
-  // site likelihood (denominator) and, for a tip child, the numerator: one column per thread
-  if (t < DT) {
-    double den = 0.0;
-    for (int k = 0; k < SP; ++k) den += Qc[k][t] * M[k][t];
-    s_inv[t] = p.weights[col0 + t] * p.rate / den;
-    if (c < p.n_tips) {
-      const unsigned code = p.codes[(size_t)c * p.cols_pad + col0 + t];
-      double num = 0.0;  // missing state: Q 1 = 0
-      if (code < (unsigned)p.n_states) {
-        const double* d = p.D + (size_t)c * SP * SP + code;
-        for (int i = 0; i < p.n_states; ++i) num += Qc[i][t] * d[(size_t)i * SP];
-      }
-      s_num[t] = num;
-    }
-  }
-  // internal child: numerator q.(Q m) and the child's pre-order partial P^T q
-  if (c >= p.n_tips) {
-    double acc[4][4];
-    __syncthreads();
-    load_matrix(A, p.QT);  // (Q m)[i] = sum_k Q[i][k] m[k]: A[k][i] = Q^T
-    __syncthreads();
-    tile_product(A, M, ti, tc, acc);
+  const int warp = t >> 5, lane = t & 31, g = lane >> 2, tg = lane & 3;
+  const int kr = t >> 5, cp = 2 * (t & 31);
+  const bool is_root = nd.v == root, internal = c >= p.n_tips;
+  unsigned lc0, lc1, rc0, rc1;
+  fetch_codes(p, nd.l, col0 + cp, lc0, lc1);
+  fetch_codes(p, nd.r, col0 + cp, rc0, rc1);
 #pragma unroll
-    for (int b = 0; b < 4; ++b) {
+  for (int h = 0; h < 2; ++h) {
+    const int k0 = kr + 32 * h;
+    double2 ml[DH], mr[DH], uu[DH], am[DH];
+    fetch_message(p, nd.l, col0 + cp, k0, lc0, lc1, ml);
+    fetch_message(p, nd.r, col0 + cp, k0, rc0, rc1, mr);
+    if (is_root) {
+#pragma unroll
+      for (int u = 0; u < DH; ++u) {
+        const double f = k0 + 8 * u < p.n_states ? p.freqs[k0 + 8 * u] : 0.0;
+        uu[u] = make_double2(f, f);
+      }
+    } else {
+      const double* g = p.pre + ((size_t)(nd.v - p.n_tips) * SP + k0) * p.cols_pad + col0 + cp;
+#pragma unroll
+      for (int u = 0; u < DH; ++u) uu[u] = *reinterpret_cast<const double2*>(g + (size_t)u * 8 * p.cols_pad);
+    }
+    if (internal) fetch_matrix(p.QT, k0, cp, am);  // (Q m)[i] = sum_k Q[i][k] m[k]: A[k][i] = Q^T
+#pragma unroll
+    for (int u = 0; u < DH; ++u) {
+      const double2 other = side ? ml[u] : mr[u];
+      uu[u].x *= other.x; uu[u].y *= other.y;
+    }
+    if (side) store_rows(M, k0, cp, mr); else store_rows(M, k0, cp, ml);
+    store_rows(Qc, k0, cp, uu);
+    if (internal) store_rows(A, k0, cp, am);
+  }
+  __syncthreads();
+  // site likelihood (denominator) of the thread's two columns
+  double den[2], num[2];
+  {
+    double qb[8][2], mb[8][2];
+    read_block(Qc, warp, lane, qb);
+    read_block(M, warp, lane, mb);
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
       double part = 0.0;
 #pragma unroll
-      for (int a = 0; a < 4; ++a) part += Qc[4 * ti + a][4 * tc + b] * acc[a][b];
-#pragma unroll
-      for (int o = 1; o < 16; o <<= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-      if (ti == 0) s_num[4 * tc + b] = part;
-    }
-    __syncthreads();
-    load_matrix(A, p.P + (size_t)c * SP * SP);  // (P^T q)[j] = sum_i P[i][j] q[i]: A[i][j] = P
-    __syncthreads();
-    tile_product(A, Qc, ti, tc, acc);
-    int bumped[4];
-    rescale_tile(acc, bumped);
-    double* out = p.pre + (size_t)(c - p.n_tips) * SP * p.cols_pad + col0 + 4 * tc;
-#pragma unroll
-    for (int a = 0; a < 4; ++a) {
-      double* o = out + (size_t)(4 * ti + a) * p.cols_pad;
-      *reinterpret_cast<double2*>(o) = make_double2(acc[a][0], acc[a][1]);
-      *reinterpret_cast<double2*>(o + 2) = make_double2(acc[a][2], acc[a][3]);
+      for (int mi = 0; mi < 8; ++mi) part = fma(qb[mi][j], mb[mi][j], part);
+      den[j] = column_sum(part);
     }
   }
-  __syncthreads();
-  double g = 0.0;
-  if (t < DT && p.weights[col0 + t] != 0.0) g = s_num[t] * s_inv[t];
-  const double sg = cta_sum(g, red);
+  if (!internal) {
+    // tip child: Q m is column `code` of D = Q P (a missing state has Q 1 = 0)
+    const uchar2 cd = *reinterpret_cast<const uchar2*>(p.codes + (size_t)c * p.cols_pad + col0 + 8 * warp + 2 * tg);
+    const unsigned code[2] = {cd.x, cd.y};
+    const double* d = p.D + ((size_t)c * SP + g) * SP;
+    double qb[8][2];
+    read_block(Qc, warp, lane, qb);
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      double part = 0.0;
+      if (code[j] < (unsigned)p.n_states) {
+#pragma unroll
+        for (int mi = 0; mi < 8; ++mi) part = fma(qb[mi][j], d[8 * mi * SP + code[j]], part);
+      }
+      num[j] = column_sum(part);
+    }
+  } else {
+    // internal child: numerator q.(Q m) and the child's pre-order partial P^T q
+    double2 pm[2][DH];
+    const double* pc = p.P + (size_t)c * SP * SP;  // (P^T q)[j] = sum_i P[i][j] q[i]: A[i][j] = P
+    fetch_matrix(pc, kr, cp, pm[0]);
+    fetch_matrix(pc, kr + 32, cp, pm[1]);
+    double acc[8][2];
+    tile_product(A, M, warp, lane, acc);
+    {
+      double qb[8][2];
+      read_block(Qc, warp, lane, qb);
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        double part = 0.0;
+#pragma unroll
+        for (int mi = 0; mi < 8; ++mi) part = fma(qb[mi][j], acc[mi][j], part);
+        num[j] = column_sum(part);
+      }
+    }
+    __syncthreads();
+    store_rows(A, kr, cp, pm[0]);
+    store_rows(A, kr + 32, cp, pm[1]);
+    __syncthreads();
+    tile_product(A, Qc, warp, lane, acc);
+    const double f0 = column_small(acc, 0) ? Scale<double>::factor() : 1.0;
+    const double f1 = column_small(acc, 1) ? Scale<double>::factor() : 1.0;
+    double* out = p.pre + ((size_t)(c - p.n_tips) * SP + g) * p.cols_pad + col0 + 8 * warp + 2 * tg;
+#pragma unroll
+    for (int mi = 0; mi < 8; ++mi)
+      *reinterpret_cast<double2*>(out + (size_t)8 * mi * p.cols_pad) = make_double2(acc[mi][0] * f0, acc[mi][1] * f1);
+  }
+  double gsum = 0.0;
+  if (g == 0) {
+    const double2 w = *reinterpret_cast<const double2*>(p.weights + col0 + 8 * warp + 2 * tg);
+    if (w.x != 0.0) gsum += w.x * p.rate * num[0] / den[0];
+    if (w.y != 0.0) gsum += w.y * p.rate * num[1] / den[1];
+  }
+  const double sg = cta_sum(gsum, red);
   if (t == 0) p.gpart[(size_t)blockIdx.y * p.n_branches + c] = sg;
 }
 
