@@ -151,7 +151,7 @@ static int dense_create(b2p_instance* h) {
   const size_t n_br = 2 * (size_t)N - 2, mat = (size_t)SP * SP * sizeof(double);
   const size_t part = (size_t)(N - 1) * SP * d->cols_pad * sizeof(double);
   int rc;
-  if ((rc = dev_alloc(h, &d->evec, sizeof(double) * S * S)) || (rc = dev_alloc(h, &d->ivec, sizeof(double) * S * S)) ||
+  if ((rc = dev_alloc(h, &d->evec, mat)) || (rc = dev_alloc(h, &d->ivec, mat)) ||
       (rc = dev_alloc(h, &d->evals, sizeof(double) * SP)) || (rc = dev_alloc(h, &d->q, mat)) || (rc = dev_alloc(h, &d->qt, mat)) ||
       (rc = dev_alloc(h, &d->freqs, sizeof(double) * SP)) || (rc = dev_alloc(h, &d->P, n_br * mat)) ||
       (rc = dev_alloc(h, &d->PT, n_br * mat)) || (rc = dev_alloc(h, &d->D, n_br * mat)) ||
@@ -169,6 +169,7 @@ static int dense_create(b2p_instance* h) {
   CU(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
   CU(cudaFuncSetAttribute((const void*)dense_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * DENSE_TILE_BYTES));
   CU(cudaFuncSetAttribute((const void*)dense_pre_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * DENSE_TILE_BYTES));
+  CU(cudaFuncSetAttribute((const void*)dense_transition_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * DENSE_TILE_BYTES));
   cudaFuncAttributes fa;
   CU(cudaFuncGetAttributes(&fa, (const void*)dense_pre_kernel));
   h->regs = fa.numRegs;
@@ -241,7 +242,14 @@ static int dense_set_weights(b2p_instance* h, const double* w) {
 static int dense_set_eigen(b2p_instance* h, const double* evec, const double* ivec, const double* evals, const double* freqs) {
   b2p_instance::Dense* d = h->dense;
   const int S = d->S;
+  // zero-padded SP x SP operands of the tile products: V^T, V^-1, Q, Q^T
   std::vector<double> q((size_t)SP * SP, 0.0), qt((size_t)SP * SP, 0.0), ev(SP, 0.0), fr(SP, 0.0);
+  std::vector<double> vt((size_t)SP * SP, 0.0), vi((size_t)SP * SP, 0.0);
+  for (int i = 0; i < S; ++i)
+    for (int j = 0; j < S; ++j) {
+      vt[(size_t)j * SP + i] = evec[i * S + j];
+      vi[(size_t)i * SP + j] = ivec[i * S + j];
+    }
   for (int i = 0; i < S; ++i)
     for (int l = 0; l < S; ++l) {
       double acc = 0.0;
@@ -251,8 +259,8 @@ static int dense_set_eigen(b2p_instance* h, const double* evec, const double* iv
     }
   for (int i = 0; i < S; ++i) { ev[i] = evals[i]; fr[i] = freqs[i]; }
   CU(cudaSetDevice(h->cfg.device));
-  CU(cudaMemcpy(d->evec, evec, sizeof(double) * S * S, cudaMemcpyHostToDevice));
-  CU(cudaMemcpy(d->ivec, ivec, sizeof(double) * S * S, cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(d->evec, vt.data(), vt.size() * sizeof(double), cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(d->ivec, vi.data(), vi.size() * sizeof(double), cudaMemcpyHostToDevice));
   CU(cudaMemcpy(d->evals, ev.data(), sizeof(double) * SP, cudaMemcpyHostToDevice));
   CU(cudaMemcpy(d->freqs, fr.data(), sizeof(double) * SP, cudaMemcpyHostToDevice));
   CU(cudaMemcpy(d->q, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice));
@@ -269,7 +277,7 @@ static cudaError_t dense_launch(b2p_instance* h, const double* d_bl, double* d_l
   p.n_tiles = d->n_tiles; p.n_branches = n_br; p.rate = h->model.rates[0];
   p.P = d->P; p.PT = d->PT; p.D = d->D; p.Q = d->q; p.QT = d->qt; p.freqs = d->freqs; p.codes = d->codes;
   p.weights = d->weights; p.msg = d->msg; p.pre = d->pre; p.scount = d->scount; p.lpart = h->d_lpart; p.gpart = h->d_gpart;
-  dense_transition_kernel<<<n_br, DNT, 0, st>>>(d->evec, d->ivec, d->evals, d->q, d_bl, p.rate, d->S, d->P, d->PT, d->D);
+  dense_transition_kernel<<<n_br, DNT, 3 * DENSE_TILE_BYTES, st>>>(d->evec, d->ivec, d->evals, d->qt, d_bl, p.rate, d->S, d->P, d->PT, d->D);
   cudaError_t e = cudaMemsetAsync(d->scount, 0, sizeof(int) * d->cols_pad, st);
   if (e != cudaSuccess) return e;
   const int slot = (int)(h->prof_count % b2p_instance::kProfRing);

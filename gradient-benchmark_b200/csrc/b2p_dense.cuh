@@ -1,9 +1,10 @@
 // Dense-state path (sm_100a): 5..64 states, e.g. the 61-state codon models of BASELINE.json
 // configs[4].  Here the state contraction is a real 64x64 matrix product per node, the path
 // is fp64-compute-bound, and the work is organised as tiled
-// matrix products: one CTA = one node x one tile of 64 patterns, 256 threads, each thread a
-// 4 states x 4 patterns register tile; operands staged in shared memory ([state][pattern]
-// layout in HBM, so a tile row is one contiguous 512-byte read).  Nodes of one tree level
+// matrix products: one CTA = one node x one tile of 64 patterns, 256 threads, the 64 x 64 x 64
+// products on the fp64 tensor cores (mma.sync m8n8k4, each warp 64 states x 8 patterns);
+// operands staged in shared memory ([state][pattern] layout in HBM, so a tile row is one
+// contiguous 512-byte read).  Nodes of one tree level
 // are launched together (level-synchronous: at 61 states a level is ~10^2 us of arithmetic,
 // launch latency is noise).  Same message formulation as the 4-state walk kernel:
 //   post-order  x_v = m_l o m_r ;  m_v = P_v x_v
@@ -18,8 +19,9 @@ namespace b2p {
 constexpr int SP = 64;   // padded state count
 constexpr int DT = 64;   // patterns per tile
 constexpr int DNT = 256; // threads per CTA
-constexpr int LD = 72;   // row stride (doubles) of every shared-memory tile: 576 B = 64 B mod 128 B, so the
-                         // four k-rows of an mma fragment land in alternating halves of the banks
+constexpr int LD = 68;   // row stride (doubles) of every shared-memory tile: 544 B = 32 B mod 128 B, so the four
+                         // k-rows of an mma fragment (lane & 3) land in four different 8-bank groups and a
+                         // half-warp's 8-byte fragment read is one conflict-free wavefront
 constexpr int DENSE_TILE_BYTES = SP * LD * 8;
 
 struct DenseNode { int v, l, r, pad; };
@@ -42,55 +44,6 @@ struct DenseParams {
   double* lpart;             // [n_tiles]
   double* gpart;             // [n_tiles][2N-2]
 };
-
-// ------------------------------------------------------------------ transition matrices
-// One CTA per branch: P = V diag(exp(lambda r t)) V^-1, its transpose, and D = Q P.
-__global__ void __launch_bounds__(DNT) dense_transition_kernel(const double* __restrict__ evec, const double* __restrict__ ivec,
-                                                              const double* __restrict__ evals, const double* __restrict__ q,
-                                                              const double* __restrict__ bl, double rate, int S,
-                                                              double* __restrict__ P, double* __restrict__ PT, double* __restrict__ D) {
-  __shared__ double ex[SP];
-  __shared__ double sp[SP][SP + 1];
-  const int b = blockIdx.x;
-  if (threadIdx.x < SP) ex[threadIdx.x] = threadIdx.x < S ? exp(evals[threadIdx.x] * bl[b] * rate) : 0.0;
-  __syncthreads();
-  // four entries per thread at a time: independent accumulators hide the latency of the 61-long chains
-  for (int e0 = threadIdx.x; e0 < SP * SP; e0 += 4 * DNT) {
-    double acc[4] = {0.0, 0.0, 0.0, 0.0};
-    const int l = e0 % SP;  // e0 + u * DNT keeps the column (DNT is a multiple of SP)
-    if (l < S)
-      for (int j = 0; j < S; ++j) {
-        const double w = ex[j] * ivec[j * S + l];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int i = (e0 + u * DNT) / SP;
-          if (i < S) acc[u] = fma(evec[i * S + j], w, acc[u]);
-        }
-      }
-#pragma unroll
-    for (int u = 0; u < 4; ++u) sp[(e0 + u * DNT) / SP][l] = acc[u];
-  }
-  __syncthreads();
-  double* p = P + (size_t)b * SP * SP;
-  double* pt = PT + (size_t)b * SP * SP;
-  double* d = D + (size_t)b * SP * SP;
-  for (int e0 = threadIdx.x; e0 < SP * SP; e0 += 4 * DNT) {
-    const int l = e0 % SP;
-    double acc[4] = {0.0, 0.0, 0.0, 0.0};
-    for (int j = 0; j < S; ++j) {
-      const double w = sp[j][l];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) acc[u] = fma(q[((e0 + u * DNT) / SP) * SP + j], w, acc[u]);
-    }
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int e = e0 + u * DNT, i = e / SP;
-      p[e] = sp[i][l];
-      pt[e] = sp[l][i];
-      d[e] = acc[u];
-    }
-  }
-}
 
 // ---------------------------------------------------------------------------- helpers
 // Thread t of the CTA owns, in every 64x64 operand tile, the column pair cp = 2 (t & 31) of the
@@ -204,9 +157,71 @@ __device__ __forceinline__ double cta_sum(double v, double* red) {
   return s;
 }
 
+// ------------------------------------------------------------------ transition matrices
+// One CTA per branch: P = V diag(exp(lambda r t)) V^-1, its transpose, and D = Q P, as two of the
+// tensor-core tile products above.  evecT[j][i] = V[i][j], ivec[j][l] = V^-1[j][l], qT[j][i] = Q[i][j],
+// all zero padded to SP x SP (so P, P^T and D come out zero padded).  Dynamic shared memory:
+// three tiles (A, X, S).
+__global__ void __launch_bounds__(DNT, 2) dense_transition_kernel(const double* __restrict__ evecT, const double* __restrict__ ivec,
+                                                                 const double* __restrict__ evals, const double* __restrict__ qT,
+                                                                 const double* __restrict__ bl, double rate, int S,
+                                                                 double* __restrict__ P, double* __restrict__ PT, double* __restrict__ D) {
+  extern __shared__ __align__(16) unsigned char dsm[];
+  double (*A)[LD] = reinterpret_cast<double (*)[LD]>(dsm);
+  double (*X)[LD] = reinterpret_cast<double (*)[LD]>(dsm + 1 * DENSE_TILE_BYTES);
+  double (*Sm)[LD] = reinterpret_cast<double (*)[LD]>(dsm + 2 * DENSE_TILE_BYTES);
+  const int b = blockIdx.x, t = threadIdx.x;
+  const int warp = t >> 5, lane = t & 31, g = lane >> 2, tg = lane & 3;
+  const int kr = t >> 5, cp = 2 * (t & 31);
+  const double tb = bl[b] * rate;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int k0 = kr + 32 * h;
+    double2 am[DH], xm[DH];
+    fetch_matrix(evecT, k0, cp, am);
+    fetch_matrix(ivec, k0, cp, xm);
+#pragma unroll
+    for (int u = 0; u < DH; ++u) {
+      const int k = k0 + 8 * u;
+      const double e = k < S ? exp(evals[k] * tb) : 0.0;
+      xm[u].x *= e; xm[u].y *= e;
+    }
+    store_rows(A, k0, cp, am);
+    store_rows(X, k0, cp, xm);
+  }
+  __syncthreads();
+  double2 qm[2][DH];
+  fetch_matrix(qT, kr, cp, qm[0]);
+  fetch_matrix(qT, kr + 32, cp, qm[1]);
+  double acc[8][2];
+  tile_product(A, X, warp, lane, acc);  // acc = P[8 mi + g][8 w + 2 tg + j]
+  __syncthreads();
+#pragma unroll
+  for (int mi = 0; mi < 8; ++mi) {
+    *reinterpret_cast<double2*>(&Sm[8 * mi + g][8 * warp + 2 * tg]) = make_double2(acc[mi][0], acc[mi][1]);
+    X[8 * warp + 2 * tg][8 * mi + g] = acc[mi][0];      // X becomes P^T
+    X[8 * warp + 2 * tg + 1][8 * mi + g] = acc[mi][1];
+  }
+  store_rows(A, kr, cp, qm[0]);
+  store_rows(A, kr + 32, cp, qm[1]);
+  __syncthreads();
+  double* p = P + (size_t)b * SP * SP;
+  double* pt = PT + (size_t)b * SP * SP;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int k = kr + 8 * j;
+    *reinterpret_cast<double2*>(p + k * SP + cp) = *reinterpret_cast<const double2*>(&Sm[k][cp]);
+    *reinterpret_cast<double2*>(pt + k * SP + cp) = *reinterpret_cast<const double2*>(&X[k][cp]);
+  }
+  tile_product(A, Sm, warp, lane, acc);  // D[i][l] = sum_j Q[i][j] P[j][l]
+  double* d = D + (size_t)b * SP * SP + g * SP + 8 * warp + 2 * tg;
+#pragma unroll
+  for (int mi = 0; mi < 8; ++mi) *reinterpret_cast<double2*>(d + 8 * mi * SP) = make_double2(acc[mi][0], acc[mi][1]);
+}
+
 // ---------------------------------------------------------------------- post-order level
 // grid (nodes of the level, tiles).  Dynamic shared memory: A [SP][SP], X [SP][DT].
-__global__ void __launch_bounds__(DNT, 2) dense_post_kernel(const DenseParams p, const DenseNode* __restrict__ nodes, int root) {
+__global__ void __launch_bounds__(DNT, 3) dense_post_kernel(const DenseParams p, const DenseNode* __restrict__ nodes, int root) {
   extern __shared__ __align__(16) unsigned char dsm[];
   double (*A)[LD] = reinterpret_cast<double (*)[LD]>(dsm);
   double (*X)[LD] = reinterpret_cast<double (*)[LD]>(dsm + DENSE_TILE_BYTES);
