@@ -331,8 +331,9 @@ def run_b200(a):
             peak_tf = 2 * 4096 ** 3 / (best * 1e-3) / 1e12
             ach_tf = flops / (k_avg_ms * 1e-3) / 1e12
             line["dtype"] = "f64"
-            line["gpu_launches"] = (2 + info["post_rounds"] + info["pre_rounds"] + 1) * a.steps
-            line["roofline"] = {"bound": "tensor", "kernel": "dense_post_kernel + dense_pre_kernel (one launch per tree level)",
+            # transition, one post-order launch per level, one pre-order launch per depth, tips, reduce
+            line["gpu_launches"] = (1 + info["post_rounds"] + info["pre_rounds"] + 2) * a.steps
+            line["roofline"] = {"bound": "tensor", "kernel": "dense_post_kernel + dense_pre_kernel (one launch per tree level) + dense_tip_kernel",
                                 "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf, "traffic": None,
                                 "alg_flops_per_eval": flops, "kernel_ms": k_avg_ms, "launches_timed": k_n,
                                 "peak_source": "fp64 torch.matmul 4096^3 (cuBLAS DGEMM), best of 5, measured in this run"}

@@ -77,7 +77,7 @@ struct b2p_instance {
     int* scount = nullptr;
     DenseNode* nodes = nullptr;                 // post-order levels, then pre-order levels
     std::vector<int> post_off, pre_off;         // level boundaries into `nodes`
-    int root = 0;
+    int root = 0, tip_off = 0;                  // tip tasks start at nodes[tip_off] (N of them)
   }* dense = nullptr;
   mutable std::string err;
 };
@@ -157,7 +157,7 @@ static int dense_create(b2p_instance* h) {
       (rc = dev_alloc(h, &d->PT, n_br * mat)) || (rc = dev_alloc(h, &d->D, n_br * mat)) ||
       (rc = dev_alloc(h, &d->weights, sizeof(double) * d->cols_pad)) || (rc = dev_alloc(h, (char**)&d->msg, part)) ||
       (rc = dev_alloc(h, (char**)&d->pre, part)) || (rc = dev_alloc(h, &d->codes, (size_t)N * d->cols_pad)) ||
-      (rc = dev_alloc(h, &d->scount, sizeof(int) * d->cols_pad)) || (rc = dev_alloc(h, &d->nodes, sizeof(DenseNode) * 2 * (N - 1))) ||
+      (rc = dev_alloc(h, &d->scount, sizeof(int) * d->cols_pad)) || (rc = dev_alloc(h, &d->nodes, sizeof(DenseNode) * (3 * (size_t)N - 3))) ||
       (rc = dev_alloc(h, &h->d_lpart, sizeof(double) * d->n_tiles)) ||
       (rc = dev_alloc(h, &h->d_gpart, sizeof(double) * (size_t)d->n_tiles * n_br)) ||
       (rc = dev_alloc(h, &h->d_bl_stage, sizeof(double) * n_br)) || (rc = dev_alloc(h, &h->d_out_stage, sizeof(double) * (n_br + 1))))
@@ -202,14 +202,26 @@ static int dense_set_topology(b2p_instance* h, const int32_t* tr) {
       if (lvl[v] == L) nodes.push_back({v, left[v], right[v], 0});
     d->post_off.push_back((int)nodes.size());
   }
+  // pre-order tasks {parent, child, sibling}: internal children by the depth of their parent
+  // (dense_pre_kernel, one launch per depth), then every tip (dense_tip_kernel, one launch)
   d->pre_off.assign(1, (int)nodes.size());
   for (int L = 0; L <= max_dep; ++L) {
     for (int v = N; v < n_nodes; ++v)
-      if (dep[v] == L) nodes.push_back({v, left[v], right[v], 0});
+      if (dep[v] == L) {
+        if (left[v] >= N) nodes.push_back({v, left[v], right[v], 0});
+        if (right[v] >= N) nodes.push_back({v, right[v], left[v], 0});
+      }
     d->pre_off.push_back((int)nodes.size());
   }
+  d->tip_off = (int)nodes.size();
+  for (int v = N; v < n_nodes; ++v) {
+    if (left[v] < N) nodes.push_back({v, left[v], right[v], 0});
+    if (right[v] < N) nodes.push_back({v, right[v], left[v], 0});
+  }
   d->root = root;
-  h->plan.rounds_post = lvl[root] + 1; h->plan.rounds_pre = max_dep + 1; h->plan.rounds = h->plan.rounds_post + h->plan.rounds_pre;
+  int pre_launches = 0;  // depths that have an internal child
+  for (size_t L = 0; L + 1 < d->pre_off.size(); ++L) pre_launches += d->pre_off[L + 1] > d->pre_off[L];
+  h->plan.rounds_post = lvl[root] + 1; h->plan.rounds_pre = pre_launches; h->plan.rounds = h->plan.rounds_post + h->plan.rounds_pre;
   h->plan.tree_depth = max_dep + 1;
   CU(cudaSetDevice(h->cfg.device));
   CU(cudaDeviceSynchronize());
@@ -286,11 +298,13 @@ static cudaError_t dense_launch(b2p_instance* h, const double* d_bl, double* d_l
     const int n = d->post_off[L + 1] - d->post_off[L];
     if (n > 0) dense_post_kernel<<<dim3(n, d->n_tiles), DNT, 2 * DENSE_TILE_BYTES, st>>>(p, d->nodes + d->post_off[L], d->root);
   }
-  if (d_grad)
+  if (d_grad) {
     for (size_t L = 0; L + 1 < d->pre_off.size(); ++L) {
       const int n = d->pre_off[L + 1] - d->pre_off[L];
-      if (n > 0) dense_pre_kernel<<<dim3(n, d->n_tiles, 2), DNT, 3 * DENSE_TILE_BYTES, st>>>(p, d->nodes + d->pre_off[L], d->root);
+      if (n > 0) dense_pre_kernel<<<dim3(n, d->n_tiles), DNT, 3 * DENSE_TILE_BYTES, st>>>(p, d->nodes + d->pre_off[L], d->root);
     }
+    dense_tip_kernel<<<dim3(N, d->n_tiles), DNT, 0, st>>>(p, d->nodes + d->tip_off, d->root);
+  }
   if (h->profiling) { cudaEventRecord(h->ev1[slot], st); ++h->prof_count; }
   const int nb = d_grad ? n_br : 0;
   reduce_kernel<<<(nb + 31) / 32 + 1, 512, 0, st>>>(h->d_gpart, h->d_lpart, d->n_tiles, nb, d_grad, d_logl);

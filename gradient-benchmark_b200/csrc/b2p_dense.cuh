@@ -284,35 +284,32 @@ __global__ void __launch_bounds__(DNT, 3) dense_post_kernel(const DenseParams p,
 }
 
 // ----------------------------------------------------------------------- pre-order level
-// grid (nodes of the depth level, tiles, 2): blockIdx.z picks the child the CTA works for, so a
-// CTA holds one matrix and that child's message / outside vector (3 x 32 KB): two CTAs fit an
-// SM and a narrow level near the root spreads over twice as many SMs.  Both CTAs of a node read
-// the same three operand tiles (the second read is an L2 hit).  Site likelihoods and numerators
-// are summed in the product's own thread layout (4 x 4 blocks, 16-lane shuffles), so no warp
-// waits on a 64-thread serial section; Q^T arrives with the operand tiles, and P_c is fetched
-// into registers while the first product runs.
-__global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, const DenseNode* __restrict__ nodes, int root) {
+// grid (internal children whose parents sit at this depth, tiles).  A task is {v = parent, l = the
+// child c the CTA works for, r = its sibling}: the CTA holds one matrix, the child's message and
+// the outside vector q_c = u_v o m_sibling (3 tiles): two CTAs fit an SM.  Site likelihoods and
+// numerators are summed in the product's own thread layout, Q^T arrives with the operand tiles,
+// and P_c is fetched into registers while the first product runs.  Tip children need no product
+// and no successor: dense_tip_kernel below handles all of them in one launch.
+__global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, const DenseNode* __restrict__ tasks, int root) {
   extern __shared__ __align__(16) unsigned char dsm[];
   double (*A)[LD] = reinterpret_cast<double (*)[LD]>(dsm);
   double (*M)[LD] = reinterpret_cast<double (*)[LD]>(dsm + 1 * DENSE_TILE_BYTES);   // the child's message
   double (*Qc)[LD] = reinterpret_cast<double (*)[LD]>(dsm + 2 * DENSE_TILE_BYTES);  // everything outside its branch
   __shared__ double red[DNT / 32];
-  const DenseNode nd = nodes[blockIdx.x];
-  const int side = blockIdx.z;
-  const int c = side ? nd.r : nd.l;
+  const DenseNode nd = tasks[blockIdx.x];
+  const int c = nd.l, sib = nd.r;
   const int col0 = blockIdx.y * DT, t = threadIdx.x;
   const int warp = t >> 5, lane = t & 31, g = lane >> 2, tg = lane & 3;
   const int kr = t >> 5, cp = 2 * (t & 31);
-  const bool is_root = nd.v == root, internal = c >= p.n_tips;
-  unsigned lc0, lc1, rc0, rc1;
-  fetch_codes(p, nd.l, col0 + cp, lc0, lc1);
-  fetch_codes(p, nd.r, col0 + cp, rc0, rc1);
+  const bool is_root = nd.v == root;
+  unsigned sc0, sc1;
+  fetch_codes(p, sib, col0 + cp, sc0, sc1);
 #pragma unroll
   for (int h = 0; h < 2; ++h) {
     const int k0 = kr + 32 * h;
-    double2 ml[DH], mr[DH], uu[DH], am[DH];
-    fetch_message(p, nd.l, col0 + cp, k0, lc0, lc1, ml);
-    fetch_message(p, nd.r, col0 + cp, k0, rc0, rc1, mr);
+    double2 mc[DH], ms[DH], uu[DH], am[DH];
+    fetch_message(p, c, col0 + cp, k0, 0u, 0u, mc);
+    fetch_message(p, sib, col0 + cp, k0, sc0, sc1, ms);
     if (is_root) {
 #pragma unroll
       for (int u = 0; u < DH; ++u) {
@@ -320,19 +317,16 @@ __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, 
         uu[u] = make_double2(f, f);
       }
     } else {
-      const double* g = p.pre + ((size_t)(nd.v - p.n_tips) * SP + k0) * p.cols_pad + col0 + cp;
+      const double* gp = p.pre + ((size_t)(nd.v - p.n_tips) * SP + k0) * p.cols_pad + col0 + cp;
 #pragma unroll
-      for (int u = 0; u < DH; ++u) uu[u] = *reinterpret_cast<const double2*>(g + (size_t)u * 8 * p.cols_pad);
+      for (int u = 0; u < DH; ++u) uu[u] = *reinterpret_cast<const double2*>(gp + (size_t)u * 8 * p.cols_pad);
     }
-    if (internal) fetch_matrix(p.QT, k0, cp, am);  // (Q m)[i] = sum_k Q[i][k] m[k]: A[k][i] = Q^T
+    fetch_matrix(p.QT, k0, cp, am);  // (Q m)[i] = sum_k Q[i][k] m[k]: A[k][i] = Q^T
 #pragma unroll
-    for (int u = 0; u < DH; ++u) {
-      const double2 other = side ? ml[u] : mr[u];
-      uu[u].x *= other.x; uu[u].y *= other.y;
-    }
-    if (side) store_rows(M, k0, cp, mr); else store_rows(M, k0, cp, ml);
+    for (int u = 0; u < DH; ++u) { uu[u].x *= ms[u].x; uu[u].y *= ms[u].y; }
+    store_rows(M, k0, cp, mc);
     store_rows(Qc, k0, cp, uu);
-    if (internal) store_rows(A, k0, cp, am);
+    store_rows(A, k0, cp, am);
   }
   __syncthreads();
   // site likelihood (denominator) of the thread's two columns
@@ -349,58 +343,105 @@ __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, 
       den[j] = column_sum(part);
     }
   }
-  if (!internal) {
-    // tip child: Q m is column `code` of D = Q P (a missing state has Q 1 = 0)
-    const uchar2 cd = *reinterpret_cast<const uchar2*>(p.codes + (size_t)c * p.cols_pad + col0 + 8 * warp + 2 * tg);
-    const unsigned code[2] = {cd.x, cd.y};
-    const double* d = p.D + ((size_t)c * SP + g) * SP;
+  // numerator q.(Q m) and the child's pre-order partial P^T q
+  double2 pm[2][DH];
+  const double* pc = p.P + (size_t)c * SP * SP;  // (P^T q)[j] = sum_i P[i][j] q[i]: A[i][j] = P
+  fetch_matrix(pc, kr, cp, pm[0]);
+  fetch_matrix(pc, kr + 32, cp, pm[1]);
+  double acc[8][2];
+  tile_product(A, M, warp, lane, acc);
+  {
     double qb[8][2];
     read_block(Qc, warp, lane, qb);
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
       double part = 0.0;
-      if (code[j] < (unsigned)p.n_states) {
 #pragma unroll
-        for (int mi = 0; mi < 8; ++mi) part = fma(qb[mi][j], d[8 * mi * SP + code[j]], part);
-      }
+      for (int mi = 0; mi < 8; ++mi) part = fma(qb[mi][j], acc[mi][j], part);
       num[j] = column_sum(part);
     }
-  } else {
-    // internal child: numerator q.(Q m) and the child's pre-order partial P^T q
-    double2 pm[2][DH];
-    const double* pc = p.P + (size_t)c * SP * SP;  // (P^T q)[j] = sum_i P[i][j] q[i]: A[i][j] = P
-    fetch_matrix(pc, kr, cp, pm[0]);
-    fetch_matrix(pc, kr + 32, cp, pm[1]);
-    double acc[8][2];
-    tile_product(A, M, warp, lane, acc);
-    {
-      double qb[8][2];
-      read_block(Qc, warp, lane, qb);
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        double part = 0.0;
-#pragma unroll
-        for (int mi = 0; mi < 8; ++mi) part = fma(qb[mi][j], acc[mi][j], part);
-        num[j] = column_sum(part);
-      }
-    }
-    __syncthreads();
-    store_rows(A, kr, cp, pm[0]);
-    store_rows(A, kr + 32, cp, pm[1]);
-    __syncthreads();
-    tile_product(A, Qc, warp, lane, acc);
-    const double f0 = column_small(acc, 0) ? Scale<double>::factor() : 1.0;
-    const double f1 = column_small(acc, 1) ? Scale<double>::factor() : 1.0;
-    double* out = p.pre + ((size_t)(c - p.n_tips) * SP + g) * p.cols_pad + col0 + 8 * warp + 2 * tg;
-#pragma unroll
-    for (int mi = 0; mi < 8; ++mi)
-      *reinterpret_cast<double2*>(out + (size_t)8 * mi * p.cols_pad) = make_double2(acc[mi][0] * f0, acc[mi][1] * f1);
   }
+  __syncthreads();
+  store_rows(A, kr, cp, pm[0]);
+  store_rows(A, kr + 32, cp, pm[1]);
+  __syncthreads();
+  tile_product(A, Qc, warp, lane, acc);
+  const double f0 = column_small(acc, 0) ? Scale<double>::factor() : 1.0;
+  const double f1 = column_small(acc, 1) ? Scale<double>::factor() : 1.0;
+  double* out = p.pre + ((size_t)(c - p.n_tips) * SP + g) * p.cols_pad + col0 + 8 * warp + 2 * tg;
+#pragma unroll
+  for (int mi = 0; mi < 8; ++mi)
+    *reinterpret_cast<double2*>(out + (size_t)8 * mi * p.cols_pad) = make_double2(acc[mi][0] * f0, acc[mi][1] * f1);
   double gsum = 0.0;
   if (g == 0) {
     const double2 w = *reinterpret_cast<const double2*>(p.weights + col0 + 8 * warp + 2 * tg);
     if (w.x != 0.0) gsum += w.x * p.rate * num[0] / den[0];
     if (w.y != 0.0) gsum += w.y * p.rate * num[1] / den[1];
+  }
+  const double sg = cta_sum(gsum, red);
+  if (t == 0) p.gpart[(size_t)blockIdx.y * p.n_branches + c] = sg;
+}
+
+// ------------------------------------------------------------------------- tip branches
+// grid (tips, tiles), after the last pre-order level.  Task {v = parent, l = the tip c, r = its
+// sibling}.  For a tip, m_c is column `code` of P_c and Q m_c column `code` of D_c = Q P_c (a
+// missing state has m = 1, Q 1 = 0), so its gradient needs no product: warp w sums rows w + 8 j of
+// q o m and q o (Q m) for two columns per lane, entirely in registers; eight partial sums per
+// column meet in shared memory.  No tile staging: several CTAs share an SM and the launch runs at
+// memory speed.
+__global__ void __launch_bounds__(DNT, 3) dense_tip_kernel(const DenseParams p, const DenseNode* __restrict__ tasks, int root) {
+  __shared__ double sden[DNT / 32][DT], snum[DNT / 32][DT];
+  __shared__ double red[DNT / 32];
+  const DenseNode nd = tasks[blockIdx.x];
+  const int c = nd.l, sib = nd.r;
+  const int col0 = blockIdx.y * DT, t = threadIdx.x;
+  const int kr = t >> 5, cp = 2 * (t & 31);
+  const bool is_root = nd.v == root;
+  unsigned sc0, sc1, cc0, cc1;
+  fetch_codes(p, sib, col0 + cp, sc0, sc1);
+  fetch_codes(p, c, col0 + cp, cc0, cc1);
+  const bool known0 = cc0 < (unsigned)p.n_states, known1 = cc1 < (unsigned)p.n_states;
+  double den0 = 0.0, den1 = 0.0, num0 = 0.0, num1 = 0.0;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int k0 = kr + 32 * h;
+    double2 mc[DH], ms[DH], uu[DH], dc[DH];
+    fetch_message(p, c, col0 + cp, k0, cc0, cc1, mc);
+    fetch_message(p, sib, col0 + cp, k0, sc0, sc1, ms);
+    const double* dg = p.D + ((size_t)c * SP + k0) * SP;
+#pragma unroll
+    for (int u = 0; u < DH; ++u) {
+      dc[u].x = known0 ? dg[u * 8 * SP + cc0] : 0.0;
+      dc[u].y = known1 ? dg[u * 8 * SP + cc1] : 0.0;
+    }
+    if (is_root) {
+#pragma unroll
+      for (int u = 0; u < DH; ++u) {
+        const double f = k0 + 8 * u < p.n_states ? p.freqs[k0 + 8 * u] : 0.0;
+        uu[u] = make_double2(f, f);
+      }
+    } else {
+      const double* gp = p.pre + ((size_t)(nd.v - p.n_tips) * SP + k0) * p.cols_pad + col0 + cp;
+#pragma unroll
+      for (int u = 0; u < DH; ++u) uu[u] = *reinterpret_cast<const double2*>(gp + (size_t)u * 8 * p.cols_pad);
+    }
+#pragma unroll
+    for (int u = 0; u < DH; ++u) {
+      const double q0 = uu[u].x * ms[u].x, q1 = uu[u].y * ms[u].y;
+      den0 = fma(q0, mc[u].x, den0); den1 = fma(q1, mc[u].y, den1);
+      num0 = fma(q0, dc[u].x, num0); num1 = fma(q1, dc[u].y, num1);
+    }
+  }
+  *reinterpret_cast<double2*>(&sden[kr][cp]) = make_double2(den0, den1);
+  *reinterpret_cast<double2*>(&snum[kr][cp]) = make_double2(num0, num1);
+  __syncthreads();
+  double gsum = 0.0;
+  if (t < DT) {
+    double den = 0.0, num = 0.0;
+#pragma unroll
+    for (int w = 0; w < DNT / 32; ++w) { den += sden[w][t]; num += snum[w][t]; }
+    const double wt = p.weights[col0 + t];
+    if (wt != 0.0) gsum = wt * p.rate * num / den;
   }
   const double sg = cta_sum(gsum, red);
   if (t == 0) p.gpart[(size_t)blockIdx.y * p.n_branches + c] = sg;
