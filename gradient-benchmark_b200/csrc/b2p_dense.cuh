@@ -4,9 +4,10 @@
 // matrix products: one CTA = one node x one tile of 64 patterns, 256 threads, the 64 x 64 x 64
 // products on the fp64 tensor cores (mma.sync m8n8k4, each warp 64 states x 8 patterns);
 // operands staged in shared memory ([state][pattern] layout in HBM, so a tile row is one
-// contiguous 512-byte read).  Nodes of one tree level
-// are launched together (level-synchronous: at 61 states a level is ~10^2 us of arithmetic,
-// launch latency is noise).  Same message formulation as the 4-state walk kernel:
+// contiguous 512-byte read).  Nodes of one tree level are launched together (level-synchronous:
+// at 61 states a level is ~10^2 us of arithmetic, launch latency is noise); tip branches, which
+// need no product, run in one launch of their own.  Same message formulation as the 4-state
+// walk kernel:
 //   post-order  x_v = m_l o m_r ;  m_v = P_v x_v
 //   pre-order   q_l = u_v o m_r, q_r = u_v o m_l ; L = q_l.m_l ; dL/dt_l = r q_l.(Q m_l) ; u_l = P_l^T q_l
 // A tip child's message is column `code` of P (Q m = column `code` of Q P), a missing state
@@ -84,6 +85,18 @@ __device__ __forceinline__ void fetch_matrix(const double* __restrict__ g, int k
 #pragma unroll
   for (int u = 0; u < DH; ++u) v[u] = *reinterpret_cast<const double2*>(g + (k0 + 8 * u) * SP + cp);
 }
+
+// Operands that need no arithmetic on the way in (matrices, an internal child's own message) go
+// straight from global to shared memory (LDGSTS): no registers, so the register-staged operands
+// of BOTH tile halves can be in flight with them in one latency round.
+__device__ __forceinline__ void copy_rows_async(double (*T)[LD], const double* __restrict__ g, size_t row_stride, int kr, int cp) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(&T[kr + 8 * j][cp]);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(g + (size_t)(kr + 8 * j) * row_stride + cp) : "memory");
+  }
+}
+__device__ __forceinline__ void copy_rows_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 __device__ __forceinline__ void store_rows(double (*T)[LD], int k0, int cp, const double2 (&v)[DH]) {
 #pragma unroll
@@ -234,18 +247,22 @@ __global__ void __launch_bounds__(DNT, 3) dense_post_kernel(const DenseParams p,
   unsigned lc0, lc1, rc0, rc1;
   fetch_codes(p, nd.l, col0 + cp, lc0, lc1);
   fetch_codes(p, nd.r, col0 + cp, rc0, rc1);
+  if (!is_root) copy_rows_async(A, p.PT + (size_t)nd.v * SP * SP, SP, kr, cp);
+  {
+    double2 ml[2][DH], mr[2][DH];
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    const int k0 = kr + 32 * h;
-    double2 ml[DH], mr[DH], am[DH];
-    fetch_message(p, nd.l, col0 + cp, k0, lc0, lc1, ml);
-    fetch_message(p, nd.r, col0 + cp, k0, rc0, rc1, mr);
-    if (!is_root) fetch_matrix(p.PT + (size_t)nd.v * SP * SP, k0, cp, am);
+    for (int h = 0; h < 2; ++h) {
+      fetch_message(p, nd.l, col0 + cp, kr + 32 * h, lc0, lc1, ml[h]);
+      fetch_message(p, nd.r, col0 + cp, kr + 32 * h, rc0, rc1, mr[h]);
+    }
 #pragma unroll
-    for (int u = 0; u < DH; ++u) { ml[u].x *= mr[u].x; ml[u].y *= mr[u].y; }
-    store_rows(X, k0, cp, ml);
-    if (!is_root) store_rows(A, k0, cp, am);
+    for (int h = 0; h < 2; ++h) {
+#pragma unroll
+      for (int u = 0; u < DH; ++u) { ml[h][u].x *= mr[h][u].x; ml[h][u].y *= mr[h][u].y; }
+      store_rows(X, kr + 32 * h, cp, ml[h]);
+    }
   }
+  copy_rows_wait();
   __syncthreads();
   if (!is_root) {
     // x_v is rescaled BEFORE the product (same rule as the 4-state kernel): the column
@@ -304,30 +321,34 @@ __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, 
   const bool is_root = nd.v == root;
   unsigned sc0, sc1;
   fetch_codes(p, sib, col0 + cp, sc0, sc1);
+  copy_rows_async(M, p.msg + (size_t)(c - p.n_tips) * SP * p.cols_pad + col0, p.cols_pad, kr, cp);
+  copy_rows_async(A, p.QT, SP, kr, cp);  // (Q m)[i] = sum_k Q[i][k] m[k]: A[k][i] = Q^T
+  {
+    double2 ms[2][DH], uu[2][DH];
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    const int k0 = kr + 32 * h;
-    double2 mc[DH], ms[DH], uu[DH], am[DH];
-    fetch_message(p, c, col0 + cp, k0, 0u, 0u, mc);
-    fetch_message(p, sib, col0 + cp, k0, sc0, sc1, ms);
-    if (is_root) {
+    for (int h = 0; h < 2; ++h) {
+      const int k0 = kr + 32 * h;
+      fetch_message(p, sib, col0 + cp, k0, sc0, sc1, ms[h]);
+      if (is_root) {
 #pragma unroll
-      for (int u = 0; u < DH; ++u) {
-        const double f = k0 + 8 * u < p.n_states ? p.freqs[k0 + 8 * u] : 0.0;
-        uu[u] = make_double2(f, f);
+        for (int u = 0; u < DH; ++u) {
+          const double f = k0 + 8 * u < p.n_states ? p.freqs[k0 + 8 * u] : 0.0;
+          uu[h][u] = make_double2(f, f);
+        }
+      } else {
+        const double* gp = p.pre + ((size_t)(nd.v - p.n_tips) * SP + k0) * p.cols_pad + col0 + cp;
+#pragma unroll
+        for (int u = 0; u < DH; ++u) uu[h][u] = *reinterpret_cast<const double2*>(gp + (size_t)u * 8 * p.cols_pad);
       }
-    } else {
-      const double* gp = p.pre + ((size_t)(nd.v - p.n_tips) * SP + k0) * p.cols_pad + col0 + cp;
-#pragma unroll
-      for (int u = 0; u < DH; ++u) uu[u] = *reinterpret_cast<const double2*>(gp + (size_t)u * 8 * p.cols_pad);
     }
-    fetch_matrix(p.QT, k0, cp, am);  // (Q m)[i] = sum_k Q[i][k] m[k]: A[k][i] = Q^T
 #pragma unroll
-    for (int u = 0; u < DH; ++u) { uu[u].x *= ms[u].x; uu[u].y *= ms[u].y; }
-    store_rows(M, k0, cp, mc);
-    store_rows(Qc, k0, cp, uu);
-    store_rows(A, k0, cp, am);
+    for (int h = 0; h < 2; ++h) {
+#pragma unroll
+      for (int u = 0; u < DH; ++u) { uu[h][u].x *= ms[h][u].x; uu[h][u].y *= ms[h][u].y; }
+      store_rows(Qc, kr + 32 * h, cp, uu[h]);
+    }
   }
+  copy_rows_wait();
   __syncthreads();
   // site likelihood (denominator) of the thread's two columns
   double den[2], num[2];
