@@ -126,6 +126,25 @@ __device__ __forceinline__ void tile_product(const double (*A)[LD], const double
   }
 }
 
+// Two products that share the right-hand operand: acc1 = A1^T-contraction with X, acc2 = A2 with X
+// (one fragment of X feeds 16 mmas).
+__device__ __forceinline__ void tile_product2(const double (*A1)[LD], const double (*A2)[LD], const double (*X)[LD], int warp, int lane,
+                                              double (&acc1)[8][2], double (&acc2)[8][2]) {
+  const int g = lane >> 2, tg = lane & 3;
+#pragma unroll
+  for (int mi = 0; mi < 8; ++mi) acc1[mi][0] = acc1[mi][1] = acc2[mi][0] = acc2[mi][1] = 0.0;
+#pragma unroll 2
+  for (int k0 = 0; k0 < SP; k0 += 4) {
+    const double b = X[k0 + tg][8 * warp + g];
+    const double* a1 = &A1[k0 + tg][g];
+    const double* a2 = &A2[k0 + tg][g];
+#pragma unroll
+    for (int mi = 0; mi < 8; ++mi) dmma(acc1[mi], a1[8 * mi], b);
+#pragma unroll
+    for (int mi = 0; mi < 8; ++mi) dmma(acc2[mi], a2[8 * mi], b);
+  }
+}
+
 // The thread's part of a shared-memory tile in the accumulator layout: rows 8 mi + g, columns
 // 8 w + 2 tg + {0, 1}.
 __device__ __forceinline__ void read_block(const double (*T)[LD], int warp, int lane, double (&v)[8][2]) {
@@ -302,16 +321,19 @@ __global__ void __launch_bounds__(DNT, 3) dense_post_kernel(const DenseParams p,
 
 // ----------------------------------------------------------------------- pre-order level
 // grid (internal children whose parents sit at this depth, tiles).  A task is {v = parent, l = the
-// child c the CTA works for, r = its sibling}: the CTA holds one matrix, the child's message and
-// the outside vector q_c = u_v o m_sibling (3 tiles): two CTAs fit an SM.  Site likelihoods and
-// numerators are summed in the product's own thread layout, Q^T arrives with the operand tiles,
-// and P_c is fetched into registers while the first product runs.  Tip children need no product
-// and no successor: dense_tip_kernel below handles all of them in one launch.
+// child c the CTA works for, r = its sibling}.  With q_c = u_v o m_sibling everything outside the
+// branch, both products of the task contract q_c:
+//   numerator   q.(Q m_c) = (Q^T q).m_c        -> acc1 = Q^T q   (A1 = Q)
+//   pre-order   u_c       = P_c^T q            -> acc2           (A2 = P_c)
+// so one pass over the fragments of q feeds 16 mmas, both matrices arrive by cp.async while q is
+// staged, and m_c is needed only elementwise: it is read from HBM straight into the accumulator
+// layout (never staged).  Three tiles (Q, P_c, q) = 102 KB: two CTAs per SM.  Tip children need
+// no product and no successor: dense_tip_kernel below handles all of them in one launch.
 __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, const DenseNode* __restrict__ tasks, int root) {
   extern __shared__ __align__(16) unsigned char dsm[];
-  double (*A)[LD] = reinterpret_cast<double (*)[LD]>(dsm);
-  double (*M)[LD] = reinterpret_cast<double (*)[LD]>(dsm + 1 * DENSE_TILE_BYTES);   // the child's message
-  double (*Qc)[LD] = reinterpret_cast<double (*)[LD]>(dsm + 2 * DENSE_TILE_BYTES);  // everything outside its branch
+  double (*A1)[LD] = reinterpret_cast<double (*)[LD]>(dsm);
+  double (*A2)[LD] = reinterpret_cast<double (*)[LD]>(dsm + 1 * DENSE_TILE_BYTES);
+  double (*Qc)[LD] = reinterpret_cast<double (*)[LD]>(dsm + 2 * DENSE_TILE_BYTES);  // everything outside the branch
   __shared__ double red[DNT / 32];
   const DenseNode nd = tasks[blockIdx.x];
   const int c = nd.l, sib = nd.r;
@@ -321,8 +343,8 @@ __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, 
   const bool is_root = nd.v == root;
   unsigned sc0, sc1;
   fetch_codes(p, sib, col0 + cp, sc0, sc1);
-  copy_rows_async(M, p.msg + (size_t)(c - p.n_tips) * SP * p.cols_pad + col0, p.cols_pad, kr, cp);
-  copy_rows_async(A, p.QT, SP, kr, cp);  // (Q m)[i] = sum_k Q[i][k] m[k]: A[k][i] = Q^T
+  copy_rows_async(A1, p.Q, SP, kr, cp);
+  copy_rows_async(A2, p.P + (size_t)c * SP * SP, SP, kr, cp);
   {
     double2 ms[2][DH], uu[2][DH];
 #pragma unroll
@@ -350,49 +372,31 @@ __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, 
   }
   copy_rows_wait();
   __syncthreads();
-  // site likelihood (denominator) of the thread's two columns
-  double den[2], num[2];
+  double acc1[8][2], acc2[8][2];
+  tile_product2(A1, A2, Qc, warp, lane, acc1, acc2);
+  // the child's own message in the accumulator layout (rows 8 mi + g, columns 8 w + 2 tg + {0, 1})
+  double den[2] = {0.0, 0.0}, num[2] = {0.0, 0.0};
   {
-    double qb[8][2], mb[8][2];
-    read_block(Qc, warp, lane, qb);
-    read_block(M, warp, lane, mb);
+    const double* gm = p.msg + ((size_t)(c - p.n_tips) * SP + g) * p.cols_pad + col0 + 8 * warp + 2 * tg;
+    double2 m[8];
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      double part = 0.0;
-#pragma unroll
-      for (int mi = 0; mi < 8; ++mi) part = fma(qb[mi][j], mb[mi][j], part);
-      den[j] = column_sum(part);
-    }
-  }
-  // numerator q.(Q m) and the child's pre-order partial P^T q
-  double2 pm[2][DH];
-  const double* pc = p.P + (size_t)c * SP * SP;  // (P^T q)[j] = sum_i P[i][j] q[i]: A[i][j] = P
-  fetch_matrix(pc, kr, cp, pm[0]);
-  fetch_matrix(pc, kr + 32, cp, pm[1]);
-  double acc[8][2];
-  tile_product(A, M, warp, lane, acc);
-  {
+    for (int mi = 0; mi < 8; ++mi) m[mi] = *reinterpret_cast<const double2*>(gm + (size_t)8 * mi * p.cols_pad);
     double qb[8][2];
     read_block(Qc, warp, lane, qb);
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      double part = 0.0;
-#pragma unroll
-      for (int mi = 0; mi < 8; ++mi) part = fma(qb[mi][j], acc[mi][j], part);
-      num[j] = column_sum(part);
+    for (int mi = 0; mi < 8; ++mi) {
+      den[0] = fma(qb[mi][0], m[mi].x, den[0]); den[1] = fma(qb[mi][1], m[mi].y, den[1]);
+      num[0] = fma(acc1[mi][0], m[mi].x, num[0]); num[1] = fma(acc1[mi][1], m[mi].y, num[1]);
     }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) { den[j] = column_sum(den[j]); num[j] = column_sum(num[j]); }
   }
-  __syncthreads();
-  store_rows(A, kr, cp, pm[0]);
-  store_rows(A, kr + 32, cp, pm[1]);
-  __syncthreads();
-  tile_product(A, Qc, warp, lane, acc);
-  const double f0 = column_small(acc, 0) ? Scale<double>::factor() : 1.0;
-  const double f1 = column_small(acc, 1) ? Scale<double>::factor() : 1.0;
+  const double f0 = column_small(acc2, 0) ? Scale<double>::factor() : 1.0;
+  const double f1 = column_small(acc2, 1) ? Scale<double>::factor() : 1.0;
   double* out = p.pre + ((size_t)(c - p.n_tips) * SP + g) * p.cols_pad + col0 + 8 * warp + 2 * tg;
 #pragma unroll
   for (int mi = 0; mi < 8; ++mi)
-    *reinterpret_cast<double2*>(out + (size_t)8 * mi * p.cols_pad) = make_double2(acc[mi][0] * f0, acc[mi][1] * f1);
+    *reinterpret_cast<double2*>(out + (size_t)8 * mi * p.cols_pad) = make_double2(acc2[mi][0] * f0, acc2[mi][1] * f1);
   double gsum = 0.0;
   if (g == 0) {
     const double2 w = *reinterpret_cast<const double2*>(p.weights + col0 + 8 * warp + 2 * tg);
