@@ -330,12 +330,18 @@ def run_b200(a):
                 best = min(best, m0.elapsed_time(m1))
             peak_tf = 2 * 4096 ** 3 / (best * 1e-3) / 1e12
             ach_tf = flops / (k_avg_ms * 1e-3) / 1e12
+            # what the message formulation actually issues on the tensor cores (64-padded tiles): one
+            # product per internal node, two per internal non-root node, two per branch in K1
+            tiles = info["n_tiles"]
+            issued = 2 * 64 ** 3 * (tiles * ((N_ - 1) + 2 * (N_ - 2)) + 2 * (2 * N_ - 2))
             line["dtype"] = "f64"
             # transition, one post-order launch per level, one pre-order launch per depth, tips, reduce
             line["gpu_launches"] = (1 + info["post_rounds"] + info["pre_rounds"] + 2) * a.steps
             line["roofline"] = {"bound": "tensor", "kernel": "dense_post_kernel + dense_pre_kernel (one launch per tree level) + dense_tip_kernel",
                                 "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf, "traffic": None,
-                                "alg_flops_per_eval": flops, "kernel_ms": k_avg_ms, "launches_timed": k_n,
+                                "alg_flops_per_eval": flops, "issued_flops_per_eval": issued,
+                                "issued_tflops": issued / (k_avg_ms * 1e-3) / 1e12, "issued_frac": issued / (k_avg_ms * 1e-3) / 1e12 / peak_tf,
+                                "kernel_ms": k_avg_ms, "launches_timed": k_n,
                                 "peak_source": "fp64 torch.matmul 4096^3 (cuBLAS DGEMM), best of 5, measured in this run"}
         if not a.no_cpu_baseline:
             rate, cores, n, secs, logl_cpu = cpu_port_rate(w, a.cpu_seconds)

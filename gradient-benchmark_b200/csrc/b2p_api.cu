@@ -289,21 +289,33 @@ static cudaError_t dense_launch(b2p_instance* h, const double* d_bl, double* d_l
   p.n_tiles = d->n_tiles; p.n_branches = n_br; p.rate = h->model.rates[0];
   p.P = d->P; p.PT = d->PT; p.D = d->D; p.Q = d->q; p.QT = d->qt; p.freqs = d->freqs; p.codes = d->codes;
   p.weights = d->weights; p.msg = d->msg; p.pre = d->pre; p.scount = d->scount; p.lpart = h->d_lpart; p.gpart = h->d_gpart;
-  dense_transition_kernel<<<n_br, DNT, 3 * DENSE_TILE_BYTES, st>>>(d->evec, d->ivec, d->evals, d->qt, d_bl, p.rate, d->S, d->P, d->PT, d->D);
   cudaError_t e = cudaMemsetAsync(d->scount, 0, sizeof(int) * d->cols_pad, st);
   if (e != cudaSuccess) return e;
   const int slot = (int)(h->prof_count % b2p_instance::kProfRing);
   if (h->profiling) cudaEventRecord(h->ev0[slot], st);
+  dense_transition_kernel<<<n_br, DNT, 3 * DENSE_TILE_BYTES, st>>>(d->evec, d->ivec, d->evals, d->qt, d_bl, p.rate, d->S, d->P, d->PT, d->D);
+  // Level kernels: programmatic dependent launch (b2p_dense.cuh, level_wait): a level's CTAs are
+  // resident and past their prologue when the previous level's last CTA retires.
+  cudaLaunchAttribute pdl[1];
+  pdl[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  pdl[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(DNT); cfg.stream = st; cfg.attrs = pdl; cfg.numAttrs = 1;
   for (size_t L = 0; L + 1 < d->post_off.size(); ++L) {
     const int n = d->post_off[L + 1] - d->post_off[L];
-    if (n > 0) dense_post_kernel<<<dim3(n, d->n_tiles), DNT, 2 * DENSE_TILE_BYTES, st>>>(p, d->nodes + d->post_off[L], d->root);
+    if (n <= 0) continue;
+    cfg.gridDim = dim3(n, d->n_tiles); cfg.dynamicSmemBytes = 2 * DENSE_TILE_BYTES;
+    if ((e = cudaLaunchKernelEx(&cfg, dense_post_kernel, p, (const DenseNode*)(d->nodes + d->post_off[L]), d->root)) != cudaSuccess) return e;
   }
   if (d_grad) {
     for (size_t L = 0; L + 1 < d->pre_off.size(); ++L) {
       const int n = d->pre_off[L + 1] - d->pre_off[L];
-      if (n > 0) dense_pre_kernel<<<dim3(n, d->n_tiles), DNT, 3 * DENSE_TILE_BYTES, st>>>(p, d->nodes + d->pre_off[L], d->root);
+      if (n <= 0) continue;
+      cfg.gridDim = dim3(n, d->n_tiles); cfg.dynamicSmemBytes = 3 * DENSE_TILE_BYTES;
+      if ((e = cudaLaunchKernelEx(&cfg, dense_pre_kernel, p, (const DenseNode*)(d->nodes + d->pre_off[L]), d->root)) != cudaSuccess) return e;
     }
-    dense_tip_kernel<<<dim3(N, d->n_tiles), DNT, 0, st>>>(p, d->nodes + d->tip_off, d->root);
+    cfg.gridDim = dim3(N, d->n_tiles); cfg.dynamicSmemBytes = 0;
+    if ((e = cudaLaunchKernelEx(&cfg, dense_tip_kernel, p, (const DenseNode*)(d->nodes + d->tip_off), d->root)) != cudaSuccess) return e;
   }
   if (h->profiling) { cudaEventRecord(h->ev1[slot], st); ++h->prof_count; }
   const int nb = d_grad ? n_br : 0;
@@ -576,7 +588,7 @@ int b2p_get_info(const b2p_instance* h, b2p_info* o) {
   if (h->dense) {
     memset(&o->precision, 0, sizeof(*o) - offsetof(b2p_info, precision));
     o->precision = h->cfg.precision; o->warps_per_block = DNT / 32; o->cols_per_tile = DT; o->n_tiles = h->dense->n_tiles;
-    o->grid_blocks = h->dense->n_tiles; o->blocks_per_sm = 1; o->n_sms = h->n_sms;
+    o->grid_blocks = h->dense->n_tiles; o->blocks_per_sm = 2; o->n_sms = h->n_sms;
     o->post_rounds = h->plan.rounds_post; o->pre_rounds = h->plan.rounds_pre; o->tree_depth = h->plan.tree_depth;
     o->regs_per_thread = h->regs; o->smem_bytes = 3 * DENSE_TILE_BYTES; o->device_bytes = h->device_bytes;
     o->alg_bytes_loglik = (2 * N - 3) * U + N * P;

@@ -86,6 +86,17 @@ __device__ __forceinline__ void fetch_matrix(const double* __restrict__ g, int k
   for (int u = 0; u < DH; ++u) v[u] = *reinterpret_cast<const double2*>(g + (k0 + 8 * u) * SP + cp);
 }
 
+// Programmatic dependent launch: the level kernels are launched with the stream-serialization
+// attribute, so a level's CTAs become resident while the previous level drains and run their
+// prologue (task, tip codes, matrices that older launches wrote) before level_wait() — which
+// returns once the previous launch has completed and its writes are visible.  A CTA releases its
+// own dependents only AFTER its wait, so by induction everything older than the previous launch
+// is complete whenever a prologue runs.
+__device__ __forceinline__ void level_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
 // Operands that need no arithmetic on the way in (matrices, an internal child's own message) go
 // straight from global to shared memory (LDGSTS): no registers, so the register-staged operands
 // of BOTH tile halves can be in flight with them in one latency round.
@@ -266,6 +277,7 @@ __global__ void __launch_bounds__(DNT, 3) dense_post_kernel(const DenseParams p,
   unsigned lc0, lc1, rc0, rc1;
   fetch_codes(p, nd.l, col0 + cp, lc0, lc1);
   fetch_codes(p, nd.r, col0 + cp, rc0, rc1);
+  level_wait();  // P^T comes from the transition launch, which may be the previous one
   if (!is_root) copy_rows_async(A, p.PT + (size_t)nd.v * SP * SP, SP, kr, cp);
   {
     double2 ml[2][DH], mr[2][DH];
@@ -345,6 +357,7 @@ __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, 
   fetch_codes(p, sib, col0 + cp, sc0, sc1);
   copy_rows_async(A1, p.Q, SP, kr, cp);
   copy_rows_async(A2, p.P + (size_t)c * SP * SP, SP, kr, cp);
+  level_wait();  // the parent's pre-order partial comes from the previous launch
   {
     double2 ms[2][DH], uu[2][DH];
 #pragma unroll
@@ -426,6 +439,7 @@ __global__ void __launch_bounds__(DNT, 3) dense_tip_kernel(const DenseParams p, 
   fetch_codes(p, sib, col0 + cp, sc0, sc1);
   fetch_codes(p, c, col0 + cp, cc0, cc1);
   const bool known0 = cc0 < (unsigned)p.n_states, known1 = cc1 < (unsigned)p.n_states;
+  level_wait();
   double den0 = 0.0, den1 = 0.0, num0 = 0.0, num1 = 0.0;
 #pragma unroll
   for (int h = 0; h < 2; ++h) {
