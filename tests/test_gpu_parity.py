@@ -206,6 +206,31 @@ def test_codon_missing_states_and_rescaling():
     assert grad_err(grad, og) < TOL_GRAD_F64
 
 
+def test_codon_full_size_properties():
+    """BASELINE.json configs[4] at its full size (500 taxa x 2000 codon patterns), where the numpy
+    oracle takes minutes: size-independent properties instead.  Two evaluations are bit-identical
+    (every sum has a fixed order), and doubling the pattern weights doubles logL and every
+    derivative exactly (a power of two commutes with every rounding)."""
+    w = make_workload("codon_500x2000")
+    assert w.n_tips == 500 and w.n_patterns == 2000
+    eng = make_engine(w)
+    try:
+        logl, grad = eng.loglik_grad_host(w.tree.branch_lengths)
+        logl2, grad2 = eng.loglik_grad_host(w.tree.branch_lengths)
+    finally:
+        eng.close()
+    assert np.isfinite(logl) and np.all(np.isfinite(grad))
+    assert logl == logl2 and np.array_equal(grad, grad2)
+    sp = w.patterns
+    w2 = Workload("codon_w2", w.tree, SitePattern(sp.names, sp.masks, sp.weights * 2.0, 61), w.subst_model, w.site_model)
+    eng = make_engine(w2)
+    try:
+        logl_w, grad_w = eng.loglik_grad_host(w2.tree.branch_lengths)
+    finally:
+        eng.close()
+    assert logl_w == 2.0 * logl and np.array_equal(grad_w, 2.0 * grad)
+
+
 @pytest.mark.parametrize("env", [{"B2P_NP": "2", "B2P_CW_LOADS": "14"}, {"B2P_NP": "1"}, {"B2P_NP": "4", "B2P_CW_LOADS": "3"},
                                  {"B2P_CPT": "1"}, {"B2P_DEPTH": "2"}, {"B2P_CTAS": "2"}])
 def test_kernel_knobs_keep_parity(env, monkeypatch):
