@@ -195,8 +195,14 @@ def run_b200(a):
         raise SystemExit("bench.py: no CUDA device; the engine has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    stdout_fd = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # NCCL writes its version banner to file descriptor 1 on first use: route everything but the
+        # JSON line to stderr, so stdout carries exactly one line
+        sys.stdout.flush()
+        stdout_fd = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
     if world != a.gpus and rank == 0:
         print(f"bench.py: --gpus {a.gpus} but WORLD_SIZE={world}; using {world}", file=sys.stderr)
@@ -351,6 +357,9 @@ def run_b200(a):
                                               + ("(numpy restatement, one core)" if dense else "(C oracle, OpenMP)"),
                                     "single_core_value": rate1,
                                     "logl_rel_diff_vs_gpu": abs(logl_cpu - result_dev[0]) / abs(logl_cpu) if world == 1 else None}
+        if stdout_fd is not None:
+            sys.stdout.flush()
+            os.dup2(stdout_fd, 1)
         print(json.dumps(line), flush=True)
     model.close()
     if world > 1:
