@@ -51,7 +51,8 @@ class _Info(ctypes.Structure):
 
 
 def library_path() -> str:
-    return os.path.join(_HERE, _LIB_NAME)
+    # B2P_LIB: a differently built copy of the same library (debug builds: -DB2P_TRACE_CLOCKS)
+    return os.environ.get("B2P_LIB") or os.path.join(_HERE, _LIB_NAME)
 
 
 _lib = None

@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -440,9 +441,14 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   if (!h->kernel) { fail(h, B2P_ERR_ARG, "b2p_create: no kernel for %d threads", h->wg.nt); return bail(B2P_ERR_ARG); }
   // function attributes are process-wide: never lower what another live instance asked for
   static std::map<const void*, size_t> smem_asked;
-  size_t& asked = smem_asked[h->kernel];
-  asked = std::max(asked, h->wg.smem);
-  if ((e = cudaFuncSetAttribute(h->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asked)) != cudaSuccess) {
+  static std::mutex smem_asked_lock;
+  {
+    std::lock_guard<std::mutex> guard(smem_asked_lock);
+    size_t& asked = smem_asked[h->kernel];
+    asked = std::max(asked, h->wg.smem);
+    e = cudaFuncSetAttribute(h->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asked);
+  }
+  if (e != cudaSuccess) {
     fail(h, B2P_ERR_CUDA, "cudaFuncSetAttribute(smem=%zu): %s", h->wg.smem, cudaGetErrorString(e));
     return bail(B2P_ERR_CUDA);
   }
@@ -455,9 +461,7 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
 
   const size_t n_br = 2 * (size_t)N - 2;
   const size_t part_bytes = (size_t)h->wg.n_tiles * (size_t)(N - 1) * (size_t)h->wg.blk;
-  if ((rc = dev_alloc(h, &h->d_tips, (size_t)h->wg.n_tiles * 2 * N * h->wg.ct_pad))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_tips_raw, (size_t)N * P))) return bail(rc);
-  if ((rc = dev_alloc(h, &h->d_tip_order, sizeof(int) * 2 * N))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_weights, sizeof(double) * P))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_mat_dst, sizeof(int) * 2 * n_br))) return bail(rc);
   if ((rc = dev_alloc(h, (char**)&h->d_msg, part_bytes))) return bail(rc);
@@ -485,18 +489,17 @@ template <typename T>
 static void fill_walk_params(const b2p_instance* h, bool grad, WalkParams<T>& p) {
   const int N = h->cfg.n_tips, K = h->cfg.n_categories, P = h->cfg.n_patterns;
   const WalkGeometry& g = h->wg;
-  p.n_tiles = g.n_tiles; p.rounds_run = grad ? h->plan.rounds : h->plan.rounds_post;
+  p.n_tiles = g.n_tiles; p.rounds_run = grad ? h->plan.rounds : h->plan.rounds_post; p.rounds_post = h->plan.rounds_post;
   p.n_branches = 2 * N - 2; p.n_cat = K; p.n_cols = P * K; p.n_patterns = P; p.n_copy_warps = g.n_copy_warps;
-  p.cw_loads = getenv("B2P_CW_LOADS") ? std::max(0, std::min(atoi(getenv("B2P_CW_LOADS")), g.nt / 32 - g.n_copy_warps)) : 0;
   p.ct = g.ct; p.ts = g.ts; p.cpw = g.cpw; p.wn = g.wn; p.stages = g.stages; p.depth = g.depth;
-  p.blk = g.blk; p.plane = g.ct * 16; p.ct_pad = g.ct_pad; p.mat_stride = g.mat_stride;
+  p.blk = g.blk; p.plane = g.ct * 16; p.ct_pad = g.ct_pad; p.row_stride = g.row_stride;
   p.frame_bytes = g.frame_bytes; p.off_frame = g.off_frame; p.rel_cr = g.rel_cr; p.rel_mats = g.rel_mats;
-  p.rel_tips = g.rel_tips;
-  p.off_bar = g.off_bar; p.off_gbuf = g.off_gbuf; p.off_gids = g.off_gids; p.off_scount = g.off_scount;
-  p.ir_base = h->plan.ir_base; p.boot_base = h->plan.boot_base;
+  p.rel_tips = g.rel_tips; p.ir_jobs = 16 + g.ir_ids;
+  p.off_bar = g.off_bar; p.off_gbuf = g.off_gbuf; p.off_scount = g.off_scount; p.off_freq = g.off_freq;
+  p.boot_base = h->plan.boot_base; p.tail_base = h->plan.tail_base + (grad ? 0u : (unsigned)g.ir_ids);
   for (int i = 0; i < 4; ++i) { p.boot_n[i] = h->plan.boot_n[i]; p.boot_tx[i] = h->plan.boot_tx[i]; }
   p.tile_stride_part = (unsigned long long)(N - 1) * g.blk;
-  p.tile_stride_tips = 2ull * N * g.ct_pad;
+  p.tile_stride_tips = (unsigned long long)h->plan.rounds * 2ull * g.wn * g.ct_pad;
   p.records = h->d_records; p.mats = (const unsigned char*)h->d_mats;
   p.msg = (unsigned char*)h->d_msg; p.pre = (unsigned char*)h->d_pre; p.tips = h->d_tips;
   p.weights = h->d_weights; p.lpart = h->d_lpart; p.gpart = h->d_gpart; p.trace = h->d_trace;
@@ -536,8 +539,8 @@ static cudaError_t launch_eval(b2p_instance* h, const double* d_bl, double* d_lo
   const int N = h->cfg.n_tips, K = h->cfg.n_categories;
   const int n_br = 2 * N - 2;
   const int total = n_br * K * 16;
-  transition_kernel<T><<<(total + 255) / 256, 256, 0, st>>>(h->model, d_bl, n_br, N, K, h->d_mat_dst,
-                                                            h->wg.mat_stride / (int)sizeof(T), (T*)h->d_mats);
+  transition_kernel<T><<<(total + 255) / 256, 256, 0, st>>>(h->model, d_bl, n_br, N, K, h->d_mat_dst, h->wg.row_stride,
+                                                            (unsigned char*)h->d_mats);
   const int slot = (int)(h->prof_count % b2p_instance::kProfRing);
   if (h->profiling) cudaEventRecord(h->ev0[slot], st);
   WalkParams<T> wp;
@@ -560,9 +563,11 @@ static cudaError_t launch_eval(b2p_instance* h, const double* d_bl, double* d_lo
 static int retile_tips(b2p_instance* h) {
   const WalkGeometry& g = h->wg;
   const int N = h->cfg.n_tips;
-  const long long total = (long long)g.n_tiles * 2 * N * g.ct_pad;
+  const int n_rows = h->plan.rounds * 2 * g.wn;
+  const long long total = (long long)g.n_tiles * n_rows * g.ct_pad;
+  (void)N;
   CU(cudaSetDevice(h->cfg.device));
-  tile_tips_kernel<<<(unsigned)((total + 255) / 256), 256>>>(h->d_tips_raw, h->d_tip_order, g.n_tiles, 2 * N, g.ct, g.ct_pad,
+  tile_tips_kernel<<<(unsigned)((total + 255) / 256), 256>>>(h->d_tips_raw, h->d_tip_order, g.n_tiles, n_rows, g.ct, g.ct_pad,
                                                               h->cfg.n_patterns, h->cfg.n_categories, h->d_tips);
   CU(cudaGetLastError());
   CU(cudaDeviceSynchronize());
@@ -620,17 +625,21 @@ int b2p_set_topology(b2p_instance* h, const int32_t* h_triples) {
     return fail(h, B2P_ERR_ARG, "b2p_set_topology: %s", why.c_str());
   CU(cudaSetDevice(h->cfg.device));
   CU(cudaDeviceSynchronize());
-  cudaFree(h->d_records); cudaFree(h->d_mats);
-  h->d_records = nullptr; h->d_mats = nullptr;
+  cudaFree(h->d_records); cudaFree(h->d_mats); cudaFree(h->d_tips); cudaFree(h->d_tip_order);
+  h->d_records = nullptr; h->d_mats = nullptr; h->d_tips = nullptr; h->d_tip_order = nullptr;
   h->have_topology = false;
-  const size_t mats_bytes = (size_t)plan.rounds * h->wg.mats_bytes;
+  const size_t mats_bytes = plan.mats_off.back();
+  const size_t tips_bytes = (size_t)h->wg.n_tiles * plan.tip_order.size() * h->wg.ct_pad;
   CU(cudaMalloc((void**)&h->d_records, plan.records.size()));
   CU(cudaMemcpy(h->d_records, plan.records.data(), plan.records.size(), cudaMemcpyHostToDevice));
   CU(cudaMalloc(&h->d_mats, mats_bytes));
   CU(cudaMemset(h->d_mats, 0, mats_bytes));
+  CU(cudaMalloc((void**)&h->d_tips, tips_bytes));
+  CU(cudaMalloc((void**)&h->d_tip_order, plan.tip_order.size() * sizeof(int32_t)));
   CU(cudaMemcpy(h->d_mat_dst, plan.mat_dst.data(), plan.mat_dst.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
-  if ((int)plan.tip_order.size() != 2 * h->cfg.n_tips) return fail(h, B2P_ERR_ARG, "b2p_set_topology: internal error (tip rows)");
+  if ((int)plan.tip_order.size() != plan.rounds * 2 * h->wg.wn) return fail(h, B2P_ERR_ARG, "b2p_set_topology: internal error (tip rows)");
   CU(cudaMemcpy(h->d_tip_order, plan.tip_order.data(), plan.tip_order.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+  plan.mats_off.clear(); plan.mats_off.shrink_to_fit();
   plan.tip_order.clear(); plan.tip_order.shrink_to_fit();
   plan.records.clear(); plan.records.shrink_to_fit();
   plan.mat_dst.clear(); plan.mat_dst.shrink_to_fit();

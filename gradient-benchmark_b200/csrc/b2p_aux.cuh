@@ -3,6 +3,7 @@
 //   K4 reduce_kernel       deterministic sum of per-CTA partial results      (rows a4, a6)
 #pragma once
 #include "b2p_device.cuh"
+#include "b2p_walk_types.h"
 
 namespace b2p {
 
@@ -17,14 +18,17 @@ struct ModelParams {  // passed by value to K1
 // One thread per (branch, category, matrix entry).  P = V e^{lambda r t} V^-1, computed
 // in fp64, stored as T — directly into the traversal kernel's per-round matrix bundles
 // (schedule order, so one bulk copy per round brings every matrix that round needs).
-// mat_dst[2b], mat_dst[2b+1]: the branch's matrix slot in the post- / pre-order rounds
-// (-1: not used there).  Tip branches are stored transposed: the traversal picks a COLUMN
-// of P by the tip's state.  (dP/dt = r Q P is never formed: the pre-order task applies Q
-// from the constant bank to P x instead.)
+// mat_dst[2b], mat_dst[2b+1]: byte offset of the branch's rows in the post- / pre-order
+// bundles (-1: not used there).  A row holds all K categories (category k at k * 4 values,
+// rows row_stride bytes apart).
+//   internal branch: 4 rows, row i = P[i][.]            (m_v = P x  and  u_c = P^T q read rows)
+//   tip branch:      5 rows, row s = P[.][s] (the message of a tip in state s is a COLUMN of
+//                    P), row 4 = all ones (gap / unknown state: P 1 = 1)
+// (dP/dt = r Q P is never formed: the pre-order task applies Q from the constant bank to P x.)
 template <typename T>
 __global__ void transition_kernel(ModelParams m, const double* __restrict__ bl, int n_branches, int n_tips,
-                                  int n_cat, const int* __restrict__ mat_dst, int mat_stride_elems,
-                                  T* __restrict__ bundles) {
+                                  int n_cat, const int* __restrict__ mat_dst, int row_stride,
+                                  unsigned char* __restrict__ bundles) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int total = n_branches * n_cat * 16;
   if (idx >= total) return;
@@ -35,17 +39,23 @@ __global__ void transition_kernel(ModelParams m, const double* __restrict__ bl, 
   double p = 0.0;
 #pragma unroll
   for (int j = 0; j < 4; ++j) p += m.evec[i * 4 + j] * m.ivec[j * 4 + l] * exp(m.evals[j] * t);
-  const int at = b < n_tips ? l * 4 + i : e;
+  const bool tip = b < n_tips;
+  const int row = tip ? l : i, pos = tip ? i : l;
 #pragma unroll
   for (int w = 0; w < 2; ++w) {
-    const int slot = mat_dst[2 * b + w];
-    if (slot >= 0) bundles[((size_t)slot * n_cat + k) * mat_stride_elems + at] = (T)p;
+    const int dst = mat_dst[2 * b + w];
+    if (dst < 0) continue;
+    T* base = reinterpret_cast<T*>(bundles + dst) + k * 4;
+    base[(size_t)row * (row_stride / (int)sizeof(T)) + pos] = (T)p;
+    if (tip && l == 0) base[(size_t)kTipAny * (row_stride / (int)sizeof(T)) + i] = (T)1;
   }
 }
 
 // ---------------------------------------------------------------------------- K0 (setup)
-// Tip state masks per tile: out[tile][row][c] = mask of tip order[row] at the pattern of
-// column tile*ct + c; 15 (any state) for padding columns.  Runs when tips or topology change.
+// Tip state codes per tile: out[tile][row][c] = code of tip order[row] at the pattern of
+// column tile*ct + c (0..3: the state; 4: any state — also padding columns and rows that
+// belong to an internal child; 16 | mask: another ambiguity set).  Runs when tips or
+// topology change.
 __global__ void tile_tips_kernel(const uint8_t* __restrict__ raw, const int* __restrict__ order, int n_tiles,
                                  int n_rows, int ct, int ct_pad, int n_patterns, int n_cat, uint8_t* __restrict__ out) {
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -55,9 +65,11 @@ __global__ void tile_tips_kernel(const uint8_t* __restrict__ raw, const int* __r
   const long long tr = idx / ct_pad;
   const int row = (int)(tr % n_rows), tile = (int)(tr / n_rows);
   const long long cg = (long long)tile * ct + c;
+  const int tip = order[row];
   uint8_t m = 15;
-  if (c < ct && cg < (long long)n_patterns * n_cat) m = raw[(size_t)order[row] * n_patterns + cg / n_cat];
-  out[idx] = m;
+  if (tip >= 0 && c < ct && cg < (long long)n_patterns * n_cat) m = raw[(size_t)tip * n_patterns + cg / n_cat];
+  const uint8_t code = m == 1 ? 0 : m == 2 ? 1 : m == 4 ? 2 : m == 8 ? 3 : m == 15 ? (uint8_t)kTipAny : (uint8_t)(kTipAmbiguous | m);
+  out[idx] = code;
 }
 
 // ---------------------------------------------------------------------------- K4

@@ -43,30 +43,45 @@ struct WalkGeometry {
   int off_frame = 0, rel_ir = 0, rel_cr = 0, rel_mats = 0, rel_tips = 0;
   int ct_pad = 0;      // bytes of one tip row of a tile (ct rounded up to 16)
   int blk = 0;         // bytes of one block
-  int mat_stride = 0;  // bytes between 4x4 matrices (padded: bank shift between categories)
-  int mats_bytes = 0;  // one round's matrix bundle: wn * 3 * K matrices
-  int cr_bytes = 0;    // one round's descriptors + branch ids
-  int ir_bytes = 0;    // one round's issue record (header + max_jobs jobs)
+  int row_bytes = 0;   // one category's 4 values of a matrix row: 4 * elem
+  int row_stride = 0;  // bytes between matrix rows: K * row_bytes (+ padding: bank shift between rows)
+  int mats_rows = 0;   // rows one round's matrix bundle may take (the scheduler keeps every round within it)
+  int mats_bytes = 0;  // mats_rows * row_stride
+  int cr_bytes = 0;    // one round's descriptors
+  int ir_ids = 0;      // bytes of the fold ids inside an issue record
+  int ir_bytes = 0;    // one round's issue record (header + fold ids + max_jobs jobs)
   int tips_bytes = 0;  // one round's tip rows: wn * 2 rows
   int max_jobs = 0;
-  int off_bar = 0, off_cr = 0, off_ir = 0, off_mats = 0, off_tips = 0, off_gbuf = 0, off_gids = 0,
-      off_scount = 0, off_pool = 0;
+  int off_bar = 0, off_cr = 0, off_ir = 0, off_mats = 0, off_tips = 0, off_gbuf = 0,
+      off_scount = 0, off_freq = 0, off_pool = 0;
   int n_pool = 0;
   size_t smem = 0;
 };
 
 inline int align16(int x) { return (x + 15) & ~15; }
 
+// Rows of the round's matrix bundle a slot gets on average (B2P_MAT_ROWS overrides): a
+// post-order task with two tip children takes 14, the mix of a random tree about 9.
+inline int mat_rows_per_slot() {
+  const char* e = getenv("B2P_MAT_ROWS");
+  return e ? std::max(8, std::min(atoi(e), kRowsTaskMax)) : 11;
+}
+
 // Shared-memory layout for a given (nt, ct, wn); returns the number of pool blocks (< 0: does not fit).
 inline int layout_walk(WalkGeometry& g, size_t smem_max) {
   const int S = g.stages, wn = g.wn, K = g.K;
   g.blk = g.ct * 4 * g.elem;
   g.ct_pad = align16(g.ct);
-  g.mat_stride = g.elem == 8 ? 144 : 80;
-  g.mats_bytes = wn * 3 * K * g.mat_stride;
-  g.cr_bytes = align16(wn * 16 + wn * 8);
+  g.row_bytes = 4 * g.elem;
+  // rows of different states / matrix rows land in different banks: one category fills 32 (16) bytes,
+  // so K = 1 needs no padding; otherwise shift each row by one category's width
+  g.row_stride = K * g.row_bytes + (K > 1 ? g.row_bytes : 0);
+  g.mats_rows = std::max(kRowsTaskMax, wn * mat_rows_per_slot());
+  g.mats_bytes = g.mats_rows * g.row_stride;
+  g.cr_bytes = wn * 32;
   g.max_jobs = 7 * wn + 3;
-  g.ir_bytes = 16 + g.max_jobs * 16;
+  g.ir_ids = align16(wn * 8);
+  g.ir_bytes = 16 + g.ir_ids + g.max_jobs * 16;
   g.tips_bytes = wn * 2 * g.ct_pad;
   int off = 0;
   g.off_bar = off; off += 64;  // up to 8 mbarriers
@@ -79,16 +94,14 @@ inline int layout_walk(WalkGeometry& g, size_t smem_max) {
   g.off_ir = g.off_frame + g.rel_ir; g.off_cr = g.off_frame + g.rel_cr;
   g.off_mats = g.off_frame + g.rel_mats; g.off_tips = g.off_frame + g.rel_tips;
   g.off_gbuf = off; off += 2 * wn * g.ts * 16;  // one (sum_a, sum_b) pair per compute thread
-  g.off_gids = off; off += align16(2 * wn * 8);
   g.off_scount = off; off += align16(g.ct * 4);
+  off = (off + 127) & ~127;
+  g.off_freq = off; off += g.blk;  // the root's parent-side partial: the frequencies, for every column
   off = (off + 127) & ~127;
   g.off_pool = off;
   const long long left = (long long)smem_max - off;
   if (left < g.blk) return -1;
-  // descriptors address shared memory in 16-byte units with 16 bits
-  long long n = left / g.blk;
-  while (n > 0 && (g.off_pool + n * g.blk) / 16 > 0xFFF0) --n;
-  g.n_pool = (int)n;
+  g.n_pool = (int)(left / g.blk);
   g.smem = (size_t)g.off_pool + (size_t)g.n_pool * g.blk;
   return g.n_pool;
 }
@@ -144,9 +157,12 @@ struct WalkPlan {
   std::vector<uint8_t> records;  // [rounds] CR, then [rounds] IR, then the boot jobs
   uint32_t ir_base = 0, boot_base = 0;
   uint32_t boot_n[4] = {0, 0, 0, 0}, boot_tx[4] = {0, 0, 0, 0};  // loads of rounds 0..depth-1
-  std::vector<int32_t> tip_order;    // tip id of every tip row in schedule order (each tip: once per pass)
-  std::vector<int32_t> tip_row_off;  // [rounds + 1] first row of each round
-  std::vector<int32_t> mat_dst;  // [2N-2][2]: matrix slot ((round*wn+slot)*3+which) in the post / pre bundles, -1 none
+  std::vector<int32_t> tip_order;    // [rounds][wn][2] tip id of every tip row (-1: that child is not a tip)
+  std::vector<int32_t> mat_dst;  // [2N-2][2]: byte offset of the branch's rows in the post / pre bundles (-1: none);
+                                 // tip branches get the 5-row table, internal ones the 4 matrix rows
+  std::vector<uint32_t> mats_off;  // [rounds + 1] byte offset of every round's bundle in the bundle array
+  uint32_t tail_base = 0;          // fold ids of the last round (read from global memory after the loop):
+                                   // of a full run, then (+ ir_ids bytes) of a post-order-only run
   long long resident_reads = 0, loads_msg = 0, loads_pre = 0, stores_msg = 0, stores_pre = 0, evictions = 0;
   int max_jobs_used = 0;
 };
@@ -175,7 +191,7 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
   out.wn_eff = wn_eff;
   const int n_nodes = 2 * N - 1, root = 2 * N - 2;
   if ((unsigned long long)(N - 1) * (unsigned long long)g.blk > 0xFFFFFFF0ull ||
-      2ull * (unsigned long long)N * (unsigned long long)g.ct_pad > 0xFFFFFFF0ull) {
+      (16ull * N + 128ull) * 2ull * (unsigned long long)g.wn * (unsigned long long)g.ct_pad > 0xFFFFFFF0ull) {
     why = "tile too large for 32-bit copy offsets";
     return false;
   }
@@ -191,6 +207,19 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
   }
   for (int v = 0; v < root; ++v)
     if (!seen[v]) { why = "tree is not connected (node without parent)"; return false; }
+  // Canonical child order: a task with exactly one tip child has it on the left, so a round
+  // holds three kinds of task (no tip / one tip / two tips) instead of four.  Everything below
+  // (descriptors, branch ids, matrix slots) follows left[] / right[], so this is only a naming.
+  const bool canon = !(getenv("B2P_PLAN_SORT") && atoi(getenv("B2P_PLAN_SORT")) == 0);
+  if (canon)
+    for (int v = N; v < n_nodes; ++v)
+      if (right[v] < N && left[v] >= N) std::swap(left[v], right[v]);
+  // task kind: number of tip children (tasks of a round are laid out by kind, so that the
+  // threads of a warp — which straddles two slots — mostly take the same branches)
+  auto kind_of = [&](int v) { return (left[v] < N) + (right[v] < N); };
+  auto by_kind = [&](std::vector<int>& chosen) {
+    if (canon) std::stable_sort(chosen.begin(), chosen.end(), [&](int a, int b) { return kind_of(a) < kind_of(b); });
+  };
   std::vector<int> depth(n_nodes, 0), height(n_nodes, 0);
   int max_depth = 0;
   for (int v = root - 1; v >= 0; --v) {
@@ -217,7 +246,10 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
   std::vector<int> cnt;
   auto cnt_at = [&](int j) -> int& { if ((int)cnt.size() <= j) cnt.resize(j + 1, 0); return cnt[j]; };
   // try to add a task to round f: operands produced in rounds px[0..n_op), n_out results
-  auto try_add = [&](int f, const int* px, int n_op, int n_out) -> bool {
+  std::vector<int> rows_used;  // matrix rows of every round's bundle (kept within g.mats_rows)
+  auto try_add = [&](int f, const int* px, int n_op, int n_out, int n_rows) -> bool {
+    if ((int)rows_used.size() <= f) rows_used.resize(f + 1, 0);
+    if (rows_used[f] + n_rows > g.mats_rows) return false;
     int inc[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // windows f-D .. f+1  (D <= 3)
     for (int o = 0; o < n_op; ++o)
       for (int j = std::max(f - D, 0); j <= f; ++j)
@@ -233,8 +265,10 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
       const int j = f - D + w;
       if (j >= 0) cnt_at(j) += inc[w];
     }
+    rows_used[f] += n_rows;
     return true;
   };
+  auto child_rows = [&](int c) { return c < N ? kRowsTip : kRowsPlain; };
   {
     std::vector<int> pending(n_nodes, 0);
     std::priority_queue<Item> ready;
@@ -257,13 +291,15 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
         int px[2], n_op = 0;
         if (left[v] >= N) px[n_op++] = rnd_post[left[v]];
         if (right[v] >= N) px[n_op++] = rnd_post[right[v]];
-        if (!try_add(q, px, n_op, v == root ? 0 : 1)) { skipped.push_back(it); continue; }
+        const int n_rows = (v == root ? 0 : kRowsPlain) + (left[v] < N ? kRowsTip : 0) + (right[v] < N ? kRowsTip : 0);
+        if (!try_add(q, px, n_op, v == root ? 0 : 1, n_rows)) { skipped.push_back(it); continue; }
         chosen.push_back(v);
         if (v == root) break;
       }
       for (const Item& it : skipped) ready.push(it);
       if (chosen.empty() && ready.empty()) { why = "post schedule stalled"; return false; }
       if ((int)tasks.size() > 8 * N + 64) { why = "pool exhausted (schedule)"; return false; }
+      by_kind(chosen);
       for (int i = 0; i < (int)chosen.size(); ++i) { rnd_post[chosen[i]] = q; slot_post[chosen[i]] = i; }
       tasks.push_back(chosen);
       // successors become ready for the NEXT round
@@ -298,7 +334,10 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
           if (left[v] >= N) px[n_op++] = rnd_post[left[v]];
           if (right[v] >= N) px[n_op++] = rnd_post[right[v]];
           if (v != root) px[n_op++] = rnd_pre[parent[v]];
-          if (!try_add(q, px, n_op, (left[v] >= N) + (right[v] >= N))) { skipped.push_back(it); continue; }
+          if (!try_add(q, px, n_op, (left[v] >= N) + (right[v] >= N), child_rows(left[v]) + child_rows(right[v]))) {
+            skipped.push_back(it);
+            continue;
+          }
           chosen.push_back(v);
         }
       }
@@ -306,6 +345,7 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
       for (const Item& it : skipped) old.push(it);
       if (chosen.empty() && old.empty()) { why = "pre schedule stalled"; return false; }
       if ((int)tasks.size() > 16 * N + 128) { why = "pool exhausted (schedule)"; return false; }
+      by_kind(chosen);
       for (int i = 0; i < (int)chosen.size(); ++i) { rnd_pre[chosen[i]] = q; slot_pre[chosen[i]] = i; }
       tasks.push_back(chosen);
       for (int v : chosen) {
@@ -459,45 +499,86 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
   // -------------------------------------------------------------------- records
   const uint32_t cr_total = (uint32_t)R * g.cr_bytes;
   out.ir_base = cr_total;
-  out.boot_base = out.ir_base + (uint32_t)R * g.ir_bytes;
-  // fixed per-round loads: tip rows (one copy: rows are stored in schedule order), matrix
-  // bundle, the round's own records
-  // row within the round's tip copy, per (task, side)
-  std::vector<uint16_t> tip_row_post(2 * (size_t)n_nodes, 0), tip_row_pre(2 * (size_t)n_nodes, 0);
-  out.tip_row_off.assign(R + 1, 0);
+  out.tail_base = out.ir_base + (uint32_t)R * g.ir_bytes;
+  out.boot_base = out.tail_base + 2u * (uint32_t)g.ir_ids;
+  // Matrix bundle of every round: the tasks' rows back to back, slot by slot —
+  //   post-order task: [own matrix, 4 rows (not the root)] [left tip table, 5] [right tip table, 5]
+  //   pre-order task:  [left child: tip table 5 / matrix 4] [right child: likewise]
+  // mat_dst tells K1 where each branch's rows go (byte offsets into the bundle array).
+  out.mat_dst.assign(2 * (size_t)(2 * N - 2), -1);
+  out.mats_off.assign(R + 1, 0);
+  std::vector<uint32_t> mrow_own(n_nodes, 0), mrow_post(2 * (size_t)n_nodes, 0), mrow_pre(2 * (size_t)n_nodes, 0);  // row within the round
+  for (int f = 0; f < R; ++f) {
+    uint32_t rows = 0;
+    for (int v : tasks[f]) {
+      const int ch[2] = {left[v], right[v]};
+      if (f < Rpost) {
+        if (v != root) { mrow_own[v] = rows; out.mat_dst[2 * (size_t)v] = (int32_t)(out.mats_off[f] + rows * g.row_stride); rows += kRowsPlain; }
+        for (int side = 0; side < 2; ++side)
+          if (ch[side] < N) {
+            mrow_post[2 * (size_t)v + side] = rows;
+            out.mat_dst[2 * (size_t)ch[side]] = (int32_t)(out.mats_off[f] + rows * g.row_stride);
+            rows += kRowsTip;
+          }
+      } else {
+        for (int side = 0; side < 2; ++side) {
+          mrow_pre[2 * (size_t)v + side] = rows;
+          out.mat_dst[2 * (size_t)ch[side] + 1] = (int32_t)(out.mats_off[f] + rows * g.row_stride);
+          rows += ch[side] < N ? kRowsTip : kRowsPlain;
+        }
+      }
+    }
+    if ((int)rows > g.mats_rows) { why = "internal error: matrix bundle over budget"; return false; }
+    out.mats_off[f + 1] = out.mats_off[f] + rows * (uint32_t)g.row_stride;
+  }
+  // fixed per-round loads: tip code rows, matrix bundle, the round's descriptors.  Tip rows sit at
+  // FIXED positions — row 2 * slot + side of the round — so a thread reads its tip codes without
+  // waiting for its descriptor; rows of internal children are never read for their value.
+  out.tip_order.assign((size_t)R * 2 * wn, -1);
   for (int f = 0; f < R; ++f) {
     const int st = f % S;
-    int rows = 0;
+    bool any = false;
     for (int s = 0; s < (int)tasks[f].size(); ++s) {
       const int v = tasks[f][s];
       for (int side = 0; side < 2; ++side) {
         const int c = side ? right[v] : left[v];
         if (c >= N) continue;
-        (f < Rpost ? tip_row_post : tip_row_pre)[2 * (size_t)v + side] = (uint16_t)rows++;
-        out.tip_order.push_back(c);
+        out.tip_order[((size_t)f * wn + s) * 2 + side] = c;
+        any = true;
       }
     }
-    out.tip_row_off[f + 1] = out.tip_row_off[f] + rows;
-    if (rows)
-      loads[f].push_back({JK_TIPS, (uint32_t)out.tip_row_off[f] * (uint32_t)g.ct_pad,
-                          (uint32_t)(g.off_tips + st * g.frame_bytes), (uint32_t)(rows * g.ct_pad)});
-    if (!tasks[f].empty())
-      loads[f].push_back({JK_MATS, (uint32_t)f * (uint32_t)g.mats_bytes, (uint32_t)(g.off_mats + st * g.frame_bytes),
-                          (uint32_t)((int)tasks[f].size() * 3 * K * g.mat_stride)});
+    if (any)
+      loads[f].push_back({JK_TIPS, (uint32_t)f * 2u * (uint32_t)wn * (uint32_t)g.ct_pad,
+                          (uint32_t)(g.off_tips + st * g.frame_bytes), (uint32_t)(2 * (int)tasks[f].size() * g.ct_pad)});
+    if (out.mats_off[f + 1] > out.mats_off[f])
+      loads[f].push_back({JK_MATS, out.mats_off[f], (uint32_t)(g.off_mats + st * g.frame_bytes),
+                          out.mats_off[f + 1] - out.mats_off[f]});
     loads[f].push_back({JK_REC, (uint32_t)f * (uint32_t)g.cr_bytes, (uint32_t)(g.off_cr + st * g.frame_bytes), (uint32_t)g.cr_bytes});
   }
-  // issue records: IR[q] = loads of round q + D, stores of round q - 1
-  std::vector<uint32_t> ir_len(R, 16);
+  // issue records: IR[q] = fold ids of round q - 1, loads of round q + D, stores of round q - 1
+  const uint32_t ir_head = 16u + (uint32_t)g.ir_ids;
+  std::vector<uint32_t> ir_len(R, ir_head);
   for (int q = 0; q < R; ++q) {
     const int n_l = q + D < R ? (int)loads[q + D].size() + 1 : 0;  // + the IR of round q + D itself
     const int n_s = (int)stores[q].size();
     if (n_l + n_s > g.max_jobs) { why = "too many copies in one round"; return false; }
     out.max_jobs_used = std::max(out.max_jobs_used, n_l + n_s);
-    ir_len[q] = 16u + 16u * (uint32_t)(n_l + n_s);
+    ir_len[q] = ir_head + 16u * (uint32_t)(n_l + n_s);
   }
   size_t n_boot = 0;
   for (int f = 0; f < std::min(D, R); ++f) n_boot += loads[f].size() + 1;
   out.records.assign((size_t)out.boot_base + n_boot * 16, 0);
+  // what the two sums of every slot belong to: the children's branches of a pre-order task,
+  // the log-likelihood term of the root's post-order task
+  auto fold_ids = [&](int q, WalkIds* ids) {
+    for (int s = 0; s < wn; ++s) ids[s] = WalkIds{-1, -1};
+    if (q < 0) return;
+    for (int s = 0; s < (int)tasks[q].size(); ++s) {
+      const int v = tasks[q][s];
+      if (q >= Rpost) ids[s] = WalkIds{left[v], right[v]};
+      else if (v == root) ids[s] = WalkIds{-2, -1};
+    }
+  };
   auto ir_job = [&](int f) {
     return WalkJob{out.ir_base + (uint32_t)f * (uint32_t)g.ir_bytes, (uint32_t)(g.off_ir + (f % S) * g.frame_bytes), ir_len[f], JK_REC};
   };
@@ -505,7 +586,8 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
   for (int q = 0; q < R; ++q) {
     uint8_t* p = out.records.data() + out.ir_base + (size_t)q * g.ir_bytes;
     WalkIssueHeader h{0, 0, 0, q >= Rpost ? 1u : 0u};
-    WalkJob* jobs = reinterpret_cast<WalkJob*>(p + 16);
+    fold_ids(q - 1, reinterpret_cast<WalkIds*>(p + 16));
+    WalkJob* jobs = reinterpret_cast<WalkJob*>(p + ir_head);
     int n = 0;
     if (q + D < R) {
       for (const LoadRec& l : loads[q + D]) { jobs[n++] = job_of(l); h.tx_bytes += l.bytes; }
@@ -516,6 +598,9 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
     h.n_stores = (uint32_t)n - h.n_loads;
     std::memcpy(p, &h, 16);
   }
+  // after the last round: of a full run, and of a run that stops after the post-order rounds
+  fold_ids(R - 1, reinterpret_cast<WalkIds*>(out.records.data() + out.tail_base));
+  fold_ids(Rpost - 1, reinterpret_cast<WalkIds*>(out.records.data() + out.tail_base + g.ir_ids));
   {
     WalkJob* jobs = reinterpret_cast<WalkJob*>(out.records.data() + out.boot_base);
     int n = 0;
@@ -526,49 +611,36 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
       out.boot_n[f] = (uint32_t)(n - n0);
     }
   }
-  // descriptors + branch ids
-  auto off16 = [&](int b) { return b < 0 ? kNoBlk : (uint16_t)((g.off_pool + b * g.blk) / 16); };
-  out.mat_dst.assign(2 * (size_t)(2 * N - 2), -1);
+  // descriptors: byte offsets into shared memory for the stage the round runs in
+  auto blk_off = [&](int b) { return (uint32_t)(g.off_pool + b * g.blk); };
   for (int q = 0; q < R; ++q) {
-    uint8_t* p = out.records.data() + (size_t)q * g.cr_bytes;
-    WalkDesc* d = reinterpret_cast<WalkDesc*>(p);
-    WalkIds* ids = reinterpret_cast<WalkIds*>(p + wn * 16);
-    for (int s = 0; s < wn; ++s) {
-      d[s] = WalkDesc{kNoBlk, kNoBlk, kNoBlk, kNoBlk, kNoBlk, 0, 0, 0};
-      ids[s] = WalkIds{-1, -1};
-    }
+    WalkDesc* d = reinterpret_cast<WalkDesc*>(out.records.data() + (size_t)q * g.cr_bytes);
+    const uint32_t mats0 = (uint32_t)(g.off_mats + (q % S) * g.frame_bytes);
+    auto mat_at = [&](uint32_t row) { return mats0 + row * (uint32_t)g.row_stride; };
+    for (int s = 0; s < wn; ++s) std::memset(&d[s], 0, sizeof(WalkDesc));
     for (int s = 0; s < (int)tasks[q].size(); ++s) {
       const int v = tasks[q][s], l = left[v], r = right[v];
-      const int slot3 = (q * wn + s) * 3;
       WalkDesc& e = d[s];
+      const bool post = q < Rpost;
+      const std::vector<int>& src = post ? src_post : src_pre;
+      const size_t so = (post ? 2 : 3) * (size_t)v;
       e.flags = WF_LIVE;
-      e.pad0 = (q < Rpost ? tip_row_post : tip_row_pre)[2 * (size_t)v];      // tip row of the left child
-      e.pad1 = (q < Rpost ? tip_row_post : tip_row_pre)[2 * (size_t)v + 1];  // ... of the right child
       if (l < N) e.flags |= WF_TIP_L;
       if (r < N) e.flags |= WF_TIP_R;
       if (v == root) e.flags |= WF_ROOT;
-      if (q < Rpost) {
-        e.src_l = off16(src_post[2 * (size_t)v]);
-        e.src_r = off16(src_post[2 * (size_t)v + 1]);
-        if (v != root) { e.dst0 = off16(dst_post[v]); out.mat_dst[2 * (size_t)v] = slot3; }
-        else ids[s] = WalkIds{-2, -1};
-        if (l < N) out.mat_dst[2 * (size_t)l] = slot3 + 1;
-        if (r < N) out.mat_dst[2 * (size_t)r] = slot3 + 2;
-      } else {
-        e.src_l = off16(src_pre[3 * (size_t)v]);
-        e.src_r = off16(src_pre[3 * (size_t)v + 1]);
-        e.src_v = v == root ? kNoBlk : off16(src_pre[3 * (size_t)v + 2]);
-        if (l >= N) { e.flags |= WF_OUT_L; e.dst0 = off16(dst_pre[2 * (size_t)v]); }
-        if (r >= N) { e.flags |= WF_OUT_R; e.dst1 = off16(dst_pre[2 * (size_t)v + 1]); }
-        out.mat_dst[2 * (size_t)l + 1] = slot3 + 1;
-        out.mat_dst[2 * (size_t)r + 1] = slot3 + 2;
-        ids[s] = WalkIds{l, r};
-      }
-      // every non-tip operand must have been resolved
-      if ((l >= N && e.src_l == kNoBlk) || (r >= N && e.src_r == kNoBlk) ||
-          (q >= Rpost && v != root && e.src_v == kNoBlk)) {
+      if ((l >= N && src[so] < 0) || (r >= N && src[so + 1] < 0) || (!post && v != root && src[so + 2] < 0)) {
         why = "internal error: unresolved operand";
         return false;
+      }
+      const std::vector<uint32_t>& mrow = post ? mrow_post : mrow_pre;
+      e.a_l = l < N ? mat_at(mrow[2 * (size_t)v]) : blk_off(src[so]);
+      e.a_r = r < N ? mat_at(mrow[2 * (size_t)v + 1]) : blk_off(src[so + 1]);
+      if (post) {
+        if (v != root) { e.a_v = mat_at(mrow_own[v]); e.dst0 = blk_off(dst_post[v]); }
+      } else {
+        e.a_v = v == root ? (uint32_t)g.off_freq : blk_off(src[so + 2]);
+        if (l >= N) { e.dst0 = blk_off(dst_pre[2 * (size_t)v]); e.m_l = (uint16_t)(mat_at(mrow_pre[2 * (size_t)v]) / 16); }
+        if (r >= N) { e.dst1 = blk_off(dst_pre[2 * (size_t)v + 1]); e.m_r = (uint16_t)(mat_at(mrow_pre[2 * (size_t)v + 1]) / 16); }
       }
     }
   }

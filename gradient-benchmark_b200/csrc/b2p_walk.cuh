@@ -6,29 +6,32 @@
 // Per round the CTA runs up to wn independent node tasks side by side; thread t works on
 // slot t / ts and on column t % ts of the tile (with two columns per thread: t % ts and
 // ts + t % ts) — slots are packed at thread granularity so an awkward tile width (68
-// columns at 1000 taxa x 10k patterns on 148 SMs) still fills the lanes.
+// columns at 1000 taxa x 10k patterns on 148 SMs) still fills the lanes.  The planner lays
+// the tasks of a round out by kind (no / one / two tip children), so the two slots a warp
+// straddles mostly take the same branches.
 //
 // Data movement is entirely asynchronous and issued by the copy warps (the last warps of
-// the CTA, which hold no compute threads) from lists the host
-// planner wrote (b2p_plan.h): every operand block, tip row, matrix bundle and descriptor
-// record of round q + depth is a cp.async.bulk (TMA, UBLKCP in SASS) global -> shared copy
-// that completes on the mbarrier of that round; every result block is written to shared
-// memory by the compute threads and leaves with a cp.async.bulk shared -> global copy.
-// Compute threads execute no global-memory instruction at all.  Shared memory is a pool of
-// blocks allocated statically by the planner (the schedule is static, so lifetimes are
-// known): a value that is re-read soon simply stays where it was produced.
+// the CTA, which hold no compute threads) from lists the host planner wrote (b2p_plan.h):
+// every operand block, tip-code row, matrix bundle and descriptor record of round q + depth
+// is a cp.async.bulk (TMA, UBLKCP in SASS) global -> shared copy that completes on the
+// mbarrier of that round; every result block is written to shared memory by the compute
+// threads and leaves with a cp.async.bulk shared -> global copy.  Compute threads execute no
+// global-memory instruction at all.  Shared memory is a pool of blocks allocated statically
+// by the planner (the schedule is static, so lifetimes are known): a value that is re-read
+// soon simply stays where it was produced.
 //
 // Message formulation: a node stores the message to its parent, m_v = P_v x_v.
 //   post-order task of v:  x_v = m_l o m_r ;  m_v = P_v x_v
 //   pre-order task of v:   q_l = u_v o m_r,  q_r = u_v o m_l,  L = q_l . m_l,
 //                          dL/dt_l = r_k q_l.(Q m_l),  u_l = P_l^T q_l   (same for r)
-// A tip child's message is a column of P picked by its state mask (stored transposed, so
-// the column is one 32-byte read); ambiguity masks sum the compatible columns.
+// A tip child's message is a column of P: K1 writes, per tip branch, a 5-row table (row s =
+// column s of P, row 4 = all ones for a gap) and the thread reads row `code` — one 32-byte
+// read, the same instructions as an internal child's block read with another address.
+// Everything a thread needs for a round comes as byte offsets in a 32-byte descriptor
+// (two LDS.128) and the tip codes sit at fixed per-slot positions, so the dependent chain at
+// the top of a round is: {descriptor, tip codes} -> operands -> arithmetic.
 // Gradient sums over a slot's columns go through shared memory and are folded one round
 // later by the copy warps (fixed order: deterministic).
-// All shared-memory traffic uses 32-bit shared addresses (ld/st.shared), and everything a
-// round needs besides operand blocks sits in one per-stage FRAME, so the per-round address
-// arithmetic of a thread is one add per pointer.
 #pragma once
 #include "b2p_device.cuh"
 #include "b2p_walk_types.h"
@@ -39,26 +42,25 @@ constexpr int kMaxCatW = 32;
 
 template <typename T>
 struct WalkParams {
-  int n_tiles, rounds_run, n_branches, n_cat;
+  int n_tiles, rounds_run, rounds_post, n_branches, n_cat;
   int n_cols, n_patterns, n_copy_warps, wn;
-  int cw_loads;  // loads of the next round issued by the compute warps, one each (0: the copy warps issue all)
   int ct, ts, cpw, stages, depth;
-  int blk, plane, ct_pad, mat_stride;
-  int frame_bytes, off_frame, rel_cr, rel_mats, rel_tips;  // rel_ir == 0
-  int off_bar, off_gbuf, off_gids, off_scount;
-  unsigned ir_base, boot_base;
+  int blk, plane, ct_pad, row_stride;
+  int frame_bytes, off_frame, rel_cr, rel_mats, rel_tips, ir_jobs;  // rel_ir == 0; ir_jobs: first job of an issue record
+  int off_bar, off_gbuf, off_scount, off_freq;
+  unsigned boot_base, tail_base;  // tail_base: fold ids of the last round that runs
   unsigned boot_n[4], boot_tx[4];
   unsigned long long tile_stride_part;  // (N-1) * blk
-  unsigned long long tile_stride_tips;  // 2N * ct_pad
+  unsigned long long tile_stride_tips;  // rounds * 2 wn * ct_pad
   const unsigned char* records;
-  const unsigned char* mats;  // [rounds][wn][3][K] matrices in schedule order (written by K1)
+  const unsigned char* mats;  // matrix bundles of all rounds, back to back (written by K1)
   unsigned char* msg;         // [tile][N-1] blocks: m_v
   unsigned char* pre;         // [tile][N-1] blocks: u_c that had to leave shared memory
-  const unsigned char* tips;  // [tile][2N][ct_pad] state masks per column, tip rows in schedule order
+  const unsigned char* tips;  // [tile][round][wn][2][ct_pad] state codes per column
   const double* weights;      // [P]
   double* lpart;              // [grid]
   double* gpart;              // [grid][2N-2]
-  long long* trace;           // debug build (-DB2P_TRACE_CLOCKS): [2][rounds][5] clock stamps of CTA 0
+  long long* trace;           // debug build (-DB2P_TRACE_CLOCKS): [2][rounds][8] clock stamps of CTA 0
   T q[16];
   double freqs[4];
   double cat_w[kMaxCatW];
@@ -102,11 +104,6 @@ __device__ __forceinline__ uint4 lds_u4(unsigned a) {
   asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
   return v;
 }
-__device__ __forceinline__ unsigned lds_u32(unsigned a) {
-  unsigned v;
-  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
-  return v;
-}
 __device__ __forceinline__ unsigned lds_u8(unsigned a) {
   unsigned v;
   asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
@@ -117,9 +114,6 @@ __device__ __forceinline__ int2 lds_i2(unsigned a) {
   asm volatile("ld.shared.v2.s32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a));
   return v;
 }
-__device__ __forceinline__ void sts_i2(unsigned a, int2 v) {
-  asm volatile("st.shared.v2.s32 [%0], {%1,%2};" ::"r"(a), "r"(v.x), "r"(v.y) : "memory");
-}
 __device__ __forceinline__ double2 lds_d2(unsigned a) {
   double2 v;
   asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a));
@@ -128,55 +122,30 @@ __device__ __forceinline__ double2 lds_d2(unsigned a) {
 __device__ __forceinline__ void sts_d2(unsigned a, double x, double y) {
   asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(a), "d"(x), "d"(y) : "memory");
 }
-// 4 consecutive values (a matrix row, or the transposed matrix's row = a column of P)
-__device__ __forceinline__ void lds_row(unsigned a, double (&r)[4]) {
-  const double2 x = lds_d2(a), y = lds_d2(a + 16);
-  r[0] = x.x; r[1] = x.y; r[2] = y.x; r[3] = y.y;
-}
-__device__ __forceinline__ void lds_row(unsigned a, float (&r)[4]) {
-  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]) : "r"(a));
-}
-// one column (4 states) of a block.  fp64: two 16-byte halves in separate planes (consecutive
-// threads -> consecutive 16 B => conflict-free LDS.128 / STS.128); fp32: one 16 B unit.
-__device__ __forceinline__ void lds_col(unsigned a, unsigned plane, double (&x)[4]) {
-  const double2 u = lds_d2(a), v = lds_d2(a + plane);
+// Four values whose halves sit at a and a + half (fp64; a matrix / table row: half = 16, a
+// column of a block: half = the plane stride) or one 16-byte unit (fp32; half unused).
+__device__ __forceinline__ void lds_vec(unsigned a, unsigned half, double (&x)[4]) {
+  const double2 u = lds_d2(a), v = lds_d2(a + half);
   x[0] = u.x; x[1] = u.y; x[2] = v.x; x[3] = v.y;
 }
-__device__ __forceinline__ void lds_col(unsigned a, unsigned, float (&x)[4]) { lds_row(a, x); }
-__device__ __forceinline__ void sts_col(unsigned a, unsigned plane, const double (&x)[4]) {
+__device__ __forceinline__ void lds_vec(unsigned a, unsigned, float (&x)[4]) {
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(x[0]), "=f"(x[1]), "=f"(x[2]), "=f"(x[3]) : "r"(a));
+}
+__device__ __forceinline__ void sts_vec(unsigned a, unsigned half, const double (&x)[4]) {
   sts_d2(a, x[0], x[1]);
-  sts_d2(a + plane, x[2], x[3]);
+  sts_d2(a + half, x[2], x[3]);
 }
-__device__ __forceinline__ void sts_col(unsigned a, unsigned, const float (&x)[4]) {
+__device__ __forceinline__ void sts_vec(unsigned a, unsigned, const float (&x)[4]) {
   asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(x[0]), "f"(x[1]), "f"(x[2]), "f"(x[3]) : "memory");
-}
-
-// Message of a tip child from the transposed matrix at mt (mt[4*j + i] = P[i][j]).
-template <typename T>
-__device__ __forceinline__ void tip_message(unsigned mt, unsigned mask, T (&y)[4]) {
-  if (__popc(mask) == 1) {
-    lds_row(mt + (__ffs(mask) - 1) * 4 * (unsigned)sizeof(T), y);
-  } else {
-#pragma unroll
-    for (int i = 0; i < 4; ++i) y[i] = (T)0;
-#pragma unroll
-    for (int j = 0; j < 4; ++j)
-      if ((mask >> j) & 1u) {
-        T r[4];
-        lds_row(mt + j * 4 * (unsigned)sizeof(T), r);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) y[i] += r[i];
-      }
-  }
 }
 
 // Power-of-two rescale shared by the K category lanes of a pattern; returns 1 if applied.
 // fp64: partials are non-negative, so the high words order like the values; a denormal
 // maximum (high word 0) is left alone — it cannot arise from one step below 2^-200.
 template <int K>
-__device__ __forceinline__ int rescale(int lane, int kk, double (&y)[4]) {
+__device__ __forceinline__ int rescale(unsigned gmask, int lane, int kk, double (&y)[4]) {
   int h = max(max(__double2hiint(y[0]), __double2hiint(y[1])), max(__double2hiint(y[2]), __double2hiint(y[3])));
-  h = group_max_int<K>(h, lane, kk);
+  h = group_max_int<K>(h, gmask, lane, kk);
   if (h < 0x33700000 && h > 0) {  // < 2^-200
 #pragma unroll
     for (int i = 0; i < 4; ++i) y[i] *= Scale<double>::factor();
@@ -185,9 +154,9 @@ __device__ __forceinline__ int rescale(int lane, int kk, double (&y)[4]) {
   return 0;
 }
 template <int K>
-__device__ __forceinline__ int rescale(int lane, int kk, float (&y)[4]) {
+__device__ __forceinline__ int rescale(unsigned gmask, int lane, int kk, float (&y)[4]) {
   float mx = fmaxf(fmaxf(y[0], y[1]), fmaxf(y[2], y[3]));
-  mx = group_max<K>(mx, lane, kk);
+  mx = group_max<K>(mx, gmask, lane, kk);
   if (mx < Scale<float>::threshold() && mx > 0.f) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) y[i] *= Scale<float>::factor();
@@ -209,198 +178,190 @@ __device__ __forceinline__ double fast_rcp(double x) {
 }
 
 // Per-thread constants (all shared-memory addresses are 32-bit).
-template <int CPT>
+template <typename T, int CPT>
 struct WalkThread {
-  unsigned sc16;   // shared base + 16 * column: block offsets (descriptor * 16) are added to this
+  unsigned sc;     // shared base + 16 * column: a block's byte offset is added to this
   unsigned dB;     // 16 * ts: the thread's second column inside a block (CPT == 2)
   unsigned plane;  // fp64: bytes between the two halves of a column
-  unsigned o_mat;  // frame-relative: matrix 0 of this thread's (slot, category)
-  unsigned mk;     // bytes between a slot's matrices 0, 1, 2 (K * mat_stride)
-  unsigned o_tip;  // frame-relative: this thread's column in tip row 0
-  unsigned ct_pad, ts;
-  int lane, kk, k;
+  unsigned km;     // shared base + k * row_bytes: a row's byte offset is added to this
+  unsigned rs;     // bytes between rows
+  unsigned gmask;  // the K lanes of this thread's pattern
+  int lane, kk, k, ts;
+  T cw, cwr;       // K != 1: category weight, category weight x rate
   double w[CPT];   // pattern weights of the thread's columns (0 for padding columns)
 };
 
-struct TaskDesc {
-  unsigned src_l, src_r, src_v, dst0, dst1, flags, tip_l, tip_r;
-};
-__device__ __forceinline__ TaskDesc unpack_desc(const uint4 dw) {
-  TaskDesc d;
-  d.src_l = dw.x & 0xffffu; d.src_r = dw.x >> 16;
-  d.src_v = dw.y & 0xffffu; d.dst0 = dw.y >> 16;
-  d.dst1 = dw.z & 0xffffu; d.flags = dw.z >> 16;
-  d.tip_l = dw.w & 0xffffu; d.tip_r = dw.w >> 16;
-  return d;
-}
-
-// Children's messages of the task -> registers (zeros for idle lanes).
+// A child's message -> registers.  tip: row `code` of its table (code from the round's tip rows);
+// otherwise the thread's column of the child's block.  Same instructions either way.
 template <typename T, int CPT>
-__device__ __forceinline__ void load_messages(const WalkThread<CPT>& th, unsigned frame, const TaskDesc& d, bool live,
-                                              T (&ma)[CPT][4], T (&mb)[CPT][4]) {
+__device__ __forceinline__ void fetch_child(const WalkThread<T, CPT>& th, unsigned a, bool tip, const unsigned (&code)[CPT],
+                                            T (&m)[CPT][4]) {
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
+    const unsigned row = min(code[c], kTipAny);
+    const unsigned at = tip ? th.km + a + row * th.rs : th.sc + a + c * th.dB;
+    lds_vec(at, tip ? 16u : th.plane, m[c]);
+    if (tip && code[c] >= kTipAmbiguous) {  // rare: an ambiguity code other than "any": sum the compatible rows
 #pragma unroll
-    for (int i = 0; i < 4; ++i) ma[c][i] = mb[c][i] = (T)0;
-    if (!live) continue;
-    if (d.flags & WF_TIP_L) tip_message(frame + th.o_mat + th.mk, lds_u8(frame + th.o_tip + d.tip_l * th.ct_pad + c * th.ts), ma[c]);
-    else lds_col(th.sc16 + d.src_l * 16 + c * th.dB, th.plane, ma[c]);
-    if (d.flags & WF_TIP_R) tip_message(frame + th.o_mat + 2 * th.mk, lds_u8(frame + th.o_tip + d.tip_r * th.ct_pad + c * th.ts), mb[c]);
-    else lds_col(th.sc16 + d.src_r * 16 + c * th.dB, th.plane, mb[c]);
+      for (int i = 0; i < 4; ++i) m[c][i] = (T)0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if ((code[c] >> j) & 1u) {
+          T r[4];
+          lds_vec(th.km + a + j * th.rs, 16u, r);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) m[c][i] += r[i];
+        }
+    }
   }
+}
+
+// The 32-byte descriptor as the planner wrote it (b2p_walk_types.h: WalkDesc), unpacked.
+struct TaskDesc {
+  unsigned a_l, a_r, a_v, dst0, dst1, m_l, m_r, flags;
+};
+__device__ __forceinline__ TaskDesc unpack_desc(const uint4 d0, const uint4 d1) {
+  TaskDesc d;
+  d.a_l = d0.x; d.a_r = d0.y; d.a_v = d0.z; d.dst0 = d0.w;
+  d.dst1 = d1.x;
+  d.m_l = (d1.y & 0xffffu) * 16u; d.m_r = (d1.y >> 16) * 16u;
+  d.flags = d1.z & 0xffffu;
+  return d;
 }
 
 // ------------------------------------------------------------------ post-order task
 //   x_v = m_l o m_r (rescaled when tiny) ;  m_v = P_v x_v ; root: site likelihoods -> log-likelihood term
 template <typename T, int K, int CPT>
-__device__ __forceinline__ void post_task(const WalkParams<T>& p, const WalkThread<CPT>& th, unsigned frame, const TaskDesc& d,
-                                          bool live, int* scount, int col, unsigned gslot, T (&ma)[CPT][4],
-                                          T (&mb)[CPT][4]) {
+__device__ __forceinline__ void post_task(const WalkParams<T>& p, const WalkThread<T, CPT>& th, const TaskDesc& d,
+                                          int* scount, int col, unsigned gslot, T (&ma)[CPT][4], T (&mb)[CPT][4]) {
   int bumped[CPT];
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) ma[c][i] *= mb[c][i];
-    bumped[c] = rescale<K>(th.lane, th.kk, ma[c]);
+    bumped[c] = rescale<K>(th.gmask, th.lane, th.kk, ma[c]);
   }
-  const bool is_root = (d.flags & WF_ROOT) != 0;
-  if (live && !is_root) {
+  if (!(d.flags & WF_ROOT)) {
     T mv[CPT][4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       T r[4];
-      lds_row(frame + th.o_mat + i * 4 * (unsigned)sizeof(T), r);
+      lds_vec(th.km + d.a_v + i * th.rs, 16u, r);
 #pragma unroll
       for (int c = 0; c < CPT; ++c)
         mv[c][i] = r[0] * ma[c][0] + r[1] * ma[c][1] + r[2] * ma[c][2] + r[3] * ma[c][3];
     }
 #pragma unroll
     for (int c = 0; c < CPT; ++c) {
+      sts_vec(th.sc + d.dst0 + c * th.dB, th.plane, mv[c]);
       if (bumped[c] && th.k == 0) atomicAdd(scount + col + c * th.ts, 1);
-      sts_col(th.sc16 + d.dst0 * 16 + c * th.dB, th.plane, mv[c]);
     }
-  }
-  if (K != 1 || is_root) {
+  } else {
     double term = 0.0;
 #pragma unroll
     for (int c = 0; c < CPT; ++c) {
       T site = (T)p.freqs[0] * ma[c][0] + (T)p.freqs[1] * ma[c][1] + (T)p.freqs[2] * ma[c][2] + (T)p.freqs[3] * ma[c][3];
-      site = group_sum<K>(site * (T)p.cat_w[th.k], th.lane, th.kk);
-      if (live && is_root && th.k == 0)
+      if (K != 1) site = group_sum<K>(site * th.cw, th.gmask, th.lane, th.kk);
+      if (th.k == 0 && th.w[c] != 0.0)
         term += th.w[c] * (log((double)site) - (double)(scount[col + c * th.ts] + bumped[c]) * Scale<T>::log_factor());
     }
-    if (live && is_root) sts_d2(gslot, term, 0.0);
+    sts_d2(gslot, term, 0.0);
+  }
+}
+
+// One child's side of a pre-order task: its gradient numerator r_k q.(Q m) and, for an internal
+// child, its pre-order partial u_c = P_c^T q (rescaled when tiny) -> shared memory.
+template <typename T, int K, int CPT>
+__device__ __forceinline__ void pre_side(const WalkParams<T>& p, const WalkThread<T, CPT>& th, bool tip, unsigned mat, unsigned dst,
+                                         const T (&q)[CPT][4], const T (&m)[CPT][4], T (&num)[CPT]) {
+#pragma unroll
+  for (int c = 0; c < CPT; ++c) {
+    num[c] = (T)0;
+    // d/dt (P x) = r Q (P x): Q comes from the constant bank
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const T dm = p.q[4 * i] * m[c][0] + p.q[4 * i + 1] * m[c][1] + p.q[4 * i + 2] * m[c][2] + p.q[4 * i + 3] * m[c][3];
+      num[c] += q[c][i] * dm;
+    }
+  }
+  if (!tip) {
+    T u[CPT][4];
+#pragma unroll
+    for (int c = 0; c < CPT; ++c)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) u[c][j] = (T)0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      T r[4];
+      lds_vec(th.km + mat + i * th.rs, 16u, r);
+#pragma unroll
+      for (int c = 0; c < CPT; ++c)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) u[c][j] += r[j] * q[c][i];
+    }
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) {
+      (void)rescale<K>(th.gmask, th.lane, th.kk, u[c]);
+      sts_vec(th.sc + dst + c * th.dB, th.plane, u[c]);
+    }
   }
 }
 
 // ------------------------------------------------------------------- pre-order task
 //   q_l = u_v o m_r, q_r = u_v o m_l ; L = q_l . m_l ; dL/dt_l = r_k q_l.(Q m_l) ; u_l = P_l^T q_l (same for r)
 template <typename T, int K, int CPT>
-__device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThread<CPT>& th, unsigned frame, const TaskDesc& d,
-                                         bool live, unsigned gslot, T (&ma)[CPT][4], T (&mb)[CPT][4]) {
-  T ql[CPT][4], qr[CPT][4];
-  double gl = 0.0, gr = 0.0;
+__device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThread<T, CPT>& th, const TaskDesc& d,
+                                         unsigned gslot, const T (&ma)[CPT][4], const T (&mb)[CPT][4]) {
+  T ql[CPT][4], qr[CPT][4], den[CPT], numl[CPT], numr[CPT];
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
     T u[4];
-    if (live && d.src_v != kNoBlk) lds_col(th.sc16 + d.src_v * 16 + c * th.dB, th.plane, u);
-    else {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) u[i] = live ? (T)p.freqs[i] : (T)0;
-    }
-    T den = (T)0, numl = (T)0, numr = (T)0;
+    lds_vec(th.sc + d.a_v + c * th.dB, th.plane, u);
+    den[c] = (T)0;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       ql[c][i] = u[i] * mb[c][i];
       qr[c][i] = u[i] * ma[c][i];
-      den += ql[c][i] * ma[c][i];
+      den[c] += ql[c][i] * ma[c][i];
     }
-    // d/dt (P x) = r Q (P x): Q comes from the constant bank
+  }
+  pre_side<T, K, CPT>(p, th, (d.flags & WF_TIP_L) != 0, d.m_l, d.dst0, ql, ma, numl);
+  pre_side<T, K, CPT>(p, th, (d.flags & WF_TIP_R) != 0, d.m_r, d.dst1, qr, mb, numr);
+  double gl = 0.0, gr = 0.0;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const T dl = p.q[4 * i] * ma[c][0] + p.q[4 * i + 1] * ma[c][1] + p.q[4 * i + 2] * ma[c][2] + p.q[4 * i + 3] * ma[c][3];
-      const T dr = p.q[4 * i] * mb[c][0] + p.q[4 * i + 1] * mb[c][1] + p.q[4 * i + 2] * mb[c][2] + p.q[4 * i + 3] * mb[c][3];
-      numl += ql[c][i] * dl;
-      numr += qr[c][i] * dr;
-    }
+  for (int c = 0; c < CPT; ++c) {
+    T dn = den[c];
     if (K != 1) {
       // the site likelihood is the sum over the pattern's K category lanes; the numerators
       // need no such exchange: every lane adds its own category's share and the fold sums
       // over all lanes of the slot anyway
-      const T cw = (T)p.cat_w[th.k], cwr = (T)(p.cat_w[th.k] * p.rates[th.k]);
-      den = group_sum<K>(den * cw, th.lane, th.kk);
-      numl *= cwr;
-      numr *= cwr;
+      dn = group_sum<K>(dn * th.cw, th.gmask, th.lane, th.kk);
+      numl[c] *= th.cwr;
+      numr[c] *= th.cwr;
     }
-    if (live) {
-      // K == 1: the single category's weight cancels, its rate multiplies the numerators
-      const double inv = (K == 1 ? th.w[c] * p.rates[0] : th.w[c]) * fast_rcp((double)den);
-      gl += (double)numl * inv;
-      gr += (double)numr * inv;
-    }
+    // K == 1: the single category's weight cancels, its rate multiplies the numerators.  A
+    // pattern of likelihood zero contributes nothing instead of inf * 0.
+    const double dd = (double)dn;
+    const double inv = dd > 0.0 ? (K == 1 ? th.w[c] * p.rates[0] : th.w[c]) * fast_rcp(dd) : 0.0;
+    gl += (double)numl[c] * inv;
+    gr += (double)numr[c] * inv;
   }
-  if (live) sts_d2(gslot, gl, gr);
-  // pre-order partials of the internal children: u_c = P_c^T q_c  (ma / mb are dead)
-  const bool want_l = live && (d.flags & WF_OUT_L), want_r = live && (d.flags & WF_OUT_R);
-  if (K != 1 || want_l) {
-#pragma unroll
-    for (int c = 0; c < CPT; ++c)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) ma[c][j] = (T)0;
-    if (want_l) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        T r[4];
-        lds_row(frame + th.o_mat + th.mk + i * 4 * (unsigned)sizeof(T), r);
-#pragma unroll
-        for (int c = 0; c < CPT; ++c)
-#pragma unroll
-          for (int j = 0; j < 4; ++j) ma[c][j] += r[j] * ql[c][i];
-      }
-    }
-#pragma unroll
-    for (int c = 0; c < CPT; ++c) {
-      (void)rescale<K>(th.lane, th.kk, ma[c]);
-      if (want_l) sts_col(th.sc16 + d.dst0 * 16 + c * th.dB, th.plane, ma[c]);
-    }
-  }
-  if (K != 1 || want_r) {
-#pragma unroll
-    for (int c = 0; c < CPT; ++c)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) mb[c][j] = (T)0;
-    if (want_r) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        T r[4];
-        lds_row(frame + th.o_mat + 2 * th.mk + i * 4 * (unsigned)sizeof(T), r);
-#pragma unroll
-        for (int c = 0; c < CPT; ++c)
-#pragma unroll
-          for (int j = 0; j < 4; ++j) mb[c][j] += r[j] * qr[c][i];
-      }
-    }
-#pragma unroll
-    for (int c = 0; c < CPT; ++c) {
-      (void)rescale<K>(th.lane, th.kk, mb[c]);
-      if (want_r) sts_col(th.sc16 + d.dst1 * 16 + c * th.dB, th.plane, mb[c]);
-    }
-  }
+  sts_d2(gslot, gl, gr);
 }
 
 // Fold one round's per-thread sums (done by the copy warps one round later): slot s2's ts
 // pairs -> (a, b), added to the branch gradients / the log-likelihood in a fixed order.
-// A warp folds four slots at a time, eight lanes each.
-template <typename T>
+// A warp folds four slots at a time, eight lanes each.  ids: what each slot's sums belong to
+// (shared memory: the issue record of the next round; after the last round: global memory).
+template <typename T, bool IDS_SHARED>
 __device__ __forceinline__ void fold_round(const WalkParams<T>& p, unsigned sbase, int par, int pw, int lane, bool first_tile,
-                                           double& ll_acc) {
-  const unsigned gids = sbase + p.off_gids + par * p.wn * 8;
+                                           unsigned ids_smem, const int2* ids_gmem, double& ll_acc) {
   const unsigned gbuf = sbase + p.off_gbuf + par * p.wn * p.ts * 16;
   const int li = lane & 7;
   for (int s0 = pw * 4; s0 < p.wn; s0 += p.n_copy_warps * 4) {
     const int s2 = s0 + (lane >> 3);
     int2 ids = make_int2(-1, -1);
-    if (s2 < p.wn) ids = lds_i2(gids + s2 * 8);
+    if (s2 < p.wn) ids = IDS_SHARED ? lds_i2(ids_smem + s2 * 8) : __ldg(ids_gmem + s2);
     double a = 0.0, b = 0.0;
     if (ids.x != -1) {
       for (int c = li; c < p.ts; c += 8) {
@@ -436,28 +397,36 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
   const int s = t / p.ts;
   const int tt = t - s * p.ts;
   int col = CPT == 2 ? tt : (tt >> 5) * p.cpw + (tt & 31);
-  const bool in_slot = s < p.wn && (CPT == 2 || ((tt & 31) < p.cpw && col < p.ct));
+  const bool in_slot = !copier && s < p.wn && (CPT == 2 || ((tt & 31) < p.cpw && col < p.ct));
   if (!in_slot) col = 0;
   const int S = p.stages, D = p.depth, R = p.rounds_run;
   const unsigned sbase = smem_u32(smem);
   const unsigned bar0 = sbase + p.off_bar;
   int* scount = reinterpret_cast<int*>(smem + p.off_scount);
 
-  WalkThread<CPT> th;
-  th.lane = lane; th.kk = kk; th.k = col % kk;
-  th.sc16 = sbase + col * 16; th.dB = p.ts * 16; th.plane = p.plane;
-  th.mk = kk * p.mat_stride;
-  th.o_mat = p.rel_mats + ((in_slot ? s : 0) * 3 * kk + th.k) * p.mat_stride;
-  th.o_tip = p.rel_tips + col;
-  th.ct_pad = p.ct_pad; th.ts = p.ts;
-  const unsigned o_desc = p.rel_cr + (in_slot ? s : 0) * 16;
-  const unsigned o_ids = p.rel_cr + p.wn * 16 + (in_slot ? s : 0) * 8;
-  const unsigned o_gslot = p.off_gbuf + ((in_slot ? s : 0) * p.ts + tt) * 16;
+  WalkThread<T, CPT> th;
+  th.lane = lane; th.kk = kk; th.k = col % kk; th.ts = p.ts;
+  th.gmask = group_mask<K>(lane, kk);
+  th.sc = sbase + col * 16; th.dB = p.ts * 16; th.plane = p.plane;
+  th.km = sbase + th.k * 4 * (unsigned)sizeof(T);
+  th.rs = p.row_stride;
+  th.cw = (T)p.cat_w[th.k]; th.cwr = (T)(p.cat_w[th.k] * p.rates[th.k]);
+  const int sl = in_slot ? s : 0;
+  const unsigned o_desc = p.rel_cr + sl * 32;
+  const unsigned o_tip = p.rel_tips + sl * 2 * p.ct_pad + col;
+  const unsigned o_gslot = sbase + p.off_gbuf + (sl * p.ts + tt) * 16;
 
   if (t == 0) {
     for (int j = 0; j < S; ++j) mbar_init(bar0 + 8 * j, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     fence_async_smem();
+  }
+  // the root's parent-side partial: the frequencies for every column (same for every tile)
+  for (int c = t; c < p.ct; c += NT) {
+    T f[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) f[i] = (T)p.freqs[i];
+    sts_vec(sbase + p.off_freq + c * 16, p.plane, f);
   }
   unsigned phase_bits = 0;
   double ll_acc = 0.0;
@@ -519,13 +488,12 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
         const unsigned st_next = st == 0 ? S - 1 : st - 1;  // (q + D) % S with S = D + 1
         const unsigned bar = bar0 + 8 * st_next;
         const unsigned n_loads = (q + D < R) ? hdr.x : 0u;
-        const unsigned jobs = frame + 16;
+        const unsigned jobs = frame + p.ir_jobs;
         const unsigned np = p.n_copy_warps, pw = warp - first_copy_warp;
         if (pw == 0 && lane == 0 && n_loads) mbar_expect_tx(bar, hdr.z);
-        // loads of round q + depth first: they are what the next round waits for (issued after
-        // the stores they arrived ~700 cycles late in the post-order rounds); the stores only
+        // loads of round q + depth first: they are what the next round waits for; the stores only
         // have to have read shared memory by the end of this round
-        for (unsigned j = p.cw_loads + pw + np * lane; j < n_loads; j += 32 * np) {
+        for (unsigned j = pw + np * lane; j < n_loads; j += 32 * np) {
           const uint4 jb = lds_u4(jobs + j * 16);
           bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar);
         }
@@ -540,52 +508,32 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
 #ifdef B2P_TRACE_CLOCKS
         if (tr) trow[2] = clock64();
 #endif
-        if (q > 0) fold_round(p, sbase, par ^ 1, pw, lane, first_tile, ll_acc);
+        if (q > 0) fold_round<T, true>(p, sbase, par ^ 1, pw, lane, first_tile, frame + 16, nullptr, ll_acc);
 #ifdef B2P_TRACE_CLOCKS
         if (tr) trow[6] = clock64();
 #endif
         asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         asm volatile("cp.async.bulk.wait_group 1;" ::: "memory");
-      } else {
-        const uint4 hdr = lds_u4(frame);
-        const unsigned pass = hdr.w;
-        TaskDesc d;
-        d.flags = 0;
-        if (in_slot) {
-          d = unpack_desc(lds_u4(frame + o_desc));
-          if (tt == 0) {  // what the fold of the next round does with this slot's sums
-            const bool sums = (d.flags & WF_LIVE) && (pass != 0 || (d.flags & WF_ROOT));
-            sts_i2(sbase + p.off_gids + (par * p.wn + s) * 8, sums ? lds_i2(frame + o_ids) : make_int2(-1, -1));
-          }
+      } else if (in_slot) {
+        // descriptor and tip codes: independent reads (the codes sit at fixed per-slot positions)
+        const uint4 d0 = lds_u4(frame + o_desc), d1 = lds_u4(frame + o_desc + 16);
+        unsigned code_l[CPT], code_r[CPT];
+#pragma unroll
+        for (int c = 0; c < CPT; ++c) {
+          code_l[c] = lds_u8(frame + o_tip + c * p.ts);
+          code_r[c] = lds_u8(frame + o_tip + p.ct_pad + c * p.ts);
         }
-        const bool live = (d.flags & WF_LIVE) != 0;
-        // ---- optionally (cw_loads > 0) one load of round q + depth per compute warp: a bulk copy
-        // costs its issuing warp 100-300 cycles, so with few copy warps these can be the round's
-        // critical path; with three copy warps they are not, and the compute warps keep the
-        // cycles (default cw_loads = 0).  In the longer pre-order rounds the issue is placed
-        // after the operand reads so that the two overlap.
-        const bool my_job = lane == 0 && q + D < R && (unsigned)warp < hdr.x && warp < p.cw_loads;
-        const unsigned bar_next = bar0 + 8 * (st == 0 ? S - 1 : st - 1);
-        if (my_job && pass == 0) {
-          const uint4 jb = lds_u4(frame + 16 + warp * 16);
-          bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar_next);
-        }
+        const TaskDesc d = unpack_desc(d0, d1);
+        if (d.flags & WF_LIVE) {
+          T ma[CPT][4], mb[CPT][4];
+          fetch_child<T, CPT>(th, d.a_l, (d.flags & WF_TIP_L) != 0, code_l, ma);
+          fetch_child<T, CPT>(th, d.a_r, (d.flags & WF_TIP_R) != 0, code_r, mb);
 #ifdef B2P_TRACE_CLOCKS
-        if (tr) trow[7] = clock64();
+          if (tr) trow[2] = clock64();
 #endif
-        T ma[CPT][4], mb[CPT][4];
-        if (K != 1 || live) load_messages<T, CPT>(th, frame, d, live, ma, mb);
-        if (my_job && pass != 0) {
-          const uint4 jb = lds_u4(frame + 16 + warp * 16);
-          bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar_next);
-        }
-#ifdef B2P_TRACE_CLOCKS
-        if (tr) trow[2] = clock64();
-#endif
-        if (K != 1 || live) {  // K == 1: no warp-collective inside a task, idle lanes skip it
-          const unsigned gslot = sbase + o_gslot + par * p.wn * p.ts * 16;
-          if (pass == 0) post_task<T, K, CPT>(p, th, frame, d, live, scount, col, gslot, ma, mb);
-          else pre_task<T, K, CPT>(p, th, frame, d, live, gslot, ma, mb);
+          const unsigned gslot = o_gslot + par * p.wn * p.ts * 16;
+          if (q < p.rounds_post) post_task<T, K, CPT>(p, th, d, scount, col, gslot, ma, mb);
+          else pre_task<T, K, CPT>(p, th, d, gslot, ma, mb);
         }
       }
       // shared-memory results of this round (generic proxy) before the bulk copies (async
@@ -601,7 +549,9 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
       if (++st == S) { st = 0; frame = sbase + p.off_frame; } else frame += p.frame_bytes;
     }
     if (copier) {
-      fold_round(p, sbase, (R - 1) & 1, warp - first_copy_warp, lane, first_tile, ll_acc);
+      // the last round's sums: their ids come from global memory (no further issue record)
+      fold_round<T, false>(p, sbase, (R - 1) & 1, warp - first_copy_warp, lane, first_tile, 0u,
+                           reinterpret_cast<const int2*>(p.records + p.tail_base), ll_acc);
       asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     }
     __syncthreads();

@@ -10,33 +10,43 @@
 //   round    one step of the static schedule: up to wn node tasks run side by side.
 //   pool     shared-memory blocks handed out by the planner (static allocation: the
 //            schedule is known, so block lifetimes are too).
+//   row      one matrix row (or tip-table row) for all K categories: K * 4 values + padding
+//            (row_stride bytes); a thread of category k reads its 4 values at k * 4 * sizeof(T).
 #pragma once
 #include <stdint.h>
 
 namespace b2p {
 
-constexpr uint16_t kNoBlk = 0xFFFFu;  // operand is a tip (child) / the root prior (parent side)
-
 // task flags
 enum : uint16_t {
   WF_LIVE = 1,    // slot holds a task this round
-  WF_ROOT = 2,    // post: root task (site likelihoods, no message); pre: parent-side operand = frequencies
-  WF_TIP_L = 4,   // left child is a tip: its message is a column of P^T picked by the tip's state mask
+  WF_ROOT = 2,    // post: root task (site likelihoods, no message); pre: parent-side operand = frequency block
+  WF_TIP_L = 4,   // left child is a tip: its message is a row of its table, picked by the tip's state code
   WF_TIP_R = 8,
-  WF_OUT_L = 16,  // pre: left child is internal -> its pre-order partial is produced (dst0)
-  WF_OUT_R = 32,  // pre: right child internal (dst1)
 };
 
-// What the compute threads of one slot need for one round: 16 bytes, one LDS.128.
-// Offsets are shared-memory byte offsets / 16.
+// Rows a task's matrices take in the round's matrix bundle.
+//   internal node / child: 4 rows (P, row i = P[i][.])
+//   tip child:             5 rows (row s = column s of P for s = 0..3, row 4 = all ones: gap / unknown)
+constexpr int kRowsPlain = 4, kRowsTip = 5;
+constexpr int kRowsTaskMax = kRowsPlain + 2 * kRowsTip;  // post-order task with two tip children
+
+// Tip state codes in the per-tile tip rows (tile_tips_kernel): 0..3 = the state, 4 = any state,
+// 16 | mask = another ambiguity mask (summed row by row in the kernel's slow path).
+constexpr unsigned kTipAny = 4, kTipAmbiguous = 16;
+
+// What the compute threads of one slot need for one round: 32 bytes, two LDS.128.
+// All offsets are byte offsets from the start of dynamic shared memory, written by the planner
+// for the stage the round runs in — the kernel adds its per-thread column / category offset.
 struct WalkDesc {
-  uint16_t src_l, src_r;  // children's messages (kNoBlk: tip)
-  uint16_t src_v;         // pre: parent-side partial of the node (kNoBlk: root)
-  uint16_t dst0, dst1;    // post: dst0 = message of the node; pre: partials of the children
-  uint16_t flags;
-  uint16_t pad0, pad1;    // tip rows (within the round's tip-row copy) of the left / right child
+  uint32_t a_l, a_r;     // children: pool block of the message, or (tip) its 5-row table
+  uint32_t a_v;          // post: the node's own matrix rows; pre: parent-side partial (root: frequency block)
+  uint32_t dst0, dst1;   // post: dst0 = message of the node; pre: partials of the internal children
+  uint16_t m_l, m_r;     // pre: matrix rows of the internal children, offset / 16
+  uint16_t flags, pad0;
+  uint32_t pad1;
 };
-static_assert(sizeof(WalkDesc) == 16, "WalkDesc must be 16 bytes");
+static_assert(sizeof(WalkDesc) == 32, "WalkDesc must be 32 bytes");
 
 // Branch ids a pre-order task's two gradient sums belong to (-1: none, -2: log-likelihood term).
 struct WalkIds {
@@ -53,9 +63,9 @@ struct WalkJob {
 };
 static_assert(sizeof(WalkJob) == 16, "WalkJob must be 16 bytes");
 
-// Issue record of one round (read by the copy warp at the top of the round):
-// header, then n_loads load jobs (operands of round q + depth), then n_stores store jobs
-// (results of round q - 1).
+// Issue record of one round (read by the copy warps at the top of the round):
+// header, then wn fold ids (what the sums of round q - 1 belong to), then n_loads load jobs
+// (operands of round q + depth), then n_stores store jobs (results of round q - 1).
 struct WalkIssueHeader {
   uint32_t n_loads, n_stores;
   uint32_t tx_bytes;  // sum of the load jobs' bytes (mbarrier transaction count)

@@ -11,6 +11,7 @@
 // usage: plan_check N shape seed ct K elem smem_bytes depth [nt [cpt]]   -> prints "OK ..." or "FAIL ..."
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <map>
 #include <random>
 #include <string>
@@ -58,15 +59,29 @@ int main(int argc, char** argv) {
   const int R = plan.rounds, Rpost = plan.rounds_post, D = g.depth, S = g.stages, wn = g.wn, root = 2 * N - 2;
   std::vector<int> left(2 * N - 1, -1), right(2 * N - 1, -1), parent(2 * N - 1, -1);
   for (int e = 0; e < N - 1; ++e) { const int v = tr[3 * e]; left[v] = tr[3 * e + 1]; right[v] = tr[3 * e + 2]; parent[left[v]] = parent[right[v]] = v; }
-  // which node is the post-order task at (round, slot)?  from the matrix destinations
-  std::map<int, int> post_node_at;  // slot3 -> node
+  // the planner's canonical child order: a lone tip child is the left one
+  if (!(getenv("B2P_PLAN_SORT") && atoi(getenv("B2P_PLAN_SORT")) == 0))
+    for (int v = N; v <= root; ++v) if (right[v] < N && left[v] >= N) std::swap(left[v], right[v]);
+  // which node is the post-order task at a given place of the matrix bundles?  (own matrix rows)
+  std::map<uint32_t, int> post_node_at;  // byte offset in the bundle array -> node
   for (int v = N; v < root; ++v) {
-    if (plan.mat_dst[2 * v] < 0 || plan.mat_dst[2 * v] % 3 != 0) FAIL("mat_dst own of %d", v);
-    post_node_at[plan.mat_dst[2 * v]] = v;
+    if (plan.mat_dst[2 * v] < 0 || plan.mat_dst[2 * v] % g.row_stride != 0) FAIL("mat_dst own of %d", v);
+    post_node_at[(uint32_t)plan.mat_dst[2 * v]] = v;
   }
   for (int b = 0; b < 2 * N - 2; ++b) {
-    if (plan.mat_dst[2 * b + 1] < 0) FAIL("branch %d has no pre-order matrix slot", b);
-    if (b < N && plan.mat_dst[2 * b] < 0) FAIL("tip %d has no post-order matrix slot", b);
+    if (plan.mat_dst[2 * b + 1] < 0) FAIL("branch %d has no pre-order matrix rows", b);
+    if (b < N && plan.mat_dst[2 * b] < 0) FAIL("tip %d has no post-order matrix rows", b);
+  }
+  if ((int)plan.mats_off.size() != plan.rounds + 1 || (int)plan.tip_order.size() != plan.rounds * 2 * g.wn) FAIL("table sizes");
+  {  // rows of different branches never overlap, every round stays within the frame's matrix region
+    std::vector<std::pair<uint32_t, uint32_t>> spans;
+    for (int b = 0; b < 2 * N - 2; ++b)
+      for (int w = 0; w < 2; ++w)
+        if (plan.mat_dst[2 * b + w] >= 0) spans.push_back({(uint32_t)plan.mat_dst[2 * b + w], (uint32_t)((b < N ? kRowsTip : kRowsPlain) * g.row_stride)});
+    std::sort(spans.begin(), spans.end());
+    for (size_t i = 1; i < spans.size(); ++i) if (spans[i - 1].first + spans[i - 1].second > spans[i].first) FAIL("matrix rows overlap");
+    if (!spans.empty() && spans.back().first + spans.back().second > plan.mats_off.back()) FAIL("matrix rows past the end");
+    for (int q = 0; q < plan.rounds; ++q) if ((int)(plan.mats_off[q + 1] - plan.mats_off[q]) > g.mats_bytes) FAIL("round %d: bundle larger than the frame region", q);
   }
   const uint8_t* rec = plan.records.data();
   // symbolic pool: tag = 1 + vid (vid: message of v -> v-N ; partial of c -> (N-1)+(c-N)), 0 = nothing
@@ -91,10 +106,10 @@ int main(int argc, char** argv) {
       ++n_loads;
     } else if (j.kind == JK_TIPS) {
       if ((int)j.soff != g.off_tips + (f % S) * g.frame_bytes || (int)j.bytes > g.tips_bytes ||
-          (int)j.goff != plan.tip_row_off[f] * g.ct_pad ||
-          (int)j.bytes != (plan.tip_row_off[f + 1] - plan.tip_row_off[f]) * g.ct_pad) return "tips job";
+          j.goff != (uint32_t)f * 2u * (uint32_t)g.wn * (uint32_t)g.ct_pad || j.bytes % (2 * g.ct_pad)) return "tips job";
     } else if (j.kind == JK_MATS) {
-      if ((int)j.soff != g.off_mats + (f % S) * g.frame_bytes || (int)j.bytes > g.mats_bytes || j.goff != (uint32_t)f * g.mats_bytes) return "mats job";
+      if ((int)j.soff != g.off_mats + (f % S) * g.frame_bytes || (int)j.bytes > g.mats_bytes || j.goff != plan.mats_off[f] ||
+          j.bytes != plan.mats_off[f + 1] - plan.mats_off[f]) return "mats job";
     } else if (j.kind == JK_REC) {
       const bool is_cr = j.goff == (uint32_t)f * g.cr_bytes && (int)j.soff == g.off_cr + (f % S) * g.frame_bytes && (int)j.bytes == g.cr_bytes;
       const bool is_ir = j.goff == plan.ir_base + (uint32_t)f * g.ir_bytes && (int)j.soff == g.off_ir + (f % S) * g.frame_bytes && (int)j.bytes <= g.ir_bytes;
@@ -120,7 +135,7 @@ int main(int argc, char** argv) {
     const uint8_t* ir = rec + plan.ir_base + (size_t)q * g.ir_bytes;
     WalkIssueHeader h;
     memcpy(&h, ir, 16);
-    const WalkJob* jobs = reinterpret_cast<const WalkJob*>(ir + 16);
+    const WalkJob* jobs = reinterpret_cast<const WalkJob*>(ir + 16 + g.ir_ids);
     if (h.pass != (q >= Rpost ? 1u : 0u)) FAIL("pass flag round %d", q);
     if ((int)(h.n_loads + h.n_stores) > g.max_jobs) FAIL("too many jobs");
     if (q + D >= R && h.n_loads) FAIL("loads past the end");
@@ -145,25 +160,35 @@ int main(int argc, char** argv) {
     if (tx != h.tx_bytes) FAIL("tx bytes round %d", q);
     // tasks of round q
     const WalkDesc* d = reinterpret_cast<const WalkDesc*>(rec + (size_t)q * g.cr_bytes);
-    const WalkIds* ids = reinterpret_cast<const WalkIds*>(rec + (size_t)q * g.cr_bytes + wn * 16);
+    // what the fold of the NEXT round is told about this round's sums
+    const WalkIds* ids = reinterpret_cast<const WalkIds*>(q + 1 < R ? rec + plan.ir_base + (size_t)(q + 1) * g.ir_bytes + 16 : rec + plan.tail_base);
+    if (q == Rpost - 1) {  // a run that stops here reads the second tail record: must say the same
+      const WalkIds* t2 = reinterpret_cast<const WalkIds*>(rec + plan.tail_base + g.ir_ids);
+      for (int s = 0; s < wn; ++s) if (t2[s].a != ids[s].a || t2[s].b != ids[s].b) FAIL("post-only tail ids");
+    }
+    const uint32_t mats0 = (uint32_t)(g.off_mats + (q % S) * g.frame_bytes);
+    auto mat_goff = [&](uint32_t soff) { return plan.mats_off[q] + (soff - mats0); };
+    auto in_mats = [&](uint32_t soff, int rows) { return soff >= mats0 && soff + (uint32_t)rows * g.row_stride <= mats0 + (plan.mats_off[q + 1] - plan.mats_off[q]); };
     std::vector<int> reads, writes;
     std::vector<std::pair<int, int>> produced;  // (block, vid)
-    auto off_blk = [&](uint16_t o) { return blk_of((uint32_t)o * 16); };
+    auto off_blk = [&](uint32_t o) { return blk_of(o); };
     for (int s = 0; s < wn; ++s) {
       const WalkDesc& e = d[s];
-      if (!(e.flags & WF_LIVE)) continue;
+      if (!(e.flags & WF_LIVE)) { if (ids[s].a != -1 || ids[s].b != -1) FAIL("round %d: fold ids of an idle slot", q); continue; }
       ++n_tasks;
       int v;
       if (q < Rpost) {
-        if (e.flags & WF_ROOT) v = root;
+        if (e.flags & WF_ROOT) { v = root; if (ids[s].a != -2 || ids[s].b != -1) FAIL("root fold ids"); }
         else {
-          auto it = post_node_at.find((q * wn + s) * 3);
+          if (!in_mats(e.a_v, kRowsPlain)) FAIL("round %d slot %d: own matrix rows outside the bundle", q, s);
+          auto it = post_node_at.find(mat_goff(e.a_v));
           if (it == post_node_at.end()) FAIL("round %d slot %d: unknown post task", q, s);
           v = it->second;
+          if (ids[s].a != -1 || ids[s].b != -1) FAIL("round %d: fold ids of a post-order task", q);
         }
         if (done_post[v]++) FAIL("post task %d twice", v);
       } else {
-        if (ids[s].a < 0 || parent[ids[s].a] != parent[ids[s].b]) FAIL("ids");
+        if (ids[s].a < 0 || ids[s].b < 0 || parent[ids[s].a] != parent[ids[s].b]) FAIL("ids");
         v = parent[ids[s].a];
         if (left[v] != ids[s].a || right[v] != ids[s].b) FAIL("ids order");
         if (done_pre[v]++) FAIL("pre task %d twice", v);
@@ -171,27 +196,47 @@ int main(int argc, char** argv) {
       }
       const int l = left[v], r = right[v];
       if (((e.flags & WF_TIP_L) != 0) != (l < N) || ((e.flags & WF_TIP_R) != 0) != (r < N)) FAIL("tip flags");
-      const int nrows = plan.tip_row_off[q + 1] - plan.tip_row_off[q];
-      if (l < N && (e.pad0 >= nrows || plan.tip_order[plan.tip_row_off[q] + e.pad0] != l)) FAIL("round %d: left tip row", q);
-      if (r < N && (e.pad1 >= nrows || plan.tip_order[plan.tip_row_off[q] + e.pad1] != r)) FAIL("round %d: right tip row", q);
-      auto need = [&](uint16_t src, int vid, const char* what) -> bool {
-        if (src == kNoBlk || !check_soff((uint32_t)src * 16)) { printf("FAIL round %d node %d: %s operand offset\n", q, v, what); return false; }
+      if (r < N && l >= N) FAIL("a lone tip child must be the left one");
+      if (s > 0 && (d[s - 1].flags & WF_LIVE)) {  // tasks of a round are laid out by kind
+        auto kind = [&](const WalkDesc& x) { return ((x.flags & WF_TIP_L) != 0) + ((x.flags & WF_TIP_R) != 0); };
+        if (kind(d[s - 1]) > kind(e)) FAIL("round %d: tasks not sorted by kind", q);
+      }
+      const int w = q < Rpost ? 0 : 1;
+      const int ch[2] = {l, r};
+      const uint32_t ao[2] = {e.a_l, e.a_r};
+      for (int side = 0; side < 2; ++side) {
+        const int want = ch[side] < N ? ch[side] : -1;
+        if (plan.tip_order[((size_t)q * wn + s) * 2 + side] != want) FAIL("round %d slot %d: tip row of side %d", q, s, side);
+        if (ch[side] < N) {
+          if (!in_mats(ao[side], kRowsTip) || (int)mat_goff(ao[side]) != plan.mat_dst[2 * ch[side] + w]) FAIL("round %d slot %d: tip table of side %d", q, s, side);
+        }
+      }
+      auto need = [&](uint32_t src, int vid, const char* what) -> bool {
+        if (!check_soff(src)) { printf("FAIL round %d node %d: %s operand offset\n", q, v, what); return false; }
         const int b = off_blk(src);
         if (tag[b] != 1 + vid) { printf("FAIL round %d node %d: %s operand block %d holds %d, want %d\n", q, v, what, b, tag[b] - 1, vid); return false; }
         if (inflight_until[b] > q) { printf("FAIL round %d node %d: %s operand load lands in round %d\n", q, v, what, inflight_until[b]); return false; }
         reads.push_back(b);
         return true;
       };
-      if (l >= N && !need(e.src_l, l - N, "left")) return 1;
-      if (r >= N && !need(e.src_r, r - N, "right")) return 1;
+      if (l >= N && !need(e.a_l, l - N, "left")) return 1;
+      if (r >= N && !need(e.a_r, r - N, "right")) return 1;
       if (q < Rpost) {
         if (!done_post[l >= N ? l : v] || !done_post[r >= N ? r : v]) FAIL("post task %d before a child", v);
-        if (v != root) { writes.push_back(off_blk(e.dst0)); produced.push_back({off_blk(e.dst0), v - N}); }
+        if (v != root) {
+          if (!check_soff(e.dst0)) FAIL("round %d: message block offset", q);
+          writes.push_back(off_blk(e.dst0)); produced.push_back({off_blk(e.dst0), v - N});
+        }
       } else {
-        if (v != root && !need(e.src_v, (N - 1) + (v - N), "parent-side")) return 1;
-        if (((e.flags & WF_OUT_L) != 0) != (l >= N) || ((e.flags & WF_OUT_R) != 0) != (r >= N)) FAIL("out flags");
-        if (l >= N) { writes.push_back(off_blk(e.dst0)); produced.push_back({off_blk(e.dst0), (N - 1) + (l - N)}); }
-        if (r >= N) { writes.push_back(off_blk(e.dst1)); produced.push_back({off_blk(e.dst1), (N - 1) + (r - N)}); }
+        if (v == root) { if ((int)e.a_v != g.off_freq) FAIL("root parent-side operand"); }
+        else if (!need(e.a_v, (N - 1) + (v - N), "parent-side")) return 1;
+        const uint32_t dsts[2] = {e.dst0, e.dst1}, ms[2] = {(uint32_t)e.m_l * 16u, (uint32_t)e.m_r * 16u};
+        for (int side = 0; side < 2; ++side) {
+          if (ch[side] < N) continue;
+          if (!check_soff(dsts[side])) FAIL("round %d: partial block offset", q);
+          if (!in_mats(ms[side], kRowsPlain) || (int)mat_goff(ms[side]) != plan.mat_dst[2 * ch[side] + 1]) FAIL("round %d slot %d: matrix rows of side %d", q, s, side);
+          writes.push_back(off_blk(dsts[side])); produced.push_back({off_blk(dsts[side]), (N - 1) + (ch[side] - N)});
+        }
       }
     }
     for (size_t i = 0; i < writes.size(); ++i) {
