@@ -15,7 +15,7 @@ from typing import Dict, List, Sequence, Tuple
 
 import numpy as np
 
-__all__ = ["Alignment", "SitePattern", "read_fasta", "write_fasta", "compress_alignment",
+__all__ = ["Alignment", "SitePattern", "read_fasta", "write_fasta", "compress_alignment", "read_beast_xml",
            "simulate_alignment", "simulate_patterns", "IUPAC_MASK"]
 
 _A, _C, _G, _T = 1, 2, 4, 8
@@ -105,6 +105,25 @@ def read_fasta(path: str) -> Alignment:
             else:
                 seqs[-1].append(line)
     return Alignment(names, ["".join(s) for s in seqs])
+
+
+def read_beast_xml(path: str) -> Alignment:
+    """The ``<alignment>`` block of a BEAST 1 XML: ``<sequence><taxon idref="NAME"/> ACGT... </sequence>``
+    (the form of /root/reference/treetime_validation/resources/beast/bedford_et_al_2015__h3_small_tree.xml:4184+,
+    which SURVEY.md §8(c) lists as reference-held input data for this path)."""
+    import re
+    with open(path) as fh:
+        text = fh.read()
+    m = re.search(r"<alignment\b.*?</alignment>", text, flags=re.S)
+    if not m:
+        raise ValueError(f"{path}: no <alignment> block")
+    names, seqs = [], []
+    for sm in re.finditer(r"<sequence>\s*<taxon\s+idref=\"([^\"]+)\"\s*/>(.*?)</sequence>", m.group(0), flags=re.S):
+        names.append(sm.group(1))
+        seqs.append("".join(sm.group(2).split()))
+    if not names:
+        raise ValueError(f"{path}: <alignment> holds no sequences")
+    return Alignment(names, seqs)
 
 
 def write_fasta(path: str, aln: Alignment) -> None:

@@ -116,9 +116,11 @@ class UnrootedTreeModel:
 class StrictClockModel:
     """One rate for every branch (/root/reference/flu_H3N2/phylotorch-JC69.template:49-58)."""
 
-    def __init__(self, id_: Optional[str], rate: torch.Tensor):
+    def __init__(self, id_: Optional[str], rate):
         self.id = id_
-        self._rate = Parameter(f"{id_}.rate" if id_ else None, rate)
+        # a tensor, or an already-built (Transformed)Parameter — the template's "rate" object, which
+        # its priors and variational blocks look up by id
+        self._rate = rate if hasattr(rate, "tensor") else Parameter(f"{id_}.rate" if id_ else None, rate)
 
     @property
     def rates(self) -> torch.Tensor:
@@ -283,11 +285,14 @@ class TreeLikelihoodModel:
                 dic[spec["id"]] = obj
             return obj
 
+        dev = data.get("device")
+        dev = dev if dev is not None else (torch.cuda.current_device() if torch.cuda.is_available() else 0)
+        cuda = torch.device(f"cuda:{dev}") if torch.cuda.is_available() else None
         site_pattern = resolve("site_pattern", lambda s: _site_pattern_from_json(s, dic))
         tree_model = resolve("tree_model", lambda s: _tree_model_from_json(s, dic, site_pattern, data.get("device")))
-        subst_model = resolve("substitution_model", _subst_model_from_json)
-        site_model = resolve("site_model", _site_model_from_json, required=False)
-        clock_model = resolve("branch_model", _clock_from_json, required=False)
+        subst_model = resolve("substitution_model", lambda s: _subst_model_from_json(s, dic))
+        site_model = resolve("site_model", lambda s: _site_model_from_json(s, dic), required=False)
+        clock_model = resolve("branch_model", lambda s: _clock_from_json(s, dic, cuda), required=False)
         obj = cls(data.get("id"), site_pattern, tree_model, subst_model, site_model, clock_model,
                   precision=data.get("precision", "float64"), device=data.get("device"))
         if "id" in data:
@@ -356,43 +361,48 @@ def _tree_model_from_json(spec, dic, site_pattern: SitePattern, device=None):
     return UnrootedTreeModel(spec.get("id"), tree, bl)
 
 
-def _subst_model_from_json(spec) -> SubstitutionModel:
+def _values_from_json(spec, dic) -> np.ndarray:
+    """Numbers of a model parameter given as a list, a ``Parameter`` object (registered under its
+    id, like every nested object of the reference JSON) or the id of one built earlier."""
+    if isinstance(spec, (str, dict)):
+        if isinstance(spec, str) and spec not in dic:
+            raise KeyError(f"parameter id {spec!r} not found")
+        return _parameter_from_json(spec, dic).tensor.detach().cpu().numpy().reshape(-1)
+    return np.asarray(spec, dtype=np.float64).reshape(-1)
+
+
+def _subst_model_from_json(spec, dic=None) -> SubstitutionModel:
+    dic = {} if dic is None else dic
     kind = (spec.get("type") or "").split(".")[-1].upper()
     freqs = spec.get("frequencies")
-    if isinstance(freqs, dict):
-        freqs = freqs.get("tensor")
-    freqs = tuple(freqs) if freqs is not None else (0.25,) * 4
+    freqs = tuple(_values_from_json(freqs, dic)) if freqs is not None else (0.25,) * 4
     if kind == "JC69":
         return JC69()
     if kind == "HKY":
-        kappa = spec.get("kappa", 1.0)
-        if isinstance(kappa, dict):
-            kappa = kappa.get("tensor")
-        return HKY(float(np.asarray(kappa).reshape(-1)[0]), freqs)
+        return HKY(float(_values_from_json(spec.get("kappa", 1.0), dic)[0]), freqs)
     if kind == "GTR":
-        rates = spec.get("rates", (1.0,) * 6)
-        if isinstance(rates, dict):
-            rates = rates.get("tensor")
-        return GTR(tuple(rates), freqs)
+        return GTR(tuple(_values_from_json(spec.get("rates", (1.0,) * 6), dic)), freqs)
     raise ValueError(f"unsupported substitution model type {spec.get('type')!r}")
 
 
-def _site_model_from_json(spec):
+def _site_model_from_json(spec, dic=None):
+    dic = {} if dic is None else dic
     kind = (spec.get("type") or "ConstantSiteModel").split(".")[-1]
     if kind == "ConstantSiteModel":
         return ConstantSiteModel()
     if kind in ("GammaSiteModel", "WeibullSiteModel"):
-        shape = spec.get("shape", 0.5)
-        if isinstance(shape, dict):
-            shape = shape.get("tensor")
+        shape = float(_values_from_json(spec.get("shape", 0.5), dic)[0])
         if kind == "WeibullSiteModel":
-            return WeibullSiteModel(float(np.asarray(shape).reshape(-1)[0]), int(spec.get("categories", 4)))
-        return GammaSiteModel(float(np.asarray(shape).reshape(-1)[0]), int(spec.get("categories", 4)))
+            return WeibullSiteModel(shape, int(spec.get("categories", 4)))
+        return GammaSiteModel(shape, int(spec.get("categories", 4)))
     raise ValueError(f"unsupported site model type {spec.get('type')!r}")
 
 
-def _clock_from_json(spec) -> StrictClockModel:
+def _clock_from_json(spec, dic=None, device=None) -> StrictClockModel:
+    dic = {} if dic is None else dic
     kind = (spec.get("type") or "").split(".")[-1]
     if kind != "StrictClockModel":
         raise ValueError(f"unsupported branch model type {spec.get('type')!r}")
-    return StrictClockModel(spec.get("id"), _tensor_from_json(spec["rate"]))
+    # the rate lives on the engine's device (no per-evaluation host copy) and is registered under
+    # its own id: the template's clock.prior and variational blocks refer to "rate"
+    return StrictClockModel(spec.get("id"), _parameter_from_json(spec["rate"], dic, device))

@@ -31,9 +31,8 @@ struct b2p_instance {
   WalkPlan plan;  // records are released after upload; the statistics stay
   const void* kernel = nullptr;
   // device scratch
-  unsigned char* d_records = nullptr;
+  unsigned char* d_records = nullptr;  // round records: descriptors | issue record | matrix rows (K1 writes these)
   int* d_mat_dst = nullptr;
-  void* d_mats = nullptr;  // [rounds][wn][3][K] matrices in schedule order
   uint8_t* d_tips = nullptr;      // [tile][2N][ct_pad] masks per column, tip rows in schedule order
   uint8_t* d_tips_raw = nullptr;  // [N][P] as given by the caller
   int* d_tip_order = nullptr;     // [2N] tip id of each scheduled row
@@ -115,6 +114,8 @@ template <typename T, int K>
 static const void* walk_select_nt(int nt, int cpt) {
   if (cpt == 2) {
     switch (nt) {
+      case 768: return (const void*)walk_kernel<T, K, 768, 2>;
+      case 640: return (const void*)walk_kernel<T, K, 640, 2>;
       case 512: return (const void*)walk_kernel<T, K, 512, 2>;
       case 256: return (const void*)walk_kernel<T, K, 256, 2>;
     }
@@ -338,7 +339,7 @@ int b2p_destroy(b2p_instance* h) {
   if (!h) return B2P_OK;
   cudaSetDevice(h->cfg.device);
   peer_release(h);
-  cudaFree(h->d_records); cudaFree(h->d_mat_dst); cudaFree(h->d_mats);
+  cudaFree(h->d_records); cudaFree(h->d_mat_dst);
   cudaFree(h->d_tips); cudaFree(h->d_tips_raw); cudaFree(h->d_tip_order); cudaFree(h->d_weights); cudaFree(h->d_msg); cudaFree(h->d_pre);
   cudaFree(h->d_lpart); cudaFree(h->d_trace); cudaFree(h->d_gpart); cudaFree(h->d_bl_stage); cudaFree(h->d_out_stage);
   if (h->dense) {
@@ -410,7 +411,7 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   if (const char* s = getenv("B2P_NT")) nt_force = atoi(s);
   if (const char* s = getenv("B2P_CT")) ct_force = atoi(s);
   if (const char* s = getenv("B2P_DEPTH")) depth = atoi(s);
-  int n_copy = 3, cpt = 2;  // three copy warps issuing every bulk copy measured best (profiles/r01_sweep_copy_warps.txt)
+  int n_copy = 3, cpt = 2;  // copy warps: every bulk copy and the fold (sweep: profiles/README.md)
   if (const char* s = getenv("B2P_NP")) n_copy = std::max(1, std::min(4, atoi(s)));
   if (const char* s = getenv("B2P_CPT")) cpt = atoi(s) == 1 ? 1 : 2;
   // B2P_CTAS=2: two 256-thread CTAs per SM, each with half the shared memory.  They run out of
@@ -424,15 +425,6 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
     if (!getenv("B2P_NP")) n_copy = 2;
   }
   bool planned = plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, ct_force, depth, n_copy, cpt, h->wg);
-  if (planned && !getenv("B2P_NP") && n_copy == 3) {
-    // The third copy warp costs a slot's worth of compute threads.  It pays (2-4 %, profiles/
-    // r01_sweep_copy_warps.txt) unless the tile width quantises badly: when two copy warps give
-    // over 15 % more tasks per round, take those (e.g. 12 500 patterns x Gamma-4: 7 slots vs 6).
-    WalkGeometry g2;
-    if (plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, ct_force, depth, 2, cpt, g2) &&
-        g2.nt == h->wg.nt && g2.ct == h->wg.ct && g2.wn * 100 > h->wg.wn * 115)
-      h->wg = g2;
-  }
   if (!planned) {
     fail(h, B2P_ERR_UNSUPPORTED, "b2p_create: no kernel geometry fits shared memory (K=%d, threads=%d)", K, nt_force);
     return bail(B2P_ERR_UNSUPPORTED);
@@ -493,16 +485,20 @@ static void fill_walk_params(const b2p_instance* h, bool grad, WalkParams<T>& p)
   p.n_branches = 2 * N - 2; p.n_cat = K; p.n_cols = P * K; p.n_patterns = P; p.n_copy_warps = g.n_copy_warps;
   p.ct = g.ct; p.ts = g.ts; p.cpw = g.cpw; p.wn = g.wn; p.stages = g.stages; p.depth = g.depth;
   p.blk = g.blk; p.plane = g.ct * 16; p.ct_pad = g.ct_pad; p.row_stride = g.row_stride;
-  p.frame_bytes = g.frame_bytes; p.off_frame = g.off_frame; p.rel_cr = g.rel_cr; p.rel_mats = g.rel_mats;
-  p.rel_tips = g.rel_tips; p.ir_jobs = 16 + g.ir_ids;
+  p.frame_bytes = g.frame_bytes; p.off_frame = g.off_frame; p.rel_cr = g.rel_cr;
+  p.rel_ir = g.rel_ir; p.rel_tips = g.rel_tips; p.ir_jobs = 16 + g.ir_ids;
   p.off_bar = g.off_bar; p.off_gbuf = g.off_gbuf; p.off_scount = g.off_scount; p.off_freq = g.off_freq;
   p.boot_base = h->plan.boot_base; p.tail_base = h->plan.tail_base + (grad ? 0u : (unsigned)g.ir_ids);
   for (int i = 0; i < 4; ++i) { p.boot_n[i] = h->plan.boot_n[i]; p.boot_tx[i] = h->plan.boot_tx[i]; }
   p.tile_stride_part = (unsigned long long)(N - 1) * g.blk;
   p.tile_stride_tips = (unsigned long long)h->plan.rounds * 2ull * g.wn * g.ct_pad;
-  p.records = h->d_records; p.mats = (const unsigned char*)h->d_mats;
+  p.records = h->d_records;
   p.msg = (unsigned char*)h->d_msg; p.pre = (unsigned char*)h->d_pre; p.tips = h->d_tips;
   p.weights = h->d_weights; p.lpart = h->d_lpart; p.gpart = h->d_gpart; p.trace = h->d_trace;
+  p.dbg = 0;
+#ifdef B2P_DBG
+  if (const char* e = getenv("B2P_DBG")) p.dbg = atoi(e);
+#endif
   for (int i = 0; i < 4; ++i) p.freqs[i] = h->freqs[i];
   for (int i = 0; i < 16; ++i) p.q[i] = (T)(h->grad_op_set ? h->grad_op[i] : h->qmat[i]);
   for (int k = 0; k < kMaxCatW; ++k) {
@@ -540,7 +536,7 @@ static cudaError_t launch_eval(b2p_instance* h, const double* d_bl, double* d_lo
   const int n_br = 2 * N - 2;
   const int total = n_br * K * 16;
   transition_kernel<T><<<(total + 255) / 256, 256, 0, st>>>(h->model, d_bl, n_br, N, K, h->d_mat_dst, h->wg.row_stride,
-                                                            (unsigned char*)h->d_mats);
+                                                            h->d_records);
   const int slot = (int)(h->prof_count % b2p_instance::kProfRing);
   if (h->profiling) cudaEventRecord(h->ev0[slot], st);
   WalkParams<T> wp;
@@ -625,21 +621,19 @@ int b2p_set_topology(b2p_instance* h, const int32_t* h_triples) {
     return fail(h, B2P_ERR_ARG, "b2p_set_topology: %s", why.c_str());
   CU(cudaSetDevice(h->cfg.device));
   CU(cudaDeviceSynchronize());
-  cudaFree(h->d_records); cudaFree(h->d_mats); cudaFree(h->d_tips); cudaFree(h->d_tip_order);
-  h->d_records = nullptr; h->d_mats = nullptr; h->d_tips = nullptr; h->d_tip_order = nullptr;
+  cudaFree(h->d_records); cudaFree(h->d_tips); cudaFree(h->d_tip_order);
+  h->d_records = nullptr; h->d_tips = nullptr; h->d_tip_order = nullptr;
   h->have_topology = false;
-  const size_t mats_bytes = plan.mats_off.back();
   const size_t tips_bytes = (size_t)h->wg.n_tiles * plan.tip_order.size() * h->wg.ct_pad;
-  CU(cudaMalloc((void**)&h->d_records, plan.records.size()));
+  CU(cudaMalloc((void**)&h->d_records, plan.records.size()));  // the matrix rows inside are zero until K1 runs
   CU(cudaMemcpy(h->d_records, plan.records.data(), plan.records.size(), cudaMemcpyHostToDevice));
-  CU(cudaMalloc(&h->d_mats, mats_bytes));
-  CU(cudaMemset(h->d_mats, 0, mats_bytes));
   CU(cudaMalloc((void**)&h->d_tips, tips_bytes));
   CU(cudaMalloc((void**)&h->d_tip_order, plan.tip_order.size() * sizeof(int32_t)));
   CU(cudaMemcpy(h->d_mat_dst, plan.mat_dst.data(), plan.mat_dst.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
   if ((int)plan.tip_order.size() != plan.rounds * 2 * h->wg.wn) return fail(h, B2P_ERR_ARG, "b2p_set_topology: internal error (tip rows)");
   CU(cudaMemcpy(h->d_tip_order, plan.tip_order.data(), plan.tip_order.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
-  plan.mats_off.clear(); plan.mats_off.shrink_to_fit();
+  plan.rec_off.clear(); plan.rec_off.shrink_to_fit();
+  plan.rec_mats.clear(); plan.rec_mats.shrink_to_fit();
   plan.tip_order.clear(); plan.tip_order.shrink_to_fit();
   plan.records.clear(); plan.records.shrink_to_fit();
   plan.mat_dst.clear(); plan.mat_dst.shrink_to_fit();

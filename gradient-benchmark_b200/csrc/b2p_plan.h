@@ -52,7 +52,7 @@ struct WalkGeometry {
   int ir_bytes = 0;    // one round's issue record (header + fold ids + max_jobs jobs)
   int tips_bytes = 0;  // one round's tip rows: wn * 2 rows
   int max_jobs = 0;
-  int off_bar = 0, off_cr = 0, off_ir = 0, off_mats = 0, off_tips = 0, off_gbuf = 0,
+  int off_bar = 0, off_cr = 0, off_ir = 0, off_tips = 0, off_gbuf = 0,
       off_scount = 0, off_freq = 0, off_pool = 0;
   int n_pool = 0;
   size_t smem = 0;
@@ -85,14 +85,19 @@ inline int layout_walk(WalkGeometry& g, size_t smem_max) {
   g.tips_bytes = wn * 2 * g.ct_pad;
   int off = 0;
   g.off_bar = off; off += 64;  // up to 8 mbarriers
-  g.rel_ir = 0;
-  g.rel_cr = g.rel_ir + g.ir_bytes;
-  g.rel_mats = g.rel_cr + g.cr_bytes;
-  g.rel_tips = g.rel_mats + align16(g.mats_bytes);
+  // A stage's frame: the round's record — descriptors | issue record (header, fold ids, as many
+  // jobs as the round has) | the matrix rows right behind the last job — and its tip rows.  The
+  // record is ONE bulk copy: it is laid out the same way in global memory (K1 writes the
+  // matrices into it), and the descriptors carry absolute offsets, so nothing needs the
+  // matrices at a fixed place.
+  g.rel_cr = 0;
+  g.rel_ir = g.cr_bytes;
+  g.rel_mats = g.rel_ir + 16 + g.ir_ids;  // + 16 * (jobs of the round)
+  g.rel_tips = align16(g.rel_ir + g.ir_bytes + g.mats_bytes);
   g.frame_bytes = g.rel_tips + g.tips_bytes;
   g.off_frame = off; off += S * g.frame_bytes;
   g.off_ir = g.off_frame + g.rel_ir; g.off_cr = g.off_frame + g.rel_cr;
-  g.off_mats = g.off_frame + g.rel_mats; g.off_tips = g.off_frame + g.rel_tips;
+  g.off_tips = g.off_frame + g.rel_tips;
   g.off_gbuf = off; off += 2 * wn * g.ts * 16;  // one (sum_a, sum_b) pair per compute thread
   g.off_scount = off; off += align16(g.ct * 4);
   off = (off + 127) & ~127;
@@ -123,7 +128,7 @@ inline bool plan_geometry_cpt(int n_tips, int n_cols, int K, int elem, int n_sms
   ct = std::min(ct, std::max(q, (n_cols + q - 1) / q * q));
   if (ct_force > 0) ct = std::max(q, ct_force / q * q);
   const int ts = packed ? ct / cpt : ((ct + cpw - 1) / cpw) * 32;  // threads per slot
-  const int nts1[4] = {1024, 768, 512, 256}, nts2[4] = {512, 256, 0, 0};
+  const int nts1[4] = {1024, 768, 512, 256}, nts2[4] = {512, 768, 640, 256};
   for (int nt : (cpt == 2 ? nts2 : nts1)) {
     if (nt == 0) continue;
     if (nt_force > 0 && nt != nt_force) continue;
@@ -154,13 +159,14 @@ inline bool plan_geometry(int n_tips, int n_cols, int K, int elem, int n_sms, si
 
 struct WalkPlan {
   int rounds_post = 0, rounds_pre = 0, rounds = 0, tree_depth = 0, wn_eff = 0;
-  std::vector<uint8_t> records;  // [rounds] CR, then [rounds] IR, then the boot jobs
-  uint32_t ir_base = 0, boot_base = 0;
+  std::vector<uint8_t> records;  // [rounds] round records, the tail fold ids, the boot jobs
+  std::vector<uint32_t> rec_off;   // [rounds + 1] byte offset of every round's record
+  std::vector<uint32_t> rec_mats;  // [rounds] offset of the matrix rows inside the round's record
+  uint32_t boot_base = 0;
   uint32_t boot_n[4] = {0, 0, 0, 0}, boot_tx[4] = {0, 0, 0, 0};  // loads of rounds 0..depth-1
   std::vector<int32_t> tip_order;    // [rounds][wn][2] tip id of every tip row (-1: that child is not a tip)
-  std::vector<int32_t> mat_dst;  // [2N-2][2]: byte offset of the branch's rows in the post / pre bundles (-1: none);
-                                 // tip branches get the 5-row table, internal ones the 4 matrix rows
-  std::vector<uint32_t> mats_off;  // [rounds + 1] byte offset of every round's bundle in the bundle array
+  std::vector<int32_t> mat_dst;  // [2N-2][2]: byte offset (in `records`) of the branch's rows for the post / pre rounds
+                                 // (-1: none); tip branches get the 5-row table, internal ones the 4 matrix rows
   uint32_t tail_base = 0;          // fold ids of the last round (read from global memory after the loop):
                                    // of a full run, then (+ ir_ids bytes) of a post-order-only run
   long long resident_reads = 0, loads_msg = 0, loads_pre = 0, stores_msg = 0, stores_pre = 0, evictions = 0;
@@ -185,7 +191,7 @@ struct LoadRec { uint32_t kind, goff, soff, bytes; };
 inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int wn_eff, int budget, WalkPlan& out,
                       std::string& why) {
   using namespace plan_detail;
-  const int wn = g.wn, D = g.depth, S = g.stages, NB = g.n_pool, K = g.K;
+  const int wn = g.wn, D = g.depth, S = g.stages, NB = g.n_pool;
   wn_eff = std::max(1, std::min(wn_eff, wn));
   out = WalkPlan();
   out.wn_eff = wn_eff;
@@ -497,46 +503,11 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
   }
 
   // -------------------------------------------------------------------- records
-  const uint32_t cr_total = (uint32_t)R * g.cr_bytes;
-  out.ir_base = cr_total;
-  out.tail_base = out.ir_base + (uint32_t)R * g.ir_bytes;
-  out.boot_base = out.tail_base + 2u * (uint32_t)g.ir_ids;
-  // Matrix bundle of every round: the tasks' rows back to back, slot by slot —
-  //   post-order task: [own matrix, 4 rows (not the root)] [left tip table, 5] [right tip table, 5]
-  //   pre-order task:  [left child: tip table 5 / matrix 4] [right child: likewise]
-  // mat_dst tells K1 where each branch's rows go (byte offsets into the bundle array).
-  out.mat_dst.assign(2 * (size_t)(2 * N - 2), -1);
-  out.mats_off.assign(R + 1, 0);
-  std::vector<uint32_t> mrow_own(n_nodes, 0), mrow_post(2 * (size_t)n_nodes, 0), mrow_pre(2 * (size_t)n_nodes, 0);  // row within the round
-  for (int f = 0; f < R; ++f) {
-    uint32_t rows = 0;
-    for (int v : tasks[f]) {
-      const int ch[2] = {left[v], right[v]};
-      if (f < Rpost) {
-        if (v != root) { mrow_own[v] = rows; out.mat_dst[2 * (size_t)v] = (int32_t)(out.mats_off[f] + rows * g.row_stride); rows += kRowsPlain; }
-        for (int side = 0; side < 2; ++side)
-          if (ch[side] < N) {
-            mrow_post[2 * (size_t)v + side] = rows;
-            out.mat_dst[2 * (size_t)ch[side]] = (int32_t)(out.mats_off[f] + rows * g.row_stride);
-            rows += kRowsTip;
-          }
-      } else {
-        for (int side = 0; side < 2; ++side) {
-          mrow_pre[2 * (size_t)v + side] = rows;
-          out.mat_dst[2 * (size_t)ch[side] + 1] = (int32_t)(out.mats_off[f] + rows * g.row_stride);
-          rows += ch[side] < N ? kRowsTip : kRowsPlain;
-        }
-      }
-    }
-    if ((int)rows > g.mats_rows) { why = "internal error: matrix bundle over budget"; return false; }
-    out.mats_off[f + 1] = out.mats_off[f] + rows * (uint32_t)g.row_stride;
-  }
-  // fixed per-round loads: tip code rows, matrix bundle, the round's descriptors.  Tip rows sit at
-  // FIXED positions — row 2 * slot + side of the round — so a thread reads its tip codes without
-  // waiting for its descriptor; rows of internal children are never read for their value.
+  // per-round loads besides the operand blocks: the tip code rows (fixed positions — row
+  // 2 * slot + side of the round — so a thread reads its codes without waiting for its
+  // descriptor; rows of internal children are never read for their value)
   out.tip_order.assign((size_t)R * 2 * wn, -1);
   for (int f = 0; f < R; ++f) {
-    const int st = f % S;
     bool any = false;
     for (int s = 0; s < (int)tasks[f].size(); ++s) {
       const int v = tasks[f][s];
@@ -549,22 +520,53 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
     }
     if (any)
       loads[f].push_back({JK_TIPS, (uint32_t)f * 2u * (uint32_t)wn * (uint32_t)g.ct_pad,
-                          (uint32_t)(g.off_tips + st * g.frame_bytes), (uint32_t)(2 * (int)tasks[f].size() * g.ct_pad)});
-    if (out.mats_off[f + 1] > out.mats_off[f])
-      loads[f].push_back({JK_MATS, out.mats_off[f], (uint32_t)(g.off_mats + st * g.frame_bytes),
-                          out.mats_off[f + 1] - out.mats_off[f]});
-    loads[f].push_back({JK_REC, (uint32_t)f * (uint32_t)g.cr_bytes, (uint32_t)(g.off_cr + st * g.frame_bytes), (uint32_t)g.cr_bytes});
+                          (uint32_t)(g.off_tips + (f % S) * g.frame_bytes), (uint32_t)(2 * (int)tasks[f].size() * g.ct_pad)});
   }
-  // issue records: IR[q] = fold ids of round q - 1, loads of round q + D, stores of round q - 1
-  const uint32_t ir_head = 16u + (uint32_t)g.ir_ids;
-  std::vector<uint32_t> ir_len(R, ir_head);
+  // Round records: descriptors | issue header | fold ids of round q - 1 | jobs (loads of round
+  // q + D, among them the record of round q + D itself; stores of round q - 1) | matrix rows of
+  // the round's tasks, slot by slot —
+  //   post-order task: [own matrix, 4 rows (not the root)] [left tip table, 5] [right tip table, 5]
+  //   pre-order task:  [left child: tip table 5 / matrix 4] [right child: likewise]
+  // mat_dst tells K1 where each branch's rows go.
+  std::vector<int> n_jobs(R, 0);
   for (int q = 0; q < R; ++q) {
-    const int n_l = q + D < R ? (int)loads[q + D].size() + 1 : 0;  // + the IR of round q + D itself
+    const int n_l = q + D < R ? (int)loads[q + D].size() + 1 : 0;
     const int n_s = (int)stores[q].size();
     if (n_l + n_s > g.max_jobs) { why = "too many copies in one round"; return false; }
     out.max_jobs_used = std::max(out.max_jobs_used, n_l + n_s);
-    ir_len[q] = ir_head + 16u * (uint32_t)(n_l + n_s);
+    n_jobs[q] = n_l + n_s;
   }
+  out.mat_dst.assign(2 * (size_t)(2 * N - 2), -1);
+  out.rec_off.assign(R + 1, 0);
+  out.rec_mats.assign(R, 0);
+  std::vector<uint32_t> mrow_own(n_nodes, 0), mrow_post(2 * (size_t)n_nodes, 0), mrow_pre(2 * (size_t)n_nodes, 0);  // row within the round
+  for (int f = 0; f < R; ++f) {
+    out.rec_mats[f] = (uint32_t)(g.rel_mats + 16 * n_jobs[f]);
+    const uint32_t m0 = out.rec_off[f] + out.rec_mats[f];
+    uint32_t rows = 0;
+    for (int v : tasks[f]) {
+      const int ch[2] = {left[v], right[v]};
+      if (f < Rpost) {
+        if (v != root) { mrow_own[v] = rows; out.mat_dst[2 * (size_t)v] = (int32_t)(m0 + rows * g.row_stride); rows += kRowsPlain; }
+        for (int side = 0; side < 2; ++side)
+          if (ch[side] < N) {
+            mrow_post[2 * (size_t)v + side] = rows;
+            out.mat_dst[2 * (size_t)ch[side]] = (int32_t)(m0 + rows * g.row_stride);
+            rows += kRowsTip;
+          }
+      } else {
+        for (int side = 0; side < 2; ++side) {
+          mrow_pre[2 * (size_t)v + side] = rows;
+          out.mat_dst[2 * (size_t)ch[side] + 1] = (int32_t)(m0 + rows * g.row_stride);
+          rows += ch[side] < N ? kRowsTip : kRowsPlain;
+        }
+      }
+    }
+    if ((int)rows > g.mats_rows) { why = "internal error: matrix rows over budget"; return false; }
+    out.rec_off[f + 1] = out.rec_off[f] + out.rec_mats[f] + rows * (uint32_t)g.row_stride;
+  }
+  out.tail_base = out.rec_off[R];
+  out.boot_base = out.tail_base + 2u * (uint32_t)g.ir_ids;
   size_t n_boot = 0;
   for (int f = 0; f < std::min(D, R); ++f) n_boot += loads[f].size() + 1;
   out.records.assign((size_t)out.boot_base + n_boot * 16, 0);
@@ -579,19 +581,19 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
       else if (v == root) ids[s] = WalkIds{-2, -1};
     }
   };
-  auto ir_job = [&](int f) {
-    return WalkJob{out.ir_base + (uint32_t)f * (uint32_t)g.ir_bytes, (uint32_t)(g.off_ir + (f % S) * g.frame_bytes), ir_len[f], JK_REC};
+  auto rec_job = [&](int f) {
+    return WalkJob{out.rec_off[f], (uint32_t)(g.off_frame + (f % S) * g.frame_bytes), out.rec_off[f + 1] - out.rec_off[f], JK_REC};
   };
   auto job_of = [&](const LoadRec& l) { return WalkJob{l.goff, l.soff, l.bytes, l.kind}; };
   for (int q = 0; q < R; ++q) {
-    uint8_t* p = out.records.data() + out.ir_base + (size_t)q * g.ir_bytes;
+    uint8_t* p = out.records.data() + out.rec_off[q] + g.rel_ir;
     WalkIssueHeader h{0, 0, 0, q >= Rpost ? 1u : 0u};
     fold_ids(q - 1, reinterpret_cast<WalkIds*>(p + 16));
-    WalkJob* jobs = reinterpret_cast<WalkJob*>(p + ir_head);
+    WalkJob* jobs = reinterpret_cast<WalkJob*>(p + 16 + g.ir_ids);
     int n = 0;
     if (q + D < R) {
+      jobs[n] = rec_job(q + D); h.tx_bytes += jobs[n].bytes; ++n;  // first: the other loads are small next to it
       for (const LoadRec& l : loads[q + D]) { jobs[n++] = job_of(l); h.tx_bytes += l.bytes; }
-      jobs[n] = ir_job(q + D); h.tx_bytes += jobs[n].bytes; ++n;
       h.n_loads = (uint32_t)n;
     }
     for (const LoadRec& l : stores[q]) jobs[n++] = job_of(l);
@@ -606,16 +608,16 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
     int n = 0;
     for (int f = 0; f < std::min(D, R); ++f) {
       const int n0 = n;
+      jobs[n] = rec_job(f); out.boot_tx[f] += jobs[n].bytes; ++n;
       for (const LoadRec& l : loads[f]) { jobs[n++] = job_of(l); out.boot_tx[f] += l.bytes; }
-      jobs[n] = ir_job(f); out.boot_tx[f] += jobs[n].bytes; ++n;
       out.boot_n[f] = (uint32_t)(n - n0);
     }
   }
   // descriptors: byte offsets into shared memory for the stage the round runs in
   auto blk_off = [&](int b) { return (uint32_t)(g.off_pool + b * g.blk); };
   for (int q = 0; q < R; ++q) {
-    WalkDesc* d = reinterpret_cast<WalkDesc*>(out.records.data() + (size_t)q * g.cr_bytes);
-    const uint32_t mats0 = (uint32_t)(g.off_mats + (q % S) * g.frame_bytes);
+    WalkDesc* d = reinterpret_cast<WalkDesc*>(out.records.data() + out.rec_off[q] + g.rel_cr);
+    const uint32_t mats0 = (uint32_t)(g.off_frame + (q % S) * g.frame_bytes) + out.rec_mats[q];
     auto mat_at = [&](uint32_t row) { return mats0 + row * (uint32_t)g.row_stride; };
     for (int s = 0; s < wn; ++s) std::memset(&d[s], 0, sizeof(WalkDesc));
     for (int s = 0; s < (int)tasks[q].size(); ++s) {

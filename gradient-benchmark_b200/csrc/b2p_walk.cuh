@@ -46,14 +46,13 @@ struct WalkParams {
   int n_cols, n_patterns, n_copy_warps, wn;
   int ct, ts, cpw, stages, depth;
   int blk, plane, ct_pad, row_stride;
-  int frame_bytes, off_frame, rel_cr, rel_mats, rel_tips, ir_jobs;  // rel_ir == 0; ir_jobs: first job of an issue record
+  int frame_bytes, off_frame, rel_cr, rel_ir, rel_tips, ir_jobs;  // ir_jobs: first job, relative to the issue record
   int off_bar, off_gbuf, off_scount, off_freq;
   unsigned boot_base, tail_base;  // tail_base: fold ids of the last round that runs
   unsigned boot_n[4], boot_tx[4];
   unsigned long long tile_stride_part;  // (N-1) * blk
   unsigned long long tile_stride_tips;  // rounds * 2 wn * ct_pad
-  const unsigned char* records;
-  const unsigned char* mats;  // matrix bundles of all rounds, back to back (written by K1)
+  const unsigned char* records;  // round records (descriptors | issue record | matrix rows written by K1), tail, boot jobs
   unsigned char* msg;         // [tile][N-1] blocks: m_v
   unsigned char* pre;         // [tile][N-1] blocks: u_c that had to leave shared memory
   const unsigned char* tips;  // [tile][round][wn][2][ct_pad] state codes per column
@@ -61,6 +60,7 @@ struct WalkParams {
   double* lpart;              // [grid]
   double* gpart;              // [grid][2N-2]
   long long* trace;           // debug build (-DB2P_TRACE_CLOCKS): [2][rounds][8] clock stamps of CTA 0
+  int dbg;                    // debug build (-DB2P_DBG): 1 skip the fold, 2 skip the stores, 4 skip the tasks (timing experiments)
   T q[16];
   double freqs[4];
   double cat_w[kMaxCatW];
@@ -139,30 +139,42 @@ __device__ __forceinline__ void sts_vec(unsigned a, unsigned, const float (&x)[4
   asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(x[0]), "f"(x[1]), "f"(x[2]), "f"(x[3]) : "memory");
 }
 
+// A value the compiler must keep in a register: it cannot re-derive it from its definition
+// (kernel parameters, %tid, the shared window base) inside the round loop, where every such
+// re-derivation is a constant-bank load or an S2R on the critical path of the round.
+__device__ __forceinline__ unsigned pinned(unsigned x) {
+  asm volatile("mov.u32 %0, %0;" : "+r"(x));
+  return x;
+}
+
 // Power-of-two rescale shared by the K category lanes of a pattern; returns 1 if applied.
 // fp64: partials are non-negative, so the high words order like the values; a denormal
 // maximum (high word 0) is left alone — it cannot arise from one step below 2^-200.
+// The multiplication is rare: it sits in a loop of at most one trip so that it stays a
+// branch instead of four predicated multiplies issued every time.
 template <int K>
 __device__ __forceinline__ int rescale(unsigned gmask, int lane, int kk, double (&y)[4]) {
   int h = max(max(__double2hiint(y[0]), __double2hiint(y[1])), max(__double2hiint(y[2]), __double2hiint(y[3])));
   h = group_max_int<K>(h, gmask, lane, kk);
-  if (h < 0x33700000 && h > 0) {  // < 2^-200
+  const int need = (h < 0x33700000 && h > 0) ? 1 : 0;  // < 2^-200
+#pragma unroll 1
+  for (unsigned z = pinned((unsigned)need); z != 0; --z) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) y[i] *= Scale<double>::factor();
-    return 1;
   }
-  return 0;
+  return need;
 }
 template <int K>
 __device__ __forceinline__ int rescale(unsigned gmask, int lane, int kk, float (&y)[4]) {
   float mx = fmaxf(fmaxf(y[0], y[1]), fmaxf(y[2], y[3]));
   mx = group_max<K>(mx, gmask, lane, kk);
-  if (mx < Scale<float>::threshold() && mx > 0.f) {
+  const int need = (mx < Scale<float>::threshold() && mx > 0.f) ? 1 : 0;
+#pragma unroll 1
+  for (unsigned z = pinned((unsigned)need); z != 0; --z) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) y[i] *= Scale<float>::factor();
-    return 1;
   }
-  return 0;
+  return need;
 }
 
 // 1 / x for a positive, normal x (a site likelihood, rescaled to stay far from the
@@ -181,7 +193,7 @@ __device__ __forceinline__ double fast_rcp(double x) {
 template <typename T, int CPT>
 struct WalkThread {
   unsigned sc;     // shared base + 16 * column: a block's byte offset is added to this
-  unsigned dB;     // 16 * ts: the thread's second column inside a block (CPT == 2)
+  unsigned dB;     // 16 * ts: the thread's next column inside a block
   unsigned plane;  // fp64: bytes between the two halves of a column
   unsigned km;     // shared base + k * row_bytes: a row's byte offset is added to this
   unsigned rs;     // bytes between rows
@@ -190,31 +202,6 @@ struct WalkThread {
   T cw, cwr;       // K != 1: category weight, category weight x rate
   double w[CPT];   // pattern weights of the thread's columns (0 for padding columns)
 };
-
-// A child's message -> registers.  tip: row `code` of its table (code from the round's tip rows);
-// otherwise the thread's column of the child's block.  Same instructions either way.
-template <typename T, int CPT>
-__device__ __forceinline__ void fetch_child(const WalkThread<T, CPT>& th, unsigned a, bool tip, const unsigned (&code)[CPT],
-                                            T (&m)[CPT][4]) {
-#pragma unroll
-  for (int c = 0; c < CPT; ++c) {
-    const unsigned row = min(code[c], kTipAny);
-    const unsigned at = tip ? th.km + a + row * th.rs : th.sc + a + c * th.dB;
-    lds_vec(at, tip ? 16u : th.plane, m[c]);
-    if (tip && code[c] >= kTipAmbiguous) {  // rare: an ambiguity code other than "any": sum the compatible rows
-#pragma unroll
-      for (int i = 0; i < 4; ++i) m[c][i] = (T)0;
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if ((code[c] >> j) & 1u) {
-          T r[4];
-          lds_vec(th.km + a + j * th.rs, 16u, r);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) m[c][i] += r[i];
-        }
-    }
-  }
-}
 
 // The 32-byte descriptor as the planner wrote it (b2p_walk_types.h: WalkDesc), unpacked.
 struct TaskDesc {
@@ -229,159 +216,167 @@ __device__ __forceinline__ TaskDesc unpack_desc(const uint4 d0, const uint4 d1) 
   return d;
 }
 
-// ------------------------------------------------------------------ post-order task
-//   x_v = m_l o m_r (rescaled when tiny) ;  m_v = P_v x_v ; root: site likelihoods -> log-likelihood term
-template <typename T, int K, int CPT>
-__device__ __forceinline__ void post_task(const WalkParams<T>& p, const WalkThread<T, CPT>& th, const TaskDesc& d,
-                                          int* scount, int col, unsigned gslot, T (&ma)[CPT][4], T (&mb)[CPT][4]) {
-  int bumped[CPT];
+// A child's message for one column -> registers.  tip: row `code` of its table (code from the
+// round's tip rows); otherwise the thread's column of the child's block (oc: byte offset of the
+// column inside a block, relative to the thread's first one).  Same instructions either way.
+template <typename T, int CPT>
+__device__ __forceinline__ void fetch_child(const WalkThread<T, CPT>& th, unsigned a, bool tip, unsigned code, unsigned oc,
+                                            T (&m)[4]) {
+  const unsigned at = tip ? th.km + a + min(code, kTipAny) * th.rs : th.sc + a + oc;
+  lds_vec(at, tip ? 16u : th.plane, m);
+  if (tip && code >= kTipAmbiguous) {  // rare: an ambiguity code other than "any": sum the compatible rows
 #pragma unroll
-  for (int c = 0; c < CPT; ++c) {
+    for (int i = 0; i < 4; ++i) m[i] = (T)0;
+#pragma unroll 1
+    for (int j = 0; j < 4; ++j)
+      if ((code >> j) & 1u) {
+        T r[4];
+        lds_vec(th.km + a + j * th.rs, 16u, r);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) ma[c][i] *= mb[c][i];
-    bumped[c] = rescale<K>(th.gmask, th.lane, th.kk, ma[c]);
+        for (int i = 0; i < 4; ++i) m[i] += r[i];
+      }
   }
+}
+
+// ------------------------------------------------------------------ post-order task, one column
+//   x_v = m_l o m_r (rescaled when tiny) ;  m_v = P_v x_v ; root: site likelihood -> log-likelihood term
+template <typename T, int K, int CPT>
+__device__ __forceinline__ void post_column(const WalkParams<T>& p, const WalkThread<T, CPT>& th, const TaskDesc& d, int* scount_c,
+                                            unsigned code_l, unsigned code_r, unsigned oc, double w, double& term) {
+  T x[4], mb[4];
+  fetch_child<T, CPT>(th, d.a_l, (d.flags & WF_TIP_L) != 0, code_l, oc, x);
+  fetch_child<T, CPT>(th, d.a_r, (d.flags & WF_TIP_R) != 0, code_r, oc, mb);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) x[i] *= mb[i];
+  const int bumped = rescale<K>(th.gmask, th.lane, th.kk, x);
   if (!(d.flags & WF_ROOT)) {
-    T mv[CPT][4];
+    T mv[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       T r[4];
       lds_vec(th.km + d.a_v + i * th.rs, 16u, r);
-#pragma unroll
-      for (int c = 0; c < CPT; ++c)
-        mv[c][i] = r[0] * ma[c][0] + r[1] * ma[c][1] + r[2] * ma[c][2] + r[3] * ma[c][3];
+      mv[i] = r[0] * x[0] + r[1] * x[1] + r[2] * x[2] + r[3] * x[3];
     }
-#pragma unroll
-    for (int c = 0; c < CPT; ++c) {
-      sts_vec(th.sc + d.dst0 + c * th.dB, th.plane, mv[c]);
-      if (bumped[c] && th.k == 0) atomicAdd(scount + col + c * th.ts, 1);
-    }
+    sts_vec(th.sc + d.dst0 + oc, th.plane, mv);
+    if (bumped && th.k == 0) atomicAdd(scount_c, 1);
   } else {
-    double term = 0.0;
-#pragma unroll
-    for (int c = 0; c < CPT; ++c) {
-      T site = (T)p.freqs[0] * ma[c][0] + (T)p.freqs[1] * ma[c][1] + (T)p.freqs[2] * ma[c][2] + (T)p.freqs[3] * ma[c][3];
-      if (K != 1) site = group_sum<K>(site * th.cw, th.gmask, th.lane, th.kk);
-      if (th.k == 0 && th.w[c] != 0.0)
-        term += th.w[c] * (log((double)site) - (double)(scount[col + c * th.ts] + bumped[c]) * Scale<T>::log_factor());
-    }
-    sts_d2(gslot, term, 0.0);
+    T site = (T)p.freqs[0] * x[0] + (T)p.freqs[1] * x[1] + (T)p.freqs[2] * x[2] + (T)p.freqs[3] * x[3];
+    if (K != 1) site = group_sum<K>(site * th.cw, th.gmask, th.lane, th.kk);
+    if (th.k == 0 && w != 0.0) term += w * (log((double)site) - (double)(*scount_c + bumped) * Scale<T>::log_factor());
   }
 }
 
-// One child's side of a pre-order task: its gradient numerator r_k q.(Q m) and, for an internal
-// child, its pre-order partial u_c = P_c^T q (rescaled when tiny) -> shared memory.
+// One child's side of a pre-order task, one column: its gradient numerator q.(Q m) and, for an
+// internal child, its pre-order partial u_c = P_c^T q (rescaled when tiny) -> shared memory.
 template <typename T, int K, int CPT>
-__device__ __forceinline__ void pre_side(const WalkParams<T>& p, const WalkThread<T, CPT>& th, bool tip, unsigned mat, unsigned dst,
-                                         const T (&q)[CPT][4], const T (&m)[CPT][4], T (&num)[CPT]) {
+__device__ __forceinline__ T pre_side(const WalkParams<T>& p, const WalkThread<T, CPT>& th, bool tip, unsigned mat, unsigned dst,
+                                      const T (&q)[4], const T (&m)[4]) {
+  T num = (T)0;
+  // d/dt (P x) = r Q (P x): Q comes from the constant bank
 #pragma unroll
-  for (int c = 0; c < CPT; ++c) {
-    num[c] = (T)0;
-    // d/dt (P x) = r Q (P x): Q comes from the constant bank
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const T dm = p.q[4 * i] * m[c][0] + p.q[4 * i + 1] * m[c][1] + p.q[4 * i + 2] * m[c][2] + p.q[4 * i + 3] * m[c][3];
-      num[c] += q[c][i] * dm;
-    }
+  for (int i = 0; i < 4; ++i) {
+    const T dm = p.q[4 * i] * m[0] + p.q[4 * i + 1] * m[1] + p.q[4 * i + 2] * m[2] + p.q[4 * i + 3] * m[3];
+    num += q[i] * dm;
   }
   if (!tip) {
-    T u[CPT][4];
-#pragma unroll
-    for (int c = 0; c < CPT; ++c)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) u[c][j] = (T)0;
+    T u[4] = {(T)0, (T)0, (T)0, (T)0};
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       T r[4];
       lds_vec(th.km + mat + i * th.rs, 16u, r);
 #pragma unroll
-      for (int c = 0; c < CPT; ++c)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) u[c][j] += r[j] * q[c][i];
+      for (int j = 0; j < 4; ++j) u[j] += r[j] * q[i];
     }
-#pragma unroll
-    for (int c = 0; c < CPT; ++c) {
-      (void)rescale<K>(th.gmask, th.lane, th.kk, u[c]);
-      sts_vec(th.sc + dst + c * th.dB, th.plane, u[c]);
-    }
+    (void)rescale<K>(th.gmask, th.lane, th.kk, u);
+    sts_vec(th.sc + dst, th.plane, u);
   }
+  return num;
 }
 
-// ------------------------------------------------------------------- pre-order task
+// ------------------------------------------------------------------- pre-order task, one column
 //   q_l = u_v o m_r, q_r = u_v o m_l ; L = q_l . m_l ; dL/dt_l = r_k q_l.(Q m_l) ; u_l = P_l^T q_l (same for r)
 template <typename T, int K, int CPT>
-__device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThread<T, CPT>& th, const TaskDesc& d,
-                                         unsigned gslot, const T (&ma)[CPT][4], const T (&mb)[CPT][4]) {
-  T ql[CPT][4], qr[CPT][4], den[CPT], numl[CPT], numr[CPT];
+__device__ __forceinline__ void pre_column(const WalkParams<T>& p, const WalkThread<T, CPT>& th, const TaskDesc& d,
+                                           unsigned code_l, unsigned code_r, unsigned oc, double w, double& gl, double& gr) {
+  T ma[4], mb[4], u[4], q[4];
+  fetch_child<T, CPT>(th, d.a_l, (d.flags & WF_TIP_L) != 0, code_l, oc, ma);
+  fetch_child<T, CPT>(th, d.a_r, (d.flags & WF_TIP_R) != 0, code_r, oc, mb);
+  lds_vec(th.sc + d.a_v + oc, th.plane, u);
+  T den = (T)0;
 #pragma unroll
-  for (int c = 0; c < CPT; ++c) {
-    T u[4];
-    lds_vec(th.sc + d.a_v + c * th.dB, th.plane, u);
-    den[c] = (T)0;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      ql[c][i] = u[i] * mb[c][i];
-      qr[c][i] = u[i] * ma[c][i];
-      den[c] += ql[c][i] * ma[c][i];
-    }
+  for (int i = 0; i < 4; ++i) {
+    q[i] = u[i] * mb[i];
+    den += q[i] * ma[i];
   }
-  pre_side<T, K, CPT>(p, th, (d.flags & WF_TIP_L) != 0, d.m_l, d.dst0, ql, ma, numl);
-  pre_side<T, K, CPT>(p, th, (d.flags & WF_TIP_R) != 0, d.m_r, d.dst1, qr, mb, numr);
-  double gl = 0.0, gr = 0.0;
+  T numl = pre_side<T, K, CPT>(p, th, (d.flags & WF_TIP_L) != 0, d.m_l, d.dst0 + oc, q, ma);
 #pragma unroll
-  for (int c = 0; c < CPT; ++c) {
-    T dn = den[c];
-    if (K != 1) {
-      // the site likelihood is the sum over the pattern's K category lanes; the numerators
-      // need no such exchange: every lane adds its own category's share and the fold sums
-      // over all lanes of the slot anyway
-      dn = group_sum<K>(dn * th.cw, th.gmask, th.lane, th.kk);
-      numl[c] *= th.cwr;
-      numr[c] *= th.cwr;
-    }
-    // K == 1: the single category's weight cancels, its rate multiplies the numerators.  A
-    // pattern of likelihood zero contributes nothing instead of inf * 0.
-    const double dd = (double)dn;
-    const double inv = dd > 0.0 ? (K == 1 ? th.w[c] * p.rates[0] : th.w[c]) * fast_rcp(dd) : 0.0;
-    gl += (double)numl[c] * inv;
-    gr += (double)numr[c] * inv;
+  for (int i = 0; i < 4; ++i) q[i] = u[i] * ma[i];
+  T numr = pre_side<T, K, CPT>(p, th, (d.flags & WF_TIP_R) != 0, d.m_r, d.dst1 + oc, q, mb);
+  if (K != 1) {
+    // the site likelihood is the sum over the pattern's K category lanes; the numerators
+    // need no such exchange: every lane adds its own category's share and the fold sums
+    // over all lanes of the slot anyway
+    den = group_sum<K>(den * th.cw, th.gmask, th.lane, th.kk);
+    numl *= th.cwr;
+    numr *= th.cwr;
   }
-  sts_d2(gslot, gl, gr);
+  // K == 1: the single category's weight cancels, its rate multiplies the numerators.  A
+  // pattern of likelihood zero contributes nothing instead of inf * 0.
+  const double dd = (double)den;
+  const double inv = dd > 0.0 ? (K == 1 ? w * p.rates[0] : w) * fast_rcp(dd) : 0.0;
+  gl += (double)numl * inv;
+  gr += (double)numr * inv;
 }
 
-// Fold one round's per-thread sums (done by the copy warps one round later): slot s2's ts
-// pairs -> (a, b), added to the branch gradients / the log-likelihood in a fixed order.
-// A warp folds four slots at a time, eight lanes each.  ids: what each slot's sums belong to
-// (shared memory: the issue record of the next round; after the last round: global memory).
+// Fold the per-thread sums of the previous round (copy warps): a slot's ts pairs -> (a, b),
+// added to the branch gradients / the log-likelihood.  The copy warps share the shared-memory
+// and fp64 pipes with thirteen busy compute warps and get an instruction through every ~15
+// cycles, so the fold is written for instruction count: a warp folds FOUR slots per pass (slots
+// s0, s0 + step, ...: eight lanes each), every lane adds ts / 8 pairs — branch-free, every load
+// independent — and three shuffle stages finish.  Fixed summation order: deterministic.
+// ids: what each slot's sums belong to (shared memory: the issue record of the next round;
+// after the last round: global memory).
 template <typename T, bool IDS_SHARED>
-__device__ __forceinline__ void fold_round(const WalkParams<T>& p, unsigned sbase, int par, int pw, int lane, bool first_tile,
-                                           unsigned ids_smem, const int2* ids_gmem, double& ll_acc) {
-  const unsigned gbuf = sbase + p.off_gbuf + par * p.wn * p.ts * 16;
-  const int li = lane & 7;
-  for (int s0 = pw * 4; s0 < p.wn; s0 += p.n_copy_warps * 4) {
-    const int s2 = s0 + (lane >> 3);
-    int2 ids = make_int2(-1, -1);
-    if (s2 < p.wn) ids = IDS_SHARED ? lds_i2(ids_smem + s2 * 8) : __ldg(ids_gmem + s2);
-    double a = 0.0, b = 0.0;
-    if (ids.x != -1) {
-      for (int c = li; c < p.ts; c += 8) {
-        // lanes of a slot that hold no column (K does not divide 32) never wrote their pair
-        if ((c & 31) >= p.cpw || (c >> 5) * p.cpw + (c & 31) >= p.ct) continue;
-        const double2 v = lds_d2(gbuf + (s2 * p.ts + c) * 16);
-        a += v.x; b += v.y;
-      }
+__device__ __forceinline__ void fold_slots(const WalkParams<T>& p, unsigned gbuf, int s0, int step, int lane, bool first_tile,
+                                           unsigned ids_smem, const int2* ids_gmem, double& ll_acc, long long* stamp = nullptr) {
+  const bool holes = p.cpw != 32;  // K does not divide 32: lanes of a slot that hold no column never wrote their pair
+  const int li = lane & 7, s2 = s0 + (lane >> 3) * step;
+  int2 ids = make_int2(-1, -1);
+  if (s2 < p.wn) ids = IDS_SHARED ? lds_i2(ids_smem + s2 * 8) : __ldg(ids_gmem + s2);
+  const bool live = ids.x != -1;
+  const unsigned row = gbuf + min(s2, p.wn - 1) * p.ts * 16;
+  double a = 0.0, b = 0.0;
+  // every lane always loads (a clamped, valid address); the value is zeroed when the pair does
+  // not exist — guarded loads cost more in branches than in loads
+  for (int c0 = li; c0 < p.ts; c0 += 32) {
+    double2 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int c = c0 + 8 * u;
+      v[u] = lds_d2(row + min(c, p.ts - 1) * 16);
+      const bool ok = live & (c < p.ts) & !(holes & (((c & 31) >= p.cpw) | ((c >> 5) * p.cpw + (c & 31) >= p.ct)));
+      v[u].x = ok ? v[u].x : 0.0;
+      v[u].y = ok ? v[u].y : 0.0;
     }
-    const double oa = __shfl_xor_sync(0xffffffffu, a, 4), ob = __shfl_xor_sync(0xffffffffu, b, 4);
-    double v = (li & 4) ? (b + ob) : (a + oa);
-    v += __shfl_xor_sync(0xffffffffu, v, 2);
-    v += __shfl_xor_sync(0xffffffffu, v, 1);
-    if ((li & 3) == 0) {
-      const int id = li ? ids.y : ids.x;
-      if (id == -2) ll_acc += v;
-      else if (id >= 0) {
-        double* gp = p.gpart + (size_t)blockIdx.x * p.n_branches + id;
-        *gp = first_tile ? v : *gp + v;
-      }
+    a += (v[0].x + v[1].x) + (v[2].x + v[3].x);
+    b += (v[0].y + v[1].y) + (v[2].y + v[3].y);
+  }
+#ifdef B2P_TRACE_CLOCKS
+  if (stamp) { stamp[0] = clock64(); }
+#endif
+  // lanes 0-3 of a slot's eight end up with the first sum, lanes 4-7 with the second
+  const double oa = __shfl_xor_sync(0xffffffffu, a, 4), ob = __shfl_xor_sync(0xffffffffu, b, 4);
+  double v = (li & 4) ? (b + ob) : (a + oa);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  if ((li & 3) == 0) {
+    const int id = li ? ids.y : ids.x;
+    if (id == -2) ll_acc += v;
+    else if (id >= 0) {
+      // a branch is written once per tile, always by this lane: plain store for the CTA's first
+      // tile, then fire-and-forget adds in tile order (deterministic, no read latency)
+      double* gp = p.gpart + (size_t)blockIdx.x * p.n_branches + id;
+      if (first_tile) *gp = v; else atomicAdd(gp, v);
     }
   }
 }
@@ -390,31 +385,33 @@ template <typename T, int K, int NT, int CPT>
 __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __grid_constant__ WalkParams<T> p) {
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ double red[NT / 32];
+  __shared__ unsigned long long gbase[4];  // global base of every job kind for the current tile
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int kk = K > 0 ? K : p.n_cat;
   const int first_copy_warp = NT / 32 - p.n_copy_warps;
   const bool copier = warp >= first_copy_warp;
   const int s = t / p.ts;
   const int tt = t - s * p.ts;
-  int col = CPT == 2 ? tt : (tt >> 5) * p.cpw + (tt & 31);
-  const bool in_slot = !copier && s < p.wn && (CPT == 2 || ((tt & 31) < p.cpw && col < p.ct));
+  int col = CPT == 1 ? (tt >> 5) * p.cpw + (tt & 31) : tt;
+  const bool in_slot = !copier && s < p.wn && (CPT != 1 || ((tt & 31) < p.cpw && col < p.ct));
   if (!in_slot) col = 0;
   const int S = p.stages, D = p.depth, R = p.rounds_run;
-  const unsigned sbase = smem_u32(smem);
+  const unsigned sbase = pinned(smem_u32(smem));
   const unsigned bar0 = sbase + p.off_bar;
+  const unsigned gb = pinned(smem_u32(gbase));
   int* scount = reinterpret_cast<int*>(smem + p.off_scount);
 
   WalkThread<T, CPT> th;
   th.lane = lane; th.kk = kk; th.k = col % kk; th.ts = p.ts;
   th.gmask = group_mask<K>(lane, kk);
-  th.sc = sbase + col * 16; th.dB = p.ts * 16; th.plane = p.plane;
-  th.km = sbase + th.k * 4 * (unsigned)sizeof(T);
+  th.sc = pinned(sbase + col * 16); th.dB = p.ts * 16; th.plane = p.plane;
+  th.km = pinned(sbase + th.k * 4 * (unsigned)sizeof(T));
   th.rs = p.row_stride;
   th.cw = (T)p.cat_w[th.k]; th.cwr = (T)(p.cat_w[th.k] * p.rates[th.k]);
   const int sl = in_slot ? s : 0;
-  const unsigned o_desc = p.rel_cr + sl * 32;
-  const unsigned o_tip = p.rel_tips + sl * 2 * p.ct_pad + col;
-  const unsigned o_gslot = sbase + p.off_gbuf + (sl * p.ts + tt) * 16;
+  const unsigned o_desc = pinned(p.rel_cr + sl * 32);
+  const unsigned o_tip = pinned(p.rel_tips + sl * 2 * p.ct_pad + col);
+  const unsigned o_gslot = pinned(sbase + p.off_gbuf + (sl * p.ts + tt) * 16);
 
   if (t == 0) {
     for (int j = 0; j < S; ++j) mbar_init(bar0 + 8 * j, 1);
@@ -431,6 +428,12 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
   unsigned phase_bits = 0;
   double ll_acc = 0.0;
   bool first_tile = true;
+  // one bulk copy of a job list entry {goff, soff, bytes, kind}
+  auto job_ptr = [&](const uint4 jb) -> unsigned char* {
+    unsigned long long b;
+    asm volatile("ld.shared.u64 %0, [%1];" : "=l"(b) : "r"(gb + jb.w * 8));
+    return reinterpret_cast<unsigned char*>(b + jb.x);
+  };
 
   for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, first_tile = false) {
 #pragma unroll
@@ -439,15 +442,13 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
       th.w[c] = (in_slot && cg < p.n_cols) ? __ldg(p.weights + cg / kk) : 0.0;
     }
     for (int i = t; i < p.ct; i += NT) scount[i] = 0;
+    if (t == 0) {
+      gbase[JK_MSG] = (unsigned long long)(p.msg + (unsigned long long)tile * p.tile_stride_part);
+      gbase[JK_PRE] = (unsigned long long)(p.pre + (unsigned long long)tile * p.tile_stride_part);
+      gbase[JK_TIPS] = (unsigned long long)(p.tips + (unsigned long long)tile * p.tile_stride_tips);
+      gbase[JK_REC] = (unsigned long long)p.records;
+    }
     __syncthreads();
-    unsigned char* base_msg = p.msg + (unsigned long long)tile * p.tile_stride_part;
-    unsigned char* base_pre = p.pre + (unsigned long long)tile * p.tile_stride_part;
-    const unsigned char* base_tips = p.tips + (unsigned long long)tile * p.tile_stride_tips;
-    auto gptr = [&](unsigned kind, unsigned goff) -> const unsigned char* {
-      const unsigned char* b = kind == JK_MSG ? base_msg : kind == JK_PRE ? base_pre : kind == JK_TIPS ? base_tips
-                               : kind == JK_MATS ? p.mats : p.records;
-      return b + goff;
-    };
     if (warp == NT / 32 - 1) {  // boot: loads of rounds 0 .. depth-1
       const uint4* jobs = reinterpret_cast<const uint4*>(p.records + p.boot_base);
       unsigned j0 = 0;
@@ -457,7 +458,7 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
         __syncwarp();
         for (unsigned j = lane; j < p.boot_n[f]; j += 32) {
           const uint4 jb = __ldg(jobs + j0 + j);
-          bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar);
+          bulk_load(sbase + jb.y, job_ptr(jb), jb.z, bar);
         }
         j0 += p.boot_n[f];
       }
@@ -477,41 +478,56 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
 #ifdef B2P_TRACE_CLOCKS
       if (tr) trow[1] = clock64();
 #endif
+      // issue record of this round: {n_loads, n_stores, tx_bytes, pass}, fold ids, jobs
+      const unsigned ir = frame + p.rel_ir, jobs = ir + p.ir_jobs;
       if (copier) {
-        // Copy warps: the loads of round q + depth, then the stores of round q-1's results.
-        // Issuing them from warps of their own lets the copies overlap the arithmetic; one warp
-        // issues a bulk copy every ~100 cycles, so several share the lists (job j belongs to
-        // copy warp j % n).  Order within the round is free: the planner never lets a load
-        // target a block whose store is issued in the same round, nor read back a value before
-        // the round after its store completed (rules S and L, tests/tools/plan_check.cpp).
-        const uint4 hdr = lds_u4(frame);
+        // Copy warps: the loads of round q + depth, the stores of round q-1's results (job j belongs
+        // to copy warp j % n: issuing a bulk copy blocks its warp for ~100 cycles, and the SM takes
+        // one every ~70 cycles at best, so the issue is kept off the compute warps), then the fold
+        // of round q-1's sums, one slot per warp at a time.  The planner never lets a load target a
+        // block whose store is issued in the same round, nor read back a value before the round
+        // after its store completed (rules S and L, plan_check.cpp).
+        const uint4 hdr = lds_u4(ir);
         const unsigned st_next = st == 0 ? S - 1 : st - 1;  // (q + D) % S with S = D + 1
         const unsigned bar = bar0 + 8 * st_next;
         const unsigned n_loads = (q + D < R) ? hdr.x : 0u;
-        const unsigned jobs = frame + p.ir_jobs;
         const unsigned np = p.n_copy_warps, pw = warp - first_copy_warp;
         if (pw == 0 && lane == 0 && n_loads) mbar_expect_tx(bar, hdr.z);
-        // loads of round q + depth first: they are what the next round waits for; the stores only
-        // have to have read shared memory by the end of this round
         for (unsigned j = pw + np * lane; j < n_loads; j += 32 * np) {
           const uint4 jb = lds_u4(jobs + j * 16);
-          bulk_load(sbase + jb.y, gptr(jb.w, jb.x), jb.z, bar);
+          bulk_load(sbase + jb.y, job_ptr(jb), jb.z, bar);
         }
 #ifdef B2P_TRACE_CLOCKS
         if (tr) trow[5] = clock64();
 #endif
+#ifdef B2P_DBG
+        if (!(p.dbg & 2))
+#endif
         for (unsigned j = pw + np * lane; j < hdr.y; j += 32 * np) {
           const uint4 jb = lds_u4(jobs + (hdr.x + j) * 16);
-          bulk_store(const_cast<unsigned char*>(gptr(jb.w, jb.x)), sbase + jb.y, jb.z);
+          bulk_store(job_ptr(jb), sbase + jb.y, jb.z);
         }
         bulk_commit();  // one (possibly empty) group per lane per round
 #ifdef B2P_TRACE_CLOCKS
         if (tr) trow[2] = clock64();
 #endif
-        if (q > 0) fold_round<T, true>(p, sbase, par ^ 1, pw, lane, first_tile, frame + 16, nullptr, ll_acc);
+#ifdef B2P_DBG
+        if (!(p.dbg & 1))
+#endif
+        if (q >= p.rounds_post) {  // sums exist from the root's post-order round on
+          for (int s0 = pw; s0 < p.wn; s0 += 4 * np)
+#ifdef B2P_TRACE_CLOCKS
+            fold_slots<T, true>(p, sbase + p.off_gbuf + (par ^ 1) * p.wn * p.ts * 16, s0, np, lane, first_tile, ir + 16, nullptr, ll_acc,
+                                tr && s0 == (int)pw ? trow + 7 : nullptr);
+#else
+            fold_slots<T, true>(p, sbase + p.off_gbuf + (par ^ 1) * p.wn * p.ts * 16, s0, np, lane, first_tile, ir + 16, nullptr, ll_acc);
+#endif
+        }
 #ifdef B2P_TRACE_CLOCKS
         if (tr) trow[6] = clock64();
 #endif
+        // this round's stores have read shared memory (their blocks may be rewritten next round);
+        // those of the round before are complete in global memory
         asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         asm volatile("cp.async.bulk.wait_group 1;" ::: "memory");
       } else if (in_slot) {
@@ -524,17 +540,26 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
           code_r[c] = lds_u8(frame + o_tip + p.ct_pad + c * p.ts);
         }
         const TaskDesc d = unpack_desc(d0, d1);
-        if (d.flags & WF_LIVE) {
-          T ma[CPT][4], mb[CPT][4];
-          fetch_child<T, CPT>(th, d.a_l, (d.flags & WF_TIP_L) != 0, code_l, ma);
-          fetch_child<T, CPT>(th, d.a_r, (d.flags & WF_TIP_R) != 0, code_r, mb);
-#ifdef B2P_TRACE_CLOCKS
-          if (tr) trow[2] = clock64();
+#ifdef B2P_DBG
+        if (!(p.dbg & 4))
 #endif
+        if (d.flags & WF_LIVE) {
           const unsigned gslot = o_gslot + par * p.wn * p.ts * 16;
-          if (q < p.rounds_post) post_task<T, K, CPT>(p, th, d, scount, col, gslot, ma, mb);
-          else pre_task<T, K, CPT>(p, th, d, gslot, ma, mb);
+          double ga = 0.0, gb2 = 0.0;  // post-order (root): log-likelihood term, 0; pre-order: the two gradient sums
+          if (q < p.rounds_post) {
+#pragma unroll
+            for (int c = 0; c < CPT; ++c)
+              post_column<T, K, CPT>(p, th, d, scount + col + c * p.ts, code_l[c], code_r[c], c * th.dB, th.w[c], ga);
+            if (d.flags & WF_ROOT) sts_d2(gslot, ga, 0.0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < CPT; ++c) pre_column<T, K, CPT>(p, th, d, code_l[c], code_r[c], c * th.dB, th.w[c], ga, gb2);
+            sts_d2(gslot, ga, gb2);
+          }
         }
+#ifdef B2P_TRACE_CLOCKS
+        if (tr) trow[2] = clock64();
+#endif
       }
       // shared-memory results of this round (generic proxy) before the bulk copies (async
       // proxy) that read them or overwrite their blocks
@@ -550,8 +575,11 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
     }
     if (copier) {
       // the last round's sums: their ids come from global memory (no further issue record)
-      fold_round<T, false>(p, sbase, (R - 1) & 1, warp - first_copy_warp, lane, first_tile, 0u,
-                           reinterpret_cast<const int2*>(p.records + p.tail_base), ll_acc);
+      const int2* tail = reinterpret_cast<const int2*>(p.records + p.tail_base);
+      for (int s0 = warp - first_copy_warp; s0 < p.wn; s0 += 4 * p.n_copy_warps)
+        fold_slots<T, false>(p, sbase + p.off_gbuf + ((R - 1) & 1) * p.wn * p.ts * 16, s0, p.n_copy_warps, lane, first_tile, 0u, tail, ll_acc);
+      // (the last round leaves nothing to store: the root's post-order task writes no message,
+      //  and a pre-order partial is stored only when a later round loads it back)
       asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     }
     __syncthreads();

@@ -54,7 +54,7 @@ struct WalkIds {
 };
 
 // One bulk copy.  goff is relative to the per-kind base (tile-relative for MSG/PRE/TIPS).
-enum : uint32_t { JK_MSG = 0, JK_PRE = 1, JK_TIPS = 2, JK_MATS = 3, JK_REC = 4 };
+enum : uint32_t { JK_MSG = 0, JK_PRE = 1, JK_TIPS = 2, JK_REC = 3 };
 struct WalkJob {
   uint32_t goff;   // bytes
   uint32_t soff;   // shared-memory byte offset
@@ -63,9 +63,10 @@ struct WalkJob {
 };
 static_assert(sizeof(WalkJob) == 16, "WalkJob must be 16 bytes");
 
-// Issue record of one round (read by the copy warps at the top of the round):
+// Issue record of one round (read at the top of the round):
 // header, then wn fold ids (what the sums of round q - 1 belong to), then n_loads load jobs
 // (operands of round q + depth), then n_stores store jobs (results of round q - 1).
+// A round's descriptors, issue record and matrix rows form ONE record — one bulk copy.
 struct WalkIssueHeader {
   uint32_t n_loads, n_stores;
   uint32_t tx_bytes;  // sum of the load jobs' bytes (mbarrier transaction count)

@@ -45,3 +45,19 @@ def make_engine(w: Workload, precision=None, **kw):
     eng.set_pattern_weights(w.patterns.weights)
     eng.set_model(w.subst_model, w.site_model)
     return eng
+
+
+def grad_report(g, g_ref):
+    """The gradient error both ways: ``floored`` is ``grad_err`` (denominator floored at 1e-4 of the
+    largest entry), ``plain`` is the entry-wise relative error |g - g_ref| / |g_ref| with no floor,
+    ``n_floored`` counts the entries whose denominator the floor replaced, ``worst_plain_entry``
+    is the reference value of the entry with the largest plain error."""
+    g, g_ref = np.asarray(g, dtype=np.float64), np.asarray(g_ref, dtype=np.float64)
+    big = np.max(np.abs(g_ref))
+    floor = big * 1e-4
+    nz = np.abs(g_ref) > 0
+    plain = np.zeros_like(g_ref)
+    plain[nz] = np.abs(g - g_ref)[nz] / np.abs(g_ref)[nz]
+    i = int(np.argmax(plain))
+    return {"floored": grad_err(g, g_ref), "plain": float(plain.max()), "n_floored": int((np.abs(g_ref) < floor).sum()),
+            "n": int(g_ref.size), "worst_plain_entry": float(g_ref[i]), "max_abs": float(big)}

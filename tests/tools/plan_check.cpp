@@ -65,14 +65,14 @@ int main(int argc, char** argv) {
   // which node is the post-order task at a given place of the matrix bundles?  (own matrix rows)
   std::map<uint32_t, int> post_node_at;  // byte offset in the bundle array -> node
   for (int v = N; v < root; ++v) {
-    if (plan.mat_dst[2 * v] < 0 || plan.mat_dst[2 * v] % g.row_stride != 0) FAIL("mat_dst own of %d", v);
+    if (plan.mat_dst[2 * v] < 0 || plan.mat_dst[2 * v] % 16 != 0) FAIL("mat_dst own of %d", v);
     post_node_at[(uint32_t)plan.mat_dst[2 * v]] = v;
   }
   for (int b = 0; b < 2 * N - 2; ++b) {
     if (plan.mat_dst[2 * b + 1] < 0) FAIL("branch %d has no pre-order matrix rows", b);
     if (b < N && plan.mat_dst[2 * b] < 0) FAIL("tip %d has no post-order matrix rows", b);
   }
-  if ((int)plan.mats_off.size() != plan.rounds + 1 || (int)plan.tip_order.size() != plan.rounds * 2 * g.wn) FAIL("table sizes");
+  if ((int)plan.rec_off.size() != plan.rounds + 1 || (int)plan.rec_mats.size() != plan.rounds || (int)plan.tip_order.size() != plan.rounds * 2 * g.wn) FAIL("table sizes");
   {  // rows of different branches never overlap, every round stays within the frame's matrix region
     std::vector<std::pair<uint32_t, uint32_t>> spans;
     for (int b = 0; b < 2 * N - 2; ++b)
@@ -80,8 +80,12 @@ int main(int argc, char** argv) {
         if (plan.mat_dst[2 * b + w] >= 0) spans.push_back({(uint32_t)plan.mat_dst[2 * b + w], (uint32_t)((b < N ? kRowsTip : kRowsPlain) * g.row_stride)});
     std::sort(spans.begin(), spans.end());
     for (size_t i = 1; i < spans.size(); ++i) if (spans[i - 1].first + spans[i - 1].second > spans[i].first) FAIL("matrix rows overlap");
-    if (!spans.empty() && spans.back().first + spans.back().second > plan.mats_off.back()) FAIL("matrix rows past the end");
-    for (int q = 0; q < plan.rounds; ++q) if ((int)(plan.mats_off[q + 1] - plan.mats_off[q]) > g.mats_bytes) FAIL("round %d: bundle larger than the frame region", q);
+    if (!spans.empty() && spans.back().first + spans.back().second > plan.rec_off.back()) FAIL("matrix rows past the end");
+    for (int q = 0; q < plan.rounds; ++q) {
+      const int len = (int)(plan.rec_off[q + 1] - plan.rec_off[q]);
+      if (len > g.rel_tips || len % 16 || plan.rec_off[q] % 16) FAIL("round %d: record larger than the frame / misaligned", q);
+      if ((int)(len - plan.rec_mats[q]) > g.mats_bytes) FAIL("round %d: more matrix rows than the budget", q);
+    }
   }
   const uint8_t* rec = plan.records.data();
   // symbolic pool: tag = 1 + vid (vid: message of v -> v-N ; partial of c -> (N-1)+(c-N)), 0 = nothing
@@ -90,7 +94,7 @@ int main(int argc, char** argv) {
   std::map<int, int> stored_at;  // vid -> iteration the store was issued
   auto blk_of = [&](uint32_t soff) { return ((int)soff - g.off_pool) / g.blk; };
   auto check_soff = [&](uint32_t soff) { return (int)soff >= g.off_pool && ((int)soff - g.off_pool) % g.blk == 0 && blk_of(soff) < NB; };
-  long long n_loads = 0, n_stores = 0, n_tasks = 0;
+  long long n_loads = 0, n_stores = 0, n_tasks = 0, n_rec_jobs = 0;
   std::vector<int> done_post(2 * N - 1, 0), done_pre(2 * N - 1, 0);
   auto do_load = [&](const WalkJob& j, int iter, int f) -> const char* {
     if (j.bytes % 16 || j.soff % 16 || j.goff % 16) return "alignment";
@@ -107,13 +111,9 @@ int main(int argc, char** argv) {
     } else if (j.kind == JK_TIPS) {
       if ((int)j.soff != g.off_tips + (f % S) * g.frame_bytes || (int)j.bytes > g.tips_bytes ||
           j.goff != (uint32_t)f * 2u * (uint32_t)g.wn * (uint32_t)g.ct_pad || j.bytes % (2 * g.ct_pad)) return "tips job";
-    } else if (j.kind == JK_MATS) {
-      if ((int)j.soff != g.off_mats + (f % S) * g.frame_bytes || (int)j.bytes > g.mats_bytes || j.goff != plan.mats_off[f] ||
-          j.bytes != plan.mats_off[f + 1] - plan.mats_off[f]) return "mats job";
     } else if (j.kind == JK_REC) {
-      const bool is_cr = j.goff == (uint32_t)f * g.cr_bytes && (int)j.soff == g.off_cr + (f % S) * g.frame_bytes && (int)j.bytes == g.cr_bytes;
-      const bool is_ir = j.goff == plan.ir_base + (uint32_t)f * g.ir_bytes && (int)j.soff == g.off_ir + (f % S) * g.frame_bytes && (int)j.bytes <= g.ir_bytes;
-      if (!is_cr && !is_ir) return "record job";
+      if (j.goff != plan.rec_off[f] || (int)j.soff != g.off_frame + (f % S) * g.frame_bytes || j.bytes != plan.rec_off[f + 1] - plan.rec_off[f]) return "record job";
+      ++n_rec_jobs;
     } else return "kind";
     return nullptr;
   };
@@ -132,7 +132,7 @@ int main(int argc, char** argv) {
     }
   }
   for (int q = 0; q < R; ++q) {
-    const uint8_t* ir = rec + plan.ir_base + (size_t)q * g.ir_bytes;
+    const uint8_t* ir = rec + plan.rec_off[q] + g.rel_ir;
     WalkIssueHeader h;
     memcpy(&h, ir, 16);
     const WalkJob* jobs = reinterpret_cast<const WalkJob*>(ir + 16 + g.ir_ids);
@@ -159,16 +159,17 @@ int main(int argc, char** argv) {
     }
     if (tx != h.tx_bytes) FAIL("tx bytes round %d", q);
     // tasks of round q
-    const WalkDesc* d = reinterpret_cast<const WalkDesc*>(rec + (size_t)q * g.cr_bytes);
+    const WalkDesc* d = reinterpret_cast<const WalkDesc*>(rec + plan.rec_off[q] + g.rel_cr);
     // what the fold of the NEXT round is told about this round's sums
-    const WalkIds* ids = reinterpret_cast<const WalkIds*>(q + 1 < R ? rec + plan.ir_base + (size_t)(q + 1) * g.ir_bytes + 16 : rec + plan.tail_base);
+    const WalkIds* ids = reinterpret_cast<const WalkIds*>(q + 1 < R ? rec + plan.rec_off[q + 1] + g.rel_ir + 16 : rec + plan.tail_base);
     if (q == Rpost - 1) {  // a run that stops here reads the second tail record: must say the same
       const WalkIds* t2 = reinterpret_cast<const WalkIds*>(rec + plan.tail_base + g.ir_ids);
       for (int s = 0; s < wn; ++s) if (t2[s].a != ids[s].a || t2[s].b != ids[s].b) FAIL("post-only tail ids");
     }
-    const uint32_t mats0 = (uint32_t)(g.off_mats + (q % S) * g.frame_bytes);
-    auto mat_goff = [&](uint32_t soff) { return plan.mats_off[q] + (soff - mats0); };
-    auto in_mats = [&](uint32_t soff, int rows) { return soff >= mats0 && soff + (uint32_t)rows * g.row_stride <= mats0 + (plan.mats_off[q + 1] - plan.mats_off[q]); };
+    const uint32_t frame0 = (uint32_t)(g.off_frame + (q % S) * g.frame_bytes), mats0 = frame0 + plan.rec_mats[q];
+    if (plan.rec_mats[q] != (uint32_t)g.rel_mats + 16u * (h.n_loads + h.n_stores)) FAIL("round %d: matrix rows do not follow the last job", q);
+    auto mat_goff = [&](uint32_t soff) { return plan.rec_off[q] + (soff - frame0); };
+    auto in_mats = [&](uint32_t soff, int rows) { return soff >= mats0 && soff + (uint32_t)rows * g.row_stride <= frame0 + (plan.rec_off[q + 1] - plan.rec_off[q]); };
     std::vector<int> reads, writes;
     std::vector<std::pair<int, int>> produced;  // (block, vid)
     auto off_blk = [&](uint32_t o) { return blk_of(o); };
@@ -249,6 +250,7 @@ int main(int argc, char** argv) {
     }
     for (auto& pr : produced) tag[pr.first] = 1 + pr.second;
   }
+  if (n_rec_jobs != R) FAIL("every round's record must be loaded exactly once (%lld of %d)", n_rec_jobs, R);
   for (int v = N; v <= root; ++v) if (!done_post[v] || !done_pre[v]) FAIL("task %d missing", v);
   for (int v = N; v < root; ++v) if (!stored_at.count(v - N)) FAIL("message %d never stored", v);
   printf("OK N=%d shape=%d ct=%d cpt=%d K=%d elem=%d depth=%d nt=%d wn=%d wn_eff=%d pool=%d rounds=%d+%d tasks=%lld resident_reads=%lld loads=%lld stores=%lld evictions=%lld max_jobs=%d/%d smem=%zu\n",
