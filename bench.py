@@ -51,6 +51,8 @@ def parse_args():
                          "--patterns 12500 --gpus 8 is BASELINE configs[3]")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true",
+                    help="skip the short runs of the other BASELINE.json configs that ride in the line's `secondary` array")
     return ap.parse_args()
 
 
@@ -126,101 +128,123 @@ def build_workload(name, precision, rank, n_patterns=0):
     return make_workload(name, precision=precision, seq_seed=SEQ_SEED + rank, n_patterns=n_patterns or None)
 
 
+def config_of(name, w, world):
+    """The workload as both arms describe it (same keys, same values: the driver compares them)."""
+    return {"workload": name, "n_taxa": w.n_tips, "patterns_per_gpu": w.n_patterns,
+            "total_patterns": w.n_patterns * world, "categories": w.n_categories,
+            "states": int(getattr(w.patterns, "n_states", 4)), "model": type(w.subst_model).__name__,
+            "tree": "coalescent, seed 20261104"}
+
+
+def cpu_port(w, n_threads=0, want_grad=True):
+    """The CPU implementation of the path for this workload and the cores it uses: the C/OpenMP
+    restatement of the analytic two-pass algorithm (oracle/phylo_oracle.c for 4 states,
+    oracle/phylo_oracle_dense.c for any state count)."""
+    from oracle import c_oracle
+    args = (w.tree.post_triples, w.patterns.masks, w.patterns.weights, w.tree.branch_lengths, *w.eigen_args())
+    fn = c_oracle.loglik_and_gradient if getattr(w.patterns, "n_states", 4) == 4 else c_oracle.dense_loglik_and_gradient
+    return (lambda: fn(*args, n_threads=n_threads, want_grad=want_grad)), (n_threads or c_oracle.max_threads())
+
+
 def cpu_port_rate(w, seconds, n_threads=0, min_evals=3):
     """Timed C oracle (CPU port of the physher/BEAGLE-style analytic two-pass path)."""
     fn, cores = cpu_port(w, n_threads)
     fn()  # warm-up
     n, t0 = 0, time.perf_counter()
     while n < min_evals or time.perf_counter() - t0 < seconds:
-        logl, _ = fn()
+        logl, grad = fn()
         n += 1
     dt = time.perf_counter() - t0
-    return n / dt, cores, n, dt, logl
+    return n / dt, cores, n, dt, logl, grad
 
 
-def cpu_port(w, n_threads=0):
-    """The CPU implementation of the path for this workload and the cores it uses: the C/OpenMP
-    port for 4-state models, the numpy restatement (BLAS threads) for dense-state models."""
-    if getattr(w.patterns, "n_states", 4) == 4:
-        from oracle import c_oracle
-        args = (w.tree.post_triples, w.patterns.masks, w.patterns.weights, w.tree.branch_lengths, *w.eigen_args())
-        return (lambda: c_oracle.loglik_and_gradient(*args, n_threads=n_threads)), (n_threads or c_oracle.max_threads())
-    from oracle import oracle
-    args = (w.tree.post_triples, w.patterns.partials(), w.patterns.weights, w.tree.branch_lengths, *w.eigen_args())
-    return (lambda: oracle.loglik_and_gradient(*args)), 1  # numpy einsum contractions: one core
+def host_cores():
+    """Every core this process may use, whatever OMP_NUM_THREADS says (torchrun sets it to 1)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
 
 
 def run_reference(a):
-    """--impl reference: the CPU implementation of the path, all host threads.  The
-    reference repo itself holds no likelihood code and its contenders (physher, BEAGLE via
-    bito, torchtree) are not installable here, so this arm times the C port (oracle/)."""
+    """--impl reference: the CPU implementation of the path, all host threads.  The reference repo
+    itself holds no likelihood code and its contenders (physher, BEAGLE via bito, torchtree) are
+    not installable here, so this arm times the C port (oracle/).  Under torchrun rank 0 alone
+    runs: it evaluates the whole N-shard alignment (the N shards the other arm's N GPUs hold) on
+    all host cores, and `value` counts shard evaluations per second like the other arm's."""
     rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return 0
-    w = build_workload(a.workload, a.precision, 0, a.patterns)
-    fn, cores = cpu_port(w)
-    for _ in range(max(a.warmup, 1)):
-        fn()
-    t0 = time.perf_counter()
-    for _ in range(a.steps):
-        fn()
+    cores = host_cores()
+    shards = [build_workload(a.workload, a.precision, r, a.patterns) for r in range(world)]
+    fns = [cpu_port(w, n_threads=cores)[0] for w in shards]
+    w = shards[0]
+
+    def step():
+        return [fn() for fn in fns]
+
+    for _ in range(max(min(a.warmup, 3), 1)):
+        step()
+    # bounded: full evaluations until --steps are done or ~60 s have passed (at least 2)
+    n, t0 = 0, time.perf_counter()
+    while n < a.steps and (n < 2 or time.perf_counter() - t0 < 60.0):
+        step()
+        n += 1
     dt = time.perf_counter() - t0
-    value = a.steps / dt
+    value = world * n / dt
     unit = UNIT_FMT.format(n=w.n_tips, p=w.n_patterns)
     line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": unit, "n_gpus": a.gpus,
-        "steps": a.steps, "warmup": a.warmup, "ms_per_step": dt / a.steps * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "gpu_launches": 0,
-        "config": {"workload": a.workload, "n_taxa": w.n_tips, "patterns_per_gpu": w.n_patterns,
-                   "categories": w.n_categories, "note": "CPU port on host cores; one shard's worth of work per step"},
+        "impl": "reference", "metric": METRIC, "value": value, "unit": unit, "n_gpus": world,
+        "steps": n, "warmup": a.warmup, "ms_per_step": dt / n * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic", "gpu_launches": 0,
+        "config": config_of(a.workload, w, world),
         "cpu_baseline": {"value": value, "unit": unit, "cores": cores, "kind": "port",
-                         "sample": f"{a.steps} full evaluations of the workload (C oracle, OpenMP over pattern blocks)"},
+                         "sample": f"{n} evaluations of all {world} shard(s) of the workload, one after the other, each on "
+                                   f"{cores} threads (C oracle, OpenMP over pattern blocks)"},
         "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
     return 0
 
+class Dist:
+    """Process-group facts of this run (one process per GPU under torchrun)."""
 
-def run_b200(a):
+    def __init__(self):
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+
+
+def measure(name, precision, patterns, steps, warmup, ctx, want_e2e=True, cpu_seconds=0.0, cpu_check=True):
+    """One workload on this rank's GPU: device-resident throughput (CUDA events on the launch stream,
+    max over ranks), live kernel timing for the roofline, clocks sampled during the timed region,
+    optionally the end-to-end rate through the public model object with host tensors, and a check
+    of the result against the CPU port.  Returns the fields of a JSON line (rank 0) or None."""
+    import numpy as np
     import torch
     import torch.distributed as dist
 
     from b200phylo.treelikelihood import TreeLikelihoodModel, UnrootedTreeModel
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; the engine has no CPU fallback")
-    torch.cuda.set_device(local)
+    rank, world, local = ctx.rank, ctx.world, ctx.local
     dev = torch.device("cuda", local)
-    stdout_fd = None
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        # NCCL writes its version banner to file descriptor 1 on first use: route everything but the
-        # JSON line to stderr, so stdout carries exactly one line
-        sys.stdout.flush()
-        stdout_fd = os.dup(1)
-        os.dup2(2, 1)
-        dist.init_process_group("nccl", device_id=dev)
-    if world != a.gpus and rank == 0:
-        print(f"bench.py: --gpus {a.gpus} but WORLD_SIZE={world}; using {world}", file=sys.stderr)
-
-    w = build_workload(a.workload, a.precision, rank, a.patterns)
+    w = build_workload(name, precision, rank, patterns)
     n_br = 2 * w.n_tips - 2
     # world_size=1 on the model: each rank already holds exactly its own shard
     bl_dev = torch.tensor(w.tree.branch_lengths, dtype=torch.float64, device=dev)
     model = TreeLikelihoodModel("like", w.patterns, UnrootedTreeModel("tree", w.tree, bl_dev), w.subst_model,
-                                w.site_model, precision=a.precision, device=local, rank=0, world_size=1)
+                                w.site_model, precision=precision, device=local, rank=0, world_size=1)
     eng = model.engine
     info = eng.info()
+    dense = info["n_states"] != 4
     out = torch.zeros(1 + n_br, dtype=torch.float64, device=dev)
     stream = torch.cuda.current_stream(dev)
     # N > 1: the engine's reduction kernel is the all-reduce (NVLink peer stores, b2p_peer_*);
     # NCCL only if the peer mapping cannot be set up or B2P_NCCL_ALLREDUCE=1 asks for it
     fused = False
-    if world > 1 and info["n_states"] == 4:
+    if world > 1 and not dense:
         from b200phylo.parallel import attach_peers
         fused = attach_peers(eng)
     model.fused_allreduce = fused
@@ -235,8 +259,7 @@ def run_b200(a):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident throughput (value) + live kernel timing for the roofline
-    for _ in range(a.warmup):
+    for _ in range(warmup):
         step_device()
     eng.set_profiling(True)
     sampler = ClockSampler(local)
@@ -247,7 +270,7 @@ def run_b200(a):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t_wall0 = time.perf_counter()
     e0.record(stream)
-    for _ in range(a.steps):
+    for _ in range(steps):
         step_device()
     e1.record(stream)
     barrier()
@@ -262,107 +285,210 @@ def run_b200(a):
     ms_total = float(t.item())
     result_dev = out.cpu().numpy().copy()
 
-    # ---- end to end through the public API with host tensors
-    bl_host = torch.tensor(w.tree.branch_lengths, dtype=torch.float64).pin_memory().requires_grad_(True)
-    model.tree_model = UnrootedTreeModel("tree", w.tree, bl_host)
-    model.world_size = world  # host path: all-reduce inside the autograd function
+    e2e = None
+    if want_e2e:
+        # end to end through the public API with host tensors
+        bl_host = torch.tensor(w.tree.branch_lengths, dtype=torch.float64).pin_memory().requires_grad_(True)
+        model.tree_model = UnrootedTreeModel("tree", w.tree, bl_host)
+        model.world_size = world  # host path: all-reduce inside the autograd function
 
-    def step_host():
-        bl_host.grad = None
-        logl = model()
-        logl.backward()
-        return float(logl.detach()), bl_host.grad
+        def step_host():
+            bl_host.grad = None
+            logl = model()
+            logl.backward()
+            return float(logl.detach()), bl_host.grad
 
-    for _ in range(max(3, a.warmup // 2)):
-        step_host()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(a.steps):
-        logl_h, grad_h = step_host()
-    torch.cuda.synchronize()
-    dt = time.perf_counter() - t0
-    t = torch.tensor([dt], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dt_e2e = float(t.item())
-    import numpy as np
-    assert abs(logl_h - result_dev[0]) <= 1e-9 * abs(result_dev[0]), (logl_h, result_dev[0])
-    assert np.allclose(grad_h.numpy(), result_dev[1:], rtol=1e-9, atol=1e-9)
+        for _ in range(max(3, warmup // 2)):
+            step_host()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            logl_h, grad_h = step_host()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        t = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt_e2e = float(t.item())
+        assert abs(logl_h - result_dev[0]) <= 1e-9 * abs(result_dev[0]), (logl_h, result_dev[0])
+        assert np.allclose(grad_h.numpy(), result_dev[1:], rtol=1e-9, atol=1e-9)
+        e2e = dt_e2e
 
+    # ---- the CPU port: every rank evaluates ITS shard (cores / world threads each); summed over
+    # ranks this is the whole alignment's logL and gradient, the same quantity the GPUs' all-reduce
+    # produced — a check of the sharded sum as well as of the kernels
+    check, cpu = None, None
+    if cpu_check or cpu_seconds > 0:
+        cores = host_cores()
+        thr = max(1, cores // world)
+        if cpu_seconds > 0 and world == 1:
+            rate, used, n, secs, logl_cpu, grad_cpu = cpu_port_rate(w, cpu_seconds, n_threads=thr)
+            rate1 = cpu_port_rate(w, min(cpu_seconds, 4.0), n_threads=1, min_evals=1)[0]
+            cpu = {"value": rate, "cores": used, "kind": "port", "single_core_value": rate1,
+                   "sample": f"{n} full evaluations of the same workload in {secs:.1f} s (C oracle, OpenMP over pattern blocks)"}
+        else:
+            logl_cpu, grad_cpu = cpu_port(w, n_threads=thr)[0]()
+        ref = torch.tensor(np.concatenate([[logl_cpu], grad_cpu]), dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ref)
+        ref = ref.cpu().numpy()
+        scale = np.maximum(np.abs(ref[1:]), np.abs(ref[1:]).max() * 1e-4)
+        check = {"logl_rel_diff_vs_cpu": float(abs(result_dev[0] - ref[0]) / abs(ref[0])),
+                 "grad_rel_diff_vs_cpu": float(np.max(np.abs(result_dev[1:] - ref[1:]) / scale)),
+                 "cpu": f"C oracle on every rank's shard ({thr} threads each), summed over {world} rank(s)"}
+
+    fields = None
     if rank == 0:
         peak, peak_src = hbm_peak()
         alg = info["alg_bytes_grad"]
         k_avg_ms = k_ms / max(k_n, 1)
         achieved = alg / (k_avg_ms * 1e-3) / 1e9
-        dense = info["n_states"] != 4
         unit = UNIT_FMT.format(n=w.n_tips, p=w.n_patterns)
-        U = w.n_patterns * w.n_categories * 4 * (8 if a.precision == "float64" else 4)
-        line = {
-            "metric": METRIC, "value": world * a.steps / (ms_total * 1e-3), "unit": unit, "n_gpus": world,
-            "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_total / a.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f64" if a.precision == "float64" else "f32", "data": "synthetic",
-            "config": {"workload": a.workload, "n_taxa": w.n_tips, "patterns_per_gpu": w.n_patterns,
-                       "total_patterns": w.n_patterns * world, "categories": w.n_categories,
-                       "model": type(w.subst_model).__name__, "tree": "coalescent, seed 20261104",
-                       "l2": f"no flush: per-step working set {(2 * (w.n_tips - 1) * U * info['n_states'] // 4) / 1e6:.0f} MB of partials > 126 MB L2",
+        U = w.n_patterns * w.n_categories * 4 * (8 if precision == "float64" else 4)
+        traffic = ncu_traffic(name, precision)
+        fields = {
+            "value": world * steps / (ms_total * 1e-3), "unit": unit, "n_gpus": world, "steps": steps, "warmup": warmup,
+            "ms_per_step": ms_total / steps, "dtype": "f64" if precision == "float64" else "f32",
+            "config": config_of(name, w, world),
+            "timing": {"l2": f"no flush: per-step working set {(2 * (w.n_tips - 1) * U * info['n_states'] // 4) / 1e6:.0f} MB "
+                             "of partials > 126 MB L2" if (2 * (w.n_tips - 1) * U * info['n_states'] // 4) > 126e6 else
+                             "no flush, and the working set fits the 126 MB L2 (a latency-bound shape; the roofline fraction is not meaningful)",
                        "collective": ("fused into the reduction kernel: NVLink peer stores + flags, sum in rank order (b2p_peer_*)" if fused
-                                      else "1 NCCL all-reduce of 2N-1 doubles per step") if world > 1 else "none",
-                       "engine": {k: info[k] for k in ("warps_per_block", "cols_per_tile", "n_tiles", "grid_blocks",
-                                                        "post_rounds", "pre_rounds", "tasks_per_round", "tree_depth",
-                                                        "regs_per_thread", "smem_bytes", "pool_blocks", "copy_depth",
-                                                        "resident_reads", "block_loads", "block_stores")}},
-            "e2e": {"value": world * a.steps / dt_e2e, "unit": unit, "ms_per_step": dt_e2e / a.steps * 1e3,
-                    "h2d_bytes_per_step": n_br * 8, "d2h_bytes_per_step": (n_br + 1) * 8,
-                    "api": "TreeLikelihoodModel()(host tensor).backward() -> b2p_loglik_grad_host"},
-            "gpu_launches": 3 * a.steps,
-            "roofline": {"bound": "hbm", "kernel": "walk_kernel", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(a.workload, a.precision),
+                                      else "1 NCCL all-reduce of 2N-1 doubles per step") if world > 1 else "none"},
+            "engine": {k: info[k] for k in ("warps_per_block", "cols_per_tile", "n_tiles", "grid_blocks", "post_rounds", "pre_rounds",
+                                            "tasks_per_round", "tree_depth", "regs_per_thread", "smem_bytes", "pool_blocks",
+                                            "copy_depth", "resident_reads", "block_loads", "block_stores")},
+            "gpu_launches": 3 * steps,
+            "roofline": {"bound": "hbm", "kernel": "walk_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": traffic,
+                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture of this workload "
+                                           "(profiles/ncu_traffic.json; the builder's box, not this run)" if traffic else None,
                          "alg_bytes_per_launch": alg, "kernel_ms": k_avg_ms, "launches_timed": k_n,
-                         "share_of_step": k_ms / (ms_total * k_n / a.steps) if k_n else None, "peak_source": peak_src},
-            "clocks": clocks,
-            "logl": float(result_dev[0]),
+                         "share_of_step": k_ms / (ms_total * k_n / steps) if k_n else None, "peak_source": peak_src},
+            "clocks": clocks, "logl": float(result_dev[0]),
         }
+        if e2e is not None:
+            fields["e2e"] = {"value": world * steps / e2e, "unit": unit, "ms_per_step": e2e / steps * 1e3,
+                             "h2d_bytes_per_step": n_br * 8, "d2h_bytes_per_step": (n_br + 1) * 8,
+                             "api": "TreeLikelihoodModel()(host tensor).backward() -> b2p_loglik_grad_host"}
+        if check:
+            fields["check"] = check
+        if cpu:
+            cpu["unit"] = unit
+            fields["cpu_baseline"] = cpu
         if dense:
-            # compute-bound; algorithmic flops per evaluation
-            # (N-1) P K (4S^2+S) + (2N-2) P K (6S^2+4S), against an fp64 matmul measured in this run
-            S, N_, P_, K_ = info["n_states"], w.n_tips, w.n_patterns, w.n_categories
-            flops = (N_ - 1) * P_ * K_ * (4 * S * S + S) + (2 * N_ - 2) * P_ * K_ * (6 * S * S + 4 * S)
-            a_ = torch.randn(4096, 4096, dtype=torch.float64, device=dev)
-            best = 1e9
-            for _ in range(5):
-                m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                m0.record(); torch.matmul(a_, a_); m1.record(); torch.cuda.synchronize()
-                best = min(best, m0.elapsed_time(m1))
-            peak_tf = 2 * 4096 ** 3 / (best * 1e-3) / 1e12
-            ach_tf = flops / (k_avg_ms * 1e-3) / 1e12
-            # what the message formulation actually issues on the tensor cores (64-padded tiles): one
-            # product per internal node, two per internal non-root node, two per branch in K1
-            tiles = info["n_tiles"]
-            issued = 2 * 64 ** 3 * (tiles * ((N_ - 1) + 2 * (N_ - 2)) + 2 * (2 * N_ - 2))
-            line["dtype"] = "f64"
-            # transition, one post-order launch per level, one pre-order launch per depth, tips, reduce
-            line["gpu_launches"] = (1 + info["post_rounds"] + info["pre_rounds"] + 2) * a.steps
-            line["roofline"] = {"bound": "tensor", "kernel": "dense_post_kernel + dense_pre_kernel (one launch per tree level) + dense_tip_kernel",
-                                "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf, "traffic": None,
-                                "alg_flops_per_eval": flops, "issued_flops_per_eval": issued,
-                                "issued_tflops": issued / (k_avg_ms * 1e-3) / 1e12, "issued_frac": issued / (k_avg_ms * 1e-3) / 1e12 / peak_tf,
-                                "kernel_ms": k_avg_ms, "launches_timed": k_n,
-                                "peak_source": "fp64 torch.matmul 4096^3 (cuBLAS DGEMM), best of 5, measured in this run"}
-        if not a.no_cpu_baseline:
-            rate, cores, n, secs, logl_cpu = cpu_port_rate(w, a.cpu_seconds)
-            rate1 = rate if dense else cpu_port_rate(w, min(a.cpu_seconds, 5.0), n_threads=1, min_evals=2)[0]
-            line["cpu_baseline"] = {"value": rate, "unit": unit, "cores": cores, "kind": "port",
-                                    "sample": f"{n} full evaluations of the same workload in {secs:.1f} s "
-                                              + ("(numpy restatement, one core)" if dense else "(C oracle, OpenMP)"),
-                                    "single_core_value": rate1,
-                                    "logl_rel_diff_vs_gpu": abs(logl_cpu - result_dev[0]) / abs(logl_cpu) if world == 1 else None}
+            fields.update(dense_roofline(info, w, k_avg_ms, k_n, steps, dev))
+    model.close()
+    return fields
+
+def dense_roofline(info, w, k_avg_ms, k_n, steps, dev):
+    """SURVEY.md §8(d) config 5 is compute-bound: algorithmic flops per evaluation
+    (N-1) P K (4S^2+S) + (2N-2) P K (6S^2+4S) against an fp64 matmul measured in this run.
+    `frac` is that SURVEY-formula figure; `issued_frac` — the flops the message formulation
+    actually issues on the tensor cores (64-padded tiles) over the same peak — is the utilisation."""
+    import torch
+    S, N_, P_, K_ = info["n_states"], w.n_tips, w.n_patterns, w.n_categories
+    flops = (N_ - 1) * P_ * K_ * (4 * S * S + S) + (2 * N_ - 2) * P_ * K_ * (6 * S * S + 4 * S)
+    a_ = torch.randn(4096, 4096, dtype=torch.float64, device=dev)
+    best = 1e9
+    for _ in range(5):
+        m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        m0.record(); torch.matmul(a_, a_); m1.record(); torch.cuda.synchronize()
+        best = min(best, m0.elapsed_time(m1))
+    peak_tf = 2 * 4096 ** 3 / (best * 1e-3) / 1e12
+    ach_tf = flops / (k_avg_ms * 1e-3) / 1e12
+    # one product per internal node, two per internal non-root node, two per branch in K1
+    tiles = info["n_tiles"]
+    issued = 2 * 64 ** 3 * (tiles * ((N_ - 1) + 2 * (N_ - 2)) + 2 * (2 * N_ - 2))
+    return {
+        # transition, one post-order launch per level, one pre-order launch per depth, tips, reduce
+        "gpu_launches": (1 + info["post_rounds"] + info["pre_rounds"] + 2) * steps,
+        "roofline": {"bound": "tensor", "kernel": "dense_post_kernel + dense_pre_kernel (one launch per tree level) + dense_tip_kernel",
+                     "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf,
+                     "frac_is": "SURVEY.md §8(d) algorithmic flops / time / peak (the formulation issues fewer: see issued_frac)",
+                     "traffic": None, "alg_flops_per_eval": flops, "issued_flops_per_eval": issued,
+                     "issued_tflops": issued / (k_avg_ms * 1e-3) / 1e12, "issued_frac": issued / (k_avg_ms * 1e-3) / 1e12 / peak_tf,
+                     "kernel_ms": k_avg_ms, "launches_timed": k_n,
+                     "peak_source": "fp64 torch.matmul 4096^3 (cuBLAS DGEMM), best of 5, measured in this run"}}
+
+
+# BASELINE.json configs besides the headline one, as short runs inside the same JSON line
+SECONDARY_1GPU = [
+    ("configs[0]", "jc69_20x1000", "float64", 0),
+    ("configs[2] fp64", "hky_g4_flu", "float64", 0),
+    ("configs[2] fp32", "hky_g4_flu", "float32", 0),
+    ("north-star gate shape (5000 taxa x 10k patterns)", "gtr_g4_5000x10k", "float64", 0),
+    ("configs[4]", "codon_500x2000", "float64", 0),
+]
+
+
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+
+    ctx = Dist()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the engine has no CPU fallback")
+    torch.cuda.set_device(ctx.local)
+    dev = torch.device("cuda", ctx.local)
+    stdout_fd = None
+    if ctx.world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # NCCL writes its version banner to file descriptor 1 on first use: route everything but the
+        # JSON line to stderr, so stdout carries exactly one line
+        sys.stdout.flush()
+        stdout_fd = os.dup(1)
+        os.dup2(2, 1)
+        dist.init_process_group("nccl", device_id=dev)
+    if ctx.world != a.gpus and ctx.rank == 0:
+        print(f"bench.py: --gpus {a.gpus} but WORLD_SIZE={ctx.world}; using {ctx.world}", file=sys.stderr)
+
+    head = measure(a.workload, a.precision, a.patterns, a.steps, a.warmup, ctx, want_e2e=True,
+                   cpu_seconds=0.0 if a.no_cpu_baseline else a.cpu_seconds, cpu_check=not a.no_cpu_baseline)
+    secondary = []
+    default_run = a.workload == "jc69_1000x10k" and a.precision == "float64" and not a.patterns
+    if default_run and not a.no_secondary and os.environ.get("B2P_BENCH_SECONDARY", "1") != "0":
+        if ctx.world == 1:
+            todo = SECONDARY_1GPU
+        else:
+            # BASELINE.json configs[3]: GTR+G4, 5000 taxa x 100k patterns sharded over the N GPUs
+            # (strong scaling: 100k / N patterns per rank; 64 GB of partials per GPU at N = 2)
+            todo = [(f"configs[3]: 100k patterns over {ctx.world} GPUs", "gtr_g4_5000x100k", "float64", 100000 // ctx.world)]
+        for label, name, prec, pat in todo:
+            try:
+                r = measure(name, prec, pat, min(a.steps, 5 if name == "gtr_g4_5000x100k" else 30), 3, ctx, want_e2e=ctx.world == 1)
+            except Exception as exc:  # a secondary run must not take the headline down with it
+                r = {"error": f"{type(exc).__name__}: {exc}"} if ctx.rank == 0 else None
+            if ctx.rank == 0 and r is not None:
+                keep = {k: r[k] for k in ("value", "unit", "ms_per_step", "steps", "dtype", "config", "roofline", "clocks", "check",
+                                          "e2e", "gpu_launches", "error") if k in r}
+                if name == "gtr_g4_5000x100k" and "value" in r:
+                    keep["scaling"] = "strong"
+                    keep["whole_alignment_evals_per_s"] = r["value"] / ctx.world
+                secondary.append({"label": label, **keep})
+
+    if ctx.rank == 0:
+        line = {"metric": METRIC, "value": head["value"], "unit": head["unit"], "n_gpus": ctx.world, "steps": a.steps,
+                "warmup": a.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": head["dtype"], "data": "synthetic"}
+        for k in ("config", "timing", "engine", "e2e", "gpu_launches", "roofline", "clocks", "logl", "check"):
+            if k in head:
+                line[k] = head[k]
+        if "cpu_baseline" in head:
+            line["cpu_baseline"] = head["cpu_baseline"]
+            line["cpu_baseline"]["logl_rel_diff_vs_gpu"] = head.get("check", {}).get("logl_rel_diff_vs_cpu")
+        elif "check" in head and not a.no_cpu_baseline:
+            # N > 1: the CPU port ran once per rank on that rank's shard (the check above); its timed
+            # all-core number is the reference arm's (bench.py --impl reference), on rank 0 at N = 1 here
+            line["cpu_baseline"] = {"value": None, "unit": head["unit"], "cores": host_cores(), "kind": "port",
+                                    "sample": "not timed at N > 1 (rank 0 times it at N = 1; see --impl reference)"}
+        if secondary:
+            line["secondary"] = secondary
         if stdout_fd is not None:
             sys.stdout.flush()
             os.dup2(stdout_fd, 1)
         print(json.dumps(line), flush=True)
-    model.close()
-    if world > 1:
+    if ctx.world > 1:
         dist.destroy_process_group()
     return 0
 

@@ -240,7 +240,11 @@ class TreeLikelihoodModel:
             return self.tree_model.branch_lengths(rate=self.clock_model.rates)
         bl = self.tree_model.branch_lengths()
         if self.clock_model is not None:
-            bl = self.clock_model.rates * bl
+            rates = self.clock_model.rates
+            # the rate lives on the engine's device; host-side branch lengths move there with it
+            if rates.device != bl.device:
+                bl = bl.to(rates.device)
+            bl = rates * bl
         return bl
 
     def __call__(self, *args, **kwargs) -> torch.Tensor:

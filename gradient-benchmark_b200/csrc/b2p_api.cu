@@ -425,6 +425,25 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
     if (!getenv("B2P_NP")) n_copy = 2;
   }
   bool planned = plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, ct_force, depth, n_copy, cpt, h->wg);
+  // Copy warps: a round has about one load and one store per slot, and a warp issues a bulk copy
+  // every ~100 cycles, so few slots need few copy warps (and a freed warp is compute threads):
+  // three from eleven slots on, two from eight, else one (sweeps: profiles/README.md, round 2).
+  if (planned && !getenv("B2P_NP")) {
+    for (int np = 2; np >= 1 && h->wg.wn <= (np == 2 ? 10 : 7); --np) {
+      WalkGeometry g2;
+      if (!plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, ct_force, depth, np, cpt, g2)) break;
+      h->wg = g2;
+    }
+  }
+  // Copy depth 2 (loads issued two rounds ahead) when three frames are a small part of shared
+  // memory: the round time no longer contains the HBM latency.  With many slots the frames (matrix
+  // rows of every task) would take the block pool's room instead.
+  if (planned && !getenv("B2P_DEPTH") && 3 * h->wg.frame_bytes <= 48 * 1024) {
+    WalkGeometry g2;
+    if (plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, h->wg.ct, 2, h->wg.n_copy_warps, cpt, g2) &&
+        g2.wn == h->wg.wn)
+      h->wg = g2;
+  }
   if (!planned) {
     fail(h, B2P_ERR_UNSUPPORTED, "b2p_create: no kernel geometry fits shared memory (K=%d, threads=%d)", K, nt_force);
     return bail(B2P_ERR_UNSUPPORTED);

@@ -120,7 +120,9 @@ inline bool plan_geometry_cpt(int n_tips, int n_cols, int K, int elem, int n_sms
   if (cpt == 2 && !packed) return false;
   const int cpw = packed ? 32 : (32 / K) * K;
   const int q = K * cpt;  // tile widths are multiples of this
-  const int ct_max = 128, ct_min = (8 + q - 1) / q * q;
+  // widest tile: 144 columns (fp64) — two waves of 136-column tiles beat three of 96 at 40 000
+  // columns (profiles/README.md, round 2); B2P_CT_MAX overrides
+  const int ct_max = getenv("B2P_CT_MAX") ? std::max(q, atoi(getenv("B2P_CT_MAX"))) : 144, ct_min = (8 + q - 1) / q * q;
   int m = std::max(1, (int)((n_cols + (long long)n_sms * ct_max - 1) / ((long long)n_sms * ct_max)));
   int ct = (int)((n_cols + (long long)n_sms * m - 1) / ((long long)n_sms * m));
   ct = (ct + q - 1) / q * q;

@@ -531,6 +531,12 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
         asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         asm volatile("cp.async.bulk.wait_group 1;" ::: "memory");
       } else if (in_slot) {
+#ifdef B2P_DBG
+        if ((p.dbg >> 8) && (warp & 1)) {  // experiment: odd compute warps start their round (dbg >> 8) * 16 cycles late
+          const long long t0 = clock64();
+          while (clock64() - t0 < (long long)(p.dbg >> 8) * 16) {}
+        }
+#endif
         // descriptor and tip codes: independent reads (the codes sit at fixed per-slot positions)
         const uint4 d0 = lds_u4(frame + o_desc), d1 = lds_u4(frame + o_desc + 16);
         unsigned code_l[CPT], code_r[CPT];

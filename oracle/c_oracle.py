@@ -13,8 +13,9 @@ _lib = None
 
 
 def build(force: bool = False) -> str:
-    if force or not os.path.exists(_LIB_PATH) or (
-            os.path.getmtime(_LIB_PATH) < os.path.getmtime(os.path.join(_HERE, "phylo_oracle.c"))):
+    if force or not os.path.exists(_LIB_PATH) or any(
+            os.path.getmtime(_LIB_PATH) < os.path.getmtime(os.path.join(_HERE, src))
+            for src in ("phylo_oracle.c", "phylo_oracle_dense.c")):
         subprocess.check_call(["make", "-s", "-C", _HERE, "-B"])
     return _LIB_PATH
 
@@ -31,6 +32,10 @@ def _load():
             ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int32),
             ctypes.POINTER(ctypes.c_uint8), dp, dp, dp, dp, dp, dp, dp, dp, dp, dp, ctypes.c_int]
         lib.oracle_max_threads.restype = ctypes.c_int
+        lib.oracle_dense_loglik_grad.restype = ctypes.c_int
+        lib.oracle_dense_loglik_grad.argtypes = [
+            ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int32),
+            ctypes.POINTER(ctypes.c_uint8), dp, dp, dp, dp, dp, dp, dp, dp, dp, dp, ctypes.c_int]
         _lib = lib
     return _lib
 
@@ -63,4 +68,30 @@ def loglik_and_gradient(triples, masks, weights, bl, evec, ivec, evals, freqs, r
         _p(grad, d) if want_grad else None, int(n_threads))
     if rc != 0:
         raise RuntimeError(f"oracle_loglik_grad failed: {rc}")
+    return float(logl.value), grad
+
+
+def dense_loglik_and_gradient(triples, codes, weights, bl, evec, ivec, evals, freqs, rates,
+                              cat_weights, n_threads: int = 0, want_grad: bool = True):
+    """Any number of states (oracle/phylo_oracle_dense.c): ``codes`` uint8 [N, P] are state codes
+    (>= n_states: missing), the eigen system is [S, S] / [S]."""
+    lib = _load()
+    triples = np.ascontiguousarray(triples, dtype=np.int32)
+    codes = np.ascontiguousarray(codes, dtype=np.uint8)
+    f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+    weights, bl, evec, ivec, evals, freqs, rates, cat_weights = map(
+        f, (weights, bl, evec, ivec, evals, freqs, rates, cat_weights))
+    n, p = codes.shape
+    s = len(evals)
+    assert evec.shape == (s, s) and ivec.shape == (s, s) and freqs.shape == (s,)
+    logl = ctypes.c_double(0.0)
+    grad = np.zeros(2 * n - 2) if want_grad else None
+    d = ctypes.c_double
+    rc = lib.oracle_dense_loglik_grad(
+        s, n, p, len(rates), _p(triples, ctypes.c_int32), _p(codes, ctypes.c_uint8),
+        _p(weights, d), _p(bl, d), _p(evec, d), _p(ivec, d), _p(evals, d), _p(freqs, d),
+        _p(rates, d), _p(cat_weights, d), ctypes.byref(logl),
+        _p(grad, d) if want_grad else None, int(n_threads))
+    if rc != 0:
+        raise RuntimeError(f"oracle_dense_loglik_grad failed: {rc}")
     return float(logl.value), grad

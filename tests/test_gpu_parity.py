@@ -232,8 +232,25 @@ def test_codon_full_size_properties():
     assert rel_err(logl_w, 2.0 * logl) < 1e-14 and grad_err(grad_w, 2.0 * grad) < 1e-14
 
 
-@pytest.mark.parametrize("env", [{"B2P_NP": "2", "B2P_CW_LOADS": "14"}, {"B2P_NP": "1"}, {"B2P_NP": "4", "B2P_CW_LOADS": "3"},
-                                 {"B2P_CPT": "1"}, {"B2P_DEPTH": "2"}, {"B2P_CTAS": "2"}])
+def test_codon_full_size_against_the_c_oracle():
+    """BASELINE.json configs[4] at its full size against oracle/phylo_oracle_dense.c (the two-pass
+    algorithm with a run-time state count; ~2 s on eight cores): logL and every branch derivative."""
+    from oracle import c_oracle
+    w = make_workload("codon_500x2000")
+    eng = make_engine(w)
+    try:
+        logl, grad = eng.loglik_grad_host(w.tree.branch_lengths)
+    finally:
+        eng.close()
+    ol, og = c_oracle.dense_loglik_and_gradient(w.tree.post_triples, w.patterns.masks, w.patterns.weights,
+                                                w.tree.branch_lengths, *w.eigen_args())
+    assert rel_err(logl, ol) < TOL_LOGL_F64, (logl, ol)
+    assert grad_err(grad, og) < TOL_GRAD_F64
+
+
+@pytest.mark.parametrize("env", [{"B2P_NP": "2"}, {"B2P_NP": "1"}, {"B2P_NP": "4"}, {"B2P_NT": "640"}, {"B2P_NT": "768"},
+                                 {"B2P_CPT": "1"}, {"B2P_DEPTH": "1"}, {"B2P_DEPTH": "3"}, {"B2P_CTAS": "2"},
+                                 {"B2P_CT_MAX": "64"}, {"B2P_MAT_ROWS": "14"}, {"B2P_PLAN_SORT": "0"}])
 def test_kernel_knobs_keep_parity(env, monkeypatch):
     """The tuning knobs (copy warps, who issues the loads, columns per thread, prefetch depth)
     select different schedules of the same arithmetic: results must not move."""

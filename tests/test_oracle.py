@@ -200,3 +200,27 @@ def test_param_oracle_value_and_branch_gradient_agree_with_the_analytic_oracle()
     ol, og = oracle_c(w)
     assert rel_err(float(ll.detach()), ol) < 1e-12
     assert grad_err(bl.grad.numpy(), og) < 1e-9
+
+
+def test_dense_c_oracle_matches_numpy_oracle():
+    """oracle/phylo_oracle_dense.c (run-time state count) against the numpy restatement: the 61-state
+    codon model, and a 4-state model with rate categories against the 4-state C oracle."""
+    from oracle import c_oracle
+    w = make_workload("codon_500x2000", n_tips=24, n_patterns=50)
+    codes = w.patterns.masks.copy()
+    codes[np.random.default_rng(1).random(codes.shape) < 0.05] = 255  # missing codons
+    from b200phylo.alignment import SitePattern
+    sp = SitePattern(w.patterns.names, codes, w.patterns.weights, 61)
+    ln, gn = oracle.loglik_and_gradient(w.tree.post_triples, sp.partials(), sp.weights, w.tree.branch_lengths, *w.eigen_args())
+    lc, gc = c_oracle.dense_loglik_and_gradient(w.tree.post_triples, codes, sp.weights, w.tree.branch_lengths, *w.eigen_args())
+    assert abs(ln - lc) <= 1e-12 * abs(ln)
+    assert np.max(np.abs(gn - gc)) <= 1e-10 * np.max(np.abs(gn))
+    w = make_workload("hky_g4_flu", n_tips=40, n_patterns=150)
+    m = w.patterns.masks
+    codes = np.select([m == 1, m == 2, m == 4, m == 8], [0, 1, 2, 3], 9).astype(np.uint8)
+    l4, g4 = c_oracle.loglik_and_gradient(w.tree.post_triples, m, w.patterns.weights, w.tree.branch_lengths, *w.eigen_args())
+    ld, gd = c_oracle.dense_loglik_and_gradient(w.tree.post_triples, codes, w.patterns.weights, w.tree.branch_lengths, *w.eigen_args())
+    assert abs(l4 - ld) <= 1e-13 * abs(l4) and np.max(np.abs(g4 - gd)) <= 1e-11 * np.max(np.abs(g4))
+    lo, _ = c_oracle.dense_loglik_and_gradient(w.tree.post_triples, codes, w.patterns.weights, w.tree.branch_lengths, *w.eigen_args(),
+                                               want_grad=False, n_threads=1)
+    assert abs(lo - ld) <= 1e-13 * abs(ld)
