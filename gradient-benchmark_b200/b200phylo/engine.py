@@ -56,6 +56,17 @@ def library_path() -> str:
 
 
 _lib = None
+_host_raw_fn = None
+
+
+def _host_raw(lib):
+    """``b2p_loglik_grad_host`` through a prototype that takes plain integer addresses (no
+    ``ctypes.cast`` objects on the per-evaluation path)."""
+    global _host_raw_fn
+    if _host_raw_fn is None:
+        vp = ctypes.c_void_p
+        _host_raw_fn = ctypes.CFUNCTYPE(ctypes.c_int, vp, vp, vp, vp)(("b2p_loglik_grad_host", lib))
+    return _host_raw_fn
 
 
 def load_library():
@@ -250,9 +261,9 @@ class Engine:
     def loglik_grad_host_ptr(self, h_bl: int, h_logl: int, h_grad: Optional[int]) -> None:
         """``b2p_loglik_grad_host`` on raw host addresses (e.g. CPU ``tensor.data_ptr()``):
         [2N-2] doubles in, one double and optionally [2N-2] doubles out; synchronous."""
-        self._check(self._lib.b2p_loglik_grad_host(
-            self._h, ctypes.cast(h_bl, ctypes.POINTER(ctypes.c_double)), ctypes.cast(h_logl, ctypes.POINTER(ctypes.c_double)),
-            ctypes.cast(h_grad, ctypes.POINTER(ctypes.c_double)) if h_grad else None), "b2p_loglik_grad_host")
+        rc = _host_raw(self._lib)(self._h, h_bl, h_logl, h_grad)
+        if rc:
+            self._check(rc, "b2p_loglik_grad_host")
 
     def set_profiling(self, enabled: bool) -> None:
         self._check(self._lib.b2p_set_profiling(self._h, int(bool(enabled))), "b2p_set_profiling")

@@ -160,7 +160,7 @@ class TreeLikelihoodFunction(torch.autograd.Function):
         else:
             # host tensors: the C entry point reads the branch lengths and writes [logL, gradient]
             # straight from / into torch's own buffers (no numpy detour, one allocation)
-            bl64 = bl.to(torch.float64).contiguous()
+            bl64 = bl if (bl.dtype == torch.float64 and bl.is_contiguous()) else bl.to(torch.float64).contiguous()
             out = torch.empty(1 + (eng.n_branches if need_grad else 0), dtype=torch.float64)
             eng.loglik_grad_host_ptr(bl64.data_ptr(), out.data_ptr(), out.data_ptr() + 8 if need_grad else None)
         if model.world_size > 1 and not model.fused_allreduce:  # fused: the engine already summed over ranks
@@ -261,6 +261,13 @@ class TreeLikelihoodModel:
         return out
 
     def close(self) -> None:
+        if getattr(self, "fused_allreduce", False):
+            # a peer's reduction kernel may still be storing into this rank's receive buffer over
+            # NVLink: nobody unmaps or frees before every rank has drained its stream
+            import torch.distributed as dist
+            torch.cuda.synchronize()
+            if dist.is_available() and dist.is_initialized():
+                dist.barrier(self.group)
         self.engine.close()
 
     # ------------------------------------------------------------------- JSON

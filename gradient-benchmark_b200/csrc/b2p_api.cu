@@ -49,11 +49,14 @@ struct b2p_instance {
     int rank = -1, world = 0;
     unsigned char* own = nullptr;            // [2][world][2N-1] doubles, then [2][world] flags, ticket, err
     void* mapped[kMaxPeers] = {};            // peers' buffers opened through CUDA IPC (own entry: own)
-    unsigned long long epoch = 0;
     bool attached = false;
   } peer;
-  double* h_pin_in = nullptr;
+  double* h_pin_in = nullptr;     // pinned + mapped: the kernels of the host entry point read / write these directly
   double* h_pin_out = nullptr;
+  // the host entry point's launches, captured once per (with / without gradient) and replayed;
+  // dropped whenever anything a launch argument depends on changes (graph_drop)
+  cudaGraphExec_t graph_exec[2] = {nullptr, nullptr};
+  bool use_graph = true;
   cudaStream_t own_stream = nullptr;
   static constexpr int kProfRing = 1024;  // event pairs kept while profiling is on
   std::vector<cudaEvent_t> ev0, ev1;
@@ -90,6 +93,11 @@ static int fail(const b2p_instance* h, int code, const char* fmt, ...) {
   va_end(ap);
   if (h) h->err = buf; else g_create_error = buf;
   return code;
+}
+
+static void graph_drop(b2p_instance* h) {
+  for (cudaGraphExec_t& g : h->graph_exec)
+    if (g) { cudaGraphExecDestroy(g); g = nullptr; }
 }
 
 #define CU(call)                                                                       \
@@ -338,6 +346,7 @@ static void peer_release(b2p_instance* h);
 int b2p_destroy(b2p_instance* h) {
   if (!h) return B2P_OK;
   cudaSetDevice(h->cfg.device);
+  graph_drop(h);
   peer_release(h);
   cudaFree(h->d_records); cudaFree(h->d_mat_dst);
   cudaFree(h->d_tips); cudaFree(h->d_tips_raw); cudaFree(h->d_tip_order); cudaFree(h->d_weights); cudaFree(h->d_msg); cudaFree(h->d_pre);
@@ -395,6 +404,7 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   if (!h) return fail(nullptr, B2P_ERR_ALLOC, "b2p_create: out of host memory");
   h->cfg = *cfg;
   h->n_sms = prop.multiProcessorCount;
+  h->use_graph = !(getenv("B2P_NO_GRAPH") && atoi(getenv("B2P_NO_GRAPH")));
   const int K = cfg->n_categories, N = cfg->n_tips, P = cfg->n_patterns;
   const size_t es = elem_size(h);
   const size_t n_cols = (size_t)P * K;
@@ -530,12 +540,11 @@ static size_t peer_recv_bytes(const b2p_instance* h, int world) {
   return sizeof(double) * 2 * (size_t)world * (2 * (size_t)h->cfg.n_tips - 1);
 }
 
-// Arguments of the fused reduction + all-reduce for the next evaluation (advances the epoch).
+// Arguments of the fused reduction + all-reduce (the epoch counter lives on the device: graph-safe).
 static PeerArgs peer_args(b2p_instance* h) {
   PeerArgs pa{};
   b2p_instance::Peer& pr = h->peer;
   pa.rank = pr.rank; pa.world = pr.world; pa.n_out = 2 * h->cfg.n_tips - 1;
-  pa.epoch = ++pr.epoch;
   const size_t recv = peer_recv_bytes(h, pr.world);
   for (int r = 0; r < pr.world; ++r) {
     unsigned char* base = (unsigned char*)pr.mapped[r];
@@ -545,6 +554,7 @@ static PeerArgs peer_args(b2p_instance* h) {
   unsigned char* tail = pr.own + recv + sizeof(unsigned long long) * 2 * pr.world;
   pa.ticket = (unsigned*)tail;
   pa.err = (unsigned*)(tail + 8);
+  pa.epoch = (unsigned long long*)(tail + 16);
   return pa;
 }
 
@@ -632,6 +642,7 @@ int b2p_get_info(const b2p_instance* h, b2p_info* o) {
 }
 
 int b2p_set_topology(b2p_instance* h, const int32_t* h_triples) {
+  if (h) graph_drop(h);
   if (!h || !h_triples) return h ? fail(h, B2P_ERR_ARG, "b2p_set_topology: null triples") : B2P_ERR_ARG;
   if (h->dense) return dense_set_topology(h, h_triples);
   WalkPlan plan;
@@ -668,6 +679,7 @@ int b2p_set_topology(b2p_instance* h, const int32_t* h_triples) {
 }
 
 int b2p_set_tip_states(b2p_instance* h, const uint8_t* h_masks) {
+  if (h) graph_drop(h);
   if (!h || !h_masks) return h ? fail(h, B2P_ERR_ARG, "b2p_set_tip_states: null masks") : B2P_ERR_ARG;
   if (h->dense) return dense_set_tips(h, h_masks);  // bytes are state codes (>= n_states: missing)
   const int N = h->cfg.n_tips, P = h->cfg.n_patterns;
@@ -682,6 +694,7 @@ int b2p_set_tip_states(b2p_instance* h, const uint8_t* h_masks) {
 }
 
 int b2p_set_pattern_weights(b2p_instance* h, const double* h_weights) {
+  if (h) graph_drop(h);
   if (!h || !h_weights) return h ? fail(h, B2P_ERR_ARG, "b2p_set_pattern_weights: null") : B2P_ERR_ARG;
   if (h->dense) return dense_set_weights(h, h_weights);
   CU(cudaSetDevice(h->cfg.device));
@@ -692,6 +705,7 @@ int b2p_set_pattern_weights(b2p_instance* h, const double* h_weights) {
 
 int b2p_set_eigen(b2p_instance* h, const double* evec, const double* ivec, const double* evals,
                   const double* freqs) {
+  if (h) graph_drop(h);
   if (!h || !evec || !ivec || !evals || !freqs)
     return h ? fail(h, B2P_ERR_ARG, "b2p_set_eigen: null argument") : B2P_ERR_ARG;
   if (h->dense) return dense_set_eigen(h, evec, ivec, evals, freqs);
@@ -710,6 +724,7 @@ int b2p_set_eigen(b2p_instance* h, const double* evec, const double* ivec, const
 }
 
 int b2p_set_categories(b2p_instance* h, const double* rates, const double* weights) {
+  if (h) graph_drop(h);
   if (!h || !rates || !weights)
     return h ? fail(h, B2P_ERR_ARG, "b2p_set_categories: null argument") : B2P_ERR_ARG;
   for (int k = 0; k < h->cfg.n_categories; ++k) {
@@ -721,6 +736,7 @@ int b2p_set_categories(b2p_instance* h, const double* rates, const double* weigh
 }
 
 int b2p_set_gradient_operator(b2p_instance* h, const double* h_op, const double* h_scale) {
+  if (h) graph_drop(h);
   if (!h) return B2P_ERR_ARG;
   if (h->dense) return fail(h, B2P_ERR_UNSUPPORTED, "b2p_set_gradient_operator: 4-state instances only");
   if (!h_op) { h->grad_op_set = false; return B2P_OK; }
@@ -729,6 +745,8 @@ int b2p_set_gradient_operator(b2p_instance* h, const double* h_op, const double*
   h->grad_op_set = true;
   return B2P_OK;
 }
+
+int b2p_peer_status(b2p_instance* h, int32_t* attached, int32_t* error_word);
 
 static int eval_common(b2p_instance* h, const double* d_bl, double* d_logl, double* d_grad,
                        void* stream) {
@@ -759,17 +777,44 @@ int b2p_loglik_grad_host(b2p_instance* h, const double* h_bl, double* h_logl, do
   const size_t n_br = 2 * (size_t)h->cfg.n_tips - 2;
   CU(cudaSetDevice(h->cfg.device));
   memcpy(h->h_pin_in, h_bl, sizeof(double) * n_br);
-  CU(cudaMemcpyAsync(h->d_bl_stage, h->h_pin_in, sizeof(double) * n_br, cudaMemcpyHostToDevice,
-                     h->own_stream));
-  rc = eval_common(h, h->d_bl_stage, h->d_out_stage, h_grad ? h->d_out_stage + 1 : nullptr,
-                   h->own_stream);
-  if (rc) return rc;
-  const size_t n_out = h_grad ? n_br + 1 : 1;
-  CU(cudaMemcpyAsync(h->h_pin_out, h->d_out_stage, sizeof(double) * n_out, cudaMemcpyDeviceToHost,
-                     h->own_stream));
+  // No copy engine on this path: the pinned staging buffers are mapped into the device's address
+  // space (unified addressing), K1 reads the 2N-2 branch lengths from host memory and the
+  // reduction kernel writes logL and the gradient straight back — two PCIe round trips of 16 KB
+  // instead of two copy-engine launches with their own latency.  The three launches are captured
+  // once into a CUDA graph and replayed with one call (4-state path; not while profiling or tracing).
+  const int gi = h_grad ? 1 : 0;
+  double* out = h->h_pin_out;
+  const bool graph = h->use_graph && !h->dense && !h->profiling && !h->d_trace;
+  if (graph) {
+    if (!h->graph_exec[gi]) {
+      cudaGraph_t g = nullptr;
+      CU(cudaStreamBeginCapture(h->own_stream, cudaStreamCaptureModeThreadLocal));
+      rc = eval_common(h, h->h_pin_in, out, h_grad ? out + 1 : nullptr, h->own_stream);
+      cudaError_t e = cudaStreamEndCapture(h->own_stream, &g);
+      if (rc) { if (g) cudaGraphDestroy(g); return rc; }
+      if (e != cudaSuccess) return fail(h, B2P_ERR_CUDA, "graph capture: %s", cudaGetErrorString(e));
+      e = cudaGraphInstantiate(&h->graph_exec[gi], g, 0);
+      cudaGraphDestroy(g);
+      if (e != cudaSuccess) { h->graph_exec[gi] = nullptr; return fail(h, B2P_ERR_CUDA, "graph instantiate: %s", cudaGetErrorString(e)); }
+    }
+    CU(cudaGraphLaunch(h->graph_exec[gi], h->own_stream));
+  } else if (h->dense) {
+    CU(cudaMemcpyAsync(h->d_bl_stage, h->h_pin_in, sizeof(double) * n_br, cudaMemcpyHostToDevice, h->own_stream));
+    rc = eval_common(h, h->d_bl_stage, h->d_out_stage, h_grad ? h->d_out_stage + 1 : nullptr, h->own_stream);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(out, h->d_out_stage, sizeof(double) * (h_grad ? n_br + 1 : 1), cudaMemcpyDeviceToHost, h->own_stream));
+  } else {
+    rc = eval_common(h, h->h_pin_in, out, h_grad ? out + 1 : nullptr, h->own_stream);
+    if (rc) return rc;
+  }
   CU(cudaStreamSynchronize(h->own_stream));
-  *h_logl = h->h_pin_out[0];
-  if (h_grad) memcpy(h_grad, h->h_pin_out + 1, sizeof(double) * n_br);
+  *h_logl = out[0];
+  if (h_grad) memcpy(h_grad, out + 1, sizeof(double) * n_br);
+  if (h->peer.attached && *h_logl != *h_logl) {  // NaN: the exchange kernel poisons its results when a peer timed out
+    int32_t err = 0;
+    b2p_peer_status(h, nullptr, &err);
+    if (err) return fail(h, B2P_ERR_CUDA, "b2p_loglik_grad_host: rank %d did not deliver its sums within the time limit (fused all-reduce)", err - 1);
+  }
   if (h->d_trace && h_grad) {
     const int R = h->plan.rounds;
     std::vector<long long> tr(16 * (size_t)R);
@@ -794,7 +839,7 @@ int b2p_peer_export(b2p_instance* h, int32_t world, void* h_handle_out) {
   if (h->peer.own) return fail(h, B2P_ERR_ARG, "b2p_peer_export: already exported");
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
   CU(cudaSetDevice(h->cfg.device));
-  const size_t bytes = peer_recv_bytes(h, world) + sizeof(unsigned long long) * 2 * world + 16;
+  const size_t bytes = peer_recv_bytes(h, world) + sizeof(unsigned long long) * 2 * world + 32;  // + ticket, err, epoch
   void* p = nullptr;
   if (cudaMalloc(&p, bytes) != cudaSuccess) return fail(h, B2P_ERR_ALLOC, "b2p_peer_export: cudaMalloc(%zu) failed", bytes);
   h->peer.own = (unsigned char*)p;
@@ -830,6 +875,7 @@ int b2p_peer_attach(b2p_instance* h, int32_t rank, int32_t world, const void* h_
   }
   pr.rank = rank;
   pr.attached = true;
+  graph_drop(h);
   return B2P_OK;
 }
 
@@ -858,6 +904,7 @@ static void peer_release(b2p_instance* h) {
 }
 
 int b2p_set_profiling(b2p_instance* h, int enabled) {
+  if (h) graph_drop(h);
   if (!h) return B2P_ERR_ARG;
   CU(cudaSetDevice(h->cfg.device));
   if (enabled && h->ev0.empty()) {

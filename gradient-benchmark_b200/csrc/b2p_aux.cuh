@@ -117,12 +117,16 @@ __global__ void __launch_bounds__(512) reduce_kernel(const double* __restrict__ 
 // the `world` slots in rank order — the same order on every rank, so all ranks get the same
 // bits.  Two slot sets alternate by epoch: a rank can be at most one evaluation ahead of a
 // peer (it needs that peer's flag to finish), so the set being written is never the set
-// still being read.
+// still being read.  A peer whose flag does not arrive within ~30 s is fatal: logL and the
+// gradient come back NaN and the error word is set (b2p_peer_status; b2p_loglik_grad_host
+// returns B2P_ERR_CUDA).
 constexpr int kMaxPeers = 8;
 
 struct PeerArgs {
   int rank, world, n_out;          // n_out = 2N-1 (slot stride; evaluation-only calls use element 0)
-  unsigned long long epoch;        // same on every rank: evaluations are issued in lock step
+  unsigned long long* epoch;       // local device counter: evaluations done so far.  Kept on the device
+                                   // (the kernel advances it) so that a launch replayed from a CUDA graph
+                                   // still sees the right epoch; the same on every rank: lock step
   double* recv[kMaxPeers];         // [2][world][n_out] on each rank
   unsigned long long* flags[kMaxPeers];  // [2][world] on each rank
   unsigned* ticket;                // local CTA completion counter
@@ -135,9 +139,14 @@ __global__ void __launch_bounds__(512) reduce_exchange_kernel(const double* __re
                                                               double* __restrict__ logl, const PeerArgs pa) {
   __shared__ double sh[16][33];
   __shared__ unsigned last;
+  __shared__ int timed_out;
   const int x = threadIdx.x & 31, y = threadIdx.x >> 5;
-  const int set = (int)(pa.epoch & 1ull);
+  // every CTA reads the counter before it takes its ticket; the last CTA advances it after all
+  // tickets are taken, so no CTA of this launch can see the new value
+  const unsigned long long epoch = *(volatile unsigned long long*)pa.epoch + 1ull;
+  const int set = (int)(epoch & 1ull);
   const size_t slot = ((size_t)set * pa.world + pa.rank) * pa.n_out;
+  if (threadIdx.x == 0) timed_out = 0;
   if (blockIdx.x == gridDim.x - 1) {  // log-likelihood
     double s = 0.0;
     for (int g = threadIdx.x; g < n_parts; g += 512) s += lpart[g];
@@ -171,22 +180,28 @@ __global__ void __launch_bounds__(512) reduce_exchange_kernel(const double* __re
   __threadfence_system();
   if (threadIdx.x < pa.world) {
     volatile unsigned long long* out = pa.flags[threadIdx.x] + (size_t)set * pa.world + pa.rank;
-    *out = pa.epoch;
+    *out = epoch;
     volatile unsigned long long* in = pa.flags[pa.rank] + (size_t)set * pa.world + threadIdx.x;
     const long long t0 = clock64();
-    while (*in < pa.epoch) {
-      if (clock64() - t0 > 8000000000ll) { *pa.err = 1u + threadIdx.x; break; }  // ~4 s: report, do not hang
+    while (*in < epoch) {
+      // ~30 s (a peer that stalls longer is taken for dead): FATAL — the results below become NaN
+      // and the error word is set, so no caller can mistake a partial sum for an evaluation
+      if (clock64() - t0 > 60000000000ll) { *pa.err = 1u + threadIdx.x; timed_out = 1; break; }
     }
   }
   __syncthreads();
   __threadfence_system();
   const double* mine = pa.recv[pa.rank] + (size_t)set * pa.world * pa.n_out;
+  const double poison = timed_out ? __longlong_as_double(0x7ff8000000000000ll) : 0.0;
   for (int i = threadIdx.x; i < 1 + n_branches; i += 512) {
-    double t = 0.0;
+    double t = poison;
     for (int r = 0; r < pa.world; ++r) t += __ldcg(mine + (size_t)r * pa.n_out + i);
     if (i == 0) *logl = t; else grad[i - 1] = t;
   }
-  if (threadIdx.x == 0) *pa.ticket = 0u;
+  if (threadIdx.x == 0) {
+    *pa.ticket = 0u;
+    *(volatile unsigned long long*)pa.epoch = epoch;
+  }
 }
 
 }  // namespace b2p
