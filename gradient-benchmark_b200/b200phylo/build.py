@@ -12,7 +12,7 @@ import sys
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _CSRC = os.path.normpath(os.path.join(_HERE, "..", "csrc"))
 _OUT = os.path.join(_HERE, "libb200phylo.so")
-_SOURCES = ["b2p_api.cu", "b2p_timetree.cu"]
+_SOURCES = ["b2p_api.cu", "b2p_timetree.cu", "b2p_noalloc.cu"]
 _DEPS = sorted(f for f in os.listdir(_CSRC) if f.endswith((".cu", ".cuh", ".h"))) + [
     os.path.join("..", "..", "include", "b200phylo.h")]
 

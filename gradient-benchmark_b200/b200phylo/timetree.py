@@ -32,6 +32,8 @@ TIMETREE_SYMBOLS = (
     "b2p_timetree_branch_lengths", "b2p_timetree_branch_lengths_vjp", "b2p_coalescent_constant",
     "b2p_joint_density_grad",
 )
+# the no-allocation entry point (csrc/b2p_noalloc.cu; no counterpart in the reference)
+NOALLOC_SYMBOLS = ("b2p_coalescent_constant_noalloc", "b2p_noalloc_max_tips", "b2p_noalloc_last_error")
 
 _declared = False
 

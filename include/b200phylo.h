@@ -255,6 +255,30 @@ int b2p_joint_density_grad(b2p_instance* like, b2p_timetree* t, const double* d_
                            double* d_out, double* d_grad_params, double* d_grad_rate,
                            double* d_grad_theta, void* cuda_stream);
 
+/* ------------------------------------------------------------------ no-allocation entry point
+ * NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid
+ * it).  The constant-population coalescent density of b2p_coalescent_constant without a set-up
+ * object: the caller passes inputs and outputs only, and the kernel's scratch (per-CTA partial
+ * sums + a completion ticket, 8.25 KB) is a file-scope `static __device__` array that every GPU
+ * which loads the library holds until the process exits (csrc/b2p_noalloc.cu).  The call makes no
+ * cudaMalloc / cudaFree and calls no allocating library routine; it enqueues one 4-byte memset and
+ * one kernel on `cuda_stream` and does not synchronise.
+ *   device            CUDA device the pointers live on
+ *   n_tips            2 .. B2P_NOALLOC_MAX_TIPS (larger: B2P_ERR_UNSUPPORTED with a message)
+ *   d_tip_heights [N] tip heights, d_heights [N-1] internal node heights, d_theta [1]
+ *   d_logp [1], d_grad_heights [N-1], d_grad_theta [1]: outputs, each may be NULL (not all)
+ * Every call on a device shares the one scratch array: calls that OVERLAP on the GPU (different
+ * streams without an ordering between them) race — serialise them. */
+#define B2P_NOALLOC_MAX_TIPS 16384
+int b2p_coalescent_constant_noalloc(int32_t device, int32_t n_tips, const double* d_tip_heights,
+                                    const double* d_heights, const double* d_theta, double* d_logp,
+                                    double* d_grad_heights, double* d_grad_theta, void* cuda_stream);
+/* B2P_NOALLOC_MAX_TIPS as the loaded library was built with. */
+int32_t b2p_noalloc_max_tips(void);
+/* Message of the calling thread's last failed b2p_coalescent_constant_noalloc call. */
+const char* b2p_noalloc_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -32,8 +32,8 @@ def test_library_builds_loads_and_exports_every_declared_symbol():
     lib = engine.load_library()
     for s in _declared_symbols():
         assert hasattr(lib, s), f"{s} declared in include/b200phylo.h but not exported"
-    from b200phylo.timetree import TIMETREE_SYMBOLS
-    assert set(_declared_symbols()) == set(engine.EXPORTED_SYMBOLS) | set(TIMETREE_SYMBOLS)
+    from b200phylo.timetree import NOALLOC_SYMBOLS, TIMETREE_SYMBOLS
+    assert set(_declared_symbols()) == set(engine.EXPORTED_SYMBOLS) | set(TIMETREE_SYMBOLS) | set(NOALLOC_SYMBOLS)
     assert lib.b2p_version() >= 1
 
 
