@@ -47,7 +47,7 @@ struct b2p_instance {
   // multi-GPU: peer-mapped receive buffers of the fused reduce + all-reduce (b2p_peer_*)
   struct Peer {
     int rank = -1, world = 0;
-    unsigned char* own = nullptr;            // [2][world][2N-1] doubles, then [2][world] flags, ticket, err
+    unsigned char* own = nullptr;            // [2][world][2N-1] doubles, then [2][world][slices] flags, ticket, err, epoch
     void* mapped[kMaxPeers] = {};            // peers' buffers opened through CUDA IPC (own entry: own)
     bool attached = false;
   } peer;
@@ -536,6 +536,8 @@ static void fill_walk_params(const b2p_instance* h, bool grad, WalkParams<T>& p)
   }
 }
 
+static int peer_slices(const b2p_instance* h) { return 1 + (2 * h->cfg.n_tips - 2 + 31) / 32; }
+static size_t peer_flag_bytes(const b2p_instance* h, int world) { return sizeof(unsigned long long) * 2 * (size_t)world * peer_slices(h); }
 static size_t peer_recv_bytes(const b2p_instance* h, int world) {
   return sizeof(double) * 2 * (size_t)world * (2 * (size_t)h->cfg.n_tips - 1);
 }
@@ -551,7 +553,8 @@ static PeerArgs peer_args(b2p_instance* h) {
     pa.recv[r] = (double*)base;
     pa.flags[r] = (unsigned long long*)(base + recv);
   }
-  unsigned char* tail = pr.own + recv + sizeof(unsigned long long) * 2 * pr.world;
+  unsigned char* tail = pr.own + recv + peer_flag_bytes(h, pr.world);
+  pa.n_slices = peer_slices(h);
   pa.ticket = (unsigned*)tail;
   pa.err = (unsigned*)(tail + 8);
   pa.epoch = (unsigned long long*)(tail + 16);
@@ -839,7 +842,7 @@ int b2p_peer_export(b2p_instance* h, int32_t world, void* h_handle_out) {
   if (h->peer.own) return fail(h, B2P_ERR_ARG, "b2p_peer_export: already exported");
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
   CU(cudaSetDevice(h->cfg.device));
-  const size_t bytes = peer_recv_bytes(h, world) + sizeof(unsigned long long) * 2 * world + 32;  // + ticket, err, epoch
+  const size_t bytes = peer_recv_bytes(h, world) + peer_flag_bytes(h, world) + 32;  // + ticket, err, epoch
   void* p = nullptr;
   if (cudaMalloc(&p, bytes) != cudaSuccess) return fail(h, B2P_ERR_ALLOC, "b2p_peer_export: cudaMalloc(%zu) failed", bytes);
   h->peer.own = (unsigned char*)p;
@@ -887,7 +890,7 @@ int b2p_peer_status(b2p_instance* h, int32_t* attached, int32_t* error_word) {
     if (h->peer.own) {
       CU(cudaSetDevice(h->cfg.device));
       unsigned e = 0;
-      const size_t off = peer_recv_bytes(h, h->peer.world) + sizeof(unsigned long long) * 2 * h->peer.world + 8;
+      const size_t off = peer_recv_bytes(h, h->peer.world) + peer_flag_bytes(h, h->peer.world) + 8;
       CU(cudaMemcpy(&e, h->peer.own + off, sizeof e, cudaMemcpyDeviceToHost));
       *error_word = (int32_t)e;
     }

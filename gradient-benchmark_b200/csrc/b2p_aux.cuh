@@ -111,95 +111,92 @@ __global__ void __launch_bounds__(512) reduce_kernel(const double* __restrict__ 
 // Multi-GPU: every rank holds a pattern shard, the results
 // [logL, g_0 .. g_{2N-3}] must be summed over ranks.  Instead of a reduction kernel followed
 // by a library all-reduce (two launches + a ~30 us latency-bound collective for 16 KB), the
-// reduction kernel itself is the collective: each CTA stores its 32 sums straight into slot
-// `rank` of EVERY peer's receive buffer over NVLink (peer-mapped memory, plain stores), the
-// last CTA to finish publishes a flag on every peer, waits for every peer's flag, and adds
-// the `world` slots in rank order — the same order on every rank, so all ranks get the same
-// bits.  Two slot sets alternate by epoch: a rank can be at most one evaluation ahead of a
-// peer (it needs that peer's flag to finish), so the set being written is never the set
-// still being read.  A peer whose flag does not arrive within ~30 s is fatal: logL and the
-// gradient come back NaN and the error word is set (b2p_peer_status; b2p_loglik_grad_host
-// returns B2P_ERR_CUDA).
+// reduction kernel itself is the collective, slice by slice: CTA c sums its slice (32 branches;
+// slice 0 is the log-likelihood) over the rank's per-CTA partials, stores the 32 sums straight
+// into slot `rank` of EVERY peer's receive buffer over NVLink (peer-mapped memory, plain
+// stores), publishes a per-slice flag on every peer, waits for the peers' flags OF THE SAME
+// SLICE, and adds the `world` slots in rank order — the same order on every rank, so all ranks
+// get the same bits.  No rank waits for a peer's last CTA, and no CTA does more than 32 x world
+// additions.  Every CTA publishes before it waits, so the waits cannot deadlock whatever the
+// order in which the CTAs of the two grids become resident.  Two slot sets alternate by epoch: a
+// rank can be at most one evaluation ahead of a peer (it needs that peer's flags to finish), so
+// the set being written is never the set still being read.  A peer whose flag does not arrive
+// within ~30 s is fatal: the slice comes back NaN and the error word is set (b2p_peer_status;
+// b2p_loglik_grad_host returns B2P_ERR_CUDA).
 constexpr int kMaxPeers = 8;
 
 struct PeerArgs {
   int rank, world, n_out;          // n_out = 2N-1 (slot stride; evaluation-only calls use element 0)
+  int n_slices;                    // flag stride: 1 + ceil((2N-2) / 32)
   unsigned long long* epoch;       // local device counter: evaluations done so far.  Kept on the device
                                    // (the kernel advances it) so that a launch replayed from a CUDA graph
                                    // still sees the right epoch; the same on every rank: lock step
   double* recv[kMaxPeers];         // [2][world][n_out] on each rank
-  unsigned long long* flags[kMaxPeers];  // [2][world] on each rank
-  unsigned* ticket;                // local CTA completion counter
+  unsigned long long* flags[kMaxPeers];  // [2][world][n_slices] on each rank
+  unsigned* ticket;                // local CTA counter (advances the epoch once every CTA has read it)
   unsigned* err;                   // local: set when a peer's flag did not arrive in time
 };
 
+// grid: 1 + ceil(n_branches / 32) CTAs; CTA 0 = log-likelihood, CTA c >= 1 = branches 32 (c-1) ..
 __global__ void __launch_bounds__(512) reduce_exchange_kernel(const double* __restrict__ gpart,
                                                               const double* __restrict__ lpart, int n_parts,
                                                               int n_branches, double* __restrict__ grad,
                                                               double* __restrict__ logl, const PeerArgs pa) {
   __shared__ double sh[16][33];
-  __shared__ unsigned last;
   __shared__ int timed_out;
   const int x = threadIdx.x & 31, y = threadIdx.x >> 5;
-  // every CTA reads the counter before it takes its ticket; the last CTA advances it after all
-  // tickets are taken, so no CTA of this launch can see the new value
+  // every CTA reads the counter before it takes its ticket; the CTA that takes the last ticket
+  // advances it, so no CTA of this launch can see the new value
   const unsigned long long epoch = *(volatile unsigned long long*)pa.epoch + 1ull;
   const int set = (int)(epoch & 1ull);
   const size_t slot = ((size_t)set * pa.world + pa.rank) * pa.n_out;
   if (threadIdx.x == 0) timed_out = 0;
-  if (blockIdx.x == gridDim.x - 1) {  // log-likelihood
-    double s = 0.0;
+  const int c = blockIdx.x;
+  const int i = c == 0 ? 0 : 1 + (c - 1) * 32 + x;  // element of [logL, g_0 ..] this lane owns (y == 0 lanes)
+  const bool mine = y == 0 && (c == 0 ? x == 0 : i < 1 + n_branches);
+  double s = 0.0;
+  if (c == 0) {
     for (int g = threadIdx.x; g < n_parts; g += 512) s += lpart[g];
     s = warp_sum(s);
     if (x == 0) sh[y][0] = s;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      double t = 0.0;
-      for (int i = 0; i < 16; ++i) t += sh[i][0];
-      for (int r = 0; r < pa.world; ++r) pa.recv[r][slot] = t;
-    }
   } else {
-    const int b = blockIdx.x * 32 + x;
-    double s = 0.0;
+    const int b = i - 1;
     if (b < n_branches)
       for (int g = y; g < n_parts; g += 16) s += gpart[(size_t)g * n_branches + b];
     sh[y][x] = s;
-    __syncthreads();
-    if (y == 0 && b < n_branches) {
-      double t = 0.0;
-#pragma unroll
-      for (int i = 0; i < 16; ++i) t += sh[i][x];
-      for (int r = 0; r < pa.world; ++r) pa.recv[r][slot + 1 + b] = t;
-    }
   }
-  __threadfence_system();
   __syncthreads();
-  if (threadIdx.x == 0) last = atomicAdd(pa.ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
+  if (mine) {
+    double t = 0.0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) t += sh[k][c == 0 ? 0 : x];
+    for (int r = 0; r < pa.world; ++r) pa.recv[r][slot + i] = t;
+    __threadfence_system();  // this lane's stores are visible system-wide before the flag below
+  }
   __syncthreads();
-  if (!last) return;
-  __threadfence_system();
   if (threadIdx.x < pa.world) {
-    volatile unsigned long long* out = pa.flags[threadIdx.x] + (size_t)set * pa.world + pa.rank;
+    const size_t f = (size_t)set * pa.world;
+    volatile unsigned long long* out = pa.flags[threadIdx.x] + (f + pa.rank) * pa.n_slices + c;
     *out = epoch;
-    volatile unsigned long long* in = pa.flags[pa.rank] + (size_t)set * pa.world + threadIdx.x;
+    volatile unsigned long long* in = pa.flags[pa.rank] + (f + threadIdx.x) * pa.n_slices + c;
     const long long t0 = clock64();
     while (*in < epoch) {
       // ~30 s (a peer that stalls longer is taken for dead): FATAL — the results below become NaN
       // and the error word is set, so no caller can mistake a partial sum for an evaluation
       if (clock64() - t0 > 60000000000ll) { *pa.err = 1u + threadIdx.x; timed_out = 1; break; }
     }
+    __threadfence_system();
   }
   __syncthreads();
-  __threadfence_system();
-  const double* mine = pa.recv[pa.rank] + (size_t)set * pa.world * pa.n_out;
-  const double poison = timed_out ? __longlong_as_double(0x7ff8000000000000ll) : 0.0;
-  for (int i = threadIdx.x; i < 1 + n_branches; i += 512) {
-    double t = poison;
-    for (int r = 0; r < pa.world; ++r) t += __ldcg(mine + (size_t)r * pa.n_out + i);
+  if (mine) {
+    const double* own = pa.recv[pa.rank] + (size_t)set * pa.world * pa.n_out;
+    double t = timed_out ? __longlong_as_double(0x7ff8000000000000ll) : 0.0;
+    for (int r = 0; r < pa.world; ++r) t += __ldcg(own + (size_t)r * pa.n_out + i);
     if (i == 0) *logl = t; else grad[i - 1] = t;
   }
-  if (threadIdx.x == 0) {
+  if (threadIdx.x == 0 && atomicAdd(pa.ticket, 1u) == gridDim.x - 1) {
     *pa.ticket = 0u;
+    __threadfence();
     *(volatile unsigned long long*)pa.epoch = epoch;
   }
 }

@@ -24,54 +24,50 @@ template <> struct Scale<float> {
 
 // ---- reductions over the K category lanes of one pattern -----------------------
 // Lanes of a pattern are adjacent and K-aligned (tile origin is a multiple of K).  Every
-// shuffle names only the K lanes of its own pattern (gmask), so the threads of one task can
-// run them while the rest of the warp — another task, or idle lanes — is somewhere else.
-template <int K>
-__device__ __forceinline__ unsigned group_mask(int lane, int kk) {
-  if (K == 1) return 1u << lane;
-  if (K == 32) return 0xffffffffu;
-  if (K == 2 || K == 4 || K == 8 || K == 16) return ((1u << K) - 1u) << (lane & ~(K - 1));
-  return ((1u << kk) - 1u) << (lane - lane % kk);
-}
+// shuffle is a FULL-WARP shuffle: all 32 lanes of a warp must reach it (the traversal kernel
+// keeps its K != 1 control flow warp-uniform around these calls; lanes without work take part
+// with neutral values).  A per-group member mask would let idle lanes skip, but a shuffle whose
+// mask differs from lane to lane is serialised by the compiler over the distinct mask values
+// (a MATCH.ANY loop: eight trips per shuffle at K = 4) — measured 15 % of the K = 4 kernels.
 template <int K, typename T>
-__device__ __forceinline__ T group_sum(T v, unsigned gmask, int lane, int kk) {
+__device__ __forceinline__ T group_sum(T v, int lane, int kk) {
   if (K == 1) return v;
   if (K == 2 || K == 4 || K == 8 || K == 16 || K == 32) {
 #pragma unroll
-    for (int o = 1; o < K; o <<= 1) v += __shfl_xor_sync(gmask, v, o);
+    for (int o = 1; o < K; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
   }
   // generic K (runtime kk): gather from the group's lanes
   const int base = lane - lane % kk;
   T s = (T)0;
-  for (int j = 0; j < kk; ++j) s += __shfl_sync(gmask, v, base + j);
+  for (int j = 0; j < kk; ++j) s += __shfl_sync(0xffffffffu, v, (base + j) & 31);
   return s;
 }
 template <int K, typename T>
-__device__ __forceinline__ T group_max(T v, unsigned gmask, int lane, int kk) {
+__device__ __forceinline__ T group_max(T v, int lane, int kk) {
   if (K == 1) return v;
   if (K == 2 || K == 4 || K == 8 || K == 16 || K == 32) {
 #pragma unroll
-    for (int o = 1; o < K; o <<= 1) v = fmax(v, __shfl_xor_sync(gmask, v, o));
+    for (int o = 1; o < K; o <<= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
   }
   const int base = lane - lane % kk;
   T s = v;
-  for (int j = 0; j < kk; ++j) s = fmax(s, __shfl_sync(gmask, v, base + j));
+  for (int j = 0; j < kk; ++j) s = fmax(s, __shfl_sync(0xffffffffu, v, (base + j) & 31));
   return s;
 }
 
 template <int K>
-__device__ __forceinline__ int group_max_int(int v, unsigned gmask, int lane, int kk) {
+__device__ __forceinline__ int group_max_int(int v, int lane, int kk) {
   if (K == 1) return v;
   if (K == 2 || K == 4 || K == 8 || K == 16 || K == 32) {
 #pragma unroll
-    for (int o = 1; o < K; o <<= 1) v = max(v, __shfl_xor_sync(gmask, v, o));
+    for (int o = 1; o < K; o <<= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
   }
   const int base = lane - lane % kk;
   int s = v;
-  for (int j = 0; j < kk; ++j) s = max(s, __shfl_sync(gmask, v, base + j));
+  for (int j = 0; j < kk; ++j) s = max(s, __shfl_sync(0xffffffffu, v, (base + j) & 31));
   return s;
 }
 

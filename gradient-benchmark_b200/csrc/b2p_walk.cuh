@@ -150,13 +150,15 @@ __device__ __forceinline__ unsigned pinned(unsigned x) {
 // Power-of-two rescale shared by the K category lanes of a pattern; returns 1 if applied.
 // fp64: partials are non-negative, so the high words order like the values; a denormal
 // maximum (high word 0) is left alone — it cannot arise from one step below 2^-200.
+// `on`: this lane holds a value (lanes without one take part in the group maximum with 0 —
+// for K != 1 every lane of the warp must call this: full-warp shuffles inside).
 // The multiplication is rare: it sits in a loop of at most one trip so that it stays a
 // branch instead of four predicated multiplies issued every time.
 template <int K>
-__device__ __forceinline__ int rescale(unsigned gmask, int lane, int kk, double (&y)[4]) {
+__device__ __forceinline__ int rescale(bool on, int lane, int kk, double (&y)[4]) {
   int h = max(max(__double2hiint(y[0]), __double2hiint(y[1])), max(__double2hiint(y[2]), __double2hiint(y[3])));
-  h = group_max_int<K>(h, gmask, lane, kk);
-  const int need = (h < 0x33700000 && h > 0) ? 1 : 0;  // < 2^-200
+  h = group_max_int<K>(on ? h : 0, lane, kk);
+  const int need = (on && h < 0x33700000 && h > 0) ? 1 : 0;  // < 2^-200
 #pragma unroll 1
   for (unsigned z = pinned((unsigned)need); z != 0; --z) {
 #pragma unroll
@@ -165,10 +167,10 @@ __device__ __forceinline__ int rescale(unsigned gmask, int lane, int kk, double 
   return need;
 }
 template <int K>
-__device__ __forceinline__ int rescale(unsigned gmask, int lane, int kk, float (&y)[4]) {
+__device__ __forceinline__ int rescale(bool on, int lane, int kk, float (&y)[4]) {
   float mx = fmaxf(fmaxf(y[0], y[1]), fmaxf(y[2], y[3]));
-  mx = group_max<K>(mx, gmask, lane, kk);
-  const int need = (mx < Scale<float>::threshold() && mx > 0.f) ? 1 : 0;
+  mx = group_max<K>(on ? mx : 0.f, lane, kk);
+  const int need = (on && mx < Scale<float>::threshold() && mx > 0.f) ? 1 : 0;
 #pragma unroll 1
   for (unsigned z = pinned((unsigned)need); z != 0; --z) {
 #pragma unroll
@@ -197,7 +199,6 @@ struct WalkThread {
   unsigned plane;  // fp64: bytes between the two halves of a column
   unsigned km;     // shared base + k * row_bytes: a row's byte offset is added to this
   unsigned rs;     // bytes between rows
-  unsigned gmask;  // the K lanes of this thread's pattern
   int lane, kk, k, ts;
   T cw, cwr;       // K != 1: category weight, category weight x rate
   double w[CPT];   // pattern weights of the thread's columns (0 for padding columns)
@@ -238,94 +239,144 @@ __device__ __forceinline__ void fetch_child(const WalkThread<T, CPT>& th, unsign
   }
 }
 
-// ------------------------------------------------------------------ post-order task, one column
-//   x_v = m_l o m_r (rescaled when tiny) ;  m_v = P_v x_v ; root: site likelihood -> log-likelihood term
-template <typename T, int K, int CPT>
-__device__ __forceinline__ void post_column(const WalkParams<T>& p, const WalkThread<T, CPT>& th, const TaskDesc& d, int* scount_c,
-                                            unsigned code_l, unsigned code_r, unsigned oc, double w, double& term) {
-  T x[4], mb[4];
-  fetch_child<T, CPT>(th, d.a_l, (d.flags & WF_TIP_L) != 0, code_l, oc, x);
-  fetch_child<T, CPT>(th, d.a_r, (d.flags & WF_TIP_R) != 0, code_r, oc, mb);
-#pragma unroll
-  for (int i = 0; i < 4; ++i) x[i] *= mb[i];
-  const int bumped = rescale<K>(th.gmask, th.lane, th.kk, x);
-  if (!(d.flags & WF_ROOT)) {
-    T mv[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      T r[4];
-      lds_vec(th.km + d.a_v + i * th.rs, 16u, r);
-      mv[i] = r[0] * x[0] + r[1] * x[1] + r[2] * x[2] + r[3] * x[3];
-    }
-    sts_vec(th.sc + d.dst0 + oc, th.plane, mv);
-    if (bumped && th.k == 0) atomicAdd(scount_c, 1);
-  } else {
-    T site = (T)p.freqs[0] * x[0] + (T)p.freqs[1] * x[1] + (T)p.freqs[2] * x[2] + (T)p.freqs[3] * x[3];
-    if (K != 1) site = group_sum<K>(site * th.cw, th.gmask, th.lane, th.kk);
-    if (th.k == 0 && w != 0.0) term += w * (log((double)site) - (double)(*scount_c + bumped) * Scale<T>::log_factor());
-  }
-}
+// Control flow of the task functions.  K == 1 has no exchange between lanes: only lanes with
+// a live task call them (`live` is true).  K != 1 exchanges over the K category lanes of a
+// pattern with FULL-WARP shuffles, so every lane of the warp makes the same calls: lanes without
+// a task (`live` false) run on whatever their zero descriptor points at — valid shared memory —
+// enter the reductions with neutral values and store nothing.
+// A thread's CPT columns belong to the same task and the same category, so they share every
+// matrix row: the operands are fetched column by column (short register lifetimes), the
+// products with P run over all columns with each row read once (at K = 4 a row read costs the
+// shared-memory pipe as much as a whole column read: four distinct addresses per warp).
 
-// One child's side of a pre-order task, one column: its gradient numerator q.(Q m) and, for an
-// internal child, its pre-order partial u_c = P_c^T q (rescaled when tiny) -> shared memory.
-template <typename T, int K, int CPT>
-__device__ __forceinline__ T pre_side(const WalkParams<T>& p, const WalkThread<T, CPT>& th, bool tip, unsigned mat, unsigned dst,
-                                      const T (&q)[4], const T (&m)[4]) {
-  T num = (T)0;
-  // d/dt (P x) = r Q (P x): Q comes from the constant bank
+// y[c] = M x[c] (TRANS false: rows of M at `at`) or y[c] = M^T x[c] for the thread's columns.
+template <typename T, int CPT, bool TRANS>
+__device__ __forceinline__ void rows_times(const WalkThread<T, CPT>& th, unsigned at, const T (&x)[CPT][4], T (&y)[CPT][4]) {
+  if (TRANS) {
+#pragma unroll
+    for (int c = 0; c < CPT; ++c)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) y[c][j] = (T)0;
+  }
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const T dm = p.q[4 * i] * m[0] + p.q[4 * i + 1] * m[1] + p.q[4 * i + 2] * m[2] + p.q[4 * i + 3] * m[3];
-    num += q[i] * dm;
-  }
-  if (!tip) {
-    T u[4] = {(T)0, (T)0, (T)0, (T)0};
+    T r[4];
+    lds_vec(at + i * th.rs, 16u, r);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      T r[4];
-      lds_vec(th.km + mat + i * th.rs, 16u, r);
+    for (int c = 0; c < CPT; ++c) {
+      if (TRANS) {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) u[j] += r[j] * q[i];
+        for (int j = 0; j < 4; ++j) y[c][j] += r[j] * x[c][i];
+      } else {
+        y[c][i] = r[0] * x[c][0] + r[1] * x[c][1] + r[2] * x[c][2] + r[3] * x[c][3];
+      }
     }
-    (void)rescale<K>(th.gmask, th.lane, th.kk, u);
-    sts_vec(th.sc + dst, th.plane, u);
   }
-  return num;
 }
 
-// ------------------------------------------------------------------- pre-order task, one column
+// ------------------------------------------------------------------ post-order task
+//   x_v = m_l o m_r (rescaled when tiny) ;  m_v = P_v x_v ; root: site likelihood -> log-likelihood term
+// root_round: this warp runs the root's task (warp-uniform: the root runs alone in its round).
+template <typename T, int K, int CPT>
+__device__ __forceinline__ void post_task(const WalkParams<T>& p, const WalkThread<T, CPT>& th, const TaskDesc& d, bool live,
+                                          bool root_round, int* scount, int col, const unsigned (&code_l)[CPT],
+                                          const unsigned (&code_r)[CPT], double& term) {
+  T x[CPT][4];
+  int bumped[CPT];
+#pragma unroll
+  for (int c = 0; c < CPT; ++c) {
+    T mb[4];
+    fetch_child<T, CPT>(th, d.a_l, (d.flags & WF_TIP_L) != 0, code_l[c], c * th.dB, x[c]);
+    fetch_child<T, CPT>(th, d.a_r, (d.flags & WF_TIP_R) != 0, code_r[c], c * th.dB, mb);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) x[c][i] *= mb[i];
+    bumped[c] = rescale<K>(live, th.lane, th.kk, x[c]);
+  }
+  if (!root_round) {
+    T mv[CPT][4];
+    rows_times<T, CPT, false>(th, th.km + d.a_v, x, mv);
+    if (live) {
+#pragma unroll
+      for (int c = 0; c < CPT; ++c) {
+        sts_vec(th.sc + d.dst0 + c * th.dB, th.plane, mv[c]);
+        if (bumped[c] && th.k == 0) atomicAdd(scount + col + c * th.ts, 1);
+      }
+    }
+  } else {
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) {
+      T site = (T)p.freqs[0] * x[c][0] + (T)p.freqs[1] * x[c][1] + (T)p.freqs[2] * x[c][2] + (T)p.freqs[3] * x[c][3];
+      if (K != 1) site = group_sum<K>(site * th.cw, th.lane, th.kk);
+      if (live && th.k == 0 && th.w[c] != 0.0)
+        term += th.w[c] * (log((double)site) - (double)(scount[col + c * th.ts] + bumped[c]) * Scale<T>::log_factor());
+    }
+  }
+}
+
+// ------------------------------------------------------------------- pre-order task
 //   q_l = u_v o m_r, q_r = u_v o m_l ; L = q_l . m_l ; dL/dt_l = r_k q_l.(Q m_l) ; u_l = P_l^T q_l (same for r)
 template <typename T, int K, int CPT>
-__device__ __forceinline__ void pre_column(const WalkParams<T>& p, const WalkThread<T, CPT>& th, const TaskDesc& d,
-                                           unsigned code_l, unsigned code_r, unsigned oc, double w, double& gl, double& gr) {
-  T ma[4], mb[4], u[4], q[4];
-  fetch_child<T, CPT>(th, d.a_l, (d.flags & WF_TIP_L) != 0, code_l, oc, ma);
-  fetch_child<T, CPT>(th, d.a_r, (d.flags & WF_TIP_R) != 0, code_r, oc, mb);
-  lds_vec(th.sc + d.a_v + oc, th.plane, u);
-  T den = (T)0;
+__device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThread<T, CPT>& th, const TaskDesc& d, bool live,
+                                         const unsigned (&code_l)[CPT], const unsigned (&code_r)[CPT], double& gl, double& gr) {
+  T ql[CPT][4], qr[CPT][4];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    q[i] = u[i] * mb[i];
-    den += q[i] * ma[i];
-  }
-  T numl = pre_side<T, K, CPT>(p, th, (d.flags & WF_TIP_L) != 0, d.m_l, d.dst0 + oc, q, ma);
+  for (int c = 0; c < CPT; ++c) {
+    T ma[4], mb[4], u[4];
+    fetch_child<T, CPT>(th, d.a_l, (d.flags & WF_TIP_L) != 0, code_l[c], c * th.dB, ma);
+    fetch_child<T, CPT>(th, d.a_r, (d.flags & WF_TIP_R) != 0, code_r[c], c * th.dB, mb);
+    lds_vec(th.sc + d.a_v + c * th.dB, th.plane, u);
+    T den = (T)0, numl = (T)0, numr = (T)0;
 #pragma unroll
-  for (int i = 0; i < 4; ++i) q[i] = u[i] * ma[i];
-  T numr = pre_side<T, K, CPT>(p, th, (d.flags & WF_TIP_R) != 0, d.m_r, d.dst1 + oc, q, mb);
-  if (K != 1) {
-    // the site likelihood is the sum over the pattern's K category lanes; the numerators
-    // need no such exchange: every lane adds its own category's share and the fold sums
-    // over all lanes of the slot anyway
-    den = group_sum<K>(den * th.cw, th.gmask, th.lane, th.kk);
-    numl *= th.cwr;
-    numr *= th.cwr;
+    for (int i = 0; i < 4; ++i) {
+      ql[c][i] = u[i] * mb[i];
+      qr[c][i] = u[i] * ma[i];
+      den += ql[c][i] * ma[i];
+    }
+    // d/dt (P x) = r Q (P x): Q comes from the constant bank
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const T dl = p.q[4 * i] * ma[0] + p.q[4 * i + 1] * ma[1] + p.q[4 * i + 2] * ma[2] + p.q[4 * i + 3] * ma[3];
+      const T dr = p.q[4 * i] * mb[0] + p.q[4 * i + 1] * mb[1] + p.q[4 * i + 2] * mb[2] + p.q[4 * i + 3] * mb[3];
+      numl += ql[c][i] * dl;
+      numr += qr[c][i] * dr;
+    }
+    if (K != 1) {
+      // the site likelihood is the sum over the pattern's K category lanes; the numerators
+      // need no such exchange: every lane adds its own category's share and the fold sums
+      // over all lanes of the slot anyway
+      den = group_sum<K>(den * th.cw, th.lane, th.kk);
+      numl *= th.cwr;
+      numr *= th.cwr;
+    }
+    // K == 1: the single category's weight cancels, its rate multiplies the numerators.  A
+    // pattern of likelihood zero contributes nothing instead of inf * 0.
+    const double dd = (double)den;
+    const double inv = (live && dd > 0.0) ? (K == 1 ? th.w[c] * p.rates[0] : th.w[c]) * fast_rcp(dd) : 0.0;
+    gl += live ? (double)numl * inv : 0.0;
+    gr += live ? (double)numr * inv : 0.0;
   }
-  // K == 1: the single category's weight cancels, its rate multiplies the numerators.  A
-  // pattern of likelihood zero contributes nothing instead of inf * 0.
-  const double dd = (double)den;
-  const double inv = dd > 0.0 ? (K == 1 ? w * p.rates[0] : w) * fast_rcp(dd) : 0.0;
-  gl += (double)numl * inv;
-  gr += (double)numr * inv;
+  // pre-order partials of the internal children: u_c = P_c^T q_c (rescaled when tiny).  K == 1: a
+  // tip child skips the product; K != 1: every lane computes it (the rescale inside is a warp-wide
+  // exchange) and only lanes with an internal child keep it.
+  const bool out_l = live && !(d.flags & WF_TIP_L), out_r = live && !(d.flags & WF_TIP_R);
+  if (K != 1 || out_l) {
+    T uc[CPT][4];
+    rows_times<T, CPT, true>(th, th.km + d.m_l, ql, uc);
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) {
+      (void)rescale<K>(out_l, th.lane, th.kk, uc[c]);
+      if (out_l) sts_vec(th.sc + d.dst0 + c * th.dB, th.plane, uc[c]);
+    }
+  }
+  if (K != 1 || out_r) {
+    T uc[CPT][4];
+    rows_times<T, CPT, true>(th, th.km + d.m_r, qr, uc);
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) {
+      (void)rescale<K>(out_r, th.lane, th.kk, uc[c]);
+      if (out_r) sts_vec(th.sc + d.dst1 + c * th.dB, th.plane, uc[c]);
+    }
+  }
 }
 
 // Fold the per-thread sums of the previous round (copy warps): a slot's ts pairs -> (a, b),
@@ -403,7 +454,6 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
 
   WalkThread<T, CPT> th;
   th.lane = lane; th.kk = kk; th.k = col % kk; th.ts = p.ts;
-  th.gmask = group_mask<K>(lane, kk);
   th.sc = pinned(sbase + col * 16); th.dB = p.ts * 16; th.plane = p.plane;
   th.km = pinned(sbase + th.k * 4 * (unsigned)sizeof(T));
   th.rs = p.row_stride;
@@ -530,14 +580,9 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
         // those of the round before are complete in global memory
         asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         asm volatile("cp.async.bulk.wait_group 1;" ::: "memory");
-      } else if (in_slot) {
-#ifdef B2P_DBG
-        if ((p.dbg >> 8) && (warp & 1)) {  // experiment: odd compute warps start their round (dbg >> 8) * 16 cycles late
-          const long long t0 = clock64();
-          while (clock64() - t0 < (long long)(p.dbg >> 8) * 16) {}
-        }
-#endif
-        // descriptor and tip codes: independent reads (the codes sit at fixed per-slot positions)
+      } else {
+        // descriptor and tip codes: independent reads (the codes sit at fixed per-slot positions);
+        // lanes outside every slot read slot 0's and ignore them
         const uint4 d0 = lds_u4(frame + o_desc), d1 = lds_u4(frame + o_desc + 16);
         unsigned code_l[CPT], code_r[CPT];
 #pragma unroll
@@ -545,22 +590,27 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
           code_l[c] = lds_u8(frame + o_tip + c * p.ts);
           code_r[c] = lds_u8(frame + o_tip + p.ct_pad + c * p.ts);
         }
-        const TaskDesc d = unpack_desc(d0, d1);
+        TaskDesc d = unpack_desc(d0, d1);
+        if (!in_slot) d.flags = 0;
+        bool live = (d.flags & WF_LIVE) != 0;
 #ifdef B2P_DBG
-        if (!(p.dbg & 4))
+        if (p.dbg & 4) live = false;
 #endif
-        if (d.flags & WF_LIVE) {
+        // K == 1: lanes without a task skip it.  K != 1: the task exchanges values over the K
+        // category lanes with full-warp shuffles, so a warp runs it as a whole (lanes without a
+        // task compute on a zero descriptor and store nothing) or, with no task at all, skips it.
+        const bool run = K == 1 ? live : __any_sync(0xffffffffu, live);
+        if (run) {
           const unsigned gslot = o_gslot + par * p.wn * p.ts * 16;
           double ga = 0.0, gb2 = 0.0;  // post-order (root): log-likelihood term, 0; pre-order: the two gradient sums
           if (q < p.rounds_post) {
-#pragma unroll
-            for (int c = 0; c < CPT; ++c)
-              post_column<T, K, CPT>(p, th, d, scount + col + c * p.ts, code_l[c], code_r[c], c * th.dB, th.w[c], ga);
-            if (d.flags & WF_ROOT) sts_d2(gslot, ga, 0.0);
+            const bool is_root = (d.flags & WF_ROOT) != 0;
+            const bool root_round = K == 1 ? is_root : __any_sync(0xffffffffu, is_root);  // the root runs alone in its round
+            post_task<T, K, CPT>(p, th, d, live, root_round, scount, col, code_l, code_r, ga);
+            if (live && is_root) sts_d2(gslot, ga, 0.0);
           } else {
-#pragma unroll
-            for (int c = 0; c < CPT; ++c) pre_column<T, K, CPT>(p, th, d, code_l[c], code_r[c], c * th.dB, th.w[c], ga, gb2);
-            sts_d2(gslot, ga, gb2);
+            pre_task<T, K, CPT>(p, th, d, live, code_l, code_r, ga, gb2);
+            if (live) sts_d2(gslot, ga, gb2);
           }
         }
 #ifdef B2P_TRACE_CLOCKS

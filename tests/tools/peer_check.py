@@ -41,6 +41,14 @@ for name, nt, npat in (("jc69_1000x10k", 200, 3001), ("hky_g4_flu", 150, 777)):
     for it in range(5):  # several epochs: both slot sets, flag reuse
         out.zero_()
         e1.loglik_grad_device(bl.data_ptr(), out.data_ptr(), out.data_ptr() + 8, torch.cuda.current_stream().cuda_stream)
+    # a late rank: the others' kernels wait for its flags (up to ~30 s) instead of summing stale slots
+    if rank == world - 1:
+        import time
+        time.sleep(1.5)
+    late = torch.zeros(1 + n_br, dtype=torch.float64, device=dev)
+    e1.loglik_grad_device(bl.data_ptr(), late.data_ptr(), late.data_ptr() + 8, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    ok = ok and torch.equal(late, out)
     ev = torch.zeros(1, dtype=torch.float64, device=dev)
     e1.loglik_grad_device(bl.data_ptr(), ev.data_ptr(), None, torch.cuda.current_stream().cuda_stream)  # evaluation-only epoch
     torch.cuda.synchronize()

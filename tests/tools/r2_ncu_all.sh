@@ -8,6 +8,11 @@ cap() {  # tag, kernel regex, launches to skip, command...
   timeout 600 "$@" > gpurun_out/plain_$tag.log 2>&1 || { echo "plain run failed: $tag"; tail -3 gpurun_out/plain_$tag.log; return; }
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:$rx -s $skip -c 1 -f -o gpurun_out/ncu_$tag "$@" > gpurun_out/ncu_$tag.log 2>&1
   echo "ncu $tag rc=$?"
+  # the reports are ~10 MB each and gpurun_out/ travels back only up to 64 MiB: summarise here
+  # (same ncu, same tool as at home) and keep only the text
+  python tests/tools/ncu_summary.py gpurun_out/ncu_$tag.ncu-rep gpurun_out/r02_ncu_${tag}_summary.txt > /dev/null 2>&1
+  case $tag in walk_*) ncu -i gpurun_out/ncu_$tag.ncu-rep --page source --csv --print-source sass 2>/dev/null | gzip > gpurun_out/r02_ncu_${tag}_sass.csv.gz;; esac
+  rm -f gpurun_out/ncu_$tag.ncu-rep gpurun_out/plain_$tag.log
 }
 cap walk_f64_k1_jc69_1000x10k      '^walk_kernel'            4 $P jc69_1000x10k --nocheck --reps 2
 cap walk_f64_k4_gtr_g4_5000x10k    '^walk_kernel'            4 $P gtr_g4_5000x10k --nocheck --reps 2
