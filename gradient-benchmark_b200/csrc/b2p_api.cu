@@ -435,15 +435,24 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
     if (!getenv("B2P_NP")) n_copy = 2;
   }
   bool planned = plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, ct_force, depth, n_copy, cpt, h->wg);
-  // Copy warps: a round has about one load and one store per slot, and a warp issues a bulk copy
-  // every ~100 cycles, so few slots need few copy warps (and a freed warp is compute threads):
-  // three from eleven slots on, two from eight, else one (sweeps: profiles/README.md, round 2).
-  if (planned && !getenv("B2P_NP")) {
-    for (int np = 2; np >= 1 && h->wg.wn <= (np == 2 ? 10 : 7); --np) {
-      WalkGeometry g2;
-      if (!plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, ct_force, depth, np, cpt, g2)) break;
+  // fp32 needs 80-96 registers per thread, so 768 threads fit (more tasks per round), with four
+  // copy warps for the larger rounds (sweep: profiles/README.md, round 2: 0.227 vs 0.270 ms at the
+  // flu shape).
+  if (planned && cfg->precision == B2P_PRECISION_F32 && !nt_force && !getenv("B2P_NP") && h->ctas_per_sm == 1) {
+    WalkGeometry g2;
+    if (plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms, smem_budget, 768, ct_force, depth, 4, cpt, g2) && g2.cpt == h->wg.cpt) {
       h->wg = g2;
+      nt_force = 768;
+      n_copy = 4;
     }
+  }
+  // Copy warps: a round has about one load and one store per slot, and a warp issues a bulk copy
+  // every ~100 cycles, so few slots need fewer copy warps (and a freed warp is compute threads):
+  // two when that leaves at most ten slots (sweeps: profiles/README.md, round 2).
+  if (planned && !getenv("B2P_NP") && n_copy == 3 && h->wg.wn <= 10) {
+    WalkGeometry g2;
+    if (plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, ct_force, depth, 2, cpt, g2) && g2.wn <= 10)
+      h->wg = g2;
   }
   // Copy depth 2 (loads issued two rounds ahead) when three frames are a small part of shared
   // memory: the round time no longer contains the HBM latency.  With many slots the frames (matrix
