@@ -456,12 +456,15 @@ def run_b200(a):
             todo = [(f"configs[3]: 100k patterns over {ctx.world} GPUs", "gtr_g4_5000x100k", "float64", 100000 // ctx.world)]
         for label, name, prec, pat in todo:
             try:
-                r = measure(name, prec, pat, min(a.steps, 5 if name == "gtr_g4_5000x100k" else 30), 3, ctx, want_e2e=ctx.world == 1)
+                # configs[0] is the shape the reference's micro benchmark times on one CPU core
+                # (/root/reference/nextflow.config:9): its entry carries the CPU port's rate too
+                r = measure(name, prec, pat, min(a.steps, 5 if name == "gtr_g4_5000x100k" else 30), 3, ctx, want_e2e=ctx.world == 1,
+                            cpu_seconds=1.0 if name == "jc69_20x1000" and not a.no_cpu_baseline else 0.0)
             except Exception as exc:  # a secondary run must not take the headline down with it
                 r = {"error": f"{type(exc).__name__}: {exc}"} if ctx.rank == 0 else None
             if ctx.rank == 0 and r is not None:
                 keep = {k: r[k] for k in ("value", "unit", "ms_per_step", "steps", "dtype", "config", "roofline", "clocks", "check",
-                                          "e2e", "gpu_launches", "error") if k in r}
+                                          "e2e", "gpu_launches", "cpu_baseline", "error") if k in r}
                 if name == "gtr_g4_5000x100k" and "value" in r:
                     keep["scaling"] = "strong"
                     keep["whole_alignment_evals_per_s"] = r["value"] / ctx.world
