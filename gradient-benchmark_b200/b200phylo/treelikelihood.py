@@ -171,12 +171,20 @@ class TreeLikelihoodFunction(torch.autograd.Function):
         if need_grad:
             ctx.save_for_backward(out[1:])
         ctx.in_dtype = branch_lengths.dtype
-        return out[0].to(branch_lengths.dtype)
+        logl = out[0]
+        return logl if logl.dtype == branch_lengths.dtype else logl.to(branch_lengths.dtype)
 
     @staticmethod
     def backward(ctx, grad_output):
         (g,) = ctx.saved_tensors
-        return (grad_output * g).to(ctx.in_dtype), None
+        # d logL / d logL = 1 is the common upstream gradient (``logl.backward()``): hand the
+        # gradient buffer over as it is instead of a multiplication by one (host tensors: a
+        # 2N-2-element multiply costs as much as a tenth of an evaluation at 1000 taxa)
+        if not grad_output.is_cuda and grad_output.dim() == 0 and grad_output.item() == 1.0:
+            out = g
+        else:
+            out = grad_output * g
+        return (out if out.dtype == ctx.in_dtype else out.to(ctx.in_dtype)), None
 
 
 class TreeLikelihoodModel:

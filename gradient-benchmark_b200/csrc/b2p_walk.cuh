@@ -147,34 +147,44 @@ __device__ __forceinline__ unsigned pinned(unsigned x) {
   return x;
 }
 
-// Power-of-two rescale shared by the K category lanes of a pattern; returns 1 if applied.
-// fp64: partials are non-negative, so the high words order like the values; a denormal
-// maximum (high word 0) is left alone — it cannot arise from one step below 2^-200.
+// Power-of-two rescale shared by the K category lanes of a pattern; returns the number of
+// factors applied (0 almost always).  The count comes from the exponent of the group's maximum,
+// so ONE call brings any positive value back above the threshold — a product of two messages
+// whose large entries sit on different states can be far more than one factor below it (fp32:
+// factor 2^40 against a range of 2^-126).  Partials are non-negative, so
+// the raw bits order like the values.  Zero and denormal maxima (exponent field 0) are left
+// alone: the pattern's likelihood is zero or about to be.
 // `on`: this lane holds a value (lanes without one take part in the group maximum with 0 —
 // for K != 1 every lane of the warp must call this: full-warp shuffles inside).
-// The multiplication is rare: it sits in a loop of at most one trip so that it stays a
-// branch instead of four predicated multiplies issued every time.
+// The multiplication is rare: it sits in a loop so that it stays a branch instead of four
+// predicated multiplies issued every time.
 template <int K>
 __device__ __forceinline__ int rescale(bool on, int lane, int kk, double (&y)[4]) {
   int h = max(max(__double2hiint(y[0]), __double2hiint(y[1])), max(__double2hiint(y[2]), __double2hiint(y[3])));
   h = group_max_int<K>(on ? h : 0, lane, kk);
-  const int need = (on && h < 0x33700000 && h > 0) ? 1 : 0;  // < 2^-200
+  int need = 0;
 #pragma unroll 1
-  for (unsigned z = pinned((unsigned)need); z != 0; --z) {
+  for (unsigned z = pinned((unsigned)(on && h < 0x33700000 && h >= 0x00100000)); z != 0; --z) {  // < 2^-200, normal
+    need = (823 - (h >> 20) + 199) / 200;  // biased exponent against 823 = 1023 - 200
+#pragma unroll 1
+    for (int r = 0; r < need; ++r)
 #pragma unroll
-    for (int i = 0; i < 4; ++i) y[i] *= Scale<double>::factor();
+      for (int i = 0; i < 4; ++i) y[i] *= Scale<double>::factor();
   }
   return need;
 }
 template <int K>
 __device__ __forceinline__ int rescale(bool on, int lane, int kk, float (&y)[4]) {
-  float mx = fmaxf(fmaxf(y[0], y[1]), fmaxf(y[2], y[3]));
-  mx = group_max<K>(on ? mx : 0.f, lane, kk);
-  const int need = (on && mx < Scale<float>::threshold() && mx > 0.f) ? 1 : 0;
+  int h = max(max(__float_as_int(y[0]), __float_as_int(y[1])), max(__float_as_int(y[2]), __float_as_int(y[3])));
+  h = group_max_int<K>(on ? h : 0, lane, kk);
+  int need = 0;
 #pragma unroll 1
-  for (unsigned z = pinned((unsigned)need); z != 0; --z) {
+  for (unsigned z = pinned((unsigned)(on && h < 0x2b800000 && h >= 0x00800000)); z != 0; --z) {  // < 2^-40, normal
+    need = (87 - (h >> 23) + 39) / 40;  // biased exponent against 87 = 127 - 40
+#pragma unroll 1
+    for (int r = 0; r < need; ++r)
 #pragma unroll
-    for (int i = 0; i < 4; ++i) y[i] *= Scale<float>::factor();
+      for (int i = 0; i < 4; ++i) y[i] *= Scale<float>::factor();
   }
   return need;
 }
@@ -299,7 +309,7 @@ __device__ __forceinline__ void post_task(const WalkParams<T>& p, const WalkThre
 #pragma unroll
       for (int c = 0; c < CPT; ++c) {
         sts_vec(th.sc + d.dst0 + c * th.dB, th.plane, mv[c]);
-        if (bumped[c] && th.k == 0) atomicAdd(scount + col + c * th.ts, 1);
+        if (bumped[c] && th.k == 0) atomicAdd(scount + col + c * th.ts, bumped[c]);
       }
     }
   } else {

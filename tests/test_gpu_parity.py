@@ -106,6 +106,20 @@ def test_rescaling_deep_tree_fp64_and_fp32():
     _check(w, precision="float32")
 
 
+def test_rescaling_divergent_balanced_tree_fp32():
+    """ADVICE.md (round 1): on a balanced tree of very divergent sequences the two children's large
+    entries sit on different states, so a node's partial can be far more than ONE rescale factor
+    (2^40 in fp32) below the threshold; with a single fixed step per node the deficit doubles per
+    level and fp32 underflows to logL = -inf within a few levels.  The rescale takes as many steps
+    as the exponent asks for; the C oracle (fp64, one step suffices there) is the reference."""
+    tree = simulate_tree(512, shape="balanced", seed=4, mean_branch=0.002)
+    sp = random_patterns(512, 200, seed=8, p_change=0.75)  # near-random tips on near-zero branches
+    w = Workload("divergent", tree, sp, JC69(), ConstantSiteModel())
+    for prec in ("float64", "float32"):
+        logl, grad = _check(w, precision=prec)
+        assert np.isfinite(logl) and np.all(np.isfinite(grad)) and logl < -1e5
+
+
 def test_ambiguity_codes_and_gaps():
     w = make_workload("hky_g4_flu", n_tips=60, n_patterns=400)
     m = w.patterns.masks.copy()
