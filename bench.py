@@ -401,9 +401,9 @@ def dense_roofline(info, w, k_avg_ms, k_n, steps, dev):
     tiles = info["n_tiles"]
     issued = 2 * 64 ** 3 * (tiles * ((N_ - 1) + 2 * (N_ - 2)) + 2 * (2 * N_ - 2))
     return {
-        # transition, one post-order launch per level, one pre-order launch per depth, tips, reduce
+        # transition, one post-order launch, one pre-order launch (dependencies by flag), tips, reduce
         "gpu_launches": (1 + info["post_rounds"] + info["pre_rounds"] + 2) * steps,
-        "roofline": {"bound": "tensor", "kernel": "dense_post_kernel + dense_pre_kernel (one launch per tree level) + dense_tip_kernel",
+        "roofline": {"bound": "tensor", "kernel": "dense_transition_kernel + dense_post_kernel + dense_pre_kernel (one launch per pass, flag-chained) + dense_tip_kernel",
                      "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf,
                      "frac_is": "SURVEY.md §8(d) algorithmic flops / time / peak (the formulation issues fewer: see issued_frac)",
                      "traffic": None, "alg_flops_per_eval": flops, "issued_flops_per_eval": issued,

@@ -77,7 +77,8 @@ struct b2p_instance {
     double *evec = nullptr, *ivec = nullptr, *evals = nullptr, *q = nullptr, *qt = nullptr, *freqs = nullptr;
     double *P = nullptr, *PT = nullptr, *D = nullptr, *weights = nullptr, *msg = nullptr, *pre = nullptr;
     uint8_t* codes = nullptr;
-    int* scount = nullptr;
+    int* scount = nullptr;                      // [cols_pad] rescale counts, then the dependency flags and the error word
+    size_t sync_ints = 0;                       // ints cleared at the start of every evaluation (scount + flags + err)
     DenseNode* nodes = nullptr;                 // post-order levels, then pre-order levels
     std::vector<int> post_off, pre_off;         // level boundaries into `nodes`
     int root = 0, tip_off = 0;                  // tip tasks start at nodes[tip_off] (N of them)
@@ -167,7 +168,7 @@ static int dense_create(b2p_instance* h) {
       (rc = dev_alloc(h, &d->PT, n_br * mat)) || (rc = dev_alloc(h, &d->D, n_br * mat)) ||
       (rc = dev_alloc(h, &d->weights, sizeof(double) * d->cols_pad)) || (rc = dev_alloc(h, (char**)&d->msg, part)) ||
       (rc = dev_alloc(h, (char**)&d->pre, part)) || (rc = dev_alloc(h, &d->codes, (size_t)N * d->cols_pad)) ||
-      (rc = dev_alloc(h, &d->scount, sizeof(int) * d->cols_pad)) || (rc = dev_alloc(h, &d->nodes, sizeof(DenseNode) * (3 * (size_t)N - 3))) ||
+      (rc = dev_alloc(h, &d->scount, sizeof(int) * (d->sync_ints = (size_t)d->cols_pad + 2 * (size_t)(N - 1) * d->n_tiles + 1))) || (rc = dev_alloc(h, &d->nodes, sizeof(DenseNode) * (3 * (size_t)N - 3))) ||
       (rc = dev_alloc(h, &h->d_lpart, sizeof(double) * d->n_tiles)) ||
       (rc = dev_alloc(h, &h->d_gpart, sizeof(double) * (size_t)d->n_tiles * n_br)) ||
       (rc = dev_alloc(h, &h->d_bl_stage, sizeof(double) * n_br)) || (rc = dev_alloc(h, &h->d_out_stage, sizeof(double) * (n_br + 1))))
@@ -231,7 +232,9 @@ static int dense_set_topology(b2p_instance* h, const int32_t* tr) {
   d->root = root;
   int pre_launches = 0;  // depths that have an internal child
   for (size_t L = 0; L + 1 < d->pre_off.size(); ++L) pre_launches += d->pre_off[L + 1] > d->pre_off[L];
-  h->plan.rounds_post = lvl[root] + 1; h->plan.rounds_pre = pre_launches; h->plan.rounds = h->plan.rounds_post + h->plan.rounds_pre;
+  (void)pre_launches;
+  // one launch per pass: the level lists only fix the ORDER of the blocks (dependencies go by flag)
+  h->plan.rounds_post = 1; h->plan.rounds_pre = 1; h->plan.rounds = 2;
   h->plan.tree_depth = max_dep + 1;
   CU(cudaSetDevice(h->cfg.device));
   CU(cudaDeviceSynchronize());
@@ -299,30 +302,32 @@ static cudaError_t dense_launch(b2p_instance* h, const double* d_bl, double* d_l
   p.n_tiles = d->n_tiles; p.n_branches = n_br; p.rate = h->model.rates[0];
   p.P = d->P; p.PT = d->PT; p.D = d->D; p.Q = d->q; p.QT = d->qt; p.freqs = d->freqs; p.codes = d->codes;
   p.weights = d->weights; p.msg = d->msg; p.pre = d->pre; p.scount = d->scount; p.lpart = h->d_lpart; p.gpart = h->d_gpart;
-  cudaError_t e = cudaMemsetAsync(d->scount, 0, sizeof(int) * d->cols_pad, st);
+  p.done_post = d->scount + d->cols_pad;
+  p.done_pre = p.done_post + (size_t)(N - 1) * d->n_tiles;
+  p.err = p.done_pre + (size_t)(N - 1) * d->n_tiles;
+  cudaError_t e = cudaMemsetAsync(d->scount, 0, sizeof(int) * d->sync_ints, st);
   if (e != cudaSuccess) return e;
   const int slot = (int)(h->prof_count % b2p_instance::kProfRing);
   if (h->profiling) cudaEventRecord(h->ev0[slot], st);
   dense_transition_kernel<<<n_br, DNT, 3 * DENSE_TILE_BYTES, st>>>(d->evec, d->ivec, d->evals, d->qt, d_bl, p.rate, d->S, d->P, d->PT, d->D);
-  // Level kernels: programmatic dependent launch (b2p_dense.cuh, level_wait): a level's CTAs are
-  // resident and past their prologue when the previous level's last CTA retires.
+  // Programmatic dependent launch (b2p_dense.cuh, level_wait): a pass's CTAs become resident while
+  // the previous launch drains and run their prologue before griddepcontrol.wait.  Inside a pass
+  // the blocks are in level order and wait for the tiles they read (tile_wait / tile_publish).
   cudaLaunchAttribute pdl[1];
   pdl[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   pdl[0].val.programmaticStreamSerializationAllowed = 1;
   cudaLaunchConfig_t cfg = {};
   cfg.blockDim = dim3(DNT); cfg.stream = st; cfg.attrs = pdl; cfg.numAttrs = 1;
-  for (size_t L = 0; L + 1 < d->post_off.size(); ++L) {
-    const int n = d->post_off[L + 1] - d->post_off[L];
-    if (n <= 0) continue;
-    cfg.gridDim = dim3(n, d->n_tiles); cfg.dynamicSmemBytes = 2 * DENSE_TILE_BYTES;
-    if ((e = cudaLaunchKernelEx(&cfg, dense_post_kernel, p, (const DenseNode*)(d->nodes + d->post_off[L]), d->root)) != cudaSuccess) return e;
+  {
+    const int n = d->post_off.back() - d->post_off.front();
+    cfg.gridDim = dim3((unsigned)n * d->n_tiles); cfg.dynamicSmemBytes = 2 * DENSE_TILE_BYTES;
+    if ((e = cudaLaunchKernelEx(&cfg, dense_post_kernel, p, (const DenseNode*)(d->nodes + d->post_off.front()), d->root)) != cudaSuccess) return e;
   }
   if (d_grad) {
-    for (size_t L = 0; L + 1 < d->pre_off.size(); ++L) {
-      const int n = d->pre_off[L + 1] - d->pre_off[L];
-      if (n <= 0) continue;
-      cfg.gridDim = dim3(n, d->n_tiles); cfg.dynamicSmemBytes = 3 * DENSE_TILE_BYTES;
-      if ((e = cudaLaunchKernelEx(&cfg, dense_pre_kernel, p, (const DenseNode*)(d->nodes + d->pre_off[L]), d->root)) != cudaSuccess) return e;
+    const int n = d->pre_off.back() - d->pre_off.front();
+    if (n > 0) {
+      cfg.gridDim = dim3((unsigned)n * d->n_tiles); cfg.dynamicSmemBytes = 3 * DENSE_TILE_BYTES;
+      if ((e = cudaLaunchKernelEx(&cfg, dense_pre_kernel, p, (const DenseNode*)(d->nodes + d->pre_off.front()), d->root)) != cudaSuccess) return e;
     }
     cfg.gridDim = dim3(N, d->n_tiles); cfg.dynamicSmemBytes = 0;
     if ((e = cudaLaunchKernelEx(&cfg, dense_tip_kernel, p, (const DenseNode*)(d->nodes + d->tip_off), d->root)) != cudaSuccess) return e;

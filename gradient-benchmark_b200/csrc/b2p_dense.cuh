@@ -42,6 +42,9 @@ struct DenseParams {
   double* msg;               // [N-1][SP][cols_pad]
   double* pre;               // [N-1][SP][cols_pad]
   int* scount;               // [cols_pad]
+  int* done_post;            // [N-1][n_tiles] 1 once the node's message tile is in HBM (cleared per evaluation)
+  int* done_pre;             // [N-1][n_tiles] 1 once the node's pre-order partial tile is in HBM
+  int* err;                  // set when a dependency did not arrive within the time limit
   double* lpart;             // [n_tiles]
   double* gpart;             // [n_tiles][2N-2]
 };
@@ -95,6 +98,27 @@ __device__ __forceinline__ void fetch_matrix(const double* __restrict__ g, int k
 __device__ __forceinline__ void level_wait() {
   asm volatile("griddepcontrol.wait;" ::: "memory");
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
+// One launch per pass, dependencies by flag.  A pass is ONE grid whose blocks are laid out in level
+// order (block = task * n_tiles + tile): a task's tile depends only on the same tile of its
+// children (post-order) or of its parent (pre-order), so instead of a launch per tree level — with
+// every level waiting for the slowest CTA of the one before, and 1-4-node levels near the root
+// that cost a launch latency each — a CTA waits for exactly the tiles it reads.  Blocks are
+// dispatched in index order, so a producer is always resident or finished before its consumer
+// spins: the waits cannot deadlock.  They are bounded all the same (~2 s, then the error word).
+__device__ __forceinline__ void tile_wait(const int* flag, int* err) {
+  const long long t0 = clock64();
+  int v;
+  do {
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+    if (!v && clock64() - t0 > 4000000000ll) { *err = 1; break; }
+  } while (!v);
+}
+// after the CTA's stores of the tile and a __syncthreads(): one thread publishes
+__device__ __forceinline__ void tile_publish(int* flag) {
+  __threadfence();
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(flag), "r"(1) : "memory");
 }
 
 // Operands that need no arithmetic on the way in (matrices, an internal child's own message) go
@@ -262,23 +286,28 @@ __global__ void __launch_bounds__(DNT, 2) dense_transition_kernel(const double* 
   for (int mi = 0; mi < 8; ++mi) *reinterpret_cast<double2*>(d + 8 * mi * SP) = make_double2(acc[mi][0], acc[mi][1]);
 }
 
-// ---------------------------------------------------------------------- post-order level
-// grid (nodes of the level, tiles).  Dynamic shared memory: A [SP][SP], X [SP][DT].
+// ---------------------------------------------------------------------- post-order pass
+// grid: internal nodes in level order x tiles (1-D, tile fastest).  Dynamic shared memory: A [SP][SP], X [SP][DT].
 __global__ void __launch_bounds__(DNT, 3) dense_post_kernel(const DenseParams p, const DenseNode* __restrict__ nodes, int root) {
   extern __shared__ __align__(16) unsigned char dsm[];
   double (*A)[LD] = reinterpret_cast<double (*)[LD]>(dsm);
   double (*X)[LD] = reinterpret_cast<double (*)[LD]>(dsm + DENSE_TILE_BYTES);
   __shared__ double red[DNT / 32];
-  const DenseNode nd = nodes[blockIdx.x];
-  const int col0 = blockIdx.y * DT, t = threadIdx.x;
+  const int tile = blockIdx.x % p.n_tiles;
+  const DenseNode nd = nodes[blockIdx.x / p.n_tiles];
+  const int col0 = tile * DT, t = threadIdx.x;
   const int warp = t >> 5, lane = t & 31, g = lane >> 2, tg = lane & 3;
   const int kr = t >> 5, cp = 2 * (t & 31);
   const bool is_root = nd.v == root;
   unsigned lc0, lc1, rc0, rc1;
   fetch_codes(p, nd.l, col0 + cp, lc0, lc1);
   fetch_codes(p, nd.r, col0 + cp, rc0, rc1);
-  level_wait();  // P^T comes from the transition launch, which may be the previous one
+  level_wait();  // P^T comes from the transition launch, the previous one
   if (!is_root) copy_rows_async(A, p.PT + (size_t)nd.v * SP * SP, SP, kr, cp);
+  // the children's message tiles (internal children only: a tip's message is a column of P)
+  if (t == 0 && nd.l >= p.n_tips) tile_wait(p.done_post + (size_t)(nd.l - p.n_tips) * p.n_tiles + tile, p.err);
+  if (t == 32 && nd.r >= p.n_tips) tile_wait(p.done_post + (size_t)(nd.r - p.n_tips) * p.n_tiles + tile, p.err);
+  __syncthreads();
   {
     double2 ml[2][DH], mr[2][DH];
 #pragma unroll
@@ -315,6 +344,8 @@ __global__ void __launch_bounds__(DNT, 3) dense_post_kernel(const DenseParams p,
 #pragma unroll
     for (int mi = 0; mi < 8; ++mi)
       *reinterpret_cast<double2*>(out + (size_t)8 * mi * p.cols_pad) = make_double2(acc[mi][0] * f0, acc[mi][1] * f1);
+    __syncthreads();
+    if (t == 0) tile_publish(p.done_post + (size_t)(nd.v - p.n_tips) * p.n_tiles + tile);
   } else {
     double term = 0.0;
     if (t < DT) {
@@ -324,15 +355,15 @@ __global__ void __launch_bounds__(DNT, 3) dense_post_kernel(const DenseParams p,
       const int b = (h < 0x33700000 && h > 0) ? 1 : 0;
       if (b) site *= Scale<double>::factor();
       const double w = p.weights[col0 + t];
-      if (w != 0.0) term = w * (log(site) - (double)(p.scount[col0 + t] + b) * Scale<double>::log_factor());
+      if (w != 0.0) term = w * (log(site) - (double)(__ldcg(p.scount + col0 + t) + b) * Scale<double>::log_factor());
     }
     const double s = cta_sum(term, red);
-    if (t == 0) p.lpart[blockIdx.y] = s;
+    if (t == 0) p.lpart[tile] = s;
   }
 }
 
-// ----------------------------------------------------------------------- pre-order level
-// grid (internal children whose parents sit at this depth, tiles).  A task is {v = parent, l = the
+// ----------------------------------------------------------------------- pre-order pass
+// grid: internal children by the depth of their parent x tiles (1-D, tile fastest).  A task is {v = parent, l = the
 // child c the CTA works for, r = its sibling}.  With q_c = u_v o m_sibling everything outside the
 // branch, both products of the task contract q_c:
 //   numerator   q.(Q m_c) = (Q^T q).m_c        -> acc1 = Q^T q   (A1 = Q)
@@ -347,9 +378,10 @@ __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, 
   double (*A2)[LD] = reinterpret_cast<double (*)[LD]>(dsm + 1 * DENSE_TILE_BYTES);
   double (*Qc)[LD] = reinterpret_cast<double (*)[LD]>(dsm + 2 * DENSE_TILE_BYTES);  // everything outside the branch
   __shared__ double red[DNT / 32];
-  const DenseNode nd = tasks[blockIdx.x];
+  const int tile = blockIdx.x % p.n_tiles;
+  const DenseNode nd = tasks[blockIdx.x / p.n_tiles];
   const int c = nd.l, sib = nd.r;
-  const int col0 = blockIdx.y * DT, t = threadIdx.x;
+  const int col0 = tile * DT, t = threadIdx.x;
   const int warp = t >> 5, lane = t & 31, g = lane >> 2, tg = lane & 3;
   const int kr = t >> 5, cp = 2 * (t & 31);
   const bool is_root = nd.v == root;
@@ -357,7 +389,12 @@ __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, 
   fetch_codes(p, sib, col0 + cp, sc0, sc1);
   copy_rows_async(A1, p.Q, SP, kr, cp);
   copy_rows_async(A2, p.P + (size_t)c * SP * SP, SP, kr, cp);
-  level_wait();  // the parent's pre-order partial comes from the previous launch
+  level_wait();  // the messages come from the post-order launch, the previous one
+  // the parent's pre-order partial tile comes from an earlier block of this launch
+  if (!is_root) {
+    if (t == 0) tile_wait(p.done_pre + (size_t)(nd.v - p.n_tips) * p.n_tiles + tile, p.err);
+    __syncthreads();
+  }
   {
     double2 ms[2][DH], uu[2][DH];
 #pragma unroll
@@ -410,6 +447,8 @@ __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, 
 #pragma unroll
   for (int mi = 0; mi < 8; ++mi)
     *reinterpret_cast<double2*>(out + (size_t)8 * mi * p.cols_pad) = make_double2(acc2[mi][0] * f0, acc2[mi][1] * f1);
+  __syncthreads();
+  if (t == 0) tile_publish(p.done_pre + (size_t)(c - p.n_tips) * p.n_tiles + tile);
   double gsum = 0.0;
   if (g == 0) {
     const double2 w = *reinterpret_cast<const double2*>(p.weights + col0 + 8 * warp + 2 * tg);
@@ -417,7 +456,7 @@ __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, 
     if (w.y != 0.0) gsum += w.y * p.rate * num[1] / den[1];
   }
   const double sg = cta_sum(gsum, red);
-  if (t == 0) p.gpart[(size_t)blockIdx.y * p.n_branches + c] = sg;
+  if (t == 0) p.gpart[(size_t)tile * p.n_branches + c] = sg;
 }
 
 // ------------------------------------------------------------------------- tip branches

@@ -8,7 +8,7 @@ for f in sys.argv[1:]:
         continue
     r = d["roofline"]
     print(f"{f}: N={d['n_gpus']} value {d['value']:.1f}/s ({d['ms_per_step']:.4f} ms/step) e2e {d['e2e']['value']:.1f}/s ({d['e2e']['ms_per_step']:.4f} ms) "
-          f"frac {r['frac']:.3f} kernel {r['kernel_ms']:.4f} ms share {r['share_of_step']:.3f} clocks {d['clocks']['sm_mhz']} {d['clocks']['reasons']} check {d.get('check', {}).get('logl_rel_diff_vs_cpu')} {d.get('check', {}).get('grad_rel_diff_vs_cpu')}")
+          f"frac {r['frac']:.3f} kernel {r['kernel_ms']:.4f} ms share {r.get('share_of_step') or 0:.3f} clocks {d['clocks']['sm_mhz']} {d['clocks']['reasons']} check {d.get('check', {}).get('logl_rel_diff_vs_cpu')} {d.get('check', {}).get('grad_rel_diff_vs_cpu')}")
     for s in d.get("secondary", []):
         if "error" in s:
             print("   ", s["label"], "ERROR", s["error"]); continue
