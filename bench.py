@@ -417,7 +417,8 @@ SECONDARY_1GPU = [
     ("configs[0]", "jc69_20x1000", "float64", 0),
     ("configs[2] fp64", "hky_g4_flu", "float64", 0),
     ("configs[2] fp32", "hky_g4_flu", "float32", 0),
-    ("north-star gate shape (5000 taxa x 10k patterns)", "gtr_g4_5000x10k", "float64", 0),
+    ("north-star gate shape (5000 taxa x 10k patterns), GTR+G4", "gtr_g4_5000x10k", "float64", 0),
+    ("north-star gate shape (5000 taxa x 10k patterns), JC69", "jc69_5000x10k", "float64", 0),
     ("configs[4]", "codon_500x2000", "float64", 0),
 ]
 

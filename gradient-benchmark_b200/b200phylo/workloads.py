@@ -97,6 +97,8 @@ def make_workload(name: str, precision: Optional[str] = None, n_tips: Optional[i
     elif name == "gtr_g4_5000x10k":  # north-star gate shape
         w = _simulated(name, n_tips or 5000, GTR((1, 2, 1, 1, 2, 1), pi), GammaSiteModel(0.5, 4),
                        n_patterns=n_patterns or 10000, seq_seed=seq_seed)
+    elif name == "jc69_5000x10k":  # north-star gate shape, one rate category
+        w = _simulated(name, n_tips or 5000, JC69(), ConstantSiteModel(), n_patterns=n_patterns or 10000, seq_seed=seq_seed)
     elif name == "codon_500x2000":  # configs[4]: 61-state GY94-style, dense state contraction
         w = _simulated(name, n_tips or 500, CodonGY94(2.0, 0.5, pi), ConstantSiteModel(),
                        n_patterns=n_patterns or 2000, seq_seed=seq_seed, mean_branch=0.05)
@@ -113,5 +115,6 @@ WORKLOADS = {
     "hky_g4_flu": "HKY+G4, 1704 taxa x 1701 sites",
     "gtr_g4_5000x100k": "GTR+G4, 5000 taxa x 100k patterns",
     "gtr_g4_5000x10k": "GTR+G4, 5000 taxa x 10k patterns",
+    "jc69_5000x10k": "JC69, 5000 taxa x 10k patterns, fp64",
     "codon_500x2000": "GY94 codon model (61 states), 500 taxa x 2000 codon patterns",
 }

@@ -102,7 +102,14 @@ int b2p_set_topology(b2p_instance* h, const int32_t* h_triples);
  * gap/N = 15).  For n_states > 4 the bytes are state CODES (0..n_states-1; any other
  * value = missing data).  Fed by "site_pattern" (/root/reference/flu_H3N2/phylotorch-JC69.template:59-69,
  * /root/reference/flu_H3N2/physher-JC69.template:11-21).  BEAGLE: beagleSetTipStates /
- * beagleSetTipPartials. */
+ * beagleSetTipPartials.
+ * There is deliberately no b2p_set_tip_partials: every tip partial on the reference's path is a
+ * 0/1 vector built from a sequence character — torchtree's SitePattern does exactly that, and
+ * physher with "tipstates": false (/root/reference/flu_H3N2/physher-JC69.template:11) stores the
+ * same 0/1 vectors as partials instead of state indices — and a 0/1 vector over 4 states IS a
+ * mask (over more states: a code or "missing").  Real-valued tip partials (sequencing-error or
+ * uncertainty models) appear nowhere in the benchmark; they would need a float tip-row layout in
+ * the traversal kernel, which the hot path should not pay for. */
 int b2p_set_tip_states(b2p_instance* h, const uint8_t* h_masks);
 
 /* Pattern weights: h_weights double [P].  BEAGLE: beagleSetPatternWeights. */
