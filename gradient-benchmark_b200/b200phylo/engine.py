@@ -27,11 +27,15 @@ EXPORTED_SYMBOLS = (
     "b2p_set_categories", "b2p_loglik", "b2p_loglik_grad", "b2p_loglik_grad_host",
     "b2p_set_profiling", "b2p_last_kernel_ms", "b2p_kernel_ms_stats", "b2p_get_branch_partials",
     "b2p_peer_export", "b2p_peer_attach", "b2p_peer_status", "b2p_set_gradient_operator",
+    "b2p_branch_outer_products",
 )
 
 
 class EngineError(RuntimeError):
     pass
+
+
+FLAG_OUTER_PRODUCTS = 1  # B2P_FLAG_OUTER_PRODUCTS (include/b200phylo.h)
 
 
 class _Config(ctypes.Structure):
@@ -100,6 +104,7 @@ def load_library():
     lib.b2p_kernel_ms_stats.argtypes = [vp, dp, ctypes.POINTER(ctypes.c_int32)]
     lib.b2p_get_branch_partials.argtypes = [vp, ctypes.c_int32, dp]
     lib.b2p_set_gradient_operator.argtypes = [vp, dp, dp]
+    lib.b2p_branch_outer_products.argtypes = [vp, vp, vp, vp, vp, vp]
     lib.b2p_peer_export.argtypes = [vp, ctypes.c_int32, ctypes.c_char_p]
     lib.b2p_peer_attach.argtypes = [vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_char_p]
     lib.b2p_peer_status.argtypes = [vp, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
@@ -124,14 +129,20 @@ class Engine:
     """
 
     def __init__(self, n_tips: int, n_patterns: int, n_categories: int = 1,
-                 precision: str = "float64", device: int = 0, warps_per_block: int = 0, n_states: int = 4):
+                 precision: str = "float64", device: int = 0, warps_per_block: int = 0, n_states: int = 4,
+                 outer_products: bool = False):
         self._h = ctypes.c_void_p()
         self._lib = load_library()
+        self._setup = {}      # what the set_* calls were given: an outer-products twin is set up from it
+        self._twin = None
+        self._twin_version = -1
+        self._version = 0
         prec = {"float64": 64, "float32": 32, 64: 64, 32: 32}.get(precision)
         if prec is None:
             raise ValueError(f"precision must be float64 or float32, got {precision!r}")
         cfg = _Config(int(n_tips), int(n_patterns), int(n_categories), int(n_states), prec, int(device),
-                      int(warps_per_block), 0)
+                      int(warps_per_block), FLAG_OUTER_PRODUCTS if outer_products else 0)
+        self.outer_products = bool(outer_products)
         self.n_states = int(n_states)
         rc = self._lib.b2p_create(ctypes.byref(cfg), ctypes.byref(self._h))
         if rc != 0:
@@ -149,6 +160,9 @@ class Engine:
             raise EngineError(f"{what} failed ({rc}): {self._lib.b2p_last_error(self._h).decode()}")
 
     def close(self) -> None:
+        if getattr(self, "_twin", None) is not None:
+            self._twin.close()
+            self._twin = None
         if getattr(self, "_h", None) is not None and self._h:
             self._lib.b2p_destroy(self._h)
             self._h = ctypes.c_void_p()
@@ -171,6 +185,7 @@ class Engine:
             raise ValueError(f"triples must have shape ({self.n_tips - 1}, 3), got {t.shape}")
         self._check(self._lib.b2p_set_topology(
             self._h, t.ctypes.data_as(ctypes.POINTER(ctypes.c_int32))), "b2p_set_topology")
+        self._remember("topology", t)
 
     def set_tip_states(self, masks) -> None:
         m = np.ascontiguousarray(masks, dtype=np.uint8)
@@ -178,12 +193,14 @@ class Engine:
             raise ValueError(f"masks must have shape ({self.n_tips}, {self.n_patterns}), got {m.shape}")
         self._check(self._lib.b2p_set_tip_states(
             self._h, m.ctypes.data_as(ctypes.POINTER(ctypes.c_uint8))), "b2p_set_tip_states")
+        self._remember("tips", m)
 
     def set_pattern_weights(self, weights) -> None:
         w = np.ascontiguousarray(weights, dtype=np.float64)
         if w.shape != (self.n_patterns,):
             raise ValueError(f"weights must have shape ({self.n_patterns},), got {w.shape}")
         self._check(self._lib.b2p_set_pattern_weights(self._h, _dptr(w)), "b2p_set_pattern_weights")
+        self._remember("weights", w)
 
     def set_eigen(self, evec, ivec, evals, freqs) -> None:
         a = [np.ascontiguousarray(x, dtype=np.float64) for x in (evec, ivec, evals, freqs)]
@@ -191,6 +208,7 @@ class Engine:
         if a[0].shape != (n, n) or a[1].shape != (n, n) or a[2].shape != (n,) or a[3].shape != (n,):
             raise ValueError(f"eigen system must be {n}x{n}, {n}x{n}, {n}, {n}")
         self._check(self._lib.b2p_set_eigen(self._h, *map(_dptr, a)), "b2p_set_eigen")
+        self._remember("eigen", a)
 
     def set_categories(self, rates, weights) -> None:
         r = np.ascontiguousarray(rates, dtype=np.float64)
@@ -198,6 +216,7 @@ class Engine:
         if r.shape != (self.n_categories,) or w.shape != (self.n_categories,):
             raise ValueError(f"rates/weights must have shape ({self.n_categories},)")
         self._check(self._lib.b2p_set_categories(self._h, _dptr(r), _dptr(w)), "b2p_set_categories")
+        self._remember("categories", (r, w))
 
     def set_model(self, subst_model, site_model) -> None:
         e = subst_model.eigen()
@@ -224,6 +243,51 @@ class Engine:
             self._h, _dptr(bl), ctypes.byref(logl), _dptr(grad) if want_grad else None),
             "b2p_loglik_grad_host")
         return float(logl.value), grad
+
+    def _remember(self, what: str, value) -> None:
+        if self.n_states == 4 and self.precision == "float64" and self.n_categories in (1, 4):
+            self._setup[what] = value
+            self._version += 1
+
+    def supports_outer_products(self) -> bool:
+        """Whether ``branch_outer_products`` runs in one pass (4 states, fp64, 1 or 4 categories)."""
+        return self.n_states == 4 and self.precision == "float64" and self.n_categories in (1, 4)
+
+    def branch_outer_products(self, d_bl: int, d_logl: int, d_grad: Optional[int], d_outer: int, stream: int = 0) -> None:
+        """G [K][2N-2][4][4] (``b2p_branch_outer_products``) on raw device pointers, in ONE
+        evaluation.  An engine created without ``outer_products=True`` keeps a twin instance in
+        that mode (same topology, tips, weights and model; set up on first use and whenever one of
+        them changes) — the default instance keeps its faster two-columns-per-thread geometry."""
+        eng = self if self.outer_products else self._outer_twin()
+        eng._check(eng._lib.b2p_branch_outer_products(eng._h, d_bl, d_logl, d_grad, d_outer, stream),
+                   "b2p_branch_outer_products")
+
+    def _outer_twin(self) -> "Engine":
+        if not self.supports_outer_products():
+            raise EngineError("branch_outer_products needs 4 states, float64 and 1 or 4 rate categories")
+        missing = [k for k in ("topology", "tips", "weights", "eigen", "categories") if k not in self._setup]
+        if missing:
+            raise EngineError(f"branch_outer_products before {', '.join(missing)} were set")
+        if self._twin is None:
+            self._twin = Engine(self.n_tips, self.n_patterns, self.n_categories, precision="float64", device=self.device,
+                                outer_products=True)
+            self._twin_version = -1
+        if self._twin_version != self._version:
+            t, st = self._twin, self._setup
+            if t._setup.get("topology") is not st["topology"]:
+                t.set_topology(st["topology"])
+            if t._setup.get("tips") is not st["tips"]:
+                t.set_tip_states(st["tips"])
+            if t._setup.get("weights") is not st["weights"]:
+                t.set_pattern_weights(st["weights"])
+            if t._setup.get("eigen") is not st["eigen"]:
+                t.set_eigen(*st["eigen"])
+                t._setup["eigen"] = st["eigen"]
+            if t._setup.get("categories") is not st["categories"]:
+                t.set_categories(*st["categories"])
+                t._setup["categories"] = st["categories"]
+            self._twin_version = self._version
+        return self._twin
 
     def set_gradient_operator(self, op=None, scale=None) -> None:
         """Replace (Q, category rates) in the pre-order contraction by a 4x4 operator and a

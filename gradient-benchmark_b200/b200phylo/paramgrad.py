@@ -12,6 +12,8 @@ b and category k the pre-order pass holds q (everything outside the branch) and 
     dlogL/dtheta = sum_{b,k} < G_{b,k} , dP_{b,k}/dtheta P_{b,k}^{-1} >  +  root-prior term,
     G_{b,k} = sum_p (w_p / L_p) c_k q m^T                                  (4x4 per branch).
 
+``b2p_branch_outer_products`` returns all of G from ONE evaluation (the pre-order pass sums the
+outer products next to the branch gradient: 4 states, fp64, 1 or 4 categories).  Elsewhere
 ``b2p_set_gradient_operator`` makes the kernel's "gradient" output one entry of G (operator
 E_ij, one-hot category scale): 16 K evaluations fill G for all branches, whatever the number
 of parameters.  The rest is 4x4 algebra on a few thousand matrices, done here with torch so
@@ -34,14 +36,25 @@ __all__ = ["branch_outer_products", "q_matrix", "gtr_exchangeabilities", "hky_ex
            "parameter_gradients"]
 
 
-def branch_outer_products(engine: Engine, bl: torch.Tensor) -> torch.Tensor:
-    """G [K, 2N-2, 4, 4] on the device: 16 K evaluations with operators E_ij / one-hot scales."""
+def branch_outer_products(engine: Engine, bl: torch.Tensor, one_pass: Optional[bool] = None) -> torch.Tensor:
+    """G [K, 2N-2, 4, 4] on the device.
+
+    One evaluation (``b2p_branch_outer_products``: the pre-order pass sums the outer products
+    itself) where the engine supports it — 4 states, fp64, 1 or 4 rate categories — else 16 K
+    evaluations with operators E_ij / one-hot scales (``one_pass=False`` forces that route)."""
     if not bl.is_cuda:
         raise ValueError("branch lengths must live on the engine's device")
     k_cat, n_br = engine.n_categories, engine.n_branches
     bl = bl.detach().to(torch.float64).contiguous()
-    out = torch.empty(k_cat, 4, 4, 1 + n_br, dtype=torch.float64, device=bl.device)
     stream = torch.cuda.current_stream(bl.device).cuda_stream
+    if one_pass is None:
+        one_pass = engine.supports_outer_products()
+    if one_pass:
+        g = torch.empty(k_cat, n_br, 4, 4, dtype=torch.float64, device=bl.device)
+        logl = torch.empty(1, dtype=torch.float64, device=bl.device)
+        engine.branch_outer_products(bl.data_ptr(), logl.data_ptr(), None, g.data_ptr(), stream)
+        return g
+    out = torch.empty(k_cat, 4, 4, 1 + n_br, dtype=torch.float64, device=bl.device)
     op = np.zeros((4, 4))
     try:
         for k in range(k_cat):

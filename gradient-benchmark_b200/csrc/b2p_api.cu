@@ -30,6 +30,8 @@ struct b2p_instance {
   WalkGeometry wg;
   WalkPlan plan;  // records are released after upload; the statistics stay
   const void* kernel = nullptr;
+  const void* kernel_outer = nullptr;  // B2P_FLAG_OUTER_PRODUCTS: the same walk, also summing the branches' outer products
+  double* d_opart = nullptr;           // [grid][2N-2][K][16]
   // device scratch
   unsigned char* d_records = nullptr;  // round records: descriptors | issue record | matrix rows (K1 writes these)
   int* d_mat_dst = nullptr;
@@ -136,6 +138,11 @@ static const void* walk_select_nt(int nt, int cpt) {
     case 512: return (const void*)walk_kernel<T, K, 512, 1>;
     case 256: return (const void*)walk_kernel<T, K, 256, 1>;
   }
+  return nullptr;
+}
+static const void* walk_select_outer(int K, bool outer) {
+  if (K == 1) return outer ? (const void*)walk_kernel<double, 1, 512, 1, true> : (const void*)walk_kernel<double, 1, 512, 1>;
+  if (K == 4) return outer ? (const void*)walk_kernel<double, 4, 512, 1, true> : (const void*)walk_kernel<double, 4, 512, 1>;
   return nullptr;
 }
 template <typename T>
@@ -355,7 +362,7 @@ int b2p_destroy(b2p_instance* h) {
   peer_release(h);
   cudaFree(h->d_records); cudaFree(h->d_mat_dst);
   cudaFree(h->d_tips); cudaFree(h->d_tips_raw); cudaFree(h->d_tip_order); cudaFree(h->d_weights); cudaFree(h->d_msg); cudaFree(h->d_pre);
-  cudaFree(h->d_lpart); cudaFree(h->d_trace); cudaFree(h->d_gpart); cudaFree(h->d_bl_stage); cudaFree(h->d_out_stage);
+  cudaFree(h->d_lpart); cudaFree(h->d_trace); cudaFree(h->d_gpart); cudaFree(h->d_opart); cudaFree(h->d_bl_stage); cudaFree(h->d_out_stage);
   if (h->dense) {
     b2p_instance::Dense* d = h->dense;
     for (void* p : {(void*)d->evec, (void*)d->ivec, (void*)d->evals, (void*)d->q, (void*)d->qt, (void*)d->freqs, (void*)d->P,
@@ -388,6 +395,12 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
                 cfg->n_states);
   if (cfg->precision != B2P_PRECISION_F64 && cfg->precision != B2P_PRECISION_F32)
     return fail(h, B2P_ERR_ARG, "b2p_create: precision must be 64 or 32");
+  if (cfg->flags & ~B2P_FLAG_OUTER_PRODUCTS) return fail(h, B2P_ERR_ARG, "b2p_create: unknown flag bits 0x%x", cfg->flags);
+  const bool outer = (cfg->flags & B2P_FLAG_OUTER_PRODUCTS) != 0;
+  if (outer && (cfg->n_states != 4 || cfg->precision != B2P_PRECISION_F64 || (cfg->n_categories != 1 && cfg->n_categories != 4)))
+    return fail(h, B2P_ERR_UNSUPPORTED,
+                "b2p_create: B2P_FLAG_OUTER_PRODUCTS is built for 4 states, fp64 and 1 or 4 rate categories "
+                "(otherwise: b2p_set_gradient_operator, one evaluation per entry)");
   int n_dev = 0;
   cudaError_t e = cudaGetDeviceCount(&n_dev);
   if (e != cudaSuccess || n_dev == 0)
@@ -439,11 +452,15 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
     nt_force = 256;
     if (!getenv("B2P_NP")) n_copy = 2;
   }
-  bool planned = plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, ct_force, depth, n_copy, cpt, h->wg);
+  if (outer) {  // one column per thread (the 4x4 products live in registers), 512 threads, warp-aligned slots
+    nt_force = 512; n_copy = 3; cpt = 1; h->ctas_per_sm = 1;
+    smem_budget = (size_t)prop.sharedMemPerBlockOptin - 1024;
+  }
+  bool planned = plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, ct_force, depth, n_copy, cpt, h->wg, outer);
   // fp32 needs 80-96 registers per thread, so 768 threads fit (more tasks per round), with four
   // copy warps for the larger rounds (sweep: profiles/README.md, round 2: 0.227 vs 0.270 ms at the
   // flu shape).
-  if (planned && cfg->precision == B2P_PRECISION_F32 && !nt_force && !getenv("B2P_NP") && h->ctas_per_sm == 1) {
+  if (planned && !outer && cfg->precision == B2P_PRECISION_F32 && !nt_force && !getenv("B2P_NP") && h->ctas_per_sm == 1) {
     WalkGeometry g2;
     if (plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms, smem_budget, 768, ct_force, depth, 4, cpt, g2) && g2.cpt == h->wg.cpt) {
       h->wg = g2;
@@ -454,7 +471,7 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   // Copy warps: a round has about one load and one store per slot, and a warp issues a bulk copy
   // every ~100 cycles, so few slots need fewer copy warps (and a freed warp is compute threads):
   // two when that leaves at most ten slots (sweeps: profiles/README.md, round 2).
-  if (planned && !getenv("B2P_NP") && n_copy == 3 && h->wg.wn <= 10) {
+  if (planned && !outer && !getenv("B2P_NP") && n_copy == 3 && h->wg.wn <= 10) {
     WalkGeometry g2;
     if (plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, ct_force, depth, 2, cpt, g2) && g2.wn <= 10)
       h->wg = g2;
@@ -464,7 +481,7 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   // rows of every task) would take the block pool's room instead.
   if (planned && !getenv("B2P_DEPTH") && 3 * h->wg.frame_bytes <= 48 * 1024) {
     WalkGeometry g2;
-    if (plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, h->wg.ct, 2, h->wg.n_copy_warps, cpt, g2) &&
+    if (plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, h->wg.ct, 2, h->wg.n_copy_warps, cpt, g2, outer) &&
         g2.wn == h->wg.wn)
       h->wg = g2;
   }
@@ -473,7 +490,11 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
     return bail(B2P_ERR_UNSUPPORTED);
   }
   h->kernel = (cfg->precision == B2P_PRECISION_F32) ? walk_select<float>(K, h->wg.nt, h->wg.cpt) : walk_select<double>(K, h->wg.nt, h->wg.cpt);
-  if (!h->kernel) { fail(h, B2P_ERR_ARG, "b2p_create: no kernel for %d threads", h->wg.nt); return bail(B2P_ERR_ARG); }
+  if (outer) { h->kernel = walk_select_outer(K, false); h->kernel_outer = walk_select_outer(K, true); }
+  if (!h->kernel || (outer && (!h->kernel_outer || h->wg.nt != 512 || h->wg.cpt != 1))) {
+    fail(h, B2P_ERR_ARG, "b2p_create: no kernel for %d threads", h->wg.nt);
+    return bail(B2P_ERR_ARG);
+  }
   // function attributes are process-wide: never lower what another live instance asked for
   static std::map<const void*, size_t> smem_asked;
   static std::mutex smem_asked_lock;
@@ -482,6 +503,11 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
     size_t& asked = smem_asked[h->kernel];
     asked = std::max(asked, h->wg.smem);
     e = cudaFuncSetAttribute(h->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asked);
+    if (e == cudaSuccess && h->kernel_outer) {
+      size_t& asked2 = smem_asked[h->kernel_outer];
+      asked2 = std::max(asked2, h->wg.smem);
+      e = cudaFuncSetAttribute(h->kernel_outer, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asked2);
+    }
   }
   if (e != cudaSuccess) {
     fail(h, B2P_ERR_CUDA, "cudaFuncSetAttribute(smem=%zu): %s", h->wg.smem, cudaGetErrorString(e));
@@ -503,6 +529,7 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   if ((rc = dev_alloc(h, (char**)&h->d_pre, part_bytes))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_lpart, sizeof(double) * h->wg.grid))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_gpart, sizeof(double) * (size_t)h->wg.grid * n_br))) return bail(rc);
+  if (outer && (rc = dev_alloc(h, &h->d_opart, sizeof(double) * (size_t)h->wg.grid * n_br * K * 16))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_bl_stage, sizeof(double) * n_br))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_out_stage, sizeof(double) * (n_br + 1)))) return bail(rc);
   if ((e = cudaMallocHost((void**)&h->h_pin_in, sizeof(double) * n_br)) != cudaSuccess ||
@@ -538,6 +565,7 @@ static void fill_walk_params(const b2p_instance* h, bool grad, WalkParams<T>& p)
   p.records = h->d_records;
   p.msg = (unsigned char*)h->d_msg; p.pre = (unsigned char*)h->d_pre; p.tips = h->d_tips;
   p.weights = h->d_weights; p.lpart = h->d_lpart; p.gpart = h->d_gpart; p.trace = h->d_trace;
+  p.opart = h->d_opart; p.off_outer = g.off_outer; p.outer_row = g.outer_row; p.off_ostage = g.off_ostage;
   p.dbg = 0;
 #ifdef B2P_DBG
   if (const char* e = getenv("B2P_DBG")) p.dbg = atoi(e);
@@ -577,7 +605,7 @@ static PeerArgs peer_args(b2p_instance* h) {
 
 template <typename T>
 static cudaError_t launch_eval(b2p_instance* h, const double* d_bl, double* d_logl, double* d_grad,
-                               cudaStream_t st) {
+                               cudaStream_t st, double* d_outer = nullptr) {
   const int N = h->cfg.n_tips, K = h->cfg.n_categories;
   const int n_br = 2 * N - 2;
   const int total = n_br * K * 16;
@@ -586,9 +614,9 @@ static cudaError_t launch_eval(b2p_instance* h, const double* d_bl, double* d_lo
   const int slot = (int)(h->prof_count % b2p_instance::kProfRing);
   if (h->profiling) cudaEventRecord(h->ev0[slot], st);
   WalkParams<T> wp;
-  fill_walk_params(h, d_grad != nullptr, wp);
+  fill_walk_params(h, d_grad != nullptr || d_outer != nullptr, wp);
   void* args[] = {&wp};
-  cudaError_t e = cudaLaunchKernel(h->kernel, dim3(h->wg.grid), dim3(h->wg.nt), args, h->wg.smem, st);
+  cudaError_t e = cudaLaunchKernel(d_outer ? h->kernel_outer : h->kernel, dim3(h->wg.grid), dim3(h->wg.nt), args, h->wg.smem, st);
   if (e != cudaSuccess) return e;
   if (h->profiling) { cudaEventRecord(h->ev1[slot], st); ++h->prof_count; }
   const int nb = d_grad ? n_br : 0;
@@ -597,6 +625,10 @@ static cudaError_t launch_eval(b2p_instance* h, const double* d_bl, double* d_lo
     reduce_exchange_kernel<<<(nb + 31) / 32 + 1, 512, 0, st>>>(h->d_gpart, h->d_lpart, h->wg.grid, nb, d_grad, d_logl, pa);
   } else {
     reduce_kernel<<<(nb + 31) / 32 + 1, 512, 0, st>>>(h->d_gpart, h->d_lpart, h->wg.grid, nb, d_grad, d_logl);
+  }
+  if (d_outer) {
+    const int n_out = n_br * K * 16;
+    reduce_outer_kernel<<<(n_out + 255) / 256, 256, 0, st>>>(h->d_opart, h->wg.grid, n_br, K, d_outer);
   }
   return cudaGetLastError();
 }
@@ -785,6 +817,19 @@ int b2p_loglik(b2p_instance* h, const double* d_bl, double* d_logl, void* stream
 int b2p_loglik_grad(b2p_instance* h, const double* d_bl, double* d_logl, double* d_grad, void* stream) {
   if (h && !d_grad) return fail(h, B2P_ERR_ARG, "b2p_loglik_grad: null d_grad");
   return eval_common(h, d_bl, d_logl, d_grad, stream);
+}
+
+int b2p_branch_outer_products(b2p_instance* h, const double* d_bl, double* d_logl, double* d_grad, double* d_outer,
+                              void* stream) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (!h->kernel_outer) return fail(h, B2P_ERR_ARG, "b2p_branch_outer_products: the instance was created without B2P_FLAG_OUTER_PRODUCTS");
+  if (!d_bl || !d_logl || !d_outer) return fail(h, B2P_ERR_ARG, "b2p_branch_outer_products: null device pointer");
+  if (h->grad_op_set) return fail(h, B2P_ERR_ARG, "b2p_branch_outer_products: a gradient operator is set (b2p_set_gradient_operator)");
+  if (h->peer.attached) return fail(h, B2P_ERR_UNSUPPORTED, "b2p_branch_outer_products: not with attached peers (sum the K x (2N-2) x 16 values with the caller's all-reduce)");
+  cudaError_t e = launch_eval<double>(h, d_bl, d_logl, d_grad, (cudaStream_t)stream, d_outer);
+  if (e != cudaSuccess) return fail(h, B2P_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
+  return B2P_OK;
 }
 
 int b2p_loglik_grad_host(b2p_instance* h, const double* h_bl, double* h_logl, double* h_grad) {

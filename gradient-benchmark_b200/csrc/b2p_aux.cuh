@@ -72,6 +72,18 @@ __global__ void tile_tips_kernel(const uint8_t* __restrict__ raw, const int* __r
   out[idx] = code;
 }
 
+// Outer-product mode: sum the per-CTA parts [grid][2N-2][K][16] in CTA order (deterministic) and
+// write them as [K][2N-2][4][4] — the layout b200phylo/paramgrad.py contracts.
+__global__ void reduce_outer_kernel(const double* __restrict__ opart, int grid, int n_br, int K, double* __restrict__ out) {
+  const int n = n_br * K * 16;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double s = 0.0;
+  for (int c = 0; c < grid; ++c) s += __ldcs(opart + (size_t)c * n + i);
+  const int e = i & 15, k = (i >> 4) % K, b = (i >> 4) / K;
+  out[((size_t)k * n_br + b) * 16 + e] = s;
+}
+
 // ---------------------------------------------------------------------------- K4
 // grad[b] = sum_g gpart[g][b];  logl = sum_g lpart[g].  Fixed summation order.
 __global__ void __launch_bounds__(512) reduce_kernel(const double* __restrict__ gpart,

@@ -56,6 +56,12 @@ struct WalkGeometry {
       off_scount = 0, off_freq = 0, off_pool = 0;
   int n_pool = 0;
   size_t smem = 0;
+  // Outer-product mode (b2p_branch_outer_products): slots start on warp boundaries (a warp's 32
+  // lanes reduce their 4x4 outer products by shuffles) and every compute warp owns a row of
+  // K * 32 sums per round parity in shared memory.
+  bool outer = false;
+  int off_outer = 0, outer_row = 0;  // bytes of one warp's row
+  int off_ostage = 0;                // 4 KB per compute warp: the columns' operands of the tensor-core sums
 };
 
 inline int align16(int x) { return (x + 15) & ~15; }
@@ -101,6 +107,11 @@ inline int layout_walk(WalkGeometry& g, size_t smem_max) {
   g.off_gbuf = off; off += 2 * wn * g.ts * 16;  // one (sum_a, sum_b) pair per compute thread
   g.off_scount = off; off += align16(g.ct * 4);
   off = (off + 127) & ~127;
+  if (g.outer) {
+    g.outer_row = K * 32 * 8;
+    g.off_outer = off; off += 2 * (g.nt / 32 - g.n_copy_warps) * g.outer_row;
+    g.off_ostage = off; off += (g.nt / 32 - g.n_copy_warps) * 4096;
+  }
   g.off_freq = off; off += g.blk;  // the root's parent-side partial: the frequencies, for every column
   off = (off + 127) & ~127;
   g.off_pool = off;
@@ -115,9 +126,10 @@ inline int layout_walk(WalkGeometry& g, size_t smem_max) {
 // (2 halves the per-column cost of descriptors, matrix reads and address arithmetic; it
 // needs the 128 registers a 512-thread CTA leaves each thread).
 inline bool plan_geometry_cpt(int n_tips, int n_cols, int K, int elem, int n_sms, size_t smem_max, int nt_force,
-                              int ct_force, int depth, int n_copy_warps, int cpt, WalkGeometry& g) {
+                              int ct_force, int depth, int n_copy_warps, int cpt, WalkGeometry& g, bool outer = false) {
   const bool packed = (32 % K) == 0;
   if (cpt == 2 && !packed) return false;
+  if (outer && (cpt != 1 || !packed)) return false;
   const int cpw = packed ? 32 : (32 / K) * K;
   const int q = K * cpt;  // tile widths are multiples of this
   // widest tile: 144 columns (fp64) — two waves of 136-column tiles beat three of 96 at 40 000
@@ -129,7 +141,7 @@ inline bool plan_geometry_cpt(int n_tips, int n_cols, int K, int elem, int n_sms
   ct = std::max(ct, ct_min);
   ct = std::min(ct, std::max(q, (n_cols + q - 1) / q * q));
   if (ct_force > 0) ct = std::max(q, ct_force / q * q);
-  const int ts = packed ? ct / cpt : ((ct + cpw - 1) / cpw) * 32;  // threads per slot
+  const int ts = packed && !outer ? ct / cpt : ((ct + cpw - 1) / cpw) * 32;  // threads per slot
   const int nts1[4] = {1024, 768, 512, 256}, nts2[4] = {512, 768, 640, 256};
   for (int nt : (cpt == 2 ? nts2 : nts1)) {
     if (nt == 0) continue;
@@ -140,6 +152,7 @@ inline bool plan_geometry_cpt(int n_tips, int n_cols, int K, int elem, int n_sms
       g = WalkGeometry();
       g.nt = nt; g.ct = ct; g.ts = ts; g.cpw = cpw; g.wn = wn; g.elem = elem; g.K = K; g.cpt = cpt;
       g.depth = std::max(1, std::min(depth, 3)); g.stages = g.depth + 1; g.n_copy_warps = n_copy_warps;
+      g.outer = outer;
       const int n_pool = layout_walk(g, smem_max);
       // enough blocks for one full round of operands in flight per stage plus the round's results
       if (n_pool >= std::max(3 * g.stages + 4, 4 * wn)) break;
@@ -152,7 +165,8 @@ inline bool plan_geometry_cpt(int n_tips, int n_cols, int K, int elem, int n_sms
   return false;
 }
 inline bool plan_geometry(int n_tips, int n_cols, int K, int elem, int n_sms, size_t smem_max, int nt_force,
-                          int ct_force, int depth, int n_copy_warps, int cpt_want, WalkGeometry& g) {
+                          int ct_force, int depth, int n_copy_warps, int cpt_want, WalkGeometry& g, bool outer = false) {
+  if (outer) return plan_geometry_cpt(n_tips, n_cols, K, elem, n_sms, smem_max, nt_force, ct_force, depth, n_copy_warps, 1, g, true);
   if (cpt_want == 2 &&
       plan_geometry_cpt(n_tips, n_cols, K, elem, n_sms, smem_max, nt_force, ct_force, depth, n_copy_warps, 2, g))
     return true;
@@ -198,6 +212,7 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
   out = WalkPlan();
   out.wn_eff = wn_eff;
   const int n_nodes = 2 * N - 1, root = 2 * N - 2;
+  if (N > (1 << 23)) { why = "more than 2^23 tips"; return false; }
   if ((unsigned long long)(N - 1) * (unsigned long long)g.blk > 0xFFFFFFF0ull ||
       (16ull * N + 128ull) * 2ull * (unsigned long long)g.wn * (unsigned long long)g.ct_pad > 0xFFFFFFF0ull) {
     why = "tile too large for 32-bit copy offsets";
@@ -643,6 +658,8 @@ inline bool plan_walk(int N, const int32_t* triples, const WalkGeometry& g, int 
         if (v != root) { e.a_v = mat_at(mrow_own[v]); e.dst0 = blk_off(dst_post[v]); }
       } else {
         e.a_v = v == root ? (uint32_t)g.off_freq : blk_off(src[so + 2]);
+        e.ids_lo = (uint32_t)l | ((uint32_t)r << 24);
+        e.ids_hi = (uint16_t)((uint32_t)r >> 8);
         if (l >= N) { e.dst0 = blk_off(dst_pre[2 * (size_t)v]); e.m_l = (uint16_t)(mat_at(mrow_pre[2 * (size_t)v]) / 16); }
         if (r >= N) { e.dst1 = blk_off(dst_pre[2 * (size_t)v + 1]); e.m_r = (uint16_t)(mat_at(mrow_pre[2 * (size_t)v + 1]) / 16); }
       }

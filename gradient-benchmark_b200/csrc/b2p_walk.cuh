@@ -59,8 +59,12 @@ struct WalkParams {
   const double* weights;      // [P]
   double* lpart;              // [grid]
   double* gpart;              // [grid][2N-2]
+  double* opart;              // outer-product mode: [grid][2N-2][K][16] per-CTA sums of (w / L) c_k q m^T
+  int off_outer, outer_row;   // outer-product mode: shared-memory rows of the compute warps, [2][warps][K * 32] doubles
+  int off_ostage;             // outer-product mode: [warps] 4 KB staging rows of the tensor-core sums
   long long* trace;           // debug build (-DB2P_TRACE_CLOCKS): [2][rounds][8] clock stamps of CTA 0
-  int dbg;                    // debug build (-DB2P_DBG): 1 skip the fold, 2 skip the stores, 4 skip the tasks (timing experiments)
+  int dbg;                    // debug build (-DB2P_DBG): 1 skip the fold, 2 skip the stores, 4 skip the tasks, 8 skip the
+                              // outer products' fold, 16 skip their sums (timing experiments)
   T q[16];
   double freqs[4];
   double cat_w[kMaxCatW];
@@ -325,9 +329,17 @@ __device__ __forceinline__ void post_task(const WalkParams<T>& p, const WalkThre
 
 // ------------------------------------------------------------------- pre-order task
 //   q_l = u_v o m_r, q_r = u_v o m_l ; L = q_l . m_l ; dL/dt_l = r_k q_l.(Q m_l) ; u_l = P_l^T q_l (same for r)
-template <typename T, int K, int CPT>
+// OUTER (b2p_branch_outer_products): the warp also sums, per category, the 4x4 outer products
+//   (w / L) c_k q_l m_l^T  and  (w / L) c_k q_r m_r^T
+// over its columns into its shared-memory row `orow` ([K][32]: entries 0-15 the left branch's
+// matrix, 16-31 the right's) — what every model-parameter gradient is a contraction of
+// (b200phylo/paramgrad.py).  Slots are warp-aligned in this mode, so all 32 lanes belong to the
+// same task and lanes of the same category differ by multiples of K.  `ostage`: the warp's 4 KB
+// of staging rows (32 columns x 8 doubles, twice).
+template <typename T, int K, int CPT, bool OUTER = false>
 __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThread<T, CPT>& th, const TaskDesc& d, bool live,
-                                         const unsigned (&code_l)[CPT], const unsigned (&code_r)[CPT], double& gl, double& gr) {
+                                         const unsigned (&code_l)[CPT], const unsigned (&code_r)[CPT], double& gl, double& gr,
+                                         unsigned orow = 0u, unsigned ostage = 0u) {
   T ql[CPT][4], qr[CPT][4];
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
@@ -364,6 +376,54 @@ __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThrea
     const double inv = (live && dd > 0.0) ? (K == 1 ? th.w[c] * p.rates[0] : th.w[c]) * fast_rcp(dd) : 0.0;
     gl += live ? (double)numl * inv : 0.0;
     gr += live ? (double)numr * inv : 0.0;
+#ifdef B2P_DBG
+    if (!(p.dbg & 16))
+#endif
+    if constexpr (OUTER) {
+      static_assert(!OUTER || (CPT == 1 && (K == 1 || K == 4)), "outer-product mode: one column per thread, K = 1 or 4");
+      // Sum over the warp's columns of (a q)(m)^T on the fp64 tensor cores: with the columns as
+      // the contraction index, A = [a q_l | a q_r]^T (8 x columns) and B = [m_l | m_r] (columns x 8)
+      // give C = A B whose diagonal 4x4 blocks are the two outer-product sums (the off-diagonal
+      // blocks are ignored).  Every lane puts its column's 8 + 8 values into the warp's staging
+      // rows; each mma.sync (m8n8k4) then takes four columns of one category.
+      const double a = (live && dd > 0.0) ? (K == 1 ? th.w[c] : th.w[c] * (double)th.cw) * fast_rcp(dd) : 0.0;
+      const unsigned row = (unsigned)th.lane ^ (((unsigned)th.lane >> 2) & 1u);  // neighbours of a category alternate bank halves
+      const unsigned wr = ostage + row * 64, sw = (row >> 1) & 3u;               // 16-byte chunks XOR-swizzled: conflict-free both ways
+      sts_d2(wr + ((0u ^ sw) << 4), a * (double)ql[c][0], a * (double)ql[c][1]);
+      sts_d2(wr + ((1u ^ sw) << 4), a * (double)ql[c][2], a * (double)ql[c][3]);
+      sts_d2(wr + ((2u ^ sw) << 4), a * (double)qr[c][0], a * (double)qr[c][1]);
+      sts_d2(wr + ((3u ^ sw) << 4), a * (double)qr[c][2], a * (double)qr[c][3]);
+      // lanes without a column: zeros (their operands are whatever their zero descriptor points at)
+      sts_d2(wr + 2048 + ((0u ^ sw) << 4), live ? (double)ma[0] : 0.0, live ? (double)ma[1] : 0.0);
+      sts_d2(wr + 2048 + ((1u ^ sw) << 4), live ? (double)ma[2] : 0.0, live ? (double)ma[3] : 0.0);
+      sts_d2(wr + 2048 + ((2u ^ sw) << 4), live ? (double)mb[0] : 0.0, live ? (double)mb[1] : 0.0);
+      sts_d2(wr + 2048 + ((3u ^ sw) << 4), live ? (double)mb[2] : 0.0, live ? (double)mb[3] : 0.0);
+      __syncwarp();
+      const unsigned g = (unsigned)th.lane >> 2, t = (unsigned)th.lane & 3u;
+      double acc[K][2];
+#pragma unroll
+      for (int k = 0; k < K; ++k) acc[k][0] = acc[k][1] = 0.0;
+#pragma unroll
+      for (int dd8 = 0; dd8 < 8; ++dd8) {
+        // K = 1: columns 4 d .. 4 d + 3;  K = 4: category d % 4, columns k + 4 (t + 4 (d / 4))
+        const unsigned col = K == 1 ? 4u * dd8 + t : (unsigned)(dd8 & 3) + 4u * (t + 4u * (unsigned)(dd8 >> 2));
+        const unsigned r2 = col ^ ((col >> 2) & 1u);
+        const unsigned at = ostage + r2 * 64 + (((g >> 1) ^ ((r2 >> 1) & 3u)) << 4) + ((g & 1u) << 3);
+        double av, bv;
+        asm volatile("ld.shared.f64 %0, [%1];" : "=d"(av) : "r"(at));
+        asm volatile("ld.shared.f64 %0, [%1];" : "=d"(bv) : "r"(at + 2048));
+        asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                     : "+d"(acc[K == 1 ? 0 : (dd8 & 3)][0]), "+d"(acc[K == 1 ? 0 : (dd8 & 3)][1])
+                     : "d"(av), "d"(bv));
+      }
+      // lane (g, t) holds C[g][2t], C[g][2t+1]: rows 0-3 x columns 0-3 = the left branch's matrix
+      // (entries 0-15 of the warp's row), rows 4-7 x columns 4-7 = the right branch's (16-31)
+      if ((g < 4) == (t < 2)) {
+        const unsigned e = (g & 3u) * 4u + (t & 1u) * 2u + (g < 4 ? 0u : 16u);
+#pragma unroll
+        for (int k = 0; k < K; ++k) sts_d2(orow + (k * 32 + e) * 8, acc[k][0], acc[k][1]);
+      }
+    }
   }
   // pre-order partials of the internal children: u_c = P_c^T q_c (rescaled when tiny).  K == 1: a
   // tip child skips the product; K != 1: every lane computes it (the rescale inside is a warp-wide
@@ -442,7 +502,30 @@ __device__ __forceinline__ void fold_slots(const WalkParams<T>& p, unsigned gbuf
   }
 }
 
-template <typename T, int K, int NT, int CPT>
+// Outer-product mode: add the rows of a slot's warps (fixed order) and put the K * 32 sums
+// into the CTA's part of `opart` — lane j handles entries j, j + 32, ...; the whole warp works
+// on slot s.  ids: the slot's (left, right) branch ids; anything negative: no pre-order task.
+template <typename T, int K>
+__device__ __forceinline__ void fold_outer(const WalkParams<T>& p, unsigned rows, int s, int lane, bool first_tile, int2 ids) {
+  if (ids.x < 0 || ids.y < 0) return;
+  const int wps = p.ts >> 5;
+  const unsigned base = rows + s * wps * p.outer_row;
+#pragma unroll
+  for (int j0 = 0; j0 < K * 32; j0 += 32) {
+    const int j = j0 + lane;
+    double v = 0.0;
+    for (int r = 0; r < wps; ++r) {
+      double x;
+      asm volatile("ld.shared.f64 %0, [%1];" : "=d"(x) : "r"(base + r * p.outer_row + j * 8));
+      v += x;
+    }
+    const int k = j >> 5, e = j & 31;
+    double* gp = p.opart + (((size_t)blockIdx.x * p.n_branches + (e < 16 ? ids.x : ids.y)) * K + k) * 16 + (e & 15);
+    if (first_tile) *gp = v; else atomicAdd(gp, v);
+  }
+}
+
+template <typename T, int K, int NT, int CPT, bool OUTER = false>
 __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __grid_constant__ WalkParams<T> p) {
   extern __shared__ __align__(128) unsigned char smem[];
   __shared__ double red[NT / 32];
@@ -484,6 +567,11 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
 #pragma unroll
     for (int i = 0; i < 4; ++i) f[i] = (T)p.freqs[i];
     sts_vec(sbase + p.off_freq + c * 16, p.plane, f);
+  }
+  if (!copier && s < p.wn && !in_slot) {
+    // warp-aligned slots: the lanes past the tile's last column never write their pair of sums
+    sts_d2(sbase + p.off_gbuf + (s * p.ts + tt) * 16, 0.0, 0.0);
+    sts_d2(sbase + p.off_gbuf + ((p.wn + s) * p.ts + tt) * 16, 0.0, 0.0);
   }
   unsigned phase_bits = 0;
   double ll_acc = 0.0;
@@ -582,6 +670,13 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
 #else
             fold_slots<T, true>(p, sbase + p.off_gbuf + (par ^ 1) * p.wn * p.ts * 16, s0, np, lane, first_tile, ir + 16, nullptr, ll_acc);
 #endif
+          if constexpr (OUTER)
+#ifdef B2P_DBG
+            if (!(p.dbg & 8))
+#endif
+            for (int s1 = pw; s1 < p.wn; s1 += np)
+              fold_outer<T, K>(p, sbase + p.off_outer + (par ^ 1) * first_copy_warp * p.outer_row, s1, lane, first_tile,
+                               lds_i2(ir + 16 + s1 * 8));
         }
 #ifdef B2P_TRACE_CLOCKS
         if (tr) trow[6] = clock64();
@@ -609,7 +704,7 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
         // K == 1: lanes without a task skip it.  K != 1: the task exchanges values over the K
         // category lanes with full-warp shuffles, so a warp runs it as a whole (lanes without a
         // task compute on a zero descriptor and store nothing) or, with no task at all, skips it.
-        const bool run = K == 1 ? live : __any_sync(0xffffffffu, live);
+        const bool run = (K == 1 && !OUTER) ? live : __any_sync(0xffffffffu, live);
         if (run) {
           const unsigned gslot = o_gslot + par * p.wn * p.ts * 16;
           double ga = 0.0, gb2 = 0.0;  // post-order (root): log-likelihood term, 0; pre-order: the two gradient sums
@@ -619,7 +714,9 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
             post_task<T, K, CPT>(p, th, d, live, root_round, scount, col, code_l, code_r, ga);
             if (live && is_root) sts_d2(gslot, ga, 0.0);
           } else {
-            pre_task<T, K, CPT>(p, th, d, live, code_l, code_r, ga, gb2);
+            pre_task<T, K, CPT, OUTER>(p, th, d, live, code_l, code_r, ga, gb2,
+                                       OUTER ? sbase + p.off_outer + (par * first_copy_warp + warp) * p.outer_row : 0u,
+                                       OUTER ? sbase + p.off_ostage + warp * 4096 : 0u);
             if (live) sts_d2(gslot, ga, gb2);
           }
         }
@@ -644,6 +741,10 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
       const int2* tail = reinterpret_cast<const int2*>(p.records + p.tail_base);
       for (int s0 = warp - first_copy_warp; s0 < p.wn; s0 += 4 * p.n_copy_warps)
         fold_slots<T, false>(p, sbase + p.off_gbuf + ((R - 1) & 1) * p.wn * p.ts * 16, s0, p.n_copy_warps, lane, first_tile, 0u, tail, ll_acc);
+      if constexpr (OUTER)
+        if (R > p.rounds_post)
+          for (int s1 = warp - first_copy_warp; s1 < p.wn; s1 += p.n_copy_warps)
+            fold_outer<T, K>(p, sbase + p.off_outer + ((R - 1) & 1) * first_copy_warp * p.outer_row, s1, lane, first_tile, __ldg(tail + s1));
       // (the last round leaves nothing to store: the root's post-order task writes no message,
       //  and a pre-order partial is stored only when a later round loads it back)
       asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");

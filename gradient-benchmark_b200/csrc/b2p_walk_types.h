@@ -43,8 +43,9 @@ struct WalkDesc {
   uint32_t a_v;          // post: the node's own matrix rows; pre: parent-side partial (root: frequency block)
   uint32_t dst0, dst1;   // post: dst0 = message of the node; pre: partials of the internal children
   uint16_t m_l, m_r;     // pre: matrix rows of the internal children, offset / 16
-  uint16_t flags, pad0;
-  uint32_t pad1;
+  uint16_t flags, ids_hi;
+  uint32_t ids_lo;       // pre: the children's branch ids, 24 bits each: left = ids_lo & 0xffffff,
+                         // right = ids_lo >> 24 | ids_hi << 8 (the outer-product mode's reduction reads them)
 };
 static_assert(sizeof(WalkDesc) == 32, "WalkDesc must be 32 bytes");
 

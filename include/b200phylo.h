@@ -55,7 +55,7 @@ typedef struct b2p_config {
   int32_t precision;    /* B2P_PRECISION_F64 | B2P_PRECISION_F32 (partials / matrices) */
   int32_t device;       /* CUDA device ordinal */
   int32_t warps_per_block; /* 0 = auto; threads per CTA / 32 (32, 24, 16 or 8) */
-  int32_t flags;        /* reserved, 0 */
+  int32_t flags;        /* 0, or B2P_FLAG_OUTER_PRODUCTS */
 } b2p_config;
 
 typedef struct b2p_info {
@@ -159,6 +159,21 @@ int b2p_loglik_grad_host(b2p_instance* h, const double* h_bl, double* h_logl,
  * a few thousand 4x4 products the caller does (b200phylo/paramgrad.py).  h_op: 16 doubles,
  * row-major (NULL restores Q and the rates); h_scale: K doubles (NULL = all 1). */
 int b2p_set_gradient_operator(b2p_instance* h, const double* h_op, const double* h_scale);
+
+/* All of G in ONE evaluation.  An instance created with B2P_FLAG_OUTER_PRODUCTS in
+ * b2p_config.flags (4 states, fp64, 1 or 4 rate categories) runs the walk with one column per
+ * thread and warp-aligned tasks; b2p_branch_outer_products then also sums, in the pre-order
+ * pass, the two 4x4 outer products of every task over its columns (warp shuffles, then one
+ * shared-memory row per warp, folded a round later like the branch gradient) and writes
+ *     d_outer [K][2N-2][4][4]:  G_{b,k}[i][j] = sum_p (w_p / L_p) c_k q_{b,k,i} m_{b,k,j}
+ * next to logL and (if d_grad is not NULL) the branch gradient.  Such an instance still serves
+ * b2p_loglik / b2p_loglik_grad, a few percent slower than a default one (one column per
+ * thread).  Replaces the 16 K evaluations of b2p_set_gradient_operator; same reference rows:
+ * torchtree differentiates these parameters by autograd of the whole recursion
+ * (/root/reference/modules/micro.nf:52, /root/reference/plot.Rmd:305). */
+#define B2P_FLAG_OUTER_PRODUCTS 1
+int b2p_branch_outer_products(b2p_instance* h, const double* d_bl, double* d_logl, double* d_grad,
+                              double* d_outer, void* cuda_stream);
 
 /* Multi-GPU, one process per GPU: pattern shards per rank, results summed
  * over ranks.  With peers attached the final reduction kernel of every evaluation IS the

@@ -73,6 +73,60 @@ def test_parameter_gradients_match_autograd_of_pruning(kind, gamma):
     eng.close()
 
 
+@pytest.mark.parametrize("name,n_tips,n_patterns,gamma", [
+    ("hky_g4_flu", 36, 240, True), ("hky_g4_flu", 36, 240, False), ("hky_g4_flu", 7, 5, True), ("hky_g4_flu", 2, 33, False),
+    ("hky_g4_flu", 120, 3000, True),      # several tiles per CTA: the parts are added across tiles
+    ("jc69_1000x10k", 300, 20011, False),  # more tiles than SMs at one category, ragged last tile
+    ("hky_g4_flu", 200, 6007, True)])
+def test_outer_products_in_one_pass_match_the_operator_route(name, n_tips, n_patterns, gamma):
+    """``b2p_branch_outer_products`` (one evaluation) against the 16 K evaluations of
+    ``b2p_set_gradient_operator``: the same sums in another order — 1e-11 of the largest entry
+    of each branch's matrix — plus logL / the branch gradient of the outer-products instance
+    against the default one (other tile widths: 1e-11 / 1e-9)."""
+    from b200phylo import paramgrad as pg
+    base = make_workload(name, n_tips=n_tips, n_patterns=n_patterns)
+    site = GammaSiteModel(0.45, 4) if gamma else ConstantSiteModel()
+    w = Workload("outer", base.tree, base.patterns, HKY(3.1, (0.33, 0.17, 0.24, 0.26)), site)
+    eng = make_engine(w)
+    bl = torch.tensor(w.tree.branch_lengths, dtype=torch.float64, device="cuda")
+    g16 = pg.branch_outer_products(eng, bl, one_pass=False)
+    g1 = pg.branch_outer_products(eng, bl, one_pass=True)
+    assert g1.shape == g16.shape == (w.n_categories, 2 * n_tips - 2, 4, 4)
+    scale = g16.abs().amax(dim=(2, 3), keepdim=True).clamp_min(1e-300)
+    assert float(((g1 - g16).abs() / scale).max()) < 1e-11
+    # twice in a row gives the same bits (fixed summation order), also after a model change
+    assert torch.equal(pg.branch_outer_products(eng, bl), g1)
+    eng.set_model(HKY(1.9, (0.33, 0.17, 0.24, 0.26)), site)
+    g2 = pg.branch_outer_products(eng, bl)
+    g2_16 = pg.branch_outer_products(eng, bl, one_pass=False)
+    assert float(((g2 - g2_16).abs() / g2_16.abs().amax(dim=(2, 3), keepdim=True).clamp_min(1e-300)).max()) < 1e-11
+    assert not torch.equal(g2, g1)
+    # the outer-products instance's own logL and branch gradient
+    twin = eng._outer_twin()
+    logl0, grad0 = eng.loglik_grad_host(w.tree.branch_lengths)
+    logl1, grad1 = twin.loglik_grad_host(w.tree.branch_lengths)
+    assert rel_err(logl1, logl0) < 1e-11 and grad_err(grad1, grad0) < 1e-9
+    out = torch.zeros(2 * n_tips - 1, dtype=torch.float64, device="cuda")
+    g3 = torch.empty_like(g2)
+    twin.branch_outer_products(bl.data_ptr(), out.data_ptr(), out.data_ptr() + 8, g3.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert torch.equal(g3, g2)
+    assert rel_err(float(out[0]), logl0) < 1e-11 and grad_err(out[1:].cpu().numpy(), grad0) < 1e-9
+    eng.close()
+
+
+def test_outer_products_unsupported_shapes_say_so():
+    from b200phylo.engine import Engine, EngineError
+    with pytest.raises(EngineError, match="OUTER_PRODUCTS"):
+        Engine(10, 100, 3, outer_products=True)
+    with pytest.raises(EngineError, match="OUTER_PRODUCTS"):
+        Engine(10, 100, 4, precision="float32", outer_products=True)
+    eng = Engine(10, 100, 4)
+    with pytest.raises(EngineError, match="before"):
+        eng.branch_outer_products(0, 0, None, 0)
+    eng.close()
+
+
 def test_gamma_shape_gradient_by_chain_rule():
     """d logL / d alpha = sum_k (d logL / d r_k) (d r_k / d alpha), the rates' derivative taken
     numerically on the host (the discretised-Gamma quantiles have no closed form)."""

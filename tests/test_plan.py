@@ -20,8 +20,11 @@ def plan_check():
     return BIN
 
 
-# N, shape (0 random joins, 1 caterpillar, 2 balanced), seed, ct, K, elem, depth, nt, cpt
+# N, shape (0 random joins, 1 caterpillar, 2 balanced), seed, ct, K, elem, depth, nt, cpt[, outer-product mode]
 CASES = [
+    (1000, 0, 1, 68, 1, 8, 1, 512, 1, 1),   # outer-product mode at the headline shape: 68 columns in 96 threads
+    (1704, 0, 2, 48, 4, 8, 1, 512, 1, 1),
+    (300, 2, 5, 136, 4, 8, 2, 512, 1, 1),
     (1000, 0, 1, 68, 1, 8, 1, 0, 2),     # headline geometry
     (1000, 0, 1, 68, 1, 8, 1, 0, 1),
     (1000, 0, 7, 68, 1, 8, 2, 0, 2),
@@ -39,7 +42,8 @@ CASES = [
 
 @pytest.mark.parametrize("case", CASES)
 def test_plan_is_consistent(plan_check, case):
-    n, shape, seed, ct, k, elem, depth, nt, cpt = case
-    out = subprocess.run([plan_check, *map(str, (n, shape, seed, ct, k, elem, SMEM, depth, nt, cpt))],
+    n, shape, seed, ct, k, elem, depth, nt, cpt = case[:9]
+    outer = case[9] if len(case) > 9 else 0
+    out = subprocess.run([plan_check, *map(str, (n, shape, seed, ct, k, elem, SMEM, depth, nt, cpt, outer))],
                          capture_output=True, text=True).stdout.strip()
     assert out.startswith("OK"), out

@@ -52,7 +52,16 @@ int main(int argc, char** argv) {
             elem = atoi(argv[6]), smem = atoi(argv[7]), depth = atoi(argv[8]), nt = argc > 9 ? atoi(argv[9]) : 0, cpt = argc > 10 ? atoi(argv[10]) : 1;
   std::vector<int32_t> tr = random_triples(N, shape, seed);
   WalkGeometry g;
-  if (!plan_geometry(N, ct * 148, K, elem, 148, smem, nt, ct, depth, 2, cpt, g)) FAIL("geometry");
+  const bool outer = argc > 11 && atoi(argv[11]) != 0;  // outer-product mode: warp-aligned slots + a row per compute warp
+  if (!plan_geometry(N, ct * 148, K, elem, 148, smem, nt, ct, depth, outer ? 3 : 2, cpt, g, outer)) FAIL("geometry");
+  if (outer) {
+    if (g.ts % 32 || g.cpt != 1 || !g.outer || g.ts < g.ct) FAIL("outer mode: slots are not warp-aligned");
+    const int rows_end = g.off_outer + 2 * (g.nt / 32 - g.n_copy_warps) * g.outer_row;
+    if (g.outer_row != K * 32 * 8 || g.off_outer < g.off_scount + g.ct * 4 || rows_end > g.off_ostage ||
+        g.off_ostage % 16 || g.off_ostage + (g.nt / 32 - g.n_copy_warps) * 4096 > g.off_freq)
+      FAIL("outer mode: rows overlap their neighbours");
+    if (g.wn * g.ts > g.nt - 32 * g.n_copy_warps) FAIL("outer mode: slots reach into the copy warps");
+  }
   WalkPlan plan;
   std::string why;
   if (!plan_walk_auto(N, tr.data(), g, plan, why)) FAIL("plan: %s", why.c_str());
@@ -192,6 +201,7 @@ int main(int argc, char** argv) {
         if (ids[s].a < 0 || ids[s].b < 0 || parent[ids[s].a] != parent[ids[s].b]) FAIL("ids");
         v = parent[ids[s].a];
         if (left[v] != ids[s].a || right[v] != ids[s].b) FAIL("ids order");
+        if ((int)(e.ids_lo & 0xffffffu) != ids[s].a || (int)((e.ids_lo >> 24) | ((uint32_t)e.ids_hi << 8)) != ids[s].b) FAIL("descriptor branch ids");
         if (done_pre[v]++) FAIL("pre task %d twice", v);
         if (v != root && !done_pre[parent[v]]) FAIL("pre task %d before its parent", v);
       }
