@@ -627,8 +627,8 @@ static cudaError_t launch_eval(b2p_instance* h, const double* d_bl, double* d_lo
     reduce_kernel<<<(nb + 31) / 32 + 1, 512, 0, st>>>(h->d_gpart, h->d_lpart, h->wg.grid, nb, d_grad, d_logl);
   }
   if (d_outer) {
-    const int n_out = n_br * K * 16;
-    reduce_outer_kernel<<<(n_out + 255) / 256, 256, 0, st>>>(h->d_opart, h->wg.grid, n_br, K, d_outer);
+    const int n_pairs = n_br * K * 8;
+    reduce_outer_kernel<<<(n_pairs + 63) / 64, dim3(64, 8), 0, st>>>(h->d_opart, h->wg.grid, n_br, K, d_outer);
   }
   return cudaGetLastError();
 }

@@ -73,15 +73,39 @@ __global__ void tile_tips_kernel(const uint8_t* __restrict__ raw, const int* __r
 }
 
 // Outer-product mode: sum the per-CTA parts [grid][2N-2][K][16] in CTA order (deterministic) and
-// write them as [K][2N-2][4][4] — the layout b200phylo/paramgrad.py contracts.
-__global__ void reduce_outer_kernel(const double* __restrict__ opart, int grid, int n_br, int K, double* __restrict__ out) {
-  const int n = n_br * K * 16;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  double s = 0.0;
-  for (int c = 0; c < grid; ++c) s += __ldcs(opart + (size_t)c * n + i);
-  const int e = i & 15, k = (i >> 4) % K, b = (i >> 4) / K;
-  out[((size_t)k * n_br + b) * 16 + e] = s;
+// write them as [K][2N-2][4][4] — the layout b200phylo/paramgrad.py contracts.  A block takes 64
+// pairs of outputs; its 8 thread rows each add a contiguous eighth of the parts (independent
+// 16-byte loads, eight in flight), then row 0 adds the eight sums in order.
+__global__ void __launch_bounds__(512) reduce_outer_kernel(const double* __restrict__ opart, int grid, int n_br, int K,
+                                                           double* __restrict__ out) {
+  __shared__ double2 part[8][64];
+  const int n2 = n_br * K * 8;  // pairs
+  const int i = blockIdx.x * 64 + threadIdx.x, y = threadIdx.y;
+  const int per = (grid + 7) / 8, c0 = y * per, c1 = min(grid, c0 + per);
+  double2 s = make_double2(0.0, 0.0);
+  if (i < n2) {
+    const double2* src = reinterpret_cast<const double2*>(opart) + i;
+    int c = c0;
+    for (; c + 8 <= c1; c += 8) {
+      double2 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = __ldcs(src + (size_t)(c + u) * n2);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) { s.x += v[u].x; s.y += v[u].y; }
+    }
+    for (; c < c1; ++c) {
+      const double2 v = __ldcs(src + (size_t)c * n2);
+      s.x += v.x; s.y += v.y;
+    }
+  }
+  part[y][threadIdx.x] = s;
+  __syncthreads();
+  if (y == 0 && i < n2) {
+#pragma unroll
+    for (int u = 1; u < 8; ++u) { s.x += part[u][threadIdx.x].x; s.y += part[u][threadIdx.x].y; }
+    const int e = (2 * i) & 15, k = (i >> 3) % K, b = (i >> 3) / K;
+    *reinterpret_cast<double2*>(out + ((size_t)k * n_br + b) * 16 + e) = s;
+  }
 }
 
 // ---------------------------------------------------------------------------- K4

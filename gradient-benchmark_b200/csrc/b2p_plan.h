@@ -58,7 +58,7 @@ struct WalkGeometry {
   size_t smem = 0;
   // Outer-product mode (b2p_branch_outer_products): slots start on warp boundaries (a warp's 32
   // lanes reduce their 4x4 outer products by shuffles) and every compute warp owns a row of
-  // K * 32 sums per round parity in shared memory.
+  // K * 32 sums in shared memory.
   bool outer = false;
   int off_outer = 0, outer_row = 0;  // bytes of one warp's row
   int off_ostage = 0;                // 4 KB per compute warp: the columns' operands of the tensor-core sums
@@ -109,7 +109,7 @@ inline int layout_walk(WalkGeometry& g, size_t smem_max) {
   off = (off + 127) & ~127;
   if (g.outer) {
     g.outer_row = K * 32 * 8;
-    g.off_outer = off; off += 2 * (g.nt / 32 - g.n_copy_warps) * g.outer_row;
+    g.off_outer = off; off += (g.nt / 32 - g.n_copy_warps) * g.outer_row;
     g.off_ostage = off; off += (g.nt / 32 - g.n_copy_warps) * 4096;
   }
   g.off_freq = off; off += g.blk;  // the root's parent-side partial: the frequencies, for every column

@@ -60,7 +60,7 @@ struct WalkParams {
   double* lpart;              // [grid]
   double* gpart;              // [grid][2N-2]
   double* opart;              // outer-product mode: [grid][2N-2][K][16] per-CTA sums of (w / L) c_k q m^T
-  int off_outer, outer_row;   // outer-product mode: shared-memory rows of the compute warps, [2][warps][K * 32] doubles
+  int off_outer, outer_row;   // outer-product mode: shared-memory rows of the compute warps, [warps][K * 32] doubles
   int off_ostage;             // outer-product mode: [warps] 4 KB staging rows of the tensor-core sums
   long long* trace;           // debug build (-DB2P_TRACE_CLOCKS): [2][rounds][8] clock stamps of CTA 0
   int dbg;                    // debug build (-DB2P_DBG): 1 skip the fold, 2 skip the stores, 4 skip the tasks, 8 skip the
@@ -221,6 +221,7 @@ struct WalkThread {
 // The 32-byte descriptor as the planner wrote it (b2p_walk_types.h: WalkDesc), unpacked.
 struct TaskDesc {
   unsigned a_l, a_r, a_v, dst0, dst1, m_l, m_r, flags;
+  unsigned id_l, id_r;  // pre-order: the children's branch ids (used by the outer-product mode only)
 };
 __device__ __forceinline__ TaskDesc unpack_desc(const uint4 d0, const uint4 d1) {
   TaskDesc d;
@@ -228,6 +229,7 @@ __device__ __forceinline__ TaskDesc unpack_desc(const uint4 d0, const uint4 d1) 
   d.dst1 = d1.x;
   d.m_l = (d1.y & 0xffffu) * 16u; d.m_r = (d1.y >> 16) * 16u;
   d.flags = d1.z & 0xffffu;
+  d.id_l = d1.w & 0xffffffu; d.id_r = (d1.w >> 24) | ((d1.z >> 16) << 8);
   return d;
 }
 
@@ -331,15 +333,25 @@ __device__ __forceinline__ void post_task(const WalkParams<T>& p, const WalkThre
 //   q_l = u_v o m_r, q_r = u_v o m_l ; L = q_l . m_l ; dL/dt_l = r_k q_l.(Q m_l) ; u_l = P_l^T q_l (same for r)
 // OUTER (b2p_branch_outer_products): the warp also sums, per category, the 4x4 outer products
 //   (w / L) c_k q_l m_l^T  and  (w / L) c_k q_r m_r^T
-// over its columns into its shared-memory row `orow` ([K][32]: entries 0-15 the left branch's
-// matrix, 16-31 the right's) — what every model-parameter gradient is a contraction of
+// over its columns into its shared-memory row ([K][32]: entries 0-15 the left branch's matrix,
+// 16-31 the right's) — what every model-parameter gradient is a contraction of
 // (b200phylo/paramgrad.py).  Slots are warp-aligned in this mode, so all 32 lanes belong to the
-// same task and lanes of the same category differ by multiples of K.  `ostage`: the warp's 4 KB
-// of staging rows (32 columns x 8 doubles, twice).
+// same task and lanes of the same category differ by multiples of K.  At the end of the task the
+// slot's warps meet at a named barrier and add their rows (fixed order) into the CTA's part of
+// `opart`, each warp a share of the categories.
+struct OuterCtx {
+  unsigned rows;    // shared-memory rows of the slot's warps (the slot's first warp first)
+  unsigned row;     // this warp's row
+  unsigned stage;   // this warp's 4 KB of staging rows (32 columns x 8 doubles, twice)
+  int wps, r, bar;  // warps per slot, this warp's index in its slot, the slot's barrier id
+  bool first_tile;
+  double* part;     // the CTA's part of opart
+};
 template <typename T, int K, int CPT, bool OUTER = false>
 __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThread<T, CPT>& th, const TaskDesc& d, bool live,
                                          const unsigned (&code_l)[CPT], const unsigned (&code_r)[CPT], double& gl, double& gr,
-                                         unsigned orow = 0u, unsigned ostage = 0u) {
+                                         const OuterCtx& oc = OuterCtx()) {
+  const unsigned orow = oc.row, ostage = oc.stage;
   T ql[CPT][4], qr[CPT][4];
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
@@ -388,7 +400,9 @@ __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThrea
       // rows; each mma.sync (m8n8k4) then takes four columns of one category.
       const double a = (live && dd > 0.0) ? (K == 1 ? th.w[c] : th.w[c] * (double)th.cw) * fast_rcp(dd) : 0.0;
       const unsigned row = (unsigned)th.lane ^ (((unsigned)th.lane >> 2) & 1u);  // neighbours of a category alternate bank halves
-      const unsigned wr = ostage + row * 64, sw = (row >> 1) & 3u;               // 16-byte chunks XOR-swizzled: conflict-free both ways
+      // 16-byte chunks XOR-swizzled so that the stores (8 lanes x 16 bytes per phase) and the loads
+      // below (four rows x 32 bytes per half-warp, at K = 4 rows 8 apart) are both conflict-free
+      const unsigned wr = ostage + row * 64, sw = ((((row >> 1) ^ (row >> 3)) & 1u) << 1) | ((row >> 2) & 1u);
       sts_d2(wr + ((0u ^ sw) << 4), a * (double)ql[c][0], a * (double)ql[c][1]);
       sts_d2(wr + ((1u ^ sw) << 4), a * (double)ql[c][2], a * (double)ql[c][3]);
       sts_d2(wr + ((2u ^ sw) << 4), a * (double)qr[c][0], a * (double)qr[c][1]);
@@ -400,21 +414,34 @@ __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThrea
       sts_d2(wr + 2048 + ((3u ^ sw) << 4), live ? (double)mb[2] : 0.0, live ? (double)mb[3] : 0.0);
       __syncwarp();
       const unsigned g = (unsigned)th.lane >> 2, t = (unsigned)th.lane & 3u;
-      double acc[K][2];
-#pragma unroll
-      for (int k = 0; k < K; ++k) acc[k][0] = acc[k][1] = 0.0;
+      // all sixteen loads first, then the products: two independent accumulation chains per category
+      double av[8], bv[8];
 #pragma unroll
       for (int dd8 = 0; dd8 < 8; ++dd8) {
         // K = 1: columns 4 d .. 4 d + 3;  K = 4: category d % 4, columns k + 4 (t + 4 (d / 4))
         const unsigned col = K == 1 ? 4u * dd8 + t : (unsigned)(dd8 & 3) + 4u * (t + 4u * (unsigned)(dd8 >> 2));
         const unsigned r2 = col ^ ((col >> 2) & 1u);
-        const unsigned at = ostage + r2 * 64 + (((g >> 1) ^ ((r2 >> 1) & 3u)) << 4) + ((g & 1u) << 3);
-        double av, bv;
-        asm volatile("ld.shared.f64 %0, [%1];" : "=d"(av) : "r"(at));
-        asm volatile("ld.shared.f64 %0, [%1];" : "=d"(bv) : "r"(at + 2048));
+        const unsigned s2 = ((((r2 >> 1) ^ (r2 >> 3)) & 1u) << 1) | ((r2 >> 2) & 1u);
+        const unsigned at = ostage + r2 * 64 + (((g >> 1) ^ s2) << 4) + ((g & 1u) << 3);
+        asm volatile("ld.shared.f64 %0, [%1];" : "=d"(av[dd8]) : "r"(at));
+        asm volatile("ld.shared.f64 %0, [%1];" : "=d"(bv[dd8]) : "r"(at + 2048));
+      }
+      constexpr int NA = K == 1 ? 2 : K;  // accumulators: K = 1 splits its eight products into two chains
+      double acc2[NA][2];
+#pragma unroll
+      for (int k = 0; k < NA; ++k) acc2[k][0] = acc2[k][1] = 0.0;
+#pragma unroll
+      for (int dd8 = 0; dd8 < 8; ++dd8) {
+        const int ai = K == 1 ? (dd8 & 1) : (dd8 & 3);
         asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
-                     : "+d"(acc[K == 1 ? 0 : (dd8 & 3)][0]), "+d"(acc[K == 1 ? 0 : (dd8 & 3)][1])
-                     : "d"(av), "d"(bv));
+                     : "+d"(acc2[ai][0]), "+d"(acc2[ai][1])
+                     : "d"(av[dd8]), "d"(bv[dd8]));
+      }
+      double acc[K][2];
+#pragma unroll
+      for (int k = 0; k < K; ++k) {
+        acc[k][0] = K == 1 ? acc2[0][0] + acc2[NA - 1][0] : acc2[k][0];
+        acc[k][1] = K == 1 ? acc2[0][1] + acc2[NA - 1][1] : acc2[k][1];
       }
       // lane (g, t) holds C[g][2t], C[g][2t+1]: rows 0-3 x columns 0-3 = the left branch's matrix
       // (entries 0-15 of the warp's row), rows 4-7 x columns 4-7 = the right branch's (16-31)
@@ -445,6 +472,27 @@ __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThrea
     for (int c = 0; c < CPT; ++c) {
       (void)rescale<K>(out_r, th.lane, th.kk, uc[c]);
       if (out_r) sts_vec(th.sc + d.dst1 + c * th.dB, th.plane, uc[c]);
+    }
+  }
+  if constexpr (OUTER) {
+#ifdef B2P_DBG
+    if (p.dbg & 8) return;
+#endif
+    // the slot's rows are complete once all its warps are here (one warp: its own lanes)
+    if (oc.wps > 1) asm volatile("bar.sync %0, %1;" ::"r"(oc.bar), "r"(oc.wps * 32) : "memory");
+    else __syncwarp();
+    // lane 0 always holds a column of the slot: its descriptor is the slot's
+    const unsigned id_l = __shfl_sync(0xffffffffu, d.id_l, 0), id_r = __shfl_sync(0xffffffffu, d.id_r, 0);
+    double* gp = oc.part + (size_t)(th.lane < 16 ? id_l : id_r) * (K * 16) + (th.lane & 15);
+    for (int k = oc.r; k < K; k += oc.wps) {
+      double v = 0.0;
+      for (int r = 0; r < oc.wps; ++r) {
+        double x;
+        asm volatile("ld.shared.f64 %0, [%1];" : "=d"(x) : "r"(oc.rows + r * p.outer_row + (k * 32 + th.lane) * 8));
+        v += x;
+      }
+      // a branch is written once per tile: plain store for the CTA's first tile, then adds in tile order
+      if (oc.first_tile) gp[k * 16] = v; else atomicAdd(gp + k * 16, v);
     }
   }
 }
@@ -499,29 +547,6 @@ __device__ __forceinline__ void fold_slots(const WalkParams<T>& p, unsigned gbuf
       double* gp = p.gpart + (size_t)blockIdx.x * p.n_branches + id;
       if (first_tile) *gp = v; else atomicAdd(gp, v);
     }
-  }
-}
-
-// Outer-product mode: add the rows of a slot's warps (fixed order) and put the K * 32 sums
-// into the CTA's part of `opart` — lane j handles entries j, j + 32, ...; the whole warp works
-// on slot s.  ids: the slot's (left, right) branch ids; anything negative: no pre-order task.
-template <typename T, int K>
-__device__ __forceinline__ void fold_outer(const WalkParams<T>& p, unsigned rows, int s, int lane, bool first_tile, int2 ids) {
-  if (ids.x < 0 || ids.y < 0) return;
-  const int wps = p.ts >> 5;
-  const unsigned base = rows + s * wps * p.outer_row;
-#pragma unroll
-  for (int j0 = 0; j0 < K * 32; j0 += 32) {
-    const int j = j0 + lane;
-    double v = 0.0;
-    for (int r = 0; r < wps; ++r) {
-      double x;
-      asm volatile("ld.shared.f64 %0, [%1];" : "=d"(x) : "r"(base + r * p.outer_row + j * 8));
-      v += x;
-    }
-    const int k = j >> 5, e = j & 31;
-    double* gp = p.opart + (((size_t)blockIdx.x * p.n_branches + (e < 16 ? ids.x : ids.y)) * K + k) * 16 + (e & 15);
-    if (first_tile) *gp = v; else atomicAdd(gp, v);
   }
 }
 
@@ -670,13 +695,6 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
 #else
             fold_slots<T, true>(p, sbase + p.off_gbuf + (par ^ 1) * p.wn * p.ts * 16, s0, np, lane, first_tile, ir + 16, nullptr, ll_acc);
 #endif
-          if constexpr (OUTER)
-#ifdef B2P_DBG
-            if (!(p.dbg & 8))
-#endif
-            for (int s1 = pw; s1 < p.wn; s1 += np)
-              fold_outer<T, K>(p, sbase + p.off_outer + (par ^ 1) * first_copy_warp * p.outer_row, s1, lane, first_tile,
-                               lds_i2(ir + 16 + s1 * 8));
         }
 #ifdef B2P_TRACE_CLOCKS
         if (tr) trow[6] = clock64();
@@ -714,9 +732,16 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
             post_task<T, K, CPT>(p, th, d, live, root_round, scount, col, code_l, code_r, ga);
             if (live && is_root) sts_d2(gslot, ga, 0.0);
           } else {
-            pre_task<T, K, CPT, OUTER>(p, th, d, live, code_l, code_r, ga, gb2,
-                                       OUTER ? sbase + p.off_outer + (par * first_copy_warp + warp) * p.outer_row : 0u,
-                                       OUTER ? sbase + p.off_ostage + warp * 4096 : 0u);
+            OuterCtx oc{};
+            if constexpr (OUTER) {
+              // the warp's slot (slots are warp-aligned; lanes past the tile's last column have sl = 0)
+              const int ws = (warp * 32) / p.ts;
+              oc.wps = p.ts >> 5; oc.r = warp - ws * oc.wps; oc.bar = 1 + ws; oc.first_tile = first_tile;
+              oc.rows = sbase + p.off_outer + ws * oc.wps * p.outer_row; oc.row = oc.rows + oc.r * p.outer_row;
+              oc.stage = sbase + p.off_ostage + warp * 4096;
+              oc.part = p.opart + (size_t)blockIdx.x * p.n_branches * (K * 16);
+            }
+            pre_task<T, K, CPT, OUTER>(p, th, d, live, code_l, code_r, ga, gb2, oc);
             if (live) sts_d2(gslot, ga, gb2);
           }
         }
@@ -741,10 +766,6 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
       const int2* tail = reinterpret_cast<const int2*>(p.records + p.tail_base);
       for (int s0 = warp - first_copy_warp; s0 < p.wn; s0 += 4 * p.n_copy_warps)
         fold_slots<T, false>(p, sbase + p.off_gbuf + ((R - 1) & 1) * p.wn * p.ts * 16, s0, p.n_copy_warps, lane, first_tile, 0u, tail, ll_acc);
-      if constexpr (OUTER)
-        if (R > p.rounds_post)
-          for (int s1 = warp - first_copy_warp; s1 < p.wn; s1 += p.n_copy_warps)
-            fold_outer<T, K>(p, sbase + p.off_outer + ((R - 1) & 1) * first_copy_warp * p.outer_row, s1, lane, first_tile, __ldg(tail + s1));
       // (the last round leaves nothing to store: the root's post-order task writes no message,
       //  and a pre-order partial is stored only when a later round loads it back)
       asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");

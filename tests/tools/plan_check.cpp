@@ -56,11 +56,12 @@ int main(int argc, char** argv) {
   if (!plan_geometry(N, ct * 148, K, elem, 148, smem, nt, ct, depth, outer ? 3 : 2, cpt, g, outer)) FAIL("geometry");
   if (outer) {
     if (g.ts % 32 || g.cpt != 1 || !g.outer || g.ts < g.ct) FAIL("outer mode: slots are not warp-aligned");
-    const int rows_end = g.off_outer + 2 * (g.nt / 32 - g.n_copy_warps) * g.outer_row;
+    const int rows_end = g.off_outer + (g.nt / 32 - g.n_copy_warps) * g.outer_row;
     if (g.outer_row != K * 32 * 8 || g.off_outer < g.off_scount + g.ct * 4 || rows_end > g.off_ostage ||
         g.off_ostage % 16 || g.off_ostage + (g.nt / 32 - g.n_copy_warps) * 4096 > g.off_freq)
       FAIL("outer mode: rows overlap their neighbours");
     if (g.wn * g.ts > g.nt - 32 * g.n_copy_warps) FAIL("outer mode: slots reach into the copy warps");
+    if (g.wn > 14) FAIL("outer mode: more slots than named barriers");
   }
   WalkPlan plan;
   std::string why;
