@@ -33,7 +33,7 @@ import torch
 from .engine import Engine
 
 __all__ = ["branch_outer_products", "q_matrix", "gtr_exchangeabilities", "hky_exchangeabilities",
-           "parameter_gradients"]
+           "parameter_gradients", "surrogate"]
 
 
 def branch_outer_products(engine: Engine, bl: torch.Tensor, one_pass: Optional[bool] = None) -> torch.Tensor:
@@ -96,6 +96,21 @@ def hky_exchangeabilities(kappa: torch.Tensor) -> torch.Tensor:
     return torch.stack([one, k, one, one, k, one])
 
 
+def surrogate(g: torch.Tensor, t: torch.Tensor, q: torch.Tensor, freqs: torch.Tensor, rates: torch.Tensor,
+              root_child: int) -> torch.Tensor:
+    """S(q, freqs, rates, t) = sum <G P^{-T}, P(q, rates, t)> + sum_i c_i pi_i with G held constant:
+    its gradient at the parameters G was computed at is dlogL/d(q, freqs, rates) (and, through P,
+    the branch gradient).  ``g`` [K, 2N-2, 4, 4], ``t`` [2N-2], ``q`` [4, 4], ``rates`` [K]."""
+    # P_{k,b} = exp(Q r_k t_b), differentiable; its inverse only as a constant
+    qt = q[None, None] * (rates[:, None] * t[None, :])[..., None, None]
+    p = torch.linalg.matrix_exp(qt)
+    with torch.no_grad():
+        p_inv_t = torch.linalg.matrix_exp(-qt).transpose(-1, -2)
+        w = g @ p_inv_t                       # G P^{-T}
+        c = torch.diagonal(g[:, int(root_child)], dim1=-2, dim2=-1).sum(0) / freqs   # root prior: dlogL/dpi_i
+    return (w * p).sum() + (c * freqs).sum()
+
+
 def parameter_gradients(engine: Engine, bl: torch.Tensor, root_children: Sequence[int],
                         model: Callable[[], Dict[str, torch.Tensor]], g: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Surrogate whose ``backward()`` leaves dlogL/dtheta in the ``.grad`` of every leaf tensor
@@ -109,14 +124,5 @@ def parameter_gradients(engine: Engine, bl: torch.Tensor, root_children: Sequenc
     if g is None:
         g = branch_outer_products(engine, bl)
     m = model()
-    q, freqs, rates = m["q"], m["freqs"], m["rates"]
     t = bl if bl.requires_grad else bl.detach()
-    # P_{k,b} = exp(Q r_k t_b), differentiable; its inverse only as a constant
-    qt = q[None, None] * (rates[:, None] * t[None, :])[..., None, None]
-    p = torch.linalg.matrix_exp(qt)
-    with torch.no_grad():
-        p_inv_t = torch.linalg.matrix_exp(-qt).transpose(-1, -2)
-        w = g @ p_inv_t                       # G P^{-T}
-        l = int(root_children[0])
-        c = torch.diagonal(g[:, l], dim1=-2, dim2=-1).sum(0) / freqs   # root prior: dlogL/dpi_i
-    return (w * p).sum() + (c * freqs).sum()
+    return surrogate(g, t, m["q"], m["freqs"], m["rates"], root_children[0])

@@ -27,13 +27,14 @@ import numpy as np
 import torch
 
 from .alignment import Alignment, SitePattern, compress_alignment
+from .diffmodels import DifferentiableGTR, DifferentiableHKY, DifferentiableWeibullSiteModel, is_differentiable
 from .engine import Engine, EngineError
 from .parallel import allreduce_sum_, attach_peers, rank_world, shard_bounds
 from .sitemodel import ConstantSiteModel, GammaSiteModel, WeibullSiteModel
 from .substitution import GTR, HKY, JC69, SubstitutionModel
 from .tree import Tree
 
-__all__ = ["TreeLikelihoodModel", "TreeLikelihoodFunction", "UnrootedTreeModel",
+__all__ = ["TreeLikelihoodModel", "TreeLikelihoodFunction", "TreeLikelihoodParameterFunction", "UnrootedTreeModel",
            "StrictClockModel", "Parameter", "TransformedParameter"]
 
 
@@ -187,6 +188,55 @@ class TreeLikelihoodFunction(torch.autograd.Function):
         return (out if out.dtype == ctx.in_dtype else out.to(ctx.in_dtype)), None
 
 
+class TreeLikelihoodParameterFunction(torch.autograd.Function):
+    """logL(branch lengths, Q, frequencies, category rates): gradients w.r.t. all four from ONE
+    engine evaluation.
+
+    ``forward`` calls ``b2p_branch_outer_products`` — log-likelihood, branch gradient and the
+    per-branch outer products G_{b,k} = sum_p (w_p / L_p) c_k q m^T in one pass — and ``backward``
+    contracts G with dP/d(Q, rates) and adds the root-prior term for the frequencies
+    (``paramgrad.surrogate``).  torchtree gets the same numbers by autograd of the whole pruning
+    recursion (/root/reference/modules/micro.nf:52 ``--gtr``)."""
+
+    @staticmethod
+    def forward(ctx, branch_lengths, q, freqs, rates, model: "TreeLikelihoodModel"):
+        eng = model.engine
+        dev = torch.device(f"cuda:{eng.device}")
+        bl = branch_lengths.detach().to(dev, torch.float64).contiguous()
+        if bl.dim() != 1 or bl.shape[0] != eng.n_branches:
+            raise ValueError(f"branch_lengths must have shape ({eng.n_branches},), got {tuple(bl.shape)}")
+        out = torch.empty(1 + eng.n_branches, dtype=torch.float64, device=dev)
+        g = torch.empty(eng.n_categories, eng.n_branches, 4, 4, dtype=torch.float64, device=dev)
+        eng.branch_outer_products(bl.data_ptr(), out.data_ptr(), out.data_ptr() + 8, g.data_ptr(),
+                                  torch.cuda.current_stream(dev).cuda_stream)
+        ctx.save_for_backward(bl, q.detach().to(dev), freqs.detach().to(dev), rates.detach().to(dev), out[1:], g)
+        ctx.root_child = int(model.tree_model.post_triples[-1][1])
+        ctx.in_devices = (branch_lengths.device, q.device, freqs.device, rates.device)
+        ctx.in_dtype = branch_lengths.dtype
+        return out[0].to(branch_lengths.device, branch_lengths.dtype)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        from .paramgrad import surrogate
+        bl, q, freqs, rates, g_bl, g = ctx.saved_tensors
+        need = ctx.needs_input_grad
+        out = [None, None, None, None, None]
+        go = grad_output.to(g_bl.device, torch.float64)
+        if need[0]:
+            out[0] = (go * g_bl).to(ctx.in_devices[0], ctx.in_dtype)
+        if need[1] or need[2] or need[3]:
+            with torch.enable_grad():
+                leaves = [x.detach().requires_grad_(n) for x, n in zip((q, freqs, rates), need[1:4])]
+                s = surrogate(g, bl, *leaves, ctx.root_child)
+                wanted = [x for x in leaves if x.requires_grad]
+                grads = list(torch.autograd.grad(s, wanted, allow_unused=True))
+            for i, x in enumerate(leaves):
+                if x.requires_grad:
+                    gx = grads.pop(0)
+                    out[1 + i] = None if gx is None else (go * gx).to(ctx.in_devices[1 + i])
+        return tuple(out)
+
+
 class TreeLikelihoodModel:
     """Tree + site patterns + substitution model + site model (+ clock) → logL tensor.
 
@@ -256,7 +306,29 @@ class TreeLikelihoodModel:
         return bl
 
     def __call__(self, *args, **kwargs) -> torch.Tensor:
+        if torch.is_grad_enabled() and (is_differentiable(self.subst_model) or is_differentiable(self.site_model)):
+            return self._call_with_model_parameters()
+        if hasattr(self.subst_model, "differentiable_parameters") or hasattr(self.site_model, "differentiable_parameters"):
+            self.update_model()  # tensors may have changed since the last call
         return TreeLikelihoodFunction.apply(self._scaled_branch_lengths(), self)
+
+    def _call_with_model_parameters(self) -> torch.Tensor:
+        """A substitution- or site-model parameter asks for a gradient: one pass that also returns
+        the per-branch outer products (``TreeLikelihoodParameterFunction``)."""
+        if self.world_size > 1:
+            raise EngineError("gradients w.r.t. model parameters are computed on one GPU (no pattern shards yet)")
+        if not self.engine.supports_outer_products():
+            raise EngineError("gradients w.r.t. model parameters need 4 states, float64 and 1 or 4 rate categories")
+        self.update_model()
+        dev = torch.device(f"cuda:{self.engine.device}")
+        sm, st = self.subst_model, self.site_model
+        if hasattr(sm, "q_tensor"):
+            q, freqs = sm.q_tensor(), sm.frequencies_tensor()
+        else:
+            e = sm.eigen()
+            q, freqs = torch.tensor(e.q, dtype=torch.float64, device=dev), torch.tensor(e.freqs, dtype=torch.float64, device=dev)
+        rates = st.rates_tensor() if hasattr(st, "rates_tensor") else torch.tensor(np.asarray(st.rates), dtype=torch.float64, device=dev)
+        return TreeLikelihoodParameterFunction.apply(self._scaled_branch_lengths(), q, freqs, rates, self)
 
     def log_likelihood(self) -> float:
         with torch.no_grad():
@@ -266,6 +338,9 @@ class TreeLikelihoodModel:
         out = list(self.tree_model.parameters())
         if self.clock_model is not None:
             out += list(self.clock_model.parameters())
+        for m in (self.subst_model, self.site_model):
+            if hasattr(m, "parameters"):
+                out += list(m.parameters())
         return out
 
     def close(self) -> None:
@@ -390,13 +465,30 @@ def _values_from_json(spec, dic) -> np.ndarray:
     return np.asarray(spec, dtype=np.float64).reshape(-1)
 
 
-def _subst_model_from_json(spec, dic=None) -> SubstitutionModel:
+def _object_or_tensor(spec, dic):
+    if isinstance(spec, (str, dict)):
+        return _parameter_from_json(spec, dic)
+    return torch.as_tensor(spec, dtype=torch.float64).reshape(-1)
+
+
+def _subst_model_from_json(spec, dic=None):
     dic = {} if dic is None else dic
     kind = (spec.get("type") or "").split(".")[-1].upper()
     freqs = spec.get("frequencies")
+    if kind in ("GTR", "HKY") and any(isinstance(spec.get(k), (str, dict)) for k in ("rates", "kappa", "frequencies")):
+        freqs = None  # handled below: the model keeps the Parameter objects
     freqs = tuple(_values_from_json(freqs, dic)) if freqs is not None else (0.25,) * 4
     if kind == "JC69":
         return JC69()
+    # parameters given as Parameter objects (or ids of them): the model keeps the objects, so that
+    # whoever holds them (an optimiser, a variational block) changes the model and gets gradients
+    is_obj = lambda x: isinstance(x, (str, dict))  # noqa: E731
+    if kind == "GTR" and (is_obj(spec.get("rates")) or is_obj(spec.get("frequencies"))):
+        return DifferentiableGTR(spec.get("id"), _object_or_tensor(spec.get("rates", [1.0] * 6), dic),
+                                 _object_or_tensor(spec.get("frequencies", [0.25] * 4), dic))
+    if kind == "HKY" and (is_obj(spec.get("kappa")) or is_obj(spec.get("frequencies"))):
+        return DifferentiableHKY(spec.get("id"), _object_or_tensor(spec.get("kappa", [1.0]), dic),
+                                 _object_or_tensor(spec.get("frequencies", [0.25] * 4), dic))
     if kind == "HKY":
         return HKY(float(_values_from_json(spec.get("kappa", 1.0), dic)[0]), freqs)
     if kind == "GTR":
@@ -409,6 +501,8 @@ def _site_model_from_json(spec, dic=None):
     kind = (spec.get("type") or "ConstantSiteModel").split(".")[-1]
     if kind == "ConstantSiteModel":
         return ConstantSiteModel()
+    if kind == "WeibullSiteModel" and isinstance(spec.get("shape"), (str, dict)):
+        return DifferentiableWeibullSiteModel(spec.get("id"), _parameter_from_json(spec["shape"], dic), int(spec.get("categories", 4)))
     if kind in ("GammaSiteModel", "WeibullSiteModel"):
         shape = float(_values_from_json(spec.get("shape", 0.5), dic)[0])
         if kind == "WeibullSiteModel":

@@ -56,9 +56,9 @@ struct WalkGeometry {
       off_scount = 0, off_freq = 0, off_pool = 0;
   int n_pool = 0;
   size_t smem = 0;
-  // Outer-product mode (b2p_branch_outer_products): slots start on warp boundaries (a warp's 32
-  // lanes reduce their 4x4 outer products by shuffles) and every compute warp owns a row of
-  // K * 32 sums in shared memory.
+  // Outer-product mode (b2p_branch_outer_products): one column per thread, at least 32 threads per
+  // slot (a warp then holds columns of at most two slots), at most 14 slots (a named barrier
+  // each); every compute warp owns 4 KB of staging rows and two rows of K * 32 sums.
   bool outer = false;
   int off_outer = 0, outer_row = 0;  // bytes of one warp's row
   int off_ostage = 0;                // 4 KB per compute warp: the columns' operands of the tensor-core sums
@@ -109,7 +109,7 @@ inline int layout_walk(WalkGeometry& g, size_t smem_max) {
   off = (off + 127) & ~127;
   if (g.outer) {
     g.outer_row = K * 32 * 8;
-    g.off_outer = off; off += (g.nt / 32 - g.n_copy_warps) * g.outer_row;
+    g.off_outer = off; off += 2 * (g.nt / 32 - g.n_copy_warps) * g.outer_row;
     g.off_ostage = off; off += (g.nt / 32 - g.n_copy_warps) * 4096;
   }
   g.off_freq = off; off += g.blk;  // the root's parent-side partial: the frequencies, for every column
@@ -141,13 +141,13 @@ inline bool plan_geometry_cpt(int n_tips, int n_cols, int K, int elem, int n_sms
   ct = std::max(ct, ct_min);
   ct = std::min(ct, std::max(q, (n_cols + q - 1) / q * q));
   if (ct_force > 0) ct = std::max(q, ct_force / q * q);
-  const int ts = packed && !outer ? ct / cpt : ((ct + cpw - 1) / cpw) * 32;  // threads per slot
+  const int ts = packed && !(outer && ct < 32) ? ct / cpt : ((ct + cpw - 1) / cpw) * 32;  // threads per slot
   const int nts1[4] = {1024, 768, 512, 256}, nts2[4] = {512, 768, 640, 256};
   for (int nt : (cpt == 2 ? nts2 : nts1)) {
     if (nt == 0) continue;
     if (nt_force > 0 && nt != nt_force) continue;
     if (ts > nt - 32 * n_copy_warps) continue;  // the last warps only issue copies
-    int wn = std::min(std::min((nt - 32 * n_copy_warps) / ts, std::max(1, n_tips - 1)), 64);
+    int wn = std::min(std::min((nt - 32 * n_copy_warps) / ts, std::max(1, n_tips - 1)), outer ? 14 : 64);
     for (; wn >= 1; --wn) {
       g = WalkGeometry();
       g.nt = nt; g.ct = ct; g.ts = ts; g.cpw = cpw; g.wn = wn; g.elem = elem; g.K = K; g.cpt = cpt;

@@ -60,7 +60,7 @@ struct WalkParams {
   double* lpart;              // [grid]
   double* gpart;              // [grid][2N-2]
   double* opart;              // outer-product mode: [grid][2N-2][K][16] per-CTA sums of (w / L) c_k q m^T
-  int off_outer, outer_row;   // outer-product mode: shared-memory rows of the compute warps, [warps][K * 32] doubles
+  int off_outer, outer_row;   // outer-product mode: shared-memory rows of the compute warps, [warps][2][K * 32] doubles
   int off_ostage;             // outer-product mode: [warps] 4 KB staging rows of the tensor-core sums
   long long* trace;           // debug build (-DB2P_TRACE_CLOCKS): [2][rounds][8] clock stamps of CTA 0
   int dbg;                    // debug build (-DB2P_DBG): 1 skip the fold, 2 skip the stores, 4 skip the tasks, 8 skip the
@@ -331,27 +331,138 @@ __device__ __forceinline__ void post_task(const WalkParams<T>& p, const WalkThre
 
 // ------------------------------------------------------------------- pre-order task
 //   q_l = u_v o m_r, q_r = u_v o m_l ; L = q_l . m_l ; dL/dt_l = r_k q_l.(Q m_l) ; u_l = P_l^T q_l (same for r)
-// OUTER (b2p_branch_outer_products): the warp also sums, per category, the 4x4 outer products
+// OUTER (b2p_branch_outer_products): the pre-order pass also sums, per task and category, the
+// 4x4 outer products
 //   (w / L) c_k q_l m_l^T  and  (w / L) c_k q_r m_r^T
-// over its columns into its shared-memory row ([K][32]: entries 0-15 the left branch's matrix,
-// 16-31 the right's) — what every model-parameter gradient is a contraction of
-// (b200phylo/paramgrad.py).  Slots are warp-aligned in this mode, so all 32 lanes belong to the
-// same task and lanes of the same category differ by multiples of K.  At the end of the task the
-// slot's warps meet at a named barrier and add their rows (fixed order) into the CTA's part of
-// `opart`, each warp a share of the categories.
+// over the task's columns — what every model-parameter gradient is a contraction of
+// (b200phylo/paramgrad.py).  One column per thread; slots are packed at thread granularity as
+// usual, so a warp holds columns of one slot or of two neighbours ("A" below its boundary lane,
+// "B" from it on; ts >= 32 and ts % K == 0, so a lane's category is lane % K).  Per warp the sum
+// over columns runs on the fp64 tensor cores (outer_sums); per slot the warps that hold its
+// columns share a named barrier: a warp ARRIVES at its slot B's barrier (no wait: otherwise the
+// slots' folds would chain through the warps they share) and WAITS at its slot A's, then adds
+// the slot's rows (fixed order) into the CTA's part of `opart`, each of the slot's A warps a
+// share of the categories (outer_fold).
+struct OuterSlot {
+  unsigned row0;    // shared-memory row of the slot's first warp for this slot
+  unsigned rows1;   // the A row of the slot's second warp (further warps: 2 rows on)
+  int n_warps;      // warps holding columns of the slot (the barrier's participants)
+  int n_fold, r;    // warps that have the slot as their A slot, this warp's index among them
+  int bar;          // named barrier of the slot
+  int lane;         // a lane of this warp that belongs to the slot (its descriptor is the slot's)
+};
 struct OuterCtx {
-  unsigned rows;    // shared-memory rows of the slot's warps (the slot's first warp first)
-  unsigned row;     // this warp's row
   unsigned stage;   // this warp's 4 KB of staging rows (32 columns x 8 doubles, twice)
-  int wps, r, bar;  // warps per slot, this warp's index in its slot, the slot's barrier id
+  unsigned row;     // this warp's A row ([K][32] doubles); its B row follows
+  int bl;           // boundary lane: lanes below belong to slot A, the others to slot B (32: no slot B)
+  OuterSlot a, b;
   bool first_tile;
   double* part;     // the CTA's part of opart
 };
+
+// Sum over the warp's columns of (a q)(m)^T: with the columns as the contraction index,
+// A = [a q_l | a q_r]^T (8 x columns) and B = [m_l | m_r] (columns x 8) give C = A B whose
+// diagonal 4x4 blocks are the two outer-product sums (the off-diagonal blocks are ignored).
+// Every lane puts its column's 8 + 8 values into the warp's staging rows; each mma.sync (m8n8k4)
+// then takes four columns of one category.  Products whose four columns all sit on one side of
+// the boundary lane go to that slot's accumulator; a mixed one runs twice with the other slot's
+// columns zeroed.
+template <int K>
+__device__ __forceinline__ void outer_sums(const OuterCtx& oc, int lane, const double (&aq)[8], const double (&m)[8]) {
+  const unsigned row = (unsigned)lane ^ (((unsigned)lane >> 2) & 1u);  // neighbours of a category alternate bank halves
+  // 16-byte chunks XOR-swizzled so that the stores (8 lanes x 16 bytes per phase) and the loads
+  // below (four rows x 32 bytes per half-warp, at K = 4 rows 8 apart) are both conflict-free
+  const unsigned wr = oc.stage + row * 64, sw = ((((row >> 1) ^ (row >> 3)) & 1u) << 1) | ((row >> 2) & 1u);
+#pragma unroll
+  for (unsigned c = 0; c < 4; ++c) {
+    sts_d2(wr + ((c ^ sw) << 4), aq[2 * c], aq[2 * c + 1]);
+    sts_d2(wr + 2048 + ((c ^ sw) << 4), m[2 * c], m[2 * c + 1]);
+  }
+  __syncwarp();
+  const unsigned g = (unsigned)lane >> 2, t = (unsigned)lane & 3u;
+  // all sixteen loads first, then the products: two independent accumulation chains per category
+  double av[8], bv[8];
+  bool in_a[8];
+#pragma unroll
+  for (int d = 0; d < 8; ++d) {
+    // K = 1: columns 4 d .. 4 d + 3;  K = 4: category d % 4, columns k + 4 (t + 4 (d / 4))
+    const unsigned col = K == 1 ? 4u * d + t : (unsigned)(d & 3) + 4u * (t + 4u * (unsigned)(d >> 2));
+    const unsigned r2 = col ^ ((col >> 2) & 1u);
+    const unsigned s2 = ((((r2 >> 1) ^ (r2 >> 3)) & 1u) << 1) | ((r2 >> 2) & 1u);
+    const unsigned at = oc.stage + r2 * 64 + (((g >> 1) ^ s2) << 4) + ((g & 1u) << 3);
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(av[d]) : "r"(at));
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(bv[d]) : "r"(at + 2048));
+    in_a[d] = (int)col < oc.bl;
+  }
+  constexpr int NA = K == 1 ? 2 : K;  // accumulators per slot: K = 1 splits its products into two chains
+  double ca[NA][2], cb[NA][2];
+#pragma unroll
+  for (int k = 0; k < NA; ++k) ca[k][0] = ca[k][1] = cb[k][0] = cb[k][1] = 0.0;
+#pragma unroll
+  for (int d = 0; d < 8; ++d) {
+    const int ai = K == 1 ? (d & 1) : (d & 3);
+    const int first = K == 1 ? 4 * d : (d & 3) + 16 * (d >> 2), last = K == 1 ? 4 * d + 3 : first + 12;  // warp-uniform
+    if (first < oc.bl) {
+      const double x = in_a[d] ? av[d] : 0.0;
+      asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                   : "+d"(ca[ai][0]), "+d"(ca[ai][1]) : "d"(x), "d"(bv[d]));
+    }
+    if (last >= oc.bl) {
+      const double x = in_a[d] ? 0.0 : av[d];
+      asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                   : "+d"(cb[ai][0]), "+d"(cb[ai][1]) : "d"(x), "d"(bv[d]));
+    }
+  }
+  // lane (g, t) holds C[g][2t], C[g][2t+1]: rows 0-3 x columns 0-3 = the left branch's matrix
+  // (entries 0-15 of the row), rows 4-7 x columns 4-7 = the right branch's (16-31)
+  if ((g < 4) == (t < 2)) {
+    const unsigned e = (g & 3u) * 4u + (t & 1u) * 2u + (g < 4 ? 0u : 16u);
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      sts_d2(oc.row + (k * 32 + e) * 8, K == 1 ? ca[0][0] + ca[1][0] : ca[k][0], K == 1 ? ca[0][1] + ca[1][1] : ca[k][1]);
+      if (oc.bl < 32)
+        sts_d2(oc.row + (K * 32 + k * 32 + e) * 8, K == 1 ? cb[0][0] + cb[1][0] : cb[k][0], K == 1 ? cb[0][1] + cb[1][1] : cb[k][1]);
+    }
+  }
+}
+
+// The warp's rows are written: tell slot B's barrier (if that slot has a task), then wait for
+// slot A's warps and add slot A's rows into the CTA's part of opart.  Every warp that holds
+// columns of a slot with a task gets here in the same round; flags / ids: the lane's descriptor.
+template <int K>
+__device__ __forceinline__ void outer_fold(const OuterCtx& oc, int lane, unsigned flags, unsigned id_l, unsigned id_r,
+                                           int outer_row) {
+  const unsigned fa = __shfl_sync(0xffffffffu, flags, 0), fb = __shfl_sync(0xffffffffu, flags, 31);
+  if (oc.bl < 32 && (fb & WF_LIVE)) {  // warp-uniform, and the same in every warp of that slot
+    __threadfence_block();
+    asm volatile("bar.arrive %0, %1;" ::"r"(oc.b.bar), "r"(oc.b.n_warps * 32) : "memory");
+  }
+  if (!(fa & WF_LIVE)) return;
+  const OuterSlot& sl = oc.a;
+  id_l = __shfl_sync(0xffffffffu, id_l, 0);
+  id_r = __shfl_sync(0xffffffffu, id_r, 0);
+  // the slot's rows are complete once all its warps are here (one warp: its own lanes)
+  if (sl.n_warps > 1) asm volatile("bar.sync %0, %1;" ::"r"(sl.bar), "r"(sl.n_warps * 32) : "memory");
+  else __syncwarp();
+  double* gp = oc.part + (size_t)(lane < 16 ? id_l : id_r) * (K * 16) + (lane & 15);
+  for (int k = sl.r; k < K; k += sl.n_fold) {
+    const unsigned off = (k * 32 + lane) * 8;
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(sl.row0 + off));
+    for (int r = 1; r < sl.n_warps; ++r) {
+      double x;
+      asm volatile("ld.shared.f64 %0, [%1];" : "=d"(x) : "r"(sl.rows1 + (r - 1) * 2 * outer_row + off));
+      v += x;
+    }
+    // a branch is written once per tile: plain store for the CTA's first tile, then adds in tile order
+    if (oc.first_tile) gp[k * 16] = v; else atomicAdd(gp + k * 16, v);
+  }
+}
+
 template <typename T, int K, int CPT, bool OUTER = false>
 __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThread<T, CPT>& th, const TaskDesc& d, bool live,
                                          const unsigned (&code_l)[CPT], const unsigned (&code_r)[CPT], double& gl, double& gr,
                                          const OuterCtx& oc = OuterCtx()) {
-  const unsigned orow = oc.row, ostage = oc.stage;
   T ql[CPT][4], qr[CPT][4];
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
@@ -393,63 +504,15 @@ __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThrea
 #endif
     if constexpr (OUTER) {
       static_assert(!OUTER || (CPT == 1 && (K == 1 || K == 4)), "outer-product mode: one column per thread, K = 1 or 4");
-      // Sum over the warp's columns of (a q)(m)^T on the fp64 tensor cores: with the columns as
-      // the contraction index, A = [a q_l | a q_r]^T (8 x columns) and B = [m_l | m_r] (columns x 8)
-      // give C = A B whose diagonal 4x4 blocks are the two outer-product sums (the off-diagonal
-      // blocks are ignored).  Every lane puts its column's 8 + 8 values into the warp's staging
-      // rows; each mma.sync (m8n8k4) then takes four columns of one category.
       const double a = (live && dd > 0.0) ? (K == 1 ? th.w[c] : th.w[c] * (double)th.cw) * fast_rcp(dd) : 0.0;
-      const unsigned row = (unsigned)th.lane ^ (((unsigned)th.lane >> 2) & 1u);  // neighbours of a category alternate bank halves
-      // 16-byte chunks XOR-swizzled so that the stores (8 lanes x 16 bytes per phase) and the loads
-      // below (four rows x 32 bytes per half-warp, at K = 4 rows 8 apart) are both conflict-free
-      const unsigned wr = ostage + row * 64, sw = ((((row >> 1) ^ (row >> 3)) & 1u) << 1) | ((row >> 2) & 1u);
-      sts_d2(wr + ((0u ^ sw) << 4), a * (double)ql[c][0], a * (double)ql[c][1]);
-      sts_d2(wr + ((1u ^ sw) << 4), a * (double)ql[c][2], a * (double)ql[c][3]);
-      sts_d2(wr + ((2u ^ sw) << 4), a * (double)qr[c][0], a * (double)qr[c][1]);
-      sts_d2(wr + ((3u ^ sw) << 4), a * (double)qr[c][2], a * (double)qr[c][3]);
       // lanes without a column: zeros (their operands are whatever their zero descriptor points at)
-      sts_d2(wr + 2048 + ((0u ^ sw) << 4), live ? (double)ma[0] : 0.0, live ? (double)ma[1] : 0.0);
-      sts_d2(wr + 2048 + ((1u ^ sw) << 4), live ? (double)ma[2] : 0.0, live ? (double)ma[3] : 0.0);
-      sts_d2(wr + 2048 + ((2u ^ sw) << 4), live ? (double)mb[0] : 0.0, live ? (double)mb[1] : 0.0);
-      sts_d2(wr + 2048 + ((3u ^ sw) << 4), live ? (double)mb[2] : 0.0, live ? (double)mb[3] : 0.0);
-      __syncwarp();
-      const unsigned g = (unsigned)th.lane >> 2, t = (unsigned)th.lane & 3u;
-      // all sixteen loads first, then the products: two independent accumulation chains per category
-      double av[8], bv[8];
+      double aq[8], m[8];
 #pragma unroll
-      for (int dd8 = 0; dd8 < 8; ++dd8) {
-        // K = 1: columns 4 d .. 4 d + 3;  K = 4: category d % 4, columns k + 4 (t + 4 (d / 4))
-        const unsigned col = K == 1 ? 4u * dd8 + t : (unsigned)(dd8 & 3) + 4u * (t + 4u * (unsigned)(dd8 >> 2));
-        const unsigned r2 = col ^ ((col >> 2) & 1u);
-        const unsigned s2 = ((((r2 >> 1) ^ (r2 >> 3)) & 1u) << 1) | ((r2 >> 2) & 1u);
-        const unsigned at = ostage + r2 * 64 + (((g >> 1) ^ s2) << 4) + ((g & 1u) << 3);
-        asm volatile("ld.shared.f64 %0, [%1];" : "=d"(av[dd8]) : "r"(at));
-        asm volatile("ld.shared.f64 %0, [%1];" : "=d"(bv[dd8]) : "r"(at + 2048));
+      for (int i = 0; i < 4; ++i) {
+        aq[i] = a * (double)ql[c][i]; aq[4 + i] = a * (double)qr[c][i];
+        m[i] = live ? (double)ma[i] : 0.0; m[4 + i] = live ? (double)mb[i] : 0.0;
       }
-      constexpr int NA = K == 1 ? 2 : K;  // accumulators: K = 1 splits its eight products into two chains
-      double acc2[NA][2];
-#pragma unroll
-      for (int k = 0; k < NA; ++k) acc2[k][0] = acc2[k][1] = 0.0;
-#pragma unroll
-      for (int dd8 = 0; dd8 < 8; ++dd8) {
-        const int ai = K == 1 ? (dd8 & 1) : (dd8 & 3);
-        asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
-                     : "+d"(acc2[ai][0]), "+d"(acc2[ai][1])
-                     : "d"(av[dd8]), "d"(bv[dd8]));
-      }
-      double acc[K][2];
-#pragma unroll
-      for (int k = 0; k < K; ++k) {
-        acc[k][0] = K == 1 ? acc2[0][0] + acc2[NA - 1][0] : acc2[k][0];
-        acc[k][1] = K == 1 ? acc2[0][1] + acc2[NA - 1][1] : acc2[k][1];
-      }
-      // lane (g, t) holds C[g][2t], C[g][2t+1]: rows 0-3 x columns 0-3 = the left branch's matrix
-      // (entries 0-15 of the warp's row), rows 4-7 x columns 4-7 = the right branch's (16-31)
-      if ((g < 4) == (t < 2)) {
-        const unsigned e = (g & 3u) * 4u + (t & 1u) * 2u + (g < 4 ? 0u : 16u);
-#pragma unroll
-        for (int k = 0; k < K; ++k) sts_d2(orow + (k * 32 + e) * 8, acc[k][0], acc[k][1]);
-      }
+      outer_sums<K>(oc, th.lane, aq, m);
     }
   }
   // pre-order partials of the internal children: u_c = P_c^T q_c (rescaled when tiny).  K == 1: a
@@ -478,22 +541,7 @@ __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThrea
 #ifdef B2P_DBG
     if (p.dbg & 8) return;
 #endif
-    // the slot's rows are complete once all its warps are here (one warp: its own lanes)
-    if (oc.wps > 1) asm volatile("bar.sync %0, %1;" ::"r"(oc.bar), "r"(oc.wps * 32) : "memory");
-    else __syncwarp();
-    // lane 0 always holds a column of the slot: its descriptor is the slot's
-    const unsigned id_l = __shfl_sync(0xffffffffu, d.id_l, 0), id_r = __shfl_sync(0xffffffffu, d.id_r, 0);
-    double* gp = oc.part + (size_t)(th.lane < 16 ? id_l : id_r) * (K * 16) + (th.lane & 15);
-    for (int k = oc.r; k < K; k += oc.wps) {
-      double v = 0.0;
-      for (int r = 0; r < oc.wps; ++r) {
-        double x;
-        asm volatile("ld.shared.f64 %0, [%1];" : "=d"(x) : "r"(oc.rows + r * p.outer_row + (k * 32 + th.lane) * 8));
-        v += x;
-      }
-      // a branch is written once per tile: plain store for the CTA's first tile, then adds in tile order
-      if (oc.first_tile) gp[k * 16] = v; else atomicAdd(gp + k * 16, v);
-    }
+    outer_fold<K>(oc, th.lane, d.flags, d.id_l, d.id_r, p.outer_row);
   }
 }
 
@@ -597,6 +645,27 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
     // warp-aligned slots: the lanes past the tile's last column never write their pair of sums
     sts_d2(sbase + p.off_gbuf + (s * p.ts + tt) * 16, 0.0, 0.0);
     sts_d2(sbase + p.off_gbuf + ((p.wn + s) * p.ts + tt) * 16, 0.0, 0.0);
+  }
+  // outer-product mode: which slots the warp's lanes belong to and who shares them (see OuterCtx)
+  OuterCtx oc{};
+  if constexpr (OUTER) {
+    const int w0 = warp * 32, sa = w0 / p.ts, end_a = (sa + 1) * p.ts;
+    const bool has_b = end_a < w0 + 32 && sa + 1 < p.wn;
+    auto slot = [&](int sx, int ln) {
+      OuterSlot o;
+      const int wf = (sx * p.ts) / 32, wl = ((sx + 1) * p.ts - 1) / 32, wa = (sx * p.ts + 31) / 32;  // wa: first warp with A = sx
+      o.n_warps = wl - wf + 1; o.n_fold = wl - wa + 1; o.r = warp - wa; o.bar = 1 + sx; o.lane = ln;
+      // the first warp holds the slot's first columns as its A columns only if the slot starts on its lane 0
+      o.row0 = sbase + p.off_outer + (2 * wf + ((sx * p.ts) % 32 ? 1 : 0)) * p.outer_row;
+      o.rows1 = sbase + p.off_outer + 2 * (wf + 1) * p.outer_row;
+      return o;
+    };
+    oc.stage = sbase + p.off_ostage + warp * 4096;
+    oc.row = sbase + p.off_outer + 2 * warp * p.outer_row;
+    oc.bl = has_b ? end_a - w0 : 32;
+    oc.a = slot(min(sa, p.wn - 1), 0);
+    oc.b = slot(min(sa + 1, p.wn - 1), 31);
+    oc.part = p.opart + (size_t)blockIdx.x * p.n_branches * (K * 16);
   }
   unsigned phase_bits = 0;
   double ll_acc = 0.0;
@@ -732,15 +801,7 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
             post_task<T, K, CPT>(p, th, d, live, root_round, scount, col, code_l, code_r, ga);
             if (live && is_root) sts_d2(gslot, ga, 0.0);
           } else {
-            OuterCtx oc{};
-            if constexpr (OUTER) {
-              // the warp's slot (slots are warp-aligned; lanes past the tile's last column have sl = 0)
-              const int ws = (warp * 32) / p.ts;
-              oc.wps = p.ts >> 5; oc.r = warp - ws * oc.wps; oc.bar = 1 + ws; oc.first_tile = first_tile;
-              oc.rows = sbase + p.off_outer + ws * oc.wps * p.outer_row; oc.row = oc.rows + oc.r * p.outer_row;
-              oc.stage = sbase + p.off_ostage + warp * 4096;
-              oc.part = p.opart + (size_t)blockIdx.x * p.n_branches * (K * 16);
-            }
+            oc.first_tile = first_tile;
             pre_task<T, K, CPT, OUTER>(p, th, d, live, code_l, code_r, ga, gb2, oc);
             if (live) sts_d2(gslot, ga, gb2);
           }

@@ -77,6 +77,8 @@ def test_parameter_gradients_match_autograd_of_pruning(kind, gamma):
     ("hky_g4_flu", 36, 240, True), ("hky_g4_flu", 36, 240, False), ("hky_g4_flu", 7, 5, True), ("hky_g4_flu", 2, 33, False),
     ("hky_g4_flu", 120, 3000, True),      # several tiles per CTA: the parts are added across tiles
     ("jc69_1000x10k", 300, 20011, False),  # more tiles than SMs at one category, ragged last tile
+    ("jc69_1000x10k", 50, 5476, False),    # 37 columns per tile: slot boundaries inside a group of four lanes
+    ("jc69_1000x10k", 90, 9000, True),     # 4 categories, wide tile
     ("hky_g4_flu", 200, 6007, True)])
 def test_outer_products_in_one_pass_match_the_operator_route(name, n_tips, n_patterns, gamma):
     """``b2p_branch_outer_products`` (one evaluation) against the 16 K evaluations of
@@ -150,3 +152,64 @@ def test_gamma_shape_gradient_by_chain_rule():
     fd_alpha = (logl(0.6 + 1e-4) - logl(0.6 - 1e-4)) / 2e-4
     assert d_alpha == pytest.approx(fd_alpha, rel=1e-5)
     eng.close()
+
+
+@pytest.mark.parametrize("where,site", [("cuda", "weibull"), ("cpu", "weibull"), ("cuda", "constant")])
+def test_tree_likelihood_model_differentiates_model_parameters(where, site):
+    """The plugin surface: ``TreeLikelihoodModel`` with ``DifferentiableGTR`` / a Weibull site model
+    whose parameters are tensors — ``model().backward()`` fills the gradients w.r.t. branch
+    lengths, exchangeabilities, (unnormalised) frequencies and the shape from ONE engine
+    evaluation; against autograd of the whole pruning recursion (oracle/param_oracle.py), 1e-8."""
+    from b200phylo import paramgrad as pg
+    from b200phylo.diffmodels import DifferentiableGTR, DifferentiableWeibullSiteModel
+    from b200phylo.treelikelihood import Parameter, TreeLikelihoodModel, UnrootedTreeModel
+    w, exch0, pi0 = _case("gtr", 40, 300, site == "weibull")
+    tree = w.tree
+
+    def leaves(device):
+        mk = lambda v: torch.tensor(v, dtype=torch.float64, device=device, requires_grad=True)  # noqa: E731
+        return mk(exch0), mk(pi0), mk([0.8]), mk(tree.branch_lengths)
+
+    ex, fr, shape, bl = leaves(where)
+    subst = DifferentiableGTR("gtr", Parameter("gtr.rates", ex), Parameter("gtr.freqs", fr))
+    site_model = DifferentiableWeibullSiteModel("site", Parameter("shape", shape), 4) if site == "weibull" else ConstantSiteModel()
+    m = TreeLikelihoodModel("like", w.patterns, UnrootedTreeModel("tree", tree, bl), subst, site_model)
+    assert [p.id for p in m.parameters()][-3 if site == "weibull" else -2:][:2] == ["gtr.rates", "gtr.freqs"]
+    logl = m()
+    assert logl.device.type == where
+    (3.0 * logl).backward()
+    # oracle: the same parameterisation on the CPU, pruning differentiated by torch
+    oex, ofr, oshape, obl = leaves("cpu")
+    f = ofr / ofr.sum()
+    q = pg.q_matrix(oex, f)
+    if site == "weibull":
+        orates = DifferentiableWeibullSiteModel(None, oshape, 4).rates_tensor()
+        weights = np.full(4, 0.25)
+    else:
+        orates, weights = torch.ones(1, dtype=torch.float64), np.ones(1)
+    ll = param_oracle.log_likelihood(tree.post_triples, w.patterns.partials(), w.patterns.weights, obl, q, f, orates, weights)
+    (3.0 * ll).backward()
+    assert rel_err(float(logl), float(ll.detach())) < 1e-10
+    pairs = [("exchangeabilities", ex.grad, oex.grad), ("frequencies", fr.grad, ofr.grad), ("branch lengths", bl.grad, obl.grad)]
+    if site == "weibull":
+        pairs.append(("shape", shape.grad, oshape.grad))
+    for name, got, want in pairs:
+        assert got is not None and got.device.type == where, name
+        assert grad_err(got.cpu().numpy(), want.numpy()) < 1e-8, (name, got.cpu().numpy(), want.numpy())
+    # a changed parameter is seen by the next call (the engine's model is refreshed), with or without gradients
+    with torch.no_grad():
+        ex[1] = 4.2
+    oex2 = oex.detach().clone()
+    oex2[1] = 4.2
+    ll2 = param_oracle.log_likelihood(tree.post_triples, w.patterns.partials(), w.patterns.weights, obl.detach(),
+                                      pg.q_matrix(oex2, f.detach()), f.detach(), orates.detach(), weights)
+    assert rel_err(float(m()), float(ll2)) < 1e-10
+    with torch.no_grad():
+        assert rel_err(float(m()), float(ll2)) < 1e-10
+    # only the branch lengths ask for a gradient: the ordinary route, same numbers
+    for t in (ex, fr, shape):
+        t.requires_grad_(False)
+    bl.grad = None
+    m().backward()
+    assert bl.grad is not None and bl.grad.shape == obl.shape
+    m.close()

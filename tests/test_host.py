@@ -156,3 +156,36 @@ def test_weibull_site_model():
     assert m.rates.mean() == pytest.approx(1.0) and np.all(np.diff(m.rates) > 0) and m.weights.sum() == pytest.approx(1.0)
     j = tl._site_model_from_json({"type": "WeibullSiteModel", "shape": {"tensor": [0.7]}, "categories": 6})
     assert len(j.rates) == 6 and j.rates.mean() == pytest.approx(1.0)
+
+
+def test_differentiable_models_match_their_host_twins():
+    """b200phylo.diffmodels: the torch-parameter models give the numbers of the numpy ones (the
+    engine is fed from ``eigen()``, ``backward`` from ``q_tensor()``)."""
+    import torch
+    from b200phylo import treelikelihood as tl
+    from b200phylo.diffmodels import DifferentiableGTR, DifferentiableHKY, DifferentiableWeibullSiteModel, is_differentiable
+    from b200phylo.sitemodel import WeibullSiteModel
+    from b200phylo.substitution import GTR, HKY
+    ex = tl.Parameter("gtr.rates", torch.tensor([1.3, 2.9, 0.7, 1.1, 3.4, 1.0], dtype=torch.float64))
+    fr = tl.Parameter("gtr.freqs", torch.tensor([0.31, 0.19, 0.22, 0.28], dtype=torch.float64))
+    m = DifferentiableGTR("gtr", ex, fr)
+    ref = GTR((1.3, 2.9, 0.7, 1.1, 3.4, 1.0), (0.31, 0.19, 0.22, 0.28))
+    np.testing.assert_allclose(m.q_tensor().numpy(), ref.q_matrix(), rtol=1e-14, atol=1e-16)
+    np.testing.assert_allclose(m.eigen().evals, ref.eigen().evals, rtol=1e-13, atol=1e-15)
+    assert m.parameters() == [ex, fr] and not is_differentiable(m)
+    ex.requires_grad = True
+    assert is_differentiable(m) and m.q_tensor().requires_grad
+    assert not is_differentiable(ref)
+    h = DifferentiableHKY("hky", torch.tensor([2.7], dtype=torch.float64), torch.tensor([0.1, 0.2, 0.3, 0.4], dtype=torch.float64))
+    np.testing.assert_allclose(h.q_tensor().numpy(), HKY(2.7, (0.1, 0.2, 0.3, 0.4)).q_matrix(), rtol=1e-14, atol=1e-16)
+    assert h.kappa == 2.7 and h.parameters() == []
+    w = DifferentiableWeibullSiteModel("site", tl.Parameter("shape", torch.tensor([0.7], dtype=torch.float64, requires_grad=True)), 6)
+    np.testing.assert_allclose(w.rates, WeibullSiteModel(0.7, 6).rates, rtol=1e-14)
+    assert is_differentiable(w) and len(w.weights) == 6
+    # the JSON parsers keep Parameter objects given by id or inline
+    dic = {}
+    g = tl._subst_model_from_json({"id": "gtr", "type": "GTR", "rates": {"id": "r", "type": "Parameter", "tensor": [1, 2, 1, 1, 2, 1]},
+                                   "frequencies": {"id": "f", "type": "Parameter", "tensor": [0.3, 0.2, 0.2, 0.3]}}, dic)
+    assert isinstance(g, DifferentiableGTR) and g.parameters() == [dic["r"], dic["f"]]
+    np.testing.assert_allclose(g.q_matrix(), GTR((1, 2, 1, 1, 2, 1), (0.3, 0.2, 0.2, 0.3)).q_matrix(), rtol=1e-14, atol=1e-16)
+    assert isinstance(tl._subst_model_from_json({"type": "GTR", "rates": [1, 2, 1, 1, 2, 1], "frequencies": [0.3, 0.2, 0.2, 0.3]}), GTR)

@@ -22,7 +22,8 @@ def plan_check():
 
 # N, shape (0 random joins, 1 caterpillar, 2 balanced), seed, ct, K, elem, depth, nt, cpt[, outer-product mode]
 CASES = [
-    (1000, 0, 1, 68, 1, 8, 1, 512, 1, 1),   # outer-product mode at the headline shape: 68 columns in 96 threads
+    (1000, 0, 1, 68, 1, 8, 1, 512, 1, 1),   # outer-product mode at the headline shape
+    (50, 0, 3, 12, 4, 8, 1, 512, 1, 1),     # narrow tile: 32 threads per slot, 13 slots
     (1704, 0, 2, 48, 4, 8, 1, 512, 1, 1),
     (300, 2, 5, 136, 4, 8, 2, 512, 1, 1),
     (1000, 0, 1, 68, 1, 8, 1, 0, 2),     # headline geometry
