@@ -619,7 +619,7 @@ static cudaError_t launch_eval(b2p_instance* h, const double* d_bl, double* d_lo
   cudaError_t e = cudaLaunchKernel(d_outer ? h->kernel_outer : h->kernel, dim3(h->wg.grid), dim3(h->wg.nt), args, h->wg.smem, st);
   if (e != cudaSuccess) return e;
   if (h->profiling) { cudaEventRecord(h->ev1[slot], st); ++h->prof_count; }
-  const int nb = d_grad ? n_br : 0;
+  const int nb = (d_grad && !d_outer) ? n_br : 0;  // outer-product mode: the gradient follows from the outer products
   if (h->peer.attached) {
     PeerArgs pa = peer_args(h);
     reduce_exchange_kernel<<<(nb + 31) / 32 + 1, 512, 0, st>>>(h->d_gpart, h->d_lpart, h->wg.grid, nb, d_grad, d_logl, pa);
@@ -629,6 +629,12 @@ static cudaError_t launch_eval(b2p_instance* h, const double* d_bl, double* d_lo
   if (d_outer) {
     const int n_pairs = n_br * K * 8;
     reduce_outer_kernel<<<(n_pairs + 63) / 64, dim3(64, 8), 0, st>>>(h->d_opart, h->wg.grid, n_br, K, d_outer);
+    if (d_grad) {
+      OuterGradArgs ga;
+      for (int i = 0; i < 16; ++i) ga.q[i] = h->qmat[i];
+      for (int k = 0; k < kMaxCat; ++k) ga.rates[k] = k < K ? h->model.rates[k] : 0.0;
+      grad_from_outer_kernel<<<(n_br + 127) / 128, 128, 0, st>>>(d_outer, n_br, K, ga, d_grad);
+    }
   }
   return cudaGetLastError();
 }

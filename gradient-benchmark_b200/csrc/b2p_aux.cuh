@@ -72,6 +72,30 @@ __global__ void tile_tips_kernel(const uint8_t* __restrict__ raw, const int* __r
   out[idx] = code;
 }
 
+// Outer-product mode: the branch gradient from the outer products,
+//   dlogL/dt_b = sum_k r_k <Q, G_{b,k}>      (G already carries c_k and w_p / L_p),
+// one thread per branch (the walk kernel of that mode leaves the numerators q.(Q m) out).
+struct OuterGradArgs {
+  double q[16];
+  double rates[kMaxCat];
+};
+__global__ void grad_from_outer_kernel(const double* __restrict__ outer, int n_br, int K, OuterGradArgs a, double* __restrict__ grad) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= n_br) return;
+  double g = 0.0;
+  for (int k = 0; k < K; ++k) {
+    const double2* src = reinterpret_cast<const double2*>(outer + ((size_t)k * n_br + b) * 16);
+    double s = 0.0;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const double2 v = src[e];
+      s += a.q[2 * e] * v.x + a.q[2 * e + 1] * v.y;
+    }
+    g += a.rates[k] * s;
+  }
+  grad[b] = g;
+}
+
 // Outer-product mode: sum the per-CTA parts [grid][2N-2][K][16] in CTA order (deterministic) and
 // write them as [K][2N-2][4][4] — the layout b200phylo/paramgrad.py contracts.  A block takes 64
 // pairs of outputs; its 8 thread rows each add a contiguous eighth of the parts (independent

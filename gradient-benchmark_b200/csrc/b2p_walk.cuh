@@ -368,11 +368,14 @@ struct OuterCtx {
 // the boundary lane go to that slot's accumulator; a mixed one runs twice with the other slot's
 // columns zeroed.
 template <int K>
-__device__ __forceinline__ void outer_sums(const OuterCtx& oc, int lane, const double (&aq)[8], const double (&m)[8]) {
+__device__ __forceinline__ void outer_sums(const OuterCtx& oc, int lane, const double (&aq)[8], const double (&m)[8], int dbg = 0) {
   const unsigned row = (unsigned)lane ^ (((unsigned)lane >> 2) & 1u);  // neighbours of a category alternate bank halves
   // 16-byte chunks XOR-swizzled so that the stores (8 lanes x 16 bytes per phase) and the loads
   // below (four rows x 32 bytes per half-warp, at K = 4 rows 8 apart) are both conflict-free
   const unsigned wr = oc.stage + row * 64, sw = ((((row >> 1) ^ (row >> 3)) & 1u) << 1) | ((row >> 2) & 1u);
+#ifdef B2P_DBG
+  if (!(dbg & 64))
+#endif
 #pragma unroll
   for (unsigned c = 0; c < 4; ++c) {
     sts_d2(wr + ((c ^ sw) << 4), aq[2 * c], aq[2 * c + 1]);
@@ -398,6 +401,12 @@ __device__ __forceinline__ void outer_sums(const OuterCtx& oc, int lane, const d
   double ca[NA][2], cb[NA][2];
 #pragma unroll
   for (int k = 0; k < NA; ++k) ca[k][0] = ca[k][1] = cb[k][0] = cb[k][1] = 0.0;
+#ifdef B2P_DBG
+  if (dbg & 32) {
+#pragma unroll
+    for (int d = 0; d < 8; ++d) ca[d % NA][0] += av[d] * bv[d];
+  } else
+#endif
 #pragma unroll
   for (int d = 0; d < 8; ++d) {
     const int ai = K == 1 ? (d & 1) : (d & 3);
@@ -477,13 +486,17 @@ __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThrea
       qr[c][i] = u[i] * ma[i];
       den += ql[c][i] * ma[i];
     }
-    // d/dt (P x) = r Q (P x): Q comes from the constant bank
+    // d/dt (P x) = r Q (P x): Q comes from the constant bank.  (Outer-product mode: the branch
+    // gradient is the contraction sum_k r_k <Q, G_{b,k}> of what it sums anyway — done after the
+    // walk, grad_from_outer_kernel — so the numerators are not formed here.)
+    if constexpr (!OUTER) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const T dl = p.q[4 * i] * ma[0] + p.q[4 * i + 1] * ma[1] + p.q[4 * i + 2] * ma[2] + p.q[4 * i + 3] * ma[3];
-      const T dr = p.q[4 * i] * mb[0] + p.q[4 * i + 1] * mb[1] + p.q[4 * i + 2] * mb[2] + p.q[4 * i + 3] * mb[3];
-      numl += ql[c][i] * dl;
-      numr += qr[c][i] * dr;
+      for (int i = 0; i < 4; ++i) {
+        const T dl = p.q[4 * i] * ma[0] + p.q[4 * i + 1] * ma[1] + p.q[4 * i + 2] * ma[2] + p.q[4 * i + 3] * ma[3];
+        const T dr = p.q[4 * i] * mb[0] + p.q[4 * i + 1] * mb[1] + p.q[4 * i + 2] * mb[2] + p.q[4 * i + 3] * mb[3];
+        numl += ql[c][i] * dl;
+        numr += qr[c][i] * dr;
+      }
     }
     if (K != 1) {
       // the site likelihood is the sum over the pattern's K category lanes; the numerators
@@ -512,7 +525,7 @@ __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThrea
         aq[i] = a * (double)ql[c][i]; aq[4 + i] = a * (double)qr[c][i];
         m[i] = live ? (double)ma[i] : 0.0; m[4 + i] = live ? (double)mb[i] : 0.0;
       }
-      outer_sums<K>(oc, th.lane, aq, m);
+      outer_sums<K>(oc, th.lane, aq, m, p.dbg);
     }
   }
   // pre-order partials of the internal children: u_c = P_c^T q_c (rescaled when tiny).  K == 1: a
@@ -756,7 +769,8 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
 #ifdef B2P_DBG
         if (!(p.dbg & 1))
 #endif
-        if (q >= p.rounds_post) {  // sums exist from the root's post-order round on
+        // sums exist from the root's post-order round on (outer-product mode: only the root's term)
+        if (OUTER ? q == p.rounds_post : q >= p.rounds_post) {
           for (int s0 = pw; s0 < p.wn; s0 += 4 * np)
 #ifdef B2P_TRACE_CLOCKS
             fold_slots<T, true>(p, sbase + p.off_gbuf + (par ^ 1) * p.wn * p.ts * 16, s0, np, lane, first_tile, ir + 16, nullptr, ll_acc,
@@ -803,7 +817,7 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
           } else {
             oc.first_tile = first_tile;
             pre_task<T, K, CPT, OUTER>(p, th, d, live, code_l, code_r, ga, gb2, oc);
-            if (live) sts_d2(gslot, ga, gb2);
+            if (!OUTER && live) sts_d2(gslot, ga, gb2);
           }
         }
 #ifdef B2P_TRACE_CLOCKS
@@ -825,6 +839,7 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
     if (copier) {
       // the last round's sums: their ids come from global memory (no further issue record)
       const int2* tail = reinterpret_cast<const int2*>(p.records + p.tail_base);
+      if (!OUTER || R == p.rounds_post)
       for (int s0 = warp - first_copy_warp; s0 < p.wn; s0 += 4 * p.n_copy_warps)
         fold_slots<T, false>(p, sbase + p.off_gbuf + ((R - 1) & 1) * p.wn * p.ts * 16, s0, p.n_copy_warps, lane, first_tile, 0u, tail, ll_acc);
       // (the last round leaves nothing to store: the root's post-order task writes no message,
