@@ -440,7 +440,7 @@ __device__ __forceinline__ void outer_sums(const OuterCtx& oc, int lane, const d
 // columns of a slot with a task gets here in the same round; flags / ids: the lane's descriptor.
 template <int K>
 __device__ __forceinline__ void outer_fold(const OuterCtx& oc, int lane, unsigned flags, unsigned id_l, unsigned id_r,
-                                           int outer_row) {
+                                           int outer_row, int dbg = 0) {
   const unsigned fa = __shfl_sync(0xffffffffu, flags, 0), fb = __shfl_sync(0xffffffffu, flags, 31);
   if (oc.bl < 32 && (fb & WF_LIVE)) {  // warp-uniform, and the same in every warp of that slot
     __threadfence_block();
@@ -453,18 +453,30 @@ __device__ __forceinline__ void outer_fold(const OuterCtx& oc, int lane, unsigne
   // the slot's rows are complete once all its warps are here (one warp: its own lanes)
   if (sl.n_warps > 1) asm volatile("bar.sync %0, %1;" ::"r"(sl.bar), "r"(sl.n_warps * 32) : "memory");
   else __syncwarp();
-  double* gp = oc.part + (size_t)(lane < 16 ? id_l : id_r) * (K * 16) + (lane & 15);
-  for (int k = sl.r; k < K; k += sl.n_fold) {
-    const unsigned off = (k * 32 + lane) * 8;
-    double v;
-    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(sl.row0 + off));
-    for (int r = 1; r < sl.n_warps; ++r) {
-      double x;
-      asm volatile("ld.shared.f64 %0, [%1];" : "=d"(x) : "r"(sl.rows1 + (r - 1) * 2 * outer_row + off));
-      v += x;
+#ifdef B2P_DBG
+  if (dbg & 256) return;
+#endif
+  // A lane adds one PAIR of adjacent entries per step (16-byte loads and stores): pair j of the
+  // slot's K * 16 sits at byte 16 j of every row; the slot's A warps take 32 pairs each per step.
+  // The tail of a round is a single warp's dependent instruction stream — few instructions, and
+  // the first two rows' loads issued together.
+  for (int j = sl.r * 32 + lane; j < K * 16; j += sl.n_fold * 32) {
+    const unsigned off = j * 16;
+    double2 v = lds_d2(sl.row0 + off);
+    const double2 x = lds_d2((sl.n_warps > 1 ? sl.rows1 : sl.row0) + off);
+    if (sl.n_warps > 1) { v.x += x.x; v.y += x.y; }
+    for (int r = 2; r < sl.n_warps; ++r) {
+      const double2 y = lds_d2(sl.rows1 + (r - 1) * 2 * outer_row + off);
+      v.x += y.x; v.y += y.y;
     }
+    const int k = j >> 4, e = (j & 15) * 2;  // entries e, e + 1 of category k: 0-15 the left branch, 16-31 the right
+    double* gp = oc.part + ((size_t)(e < 16 ? id_l : id_r) * K + k) * 16 + (e & 15);
+#ifdef B2P_DBG
+    if (dbg & 128) { if (v.x == 1.2345e-300) gp[0] = v.x; continue; }
+#endif
     // a branch is written once per tile: plain store for the CTA's first tile, then adds in tile order
-    if (oc.first_tile) gp[k * 16] = v; else atomicAdd(gp + k * 16, v);
+    if (oc.first_tile) *reinterpret_cast<double2*>(gp) = v;
+    else { atomicAdd(gp, v.x); atomicAdd(gp + 1, v.y); }
   }
 }
 
@@ -554,7 +566,7 @@ __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThrea
 #ifdef B2P_DBG
     if (p.dbg & 8) return;
 #endif
-    outer_fold<K>(oc, th.lane, d.flags, d.id_l, d.id_r, p.outer_row);
+    outer_fold<K>(oc, th.lane, d.flags, d.id_l, d.id_r, p.outer_row, p.dbg);
   }
 }
 
