@@ -27,7 +27,7 @@ EXPORTED_SYMBOLS = (
     "b2p_set_categories", "b2p_loglik", "b2p_loglik_grad", "b2p_loglik_grad_host",
     "b2p_set_profiling", "b2p_last_kernel_ms", "b2p_kernel_ms_stats", "b2p_get_branch_partials",
     "b2p_peer_export", "b2p_peer_attach", "b2p_peer_status", "b2p_set_gradient_operator",
-    "b2p_branch_outer_products",
+    "b2p_branch_outer_products", "b2p_model_gradients",
 )
 
 
@@ -105,6 +105,7 @@ def load_library():
     lib.b2p_get_branch_partials.argtypes = [vp, ctypes.c_int32, dp]
     lib.b2p_set_gradient_operator.argtypes = [vp, dp, dp]
     lib.b2p_branch_outer_products.argtypes = [vp, vp, vp, vp, vp, vp]
+    lib.b2p_model_gradients.argtypes = [vp, vp, vp, ctypes.c_int32, vp, vp]
     lib.b2p_peer_export.argtypes = [vp, ctypes.c_int32, ctypes.c_char_p]
     lib.b2p_peer_attach.argtypes = [vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_char_p]
     lib.b2p_peer_status.argtypes = [vp, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
@@ -261,6 +262,12 @@ class Engine:
         eng = self if self.outer_products else self._outer_twin()
         eng._check(eng._lib.b2p_branch_outer_products(eng._h, d_bl, d_logl, d_grad, d_outer, stream),
                    "b2p_branch_outer_products")
+
+    def model_gradients(self, d_bl: int, d_outer: int, root_child: int, d_out: int, stream: int = 0) -> None:
+        """``b2p_model_gradients``: [16] dlogL/dQ | [4] dlogL/dpi (root prior) | [K] dlogL/dr_k from the
+        outer products a ``branch_outer_products`` call with the same branch lengths left in ``d_outer``."""
+        eng = self if self.outer_products else self._outer_twin()
+        eng._check(eng._lib.b2p_model_gradients(eng._h, d_bl, d_outer, int(root_child), d_out, stream), "b2p_model_gradients")
 
     def _outer_twin(self) -> "Engine":
         if not self.supports_outer_products():

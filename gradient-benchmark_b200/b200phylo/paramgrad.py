@@ -112,7 +112,8 @@ def surrogate(g: torch.Tensor, t: torch.Tensor, q: torch.Tensor, freqs: torch.Te
 
 
 def parameter_gradients(engine: Engine, bl: torch.Tensor, root_children: Sequence[int],
-                        model: Callable[[], Dict[str, torch.Tensor]], g: Optional[torch.Tensor] = None) -> torch.Tensor:
+                        model: Callable[[], Dict[str, torch.Tensor]], g: Optional[torch.Tensor] = None,
+                        algebra: Optional[str] = None) -> torch.Tensor:
     """Surrogate whose ``backward()`` leaves dlogL/dtheta in the ``.grad`` of every leaf tensor
     ``model()`` depends on.
 
@@ -120,9 +121,29 @@ def parameter_gradients(engine: Engine, bl: torch.Tensor, root_children: Sequenc
     device: ``{"q": [4,4] rate matrix, "freqs": [4], "rates": [K] category rates}`` (and may
     also depend on ``bl``, which then receives the ordinary branch gradient).  The engine must
     already hold the same model (``Engine.set_model``).  Returns S (call ``.backward()``).
+
+    ``algebra``: "device" — ``b2p_model_gradients`` contracts G with dP/d(Q, rates) in two small
+    launches and S is linear in (q, freqs, rates, bl); "torch" — S = sum <G P^{-T}, P(theta)> with
+    torch's matrix exponentials (the round-1 route; the only one when the engine cannot return
+    G in one pass).  Default: "device" where available and ``g`` is not given.
     """
-    if g is None:
-        g = branch_outer_products(engine, bl)
+    if algebra is None:
+        algebra = "device" if (g is None and engine.supports_outer_products()) else "torch"
     m = model()
     t = bl if bl.requires_grad else bl.detach()
+    if algebra == "device":
+        if g is not None:
+            raise ValueError("algebra='device' computes the outer products itself")
+        k_cat, n_br = engine.n_categories, engine.n_branches
+        b = bl.detach().to(torch.float64).contiguous()
+        stream = torch.cuda.current_stream(b.device).cuda_stream
+        g = torch.empty(k_cat, n_br, 4, 4, dtype=torch.float64, device=b.device)
+        out = torch.empty(1 + n_br, dtype=torch.float64, device=b.device)
+        mg = torch.empty(20 + k_cat, dtype=torch.float64, device=b.device)
+        engine.branch_outer_products(b.data_ptr(), out.data_ptr(), out.data_ptr() + 8, g.data_ptr(), stream)
+        engine.model_gradients(b.data_ptr(), g.data_ptr(), int(root_children[0]), mg.data_ptr(), stream)
+        s = (mg[:16].reshape(4, 4) * m["q"]).sum() + (mg[16:20] * m["freqs"]).sum() + (mg[20:] * m["rates"]).sum()
+        return s + (out[1:] * t).sum() if t.requires_grad else s
+    if g is None:
+        g = branch_outer_products(engine, bl)
     return surrogate(g, t, m["q"], m["freqs"], m["rates"], root_children[0])

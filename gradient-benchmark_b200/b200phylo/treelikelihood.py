@@ -193,9 +193,10 @@ class TreeLikelihoodParameterFunction(torch.autograd.Function):
     engine evaluation.
 
     ``forward`` calls ``b2p_branch_outer_products`` — log-likelihood, branch gradient and the
-    per-branch outer products G_{b,k} = sum_p (w_p / L_p) c_k q m^T in one pass — and ``backward``
-    contracts G with dP/d(Q, rates) and adds the root-prior term for the frequencies
-    (``paramgrad.surrogate``).  torchtree gets the same numbers by autograd of the whole pruning
+    per-branch outer products G_{b,k} = sum_p (w_p / L_p) c_k q m^T in one pass — and
+    ``b2p_model_gradients``, which contracts G with dP/d(Q, rates) on the device (divided
+    differences of the eigenvalues) and adds the root-prior term for the frequencies;
+    ``backward`` only scales.  torchtree gets the same numbers by autograd of the whole pruning
     recursion (/root/reference/modules/micro.nf:52 ``--gtr``)."""
 
     @staticmethod
@@ -207,33 +208,29 @@ class TreeLikelihoodParameterFunction(torch.autograd.Function):
             raise ValueError(f"branch_lengths must have shape ({eng.n_branches},), got {tuple(bl.shape)}")
         out = torch.empty(1 + eng.n_branches, dtype=torch.float64, device=dev)
         g = torch.empty(eng.n_categories, eng.n_branches, 4, 4, dtype=torch.float64, device=dev)
-        eng.branch_outer_products(bl.data_ptr(), out.data_ptr(), out.data_ptr() + 8, g.data_ptr(),
-                                  torch.cuda.current_stream(dev).cuda_stream)
-        ctx.save_for_backward(bl, q.detach().to(dev), freqs.detach().to(dev), rates.detach().to(dev), out[1:], g)
-        ctx.root_child = int(model.tree_model.post_triples[-1][1])
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        eng.branch_outer_products(bl.data_ptr(), out.data_ptr(), out.data_ptr() + 8, g.data_ptr(), stream)
+        mg = torch.empty(20 + eng.n_categories, dtype=torch.float64, device=dev)
+        eng.model_gradients(bl.data_ptr(), g.data_ptr(), int(model.tree_model.post_triples[-1][1]), mg.data_ptr(), stream)
+        ctx.save_for_backward(out[1:], mg)
         ctx.in_devices = (branch_lengths.device, q.device, freqs.device, rates.device)
         ctx.in_dtype = branch_lengths.dtype
         return out[0].to(branch_lengths.device, branch_lengths.dtype)
 
     @staticmethod
     def backward(ctx, grad_output):
-        from .paramgrad import surrogate
-        bl, q, freqs, rates, g_bl, g = ctx.saved_tensors
+        g_bl, mg = ctx.saved_tensors
         need = ctx.needs_input_grad
-        out = [None, None, None, None, None]
         go = grad_output.to(g_bl.device, torch.float64)
+        out = [None, None, None, None, None]
         if need[0]:
             out[0] = (go * g_bl).to(ctx.in_devices[0], ctx.in_dtype)
-        if need[1] or need[2] or need[3]:
-            with torch.enable_grad():
-                leaves = [x.detach().requires_grad_(n) for x, n in zip((q, freqs, rates), need[1:4])]
-                s = surrogate(g, bl, *leaves, ctx.root_child)
-                wanted = [x for x in leaves if x.requires_grad]
-                grads = list(torch.autograd.grad(s, wanted, allow_unused=True))
-            for i, x in enumerate(leaves):
-                if x.requires_grad:
-                    gx = grads.pop(0)
-                    out[1 + i] = None if gx is None else (go * gx).to(ctx.in_devices[1 + i])
+        if need[1]:
+            out[1] = (go * mg[:16]).reshape(4, 4).to(ctx.in_devices[1])
+        if need[2]:
+            out[2] = (go * mg[16:20]).to(ctx.in_devices[2])
+        if need[3]:
+            out[3] = (go * mg[20:]).to(ctx.in_devices[3])
         return tuple(out)
 
 

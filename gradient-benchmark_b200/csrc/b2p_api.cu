@@ -32,6 +32,7 @@ struct b2p_instance {
   const void* kernel = nullptr;
   const void* kernel_outer = nullptr;  // B2P_FLAG_OUTER_PRODUCTS: the same walk, also summing the branches' outer products
   double* d_opart = nullptr;           // [grid][2N-2][K][16]
+  double* d_mgpart = nullptr;          // b2p_model_gradients: [K][blocks][17] partial sums
   // device scratch
   unsigned char* d_records = nullptr;  // round records: descriptors | issue record | matrix rows (K1 writes these)
   int* d_mat_dst = nullptr;
@@ -362,7 +363,7 @@ int b2p_destroy(b2p_instance* h) {
   peer_release(h);
   cudaFree(h->d_records); cudaFree(h->d_mat_dst);
   cudaFree(h->d_tips); cudaFree(h->d_tips_raw); cudaFree(h->d_tip_order); cudaFree(h->d_weights); cudaFree(h->d_msg); cudaFree(h->d_pre);
-  cudaFree(h->d_lpart); cudaFree(h->d_trace); cudaFree(h->d_gpart); cudaFree(h->d_opart); cudaFree(h->d_bl_stage); cudaFree(h->d_out_stage);
+  cudaFree(h->d_lpart); cudaFree(h->d_trace); cudaFree(h->d_gpart); cudaFree(h->d_opart); cudaFree(h->d_mgpart); cudaFree(h->d_bl_stage); cudaFree(h->d_out_stage);
   if (h->dense) {
     b2p_instance::Dense* d = h->dense;
     for (void* p : {(void*)d->evec, (void*)d->ivec, (void*)d->evals, (void*)d->q, (void*)d->qt, (void*)d->freqs, (void*)d->P,
@@ -530,6 +531,7 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   if ((rc = dev_alloc(h, &h->d_lpart, sizeof(double) * h->wg.grid))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_gpart, sizeof(double) * (size_t)h->wg.grid * n_br))) return bail(rc);
   if (outer && (rc = dev_alloc(h, &h->d_opart, sizeof(double) * (size_t)h->wg.grid * n_br * K * 16))) return bail(rc);
+  if (outer && (rc = dev_alloc(h, &h->d_mgpart, sizeof(double) * 17 * K * ((n_br + kModelGradThreads - 1) / kModelGradThreads)))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_bl_stage, sizeof(double) * n_br))) return bail(rc);
   if ((rc = dev_alloc(h, &h->d_out_stage, sizeof(double) * (n_br + 1)))) return bail(rc);
   if ((e = cudaMallocHost((void**)&h->h_pin_in, sizeof(double) * n_br)) != cudaSuccess ||
@@ -834,6 +836,30 @@ int b2p_branch_outer_products(b2p_instance* h, const double* d_bl, double* d_log
   if (h->grad_op_set) return fail(h, B2P_ERR_ARG, "b2p_branch_outer_products: a gradient operator is set (b2p_set_gradient_operator)");
   if (h->peer.attached) return fail(h, B2P_ERR_UNSUPPORTED, "b2p_branch_outer_products: not with attached peers (sum the K x (2N-2) x 16 values with the caller's all-reduce)");
   cudaError_t e = launch_eval<double>(h, d_bl, d_logl, d_grad, (cudaStream_t)stream, d_outer);
+  if (e != cudaSuccess) return fail(h, B2P_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
+  return B2P_OK;
+}
+
+int b2p_model_gradients(b2p_instance* h, const double* d_bl, const double* d_outer, int32_t root_child, double* d_out,
+                        void* stream) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (!h->d_mgpart) return fail(h, B2P_ERR_ARG, "b2p_model_gradients: the instance was created without B2P_FLAG_OUTER_PRODUCTS");
+  if (!d_bl || !d_outer || !d_out) return fail(h, B2P_ERR_ARG, "b2p_model_gradients: null device pointer");
+  const int N = h->cfg.n_tips, K = h->cfg.n_categories, n_br = 2 * N - 2;
+  if (root_child < 0 || root_child >= n_br) return fail(h, B2P_ERR_ARG, "b2p_model_gradients: root_child %d out of range", root_child);
+  ModelGradArgs a;
+  memcpy(a.evec, h->model.evec, sizeof a.evec);
+  memcpy(a.ivec, h->model.ivec, sizeof a.ivec);
+  memcpy(a.evals, h->model.evals, sizeof a.evals);
+  memcpy(a.q, h->qmat, sizeof a.q);
+  memcpy(a.freqs, h->freqs, sizeof a.freqs);
+  for (int k = 0; k < kMaxCat; ++k) a.rates[k] = k < K ? h->model.rates[k] : 0.0;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int blocks = (n_br + kModelGradThreads - 1) / kModelGradThreads;
+  model_grad_kernel<<<dim3(blocks, K), kModelGradThreads, 0, st>>>(d_outer, d_bl, n_br, a, h->d_mgpart);
+  model_grad_finish_kernel<<<1, 64, 0, st>>>(h->d_mgpart, blocks, K, d_outer, n_br, root_child, a, d_out);
+  cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(h, B2P_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
   return B2P_OK;
 }

@@ -96,6 +96,97 @@ __global__ void grad_from_outer_kernel(const double* __restrict__ outer, int n_b
   grad[b] = g;
 }
 
+// Outer-product mode: gradients w.r.t. the rate matrix, the category rates and the frequencies
+// from the outer products.  With P = V e^{L tau} V^-1, tau = r_k t_b, and
+// W = G P^-T (so that dlogL = sum <W, dP>), the Frechet derivative of the exponential gives
+//   dlogL/dQ   = V^-T [ sum_{b,k} (V^T G_{b,k} V^-T) o psi(tau_{b,k}) ] V^T,
+//                psi_ij = (e^{(l_i - l_j) tau} - 1) / (l_i - l_j)   (tau where l_i = l_j),
+//   dlogL/dr_k = sum_b t_b <Q, G_{b,k}>        (Q and P commute),
+//   dlogL/dpi_i (root prior only) = sum_k G_{c,k}[i][i] / pi_i for a child c of the root.
+// Q is treated as 16 free entries: the caller chains dQ/dtheta (any parameterisation).
+// Stage 1: one thread per (branch, category), blockIdx.y = category; a block leaves its 16 + 1
+// sums in part[category][block][17].  Stage 2 (one block) adds them in order and finishes.
+struct ModelGradArgs {
+  double evec[16], ivec[16], evals[4], q[16], freqs[4];
+  double rates[kMaxCat];
+};
+constexpr int kModelGradThreads = 128;
+__global__ void __launch_bounds__(kModelGradThreads) model_grad_kernel(const double* __restrict__ outer, const double* __restrict__ bl,
+                                                                       int n_br, ModelGradArgs a, double* __restrict__ part) {
+  __shared__ double red[kModelGradThreads / 32][17];
+  const int b = blockIdx.x * kModelGradThreads + threadIdx.x, k = blockIdx.y;
+  double s[17];
+#pragma unroll
+  for (int i = 0; i < 17; ++i) s[i] = 0.0;
+  if (b < n_br) {
+    double g[16], x[16];
+    const double2* src = reinterpret_cast<const double2*>(outer + ((size_t)k * n_br + b) * 16);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { const double2 v = src[e]; g[2 * e] = v.x; g[2 * e + 1] = v.y; }
+    const double t = bl[b], tau = a.rates[k] * t;
+    double qg = 0.0;
+#pragma unroll
+    for (int e = 0; e < 16; ++e) qg += a.q[e] * g[e];
+    s[16] = t * qg;
+    // x = V^T g, h = x V^-T
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        x[4 * i + j] = a.evec[i] * g[j] + a.evec[4 + i] * g[4 + j] + a.evec[8 + i] * g[8 + j] + a.evec[12 + i] * g[12 + j];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const double h = x[4 * i] * a.ivec[4 * j] + x[4 * i + 1] * a.ivec[4 * j + 1] + x[4 * i + 2] * a.ivec[4 * j + 2] +
+                         x[4 * i + 3] * a.ivec[4 * j + 3];
+        const double d = a.evals[i] - a.evals[j], z = d * tau;
+        const double psi = fabs(z) < 1e-9 ? tau * (1.0 + 0.5 * z) : expm1(z) / d;
+        s[4 * i + j] = h * psi;
+      }
+  }
+#pragma unroll
+  for (int i = 0; i < 17; ++i) {
+    const double v = warp_sum(s[i]);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5][i] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 17) {
+    double v = 0.0;
+    for (int w = 0; w < kModelGradThreads / 32; ++w) v += red[w][threadIdx.x];
+    part[((size_t)k * gridDim.x + blockIdx.x) * 17 + threadIdx.x] = v;
+  }
+}
+// out: [16] dlogL/dQ (row-major) | [4] dlogL/dpi (root prior) | [K] dlogL/dr_k
+__global__ void model_grad_finish_kernel(const double* __restrict__ part, int n_blocks, int K, const double* __restrict__ outer,
+                                         int n_br, int root_child, ModelGradArgs a, double* __restrict__ out) {
+  __shared__ double sm[16];
+  const int i = threadIdx.x;
+  if (i < 16) {
+    double v = 0.0;
+    for (int j = 0; j < K * n_blocks; ++j) v += part[(size_t)j * 17 + i];
+    sm[i] = v;
+  }
+  __syncthreads();
+  if (i < 16) {  // dQ = V^-T S V^T
+    const int r = i >> 2, c = i & 3;
+    double v = 0.0;
+    for (int x = 0; x < 4; ++x)
+      for (int y = 0; y < 4; ++y) v += a.ivec[4 * x + r] * sm[4 * x + y] * a.evec[4 * c + y];
+    out[i] = v;
+  } else if (i < 20) {
+    const int d = i - 16;
+    double v = 0.0;
+    for (int k = 0; k < K; ++k) v += outer[((size_t)k * n_br + root_child) * 16 + 5 * d];
+    out[i] = v / a.freqs[d];
+  } else if (i < 20 + K) {
+    const int k = i - 20;
+    double v = 0.0;
+    for (int j = 0; j < n_blocks; ++j) v += part[((size_t)k * n_blocks + j) * 17 + 16];
+    out[i] = v;
+  }
+}
+
 // Outer-product mode: sum the per-CTA parts [grid][2N-2][K][16] in CTA order (deterministic) and
 // write them as [K][2N-2][4][4] — the layout b200phylo/paramgrad.py contracts.  A block takes 64
 // pairs of outputs; its 8 thread rows each add a contiguous eighth of the parts (independent

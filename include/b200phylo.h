@@ -175,6 +175,20 @@ int b2p_set_gradient_operator(b2p_instance* h, const double* h_op, const double*
 int b2p_branch_outer_products(b2p_instance* h, const double* d_bl, double* d_logl, double* d_grad,
                               double* d_outer, void* cuda_stream);
 
+/* Gradients w.r.t. the model from the outer products, on the device (same instance, same
+ * branch lengths and model as the b2p_branch_outer_products call that filled d_outer):
+ *     d_out[0..15]     dlogL/dQ_ij, row-major, Q's 16 entries taken as free (P = exp(Q r t)):
+ *                      V^-T [ sum_{b,k} (V^T G V^-T) o psi(r_k t_b) ] V^T with the divided
+ *                      differences psi_ij = (e^{(l_i-l_j) tau} - 1)/(l_i-l_j) of the eigenvalues
+ *     d_out[16..19]    dlogL/dpi_i through the root prior only: sum_k G_{root_child,k}[i][i]/pi_i
+ *     d_out[20..20+K)  dlogL/dr_k = sum_b t_b <Q, G_{b,k}>
+ * The caller chains dQ/dtheta, dpi/dtheta, dr/dtheta of its parameterisation (GTR
+ * exchangeabilities, kappa, frequencies, Gamma / Weibull shape) — a few dozen flops.  Two small
+ * launches; replaces the 4x4 matrix exponentials b200phylo/paramgrad.py did with torch.
+ * root_child: branch id of either child of the root. */
+int b2p_model_gradients(b2p_instance* h, const double* d_bl, const double* d_outer, int32_t root_child,
+                        double* d_out, void* cuda_stream);
+
 /* Multi-GPU, one process per GPU: pattern shards per rank, results summed
  * over ranks.  With peers attached the final reduction kernel of every evaluation IS the
  * all-reduce: it stores its sums into every peer's receive buffer over NVLink (CUDA IPC

@@ -55,8 +55,15 @@ def test_parameter_gradients_match_autograd_of_pruning(kind, gamma):
         return {"q": q, "freqs": f, "rates": rt}
 
     root_children = tree.children[tree.root]
-    s = pg.parameter_gradients(eng, bl, root_children, model)
+    s = pg.parameter_gradients(eng, bl, root_children, model)  # G in one pass, b2p_model_gradients
     s.backward()
+    # the round-1 route (16 K evaluations, torch's matrix exponentials) gives the same gradients
+    dev_grads = [x.grad.clone() for x in (ex, fr, rt, bl)]
+    for x in (ex, fr, rt, bl):
+        x.grad = None
+    pg.parameter_gradients(eng, bl, root_children, model, g=pg.branch_outer_products(eng, bl, one_pass=False)).backward()
+    for a, b in zip(dev_grads, (ex, fr, rt, bl)):
+        assert grad_err(a.cpu().numpy(), b.grad.cpu().numpy()) < 1e-10
     # oracle route
     oex, ofr, ort, obl = leaves("cpu")
     q, f = build(oex, ofr)

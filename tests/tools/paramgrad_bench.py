@@ -64,7 +64,15 @@ for name in ("gtr_1000x10k", "hky_g4_flu", "gtr_g4_5000x10k"):
     twin = eng._outer_twin()
     ms_twin_eval, _ = timed(lambda: twin.loglik_grad_device(bl.data_ptr(), out.data_ptr(), out.data_ptr() + 8, stream), n=50)
     ms_g16_dev, ms_g16 = timed(lambda: pg.branch_outer_products(eng, bl, one_pass=False), n=3, warm=1)
-    _, ms = timed(run, n=10)
+    ms_dev, ms = timed(run, n=20)
+    mg = torch.empty(20 + eng.n_categories, dtype=torch.float64, device=dev)
+    root_child = int(w.tree.children[w.tree.root][0])
+
+    def device_part():
+        eng.branch_outer_products(bl.data_ptr(), out.data_ptr(), out.data_ptr() + 8, g_buf.data_ptr(), stream)
+        eng.model_gradients(bl.data_ptr(), g_buf.data_ptr(), root_child, mg.data_ptr(), stream)
+
+    ms_all_dev, _ = timed(device_part, n=50)
     g1 = pg.branch_outer_products(eng, bl)
     g16 = pg.branch_outer_products(eng, bl, one_pass=False)
     err = float(((g1 - g16).abs() / g16.abs().amax(dim=(2, 3), keepdim=True).clamp_min(1e-300)).max())
@@ -73,7 +81,8 @@ for name in ("gtr_1000x10k", "hky_g4_flu", "gtr_g4_5000x10k"):
                  "ms_branch_gradient_on_the_outer_products_instance": ms_twin_eval,
                  "ms_outer_products_one_pass": ms_g1_dev, "one_pass_over_one_evaluation": ms_g1_dev / ms_eval,
                  "ms_outer_products_16K_evaluations": ms_g16_dev, "evaluations_16K": 16 * w.n_categories,
-                 "ms_all_parameter_gradients_wall": ms, "one_pass_vs_16K_max_rel_diff": err,
+                 "ms_outer_products_and_model_gradients": ms_all_dev, "all_gradients_over_one_evaluation": ms_all_dev / ms_eval,
+                 "ms_all_parameter_gradients_wall": ms, "ms_all_parameter_gradients_device_events": ms_dev, "one_pass_vs_16K_max_rel_diff": err,
                  "twin_geometry": {k: eng._outer_twin().info()[k] for k in ("warps_per_block", "cols_per_tile", "tasks_per_round", "grid_blocks", "n_tiles",
                                                                              "regs_per_thread", "copy_depth", "pool_blocks")},
                  "d_exchangeabilities": ex.grad.cpu().tolist(), "d_rates": rt.grad.cpu().tolist()})
