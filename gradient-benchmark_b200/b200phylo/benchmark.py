@@ -10,7 +10,9 @@ and writes the CSV whose header, once ``program,size,rep,precision,`` is prepend
 the pipeline's awk (/root/reference/modules/micro.nf:54-56), yields the columns
 ``plot.Rmd`` reads: ``function,mode,JIT,time`` (/root/reference/plot.Rmd:257-266).
 Rows: ``treelikelihoodJC69,{evaluation,gradient},off,<seconds for all replicates>``
-and, with ``--gtr``, ``treelikelihoodGTR,...`` (/root/reference/plot.Rmd:262,305).
+and, with ``--gtr``, ``treelikelihoodGTR,...`` (/root/reference/plot.Rmd:262,305) — whose
+gradient row differentiates w.r.t. the branch lengths AND the GTR exchangeabilities and
+frequencies (held as parameters, as in torchtree), from one outer-products evaluation.
 
 When the tip labels carry sampling dates (``name_date``, /root/reference/bin/helper.py:28-47)
 the time-tree functions of the micro benchmark are timed too
@@ -36,10 +38,11 @@ import torch
 
 from .alignment import compress_alignment, read_fasta
 from .sitemodel import ConstantSiteModel
+from .diffmodels import DifferentiableGTR
 from .substitution import GTR, JC69
 from .timetree import (ConstantCoalescentModel, ReparameterizedTimeTreeModel, tip_heights_from_names)
 from .tree import Tree
-from .treelikelihood import TreeLikelihoodModel, UnrootedTreeModel
+from .treelikelihood import Parameter, TreeLikelihoodModel, UnrootedTreeModel
 
 __all__ = ["main", "run_benchmark"]
 
@@ -70,10 +73,20 @@ def run_benchmark(fasta: str, newick: str, replicates: int, scaler: float, gtr: 
     torch.cuda.set_device(dev)
     rows = []
     models = [("treelikelihoodJC69", JC69())]
+    gtr_params = []
     if gtr:
-        # the reference's --gtr run uses fixed, non-trivial GTR parameters; only time is recorded
-        models.append(("treelikelihoodGTR", GTR((1.0, 2.0, 1.0, 1.0, 2.0, 1.0), (0.3, 0.2, 0.2, 0.3))))
+        # torchtree's GTR holds its exchangeabilities and frequencies as parameters and the --gtr
+        # gradient rows differentiate w.r.t. them as well as the branch lengths (by autograd of the
+        # pruning recursion there; here: one outer-products evaluation).  float32 engines have no
+        # outer-products mode: there the row is the branch gradient only, as in round 1.
+        if dtype == "float64":
+            gtr_params = [Parameter("gtr.rates", torch.tensor([1.0, 2.0, 1.0, 1.0, 2.0, 1.0], dtype=torch.float64, device=dev)),
+                          Parameter("gtr.frequencies", torch.tensor([0.3, 0.2, 0.2, 0.3], dtype=torch.float64, device=dev))]
+            models.append(("treelikelihoodGTR", DifferentiableGTR("gtr", *gtr_params)))
+        else:
+            models.append(("treelikelihoodGTR", GTR((1.0, 2.0, 1.0, 1.0, 2.0, 1.0), (0.3, 0.2, 0.2, 0.3))))
     for fname, subst in models:
+        own = gtr_params if fname == "treelikelihoodGTR" else []
         bl = torch.tensor(tree.branch_lengths, dtype=torch.float64, device=dev)
         tm = UnrootedTreeModel("tree", tree, bl)
         model = TreeLikelihoodModel("like", sp, tm, subst, ConstantSiteModel(), precision=dtype,
@@ -85,6 +98,8 @@ def run_benchmark(fasta: str, newick: str, replicates: int, scaler: float, gtr: 
 
         def gradient():
             bl.grad = None
+            for p in own:
+                p.tensor.grad = None
             model().backward()
 
         bl.requires_grad_(False)
@@ -93,6 +108,8 @@ def run_benchmark(fasta: str, newick: str, replicates: int, scaler: float, gtr: 
         t_eval = _time_loop(evaluation, replicates)
         logl = float(evaluation())
         bl.requires_grad_(True)
+        for p in own:
+            p.requires_grad = True
         for _ in range(warmup):
             gradient()
         t_grad = _time_loop(gradient, replicates)
@@ -101,7 +118,10 @@ def run_benchmark(fasta: str, newick: str, replicates: int, scaler: float, gtr: 
                      "logl": logl, "alg_bytes": info["alg_bytes_loglik"]})
         rows.append({"function": fname, "mode": "gradient", "JIT": "off", "time": t_grad,
                      "logl": logl, "alg_bytes": info["alg_bytes_grad"],
-                     "grad_norm": float(bl.grad.norm())})
+                     "grad_norm": float(bl.grad.norm()),
+                     **({"grad_wrt": "branch lengths, GTR rates, frequencies",
+                         "grad_rates": own[0].tensor.grad.cpu().tolist(), "grad_frequencies": own[1].tensor.grad.cpu().tolist()}
+                        if own else {})})
         model.close()
     if dated:
         rows += run_time_functions(time_tree, replicates, device, warmup)

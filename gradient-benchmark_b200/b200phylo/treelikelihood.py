@@ -286,8 +286,28 @@ class TreeLikelihoodModel:
             self.fused_allreduce = attach_peers(self.engine, group)
 
     def update_model(self) -> None:
-        """Push the substitution / site model to the engine (call after changing them)."""
+        """Push the substitution / site model to the engine (call after changing them; models whose
+        parameters are tensors are followed automatically, see ``_refresh_model``)."""
         self.engine.set_model(self.subst_model, self.site_model)
+        self._model_key = self._current_model_key()
+
+    def _current_model_key(self):
+        """Identity and in-place version of every tensor a differentiable model is made of."""
+        key = []
+        for m in (self.subst_model, self.site_model):
+            ps = getattr(m, "differentiable_parameters", None)
+            if ps is not None:
+                for p in ps():
+                    t = p.tensor if hasattr(p, "tensor") else p
+                    key.append((id(t), t._version))
+        return tuple(key)
+
+    def _refresh_model(self) -> None:
+        """Tensor-valued model parameters may have changed since the last call (an optimiser step):
+        redo the eigen system and push it — only then (a 4x4 eigendecomposition on the host and a
+        dropped CUDA graph cost about as much as a small evaluation)."""
+        if self._current_model_key() != self._model_key:
+            self.update_model()
 
     # ---------------------------------------------------------------- evaluation
     def _scaled_branch_lengths(self) -> torch.Tensor:
@@ -305,8 +325,7 @@ class TreeLikelihoodModel:
     def __call__(self, *args, **kwargs) -> torch.Tensor:
         if torch.is_grad_enabled() and (is_differentiable(self.subst_model) or is_differentiable(self.site_model)):
             return self._call_with_model_parameters()
-        if hasattr(self.subst_model, "differentiable_parameters") or hasattr(self.site_model, "differentiable_parameters"):
-            self.update_model()  # tensors may have changed since the last call
+        self._refresh_model()
         return TreeLikelihoodFunction.apply(self._scaled_branch_lengths(), self)
 
     def _call_with_model_parameters(self) -> torch.Tensor:
@@ -316,7 +335,7 @@ class TreeLikelihoodModel:
             raise EngineError("gradients w.r.t. model parameters are computed on one GPU (no pattern shards yet)")
         if not self.engine.supports_outer_products():
             raise EngineError("gradients w.r.t. model parameters need 4 states, float64 and 1 or 4 rate categories")
-        self.update_model()
+        self._refresh_model()
         dev = torch.device(f"cuda:{self.engine.device}")
         sm, st = self.subst_model, self.site_model
         if hasattr(sm, "q_tensor"):

@@ -196,7 +196,7 @@ def test_tree_likelihood_model_differentiates_model_parameters(where, site):
         orates, weights = torch.ones(1, dtype=torch.float64), np.ones(1)
     ll = param_oracle.log_likelihood(tree.post_triples, w.patterns.partials(), w.patterns.weights, obl, q, f, orates, weights)
     (3.0 * ll).backward()
-    assert rel_err(float(logl), float(ll.detach())) < 1e-10
+    assert rel_err(float(logl.detach()), float(ll.detach())) < 1e-10
     pairs = [("exchangeabilities", ex.grad, oex.grad), ("frequencies", fr.grad, ofr.grad), ("branch lengths", bl.grad, obl.grad)]
     if site == "weibull":
         pairs.append(("shape", shape.grad, oshape.grad))
