@@ -352,7 +352,8 @@ struct OuterSlot {
   int lane;         // a lane of this warp that belongs to the slot (its descriptor is the slot's)
 };
 struct OuterCtx {
-  unsigned stage;   // this warp's 4 KB of staging rows (32 columns x 8 doubles, twice)
+  unsigned st[4];   // where this lane stores the four 16-byte chunks of its column's A values (B: + 2048)
+  unsigned ld[4];   // where this lane loads its A element of product d from: ld[d % 4] + (d / 4) * 1024 (B: + 2048)
   unsigned row;     // this warp's A row ([K][32] doubles); its B row follows
   int bl;           // boundary lane: lanes below belong to slot A, the others to slot B (32: no slot B)
   OuterSlot a, b;
@@ -367,35 +368,47 @@ struct OuterCtx {
 // then takes four columns of one category.  Products whose four columns all sit on one side of
 // the boundary lane go to that slot's accumulator; a mixed one runs twice with the other slot's
 // columns zeroed.
+// Staging layout: a column (lane) has a 64-byte row of A values and, 2048 bytes on, one of B
+// values.  Row of lane l: l ^ ((l >> 2) & 1) — neighbours of a category alternate bank halves —
+// and the row's 16-byte chunks are XOR-swizzled, so that the stores (8 lanes x 16 bytes per
+// phase) and the loads (four rows x 32 bytes per half-warp, at K = 4 rows 8 apart) are both
+// conflict-free.  Product d takes, at K = 1, columns 4 d .. 4 d + 3; at K = 4, category d % 4,
+// columns d % 4 + 4 (t + 4 (d / 4)), t = 0..3; lane (g, t) loads element g of column t of the
+// four.  All of this depends on the lane only: outer_addresses runs once per kernel.
+__device__ __forceinline__ unsigned outer_swizzle(unsigned row) { return ((((row >> 1) ^ (row >> 3)) & 1u) << 1) | ((row >> 2) & 1u); }
+template <int K>
+__device__ __forceinline__ unsigned outer_column(int d, unsigned t) {
+  return K == 1 ? 4u * d + t : (unsigned)(d & 3) + 4u * (t + 4u * (unsigned)(d >> 2));
+}
+template <int K>
+__device__ __forceinline__ void outer_addresses(OuterCtx& oc, unsigned stage, int lane) {
+  const unsigned row = (unsigned)lane ^ (((unsigned)lane >> 2) & 1u), sw = outer_swizzle(row);
+  const unsigned g = (unsigned)lane >> 2, t = (unsigned)lane & 3u;
+#pragma unroll
+  for (unsigned c = 0; c < 4; ++c) {
+    oc.st[c] = stage + row * 64 + ((c ^ sw) << 4);
+    const unsigned col = outer_column<K>((int)c, t), r2 = col ^ ((col >> 2) & 1u);
+    oc.ld[c] = stage + r2 * 64 + (((g >> 1) ^ outer_swizzle(r2)) << 4) + ((g & 1u) << 3);  // products c + 4: 16 rows = 1024 bytes on
+  }
+}
+
 template <int K>
 __device__ __forceinline__ void outer_sums(const OuterCtx& oc, int lane, const double (&aq)[8], const double (&m)[8], int dbg = 0) {
-  const unsigned row = (unsigned)lane ^ (((unsigned)lane >> 2) & 1u);  // neighbours of a category alternate bank halves
-  // 16-byte chunks XOR-swizzled so that the stores (8 lanes x 16 bytes per phase) and the loads
-  // below (four rows x 32 bytes per half-warp, at K = 4 rows 8 apart) are both conflict-free
-  const unsigned wr = oc.stage + row * 64, sw = ((((row >> 1) ^ (row >> 3)) & 1u) << 1) | ((row >> 2) & 1u);
 #ifdef B2P_DBG
   if (!(dbg & 64))
 #endif
 #pragma unroll
-  for (unsigned c = 0; c < 4; ++c) {
-    sts_d2(wr + ((c ^ sw) << 4), aq[2 * c], aq[2 * c + 1]);
-    sts_d2(wr + 2048 + ((c ^ sw) << 4), m[2 * c], m[2 * c + 1]);
+  for (int c = 0; c < 4; ++c) {
+    sts_d2(oc.st[c], aq[2 * c], aq[2 * c + 1]);
+    sts_d2(oc.st[c] + 2048, m[2 * c], m[2 * c + 1]);
   }
   __syncwarp();
-  const unsigned g = (unsigned)lane >> 2, t = (unsigned)lane & 3u;
   // all sixteen loads first, then the products: two independent accumulation chains per category
   double av[8], bv[8];
-  bool in_a[8];
 #pragma unroll
   for (int d = 0; d < 8; ++d) {
-    // K = 1: columns 4 d .. 4 d + 3;  K = 4: category d % 4, columns k + 4 (t + 4 (d / 4))
-    const unsigned col = K == 1 ? 4u * d + t : (unsigned)(d & 3) + 4u * (t + 4u * (unsigned)(d >> 2));
-    const unsigned r2 = col ^ ((col >> 2) & 1u);
-    const unsigned s2 = ((((r2 >> 1) ^ (r2 >> 3)) & 1u) << 1) | ((r2 >> 2) & 1u);
-    const unsigned at = oc.stage + r2 * 64 + (((g >> 1) ^ s2) << 4) + ((g & 1u) << 3);
-    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(av[d]) : "r"(at));
-    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(bv[d]) : "r"(at + 2048));
-    in_a[d] = (int)col < oc.bl;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(av[d]) : "r"(oc.ld[d & 3] + (d >> 2) * 1024));
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(bv[d]) : "r"(oc.ld[d & 3] + (d >> 2) * 1024 + 2048));
   }
   constexpr int NA = K == 1 ? 2 : K;  // accumulators per slot: K = 1 splits its products into two chains
   double ca[NA][2], cb[NA][2];
@@ -410,20 +423,25 @@ __device__ __forceinline__ void outer_sums(const OuterCtx& oc, int lane, const d
 #pragma unroll
   for (int d = 0; d < 8; ++d) {
     const int ai = K == 1 ? (d & 1) : (d & 3);
-    const int first = K == 1 ? 4 * d : (d & 3) + 16 * (d >> 2), last = K == 1 ? 4 * d + 3 : first + 12;  // warp-uniform
-    if (first < oc.bl) {
-      const double x = in_a[d] ? av[d] : 0.0;
+    const int first = (int)outer_column<K>(d, 0u), last = (int)outer_column<K>(d, 3u);  // warp-uniform branches below
+    if (last < oc.bl) {
       asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
-                   : "+d"(ca[ai][0]), "+d"(ca[ai][1]) : "d"(x), "d"(bv[d]));
-    }
-    if (last >= oc.bl) {
-      const double x = in_a[d] ? 0.0 : av[d];
+                   : "+d"(ca[ai][0]), "+d"(ca[ai][1]) : "d"(av[d]), "d"(bv[d]));
+    } else if (first >= oc.bl) {
       asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
-                   : "+d"(cb[ai][0]), "+d"(cb[ai][1]) : "d"(x), "d"(bv[d]));
+                   : "+d"(cb[ai][0]), "+d"(cb[ai][1]) : "d"(av[d]), "d"(bv[d]));
+    } else {  // the boundary lane is among the four columns: once per slot, the other slot's columns zeroed
+      const bool in_a = (int)outer_column<K>(d, (unsigned)lane & 3u) < oc.bl;
+      const double xa = in_a ? av[d] : 0.0, xb = in_a ? 0.0 : av[d];
+      asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                   : "+d"(ca[ai][0]), "+d"(ca[ai][1]) : "d"(xa), "d"(bv[d]));
+      asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                   : "+d"(cb[ai][0]), "+d"(cb[ai][1]) : "d"(xb), "d"(bv[d]));
     }
   }
   // lane (g, t) holds C[g][2t], C[g][2t+1]: rows 0-3 x columns 0-3 = the left branch's matrix
   // (entries 0-15 of the row), rows 4-7 x columns 4-7 = the right branch's (16-31)
+  const unsigned g = (unsigned)lane >> 2, t = (unsigned)lane & 3u;
   if ((g < 4) == (t < 2)) {
     const unsigned e = (g & 3u) * 4u + (t & 1u) * 2u + (g < 4 ? 0u : 16u);
 #pragma unroll
@@ -530,13 +548,18 @@ __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThrea
     if constexpr (OUTER) {
       static_assert(!OUTER || (CPT == 1 && (K == 1 || K == 4)), "outer-product mode: one column per thread, K = 1 or 4");
       const double a = (live && dd > 0.0) ? (K == 1 ? th.w[c] : th.w[c] * (double)th.cw) * fast_rcp(dd) : 0.0;
-      // lanes without a column: zeros (their operands are whatever their zero descriptor points at)
       double aq[8], m[8];
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         aq[i] = a * (double)ql[c][i]; aq[4 + i] = a * (double)qr[c][i];
-        m[i] = live ? (double)ma[i] : 0.0; m[4 + i] = live ? (double)mb[i] : 0.0;
+        m[i] = (double)ma[i]; m[4 + i] = (double)mb[i];
       }
+      // lanes without a column: zeros (their operands are whatever their zero descriptor points
+      // at — 0 x NaN would spoil the sum).  Rare, so a branch rather than sixteen selects.
+#pragma unroll 1
+      for (unsigned z = pinned((unsigned)!live); z != 0; --z)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) m[i] = 0.0;
       outer_sums<K>(oc, th.lane, aq, m, p.dbg);
     }
   }
@@ -685,7 +708,7 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
       o.rows1 = sbase + p.off_outer + 2 * (wf + 1) * p.outer_row;
       return o;
     };
-    oc.stage = sbase + p.off_ostage + warp * 4096;
+    outer_addresses<K>(oc, sbase + p.off_ostage + warp * 4096, lane);
     oc.row = sbase + p.off_outer + 2 * warp * p.outer_row;
     oc.bl = has_b ? end_a - w0 : 32;
     oc.a = slot(min(sa, p.wn - 1), 0);
