@@ -169,11 +169,10 @@ __device__ __forceinline__ int rescale(bool on, int lane, int kk, double (&y)[4]
   int need = 0;
 #pragma unroll 1
   for (unsigned z = pinned((unsigned)(on && h < 0x33700000 && h >= 0x00100000)); z != 0; --z) {  // < 2^-200, normal
-    need = (823 - (h >> 20) + 199) / 200;  // biased exponent against 823 = 1023 - 200
-#pragma unroll 1
-    for (int r = 0; r < need; ++r)
+    need = (823 - (h >> 20) + 199) / 200;  // biased exponent against 823 = 1023 - 200; at most 5
+    const double f = __hiloint2double((1023 + 200 * need) << 20, 0);  // factor^need, one multiplication
 #pragma unroll
-      for (int i = 0; i < 4; ++i) y[i] *= Scale<double>::factor();
+    for (int i = 0; i < 4; ++i) y[i] *= f;
   }
   return need;
 }
@@ -184,11 +183,10 @@ __device__ __forceinline__ int rescale(bool on, int lane, int kk, float (&y)[4])
   int need = 0;
 #pragma unroll 1
   for (unsigned z = pinned((unsigned)(on && h < 0x2b800000 && h >= 0x00800000)); z != 0; --z) {  // < 2^-40, normal
-    need = (87 - (h >> 23) + 39) / 40;  // biased exponent against 87 = 127 - 40
-#pragma unroll 1
-    for (int r = 0; r < need; ++r)
+    need = (87 - (h >> 23) + 39) / 40;  // biased exponent against 87 = 127 - 40; at most 3
+    const float f = __int_as_float((127 + 40 * need) << 23);  // factor^need, one multiplication
 #pragma unroll
-      for (int i = 0; i < 4; ++i) y[i] *= Scale<float>::factor();
+    for (int i = 0; i < 4; ++i) y[i] *= f;
   }
   return need;
 }
