@@ -313,6 +313,25 @@ static cudaError_t dense_launch(b2p_instance* h, const double* d_bl, double* d_l
   p.done_post = d->scount + d->cols_pad;
   p.done_pre = p.done_post + (size_t)(N - 1) * d->n_tiles;
   p.err = p.done_pre + (size_t)(N - 1) * d->n_tiles;
+  p.prof = nullptr;
+#ifdef B2P_DBG
+  static unsigned long long* g_dense_prof = nullptr;
+  if (getenv("B2P_DENSE_PROF")) {
+    if (!g_dense_prof) { cudaMalloc(&g_dense_prof, 16 * sizeof(unsigned long long)); cudaMemset(g_dense_prof, 0, 16 * sizeof(unsigned long long)); }
+    else {  // print what the previous evaluation left, then clear
+      unsigned long long hp[16];
+      cudaMemcpy(hp, g_dense_prof, sizeof hp, cudaMemcpyDeviceToHost);
+      for (int k = 0; k < 2; ++k)
+        if (hp[8 * k]) {
+          fprintf(stderr, "dense %s CTAs %llu, mean clocks per phase: wait %.0f, load %.0f, product %.0f, store %.0f, publish %.0f\n", k ? "pre " : "post",
+                  hp[8 * k], (double)hp[8 * k + 1] / hp[8 * k], (double)hp[8 * k + 2] / hp[8 * k], (double)hp[8 * k + 3] / hp[8 * k],
+                  (double)hp[8 * k + 4] / hp[8 * k], (double)hp[8 * k + 5] / hp[8 * k]);
+        }
+      cudaMemset(g_dense_prof, 0, sizeof hp);
+    }
+    p.prof = g_dense_prof;
+  }
+#endif
   cudaError_t e = cudaMemsetAsync(d->scount, 0, sizeof(int) * d->sync_ints, st);
   if (e != cudaSuccess) return e;
   const int slot = (int)(h->prof_count % b2p_instance::kProfRing);

@@ -47,7 +47,15 @@ struct DenseParams {
   int* err;                  // set when a dependency did not arrive within the time limit
   double* lpart;             // [n_tiles]
   double* gpart;             // [n_tiles][2N-2]
+  unsigned long long* prof;  // debug build (-DB2P_DBG, B2P_DENSE_PROF=1): [2][8] summed clocks per phase of the post / pre CTAs
 };
+#ifdef B2P_DBG
+#define DENSE_STAMP(i) do { if (p.prof && threadIdx.x == 0) stamp[i] = clock64(); } while (0)
+#define DENSE_STAMPS_FLUSH(k, n) do { if (p.prof && threadIdx.x == 0) { for (int i_ = 1; i_ < (n); ++i_) atomicAdd(p.prof + 8 * (k) + i_, (unsigned long long)(stamp[i_] - stamp[i_ - 1])); atomicAdd(p.prof + 8 * (k), 1ull); } } while (0)
+#else
+#define DENSE_STAMP(i) do { } while (0)
+#define DENSE_STAMPS_FLUSH(k, n) do { } while (0)
+#endif
 
 // ---------------------------------------------------------------------------- helpers
 // Thread t of the CTA owns, in every 64x64 operand tile, the column pair cp = 2 (t & 31) of the
@@ -299,6 +307,10 @@ __global__ void __launch_bounds__(DNT, 3) dense_post_kernel(const DenseParams p,
   const int warp = t >> 5, lane = t & 31, g = lane >> 2, tg = lane & 3;
   const int kr = t >> 5, cp = 2 * (t & 31);
   const bool is_root = nd.v == root;
+#ifdef B2P_DBG
+  long long stamp[6];
+#endif
+  DENSE_STAMP(0);
   unsigned lc0, lc1, rc0, rc1;
   fetch_codes(p, nd.l, col0 + cp, lc0, lc1);
   fetch_codes(p, nd.r, col0 + cp, rc0, rc1);
@@ -308,6 +320,7 @@ __global__ void __launch_bounds__(DNT, 3) dense_post_kernel(const DenseParams p,
   if (t == 0 && nd.l >= p.n_tips) tile_wait(p.done_post + (size_t)(nd.l - p.n_tips) * p.n_tiles + tile, p.err);
   if (t == 32 && nd.r >= p.n_tips) tile_wait(p.done_post + (size_t)(nd.r - p.n_tips) * p.n_tiles + tile, p.err);
   __syncthreads();
+  DENSE_STAMP(1);  // 0-1: codes, launch wait, dependency flags
   {
     double2 ml[2][DH], mr[2][DH];
 #pragma unroll
@@ -324,6 +337,7 @@ __global__ void __launch_bounds__(DNT, 3) dense_post_kernel(const DenseParams p,
   }
   copy_rows_wait();
   __syncthreads();
+  DENSE_STAMP(2);  // 1-2: operands from global memory into shared memory
   if (!is_root) {
     // x_v is rescaled BEFORE the product (same rule as the 4-state kernel): the column
     // maximum of X decides, the product carries the factor through.
@@ -339,13 +353,17 @@ __global__ void __launch_bounds__(DNT, 3) dense_post_kernel(const DenseParams p,
     }
     double acc[8][2];
     tile_product(A, X, warp, lane, acc);
+    DENSE_STAMP(3);  // 2-3: rescale decision + product (thread 0's warp)
     double* out = p.msg + ((size_t)(nd.v - p.n_tips) * SP + g) * p.cols_pad + col0 + 8 * warp + 2 * tg;
     const double f0 = bump[0] ? Scale<double>::factor() : 1.0, f1 = bump[1] ? Scale<double>::factor() : 1.0;
 #pragma unroll
     for (int mi = 0; mi < 8; ++mi)
       *reinterpret_cast<double2*>(out + (size_t)8 * mi * p.cols_pad) = make_double2(acc[mi][0] * f0, acc[mi][1] * f1);
     __syncthreads();
+    DENSE_STAMP(4);  // 3-4: stores + the slowest warp
     if (t == 0) tile_publish(p.done_post + (size_t)(nd.v - p.n_tips) * p.n_tiles + tile);
+    DENSE_STAMP(5);  // 4-5: fence + flag
+    DENSE_STAMPS_FLUSH(0, 6);
   } else {
     double term = 0.0;
     if (t < DT) {
@@ -385,6 +403,10 @@ __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, 
   const int warp = t >> 5, lane = t & 31, g = lane >> 2, tg = lane & 3;
   const int kr = t >> 5, cp = 2 * (t & 31);
   const bool is_root = nd.v == root;
+#ifdef B2P_DBG
+  long long stamp[6];
+#endif
+  DENSE_STAMP(0);
   unsigned sc0, sc1;
   fetch_codes(p, sib, col0 + cp, sc0, sc1);
   copy_rows_async(A1, p.Q, SP, kr, cp);
@@ -395,6 +417,7 @@ __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, 
     if (t == 0) tile_wait(p.done_pre + (size_t)(nd.v - p.n_tips) * p.n_tiles + tile, p.err);
     __syncthreads();
   }
+  DENSE_STAMP(1);
   {
     double2 ms[2][DH], uu[2][DH];
 #pragma unroll
@@ -422,8 +445,10 @@ __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, 
   }
   copy_rows_wait();
   __syncthreads();
+  DENSE_STAMP(2);
   double acc1[8][2], acc2[8][2];
   tile_product2(A1, A2, Qc, warp, lane, acc1, acc2);
+  DENSE_STAMP(3);
   // the child's own message in the accumulator layout (rows 8 mi + g, columns 8 w + 2 tg + {0, 1})
   double den[2] = {0.0, 0.0}, num[2] = {0.0, 0.0};
   {
@@ -448,7 +473,10 @@ __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, 
   for (int mi = 0; mi < 8; ++mi)
     *reinterpret_cast<double2*>(out + (size_t)8 * mi * p.cols_pad) = make_double2(acc2[mi][0] * f0, acc2[mi][1] * f1);
   __syncthreads();
+  DENSE_STAMP(4);
   if (t == 0) tile_publish(p.done_pre + (size_t)(c - p.n_tips) * p.n_tiles + tile);
+  DENSE_STAMP(5);
+  DENSE_STAMPS_FLUSH(1, 6);
   double gsum = 0.0;
   if (g == 0) {
     const double2 w = *reinterpret_cast<const double2*>(p.weights + col0 + 8 * warp + 2 * tg);
