@@ -39,7 +39,7 @@ import torch
 from .alignment import compress_alignment, read_fasta
 from .sitemodel import ConstantSiteModel
 from .diffmodels import DifferentiableGTR
-from .substitution import GTR, JC69
+from .substitution import JC69
 from .timetree import (ConstantCoalescentModel, ReparameterizedTimeTreeModel, tip_heights_from_names)
 from .tree import Tree
 from .treelikelihood import Parameter, TreeLikelihoodModel, UnrootedTreeModel
@@ -77,14 +77,11 @@ def run_benchmark(fasta: str, newick: str, replicates: int, scaler: float, gtr: 
     if gtr:
         # torchtree's GTR holds its exchangeabilities and frequencies as parameters and the --gtr
         # gradient rows differentiate w.r.t. them as well as the branch lengths (by autograd of the
-        # pruning recursion there; here: one outer-products evaluation).  float32 engines have no
-        # outer-products mode: there the row is the branch gradient only, as in round 1.
-        if dtype == "float64":
-            gtr_params = [Parameter("gtr.rates", torch.tensor([1.0, 2.0, 1.0, 1.0, 2.0, 1.0], dtype=torch.float64, device=dev)),
-                          Parameter("gtr.frequencies", torch.tensor([0.3, 0.2, 0.2, 0.3], dtype=torch.float64, device=dev))]
-            models.append(("treelikelihoodGTR", DifferentiableGTR("gtr", *gtr_params)))
-        else:
-            models.append(("treelikelihoodGTR", GTR((1.0, 2.0, 1.0, 1.0, 2.0, 1.0), (0.3, 0.2, 0.2, 0.3))))
+        # pruning recursion there; here: one outer-products evaluation — in fp64 also under
+        # -d float32: the outer-products instance has no fp32 form).
+        gtr_params = [Parameter("gtr.rates", torch.tensor([1.0, 2.0, 1.0, 1.0, 2.0, 1.0], dtype=torch.float64, device=dev)),
+                      Parameter("gtr.frequencies", torch.tensor([0.3, 0.2, 0.2, 0.3], dtype=torch.float64, device=dev))]
+        models.append(("treelikelihoodGTR", DifferentiableGTR("gtr", *gtr_params)))
     for fname, subst in models:
         own = gtr_params if fname == "treelikelihoodGTR" else []
         bl = torch.tensor(tree.branch_lengths, dtype=torch.float64, device=dev)

@@ -246,13 +246,14 @@ class Engine:
         return float(logl.value), grad
 
     def _remember(self, what: str, value) -> None:
-        if self.n_states == 4 and self.precision == "float64" and self.n_categories in (1, 4):
+        if self.supports_outer_products():
             self._setup[what] = value
             self._version += 1
 
     def supports_outer_products(self) -> bool:
-        """Whether ``branch_outer_products`` runs in one pass (4 states, fp64, 1 or 4 categories)."""
-        return self.n_states == 4 and self.precision == "float64" and self.n_categories in (1, 4)
+        """Whether ``branch_outer_products`` runs in one pass: 4 states and 1 or 4 rate categories
+        (the outer-products instance itself always works in fp64, also next to an fp32 engine)."""
+        return self.n_states == 4 and self.n_categories in (1, 4)
 
     def branch_outer_products(self, d_bl: int, d_logl: int, d_grad: Optional[int], d_outer: int, stream: int = 0) -> None:
         """G [K][2N-2][4][4] (``b2p_branch_outer_products``) on raw device pointers, in ONE
@@ -271,7 +272,7 @@ class Engine:
 
     def _outer_twin(self) -> "Engine":
         if not self.supports_outer_products():
-            raise EngineError("branch_outer_products needs 4 states, float64 and 1 or 4 rate categories")
+            raise EngineError("branch_outer_products needs 4 states and 1 or 4 rate categories")
         missing = [k for k in ("topology", "tips", "weights", "eigen", "categories") if k not in self._setup]
         if missing:
             raise EngineError(f"branch_outer_products before {', '.join(missing)} were set")

@@ -210,6 +210,11 @@ class TreeLikelihoodParameterFunction(torch.autograd.Function):
         g = torch.empty(eng.n_categories, eng.n_branches, 4, 4, dtype=torch.float64, device=dev)
         stream = torch.cuda.current_stream(dev).cuda_stream
         eng.branch_outer_products(bl.data_ptr(), out.data_ptr(), out.data_ptr() + 8, g.data_ptr(), stream)
+        if model.world_size > 1:
+            # pattern shards: logL, the branch gradient and the outer products are sums over patterns
+            # (the outer-products instance is not peer-attached: one NCCL all-reduce each)
+            allreduce_sum_(out, model.group)
+            allreduce_sum_(g, model.group)
         mg = torch.empty(20 + eng.n_categories, dtype=torch.float64, device=dev)
         eng.model_gradients(bl.data_ptr(), g.data_ptr(), int(model.tree_model.post_triples[-1][1]), mg.data_ptr(), stream)
         ctx.save_for_backward(out[1:], mg)
@@ -331,10 +336,8 @@ class TreeLikelihoodModel:
     def _call_with_model_parameters(self) -> torch.Tensor:
         """A substitution- or site-model parameter asks for a gradient: one pass that also returns
         the per-branch outer products (``TreeLikelihoodParameterFunction``)."""
-        if self.world_size > 1:
-            raise EngineError("gradients w.r.t. model parameters are computed on one GPU (no pattern shards yet)")
         if not self.engine.supports_outer_products():
-            raise EngineError("gradients w.r.t. model parameters need 4 states, float64 and 1 or 4 rate categories")
+            raise EngineError("gradients w.r.t. model parameters need 4 states and 1 or 4 rate categories")
         self._refresh_model()
         dev = torch.device(f"cuda:{self.engine.device}")
         sm, st = self.subst_model, self.site_model

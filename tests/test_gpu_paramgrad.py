@@ -130,6 +130,7 @@ def test_outer_products_unsupported_shapes_say_so():
         Engine(10, 100, 3, outer_products=True)
     with pytest.raises(EngineError, match="OUTER_PRODUCTS"):
         Engine(10, 100, 4, precision="float32", outer_products=True)
+    assert Engine(10, 100, 4, precision="float32").supports_outer_products()  # through an fp64 twin
     eng = Engine(10, 100, 4)
     with pytest.raises(EngineError, match="before"):
         eng.branch_outer_products(0, 0, None, 0)
