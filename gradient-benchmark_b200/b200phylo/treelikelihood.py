@@ -287,7 +287,7 @@ class TreeLikelihoodModel:
         # multi-GPU: the engine's own reduction kernel doubles as the all-reduce over NVLink
         # peer memory; NCCL stays the path only where that cannot be set up
         self.fused_allreduce = False
-        if self.world_size > 1 and getattr(site_pattern, "n_states", 4) == 4 and rank is None:
+        if self.world_size > 1 and rank is None:
             self.fused_allreduce = attach_peers(self.engine, group)
 
     def update_model(self) -> None:

@@ -302,6 +302,7 @@ static int dense_set_eigen(b2p_instance* h, const double* evec, const double* iv
   return B2P_OK;
 }
 
+static PeerArgs peer_args(b2p_instance* h);
 static cudaError_t dense_launch(b2p_instance* h, const double* d_bl, double* d_logl, double* d_grad, cudaStream_t st) {
   b2p_instance::Dense* d = h->dense;
   const int N = h->cfg.n_tips, n_br = 2 * N - 2;
@@ -361,7 +362,12 @@ static cudaError_t dense_launch(b2p_instance* h, const double* d_bl, double* d_l
   }
   if (h->profiling) { cudaEventRecord(h->ev1[slot], st); ++h->prof_count; }
   const int nb = d_grad ? n_br : 0;
-  reduce_kernel<<<(nb + 31) / 32 + 1, 512, 0, st>>>(h->d_gpart, h->d_lpart, d->n_tiles, nb, d_grad, d_logl);
+  if (h->peer.attached) {  // the reduction over tiles doubles as the all-reduce over ranks, as on the 4-state path
+    PeerArgs pa = peer_args(h);
+    reduce_exchange_kernel<<<(nb + 31) / 32 + 1, 512, 0, st>>>(h->d_gpart, h->d_lpart, d->n_tiles, nb, d_grad, d_logl, pa);
+  } else {
+    reduce_kernel<<<(nb + 31) / 32 + 1, 512, 0, st>>>(h->d_gpart, h->d_lpart, d->n_tiles, nb, d_grad, d_logl);
+  }
   return cudaGetLastError();
 }
 
@@ -947,7 +953,6 @@ int b2p_loglik_grad_host(b2p_instance* h, const double* h_bl, double* h_logl, do
 // ------------------------------------------------------------------ multi-GPU peer exchange
 int b2p_peer_export(b2p_instance* h, int32_t world, void* h_handle_out) {
   if (!h || !h_handle_out) return h ? fail(h, B2P_ERR_ARG, "b2p_peer_export: null pointer") : B2P_ERR_ARG;
-  if (h->dense) return fail(h, B2P_ERR_UNSUPPORTED, "b2p_peer_export: the dense-state path all-reduces through the caller");
   if (world < 2 || world > kMaxPeers) return fail(h, B2P_ERR_ARG, "b2p_peer_export: world must be 2..%d", kMaxPeers);
   if (h->peer.own) return fail(h, B2P_ERR_ARG, "b2p_peer_export: already exported");
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");

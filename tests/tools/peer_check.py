@@ -21,7 +21,7 @@ torch.cuda.set_device(local)
 dev = torch.device(f"cuda:{local}")
 dist.init_process_group("nccl", device_id=dev)
 ok = True
-for name, nt, npat in (("jc69_1000x10k", 200, 3001), ("hky_g4_flu", 150, 777)):
+for name, nt, npat in (("jc69_1000x10k", 200, 3001), ("hky_g4_flu", 150, 777), ("codon_500x2000", 40, 700)):
     w = make_workload(name, n_tips=nt, n_patterns=npat)
     lo, hi = shard_bounds(w.n_patterns, world, rank)
     sub = make_workload(name, n_tips=nt, n_patterns=npat)
@@ -60,7 +60,12 @@ for name, nt, npat in (("jc69_1000x10k", 200, 3001), ("hky_g4_flu", 150, 777)):
     same = all(torch.equal(g, gathered[0]) for g in gathered)
     line = f"rank {rank} {name}: attached={attached} err={err} rel_vs_nccl={rel:.2e} identical_across_ranks={same} evalonly_rel={abs(float(ev) - float(ref[0])) / abs(float(ref[0])):.2e}"
     if rank == 0:
-        ol, og = oracle_c(w)
+        if getattr(w.patterns, "n_states", 4) == 4:
+            ol, og = oracle_c(w)
+        else:  # dense-state path: the run-time-S C port
+            from oracle import c_oracle
+            ol, og = c_oracle.dense_loglik_and_gradient(w.tree.post_triples, w.patterns.masks, w.patterns.weights, w.tree.branch_lengths,
+                                                        *w.eigen_args())
         line += f" logl_rel_vs_oracle={abs(float(out[0]) - ol) / abs(ol):.2e} grad_vs_oracle={grad_err(out[1:].cpu().numpy(), og):.2e}"
         ok = ok and abs(float(out[0]) - ol) / abs(ol) < 1e-10 and grad_err(out[1:].cpu().numpy(), og) < 1e-8
     print(line, flush=True)
