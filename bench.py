@@ -412,6 +412,56 @@ def dense_roofline(info, w, k_avg_ms, k_n, steps, dev):
                      "peak_source": "fp64 torch.matmul 4096^3 (cuBLAS DGEMM), best of 5, measured in this run"}}
 
 
+def measure_parameter_gradients(dev, steps=30):
+    """SURVEY.md §8(f) row 3 as an extra entry of the line (N = 1): every substitution- / site-model
+    gradient of a GTR model at the headline shape from ONE outer-products walk + b2p_model_gradients,
+    next to one branch-gradient evaluation of the same model (device events, resident inputs)."""
+    import torch
+    from b200phylo.engine import Engine
+    from b200phylo.sitemodel import ConstantSiteModel
+    from b200phylo.substitution import GTR
+    from b200phylo.workloads import make_workload
+    w = make_workload("jc69_1000x10k")
+    eng = Engine(w.n_tips, w.n_patterns, 1, device=dev.index or 0)
+    try:
+        eng.set_topology(w.tree.post_triples)
+        eng.set_tip_states(w.patterns.masks)
+        eng.set_pattern_weights(w.patterns.weights)
+        eng.set_model(GTR((1.3, 2.9, 0.7, 1.1, 3.4, 1.0), (0.31, 0.19, 0.22, 0.28)), ConstantSiteModel())
+        bl = torch.tensor(w.tree.branch_lengths, dtype=torch.float64, device=dev)
+        out = torch.empty(1 + eng.n_branches, dtype=torch.float64, device=dev)
+        g = torch.empty(1, eng.n_branches, 4, 4, dtype=torch.float64, device=dev)
+        mg = torch.empty(21, dtype=torch.float64, device=dev)
+        st = torch.cuda.current_stream(dev).cuda_stream
+        root_child = int(w.tree.post_triples[-1][1])
+
+        def plain():
+            eng.loglik_grad_device(bl.data_ptr(), out.data_ptr(), out.data_ptr() + 8, st)
+
+        def everything():
+            eng.branch_outer_products(bl.data_ptr(), out.data_ptr(), out.data_ptr() + 8, g.data_ptr(), st)
+            eng.model_gradients(bl.data_ptr(), g.data_ptr(), root_child, mg.data_ptr(), st)
+
+        ms = []
+        for fn in (plain, everything):
+            for _ in range(3):
+                fn()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize(dev)
+            e0.record()
+            for _ in range(steps):
+                fn()
+            e1.record()
+            torch.cuda.synchronize(dev)
+            ms.append(e0.elapsed_time(e1) / steps)
+        return {"label": "f3: gradients w.r.t. GTR exchangeabilities, frequencies, category rates AND branch lengths in one pass",
+                "config": {"workload": "gtr_1000x10k (headline tree and alignment, GTR)", "n_taxa": w.n_tips, "n_patterns": w.n_patterns},
+                "ms_one_branch_gradient_evaluation": ms[0], "ms_all_gradients": ms[1], "ratio": ms[1] / ms[0], "steps": steps,
+                "api": "b2p_branch_outer_products + b2p_model_gradients", "dlogl_dQ_diag": [float(x) for x in mg[[0, 5, 10, 15]].cpu()]}
+    finally:
+        eng.close()
+
+
 # BASELINE.json configs besides the headline one, as short runs inside the same JSON line
 SECONDARY_1GPU = [
     ("configs[0]", "jc69_20x1000", "float64", 0),
@@ -470,6 +520,11 @@ def run_b200(a):
                     keep["scaling"] = "strong"
                     keep["whole_alignment_evals_per_s"] = r["value"] / ctx.world
                 secondary.append({"label": label, **keep})
+        if ctx.world == 1:
+            try:
+                secondary.append(measure_parameter_gradients(dev))
+            except Exception as exc:
+                secondary.append({"label": "f3: parameter gradients", "error": f"{type(exc).__name__}: {exc}"})
 
     if ctx.rank == 0:
         line = {"metric": METRIC, "value": head["value"], "unit": head["unit"], "n_gpus": ctx.world, "steps": a.steps,

@@ -12,6 +12,9 @@ for f in sys.argv[1:]:
     for s in d.get("secondary", []):
         if "error" in s:
             print("   ", s["label"], "ERROR", s["error"]); continue
+        if "ms_all_gradients" in s:
+            print(f"    f3 all parameter gradients: {s['ms_all_gradients']:.4f} ms = {s['ratio']:.2f} x one branch-gradient evaluation ({s['ms_one_branch_gradient_evaluation']:.4f} ms)")
+            continue
         rr = s["roofline"]
         print(f"    {s['label']}: {s['ms_per_step']:.4f} ms/step frac {rr['frac']:.3f}" + (f" issued {rr['issued_frac']:.3f}" if "issued_frac" in rr else "")
               + (f" whole-alignment {s['whole_alignment_evals_per_s']:.1f}/s" if "whole_alignment_evals_per_s" in s else "")
