@@ -57,8 +57,8 @@ struct WalkGeometry {
   int n_pool = 0;
   size_t smem = 0;
   // Outer-product mode (b2p_branch_outer_products): one column per thread, at least 32 threads per
-  // slot (a warp then holds columns of at most two slots), at most 14 slots (a named barrier
-  // each); every compute warp owns 4 KB of staging rows and two rows of K * 32 sums.
+  // slot (a warp then holds columns of at most two slots); every compute warp owns 4 KB of staging
+  // rows and, per round parity, two rows of K * 32 sums.
   bool outer = false;
   int off_outer = 0, outer_row = 0;  // bytes of one warp's row
   int off_ostage = 0;                // 4 KB per compute warp: the columns' operands of the tensor-core sums
@@ -109,7 +109,7 @@ inline int layout_walk(WalkGeometry& g, size_t smem_max) {
   off = (off + 127) & ~127;
   if (g.outer) {
     g.outer_row = K * 32 * 8;
-    g.off_outer = off; off += 2 * (g.nt / 32 - g.n_copy_warps) * g.outer_row;
+    g.off_outer = off; off += 4 * (g.nt / 32 - g.n_copy_warps) * g.outer_row;  // two rows per warp, two round parities
     g.off_ostage = off; off += (g.nt / 32 - g.n_copy_warps) * 4096;
   }
   g.off_freq = off; off += g.blk;  // the root's parent-side partial: the frequencies, for every column

@@ -60,7 +60,7 @@ struct WalkParams {
   double* lpart;              // [grid]
   double* gpart;              // [grid][2N-2]
   double* opart;              // outer-product mode: [grid][2N-2][K][16] per-CTA sums of (w / L) c_k q m^T
-  int off_outer, outer_row;   // outer-product mode: shared-memory rows of the compute warps, [warps][2][K * 32] doubles
+  int off_outer, outer_row;   // outer-product mode: shared-memory rows of the compute warps, [2 parities][warps][2][K * 32] doubles
   int off_ostage;             // outer-product mode: [warps] 4 KB staging rows of the tensor-core sums
   long long* trace;           // debug build (-DB2P_TRACE_CLOCKS): [2][rounds][8] clock stamps of CTA 0
   int dbg;                    // debug build (-DB2P_DBG): 1 skip the fold, 2 skip the stores, 4 skip the tasks, 8 skip the
@@ -336,27 +336,28 @@ __device__ __forceinline__ void post_task(const WalkParams<T>& p, const WalkThre
 // (b200phylo/paramgrad.py).  One column per thread; slots are packed at thread granularity as
 // usual, so a warp holds columns of one slot or of two neighbours ("A" below its boundary lane,
 // "B" from it on; ts >= 32 and ts % K == 0, so a lane's category is lane % K).  Per warp the sum
-// over columns runs on the fp64 tensor cores (outer_sums); per slot the warps that hold its
-// columns share a named barrier: a warp ARRIVES at its slot B's barrier (no wait: otherwise the
-// slots' folds would chain through the warps they share) and WAITS at its slot A's, then adds
-// the slot's rows (fixed order) into the CTA's part of `opart`, each of the slot's A warps a
-// share of the categories (outer_fold).
+// over columns runs on the fp64 tensor cores (outer_sums) and lands in the warp's rows of the
+// round's parity; per slot, the warps that have it as their slot A add the rows of all its warps
+// (fixed order) into the CTA's part of `opart` at the TOP of the next round (outer_fold) — the
+// round's barrier has made the rows complete, the rows of the other parity are being written,
+// and the additions overlap the wait for the next operands instead of sitting at a round's tail.
 struct OuterSlot {
-  unsigned row0;    // shared-memory row of the slot's first warp for this slot
+  unsigned row0;    // shared-memory row of the slot's first warp for this slot (parity 0)
   unsigned rows1;   // the A row of the slot's second warp (further warps: 2 rows on)
-  int n_warps;      // warps holding columns of the slot (the barrier's participants)
+  int n_warps;      // warps holding columns of the slot
   int n_fold, r;    // warps that have the slot as their A slot, this warp's index among them
-  int bar;          // named barrier of the slot
-  int lane;         // a lane of this warp that belongs to the slot (its descriptor is the slot's)
 };
 struct OuterCtx {
   unsigned st[4];   // where this lane stores the four 16-byte chunks of its column's A values (B: + 2048)
   unsigned ld[4];   // where this lane loads its A element of product d from: ld[d % 4] + (d / 4) * 1024 (B: + 2048)
-  unsigned row;     // this warp's A row ([K][32] doubles); its B row follows
+  unsigned row;     // this warp's A row ([K][32] doubles) of parity 0; its B row follows
+  unsigned par;     // bytes from a row of parity 0 to the same row of parity 1
   int bl;           // boundary lane: lanes below belong to slot A, the others to slot B (32: no slot B)
-  OuterSlot a, b;
-  bool first_tile;
+  OuterSlot a;      // the slot of the warp's lane 0
   double* part;     // the CTA's part of opart
+  // what the warp's slot A did in the round just finished (warp-uniform): set by pre_task, consumed by outer_fold
+  bool pending;
+  unsigned pend_l, pend_r, pend_par;
 };
 
 // Sum over the warp's columns of (a q)(m)^T: with the columns as the contraction index,
@@ -391,7 +392,8 @@ __device__ __forceinline__ void outer_addresses(OuterCtx& oc, unsigned stage, in
 }
 
 template <int K>
-__device__ __forceinline__ void outer_sums(const OuterCtx& oc, int lane, const double (&aq)[8], const double (&m)[8], int dbg = 0) {
+__device__ __forceinline__ void outer_sums(const OuterCtx& oc, unsigned row, int lane, const double (&aq)[8], const double (&m)[8],
+                                           int dbg = 0) {
 #ifdef B2P_DBG
   if (!(dbg & 64))
 #endif
@@ -444,54 +446,39 @@ __device__ __forceinline__ void outer_sums(const OuterCtx& oc, int lane, const d
     const unsigned e = (g & 3u) * 4u + (t & 1u) * 2u + (g < 4 ? 0u : 16u);
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-      sts_d2(oc.row + (k * 32 + e) * 8, K == 1 ? ca[0][0] + ca[1][0] : ca[k][0], K == 1 ? ca[0][1] + ca[1][1] : ca[k][1]);
+      sts_d2(row + (k * 32 + e) * 8, K == 1 ? ca[0][0] + ca[1][0] : ca[k][0], K == 1 ? ca[0][1] + ca[1][1] : ca[k][1]);
       if (oc.bl < 32)
-        sts_d2(oc.row + (K * 32 + k * 32 + e) * 8, K == 1 ? cb[0][0] + cb[1][0] : cb[k][0], K == 1 ? cb[0][1] + cb[1][1] : cb[k][1]);
+        sts_d2(row + (K * 32 + k * 32 + e) * 8, K == 1 ? cb[0][0] + cb[1][0] : cb[k][0], K == 1 ? cb[0][1] + cb[1][1] : cb[k][1]);
     }
   }
 }
 
-// The warp's rows are written: tell slot B's barrier (if that slot has a task), then wait for
-// slot A's warps and add slot A's rows into the CTA's part of opart.  Every warp that holds
-// columns of a slot with a task gets here in the same round; flags / ids: the lane's descriptor.
+// Slot A's sums of the round just finished -> the CTA's part of opart (top of the next round, or
+// after a tile's last round).  Warp-uniform; the rows were completed by the round's barrier.
 template <int K>
-__device__ __forceinline__ void outer_fold(const OuterCtx& oc, int lane, unsigned flags, unsigned id_l, unsigned id_r,
-                                           int outer_row, int dbg = 0) {
-  const unsigned fa = __shfl_sync(0xffffffffu, flags, 0), fb = __shfl_sync(0xffffffffu, flags, 31);
-  if (oc.bl < 32 && (fb & WF_LIVE)) {  // warp-uniform, and the same in every warp of that slot
-    __threadfence_block();
-    asm volatile("bar.arrive %0, %1;" ::"r"(oc.b.bar), "r"(oc.b.n_warps * 32) : "memory");
-  }
-  if (!(fa & WF_LIVE)) return;
-  const OuterSlot& sl = oc.a;
-  id_l = __shfl_sync(0xffffffffu, id_l, 0);
-  id_r = __shfl_sync(0xffffffffu, id_r, 0);
-  // the slot's rows are complete once all its warps are here (one warp: its own lanes)
-  if (sl.n_warps > 1) asm volatile("bar.sync %0, %1;" ::"r"(sl.bar), "r"(sl.n_warps * 32) : "memory");
-  else __syncwarp();
+__device__ __forceinline__ void outer_fold(OuterCtx& oc, int lane, bool first_tile, int outer_row, int dbg = 0) {
+  if (!oc.pending) return;
+  oc.pending = false;
 #ifdef B2P_DBG
-  if (dbg & 256) return;
+  if (dbg & 8) return;
 #endif
+  const OuterSlot& sl = oc.a;
+  const unsigned row0 = sl.row0 + oc.pend_par, rows1 = sl.rows1 + oc.pend_par;
   // A lane adds one PAIR of adjacent entries per step (16-byte loads and stores): pair j of the
   // slot's K * 16 sits at byte 16 j of every row; the slot's A warps take 32 pairs each per step.
-  // The tail of a round is a single warp's dependent instruction stream — few instructions, and
-  // the first two rows' loads issued together.
   for (int j = sl.r * 32 + lane; j < K * 16; j += sl.n_fold * 32) {
     const unsigned off = j * 16;
-    double2 v = lds_d2(sl.row0 + off);
-    const double2 x = lds_d2((sl.n_warps > 1 ? sl.rows1 : sl.row0) + off);
+    double2 v = lds_d2(row0 + off);
+    const double2 x = lds_d2((sl.n_warps > 1 ? rows1 : row0) + off);
     if (sl.n_warps > 1) { v.x += x.x; v.y += x.y; }
     for (int r = 2; r < sl.n_warps; ++r) {
-      const double2 y = lds_d2(sl.rows1 + (r - 1) * 2 * outer_row + off);
+      const double2 y = lds_d2(rows1 + (r - 1) * 2 * outer_row + off);
       v.x += y.x; v.y += y.y;
     }
     const int k = j >> 4, e = (j & 15) * 2;  // entries e, e + 1 of category k: 0-15 the left branch, 16-31 the right
-    double* gp = oc.part + ((size_t)(e < 16 ? id_l : id_r) * K + k) * 16 + (e & 15);
-#ifdef B2P_DBG
-    if (dbg & 128) { if (v.x == 1.2345e-300) gp[0] = v.x; continue; }
-#endif
+    double* gp = oc.part + ((size_t)(e < 16 ? oc.pend_l : oc.pend_r) * K + k) * 16 + (e & 15);
     // a branch is written once per tile: plain store for the CTA's first tile, then adds in tile order
-    if (oc.first_tile) *reinterpret_cast<double2*>(gp) = v;
+    if (first_tile) *reinterpret_cast<double2*>(gp) = v;
     else { atomicAdd(gp, v.x); atomicAdd(gp + 1, v.y); }
   }
 }
@@ -499,7 +486,7 @@ __device__ __forceinline__ void outer_fold(const OuterCtx& oc, int lane, unsigne
 template <typename T, int K, int CPT, bool OUTER = false>
 __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThread<T, CPT>& th, const TaskDesc& d, bool live,
                                          const unsigned (&code_l)[CPT], const unsigned (&code_r)[CPT], double& gl, double& gr,
-                                         const OuterCtx& oc = OuterCtx()) {
+                                         OuterCtx* ocp = nullptr, unsigned par = 0u) {
   T ql[CPT][4], qr[CPT][4];
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
@@ -558,7 +545,7 @@ __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThrea
       for (unsigned z = pinned((unsigned)!live); z != 0; --z)
 #pragma unroll
         for (int i = 0; i < 8; ++i) m[i] = 0.0;
-      outer_sums<K>(oc, th.lane, aq, m, p.dbg);
+      outer_sums<K>(*ocp, ocp->row + par * ocp->par, th.lane, aq, m, p.dbg);
     }
   }
   // pre-order partials of the internal children: u_c = P_c^T q_c (rescaled when tiny).  K == 1: a
@@ -584,10 +571,12 @@ __device__ __forceinline__ void pre_task(const WalkParams<T>& p, const WalkThrea
     }
   }
   if constexpr (OUTER) {
-#ifdef B2P_DBG
-    if (p.dbg & 8) return;
-#endif
-    outer_fold<K>(oc, th.lane, d.flags, d.id_l, d.id_r, p.outer_row, p.dbg);
+    // slot A's task of this round (lane 0 always holds a column of slot A): folded at the top of the next round
+    const unsigned fa = __shfl_sync(0xffffffffu, d.flags, 0);
+    ocp->pending = (fa & WF_LIVE) != 0;
+    ocp->pend_l = __shfl_sync(0xffffffffu, d.id_l, 0);
+    ocp->pend_r = __shfl_sync(0xffffffffu, d.id_r, 0);
+    ocp->pend_par = par * ocp->par;
   }
 }
 
@@ -697,10 +686,10 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
   if constexpr (OUTER) {
     const int w0 = warp * 32, sa = w0 / p.ts, end_a = (sa + 1) * p.ts;
     const bool has_b = end_a < w0 + 32 && sa + 1 < p.wn;
-    auto slot = [&](int sx, int ln) {
+    auto slot = [&](int sx) {
       OuterSlot o;
       const int wf = (sx * p.ts) / 32, wl = ((sx + 1) * p.ts - 1) / 32, wa = (sx * p.ts + 31) / 32;  // wa: first warp with A = sx
-      o.n_warps = wl - wf + 1; o.n_fold = wl - wa + 1; o.r = warp - wa; o.bar = 1 + sx; o.lane = ln;
+      o.n_warps = wl - wf + 1; o.n_fold = wl - wa + 1; o.r = warp - wa;
       // the first warp holds the slot's first columns as its A columns only if the slot starts on its lane 0
       o.row0 = sbase + p.off_outer + (2 * wf + ((sx * p.ts) % 32 ? 1 : 0)) * p.outer_row;
       o.rows1 = sbase + p.off_outer + 2 * (wf + 1) * p.outer_row;
@@ -709,8 +698,9 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
     outer_addresses<K>(oc, sbase + p.off_ostage + warp * 4096, lane);
     oc.row = sbase + p.off_outer + 2 * warp * p.outer_row;
     oc.bl = has_b ? end_a - w0 : 32;
-    oc.a = slot(min(sa, p.wn - 1), 0);
-    oc.b = slot(min(sa + 1, p.wn - 1), 31);
+    oc.a = slot(min(sa, p.wn - 1));
+    oc.par = 2 * first_copy_warp * p.outer_row;
+    oc.pending = false;
     oc.part = p.opart + (size_t)blockIdx.x * p.n_branches * (K * 16);
   }
   unsigned phase_bits = 0;
@@ -761,6 +751,9 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
       long long* trow = tr ? p.trace + ((t ? 1 : 0) * (long long)R + q) * 8 : nullptr;
       if (tr) trow[0] = clock64();
 #endif
+      // outer-product mode: the previous round's sums of the warp's slot go out while the operands arrive
+      if constexpr (OUTER)
+        if (!copier) outer_fold<K>(oc, lane, first_tile, p.outer_row, p.dbg);
       mbar_wait(bar0 + 8 * st, (phase_bits >> st) & 1u);
       phase_bits ^= 1u << st;
 #ifdef B2P_TRACE_CLOCKS
@@ -848,8 +841,7 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
             post_task<T, K, CPT>(p, th, d, live, root_round, scount, col, code_l, code_r, ga);
             if (live && is_root) sts_d2(gslot, ga, 0.0);
           } else {
-            oc.first_tile = first_tile;
-            pre_task<T, K, CPT, OUTER>(p, th, d, live, code_l, code_r, ga, gb2, oc);
+            pre_task<T, K, CPT, OUTER>(p, th, d, live, code_l, code_r, ga, gb2, &oc, (unsigned)par);
             if (!OUTER && live) sts_d2(gslot, ga, gb2);
           }
         }
@@ -878,6 +870,8 @@ __global__ void __launch_bounds__(NT, NT <= 256 ? 2 : 1) walk_kernel(const __gri
       // (the last round leaves nothing to store: the root's post-order task writes no message,
       //  and a pre-order partial is stored only when a later round loads it back)
       asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    } else if constexpr (OUTER) {
+      outer_fold<K>(oc, lane, first_tile, p.outer_row, p.dbg);  // the tile's last round
     }
     __syncthreads();
   }

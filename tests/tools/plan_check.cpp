@@ -56,7 +56,7 @@ int main(int argc, char** argv) {
   if (!plan_geometry(N, ct * 148, K, elem, 148, smem, nt, ct, depth, outer ? 3 : 2, cpt, g, outer)) FAIL("geometry");
   if (outer) {
     if (g.ts < 32 || g.ts % K || g.cpt != 1 || !g.outer || g.ts < g.ct || (g.ts != g.ct && g.ts != 32)) FAIL("outer mode: threads per slot");
-    const int rows_end = g.off_outer + 2 * (g.nt / 32 - g.n_copy_warps) * g.outer_row;
+    const int rows_end = g.off_outer + 4 * (g.nt / 32 - g.n_copy_warps) * g.outer_row;
     if (g.outer_row != K * 32 * 8 || g.off_outer < g.off_scount + g.ct * 4 || rows_end > g.off_ostage ||
         g.off_ostage % 16 || g.off_ostage + (g.nt / 32 - g.n_copy_warps) * 4096 > g.off_freq)
       FAIL("outer mode: rows overlap their neighbours");
