@@ -479,7 +479,8 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
     if (!getenv("B2P_NP")) n_copy = 2;
   }
   if (outer) {  // one column per thread (the 4x4 products live in registers), 512 threads, warp-aligned slots
-    nt_force = 512; n_copy = 3; cpt = 1; h->ctas_per_sm = 1;
+    nt_force = 512; cpt = 1; h->ctas_per_sm = 1;
+    if (!getenv("B2P_NP")) n_copy = 3;
     smem_budget = (size_t)prop.sharedMemPerBlockOptin - 1024;
   }
   bool planned = plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, ct_force, depth, n_copy, cpt, h->wg, outer);
