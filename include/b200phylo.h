@@ -162,15 +162,19 @@ int b2p_set_gradient_operator(b2p_instance* h, const double* h_op, const double*
 
 /* All of G in ONE evaluation.  An instance created with B2P_FLAG_OUTER_PRODUCTS in
  * b2p_config.flags (4 states, fp64, 1 or 4 rate categories) runs the walk with one column per
- * thread and warp-aligned tasks; b2p_branch_outer_products then also sums, in the pre-order
- * pass, the two 4x4 outer products of every task over its columns (warp shuffles, then one
- * shared-memory row per warp, folded a round later like the branch gradient) and writes
+ * thread; b2p_branch_outer_products then also sums, in the pre-order pass, the two 4x4 outer
+ * products of every task over its columns — per warp on the fp64 tensor cores (the columns are
+ * the contraction index of an m8n8k4 product), per task by adding the warps' shared-memory rows
+ * at the top of the next round, per evaluation by a reduction over CTAs — and writes
  *     d_outer [K][2N-2][4][4]:  G_{b,k}[i][j] = sum_p (w_p / L_p) c_k q_{b,k,i} m_{b,k,j}
- * next to logL and (if d_grad is not NULL) the branch gradient.  Such an instance still serves
- * b2p_loglik / b2p_loglik_grad, a few percent slower than a default one (one column per
- * thread).  Replaces the 16 K evaluations of b2p_set_gradient_operator; same reference rows:
- * torchtree differentiates these parameters by autograd of the whole recursion
- * (/root/reference/modules/micro.nf:52, /root/reference/plot.Rmd:305). */
+ * next to logL and (if d_grad is not NULL) the branch gradient, which is then contracted from G
+ * (sum_k r_k <Q, G_{b,k}>: this walk leaves the q.(Q m) numerators out).  Costs 1.7-2.0x a
+ * b2p_loglik_grad of a default instance.  Such an instance still serves b2p_loglik /
+ * b2p_loglik_grad, about a third slower than a default one (one column per thread).  Replaces
+ * the 16 K evaluations of b2p_set_gradient_operator; same reference rows: torchtree
+ * differentiates these parameters by autograd of the whole recursion
+ * (/root/reference/modules/micro.nf:52, /root/reference/plot.Rmd:305).  Sums are added in a
+ * fixed order: results are bit-identical from call to call. */
 #define B2P_FLAG_OUTER_PRODUCTS 1
 int b2p_branch_outer_products(b2p_instance* h, const double* d_bl, double* d_logl, double* d_grad,
                               double* d_outer, void* cuda_stream);
