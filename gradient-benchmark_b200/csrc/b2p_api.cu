@@ -509,7 +509,10 @@ int b2p_create(const b2p_config* cfg, b2p_instance** out) {
   if (planned && !getenv("B2P_DEPTH") && 3 * h->wg.frame_bytes <= 48 * 1024) {
     WalkGeometry g2;
     if (plan_geometry(N, (int)n_cols, K, (int)es, h->n_sms * h->ctas_per_sm, smem_budget, nt_force, h->wg.ct, 2, h->wg.n_copy_warps, cpt, g2, outer) &&
-        g2.wn == h->wg.wn)
+        g2.wn == h->wg.wn &&
+        // outer-product mode gives ~100 KB to staging and sum rows: with fewer than ~5.5 pool blocks per
+        // slot the third frame costs more rounds than the hidden latency saves (flu shape: 0.700 -> 0.686 ms)
+        !(outer && 2 * g2.n_pool < 11 * g2.wn))
       h->wg = g2;
   }
   if (!planned) {
