@@ -412,6 +412,17 @@ __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, 
   copy_rows_async(A1, p.Q, SP, kr, cp);
   copy_rows_async(A2, p.P + (size_t)c * SP * SP, SP, kr, cp);
   level_wait();  // the messages come from the post-order launch, the previous one
+  // What does not depend on the parent's flag is requested BEFORE waiting for it: the sibling's
+  // message (into registers) and, towards L2, the child's own message, which is read after the
+  // products in the accumulator layout (a 16-byte piece of every row per thread).
+  double2 ms[2][DH], uu[2][DH];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) fetch_message(p, sib, col0 + cp, kr + 32 * h, sc0, sc1, ms[h]);
+  {
+    const double* gm = p.msg + ((size_t)(c - p.n_tips) * SP + g) * p.cols_pad + col0 + 8 * warp + 2 * tg;
+#pragma unroll
+    for (int mi = 0; mi < 8; ++mi) asm volatile("prefetch.global.L2 [%0];" ::"l"(gm + (size_t)8 * mi * p.cols_pad));
+  }
   // the parent's pre-order partial tile comes from an earlier block of this launch
   if (!is_root) {
     if (t == 0) tile_wait(p.done_pre + (size_t)(nd.v - p.n_tips) * p.n_tiles + tile, p.err);
@@ -419,11 +430,9 @@ __global__ void __launch_bounds__(DNT, 2) dense_pre_kernel(const DenseParams p, 
   }
   DENSE_STAMP(1);
   {
-    double2 ms[2][DH], uu[2][DH];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       const int k0 = kr + 32 * h;
-      fetch_message(p, sib, col0 + cp, k0, sc0, sc1, ms[h]);
       if (is_root) {
 #pragma unroll
         for (int u = 0; u < DH; ++u) {
