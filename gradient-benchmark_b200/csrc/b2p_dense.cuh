@@ -317,16 +317,24 @@ __global__ void __launch_bounds__(DNT, 3) dense_post_kernel(const DenseParams p,
   level_wait();  // P^T comes from the transition launch, the previous one
   if (!is_root) copy_rows_async(A, p.PT + (size_t)nd.v * SP * SP, SP, kr, cp);
   // the children's message tiles (internal children only: a tip's message is a column of P)
-  if (t == 0 && nd.l >= p.n_tips) tile_wait(p.done_post + (size_t)(nd.l - p.n_tips) * p.n_tiles + tile, p.err);
-  if (t == 32 && nd.r >= p.n_tips) tile_wait(p.done_post + (size_t)(nd.r - p.n_tips) * p.n_tiles + tile, p.err);
+  // a tip child's message (columns of P: the transition launch wrote them) does not depend on any
+  // flag: requested before the wait for the internal child's tile
+  double2 ml[2][DH], mr[2][DH];
+  const bool tip_l = nd.l < p.n_tips, tip_r = nd.r < p.n_tips;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    if (tip_l) fetch_message(p, nd.l, col0 + cp, kr + 32 * h, lc0, lc1, ml[h]);
+    if (tip_r) fetch_message(p, nd.r, col0 + cp, kr + 32 * h, rc0, rc1, mr[h]);
+  }
+  if (t == 0 && !tip_l) tile_wait(p.done_post + (size_t)(nd.l - p.n_tips) * p.n_tiles + tile, p.err);
+  if (t == 32 && !tip_r) tile_wait(p.done_post + (size_t)(nd.r - p.n_tips) * p.n_tiles + tile, p.err);
   __syncthreads();
   DENSE_STAMP(1);  // 0-1: codes, launch wait, dependency flags
   {
-    double2 ml[2][DH], mr[2][DH];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-      fetch_message(p, nd.l, col0 + cp, kr + 32 * h, lc0, lc1, ml[h]);
-      fetch_message(p, nd.r, col0 + cp, kr + 32 * h, rc0, rc1, mr[h]);
+      if (!tip_l) fetch_message(p, nd.l, col0 + cp, kr + 32 * h, lc0, lc1, ml[h]);
+      if (!tip_r) fetch_message(p, nd.r, col0 + cp, kr + 32 * h, rc0, rc1, mr[h]);
     }
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
