@@ -132,6 +132,41 @@ def loglik_and_gradient(triples, tip_partials, weights, bl, evec, ivec, evals, f
     return logl, grad
 
 
+def branch_outer_products(triples, tip_partials, weights, bl, evec, ivec, evals, freqs,
+                          rates, cat_weights) -> np.ndarray:
+    """G [K, 2N-2, S, S]:  G_{c,k} = sum_p (w_p / L_p) c_k q_c m_c^T  with  q_c = pre_v o (P_s post_s)
+    (everything outside branch c) and m_c = P_c post_c (the branch's message) — the per-branch sums
+    every gradient w.r.t. the substitution / site model is a contraction of (SURVEY.md §8(f) row 3;
+    b2p_branch_outer_products computes them on the GPU).  Same two passes as loglik_and_gradient;
+    the ratio is scale-free for the same reason.  Identities the tests use:
+    sum_k r_k <Q, G_{c,k}> = dlogL/dt_c  and  sum_{k,i} G_{c,k}[i][i] = sum_p w_p for every c."""
+    triples = np.asarray(triples)
+    rates = np.asarray(rates, dtype=np.float64)
+    cw = np.asarray(cat_weights, dtype=np.float64)
+    pm = transition_matrices(bl, evec, ivec, evals, rates)
+    post, _ = post_order(triples, tip_partials, pm)
+    n, p, s = tip_partials.shape
+    k = len(rates)
+    root = int(triples[-1, 0])
+    pre = np.empty((2 * n - 1, k, p, s))
+    pre[root] = np.broadcast_to(freqs, (k, p, s))
+    g = np.zeros((k, 2 * n - 2, s, s))
+    for v, l, r in triples[::-1]:
+        for c, sib in ((l, r), (r, l)):
+            msib = np.einsum("kij,kpj->kpi", pm[sib], post[sib])
+            qc = pre[v] * msib
+            mc = np.einsum("kij,kpj->kpi", pm[c], post[c])
+            den = np.einsum("k,kpi,kpi->p", cw, qc, mc)
+            with np.errstate(divide="ignore", invalid="ignore"):
+                a = np.where(den > 0, weights / den, 0.0)
+            g[:, c] = np.einsum("k,p,kpi,kpj->kij", cw, a, qc, mc)
+            pc = np.einsum("kij,kpi->kpj", pm[c], qc)
+            mx = pc.max(axis=(0, 2))
+            mx = np.where(mx > 0, mx, 1.0)
+            pre[c] = pc / mx[None, :, None]
+    return g
+
+
 def finite_difference(fn, bl, eps: float = 1e-6) -> np.ndarray:
     """Central differences of ``fn(bl) -> float`` (formulation C)."""
     bl = np.asarray(bl, dtype=np.float64)

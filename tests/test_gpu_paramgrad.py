@@ -145,6 +145,25 @@ def test_outer_products_for_every_kind_of_slot_boundary(k_cat, ct):
     eng.close()
 
 
+@pytest.mark.parametrize("n_tips,n_patterns,gamma", [(14, 60, True), (14, 60, False), (60, 700, True), (33, 5000, False)])
+def test_outer_products_match_the_cpu_oracle(n_tips, n_patterns, gamma):
+    """b2p_branch_outer_products against oracle.branch_outer_products (numpy, the analytic two passes
+    with q and m kept): 1e-10 of the largest entry of each branch's matrix."""
+    from b200phylo import paramgrad as pg
+    from oracle import oracle
+    base = make_workload("hky_g4_flu", n_tips=n_tips, n_patterns=n_patterns)
+    site = GammaSiteModel(0.6, 4) if gamma else ConstantSiteModel()
+    w = Workload("g", base.tree, base.patterns, GTR((1.3, 2.9, 0.7, 1.1, 3.4, 1.0), (0.31, 0.19, 0.22, 0.28)), site)
+    eng = make_engine(w)
+    bl = torch.tensor(w.tree.branch_lengths, dtype=torch.float64, device="cuda")
+    got = pg.branch_outer_products(eng, bl, one_pass=True).cpu().numpy()
+    want = oracle.branch_outer_products(w.tree.post_triples, w.patterns.partials(), w.patterns.weights, w.tree.branch_lengths,
+                                        *w.eigen_args())
+    scale = np.abs(want).max(axis=(2, 3), keepdims=True)
+    assert np.max(np.abs(got - want) / scale) < 1e-10
+    eng.close()
+
+
 def test_outer_products_unsupported_shapes_say_so():
     from b200phylo.engine import Engine, EngineError
     with pytest.raises(EngineError, match="OUTER_PRODUCTS"):

@@ -224,3 +224,25 @@ def test_dense_c_oracle_matches_numpy_oracle():
     lo, _ = c_oracle.dense_loglik_and_gradient(w.tree.post_triples, codes, w.patterns.weights, w.tree.branch_lengths, *w.eigen_args(),
                                                want_grad=False, n_threads=1)
     assert abs(lo - ld) <= 1e-13 * abs(ld)
+
+
+def test_branch_outer_products_identities():
+    """oracle.branch_outer_products: contracting G with r_k Q gives the branch gradient, its traces
+    sum to the number of sites (sum_k c_k q.m = L), and it follows the analytic two-pass gradient's
+    partials — for one and four categories, with ambiguity codes in the tips."""
+    from b200phylo.sitemodel import ConstantSiteModel, GammaSiteModel
+    from b200phylo.substitution import GTR
+    from b200phylo.workloads import Workload, make_workload
+    from oracle import oracle
+    for site in (ConstantSiteModel(), GammaSiteModel(0.6, 4)):
+        base = make_workload("hky_g4_flu", n_tips=14, n_patterns=60)
+        w = Workload("g", base.tree, base.patterns, GTR((1.3, 2.9, 0.7, 1.1, 3.4, 1.0), (0.31, 0.19, 0.22, 0.28)), site)
+        args = (w.tree.post_triples, w.patterns.partials(), w.patterns.weights, w.tree.branch_lengths, *w.eigen_args())
+        g = oracle.branch_outer_products(*args)
+        _, grad = oracle.loglik_and_gradient(*args)
+        e = w.eigen_args()
+        q = oracle.q_from_eigen(e[0], e[1], e[2])
+        rates = np.asarray(w.site_model.rates)
+        assert g.shape == (len(rates), 2 * w.n_tips - 2, 4, 4)
+        np.testing.assert_allclose(np.einsum("k,ij,kbij->b", rates, q, g), grad, rtol=1e-11, atol=1e-9)
+        np.testing.assert_allclose(np.einsum("kbii->b", g), np.full(2 * w.n_tips - 2, w.patterns.weights.sum()), rtol=1e-12)
