@@ -209,14 +209,30 @@ class TreeLikelihoodParameterFunction(torch.autograd.Function):
         out = torch.empty(1 + eng.n_branches, dtype=torch.float64, device=dev)
         g = torch.empty(eng.n_categories, eng.n_branches, 4, 4, dtype=torch.float64, device=dev)
         stream = torch.cuda.current_stream(dev).cuda_stream
-        eng.branch_outer_products(bl.data_ptr(), out.data_ptr(), out.data_ptr() + 8, g.data_ptr(), stream)
+        one_pass = eng.supports_outer_products()
+        if one_pass:
+            eng.branch_outer_products(bl.data_ptr(), out.data_ptr(), out.data_ptr() + 8, g.data_ptr(), stream)
+        else:
+            # other category counts: the outer products entry by entry (16 K evaluations with
+            # b2p_set_gradient_operator), then logL and the branch gradient
+            from .paramgrad import branch_outer_products
+            g = branch_outer_products(eng, bl, one_pass=False)
+            eng.loglik_grad_device(bl.data_ptr(), out.data_ptr(), out.data_ptr() + 8, stream)
         if model.world_size > 1:
             # pattern shards: logL, the branch gradient and the outer products are sums over patterns
             # (the outer-products instance is not peer-attached: one NCCL all-reduce each)
             allreduce_sum_(out, model.group)
             allreduce_sum_(g, model.group)
-        mg = torch.empty(20 + eng.n_categories, dtype=torch.float64, device=dev)
-        eng.model_gradients(bl.data_ptr(), g.data_ptr(), int(model.tree_model.post_triples[-1][1]), mg.data_ptr(), stream)
+        root_child = int(model.tree_model.post_triples[-1][1])
+        if one_pass:
+            mg = torch.empty(20 + eng.n_categories, dtype=torch.float64, device=dev)
+            eng.model_gradients(bl.data_ptr(), g.data_ptr(), root_child, mg.data_ptr(), stream)
+        else:  # ... and the contraction with dP/d(Q, rates) by torch (matrix exponentials of 4x4 matrices)
+            from .paramgrad import surrogate
+            with torch.enable_grad():
+                leaves = [x.detach().to(dev).requires_grad_(True) for x in (q, freqs, rates)]
+                grads = torch.autograd.grad(surrogate(g, bl, *leaves, root_child), leaves, allow_unused=True)
+            mg = torch.cat([(gx if gx is not None else torch.zeros_like(x)).reshape(-1) for gx, x in zip(grads, leaves)])
         ctx.save_for_backward(out[1:], mg)
         ctx.in_devices = (branch_lengths.device, q.device, freqs.device, rates.device)
         ctx.in_dtype = branch_lengths.dtype
@@ -336,8 +352,10 @@ class TreeLikelihoodModel:
     def _call_with_model_parameters(self) -> torch.Tensor:
         """A substitution- or site-model parameter asks for a gradient: one pass that also returns
         the per-branch outer products (``TreeLikelihoodParameterFunction``)."""
-        if not self.engine.supports_outer_products():
-            raise EngineError("gradients w.r.t. model parameters need 4 states and 1 or 4 rate categories")
+        if self.engine.n_states != 4:
+            raise EngineError("gradients w.r.t. model parameters are built for 4-state models")
+        if self.world_size > 1 and self.fused_allreduce and not self.engine.supports_outer_products():
+            raise EngineError("gradients w.r.t. model parameters on pattern shards need 1 or 4 rate categories")
         self._refresh_model()
         dev = torch.device(f"cuda:{self.engine.device}")
         sm, st = self.subst_model, self.site_model

@@ -202,7 +202,7 @@ def test_gamma_shape_gradient_by_chain_rule():
     eng.close()
 
 
-@pytest.mark.parametrize("where,site", [("cuda", "weibull"), ("cpu", "weibull"), ("cuda", "constant")])
+@pytest.mark.parametrize("where,site", [("cuda", "weibull"), ("cpu", "weibull"), ("cuda", "constant"), ("cuda", "weibull3")])
 def test_tree_likelihood_model_differentiates_model_parameters(where, site):
     """The plugin surface: ``TreeLikelihoodModel`` with ``DifferentiableGTR`` / a Weibull site model
     whose parameters are tensors — ``model().backward()`` fills the gradients w.r.t. branch
@@ -211,7 +211,11 @@ def test_tree_likelihood_model_differentiates_model_parameters(where, site):
     from b200phylo import paramgrad as pg
     from b200phylo.diffmodels import DifferentiableGTR, DifferentiableWeibullSiteModel
     from b200phylo.treelikelihood import Parameter, TreeLikelihoodModel, UnrootedTreeModel
+    n_cat = {"weibull": 4, "weibull3": 3, "constant": 1}[site]  # 3 categories: no one-pass kernel, the operator route
     w, exch0, pi0 = _case("gtr", 40, 300, site == "weibull")
+    if site == "weibull3":
+        from b200phylo.sitemodel import WeibullSiteModel
+        w = Workload("gtr", w.tree, w.patterns, w.subst_model, WeibullSiteModel(0.8, 3))
     tree = w.tree
 
     def leaves(device):
@@ -220,9 +224,9 @@ def test_tree_likelihood_model_differentiates_model_parameters(where, site):
 
     ex, fr, shape, bl = leaves(where)
     subst = DifferentiableGTR("gtr", Parameter("gtr.rates", ex), Parameter("gtr.freqs", fr))
-    site_model = DifferentiableWeibullSiteModel("site", Parameter("shape", shape), 4) if site == "weibull" else ConstantSiteModel()
+    site_model = DifferentiableWeibullSiteModel("site", Parameter("shape", shape), n_cat) if n_cat > 1 else ConstantSiteModel()
     m = TreeLikelihoodModel("like", w.patterns, UnrootedTreeModel("tree", tree, bl), subst, site_model)
-    assert [p.id for p in m.parameters()][-3 if site == "weibull" else -2:][:2] == ["gtr.rates", "gtr.freqs"]
+    assert [p.id for p in m.parameters()][-3 if n_cat > 1 else -2:][:2] == ["gtr.rates", "gtr.freqs"]
     logl = m()
     assert logl.device.type == where
     (3.0 * logl).backward()
@@ -230,16 +234,16 @@ def test_tree_likelihood_model_differentiates_model_parameters(where, site):
     oex, ofr, oshape, obl = leaves("cpu")
     f = ofr / ofr.sum()
     q = pg.q_matrix(oex, f)
-    if site == "weibull":
-        orates = DifferentiableWeibullSiteModel(None, oshape, 4).rates_tensor()
-        weights = np.full(4, 0.25)
+    if n_cat > 1:
+        orates = DifferentiableWeibullSiteModel(None, oshape, n_cat).rates_tensor()
+        weights = np.full(n_cat, 1.0 / n_cat)
     else:
         orates, weights = torch.ones(1, dtype=torch.float64), np.ones(1)
     ll = param_oracle.log_likelihood(tree.post_triples, w.patterns.partials(), w.patterns.weights, obl, q, f, orates, weights)
     (3.0 * ll).backward()
     assert rel_err(float(logl.detach()), float(ll.detach())) < 1e-10
     pairs = [("exchangeabilities", ex.grad, oex.grad), ("frequencies", fr.grad, ofr.grad), ("branch lengths", bl.grad, obl.grad)]
-    if site == "weibull":
+    if n_cat > 1:
         pairs.append(("shape", shape.grad, oshape.grad))
     for name, got, want in pairs:
         assert got is not None and got.device.type == where, name
