@@ -27,7 +27,8 @@ import numpy as np
 import torch
 
 from .alignment import Alignment, SitePattern, compress_alignment
-from .diffmodels import DifferentiableGTR, DifferentiableHKY, DifferentiableWeibullSiteModel, is_differentiable
+from .diffmodels import (DifferentiableGammaSiteModel, DifferentiableGTR, DifferentiableHKY,
+                         DifferentiableWeibullSiteModel, is_differentiable)
 from .engine import Engine, EngineError
 from .parallel import allreduce_sum_, attach_peers, rank_world, shard_bounds
 from .sitemodel import ConstantSiteModel, GammaSiteModel, WeibullSiteModel
@@ -540,6 +541,8 @@ def _site_model_from_json(spec, dic=None):
         return ConstantSiteModel()
     if kind == "WeibullSiteModel" and isinstance(spec.get("shape"), (str, dict)):
         return DifferentiableWeibullSiteModel(spec.get("id"), _parameter_from_json(spec["shape"], dic), int(spec.get("categories", 4)))
+    if kind == "GammaSiteModel" and isinstance(spec.get("shape"), (str, dict)):
+        return DifferentiableGammaSiteModel(spec.get("id"), _parameter_from_json(spec["shape"], dic), int(spec.get("categories", 4)))
     if kind in ("GammaSiteModel", "WeibullSiteModel"):
         shape = float(_values_from_json(spec.get("shape", 0.5), dic)[0])
         if kind == "WeibullSiteModel":

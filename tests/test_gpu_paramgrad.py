@@ -265,3 +265,26 @@ def test_tree_likelihood_model_differentiates_model_parameters(where, site):
     m().backward()
     assert bl.grad is not None and bl.grad.shape == obl.shape
     m.close()
+
+
+def test_gamma_shape_through_the_model_object():
+    """``DifferentiableGammaSiteModel``: ``model().backward()`` leaves dlogL/dalpha on the shape —
+    against a central difference of the model's own log-likelihood in alpha."""
+    from b200phylo.diffmodels import DifferentiableGammaSiteModel
+    from b200phylo.treelikelihood import Parameter, TreeLikelihoodModel, UnrootedTreeModel
+    w, _, _ = _case("hky", 30, 200, True)
+    alpha = torch.tensor([0.6], dtype=torch.float64, requires_grad=True)
+    bl = torch.tensor(w.tree.branch_lengths, dtype=torch.float64, device="cuda")
+    m = TreeLikelihoodModel("like", w.patterns, UnrootedTreeModel("tree", w.tree, bl), w.subst_model,
+                            DifferentiableGammaSiteModel("site", Parameter("alpha", alpha), 4))
+    m().backward()
+    got = float(alpha.grad)
+
+    def logl(a):
+        with torch.no_grad():
+            alpha[0] = a
+            return float(m())
+
+    fd = (logl(0.6 + 1e-4) - logl(0.6 - 1e-4)) / 2e-4
+    assert got == pytest.approx(fd, rel=1e-5)
+    m.close()

@@ -189,3 +189,23 @@ def test_differentiable_models_match_their_host_twins():
     assert isinstance(g, DifferentiableGTR) and g.parameters() == [dic["r"], dic["f"]]
     np.testing.assert_allclose(g.q_matrix(), GTR((1, 2, 1, 1, 2, 1), (0.3, 0.2, 0.2, 0.3)).q_matrix(), rtol=1e-14, atol=1e-16)
     assert isinstance(tl._subst_model_from_json({"type": "GTR", "rates": [1, 2, 1, 1, 2, 1], "frequencies": [0.3, 0.2, 0.2, 0.3]}), GTR)
+
+
+def test_differentiable_gamma_site_model():
+    """Gamma shape as a tensor: the rates of sitemodel.GammaSiteModel, d rates / d alpha by central
+    difference inside a custom autograd function (checked against a wider difference here)."""
+    import torch
+    from b200phylo import treelikelihood as tl
+    from b200phylo.diffmodels import DifferentiableGammaSiteModel, is_differentiable
+    from b200phylo.sitemodel import GammaSiteModel
+    alpha = tl.Parameter("alpha", torch.tensor([0.6], dtype=torch.float64, requires_grad=True))
+    m = DifferentiableGammaSiteModel("site", alpha, 4)
+    np.testing.assert_allclose(m.rates, GammaSiteModel(0.6, 4).rates, rtol=1e-15)
+    assert is_differentiable(m) and m.parameters() == [alpha]
+    c = torch.tensor([0.3, -1.0, 2.0, 0.5], dtype=torch.float64)
+    (m.rates_tensor() * c).sum().backward()
+    h = 1e-4
+    want = float(((GammaSiteModel(0.6 + h, 4).rates - GammaSiteModel(0.6 - h, 4).rates) / (2 * h) * c.numpy()).sum())
+    assert float(alpha.tensor.grad) == pytest.approx(want, rel=1e-6)
+    j = tl._site_model_from_json({"type": "GammaSiteModel", "shape": {"id": "a", "type": "Parameter", "tensor": [0.5]}, "categories": 4}, {})
+    assert isinstance(j, DifferentiableGammaSiteModel) and len(j.rates) == 4
