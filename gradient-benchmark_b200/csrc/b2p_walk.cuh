@@ -63,8 +63,9 @@ struct WalkParams {
   int off_outer, outer_row;   // outer-product mode: shared-memory rows of the compute warps, [2 parities][warps][2][K * 32] doubles
   int off_ostage;             // outer-product mode: [warps] 4 KB staging rows of the tensor-core sums
   long long* trace;           // debug build (-DB2P_TRACE_CLOCKS): [2][rounds][8] clock stamps of CTA 0
-  int dbg;                    // debug build (-DB2P_DBG): 1 skip the fold, 2 skip the stores, 4 skip the tasks, 8 skip the
-                              // outer products' fold, 16 skip their sums (timing experiments)
+  int dbg;                    // debug build (-DB2P_DBG): 1 skip the fold, 2 skip the stores, 4 skip the tasks; outer-product
+                              // mode: 8 skip its fold, 16 skip its sums, 32 its tensor-core products only, 64 its staging
+                              // stores only (timing experiments: results are wrong by design)
   T q[16];
   double freqs[4];
   double cat_w[kMaxCatW];
