@@ -7,12 +7,12 @@ and every variational run that estimates them differentiate the tree likelihood 
 by autograd of the whole pruning recursion.  The classes here keep that surface — the model
 owns ``Parameter`` objects (``treelikelihood.Parameter``: an id and a tensor), ``parameters()``
 lists them — and ``TreeLikelihoodModel`` routes a call that needs their gradient through
-``b2p_branch_outer_products``: ONE evaluation returns logL, the branch gradient and the
-per-branch outer products G, and ``backward`` contracts G with dP/dtheta
-(``paramgrad.surrogate``: 4x4 algebra on 2N-2 matrices).
+``b2p_branch_outer_products`` + ``b2p_model_gradients``: ONE evaluation returns logL, the branch
+gradient and the per-branch outer products G, two small kernels contract G with dP/d(Q, rates)
+and the root prior, and torch chains the parameterisation (``q_tensor()``, ``rates_tensor()``).
 
 The engine itself consumes an eigen system (``eigen()``, host side, from the current values);
-the differentiable rate matrix (``q_tensor()``) is only used in ``backward``.
+the differentiable rate matrix is only the link between dlogL/dQ and the parameters.
 """
 from __future__ import annotations
 
